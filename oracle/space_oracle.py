@@ -1,0 +1,554 @@
+"""CPU restatement (numpy/scipy) of Orion's candidate-generation path.
+
+TEST INFRASTRUCTURE ONLY -- see ``oracle/__init__.py``.  The product package
+never imports this module; it exists to check the CUDA kernels and to be timed
+as the CPU baseline.
+
+Parity status
+-------------
+* sample / contains: **pinned** against the reference itself.  The reference
+  (``/root/reference/src/orion/algo/space.py``) is pure Python, so it is
+  imported in the build container by ``tests/golden/make_golden.py`` with a
+  replayed uniform stream and its outputs are committed as fixtures
+  (``tests/golden/*.npz``); ``tests/test_oracle_golden.py`` checks this module
+  against them bit for bit.
+* transform / reverse / dedup: **parity unpinned** -- they do not exist in
+  the reference snapshot (``src/orion/core/worker/primary_algo.py:13-14,42,55``
+  are TODOs; ``src/orion/core/worker/producer.py:42-52`` registers without any
+  dedup).  They follow SURVEY.md Appendix B (a restatement of upstream Orion's
+  ``transformer.py`` and set-semantics dedup) and are checked against
+  builder-authored known-answer tests only.
+
+Third-party arithmetic restated here (un-pinned ``numpy``/``scipy`` in the
+reference's ``setup.py:71``; versions in the build container numpy 2.3.5,
+scipy 1.18.1):
+
+* ``rv_generic.rvs``: ``vals = _rvs(...); vals = vals * scale + loc`` (rounded
+  multiply, then rounded add).
+* ``uniform_gen._rvs`` = ``random_state.uniform(0, 1, size)`` = the raw draw.
+* ``reciprocal_gen._ppf(q, a, b) = exp(log(a) + q*(log(b) - log(a)))`` fed by
+  ``random_state.uniform(size=size)`` (default ``rv_generic._rvs``).
+* ``norm_gen``: the reference draws with ``standard_normal`` (polar method, not
+  a function of one uniform), so under an injected uniform the restatement is
+  the inverse CDF ``ndtri(u)`` (== ``norm.ppf``); parity with the reference's
+  own normal draws is distributional only.
+* ``RandomState.choice(a, p=p)``: ``cdf = p.cumsum(); cdf /= cdf[-1];
+  idx = cdf.searchsorted(random_sample(size), side='right')``.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+from scipy import special as _sc
+from scipy.stats import distributions as _dists
+
+U32 = np.uint32
+U64 = np.uint64
+
+# --------------------------------------------------------------------------
+# Philox4x32-10 (Salmon et al., "Parallel random numbers: as easy as 1, 2, 3",
+# SC'11) -- the counter-based generator north_star names.  Not in the
+# reference (which uses MT19937 through numpy); defined here so the Philox
+# mode of the CUDA sampler can be checked bit for bit.
+# --------------------------------------------------------------------------
+PHILOX_M0 = 0xD2511F53
+PHILOX_M1 = 0xCD9E8D57
+PHILOX_W0 = 0x9E3779B9
+PHILOX_W1 = 0xBB67AE85
+
+
+def philox4x32_10(c0, c1, c2, c3, k0, k1):
+    """Vectorised Philox4x32-10.  All inputs broadcastable uint32 arrays."""
+    c0 = np.asarray(c0, dtype=U64)
+    c1 = np.asarray(c1, dtype=U64)
+    c2 = np.asarray(c2, dtype=U64)
+    c3 = np.asarray(c3, dtype=U64)
+    c0, c1, c2, c3 = np.broadcast_arrays(c0, c1, c2, c3)
+    k0 = int(k0) & 0xFFFFFFFF
+    k1 = int(k1) & 0xFFFFFFFF
+    mask = U64(0xFFFFFFFF)
+    sh = U64(32)
+    for _ in range(10):
+        p0 = U64(PHILOX_M0) * c0
+        p1 = U64(PHILOX_M1) * c2
+        hi0, lo0 = p0 >> sh, p0 & mask
+        hi1, lo1 = p1 >> sh, p1 & mask
+        n0 = hi1 ^ c1 ^ U64(k0)
+        n2 = hi0 ^ c3 ^ U64(k1)
+        c0, c1, c2, c3 = n0, lo1, n2, lo0
+        k0 = (k0 + PHILOX_W0) & 0xFFFFFFFF
+        k1 = (k1 + PHILOX_W1) & 0xFFFFFFFF
+    return (c0.astype(U32), c1.astype(U32), c2.astype(U32), c3.astype(U32))
+
+
+def u53(w0, w1):
+    """Two 32-bit words -> double in [0, 1) with 53 random bits
+    (the MT19937 ``genrand_res53`` construction numpy's ``random_sample``
+    uses): ``((w0 >> 5) * 2**26 + (w1 >> 6)) / 2**53``."""
+    a = (np.asarray(w0, dtype=U64) >> U64(5)).astype(np.float64)
+    b = (np.asarray(w1, dtype=U64) >> U64(6)).astype(np.float64)
+    return (a * 67108864.0 + b) / 9007199254740992.0
+
+
+def philox_uniform(seed: int, index, slot: int, attempt: int = 0):
+    """Uniform for (candidate ``index``, scalar slot ``slot``, ``attempt``).
+
+    Counter = (index_lo, index_hi, slot >> 1, attempt), key = (seed_lo,
+    seed_hi).  Even slots take words 0,1 of the block, odd slots words 2,3.
+    """
+    index = np.asarray(index, dtype=U64)
+    ilo = (index & U64(0xFFFFFFFF)).astype(U32)
+    ihi = (index >> U64(32)).astype(U32)
+    r = philox4x32_10(ilo, ihi, U32(slot >> 1), U32(attempt),
+                      seed & 0xFFFFFFFF, (seed >> 32) & 0xFFFFFFFF)
+    if slot & 1:
+        return u53(r[2], r[3])
+    return u53(r[0], r[1])
+
+
+# --------------------------------------------------------------------------
+# Space description
+# --------------------------------------------------------------------------
+@dataclass
+class DimSpec:
+    """One search-space dimension, as the reference constructs it.
+
+    ``Real(name, prior, *args, **kwargs)`` / ``Integer(...)`` /
+    ``Categorical(name, categories, **kwargs)`` --
+    reference ``space.py:64-108, 216-241, 365-390``.
+    """
+    name: str
+    kind: str                      # 'real' | 'integer' | 'categorical'
+    prior: Optional[str] = None    # scipy distribution name
+    args: tuple = ()
+    kwargs: dict = field(default_factory=dict)
+    shape: tuple = ()
+    low: float = -np.inf
+    high: float = np.inf
+    categories: tuple = ()
+    probs: tuple = ()
+
+    @property
+    def n_slots(self) -> int:
+        return int(np.prod(self.shape, dtype=np.int64)) if self.shape else 1
+
+
+def _parse(spec: DimSpec):
+    """scipy's own argument parsing (``space.py:193-195`` uses the same call)."""
+    dist = getattr(_dists, spec.prior)
+    args, loc, scale, _ = dist._parse_args_rvs(*spec.args, size=None, **spec.kwargs)
+    return dist, args, float(loc), float(scale)
+
+
+def dim_interval(spec: DimSpec) -> Tuple[float, float]:
+    """Half-open ``[low, high)`` bounds of a Real/Integer dimension.
+
+    Restates ``Dimension.interval`` (space.py:138-148), ``Real.interval``
+    (:243-254) and ``_Discrete.interval`` (:296-319) with ``alpha=1.0``; the
+    MRO of ``Integer(Real, _Discrete)`` floors the prior's interval first and
+    clips with the user's low/high afterwards.
+    """
+    dist = getattr(_dists, spec.prior)
+    lo, hi = dist.interval(1.0, *spec.args, **spec.kwargs)
+    lo, hi = float(lo), float(hi)
+    if spec.kind == 'integer':
+        ilo = np.floor(lo)
+        ihi = np.floor(hi)
+        if ihi < hi:
+            ihi += 1
+        lo, hi = float(ilo), float(ihi)
+    return (max(lo, spec.low), min(hi, spec.high))
+
+
+def categorical_cdf(probs: Sequence[float]) -> np.ndarray:
+    """Legacy ``RandomState.choice`` cdf: cumsum then divide by the last."""
+    cdf = np.asarray(probs, dtype=np.float64).cumsum()
+    cdf /= cdf[-1]
+    return cdf
+
+
+def slot_table(specs: Sequence[DimSpec]) -> List[Tuple[int, int]]:
+    """[(dim index, element index)] for every scalar slot, space order, C order."""
+    out = []
+    for d, spec in enumerate(specs):
+        for e in range(spec.n_slots):
+            out.append((d, e))
+    return out
+
+
+def _draw(spec: DimSpec, u: np.ndarray) -> np.ndarray:
+    """Inverse-CDF draw of one scalar slot from uniforms (Appendix A.1/A.2)."""
+    if spec.kind == 'categorical':
+        cdf = categorical_cdf(spec.probs)
+        return cdf.searchsorted(u, side='right').astype(np.int32)
+    dist, args, loc, scale = _parse(spec)
+    name = spec.prior
+    if scale == 0:
+        x = np.full(u.shape, loc, dtype=np.float64)
+    else:
+        if name == 'uniform':
+            base = u
+        elif name == 'reciprocal':
+            a, b = float(args[0]), float(args[1])
+            base = np.exp(np.log(a) + u * (np.log(b) - np.log(a)))
+        elif name == 'norm':
+            base = _sc.ndtri(u)
+        else:
+            raise NotImplementedError(name)
+        x = base * scale + loc          # rounded mul, then rounded add
+    if spec.kind == 'integer':
+        with np.errstate(invalid='ignore'):
+            return np.floor(x).astype(np.int64)   # space.py:294
+    return x
+
+
+def _in_bounds(spec: DimSpec, x: np.ndarray) -> np.ndarray:
+    """``low <= x < high`` (space.py:160-164); Categorical: valid index."""
+    if spec.kind == 'categorical':
+        return (x >= 0) & (x < len(spec.categories))
+    lo, hi = dim_interval(spec)
+    xf = x.astype(np.float64) if x.dtype != np.float64 else x
+    return (xf < hi) & (xf >= lo)
+
+
+def sample_from_uniform(specs: Sequence[DimSpec], U: np.ndarray):
+    """Single-attempt draw of every slot from an injected ``U[S][N]``.
+
+    Returns (columns, ok[N]); ``ok`` is the conjunction of the bounds checks
+    the reference applies in ``Real.sample`` (space.py:266).
+    """
+    U = np.asarray(U, dtype=np.float64)
+    n = U.shape[1]
+    cols = []
+    ok = np.ones(n, dtype=bool)
+    for s, (d, _) in enumerate(slot_table(specs)):
+        x = _draw(specs[d], U[s])
+        cols.append(x)
+        if specs[d].kind != 'categorical':
+            ok &= _in_bounds(specs[d], x)
+    return cols, ok
+
+
+def replay_reference_stream(specs: Sequence[DimSpec], n: int, stream: np.ndarray):
+    """Literal restatement of ``Space.sample`` consuming ONE uniform stream.
+
+    Dimension-major, sample-minor, <=4 attempts per Real/Integer sample with
+    the whole (shaped) value redrawn, ValueError after 4 misses -- reference
+    ``space.py:256-276, 456-484``; stream layout SURVEY Appendix A.3.
+    Python loop: small cases only.
+    """
+    pos = 0
+    per_dim = []
+    for spec in specs:
+        k = spec.n_slots
+        vals = []
+        for _ in range(n):
+            if spec.kind == 'categorical':
+                u = stream[pos:pos + k]
+                pos += k
+                vals.append(_draw(spec, u))
+                continue
+            nice = False
+            for _attempt in range(4):
+                u = stream[pos:pos + k]
+                pos += k
+                x = _draw(spec, u)
+                if bool(np.all(_in_bounds(spec, x))):
+                    nice = True
+                    vals.append(x)
+                    break
+            if not nice:
+                raise ValueError("Improbable bounds: (low={0}, high={1}). "
+                                 "Please make interval larger.".format(spec.low, spec.high))
+        per_dim.append(np.stack(vals, axis=1))      # [k][n]
+    cols = [row for block in per_dim for row in block]
+    return cols, pos
+
+
+def sample_philox(specs: Sequence[DimSpec], n: int, seed: int, base_index: int = 0):
+    """Philox-mode draw with the reference's <=4-attempt rejection.
+
+    Attempt ``a`` of dimension ``d`` for candidate ``i`` uses
+    ``philox_uniform(seed, i, slot, a)`` for each of the dimension's slots; the
+    whole dimension value is accepted iff every element is in bounds
+    (space.py:263-270).  Returns (columns, failed[N]); a True in ``failed`` is
+    the reference's ValueError("Improbable bounds").
+    """
+    index = np.arange(n, dtype=U64) + U64(base_index)
+    cols: List[np.ndarray] = []
+    failed = np.zeros(n, dtype=bool)
+    s0 = 0
+    for spec in specs:
+        k = spec.n_slots
+        dt = {'real': np.float64, 'integer': np.int64, 'categorical': np.int32}[spec.kind]
+        block = np.zeros((k, n), dtype=dt)
+        pending = np.ones(n, dtype=bool)
+        attempts = 1 if spec.kind == 'categorical' else 4
+        for a in range(attempts):
+            rows = np.nonzero(pending)[0]
+            if rows.size == 0:
+                break
+            vals = []
+            ok = np.ones(rows.size, dtype=bool)
+            for e in range(k):
+                u = philox_uniform(seed, index[rows], s0 + e, a)
+                x = _draw(spec, u)
+                vals.append(x)
+                if spec.kind != 'categorical':
+                    ok &= _in_bounds(spec, x)
+            # rejected rows keep the value of their last attempt (the device
+            # leaves it in place too); only accepted ones stop retrying
+            for e in range(k):
+                block[e, rows] = vals[e]
+            pending[rows[ok]] = False
+        failed |= pending
+        cols.extend(block)
+        s0 += k
+    return cols, failed
+
+
+def contains(specs: Sequence[DimSpec], cols: Sequence[np.ndarray]) -> np.ndarray:
+    """``point in space`` for N points at once (space.py:521-545 over
+    :150-164, :335-347, :415-426).  Integer columns may be passed as float64,
+    in which case the ``mod(x, 1) == 0`` test of ``Integer.__contains__``
+    applies."""
+    n = len(cols[0]) if len(cols) else 0
+    if not specs:
+        return np.zeros(n, dtype=bool)          # empty space -> False (:538-539)
+    ok = np.ones(n, dtype=bool)
+    for s, (d, _) in enumerate(slot_table(specs)):
+        spec = specs[d]
+        x = np.asarray(cols[s])
+        if spec.kind == 'integer' and x.dtype.kind == 'f':
+            with np.errstate(invalid='ignore'):
+                ok &= np.equal(np.mod(x, 1), 0)
+        ok &= _in_bounds(spec, x)
+    return ok
+
+
+# --------------------------------------------------------------------------
+# Transform chain.  PARITY UNPINNED.
+# --------------------------------------------------------------------------
+OP_IDENTITY = 0      # copy, dtype preserved
+OP_QUANTIZE = 1      # real -> integer (numpy.round -> int64)
+OP_TO_REAL = 2       # Reverse(Quantize): integer -> float64
+OP_ENUMERATE = 3     # categorical -> integer index (already an index here)
+OP_ONEHOT = 4        # Compose[Enumerate, OneHotEncode(k)]
+
+_REQ = {
+    'real':      {'real': OP_IDENTITY, 'integer': OP_TO_REAL, 'categorical': OP_ONEHOT},
+    'integer':   {'real': OP_QUANTIZE, 'integer': OP_IDENTITY, 'categorical': OP_ENUMERATE},
+    'numerical': {'real': OP_IDENTITY, 'integer': OP_IDENTITY, 'categorical': OP_ONEHOT},
+    None:        {'real': OP_IDENTITY, 'integer': OP_IDENTITY, 'categorical': OP_IDENTITY},
+}
+
+
+def required_ops(specs: Sequence[DimSpec], requirement) -> List[int]:
+    """Per-dimension transformer chosen by ``build_required_space`` (B.2)."""
+    return [_REQ[requirement][spec.kind] for spec in specs]
+
+
+def onehot_width(k: int) -> int:
+    """``OneHotEncode.infer_target_shape``: one column if k <= 2, else k."""
+    return 1 if k <= 2 else k
+
+
+def transform(specs: Sequence[DimSpec], requirement, cols: Sequence[np.ndarray],
+              quantize: str = 'round') -> List[np.ndarray]:
+    """Original columns -> transformed columns (B.1).  One-hot columns of a
+    slot are adjacent (trailing axis), slots in space order."""
+    ops = required_ops(specs, requirement)
+    out: List[np.ndarray] = []
+    for s, (d, _) in enumerate(slot_table(specs)):
+        x = np.asarray(cols[s])
+        op = ops[d]
+        if op in (OP_IDENTITY, OP_ENUMERATE):
+            out.append(x.copy())
+        elif op == OP_QUANTIZE:
+            q = np.round(x) if quantize == 'round' else np.floor(x)
+            out.append(q.astype(np.int64))
+        elif op == OP_TO_REAL:
+            out.append(x.astype(np.float64))
+        elif op == OP_ONEHOT:
+            k = len(specs[d].categories)
+            assert np.all((x >= 0) & (x < k))
+            if k <= 2:
+                out.append(x.astype(np.float64))
+            else:
+                for j in range(k):
+                    out.append((x == j).astype(np.float64))
+        else:
+            raise ValueError(op)
+    return out
+
+
+def reverse(specs: Sequence[DimSpec], requirement, tcols: Sequence[np.ndarray],
+            quantize: str = 'round') -> List[np.ndarray]:
+    """Transformed columns -> original columns (B.1 ``reverse``)."""
+    ops = required_ops(specs, requirement)
+    out: List[np.ndarray] = []
+    t = 0
+    for s, (d, _) in enumerate(slot_table(specs)):
+        op = ops[d]
+        if op in (OP_IDENTITY, OP_ENUMERATE):
+            out.append(np.asarray(tcols[t]).copy())
+            t += 1
+        elif op == OP_QUANTIZE:            # Quantize.reverse: cast to float
+            out.append(np.asarray(tcols[t]).astype(np.float64))
+            t += 1
+        elif op == OP_TO_REAL:             # Reverse(Quantize).reverse = Quantize.transform
+            x = np.asarray(tcols[t])
+            q = np.round(x) if quantize == 'round' else np.floor(x)
+            out.append(q.astype(np.int64))
+            t += 1
+        elif op == OP_ONEHOT:
+            k = len(specs[d].categories)
+            if k == 1:
+                out.append(np.zeros(len(tcols[t]), dtype=np.int32))
+                t += 1
+            elif k == 2:
+                out.append((np.asarray(tcols[t]) > 0.5).astype(np.int32))
+                t += 1
+            else:
+                block = np.stack([np.asarray(tcols[t + j]) for j in range(k)], axis=-1)
+                out.append(block.argmax(axis=-1).astype(np.int32))   # first max on ties
+                t += k
+        else:
+            raise ValueError(op)
+    return out
+
+
+# --------------------------------------------------------------------------
+# Row fingerprint + dedup.  PARITY UNPINNED.
+# --------------------------------------------------------------------------
+_M64 = (1 << 64) - 1
+
+
+def _splitmix64(x: int) -> int:
+    x = (x + 0x9E3779B97F4A7C15) & _M64
+    z = x
+    z = ((z ^ (z >> 30)) * 0xBF58476D1CE4E5B9) & _M64
+    z = ((z ^ (z >> 27)) * 0x94D049BB133111EB) & _M64
+    return z ^ (z >> 31)
+
+
+def slot_hash_keys(n_slots: int) -> np.ndarray:
+    """[S][4] uint64: (xor key A, odd multiplier A, xor key B, odd multiplier B)."""
+    out = np.zeros((n_slots, 4), dtype=U64)
+    for s in range(n_slots):
+        for j in range(4):
+            v = _splitmix64((4 * s + j + 1) * 0xD6E8FEB86659FD93 & _M64)
+            if j & 1:
+                v |= 1
+            out[s, j] = v
+    return out
+
+
+def _mul_hi_lo(x: np.ndarray, m: int):
+    """64x64 -> 128-bit product of a uint64 array with a scalar, via 32-bit limbs."""
+    mask = U64(0xFFFFFFFF)
+    sh = U64(32)
+    x0, x1 = x & mask, x >> sh
+    m0, m1 = U64(m & 0xFFFFFFFF), U64(m >> 32)
+    p00 = x0 * m0
+    p01 = x0 * m1
+    p10 = x1 * m0
+    p11 = x1 * m1
+    mid = (p00 >> sh) + (p01 & mask) + (p10 & mask)
+    lo = (p00 & mask) | ((mid & mask) << sh)
+    hi = p11 + (p01 >> sh) + (p10 >> sh) + (mid >> sh)
+    return hi, lo
+
+
+def _fmix64(x: np.ndarray) -> np.ndarray:
+    x = x ^ (x >> U64(33))
+    x = x * U64(0xFF51AFD7ED558CCD)
+    x = x ^ (x >> U64(33))
+    x = x * U64(0xC4CEB9FE1A85EC53)
+    return x ^ (x >> U64(33))
+
+
+def canonical_words(cols: Sequence[np.ndarray]) -> List[np.ndarray]:
+    """Each slot value as a 64-bit word: float64 bit pattern with -0.0 -> +0.0,
+    int64 as is, int32 sign-extended."""
+    words = []
+    for x in cols:
+        x = np.asarray(x)
+        if x.dtype == np.float64:
+            y = np.where(x == 0.0, 0.0, x)
+            words.append(y.view(U64))
+        else:
+            words.append(x.astype(np.int64).view(U64))
+    return words
+
+
+def fingerprint(cols: Sequence[np.ndarray]):
+    """128-bit row fingerprint as (lo, hi) uint64 arrays.
+
+    Two independent lanes; each is the wrapping sum over slots of
+    ``mum(word ^ key, mult)`` (``mum`` = hi64 ^ lo64 of the 128-bit product),
+    finished with murmur3's ``fmix64``.  ``lo`` is never 0 (0 marks an empty
+    hash-set slot).
+    """
+    S = len(cols)
+    keys = slot_hash_keys(S)
+    n = len(cols[0])
+    acc_a = np.zeros(n, dtype=U64)
+    acc_b = np.zeros(n, dtype=U64)
+    with np.errstate(over='ignore'):
+        for s, w in enumerate(canonical_words(cols)):
+            hi, lo = _mul_hi_lo(w ^ keys[s, 0], int(keys[s, 1]))
+            acc_a = acc_a + (hi ^ lo)
+            hi, lo = _mul_hi_lo(w ^ keys[s, 2], int(keys[s, 3]))
+            acc_b = acc_b + (hi ^ lo)
+        lo = _fmix64(acc_a ^ U64((S * 0x9E3779B97F4A7C15) & _M64))
+        hi = _fmix64(acc_b + U64((S * 0xC2B2AE3D27D4EB4F) & _M64))
+    lo = np.where(lo == 0, U64(1), lo)
+    return lo, hi
+
+
+def _row_keys(cols: Sequence[np.ndarray]) -> List[bytes]:
+    words = np.stack(canonical_words(cols), axis=1)      # [N][S]
+    return [row.tobytes() for row in words]
+
+
+class ExactHistory:
+    """Exact-row history set: the dedup contract of B.3 without hashing."""
+
+    def __init__(self):
+        self.rows = set()
+
+    def insert(self, cols: Sequence[np.ndarray]) -> None:
+        self.rows.update(_row_keys(cols))
+
+    def dedup(self, cols: Sequence[np.ndarray]) -> np.ndarray:
+        """keep[i] = row i not in history and no j < i in the batch equals it;
+        kept rows join the history."""
+        keys = _row_keys(cols)
+        keep = np.zeros(len(keys), dtype=bool)
+        for i, key in enumerate(keys):
+            if key not in self.rows:
+                self.rows.add(key)
+                keep[i] = True
+        return keep
+
+
+def dedup_fingerprints(history: set, lo: np.ndarray, hi: np.ndarray) -> np.ndarray:
+    """Same contract on fingerprints (what the device computes): first
+    occurrence by batch index wins; kept fingerprints are added to ``history``
+    (a Python set of (lo, hi) ints).  Vectorised through ``np.unique`` so it is
+    usable at 1e6-1e7 rows."""
+    n = len(lo)
+    packed = np.empty(n, dtype=[('lo', U64), ('hi', U64)])
+    packed['lo'] = lo
+    packed['hi'] = hi
+    _, first = np.unique(packed, return_index=True)
+    keep = np.zeros(n, dtype=bool)
+    for i in first:
+        key = (int(lo[i]), int(hi[i]))
+        if key not in history:
+            history.add(key)
+            keep[i] = True
+    return keep

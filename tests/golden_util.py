@@ -1,0 +1,40 @@
+"""Load the committed golden fixtures (made by tests/golden/make_golden.py
+from the unmodified reference) into oracle DimSpecs and column lists."""
+import json
+import os
+
+import numpy as np
+
+from oracle.space_oracle import DimSpec
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), 'golden')
+CASES = ['mixed_scalar', 'shaped', 'bounded_reject', 'loc_scale_kwargs']
+
+
+def specs_from_json(dims):
+    specs = []
+    for d in dims:
+        shape = tuple(d.get('shape') or ())
+        if d['kind'] == 'categorical':
+            cats = tuple(tuple(c) if isinstance(c, list) else c for c in d['categories'])
+            probs = tuple(d['probs']) if d.get('probs') else tuple(np.tile(1. / len(cats), len(cats)))
+            specs.append(DimSpec(d['name'], 'categorical', shape=shape, categories=cats, probs=probs))
+        else:
+            specs.append(DimSpec(d['name'], d['kind'], prior=d['prior'], args=tuple(d['args']),
+                                 kwargs=dict(d.get('kwargs', {})), shape=shape,
+                                 low=d.get('low', -np.inf), high=d.get('high', np.inf)))
+    return specs
+
+
+def load(name):
+    z = np.load(os.path.join(GOLDEN, name + '.npz'), allow_pickle=False)
+    dims = json.loads(str(z['spec']))
+    out = dict(dims=dims, specs=specs_from_json(dims), n=int(z['n']), stream=z['stream'])
+    if 'error' in z.files:
+        out['error'] = str(z['error'])
+        return out
+    out['consumed'] = int(z['consumed'])
+    out['cols'] = [z[k] for k in sorted(f for f in z.files if f.startswith('col'))]
+    out['probes'] = [z[k] for k in sorted(f for f in z.files if f.startswith('probe0') or f.startswith('probe1'))]
+    out['probe_verdict'] = z['probe_verdict']
+    return out
