@@ -1,0 +1,441 @@
+#!/usr/bin/env python
+"""Benchmark of the candidate-generation hot path (BASELINE.json metric).
+
+    python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
+    python bench.py --impl reference --gpus N --steps K ...  # CPU arm (oracle port of the reference path)
+
+One "step" = one pass of the whole path over one batch of synthetic candidates
+of the `mixed64` space: sample (Philox, fused bounds check and
+fingerprint) -> transform('real') -> reverse -> dedup against the history
+shard.  Per GPU a step processes CANDS_PER_GPU candidates against a history
+shard of HISTORY_PER_GPU rows; at 8 GPUs that is exactly BASELINE.json config 5
+(1e8 candidates vs 1e9-row history) with config 3's transform chain on top.
+10 % of each batch are planted duplicates of history rows and 1 % duplicates of
+earlier rows of the same batch (continuous dimensions never collide by chance).
+
+Prints ONE JSON line (rank 0).
+"""
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+CANDS_PER_GPU = 12_500_000
+HISTORY_PER_GPU = 125_000_000
+HISTORY_BASE = 1 << 40
+SEED = 20240005
+METRIC = "deduplicated candidates/sec (64-dim mixed space)"
+UNIT = "candidates/s"
+
+# algorithmic HBM bytes per candidate (SURVEY.md 8d / BASELINE.md section 5; fixed yard-sticks)
+BYTES_SAMPLE = 448
+BYTES_TRANSFORM = 448 + 1408
+BYTES_REVERSE = 1408 + 448
+BYTES_DEDUP = 16 + 32 + 16 + 4 + 4 + 1      # fp read, probe sector, insert, scratch w+r, keep
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=5)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
+    ap.add_argument('--cands', type=int, default=CANDS_PER_GPU, help='candidates per GPU per step')
+    ap.add_argument('--history', type=int, default=HISTORY_PER_GPU, help='history rows per GPU')
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--e2e-steps', type=int, default=2)
+    return ap.parse_args()
+
+
+# --------------------------------------------------------------------------
+# CPU arm: the oracle port, all host cores
+# --------------------------------------------------------------------------
+def _cpu_worker(job):
+    """One process: the whole path on `n` candidates with numpy (oracle port)."""
+    import numpy as np
+    from oracle import space_oracle as so
+    from tests.spec_util import specs_from_space  # noqa: F401  (kept importable on the box)
+    n, base, seed, n_hist = job
+    specs = _mixed64_specs()
+    hist_cols, _ = so.sample_philox(specs, n_hist, seed, base_index=HISTORY_BASE + base)
+    history = set(zip(*[x.tolist() for x in so.fingerprint(hist_cols)]))
+    t0 = time.perf_counter()
+    # planted duplicates: 10 % history counters, 1 % repeat an earlier counter
+    idx = np.arange(n, dtype=np.uint64) + np.uint64(base)
+    cols, failed = so.sample_philox(specs, n, seed, base_index=base)
+    dup = np.arange(n) % 10 == 3
+    for c, h in zip(cols, hist_cols):
+        c[dup] = h[np.arange(n)[dup] % n_hist]
+    ok = so.contains(specs, cols)
+    t = so.transform(specs, 'real', cols)
+    back = so.reverse(specs, 'real', t)
+    lo, hi = so.fingerprint(back)
+    keep = so.dedup_fingerprints(history, lo, hi)
+    dt = time.perf_counter() - t0
+    assert ok.all() and not failed.any() and len(idx) == n
+    return dt, int(keep.sum())
+
+
+def _mixed64_specs():
+    from oracle.space_oracle import DimSpec
+    import numpy as np
+    specs = []
+    for i in range(16):
+        specs.append(DimSpec('u%d' % i, 'real', prior='uniform', args=(-1, 2)))
+    for i in range(8):
+        specs.append(DimSpec('l%d' % i, 'real', prior='reciprocal', args=(1e-5, 1)))
+    for i in range(8):
+        specs.append(DimSpec('g%d' % i, 'real', prior='norm', args=(0, 1)))
+    for i in range(16):
+        specs.append(DimSpec('i%d' % i, 'integer', prior='uniform', args=(-100, 200)))
+    for i in range(16):
+        specs.append(DimSpec('c%d' % i, 'categorical', categories=tuple(range(8)),
+                             probs=tuple(np.tile(1. / 8, 8))))
+    return specs
+
+
+def cpu_path_rate(n_per_proc, procs, steps=1):
+    """candidates/s of the oracle port with `procs` processes; returns
+    (rate, total candidates, seconds)."""
+    import multiprocessing as mp
+    ctx = mp.get_context('fork')
+    jobs = [(n_per_proc, p * n_per_proc, SEED, max(n_per_proc // 4, 16)) for p in range(procs)]
+    total_t = 0.0
+    total_n = 0
+    with ctx.Pool(procs) as pool:
+        pool.map(_cpu_worker, [(256, 0, SEED, 64)] * procs)          # warm imports
+        for _ in range(steps):
+            t0 = time.perf_counter()
+            pool.map(_cpu_worker, jobs)
+            total_t += time.perf_counter() - t0
+            total_n += n_per_proc * procs
+    return total_n / total_t, total_n, total_t
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def run_reference(args):
+    """`--impl reference`: the reference's CPU path (numpy oracle port -- the
+    reference itself is pure Python and cannot travel to the GPU box), all host
+    cores, on bounded samples of the same workload."""
+    rank = int(os.environ.get('RANK', '0'))
+    if rank != 0:
+        return
+    procs = host_cores()
+    n_per_proc = 20000
+    for _ in range(args.warmup and 1):
+        cpu_path_rate(2000, procs)
+    rate, total_n, secs = cpu_path_rate(n_per_proc, procs, steps=args.steps)
+    sample = "%d candidates/step (%d per process x %d processes) of the mixed64 workload" % (
+        n_per_proc * procs, n_per_proc, procs)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * secs / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic", "config": workload_config(args, 1),
+        "cpu_baseline": {"value": rate, "unit": UNIT, "cores": procs, "kind": "port", "sample": sample},
+        "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line))
+
+
+def workload_config(args, world):
+    return {
+        "workload": "mixed64 (16 uniform + 8 loguniform + 8 normal Real, 16 uniform Integer, 16 Categorical x 8): "
+                    "sample + contains + transform('real') + reverse + fingerprint + dedup vs history",
+        "candidates_per_gpu_per_step": args.cands, "history_rows_per_gpu": args.history,
+        "planted_duplicates": "10% history rows, 1% earlier rows of the batch",
+        "parallelism": "dp%d (candidates sharded by counter; history hash set sharded by fingerprint)" % world,
+        "l2": "inputs larger than L2 (>= 5.6 GB touched per kernel)",
+    }
+
+
+# --------------------------------------------------------------------------
+# GPU arm
+# --------------------------------------------------------------------------
+class Clocks(object):
+    """nvidia-smi sampler running during the timed region."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu = gpu_index
+        self.f = tempfile.NamedTemporaryFile('w+', suffix='.csv', delete=False)
+        self.p = None
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(['nvidia-smi', '-i', str(self.gpu), '--query-gpu=' + self.Q,
+                                       '--format=csv,noheader,nounits', '-lms', '100'],
+                                      stdout=self.f, stderr=subprocess.DEVNULL)
+        except OSError:
+            self.p = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        if self.p is None:
+            return out
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        sm, mx, reasons, power = [], [], set(), []
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        for row in self.f.read().splitlines():
+            parts = [x.strip() for x in row.split(',')]
+            if len(parts) < 8:
+                continue
+            try:
+                sm.append(float(parts[1]))
+                mx.append(float(parts[2]))
+                power.append(float(parts[3]))
+            except ValueError:
+                continue
+            for name, val in zip(names, parts[4:8]):
+                if val.lower().startswith('active'):
+                    reasons.add(name)
+        self.f.close()
+        os.unlink(self.f.name)
+        if sm:
+            sm.sort()
+            out = {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": max(mx), "reasons": sorted(reasons),
+                   "samples": len(sm), "power_w_max": max(power) if power else None}
+        return out
+
+
+def run_b200(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from orion_b200 import spaces
+    from orion_b200.dist import ShardedHistory
+    from orion_b200.history import TrialHistory, table_slots_for
+    from orion_b200.transformer import build_required_space
+
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    rank = int(os.environ.get('RANK', '0'))
+    local_rank = int(os.environ.get('LOCAL_RANK', '0'))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device; there is no CPU fallback for the product path")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device('cuda', local_rank)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=dev)
+    assert world == args.gpus or world == 1, "launch with torchrun --nproc-per-node == --gpus"
+
+    n = args.cands
+    K, W = args.steps, args.warmup
+    total_steps = K + W + args.e2e_steps + 1
+    space = spaces.mixed64()
+    tspace = build_required_space('real', space)
+    compiled = tspace.compiled()
+
+    # ---- history shard: rows from counters [2^40 + rank*H, ...), fingerprints only
+    H = args.history
+    cap_rows = H + int(0.92 * n) * total_steps + n
+    history = TrialHistory(compiled, n_slots=table_slots_for(cap_rows, load=0.5))
+    sharded = ShardedHistory(history, device=dev)
+    chunk = n
+    hb = compiled.empty_columns(chunk)
+    done = 0
+    while done < H:
+        m = min(chunk, H - done)
+        b = compiled.sample(m, SEED, base_index=HISTORY_BASE + rank * H + done, with_mask=False,
+                            with_fingerprint=True, out=hb if m == chunk else None)
+        sharded.insert(b.fp, m)
+        done += m
+    torch.cuda.synchronize()
+    hist_rows0 = len(history)
+
+    # ---- per-step candidate counters with planted duplicates (synthetic input, built before timing)
+    def step_index(step):
+        g = torch.Generator(device=dev)
+        g.manual_seed(SEED + 1000 * step + rank)
+        base = (step * world + rank) * n
+        idx = torch.arange(base, base + n, dtype=torch.int64, device=dev)
+        r = torch.rand(n, generator=g, device=dev)
+        hist_pick = torch.randint(0, H * world, (n,), generator=g, device=dev, dtype=torch.int64) + HISTORY_BASE
+        idx = torch.where(r < 0.10, hist_pick, idx)
+        early = base + torch.randint(0, max(n // 100, 1), (n,), generator=g, device=dev, dtype=torch.int64)
+        idx = torch.where((r >= 0.10) & (r < 0.11), early, idx)
+        return idx
+
+    index_dev = [step_index(s) for s in range(W + K)]
+    batch = compiled.empty_columns(n)
+    tbatch = compiled.empty_columns(n, transformed=True)
+    back = compiled.empty_columns(n)
+    batch.keep = torch.empty(batch.n_stride, dtype=torch.uint8, device=dev)
+    kernel_names = ['sample', 'transform', 'reverse', 'dedup']
+    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(len(kernel_names) + 1)] for _ in range(K)]
+    launches = [0]
+
+    def one_step(step, events=None):
+        compiled.sample(n, SEED, index=index_dev[step], with_mask=True, with_fingerprint=True, out=batch)
+        if events:
+            events[1].record()
+        compiled.transform(batch, out=tbatch)
+        if events:
+            events[2].record()
+        compiled.reverse(tbatch, out=back)
+        if events:
+            events[3].record()
+        sharded.dedup(batch.fp, n, per_rank_n=n, keep=batch.keep, check=False)
+        if events:
+            events[4].record()
+        launches[0] += 5 if world == 1 else 8
+
+    def sync_all():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for s in range(W):
+        one_step(s)
+    sync_all()
+    launches[0] = 0
+    clocks = Clocks(local_rank)
+    if rank == 0:
+        clocks.start()
+    t_begin = torch.cuda.Event(enable_timing=True)
+    t_end = torch.cuda.Event(enable_timing=True)
+    t_begin.record()
+    for s in range(K):
+        ev[s][0].record()
+        one_step(W + s, ev[s])
+    t_end.record()
+    sync_all()
+    clock_info = clocks.stop() if rank == 0 else None
+    elapsed_ms = t_begin.elapsed_time(t_end)
+    if world > 1:
+        t = torch.tensor([elapsed_ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        elapsed_ms = float(t.item())
+    kept_last = int(batch.keep[:n].sum().item())
+    mask_ok = bool(batch.mask[:n].all().item())
+    round_trip_ok = bool(torch.equal(back.buf, batch.buf))
+    sharded._check_overflow(sharded._buffers(n)) if world > 1 else None
+    hist_rows1 = len(history)
+
+    per_kernel_ms = {}
+    for j, name in enumerate(kernel_names):
+        per_kernel_ms[name] = sum(ev[s][j].elapsed_time(ev[s][j + 1]) for s in range(K)) / K
+
+    # ---- end to end through the public API with host buffers
+    e2e = None
+    if args.e2e_steps > 0:
+        from orion_b200.algo.random import Random  # noqa: F401  (public entry; the column path below is what it calls)
+        host_idx = [torch.empty(n, dtype=torch.int64).pin_memory() for _ in range(args.e2e_steps + 1)]
+        for j, h in enumerate(host_idx):
+            h.copy_(step_index(W + K + j))
+        host_cols = torch.empty(batch.buf.numel(), dtype=torch.uint8).pin_memory()
+        host_keep = torch.empty(batch.n_stride, dtype=torch.uint8).pin_memory()
+        idx_dev = torch.empty(n, dtype=torch.int64, device=dev)
+
+        def e2e_step(j):
+            idx_dev.copy_(host_idx[j], non_blocking=True)                       # H2D: this step's input
+            compiled.sample(n, SEED, index=idx_dev, with_mask=True, with_fingerprint=True, out=batch)
+            compiled.transform(batch, out=tbatch)
+            compiled.reverse(tbatch, out=back)
+            sharded.dedup(batch.fp, n, per_rank_n=n, keep=batch.keep, check=False)
+            host_cols.copy_(back.buf, non_blocking=True)                        # D2H: the candidates
+            host_keep.copy_(batch.keep, non_blocking=True)                      # D2H: the verdicts
+            torch.cuda.current_stream().synchronize()
+            return int(host_keep[:n].sum())
+
+        e2e_step(0)
+        sync_all()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for j in range(args.e2e_steps):
+            e2e_step(1 + j)
+        e1.record()
+        sync_all()
+        e2e_ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([e2e_ms], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            e2e_ms = float(t.item())
+        e2e = {"value": world * n * args.e2e_steps / (e2e_ms * 1e-3), "unit": UNIT,
+               "h2d_bytes_per_step": int(n * 8), "d2h_bytes_per_step": int(host_cols.numel() + host_keep.numel()),
+               "steps": args.e2e_steps,
+               "api": "sample(index from pinned host) -> transform -> reverse -> dedup -> columns+keep to pinned host"}
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    peaks_path = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    if os.path.exists(peaks_path):
+        peak = float(json.load(open(peaks_path))['hbm_gbs'])
+        peak_src = "MEASURED_PEAKS.json hbm_gbs (of measured)"
+    else:
+        peak, peak_src = 6650.0, "B200_PROFILING.md fallback 6.65 TB/s (of fallback)"
+    algo_bytes = {'sample': BYTES_SAMPLE, 'transform': BYTES_TRANSFORM, 'reverse': BYTES_REVERSE, 'dedup': BYTES_DEDUP}
+    dominant = max(per_kernel_ms, key=per_kernel_ms.get)
+    achieved = algo_bytes[dominant] * n / (per_kernel_ms[dominant] * 1e-3) / 1e9
+    traffic = None
+    tpath = os.path.join(ROOT, 'profiles', 'traffic.json')
+    if os.path.exists(tpath):
+        traffic = json.load(open(tpath)).get(dominant)
+    kernels = {k: {"ms": per_kernel_ms[k], "algorithmic_GBps": algo_bytes[k] * n / (per_kernel_ms[k] * 1e-3) / 1e9,
+                   "frac_of_hbm_peak": algo_bytes[k] * n / (per_kernel_ms[k] * 1e-3) / 1e9 / peak}
+               for k in kernel_names}
+    step_bytes = sum(algo_bytes.values())
+    ms_per_step = elapsed_ms / K
+    line = {
+        "metric": METRIC, "value": world * n * K / (elapsed_ms * 1e-3), "unit": UNIT, "n_gpus": world,
+        "steps": K, "warmup": W, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": workload_config(args, world),
+        "roofline": {"bound": "hbm", "kernel": dominant, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                     "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                     "algorithmic_bytes_per_candidate": algo_bytes[dominant]},
+        "kernels": kernels,
+        "step_roofline": {"algorithmic_bytes_per_candidate": step_bytes,
+                          "achieved_GBps": step_bytes * n / (ms_per_step * 1e-3) / 1e9,
+                          "frac": step_bytes * n / (ms_per_step * 1e-3) / 1e9 / peak},
+        "e2e": e2e, "gpu_launches": launches[0], "clocks": clock_info,
+        "checks": {"kept_last_step": kept_last, "kept_frac_last_step": kept_last / float(n), "all_in_space": mask_ok,
+                   "reverse_of_transform_is_identity": round_trip_ok,
+                   "history_rows_before": hist_rows0, "history_rows_after": hist_rows1},
+    }
+    if not args.no_cpu_baseline and world == 1:
+        procs = host_cores()
+        n_per_proc = 20000
+        rate, total_n, secs = cpu_path_rate(n_per_proc, procs, steps=1)
+        line["cpu_baseline"] = {"value": rate, "unit": UNIT, "cores": procs, "kind": "port",
+                                "sample": "%d candidates (%d per process x %d processes, %.1f s) of the same workload "
+                                          "through the numpy oracle" % (total_n, n_per_proc, procs, secs)}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == 'reference':
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == '__main__':
+    main()

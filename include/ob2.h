@@ -1,0 +1,168 @@
+/* ob2.h -- C ABI of libob2: B200-native kernels for Orion's candidate-generation
+ * hot path (sample -> contains -> transform/reverse -> fingerprint -> dedup).
+ *
+ * The reference (DatCorno/orion) is pure Python and has NO FFI of its own; the
+ * boundary a maintainer binds is therefore new, and each entry point below
+ * cites the reference function it stands in for (paths relative to the
+ * reference checkout).  INTEGRATION.md shows the ctypes stub.
+ *
+ * Conventions
+ *   - every function returns 0 on success, a negative OB2_E* code otherwise;
+ *     ob2_last_error() gives the message for the calling thread.
+ *   - all data pointers are DEVICE pointers owned by the caller; the library
+ *     never allocates caller-visible memory.  Handles own only their small
+ *     descriptor tables.
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default
+ *     stream).  Calls are asynchronous on that stream unless stated.
+ *   - column sets: one contiguous block per batch; the column of scalar slot s
+ *     starts at byte offset  col_units[s] * n_stride  where col_units is the
+ *     running sum of element sizes (8 for Real/Integer, 4 for Categorical) and
+ *     n_stride >= n is a multiple of 32 (so every column is 128-byte aligned).
+ *     Per-candidate arrays (mask, keep, fingerprints, U) are n_stride long.
+ */
+#ifndef OB2_H_
+#define OB2_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define OB2_VERSION 1
+
+enum { OB2_OK = 0, OB2_EINVAL = -1, OB2_ECUDA = -2, OB2_ETOOBIG = -3, OB2_ENOMEM = -4 };
+
+/* dimension kinds: Real / Integer / Categorical, src/orion/algo/space.py:199,322,350 */
+enum { OB2_KIND_REAL = 0, OB2_KIND_INTEGER = 1, OB2_KIND_CATEGORICAL = 2 };
+
+/* priors with a device inverse CDF (scipy names the reference's DSL maps to,
+ * src/orion/core/io/space_builder.py:124-154).  CONST = scale == 0 (rvs returns loc). */
+enum { OB2_DIST_UNIFORM = 0, OB2_DIST_RECIPROCAL = 1, OB2_DIST_NORM = 2, OB2_DIST_CONST = 3 };
+
+/* per-slot transformer (build_required_space table) */
+enum {
+    OB2_OP_IDENTITY = 0,  /* copy, dtype kept                                     */
+    OB2_OP_QUANTIZE = 1,  /* Quantize: f64 -> i64 (round half-even, or floor)     */
+    OB2_OP_TO_REAL = 2,   /* Reverse(Quantize): i64 -> f64                        */
+    OB2_OP_ENUMERATE = 3, /* Enumerate: category index i32 -> i32                 */
+    OB2_OP_ONEHOT = 4     /* Compose[Enumerate, OneHotEncode(k)]: i32 -> k x f64  */
+};
+#define OB2_TFLAG_FLOOR 1 /* Quantize rounds with floor instead of rint */
+#define OB2_SLOT_DIM_LAST 1
+
+/* One scalar slot of the space (a dimension with shape contributes prod(shape)
+ * slots, C order).  Plain data, identical layout on host and device. */
+typedef struct ob2_slot_desc {
+    int32_t kind;      /* OB2_KIND_*                                              */
+    int32_t dist;      /* OB2_DIST_* (unused for categorical)                     */
+    int32_t dim_first; /* index of the first slot of this slot's dimension        */
+    int32_t flags;     /* OB2_SLOT_DIM_LAST on the last slot of a dimension       */
+    int32_t n_cats;    /* categorical: number of categories                       */
+    int32_t cdf_off;   /* categorical: offset of its cdf in the cdf table         */
+    int32_t col_units; /* byte offset of this column per unit of n_stride         */
+    int32_t t_op;      /* OB2_OP_*                                                */
+    int32_t t_units;   /* same as col_units, in the transformed column set        */
+    int32_t t_flags;   /* OB2_TFLAG_*                                             */
+    int32_t t_width;   /* number of transformed columns this slot expands to      */
+    int32_t reserved;  /* keeps the struct at 128 bytes                           */
+    double p0, p1;     /* reciprocal: log(a), log(b) - log(a)                     */
+    double loc, scale; /* x = base(u) * scale + loc  (scipy rv_generic.rvs)       */
+    double low, high;  /* accepted iff low <= x < high (space.py:160-164)         */
+    uint64_t hk[4];    /* fingerprint keys: xorA, multA(odd), xorB, multB(odd)    */
+} ob2_slot_desc;
+
+typedef struct ob2_space ob2_space;
+typedef struct ob2_set ob2_set;
+
+const char *ob2_last_error(void);
+int ob2_version(void);
+
+/* Compile a Space into device tables.  Replaces the per-call Python walk over
+ * `Space.values()` (src/orion/algo/space.py:483) and the per-scalar
+ * `interval()` recomputation (space.py:160).  `cdf` holds the categorical cdf
+ * tables (cumsum(p) / cumsum(p)[-1], as numpy's legacy RandomState.choice
+ * builds them, space.py:400).  Synchronous; uses the current device. */
+int ob2_space_create(const ob2_slot_desc *slots, int32_t n_slots, const double *cdf,
+                     int32_t cdf_len, ob2_space **out);
+void ob2_space_destroy(ob2_space *space);
+int64_t ob2_space_row_bytes(const ob2_space *space);  /* bytes per candidate, original set   */
+int64_t ob2_space_trow_bytes(const ob2_space *space); /* bytes per candidate, transformed set */
+
+/* Space.sample(n, seed) -- src/orion/algo/space.py:456-484, with Real.sample's
+ * <=4-attempt rejection (space.py:256-276), _Discrete.sample's floor
+ * (space.py:281-294) and Categorical.sample (space.py:392-402), as called by
+ * Random.suggest (src/orion/algo/random.py:24-33).  Uniforms come from
+ * Philox4x32-10: counter (index_lo, index_hi, slot >> 1, attempt), key = seed,
+ * candidate index = base_index + i.  `mask[i]` (nullable) is the fused
+ * `point in space` of PrimaryAlgo.suggest (src/orion/core/worker/primary_algo.py:53-54);
+ * `fp` (nullable, [n_stride][2] u64) receives the row fingerprints;
+ * `n_failed` (device u32[n_slots], nullable, zeroed by the caller) counts, at
+ * the index of a dimension's first slot, the candidates for which that
+ * dimension missed its bounds 4 times (the reference's ValueError). */
+int ob2_sample(const ob2_space *space, int64_t n, int64_t n_stride, uint64_t seed,
+               uint64_t base_index, void *cols, uint8_t *mask, uint64_t *fp,
+               uint32_t *n_failed, void *stream);
+
+/* Parity mode of the same kernel: uniforms are read from U[S][n_stride] (one
+ * attempt, no redraw); ok[i] = every Real/Integer slot landed in bounds. */
+int ob2_sample_from_uniform(const ob2_space *space, int64_t n, int64_t n_stride,
+                            const double *U, void *cols, uint8_t *ok, uint64_t *fp,
+                            void *stream);
+
+/* Space.__contains__ over N points -- src/orion/algo/space.py:521-545 over
+ * Dimension.__contains__ :150-164, Integer.__contains__ :335-347 and
+ * Categorical.__contains__ :415-426 (device: 0 <= index < n_cats).  With
+ * int_as_f64 != 0 Integer columns hold float64 and `mod(x, 1) == 0` is checked. */
+int ob2_contains(const ob2_space *space, int64_t n, int64_t n_stride, const void *cols,
+                 int32_t int_as_f64, uint8_t *mask, void *stream);
+
+/* TransformedSpace.transform / .reverse -- absent from the reference snapshot
+ * (TODOs at src/orion/core/worker/primary_algo.py:13-14,42,55); contract in
+ * SURVEY.md Appendix B.1/B.2. */
+int ob2_transform(const ob2_space *space, int64_t n, int64_t n_stride, const void *cols,
+                  void *tcols, void *stream);
+int ob2_reverse(const ob2_space *space, int64_t n, int64_t n_stride, const void *tcols,
+                void *cols, void *stream);
+
+/* 128-bit row fingerprint of existing columns (history ingestion); the trial
+ * identity the producer dedups on.  No counterpart in the snapshot
+ * (src/orion/core/worker/producer.py:42-52 registers blindly); SURVEY B.3. */
+int ob2_fingerprint(const ob2_space *space, int64_t n, int64_t n_stride, const void *cols,
+                    uint64_t *fp, void *stream);
+
+/* History hash set over caller-owned memory: n_slots (power of two) slots of
+ * OB2_SET_SLOT_BYTES, preceded by an OB2_SET_HEADER_BYTES header.  create
+ * zeroes the memory on `stream`. */
+#define OB2_SET_SLOT_BYTES 32
+#define OB2_SET_HEADER_BYTES 256
+int ob2_set_create(void *mem, uint64_t n_slots, void *stream, ob2_set **out);
+void ob2_set_destroy(ob2_set *set);
+/* insert fingerprints (history load / observe); duplicates collapse */
+int ob2_set_insert(ob2_set *set, int64_t n, const uint64_t *fp, void *stream);
+/* keep[i] = fp[i] not in the set before this call AND no entry of this call
+ * with a smaller order key has the same fingerprint (order = `order[i]`, or i
+ * when NULL).  Entries with fp.lo == 0 are padding (keep = 0).  Kept
+ * fingerprints stay in the set.  `scratch` is n u32 of caller scratch. */
+int ob2_set_dedup(ob2_set *set, int64_t n, const uint64_t *fp, const uint32_t *order,
+                  uint32_t *scratch, uint8_t *keep, void *stream);
+int ob2_set_probe(const ob2_set *set, int64_t n, const uint64_t *fp, uint8_t *found,
+                  void *stream);
+/* number of distinct fingerprints stored; synchronises `stream` */
+int ob2_set_count(const ob2_set *set, uint64_t *count, void *stream);
+
+/* Multi-GPU exchange helpers: owner rank of a fingerprint is
+ * fp.hi % n_ranks.  bucket writes (fp, global order key) into
+ * out_fp[n_ranks][cap][2] / out_key[n_ranks][cap], zero-pads each bucket's
+ * tail, and sets counts[r]; overflow beyond cap is reported through
+ * counts[r] > cap.  scatter writes verdict bytes back by local index. */
+int ob2_bucket_by_owner(int64_t n, const uint64_t *fp, uint32_t key_base, int32_t n_ranks,
+                        int64_t cap, uint64_t *out_fp, uint32_t *out_key, uint32_t *out_src,
+                        uint32_t *counts, void *stream);
+int ob2_scatter_verdict(int64_t n_entries, const uint32_t *src_index, const uint8_t *verdict,
+                        const uint64_t *fp, uint8_t *keep, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* OB2_H_ */

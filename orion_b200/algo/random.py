@@ -1,0 +1,62 @@
+"""Random search on the device.
+
+Mirror of ``src/orion/algo/random.py:15-41`` (``suggest(num)`` =
+``space.sample(num)``), plus:
+
+* ``suggest_columns(num)``: the tensor-returning fast path (a ColumnBatch whose
+  ``mask`` is the fused ``point in space`` and, with a history attached,
+  ``keep`` the dedup verdict);
+* optional dedup against the trial history: with
+  ``dedup=True`` the list path tops up until ``num`` unique points.
+"""
+import numpy
+
+from .base import BaseAlgorithm
+
+
+class Random(BaseAlgorithm):
+    """Sample candidates independently from the space's priors."""
+
+    def __init__(self, space, seed=None, dedup=False, history_capacity=1 << 20):
+        super(Random, self).__init__(space, seed=seed, dedup=dedup, history_capacity=history_capacity)
+        self._rng = numpy.random.RandomState(seed) if seed is not None else None
+        self._history = None
+        self._next_index = 0
+
+    @property
+    def history(self):
+        """Lazily created :class:`orion_b200.history.TrialHistory`."""
+        if self._history is None:
+            from ..history import TrialHistory
+            self._history = TrialHistory(self.space, capacity=self.history_capacity)
+        return self._history
+
+    def suggest_columns(self, num=1, check=True):
+        """Device-resident suggestion: ColumnBatch with ``mask`` (and ``keep``
+        when dedup is on; kept rows join the history)."""
+        batch = self.space.sample_columns(num, self._rng, with_fingerprint=bool(self.dedup), check=check)
+        if self.dedup:
+            self.history.dedup(batch)
+        return batch
+
+    def suggest(self, num=1):
+        """``num`` points as a list of tuples.  Without dedup this is exactly
+        ``space.sample(num)`` (seed None -> numpy's global RNG)."""
+        if not self.dedup:
+            return self.space.sample(num, self._rng)
+        points = []
+        for _ in range(8):                              # bounded top-up
+            need = num - len(points)
+            if need <= 0:
+                break
+            batch = self.suggest_columns(need)
+            keep = batch.keep[:batch.n].cpu().numpy().astype(bool)
+            rows = self.space.rows_from_columns(batch.to_numpy(), batch.n)
+            points.extend(r for r, k in zip(rows, keep) if k)
+        return points[:num]
+
+    def observe(self, points, results):
+        """Random search learns nothing from results; with dedup on, observed
+        points are recorded so they are never suggested again."""
+        if self.dedup and points:
+            self.history.observe_points(points)

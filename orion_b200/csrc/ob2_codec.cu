@@ -1,0 +1,194 @@
+// K2: TransformedSpace.transform / .reverse as fused columnar kernels
+// (Identity, Quantize, Reverse(Quantize), Enumerate, OneHotEncode in one pass
+// over the batch).
+//
+// Same mapping as the sampler: a thread owns 2 consecutive candidates and walks
+// the slots, so each warp-level access is 512 contiguous bytes of one column.
+// The one-hot expansion is pure store traffic (k columns of 16 B per thread).
+#include "ob2_internal.cuh"
+
+namespace {
+
+__device__ __forceinline__ long long quantize(double x, int t_flags) {
+    // numpy.round (half to even) by default; floor when the descriptor asks
+    const double r = (t_flags & OB2_TFLAG_FLOOR) ? floor(x) : rint(x);
+    return __double2ll_rz(r);
+}
+
+__global__ void __launch_bounds__(OB2_BLOCK)
+transform_kernel(const ob2_slot_desc *__restrict__ g_slots, int n_slots, int64_t n, int64_t n_stride,
+                 const char *__restrict__ cols, char *__restrict__ tcols) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    ob2_slot_desc *s_slots = reinterpret_cast<ob2_slot_desc *>(smem);
+    ob2_stage_tables(g_slots, n_slots, nullptr, 0, s_slots, nullptr);
+    const int64_t i0 = ((int64_t)blockIdx.x * OB2_BLOCK + threadIdx.x) * OB2_CPT;
+    if (i0 >= n) return;
+    for (int s = 0; s < n_slots; ++s) {
+        const ob2_slot_desc &d = s_slots[s];
+        const char *src = cols + (int64_t)d.col_units * n_stride;
+        char *dst = tcols + (int64_t)d.t_units * n_stride;
+        switch (d.t_op) {
+            case OB2_OP_ONEHOT: {
+                int c0, c1;
+                ld_i32x2(reinterpret_cast<const int *>(src) + i0, c0, c1);
+                if (d.t_width == 1) {  // k <= 2: a single float column
+                    st_f64x2(reinterpret_cast<double *>(dst) + i0, (double)c0, (double)c1);
+                } else {
+                    double *out = reinterpret_cast<double *>(dst) + i0;
+                    for (int j = 0; j < d.t_width; ++j) {
+                        st_f64x2(out, c0 == j ? 1.0 : 0.0, c1 == j ? 1.0 : 0.0);
+                        out += n_stride;
+                    }
+                }
+                break;
+            }
+            case OB2_OP_QUANTIZE: {
+                double x0, x1;
+                ld_f64x2(reinterpret_cast<const double *>(src) + i0, x0, x1);
+                st_i64x2(reinterpret_cast<long long *>(dst) + i0, quantize(x0, d.t_flags), quantize(x1, d.t_flags));
+                break;
+            }
+            case OB2_OP_TO_REAL: {
+                long long q0, q1;
+                ld_i64x2(reinterpret_cast<const long long *>(src) + i0, q0, q1);
+                st_f64x2(reinterpret_cast<double *>(dst) + i0, __ll2double_rn(q0), __ll2double_rn(q1));
+                break;
+            }
+            default: {  // IDENTITY / ENUMERATE: copy with the slot's own width
+                if (d.kind == OB2_KIND_CATEGORICAL) {
+                    int c0, c1;
+                    ld_i32x2(reinterpret_cast<const int *>(src) + i0, c0, c1);
+                    st_i32x2(reinterpret_cast<int *>(dst) + i0, c0, c1);
+                } else {
+                    long long q0, q1;
+                    ld_i64x2(reinterpret_cast<const long long *>(src) + i0, q0, q1);
+                    st_i64x2(reinterpret_cast<long long *>(dst) + i0, q0, q1);
+                }
+                break;
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(OB2_BLOCK)
+reverse_kernel(const ob2_slot_desc *__restrict__ g_slots, int n_slots, int64_t n, int64_t n_stride,
+               const char *__restrict__ tcols, char *__restrict__ cols) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    ob2_slot_desc *s_slots = reinterpret_cast<ob2_slot_desc *>(smem);
+    ob2_stage_tables(g_slots, n_slots, nullptr, 0, s_slots, nullptr);
+    const int64_t i0 = ((int64_t)blockIdx.x * OB2_BLOCK + threadIdx.x) * OB2_CPT;
+    if (i0 >= n) return;
+    for (int s = 0; s < n_slots; ++s) {
+        const ob2_slot_desc &d = s_slots[s];
+        const char *src = tcols + (int64_t)d.t_units * n_stride;
+        char *dst = cols + (int64_t)d.col_units * n_stride;
+        switch (d.t_op) {
+            case OB2_OP_ONEHOT: {
+                int c0 = 0, c1 = 0;
+                const double *in = reinterpret_cast<const double *>(src) + i0;
+                if (d.t_width == 1) {
+                    if (d.n_cats == 2) {  // (v > 0.5).astype(int)
+                        double v0, v1;
+                        ld_f64x2(in, v0, v1);
+                        c0 = v0 > 0.5 ? 1 : 0;
+                        c1 = v1 > 0.5 ? 1 : 0;
+                    }                     // k == 1: always category 0
+                } else {                  // argmax over the trailing axis, first max wins
+                    double b0, b1;
+                    ld_f64x2(in, b0, b1);
+                    // 4 loads in flight per step to cover HBM latency on wide encodings
+                    int j = 1;
+                    for (; j + 3 < d.t_width; j += 4) {
+                        double v[8];
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) ld_f64x2(in + (int64_t)(j + q) * n_stride, v[2 * q], v[2 * q + 1]);
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            if (v[2 * q] > b0) {
+                                b0 = v[2 * q];
+                                c0 = j + q;
+                            }
+                            if (v[2 * q + 1] > b1) {
+                                b1 = v[2 * q + 1];
+                                c1 = j + q;
+                            }
+                        }
+                    }
+                    for (; j < d.t_width; ++j) {
+                        double v0, v1;
+                        ld_f64x2(in + (int64_t)j * n_stride, v0, v1);
+                        if (v0 > b0) {
+                            b0 = v0;
+                            c0 = j;
+                        }
+                        if (v1 > b1) {
+                            b1 = v1;
+                            c1 = j;
+                        }
+                    }
+                }
+                st_i32x2(reinterpret_cast<int *>(dst) + i0, c0, c1);
+                break;
+            }
+            case OB2_OP_QUANTIZE: {  // Quantize.reverse: cast back to float
+                long long q0, q1;
+                ld_i64x2(reinterpret_cast<const long long *>(src) + i0, q0, q1);
+                st_f64x2(reinterpret_cast<double *>(dst) + i0, __ll2double_rn(q0), __ll2double_rn(q1));
+                break;
+            }
+            case OB2_OP_TO_REAL: {  // Reverse(Quantize).reverse = Quantize.transform
+                double x0, x1;
+                ld_f64x2(reinterpret_cast<const double *>(src) + i0, x0, x1);
+                st_i64x2(reinterpret_cast<long long *>(dst) + i0, quantize(x0, d.t_flags), quantize(x1, d.t_flags));
+                break;
+            }
+            default: {
+                if (d.kind == OB2_KIND_CATEGORICAL) {
+                    int c0, c1;
+                    ld_i32x2(reinterpret_cast<const int *>(src) + i0, c0, c1);
+                    st_i32x2(reinterpret_cast<int *>(dst) + i0, c0, c1);
+                } else {
+                    long long q0, q1;
+                    ld_i64x2(reinterpret_cast<const long long *>(src) + i0, q0, q1);
+                    st_i64x2(reinterpret_cast<long long *>(dst) + i0, q0, q1);
+                }
+                break;
+            }
+        }
+    }
+}
+
+template <typename K>
+int launch_codec(K kernel, const char *what, const ob2_space *sp, int64_t n, int64_t n_stride, const void *in,
+                 void *out, void *stream) {
+    int rc = ob2_check_batch(sp, n, n_stride);
+    if (rc != OB2_OK) return rc;
+    if (in == nullptr || out == nullptr) {
+        ob2_set_error("%s: null buffer", what);
+        return OB2_EINVAL;
+    }
+    if (n == 0) return OB2_OK;
+    const int64_t threads = (n + OB2_CPT - 1) / OB2_CPT;
+    const int64_t blocks = (threads + OB2_BLOCK - 1) / OB2_BLOCK;
+    const size_t smem = (size_t)sp->n_slots * sizeof(ob2_slot_desc);
+    if (smem > 48 * 1024) {
+        rc = ob2_check_cuda(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
+                            "cudaFuncSetAttribute(smem)");
+        if (rc != OB2_OK) return rc;
+    }
+    kernel<<<(unsigned)blocks, OB2_BLOCK, smem, static_cast<cudaStream_t>(stream)>>>(
+        sp->d_slots, sp->n_slots, n, n_stride, (const char *)in, (char *)out);
+    return ob2_check_cuda(cudaGetLastError(), what);
+}
+
+}  // namespace
+
+extern "C" int ob2_transform(const ob2_space *space, int64_t n, int64_t n_stride, const void *cols, void *tcols,
+                             void *stream) {
+    return launch_codec(transform_kernel, "transform_kernel", space, n, n_stride, cols, tcols, stream);
+}
+
+extern "C" int ob2_reverse(const ob2_space *space, int64_t n, int64_t n_stride, const void *tcols, void *cols,
+                           void *stream) {
+    return launch_codec(reverse_kernel, "reverse_kernel", space, n, n_stride, tcols, cols, stream);
+}

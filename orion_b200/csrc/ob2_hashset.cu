@@ -1,0 +1,477 @@
+// K3: row fingerprints and the history hash set.
+//
+// The set is an open-addressing table of 32-byte slots -- one DRAM sector per
+// probe -- keyed by the 128-bit fingerprint:
+//     { u64 lo, u64 hi, u64 stamp, u32 born, u32 pad }
+// lo == 0 marks an empty slot (fingerprints never have lo == 0).  Keys are
+// claimed with one 128-bit compare-and-swap, so a slot is either empty or holds
+// a complete key.  Deterministic first-wins inside a batch: every call gets a
+// new epoch; pass 1 finds-or-inserts each fingerprint and raises the slot's
+// stamp to max((epoch << 32) | ~order); pass 2 keeps entry i iff the slot was
+// born in this epoch and its stamp is i's own.  No sort, no per-batch clearing.
+#include <new>
+
+#include "ob2_internal.cuh"
+
+namespace {
+
+struct __align__(32) SetSlot {
+    uint64_t lo, hi;
+    unsigned long long stamp;
+    uint32_t born;
+    uint32_t pad;
+};
+static_assert(sizeof(SetSlot) == OB2_SET_SLOT_BYTES, "slot size");
+
+struct SetHeader {
+    unsigned long long count;  // distinct fingerprints stored
+    uint32_t overflow;         // a probe sequence wrapped the whole table
+};
+
+}  // namespace
+
+struct ob2_set {
+    int device;
+    SetHeader *header;
+    SetSlot *slots;
+    uint64_t n_slots;
+    uint64_t upper_bound;  // host-side bound on entries inserted so far
+    uint32_t epoch;
+};
+
+namespace {
+
+// 128-bit CAS on the key; returns the previous (lo, hi).
+__device__ __forceinline__ void cas128(SetSlot *slot, uint64_t cmp_lo, uint64_t cmp_hi, uint64_t new_lo,
+                                       uint64_t new_hi, uint64_t &old_lo, uint64_t &old_hi) {
+    asm volatile(
+        "{\n"
+        ".reg .b128 cmp, val, old;\n"
+        "mov.b128 cmp, {%2, %3};\n"
+        "mov.b128 val, {%4, %5};\n"
+        "atom.relaxed.gpu.global.cas.b128 old, [%6], cmp, val;\n"
+        "mov.b128 {%0, %1}, old;\n"
+        "}\n"
+        : "=l"(old_lo), "=l"(old_hi)
+        : "l"(cmp_lo), "l"(cmp_hi), "l"(new_lo), "l"(new_hi), "l"(slot)
+        : "memory");
+}
+
+__device__ __forceinline__ void ld_key(const SetSlot *slot, uint64_t &lo, uint64_t &hi) {
+    // L2-coherent read: keys only ever go empty -> set, so a stale "empty" is
+    // resolved by the CAS and a complete key never changes again
+    asm volatile("ld.global.cg.v2.u64 {%0, %1}, [%2];" : "=l"(lo), "=l"(hi) : "l"(slot));
+}
+
+enum { FOUND = 0, INSERTED = 1, OVERFLOW = 2 };
+
+// Find the slot holding (lo, hi), inserting it if absent.
+__device__ __forceinline__ int find_or_insert(SetSlot *slots, uint64_t mask, uint64_t lo, uint64_t hi, uint64_t &pos) {
+    pos = lo & mask;
+    for (uint64_t step = 0; step <= mask; ++step) {
+        SetSlot *slot = slots + pos;
+        uint64_t klo, khi;
+        ld_key(slot, klo, khi);
+        if (klo == 0) {
+            cas128(slot, 0, 0, lo, hi, klo, khi);
+            if (klo == 0 && khi == 0) return INSERTED;
+            if (klo == lo && khi == hi) return FOUND;
+        } else if (klo == lo) {
+            if (khi == hi) return FOUND;
+            // same low word, different high word: true 64-bit collision or a torn
+            // read of a key being written -- re-read atomically to tell
+            cas128(slot, lo, hi, lo, hi, klo, khi);
+            if (klo == lo && khi == hi) return FOUND;
+        }
+        pos = (pos + 1) & mask;
+    }
+    return OVERFLOW;
+}
+
+// Read-only lookup.
+__device__ __forceinline__ bool find(const SetSlot *slots, uint64_t mask, uint64_t lo, uint64_t hi) {
+    uint64_t pos = lo & mask;
+    for (uint64_t step = 0; step <= mask; ++step) {
+        uint64_t klo, khi;
+        ld_key(slots + pos, klo, khi);
+        if (klo == 0) return false;
+        if (klo == lo && khi == hi) return true;
+        pos = (pos + 1) & mask;
+    }
+    return false;
+}
+
+__device__ __forceinline__ void warp_count_add(unsigned long long *counter, bool flag) {
+    const unsigned ballot = __ballot_sync(__activemask(), flag);
+    if (flag && (threadIdx.x & 31) == (__ffs(ballot) - 1)) atomicAdd(counter, (unsigned long long)__popc(ballot));
+}
+
+__global__ void __launch_bounds__(OB2_BLOCK)
+set_insert_kernel(SetHeader *hdr, SetSlot *slots, uint64_t mask, int64_t n, const uint64_t *__restrict__ fp) {
+    const int64_t i = (int64_t)blockIdx.x * OB2_BLOCK + threadIdx.x;
+    bool inserted = false;
+    if (i < n) {
+        const ulonglong2 key = __ldg(reinterpret_cast<const ulonglong2 *>(fp) + i);
+        if (key.x != 0) {
+            uint64_t pos;
+            const int r = find_or_insert(slots, mask, key.x, key.y, pos);
+            inserted = r == INSERTED;
+            if (r == OVERFLOW) hdr->overflow = 1;
+        }
+    }
+    warp_count_add(&hdr->count, inserted);
+}
+
+__global__ void __launch_bounds__(OB2_BLOCK)
+set_dedup_pass1(SetHeader *hdr, SetSlot *slots, uint64_t mask, int64_t n, const uint64_t *__restrict__ fp,
+                const uint32_t *__restrict__ order, uint32_t epoch, uint32_t *__restrict__ scratch) {
+    const int64_t i = (int64_t)blockIdx.x * OB2_BLOCK + threadIdx.x;
+    if (i >= n) return;
+    const ulonglong2 key = __ldg(reinterpret_cast<const ulonglong2 *>(fp) + i);
+    if (key.x == 0) return;  // padding
+    uint64_t pos;
+    const int r = find_or_insert(slots, mask, key.x, key.y, pos);
+    if (r == OVERFLOW) {
+        hdr->overflow = 1;
+        scratch[i] = 0xFFFFFFFFu;
+        return;
+    }
+    SetSlot *slot = slots + pos;
+    if (r == INSERTED) slot->born = epoch;  // read only by pass 2, after this grid retires
+    const uint32_t ord = order ? __ldg(order + i) : (uint32_t)i;
+    atomicMax(&slot->stamp, ((unsigned long long)epoch << 32) | (unsigned long long)(0xFFFFFFFFu - ord));
+    scratch[i] = (uint32_t)pos;
+}
+
+__global__ void __launch_bounds__(OB2_BLOCK)
+set_dedup_pass2(SetHeader *hdr, const SetSlot *__restrict__ slots, int64_t n, const uint64_t *__restrict__ fp,
+                const uint32_t *__restrict__ order, uint32_t epoch, const uint32_t *__restrict__ scratch,
+                uint8_t *__restrict__ keep) {
+    const int64_t i = (int64_t)blockIdx.x * OB2_BLOCK + threadIdx.x;
+    bool kept = false;
+    if (i < n) {
+        const uint64_t lo = __ldg(fp + 2 * i);
+        const uint32_t pos = scratch[i];
+        if (lo != 0 && pos != 0xFFFFFFFFu) {
+            const SetSlot *slot = slots + pos;
+            const uint32_t ord = order ? __ldg(order + i) : (uint32_t)i;
+            const unsigned long long mine = ((unsigned long long)epoch << 32) | (unsigned long long)(0xFFFFFFFFu - ord);
+            kept = (slot->born == epoch) && (slot->stamp == mine);
+        }
+        keep[i] = kept ? 1 : 0;
+    }
+    warp_count_add(&hdr->count, kept);
+}
+
+__global__ void __launch_bounds__(OB2_BLOCK)
+set_probe_kernel(const SetSlot *__restrict__ slots, uint64_t mask, int64_t n, const uint64_t *__restrict__ fp,
+                 uint8_t *__restrict__ found) {
+    const int64_t i = (int64_t)blockIdx.x * OB2_BLOCK + threadIdx.x;
+    if (i >= n) return;
+    const ulonglong2 key = __ldg(reinterpret_cast<const ulonglong2 *>(fp) + i);
+    found[i] = (key.x != 0 && find(slots, mask, key.x, key.y)) ? 1 : 0;
+}
+
+// Fingerprint of existing columns (same arithmetic as the fused path in the sampler).
+__global__ void __launch_bounds__(OB2_BLOCK)
+fingerprint_kernel(const ob2_slot_desc *__restrict__ g_slots, int n_slots, int64_t n, int64_t n_stride,
+                   const char *__restrict__ cols, uint64_t *__restrict__ fp) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    ob2_slot_desc *s_slots = reinterpret_cast<ob2_slot_desc *>(smem);
+    ob2_stage_tables(g_slots, n_slots, nullptr, 0, s_slots, nullptr);
+    const int64_t i0 = ((int64_t)blockIdx.x * OB2_BLOCK + threadIdx.x) * OB2_CPT;
+    if (i0 >= n) return;
+    FpAcc acc0{0, 0}, acc1{0, 0};
+    for (int s = 0; s < n_slots; ++s) {
+        const ob2_slot_desc &d = s_slots[s];
+        const char *col = cols + (int64_t)d.col_units * n_stride;
+        uint64_t w0, w1;
+        if (d.kind == OB2_KIND_CATEGORICAL) {
+            int c0, c1;
+            ld_i32x2(reinterpret_cast<const int *>(col) + i0, c0, c1);
+            w0 = (uint64_t)(int64_t)c0;
+            w1 = (uint64_t)(int64_t)c1;
+        } else if (d.kind == OB2_KIND_INTEGER) {
+            long long q0, q1;
+            ld_i64x2(reinterpret_cast<const long long *>(col) + i0, q0, q1);
+            w0 = (uint64_t)q0;
+            w1 = (uint64_t)q1;
+        } else {
+            double x0, x1;
+            ld_f64x2(reinterpret_cast<const double *>(col) + i0, x0, x1);
+            w0 = canon_f64(x0);
+            w1 = canon_f64(x1);
+        }
+        fp_add(acc0, d, w0);
+        fp_add(acc1, d, w1);
+    }
+    uint64_t lo0, hi0, lo1, hi1;
+    fp_finish(acc0, n_slots, lo0, hi0);
+    fp_finish(acc1, n_slots, lo1, hi1);
+    if (i0 + 1 >= n) lo1 = hi1 = 0;
+    st_u64x4(fp + 2 * i0, lo0, hi0, lo1, hi1);
+}
+
+// ---- multi-GPU exchange helpers
+#define OB2_MAX_RANKS 64
+
+__global__ void __launch_bounds__(OB2_BLOCK)
+bucket_kernel(int64_t n, const uint64_t *__restrict__ fp, uint32_t key_base, int n_ranks, int64_t cap,
+              uint64_t *__restrict__ out_fp, uint32_t *__restrict__ out_key, uint32_t *__restrict__ out_src,
+              uint32_t *__restrict__ counts) {
+    __shared__ uint32_t s_cnt[OB2_MAX_RANKS];
+    __shared__ uint32_t s_base[OB2_MAX_RANKS];
+    if (threadIdx.x < n_ranks) s_cnt[threadIdx.x] = 0;
+    __syncthreads();
+    const int64_t i = (int64_t)blockIdx.x * OB2_BLOCK + threadIdx.x;
+    int owner = -1;
+    uint32_t rank_in_block = 0;
+    ulonglong2 key = make_ulonglong2(0, 0);
+    if (i < n) {
+        key = __ldg(reinterpret_cast<const ulonglong2 *>(fp) + i);
+        if (key.x != 0) {
+            owner = (int)(key.y % (uint64_t)n_ranks);
+            rank_in_block = atomicAdd(&s_cnt[owner], 1u);
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x < n_ranks) s_base[threadIdx.x] = s_cnt[threadIdx.x] ? atomicAdd(&counts[threadIdx.x], s_cnt[threadIdx.x]) : 0;
+    __syncthreads();
+    if (owner >= 0) {
+        const int64_t pos = (int64_t)s_base[owner] + rank_in_block;
+        if (pos < cap) {
+            const int64_t o = (int64_t)owner * cap + pos;
+            reinterpret_cast<ulonglong2 *>(out_fp)[o] = key;
+            out_key[o] = key_base + (uint32_t)i;
+            out_src[o] = (uint32_t)i;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(OB2_BLOCK)
+bucket_pad_kernel(int n_ranks, int64_t cap, const uint32_t *__restrict__ counts, uint64_t *__restrict__ out_fp) {
+    const int r = blockIdx.y;
+    const int64_t used = min((int64_t)counts[r], cap);
+    for (int64_t p = used + (int64_t)blockIdx.x * OB2_BLOCK + threadIdx.x; p < cap; p += (int64_t)gridDim.x * OB2_BLOCK) {
+        reinterpret_cast<ulonglong2 *>(out_fp)[(int64_t)r * cap + p] = make_ulonglong2(0, 0);
+    }
+}
+
+__global__ void __launch_bounds__(OB2_BLOCK)
+scatter_verdict_kernel(int64_t n_entries, const uint32_t *__restrict__ src_index, const uint8_t *__restrict__ verdict,
+                       const uint64_t *__restrict__ fp, uint8_t *__restrict__ keep) {
+    const int64_t o = (int64_t)blockIdx.x * OB2_BLOCK + threadIdx.x;
+    if (o >= n_entries) return;
+    if (__ldg(fp + 2 * o) == 0) return;  // padding
+    keep[src_index[o]] = verdict[o];
+}
+
+int grid_for(int64_t n, unsigned *blocks) {
+    const int64_t b = (n + OB2_BLOCK - 1) / OB2_BLOCK;
+    if (b > 0x7FFFFFFFll) {
+        ob2_set_error("batch too large for one launch");
+        return OB2_ETOOBIG;
+    }
+    *blocks = (unsigned)b;
+    return OB2_OK;
+}
+
+int check_set_args(const ob2_set *set, int64_t n, const void *fp) {
+    if (set == nullptr || n < 0 || (n > 0 && fp == nullptr)) {
+        ob2_set_error("hash set: bad arguments");
+        return OB2_EINVAL;
+    }
+    if (n >= 0xFFFFFFFFll) {
+        ob2_set_error("hash set: at most 2^32 - 2 entries per call");
+        return OB2_ETOOBIG;
+    }
+    return OB2_OK;
+}
+
+// Refuse to push the load factor past 7/8: linear probing degrades sharply and a
+// full table would spin.  The host bound counts every submitted entry; when it
+// trips, fall back to the exact device count (one synchronising read).
+int reserve(ob2_set *set, int64_t n, cudaStream_t st) {
+    const uint64_t limit = set->n_slots - set->n_slots / 8;
+    if (set->upper_bound + (uint64_t)n > limit) {
+        unsigned long long exact = 0;
+        OB2_CUDA(cudaMemcpyAsync(&exact, &set->header->count, sizeof(exact), cudaMemcpyDeviceToHost, st));
+        OB2_CUDA(cudaStreamSynchronize(st));
+        set->upper_bound = exact;
+        if (exact + (uint64_t)n > limit) {
+            ob2_set_error("hash set full: %llu stored + %lld incoming exceeds 7/8 of %llu slots", exact, (long long)n,
+                          (unsigned long long)set->n_slots);
+            return OB2_ENOMEM;
+        }
+    }
+    set->upper_bound += (uint64_t)n;
+    return OB2_OK;
+}
+
+}  // namespace
+
+extern "C" int ob2_fingerprint(const ob2_space *space, int64_t n, int64_t n_stride, const void *cols, uint64_t *fp,
+                               void *stream) {
+    int rc = ob2_check_batch(space, n, n_stride);
+    if (rc != OB2_OK) return rc;
+    if (cols == nullptr || fp == nullptr) {
+        ob2_set_error("fingerprint: null buffer");
+        return OB2_EINVAL;
+    }
+    if (n == 0) return OB2_OK;
+    unsigned blocks;
+    rc = grid_for((n + OB2_CPT - 1) / OB2_CPT, &blocks);
+    if (rc != OB2_OK) return rc;
+    const size_t smem = (size_t)space->n_slots * sizeof(ob2_slot_desc);
+    if (smem > 48 * 1024)
+        OB2_CUDA(cudaFuncSetAttribute(fingerprint_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    fingerprint_kernel<<<blocks, OB2_BLOCK, smem, static_cast<cudaStream_t>(stream)>>>(
+        space->d_slots, space->n_slots, n, n_stride, (const char *)cols, fp);
+    return ob2_check_cuda(cudaGetLastError(), "fingerprint_kernel launch");
+}
+
+extern "C" int ob2_set_create(void *mem, uint64_t n_slots, void *stream, ob2_set **out) {
+    if (out == nullptr || mem == nullptr || n_slots < 64 || (n_slots & (n_slots - 1)) != 0 || n_slots > (1ull << 32)) {
+        ob2_set_error("ob2_set_create: n_slots must be a power of two in [64, 2^32] (got %llu)", (unsigned long long)n_slots);
+        return OB2_EINVAL;
+    }
+    if ((reinterpret_cast<uintptr_t>(mem) & 255) != 0) {
+        ob2_set_error("ob2_set_create: memory must be 256-byte aligned");
+        return OB2_EINVAL;
+    }
+    *out = nullptr;
+    ob2_set *set = new (std::nothrow) ob2_set();
+    if (set == nullptr) {
+        ob2_set_error("out of host memory");
+        return OB2_ENOMEM;
+    }
+    set->header = reinterpret_cast<SetHeader *>(mem);
+    set->slots = reinterpret_cast<SetSlot *>(reinterpret_cast<char *>(mem) + OB2_SET_HEADER_BYTES);
+    set->n_slots = n_slots;
+    set->upper_bound = 0;
+    set->epoch = 0;
+    int rc = ob2_check_cuda(cudaGetDevice(&set->device), "cudaGetDevice");
+    if (rc == OB2_OK)
+        rc = ob2_check_cuda(cudaMemsetAsync(mem, 0, OB2_SET_HEADER_BYTES + n_slots * OB2_SET_SLOT_BYTES,
+                                            static_cast<cudaStream_t>(stream)),
+                            "cudaMemsetAsync(table)");
+    if (rc != OB2_OK) {
+        delete set;
+        return rc;
+    }
+    *out = set;
+    return OB2_OK;
+}
+
+extern "C" void ob2_set_destroy(ob2_set *set) { delete set; }
+
+extern "C" int ob2_set_insert(ob2_set *set, int64_t n, const uint64_t *fp, void *stream) {
+    int rc = check_set_args(set, n, fp);
+    if (rc != OB2_OK) return rc;
+    if (n == 0) return OB2_OK;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    rc = reserve(set, n, st);
+    if (rc != OB2_OK) return rc;
+    unsigned blocks;
+    rc = grid_for(n, &blocks);
+    if (rc != OB2_OK) return rc;
+    set_insert_kernel<<<blocks, OB2_BLOCK, 0, st>>>(set->header, set->slots, set->n_slots - 1, n, fp);
+    return ob2_check_cuda(cudaGetLastError(), "set_insert_kernel launch");
+}
+
+extern "C" int ob2_set_dedup(ob2_set *set, int64_t n, const uint64_t *fp, const uint32_t *order, uint32_t *scratch,
+                             uint8_t *keep, void *stream) {
+    int rc = check_set_args(set, n, fp);
+    if (rc != OB2_OK) return rc;
+    if (n == 0) return OB2_OK;
+    if (scratch == nullptr || keep == nullptr) {
+        ob2_set_error("ob2_set_dedup: null scratch/keep");
+        return OB2_EINVAL;
+    }
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    rc = reserve(set, n, st);
+    if (rc != OB2_OK) return rc;
+    unsigned blocks;
+    rc = grid_for(n, &blocks);
+    if (rc != OB2_OK) return rc;
+    if (set->epoch == 0xFFFFFFFFu) {
+        ob2_set_error("ob2_set_dedup: epoch counter exhausted");
+        return OB2_ETOOBIG;
+    }
+    const uint32_t epoch = ++set->epoch;
+    set_dedup_pass1<<<blocks, OB2_BLOCK, 0, st>>>(set->header, set->slots, set->n_slots - 1, n, fp, order, epoch, scratch);
+    rc = ob2_check_cuda(cudaGetLastError(), "set_dedup_pass1 launch");
+    if (rc != OB2_OK) return rc;
+    set_dedup_pass2<<<blocks, OB2_BLOCK, 0, st>>>(set->header, set->slots, n, fp, order, epoch, scratch, keep);
+    return ob2_check_cuda(cudaGetLastError(), "set_dedup_pass2 launch");
+}
+
+extern "C" int ob2_set_probe(const ob2_set *set, int64_t n, const uint64_t *fp, uint8_t *found, void *stream) {
+    int rc = check_set_args(set, n, fp);
+    if (rc != OB2_OK) return rc;
+    if (n == 0) return OB2_OK;
+    if (found == nullptr) {
+        ob2_set_error("ob2_set_probe: null output");
+        return OB2_EINVAL;
+    }
+    unsigned blocks;
+    rc = grid_for(n, &blocks);
+    if (rc != OB2_OK) return rc;
+    set_probe_kernel<<<blocks, OB2_BLOCK, 0, static_cast<cudaStream_t>(stream)>>>(set->slots, set->n_slots - 1, n, fp, found);
+    return ob2_check_cuda(cudaGetLastError(), "set_probe_kernel launch");
+}
+
+extern "C" int ob2_set_count(const ob2_set *set, uint64_t *count, void *stream) {
+    if (set == nullptr || count == nullptr) {
+        ob2_set_error("ob2_set_count: bad arguments");
+        return OB2_EINVAL;
+    }
+    SetHeader h;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    OB2_CUDA(cudaMemcpyAsync(&h, set->header, sizeof(h), cudaMemcpyDeviceToHost, st));
+    OB2_CUDA(cudaStreamSynchronize(st));
+    if (h.overflow) {
+        ob2_set_error("hash set overflowed: a probe sequence wrapped the whole table");
+        return OB2_ENOMEM;
+    }
+    *count = h.count;
+    return OB2_OK;
+}
+
+extern "C" int ob2_bucket_by_owner(int64_t n, const uint64_t *fp, uint32_t key_base, int32_t n_ranks, int64_t cap,
+                                   uint64_t *out_fp, uint32_t *out_key, uint32_t *out_src, uint32_t *counts,
+                                   void *stream) {
+    if (n < 0 || n_ranks < 1 || n_ranks > OB2_MAX_RANKS || cap < 1 || fp == nullptr || out_fp == nullptr ||
+        out_key == nullptr || out_src == nullptr || counts == nullptr) {
+        ob2_set_error("ob2_bucket_by_owner: bad arguments (n=%lld ranks=%d cap=%lld)", (long long)n, n_ranks, (long long)cap);
+        return OB2_EINVAL;
+    }
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    OB2_CUDA(cudaMemsetAsync(counts, 0, sizeof(uint32_t) * n_ranks, st));
+    if (n > 0) {
+        unsigned blocks;
+        int rc = grid_for(n, &blocks);
+        if (rc != OB2_OK) return rc;
+        bucket_kernel<<<blocks, OB2_BLOCK, 0, st>>>(n, fp, key_base, n_ranks, cap, out_fp, out_key, out_src, counts);
+        rc = ob2_check_cuda(cudaGetLastError(), "bucket_kernel launch");
+        if (rc != OB2_OK) return rc;
+    }
+    const int64_t pad_blocks = (cap + OB2_BLOCK - 1) / OB2_BLOCK;
+    dim3 grid((unsigned)(pad_blocks < 256 ? pad_blocks : 256), (unsigned)n_ranks);
+    bucket_pad_kernel<<<grid, OB2_BLOCK, 0, st>>>(n_ranks, cap, counts, out_fp);
+    return ob2_check_cuda(cudaGetLastError(), "bucket_pad_kernel launch");
+}
+
+extern "C" int ob2_scatter_verdict(int64_t n_entries, const uint32_t *src_index, const uint8_t *verdict,
+                                   const uint64_t *fp, uint8_t *keep, void *stream) {
+    if (n_entries < 0 || src_index == nullptr || verdict == nullptr || fp == nullptr || keep == nullptr) {
+        ob2_set_error("ob2_scatter_verdict: bad arguments");
+        return OB2_EINVAL;
+    }
+    if (n_entries == 0) return OB2_OK;
+    unsigned blocks;
+    int rc = grid_for(n_entries, &blocks);
+    if (rc != OB2_OK) return rc;
+    scatter_verdict_kernel<<<blocks, OB2_BLOCK, 0, static_cast<cudaStream_t>(stream)>>>(n_entries, src_index, verdict, fp, keep);
+    return ob2_check_cuda(cudaGetLastError(), "scatter_verdict_kernel launch");
+}

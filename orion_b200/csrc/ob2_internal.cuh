@@ -1,0 +1,171 @@
+// Shared device helpers for libob2 (sm_100a).  Everything here is inline; the
+// .cu files do not call across translation units on the device.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "ob2.h"
+
+// ---------------------------------------------------------------- host side
+struct ob2_space {
+    int device;
+    int32_t n_slots;
+    int32_t cdf_len;
+    int64_t row_bytes;   // bytes per candidate in the original column set
+    int64_t trow_bytes;  // bytes per candidate in the transformed column set
+    int32_t t_cols;      // number of transformed columns
+    size_t smem_bytes;   // descriptor + cdf staging size
+    ob2_slot_desc *d_slots;
+    double *d_cdf;
+    bool has_onehot;
+};
+
+void ob2_set_error(const char *fmt, ...);
+int ob2_check_cuda(cudaError_t err, const char *what);
+#define OB2_CUDA(call)                                      \
+    do {                                                    \
+        int _rc = ob2_check_cuda((call), #call);            \
+        if (_rc != OB2_OK) return _rc;                      \
+    } while (0)
+
+static inline int ob2_check_batch(const ob2_space *sp, int64_t n, int64_t n_stride) {
+    if (sp == nullptr) {
+        ob2_set_error("null space handle");
+        return OB2_EINVAL;
+    }
+    if (n < 0 || n_stride < n || (n_stride & 31) != 0) {
+        ob2_set_error("bad batch shape: n=%lld n_stride=%lld (need 0 <= n <= n_stride, n_stride %% 32 == 0)",
+                      (long long)n, (long long)n_stride);
+        return OB2_EINVAL;
+    }
+    return OB2_OK;
+}
+
+// -------------------------------------------------------------- device side
+#define OB2_BLOCK 256
+#define OB2_CPT 2  // candidates per thread: 2 x 8 B = one 128-bit store per column
+
+__device__ __forceinline__ void ob2_stage_tables(const ob2_slot_desc *__restrict__ g_slots, int n_slots,
+                                                 const double *__restrict__ g_cdf, int cdf_len,
+                                                 ob2_slot_desc *s_slots, double *s_cdf) {
+    // descriptors are 16-byte multiples: copy as uint4
+    const uint4 *src = reinterpret_cast<const uint4 *>(g_slots);
+    uint4 *dst = reinterpret_cast<uint4 *>(s_slots);
+    const int n16 = n_slots * (int)(sizeof(ob2_slot_desc) / 16);
+    for (int i = threadIdx.x; i < n16; i += blockDim.x) dst[i] = __ldg(src + i);
+    for (int i = threadIdx.x; i < cdf_len; i += blockDim.x) s_cdf[i] = __ldg(g_cdf + i);
+    __syncthreads();
+}
+
+// Philox4x32-10 (Salmon et al. SC'11).
+struct Philox4 {
+    uint32_t x, y, z, w;
+};
+__device__ __forceinline__ Philox4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
+                                                 uint32_t k0, uint32_t k1) {
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+        const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+        c0 = hi1 ^ c1 ^ k0;
+        c2 = hi0 ^ c3 ^ k1;
+        c1 = lo1;
+        c3 = lo0;
+        k0 += 0x9E3779B9u;
+        k1 += 0xBB67AE85u;
+    }
+    return Philox4{c0, c1, c2, c3};
+}
+
+// ((w0 >> 5) * 2^26 + (w1 >> 6)) / 2^53, exactly (53-bit integer -> double -> scale)
+__device__ __forceinline__ double u53(uint32_t w0, uint32_t w1) {
+    const unsigned long long v = ((unsigned long long)(w0 >> 5) << 26) | (unsigned long long)(w1 >> 6);
+    return __ull2double_rn(v) * 1.1102230246251565e-16;  // 2^-53
+}
+
+// base(u) * scale + loc, rounded multiply then rounded add (scipy rv_generic.rvs)
+__device__ __forceinline__ double draw_real(const ob2_slot_desc &d, double u) {
+    double b;
+    switch (d.dist) {
+        case OB2_DIST_UNIFORM:
+            b = u;
+            break;
+        case OB2_DIST_RECIPROCAL:
+            b = exp(__dadd_rn(d.p0, __dmul_rn(u, d.p1)));
+            break;
+        case OB2_DIST_NORM:
+            b = normcdfinv(u);
+            break;
+        default:
+            return d.loc;  // scale == 0
+    }
+    return __dadd_rn(__dmul_rn(b, d.scale), d.loc);
+}
+
+// numpy searchsorted(cdf, u, side='right')
+__device__ __forceinline__ int draw_cat(const double *cdf, int k, double u) {
+    int lo = 0, hi = k;
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (cdf[mid] <= u)
+            lo = mid + 1;
+        else
+            hi = mid;
+    }
+    return lo;
+}
+
+// ---- fingerprint pieces
+__device__ __forceinline__ uint64_t mum64(uint64_t x, uint64_t m) {
+    return __umul64hi(x, m) ^ (x * m);
+}
+__device__ __forceinline__ uint64_t fmix64(uint64_t x) {
+    x ^= x >> 33;
+    x *= 0xFF51AFD7ED558CCDull;
+    x ^= x >> 33;
+    x *= 0xC4CEB9FE1A85EC53ull;
+    x ^= x >> 33;
+    return x;
+}
+__device__ __forceinline__ uint64_t canon_f64(double x) {
+    if (x == 0.0) x = 0.0;  // -0.0 -> +0.0
+    return (uint64_t)__double_as_longlong(x);
+}
+struct FpAcc {
+    uint64_t a, b;
+};
+__device__ __forceinline__ void fp_add(FpAcc &acc, const ob2_slot_desc &d, uint64_t w) {
+    acc.a += mum64(w ^ d.hk[0], d.hk[1]);
+    acc.b += mum64(w ^ d.hk[2], d.hk[3]);
+}
+__device__ __forceinline__ void fp_finish(const FpAcc &acc, int n_slots, uint64_t &lo, uint64_t &hi) {
+    lo = fmix64(acc.a ^ ((uint64_t)n_slots * 0x9E3779B97F4A7C15ull));
+    hi = fmix64(acc.b + ((uint64_t)n_slots * 0xC2B2AE3D27D4EB4Full));
+    if (lo == 0) lo = 1;
+}
+
+// ---- streaming vector stores / loads (output is written once and not re-read
+// by this kernel: keep it out of L1)
+__device__ __forceinline__ void st_f64x2(double *p, double a, double b) {
+    asm volatile("st.global.cs.v2.f64 [%0], {%1, %2};" ::"l"(p), "d"(a), "d"(b) : "memory");
+}
+__device__ __forceinline__ void st_i64x2(long long *p, long long a, long long b) {
+    asm volatile("st.global.cs.v2.s64 [%0], {%1, %2};" ::"l"(p), "l"(a), "l"(b) : "memory");
+}
+__device__ __forceinline__ void st_i32x2(int *p, int a, int b) {
+    asm volatile("st.global.cs.v2.s32 [%0], {%1, %2};" ::"l"(p), "r"(a), "r"(b) : "memory");
+}
+__device__ __forceinline__ void st_u64x4(uint64_t *p, uint64_t a, uint64_t b, uint64_t c, uint64_t d) {
+    asm volatile("st.global.cs.v2.u64 [%0], {%1, %2};" ::"l"(p), "l"(a), "l"(b) : "memory");
+    asm volatile("st.global.cs.v2.u64 [%0], {%1, %2};" ::"l"(p + 2), "l"(c), "l"(d) : "memory");
+}
+__device__ __forceinline__ void ld_f64x2(const double *p, double &a, double &b) {
+    asm volatile("ld.global.nc.L1::no_allocate.v2.f64 {%0, %1}, [%2];" : "=d"(a), "=d"(b) : "l"(p));
+}
+__device__ __forceinline__ void ld_i64x2(const long long *p, long long &a, long long &b) {
+    asm volatile("ld.global.nc.L1::no_allocate.v2.s64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "l"(p));
+}
+__device__ __forceinline__ void ld_i32x2(const int *p, int &a, int &b) {
+    asm volatile("ld.global.nc.L1::no_allocate.v2.s32 {%0, %1}, [%2];" : "=r"(a), "=r"(b) : "l"(p));
+}

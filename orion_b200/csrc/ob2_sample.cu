@@ -1,0 +1,266 @@
+// K1: candidate sampling (Philox4x32-10 or injected uniforms -> per-slot
+// inverse CDF), fused with the bounds check, the <=4-attempt rejection and the
+// row fingerprint; and the standalone Space.__contains__ kernel.
+//
+// Mapping: one thread owns OB2_CPT = 2 consecutive candidates and walks the
+// slots in space order.  At any instant a warp therefore works on ONE slot
+// (no divergence on the prior / kind switch) and stores 32 x 16 B = 512
+// contiguous bytes of that slot's column.  Output is columnar [S][n_stride].
+#include "ob2_internal.cuh"
+
+namespace {
+
+
+template <bool WITH_FP>
+__device__ __noinline__ bool retry_dim(const ob2_slot_desc *s_slots, int s_last, uint64_t index, int64_t i,
+                                       int64_t n_stride, char *cols, uint32_t k0, uint32_t k1, FpAcc &tmp) {
+    // Real.sample (space.py:263-270): redraw the whole (shaped) value, attempts 1..3
+    const int first = s_slots[s_last].dim_first;
+    const uint32_t ilo = (uint32_t)index, ihi = (uint32_t)(index >> 32);
+    for (uint32_t a = 1; a < 4; ++a) {
+        bool ok = true;
+        FpAcc t{0, 0};
+        for (int e = first; e <= s_last; ++e) {
+            const ob2_slot_desc &d = s_slots[e];
+            const Philox4 r = philox4x32_10(ilo, ihi, (uint32_t)(e >> 1), a, k0, k1);
+            const double u = (e & 1) ? u53(r.z, r.w) : u53(r.x, r.y);
+            double x = draw_real(d, u);
+            char *col = cols + (int64_t)d.col_units * n_stride;
+            uint64_t w;
+            if (d.kind == OB2_KIND_INTEGER) {
+                x = floor(x);
+                const long long k = __double2ll_rz(x);
+                reinterpret_cast<long long *>(col)[i] = k;
+                w = (uint64_t)k;
+            } else {
+                reinterpret_cast<double *>(col)[i] = x;
+                w = canon_f64(x);
+            }
+            ok &= (x >= d.low) && (x < d.high);
+            if (WITH_FP) fp_add(t, d, w);
+        }
+        tmp = t;
+        if (ok) return true;
+    }
+    return false;
+}
+
+template <bool PHILOX, bool WITH_FP>
+__global__ void __launch_bounds__(OB2_BLOCK)
+sample_kernel(const ob2_slot_desc *__restrict__ g_slots, int n_slots, const double *__restrict__ g_cdf,
+              int cdf_len, int64_t n, int64_t n_stride, uint32_t k0, uint32_t k1, uint64_t base_index,
+              const double *__restrict__ U, char *__restrict__ cols, uint8_t *__restrict__ mask,
+              uint64_t *__restrict__ fp, uint32_t *__restrict__ n_failed) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    ob2_slot_desc *s_slots = reinterpret_cast<ob2_slot_desc *>(smem);
+    double *s_cdf = reinterpret_cast<double *>(smem + (size_t)n_slots * sizeof(ob2_slot_desc));
+    ob2_stage_tables(g_slots, n_slots, g_cdf, cdf_len, s_slots, s_cdf);
+
+    const int64_t i0 = ((int64_t)blockIdx.x * OB2_BLOCK + threadIdx.x) * OB2_CPT;
+    if (i0 >= n) return;
+    const bool has1 = i0 + 1 < n;
+    const uint64_t idx0 = base_index + (uint64_t)i0, idx1 = idx0 + 1;
+
+    FpAcc acc0{0, 0}, acc1{0, 0}, tmp0{0, 0}, tmp1{0, 0};
+    bool ok0 = true, ok1 = true;    // current dimension
+    bool all0 = true, all1 = true;  // whole candidate
+    Philox4 r0{0, 0, 0, 0}, r1{0, 0, 0, 0};
+
+    for (int s = 0; s < n_slots; ++s) {
+        const ob2_slot_desc &d = s_slots[s];
+        double u0, u1;
+        if (PHILOX) {
+            if ((s & 1) == 0) {
+                r0 = philox4x32_10((uint32_t)idx0, (uint32_t)(idx0 >> 32), (uint32_t)(s >> 1), 0u, k0, k1);
+                r1 = philox4x32_10((uint32_t)idx1, (uint32_t)(idx1 >> 32), (uint32_t)(s >> 1), 0u, k0, k1);
+                u0 = u53(r0.x, r0.y);
+                u1 = u53(r1.x, r1.y);
+            } else {
+                u0 = u53(r0.z, r0.w);
+                u1 = u53(r1.z, r1.w);
+            }
+        } else {
+            ld_f64x2(U + (int64_t)s * n_stride + i0, u0, u1);
+        }
+        char *col = cols + (int64_t)d.col_units * n_stride;
+        uint64_t w0, w1;
+        if (d.kind == OB2_KIND_CATEGORICAL) {
+            const double *cdf = s_cdf + d.cdf_off;
+            const int c0 = draw_cat(cdf, d.n_cats, u0);
+            const int c1 = draw_cat(cdf, d.n_cats, u1);
+            st_i32x2(reinterpret_cast<int *>(col) + i0, c0, c1);
+            w0 = (uint64_t)(int64_t)c0;
+            w1 = (uint64_t)(int64_t)c1;
+            ok0 &= c0 < d.n_cats;
+            ok1 &= c1 < d.n_cats;
+        } else {
+            double x0 = draw_real(d, u0);
+            double x1 = draw_real(d, u1);
+            if (d.kind == OB2_KIND_INTEGER) {
+                x0 = floor(x0);  // _Discrete.sample, space.py:294
+                x1 = floor(x1);
+                const long long q0 = __double2ll_rz(x0), q1 = __double2ll_rz(x1);
+                st_i64x2(reinterpret_cast<long long *>(col) + i0, q0, q1);
+                w0 = (uint64_t)q0;
+                w1 = (uint64_t)q1;
+            } else {
+                st_f64x2(reinterpret_cast<double *>(col) + i0, x0, x1);
+                w0 = canon_f64(x0);
+                w1 = canon_f64(x1);
+            }
+            ok0 &= (x0 >= d.low) && (x0 < d.high);  // half-open, space.py:164
+            ok1 &= (x1 >= d.low) && (x1 < d.high);
+        }
+        if (WITH_FP) {
+            fp_add(tmp0, d, w0);
+            fp_add(tmp1, d, w1);
+        }
+        if (d.flags & OB2_SLOT_DIM_LAST) {
+            if (PHILOX && d.kind != OB2_KIND_CATEGORICAL) {
+                if (!ok0) ok0 = retry_dim<WITH_FP>(s_slots, s, idx0, i0, n_stride, cols, k0, k1, tmp0);
+                if (!ok1 && has1) ok1 = retry_dim<WITH_FP>(s_slots, s, idx1, i0 + 1, n_stride, cols, k0, k1, tmp1);
+                if (n_failed != nullptr) {  // 4 misses: the reference raises "Improbable bounds"
+                    const unsigned bad = (ok0 ? 0u : 1u) + ((ok1 || !has1) ? 0u : 1u);
+                    if (bad) atomicAdd(n_failed + d.dim_first, bad);
+                }
+            }
+            all0 &= ok0;
+            all1 &= ok1;
+            if (WITH_FP) {
+                acc0.a += tmp0.a;
+                acc0.b += tmp0.b;
+                acc1.a += tmp1.a;
+                acc1.b += tmp1.b;
+                tmp0 = FpAcc{0, 0};
+                tmp1 = FpAcc{0, 0};
+            }
+            ok0 = ok1 = true;
+        }
+    }
+    if (mask != nullptr) {
+        *reinterpret_cast<uchar2 *>(mask + i0) = make_uchar2(all0 ? 1 : 0, (all1 && has1) ? 1 : 0);
+    }
+    if (WITH_FP) {
+        uint64_t lo0, hi0, lo1, hi1;
+        fp_finish(acc0, n_slots, lo0, hi0);
+        fp_finish(acc1, n_slots, lo1, hi1);
+        if (!has1) lo1 = hi1 = 0;  // padding entry
+        st_u64x4(fp + 2 * i0, lo0, hi0, lo1, hi1);
+    }
+}
+
+// Space.__contains__ over columns.
+__global__ void __launch_bounds__(OB2_BLOCK)
+contains_kernel(const ob2_slot_desc *__restrict__ g_slots, int n_slots, int64_t n, int64_t n_stride,
+                const char *__restrict__ cols, int int_as_f64, uint8_t *__restrict__ mask) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    ob2_slot_desc *s_slots = reinterpret_cast<ob2_slot_desc *>(smem);
+    ob2_stage_tables(g_slots, n_slots, nullptr, 0, s_slots, nullptr);
+    const int64_t i0 = ((int64_t)blockIdx.x * OB2_BLOCK + threadIdx.x) * OB2_CPT;
+    if (i0 >= n) return;
+    const bool has1 = i0 + 1 < n;
+    bool ok0 = true, ok1 = true;
+    for (int s = 0; s < n_slots; ++s) {
+        const ob2_slot_desc &d = s_slots[s];
+        // with int_as_f64 the Integer columns are 8-byte doubles: same width, same offsets
+        const char *col = cols + (int64_t)d.col_units * n_stride;
+        if (d.kind == OB2_KIND_CATEGORICAL) {
+            int c0, c1;
+            ld_i32x2(reinterpret_cast<const int *>(col) + i0, c0, c1);
+            ok0 &= (c0 >= 0) && (c0 < d.n_cats);
+            ok1 &= (c1 >= 0) && (c1 < d.n_cats);
+        } else if (d.kind == OB2_KIND_INTEGER && !int_as_f64) {
+            long long q0, q1;
+            ld_i64x2(reinterpret_cast<const long long *>(col) + i0, q0, q1);
+            const double x0 = __ll2double_rn(q0), x1 = __ll2double_rn(q1);
+            ok0 &= (x0 >= d.low) && (x0 < d.high);
+            ok1 &= (x1 >= d.low) && (x1 < d.high);
+        } else {
+            double x0, x1;
+            ld_f64x2(reinterpret_cast<const double *>(col) + i0, x0, x1);
+            if (d.kind == OB2_KIND_INTEGER) {  // numpy.mod(x, 1) == 0, space.py:344
+                ok0 &= (x0 == floor(x0)) && !isinf(x0);
+                ok1 &= (x1 == floor(x1)) && !isinf(x1);
+            }
+            ok0 &= (x0 >= d.low) && (x0 < d.high);
+            ok1 &= (x1 >= d.low) && (x1 < d.high);
+        }
+    }
+    *reinterpret_cast<uchar2 *>(mask + i0) = make_uchar2(ok0 ? 1 : 0, (ok1 && has1) ? 1 : 0);
+}
+
+template <typename K>
+int prepare_smem(K kernel, size_t smem) {
+    if (smem > 48 * 1024) {
+        return ob2_check_cuda(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
+                              "cudaFuncSetAttribute(smem)");
+    }
+    return OB2_OK;
+}
+
+template <bool PHILOX>
+int launch_sample(const ob2_space *sp, int64_t n, int64_t n_stride, uint64_t seed, uint64_t base_index,
+                  const double *U, void *cols, uint8_t *mask, uint64_t *fp, uint32_t *n_failed, void *stream) {
+    int rc = ob2_check_batch(sp, n, n_stride);
+    if (rc != OB2_OK) return rc;
+    if (cols == nullptr || (!PHILOX && U == nullptr)) {
+        ob2_set_error("sample: null buffer");
+        return OB2_EINVAL;
+    }
+    if (n == 0) return OB2_OK;
+    const int64_t threads = (n + OB2_CPT - 1) / OB2_CPT;
+    const int64_t blocks = (threads + OB2_BLOCK - 1) / OB2_BLOCK;
+    if (blocks > 0x7FFFFFFFll) {
+        ob2_set_error("batch too large for one launch");
+        return OB2_ETOOBIG;
+    }
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
+    if (fp != nullptr) {
+        auto kern = sample_kernel<PHILOX, true>;
+        rc = prepare_smem(kern, sp->smem_bytes);
+        if (rc != OB2_OK) return rc;
+        kern<<<(unsigned)blocks, OB2_BLOCK, sp->smem_bytes, st>>>(sp->d_slots, sp->n_slots, sp->d_cdf, sp->cdf_len, n,
+                                                                   n_stride, k0, k1, base_index, U, (char *)cols, mask,
+                                                                   fp, n_failed);
+    } else {
+        auto kern = sample_kernel<PHILOX, false>;
+        rc = prepare_smem(kern, sp->smem_bytes);
+        if (rc != OB2_OK) return rc;
+        kern<<<(unsigned)blocks, OB2_BLOCK, sp->smem_bytes, st>>>(sp->d_slots, sp->n_slots, sp->d_cdf, sp->cdf_len, n,
+                                                                   n_stride, k0, k1, base_index, U, (char *)cols, mask,
+                                                                   nullptr, n_failed);
+    }
+    return ob2_check_cuda(cudaGetLastError(), "sample_kernel launch");
+}
+
+}  // namespace
+
+extern "C" int ob2_sample(const ob2_space *space, int64_t n, int64_t n_stride, uint64_t seed, uint64_t base_index,
+                          void *cols, uint8_t *mask, uint64_t *fp, uint32_t *n_failed, void *stream) {
+    return launch_sample<true>(space, n, n_stride, seed, base_index, nullptr, cols, mask, fp, n_failed, stream);
+}
+
+extern "C" int ob2_sample_from_uniform(const ob2_space *space, int64_t n, int64_t n_stride, const double *U,
+                                       void *cols, uint8_t *ok, uint64_t *fp, void *stream) {
+    return launch_sample<false>(space, n, n_stride, 0, 0, U, cols, ok, fp, nullptr, stream);
+}
+
+extern "C" int ob2_contains(const ob2_space *space, int64_t n, int64_t n_stride, const void *cols,
+                            int32_t int_as_f64, uint8_t *mask, void *stream) {
+    int rc = ob2_check_batch(space, n, n_stride);
+    if (rc != OB2_OK) return rc;
+    if (cols == nullptr || mask == nullptr) {
+        ob2_set_error("contains: null buffer");
+        return OB2_EINVAL;
+    }
+    if (n == 0) return OB2_OK;
+    const int64_t threads = (n + OB2_CPT - 1) / OB2_CPT;
+    const int64_t blocks = (threads + OB2_BLOCK - 1) / OB2_BLOCK;
+    const size_t smem = (size_t)space->n_slots * sizeof(ob2_slot_desc);
+    rc = prepare_smem(contains_kernel, smem);
+    if (rc != OB2_OK) return rc;
+    contains_kernel<<<(unsigned)blocks, OB2_BLOCK, smem, static_cast<cudaStream_t>(stream)>>>(
+        space->d_slots, space->n_slots, n, n_stride, (const char *)cols, int_as_f64, mask);
+    return ob2_check_cuda(cudaGetLastError(), "contains_kernel launch");
+}

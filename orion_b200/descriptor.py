@@ -1,0 +1,286 @@
+"""Space -> device descriptor compiler and the batch-level device operations.
+
+`compile_space` accepts any object that quacks like the reference's
+``orion.algo.space.Space`` (an ordered mapping of dimensions exposing ``type``,
+``prior``, ``_prior_name``, ``_args``, ``_kwargs``, ``shape``, ``interval()``,
+and for categoricals ``categories`` / ``_probs``) -- i.e. both the reference's
+own classes and the mirror in :mod:`orion_b200.space`.
+
+Everything static about a dimension is resolved here, once, on the host:
+``interval()`` (which the reference recomputes through two scipy ``ppf`` calls
+for every scalar it checks, ``space.py:160``), ``log(a)`` / ``log(b) - log(a)``
+of a loguniform prior, and the categorical cdf exactly as numpy's legacy
+``RandomState.choice`` builds it.  The kernels then only do arithmetic.
+"""
+import ctypes
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import SlotDesc
+
+REQUIREMENTS = ('real', 'integer', 'numerical', None)
+
+_KIND = {'real': _lib.KIND_REAL, 'integer': _lib.KIND_INTEGER, 'categorical': _lib.KIND_CATEGORICAL}
+_OPS = {
+    'real': {'real': _lib.OP_IDENTITY, 'integer': _lib.OP_TO_REAL, 'categorical': _lib.OP_ONEHOT},
+    'integer': {'real': _lib.OP_QUANTIZE, 'integer': _lib.OP_IDENTITY, 'categorical': _lib.OP_ENUMERATE},
+    'numerical': {'real': _lib.OP_IDENTITY, 'integer': _lib.OP_IDENTITY, 'categorical': _lib.OP_ONEHOT},
+    None: {'real': _lib.OP_IDENTITY, 'integer': _lib.OP_IDENTITY, 'categorical': _lib.OP_IDENTITY},
+}
+_NP_DTYPE = {8: {'f': np.float64, 'i': np.int64}, 4: {'i': np.int32}}
+_TORCH_DTYPE = {'f8': torch.float64, 'i8': torch.int64, 'i4': torch.int32}
+
+_M64 = (1 << 64) - 1
+
+
+def _splitmix64(x):
+    x = (x + 0x9E3779B97F4A7C15) & _M64
+    z = x
+    z = ((z ^ (z >> 30)) * 0xBF58476D1CE4E5B9) & _M64
+    z = ((z ^ (z >> 27)) * 0x94D049BB133111EB) & _M64
+    return z ^ (z >> 31)
+
+
+def _hash_keys(slot):
+    """Per-slot fingerprint constants (xor key, odd multiplier) x 2 lanes."""
+    out = []
+    for j in range(4):
+        v = _splitmix64((4 * slot + j + 1) * 0xD6E8FEB86659FD93 & _M64)
+        if j & 1:
+            v |= 1
+        out.append(v)
+    return out
+
+
+def round_up(n, m=32):
+    return (int(n) + m - 1) // m * m
+
+
+def _prior_params(dim):
+    """(dist code, p0, p1, loc, scale) of a Real/Integer dimension."""
+    name = dim._prior_name
+    try:
+        args, loc, scale, _ = dim.prior._parse_args_rvs(*dim._args, size=None, **dim._kwargs)
+    except TypeError as exc:
+        raise TypeError("Parameter '{}': incorrect arguments for prior '{}': {}".format(dim.name, name, exc))
+    loc, scale = float(loc), float(scale)
+    if not (scale >= 0) or not np.all(dim.prior._argcheck(*args)):
+        raise ValueError("Domain error in arguments of prior '{}' of '{}'".format(name, dim.name))
+    if scale == 0:
+        return _lib.DIST_CONST, 0.0, 0.0, loc, scale
+    if name == 'uniform':
+        return _lib.DIST_UNIFORM, 0.0, 0.0, loc, scale
+    if name in ('reciprocal', 'loguniform'):
+        a, b = float(args[0]), float(args[1])
+        la = np.log(a)
+        return _lib.DIST_RECIPROCAL, float(la), float(np.log(b) - la), loc, scale
+    if name == 'norm':
+        return _lib.DIST_NORM, 0.0, 0.0, loc, scale
+    raise NotImplementedError(
+        "Dimension '{}': prior '{}' has no device inverse CDF yet (supported: uniform, "
+        "reciprocal/loguniform, norm). There is no CPU fallback.".format(dim.name, name))
+
+
+class CompiledSpace(object):
+    """A Space compiled for the device, under one transform requirement."""
+
+    def __init__(self, space, requirement=None, quantize='round', device=None):
+        if requirement not in REQUIREMENTS:
+            raise TypeError("Unsupported requirement: {}".format(requirement))
+        if quantize not in ('round', 'floor'):
+            raise ValueError("quantize must be 'round' or 'floor'")
+        self.lib = _lib.load()
+        self.requirement = requirement
+        self.device = torch.device('cuda', torch.cuda.current_device()) if device is None else torch.device(device)
+        dims = list(space.values())
+        if not dims:
+            raise ValueError("cannot compile an empty Space")
+        self.dim_names = [d.name for d in dims]
+        self.dim_kinds = ['real' if d.type == 'dimension' else d.type for d in dims]
+        self.dim_shapes = [tuple(d.shape) for d in dims]
+        self.dim_categories = [tuple(d.categories) if d.type == 'categorical' else None for d in dims]
+        self.dim_first = []            # first slot of each dimension
+        self.dim_bounds = []
+        slots = []
+        cdf = []
+        col_units = t_units = 0
+        self.col_meta = []             # per slot: (byte offset units, numpy dtype str)
+        self.tcol_meta = []            # per transformed column
+        for d_idx, dim in enumerate(dims):
+            kind = dim.type
+            if kind == 'dimension':     # bare `Dimension`: a Real without extra bounds
+                kind = 'real'
+            if kind not in _KIND:
+                raise TypeError("Dimension '{}' of type '{}' cannot be compiled".format(dim.name, kind))
+            k = int(np.prod(dim.shape, dtype=np.int64)) if len(dim.shape) else 1
+            first = len(slots)
+            self.dim_first.append(first)
+            if kind == 'categorical':
+                probs = np.asarray(dim._probs, dtype=np.float64)
+                c = probs.cumsum()
+                c /= c[-1]
+                cdf_off = len(cdf)
+                cdf.extend(c.tolist())
+                n_cats = len(dim.categories)
+                dist = p0 = p1 = loc = scale = 0
+                low, high = 0.0, float(n_cats)
+            else:
+                dist, p0, p1, loc, scale = _prior_params(dim)
+                low, high = dim.interval()
+                low, high = float(low), float(high)
+                cdf_off = n_cats = 0
+            self.dim_bounds.append((low, high))
+            op = _OPS[requirement][kind]
+            if op == _lib.OP_ONEHOT:
+                width, t_elem, t_dt = (1 if n_cats <= 2 else n_cats), 8, 'f8'
+            elif op in (_lib.OP_QUANTIZE,):
+                width, t_elem, t_dt = 1, 8, 'i8'
+            elif op == _lib.OP_TO_REAL:
+                width, t_elem, t_dt = 1, 8, 'f8'
+            else:
+                width = 1
+                t_elem = 4 if kind == 'categorical' else 8
+                t_dt = {'real': 'f8', 'integer': 'i8', 'categorical': 'i4'}[kind]
+            elem = 4 if kind == 'categorical' else 8
+            dt = {'real': 'f8', 'integer': 'i8', 'categorical': 'i4'}[kind]
+            for e in range(k):
+                sd = SlotDesc()
+                s = len(slots)
+                sd.kind, sd.dist = _KIND[kind], dist
+                sd.dim_first = first
+                sd.flags = _lib.SLOT_DIM_LAST if e == k - 1 else 0
+                sd.n_cats, sd.cdf_off = n_cats, cdf_off
+                sd.col_units, sd.t_units = col_units, t_units
+                sd.t_op = op
+                sd.t_flags = _lib.TFLAG_FLOOR if quantize == 'floor' else 0
+                sd.t_width = width
+                sd.p0, sd.p1, sd.loc, sd.scale = p0, p1, loc, scale
+                sd.low, sd.high = low, high
+                for j, v in enumerate(_hash_keys(s)):
+                    sd.hk[j] = v
+                slots.append(sd)
+                self.col_meta.append((col_units, dt))
+                for j in range(width):
+                    self.tcol_meta.append((t_units + j * t_elem, t_dt, s))
+                col_units += elem
+                t_units += t_elem * width
+        self.n_slots = len(slots)
+        self.n_tcols = len(self.tcol_meta)
+        self.row_bytes = col_units
+        self.trow_bytes = t_units
+        arr = (SlotDesc * self.n_slots)(*slots)
+        cdf_arr = (ctypes.c_double * max(1, len(cdf)))(*cdf)
+        handle = ctypes.c_void_p()
+        with torch.cuda.device(self.device):
+            _lib.check(self.lib.ob2_space_create(arr, self.n_slots, cdf_arr, len(cdf), ctypes.byref(handle)))
+        self.handle = handle
+        assert self.lib.ob2_space_row_bytes(handle) == self.row_bytes
+        assert self.lib.ob2_space_trow_bytes(handle) == self.trow_bytes
+
+    def __del__(self):
+        handle = getattr(self, 'handle', None)
+        if handle:
+            try:
+                self.lib.ob2_space_destroy(handle)
+            except Exception:      # interpreter shutdown
+                pass
+            self.handle = None
+
+    # ------------------------------------------------------------ buffers
+    def _stream(self):
+        return ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def empty_columns(self, n, transformed=False):
+        """Uninitialised column block for n candidates."""
+        from .columns import ColumnBatch
+        n_stride = round_up(max(int(n), 1))
+        row = self.trow_bytes if transformed else self.row_bytes
+        buf = torch.empty(row * n_stride, dtype=torch.uint8, device=self.device)
+        return ColumnBatch(self, int(n), n_stride, buf, transformed)
+
+    # ------------------------------------------------------------ kernels
+    def sample(self, n, seed, base_index=0, with_mask=True, with_fingerprint=False, out=None):
+        """Philox-mode Space.sample: returns a ColumnBatch (device)."""
+        batch = out if out is not None else self.empty_columns(n)
+        assert not batch.transformed and batch.n == n
+        ns = batch.n_stride
+        if with_mask and batch.mask is None:
+            batch.mask = torch.empty(ns, dtype=torch.uint8, device=self.device)
+        if with_fingerprint and batch.fp is None:
+            batch.fp = torch.empty((ns, 2), dtype=torch.int64, device=self.device)
+        if batch.n_failed is None:
+            batch.n_failed = torch.zeros(self.n_slots, dtype=torch.int32, device=self.device)
+        else:
+            batch.n_failed.zero_()
+        _lib.check(self.lib.ob2_sample(
+            self.handle, n, ns, int(seed) & _M64, int(base_index) & _M64, batch.buf.data_ptr(),
+            batch.mask.data_ptr() if with_mask else None,
+            batch.fp.data_ptr() if with_fingerprint else None,
+            batch.n_failed.data_ptr(), self._stream()))
+        return batch
+
+    def sample_from_uniform(self, U, n=None, with_fingerprint=False):
+        """Parity mode: U is a float64 tensor [n_slots][n_stride] (device)."""
+        assert U.dtype == torch.float64 and U.is_cuda and U.dim() == 2 and U.shape[0] == self.n_slots
+        ns = U.shape[1]
+        if ns % 32:
+            raise ValueError("U must be padded to a multiple of 32 columns")
+        n = ns if n is None else int(n)
+        batch = self.empty_columns(ns)
+        batch.n = n
+        batch.mask = torch.empty(ns, dtype=torch.uint8, device=self.device)
+        if with_fingerprint:
+            batch.fp = torch.empty((ns, 2), dtype=torch.int64, device=self.device)
+        _lib.check(self.lib.ob2_sample_from_uniform(
+            self.handle, n, ns, U.data_ptr(), batch.buf.data_ptr(), batch.mask.data_ptr(),
+            batch.fp.data_ptr() if with_fingerprint else None, self._stream()))
+        return batch
+
+    def contains(self, batch, int_as_f64=False):
+        """Space.__contains__ over a ColumnBatch -> uint8 tensor [n]."""
+        assert not batch.transformed
+        mask = torch.empty(batch.n_stride, dtype=torch.uint8, device=self.device)
+        _lib.check(self.lib.ob2_contains(self.handle, batch.n, batch.n_stride, batch.buf.data_ptr(),
+                                         1 if int_as_f64 else 0, mask.data_ptr(), self._stream()))
+        return mask[:batch.n]
+
+    def transform(self, batch, out=None):
+        assert not batch.transformed
+        tb = out if out is not None else self.empty_columns(batch.n, transformed=True)
+        assert tb.transformed and tb.n_stride == batch.n_stride
+        _lib.check(self.lib.ob2_transform(self.handle, batch.n, batch.n_stride, batch.buf.data_ptr(),
+                                          tb.buf.data_ptr(), self._stream()))
+        return tb
+
+    def reverse(self, tbatch, out=None):
+        assert tbatch.transformed
+        b = out if out is not None else self.empty_columns(tbatch.n)
+        assert not b.transformed and b.n_stride == tbatch.n_stride
+        _lib.check(self.lib.ob2_reverse(self.handle, tbatch.n, tbatch.n_stride, tbatch.buf.data_ptr(),
+                                        b.buf.data_ptr(), self._stream()))
+        return b
+
+    def fingerprint(self, batch):
+        assert not batch.transformed
+        if batch.fp is None:
+            batch.fp = torch.empty((batch.n_stride, 2), dtype=torch.int64, device=self.device)
+        _lib.check(self.lib.ob2_fingerprint(self.handle, batch.n, batch.n_stride, batch.buf.data_ptr(),
+                                            batch.fp.data_ptr(), self._stream()))
+        return batch.fp
+
+
+_CACHE_ATTR = '_ob2_compiled'
+
+
+def compile_space(space, requirement=None, quantize='round', device=None):
+    """Compile (and memoise on the Space object) for the given requirement."""
+    key = (requirement, quantize, str(device) if device is not None else torch.cuda.current_device(),
+           tuple(id(d) for d in space.values()))
+    cache = space.__dict__.setdefault(_CACHE_ATTR, {}) if hasattr(space, '__dict__') else {}
+    hit = cache.get(key)
+    if hit is None:
+        hit = CompiledSpace(space, requirement, quantize, device)
+        cache[key] = hit
+    return hit

@@ -1,0 +1,140 @@
+"""Sharded trial history: dedup across the GPUs of one box.
+
+One process per GPU (``torch.distributed``).  Sampling, bounds checks and the
+transform chain shard trivially (rank g owns candidate indices
+``[g * n, (g + 1) * n)``) and never communicate.  Dedup has one real exchange:
+the history hash set is partitioned by fingerprint (owner = ``fp.hi % world``),
+so every rank
+
+  1. buckets its fingerprints by owner (``ob2_bucket_by_owner``),
+  2. all-to-alls ``(fp128, u32 global order key)`` to the owners (NCCL),
+  3. dedups what it received against its shard, first-wins by global
+     candidate index (``ob2_set_dedup`` with the received order keys),
+  4. all-to-alls the 1-byte verdicts back, and
+  5. scatters them into its local keep mask (``ob2_scatter_verdict``).
+
+Equal rows share a fingerprint, hence an owner, so duplicates that straddle
+GPUs resolve exactly as on one GPU.  Buckets have fixed capacity (mean + slack;
+fingerprints are uniform) and are zero-padded, so no size pre-exchange is
+needed; an overflow is detected from the counts and raised.
+
+The kernel calls are injected (``ops``) so the choreography can be exercised
+on CPU with the ``gloo`` backend in the tests.
+"""
+import ctypes
+import math
+
+import torch
+import torch.distributed as dist
+
+from . import _lib
+
+
+def bucket_capacity(n, world):
+    """Slots per (source, owner) bucket: mean + 5 % + 6 sigma + 64."""
+    mean = n / float(world)
+    return int(mean * 1.05 + 6.0 * math.sqrt(max(mean, 1.0))) + 64
+
+
+class DeviceOps(object):
+    """The CUDA kernels behind the exchange (product path)."""
+
+    def __init__(self, device):
+        self.lib = _lib.load()
+        self.device = torch.device(device)
+
+    def _stream(self):
+        return ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def bucket(self, fp, n, key_base, world, cap, out):
+        out_fp, out_key, out_src, counts = out
+        _lib.check(self.lib.ob2_bucket_by_owner(n, fp.data_ptr(), key_base, world, cap, out_fp.data_ptr(),
+                                                out_key.data_ptr(), out_src.data_ptr(), counts.data_ptr(),
+                                                self._stream()))
+
+    def dedup(self, history, fp, order, keep):
+        history.dedup_fingerprints(fp, fp.shape[0], order=order, keep=keep)
+
+    def insert(self, history, fp):
+        history.insert_fingerprints(fp, fp.shape[0])
+
+    def scatter(self, out_src, verdict, out_fp, keep):
+        _lib.check(self.lib.ob2_scatter_verdict(out_src.numel(), out_src.data_ptr(), verdict.data_ptr(),
+                                                out_fp.data_ptr(), keep.data_ptr(), self._stream()))
+
+
+class ShardedHistory(object):
+    """The history shard of this rank plus the exchange around it."""
+
+    def __init__(self, history, ops=None, group=None, device=None):
+        self.history = history
+        self.group = group
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.device = torch.device(device) if device is not None else history.device
+        self.ops = ops if ops is not None else DeviceOps(self.device)
+        self._bufs = {}
+
+    def _buffers(self, n):
+        cap = bucket_capacity(n, self.world)
+        key = (n, cap)
+        if key not in self._bufs:
+            w, dev = self.world, self.device
+            self._bufs = {key: dict(
+                cap=cap,
+                out_fp=torch.empty((w, cap, 2), dtype=torch.int64, device=dev),
+                out_key=torch.empty((w, cap), dtype=torch.int32, device=dev),
+                out_src=torch.empty((w, cap), dtype=torch.int32, device=dev),
+                counts=torch.zeros(w, dtype=torch.int32, device=dev),
+                in_fp=torch.empty((w, cap, 2), dtype=torch.int64, device=dev),
+                in_key=torch.empty((w, cap), dtype=torch.int32, device=dev),
+                verdict=torch.empty(w * cap, dtype=torch.uint8, device=dev),
+                back=torch.empty(w * cap, dtype=torch.uint8, device=dev),
+            )}
+        return self._bufs[key]
+
+    def _route(self, fp, n, per_rank_n):
+        """Steps 1-2: returns the buffers with ``in_fp`` / ``in_key`` filled."""
+        b = self._buffers(n)
+        key_base = self.rank * per_rank_n
+        if (self.world - 1) * per_rank_n + n >= 2 ** 32 - 1:
+            raise ValueError("global candidate index does not fit the 32-bit order key")
+        self.ops.bucket(fp, n, key_base, self.world, b['cap'], (b['out_fp'], b['out_key'], b['out_src'], b['counts']))
+        dist.all_to_all_single(b['in_fp'], b['out_fp'], group=self.group)
+        dist.all_to_all_single(b['in_key'], b['out_key'], group=self.group)
+        return b
+
+    def _check_overflow(self, b):
+        worst = int(b['counts'].max().item())
+        if worst > b['cap']:
+            raise RuntimeError("exchange bucket overflow: %d fingerprints for one owner, capacity %d"
+                               % (worst, b['cap']))
+
+    def dedup(self, fp, n, per_rank_n=None, keep=None, check=True):
+        """keep mask (uint8 [>= n]) for this rank's ``n`` fingerprints
+        (int64 [m][2], m >= n), deduplicated against the whole sharded history
+        and against every rank's batch, first global index wins."""
+        per_rank_n = n if per_rank_n is None else per_rank_n
+        if keep is None:
+            keep = torch.empty(fp.shape[0], dtype=torch.uint8, device=self.device)
+        if self.world == 1:
+            self.ops.dedup(self.history, fp[:n], None, keep)
+            return keep
+        b = self._route(fp, n, per_rank_n)
+        self.ops.dedup(self.history, b['in_fp'].view(-1, 2), b['in_key'].view(-1), b['verdict'])
+        dist.all_to_all_single(b['back'], b['verdict'], group=self.group)
+        keep.zero_()
+        self.ops.scatter(b['out_src'].view(-1), b['back'], b['out_fp'].view(-1, 2), keep)
+        if check:
+            self._check_overflow(b)
+        return keep
+
+    def insert(self, fp, n, check=True):
+        """Add this rank's ``n`` fingerprints to whichever shards own them."""
+        if self.world == 1:
+            self.ops.insert(self.history, fp[:n])
+            return
+        b = self._route(fp, n, n)
+        self.ops.insert(self.history, b['in_fp'].view(-1, 2))
+        if check:
+            self._check_overflow(b)

@@ -1,0 +1,384 @@
+"""Search-space objects with the reference's interface, backed by the device.
+
+Host-side mirror of ``src/orion/algo/space.py`` (reference): the same class
+names (`Dimension`, `Real`, `Integer`, `Categorical`, `Space`), constructor
+arguments, error behaviour and return types, so code written against
+``orion.algo.space`` runs unchanged.  What differs is where the work happens:
+
+* ``sample`` draws on the GPU (Philox4x32-10 -> inverse CDF -> fused bounds
+  check and <=4-attempt rejection; :mod:`orion_b200.csrc`), not through
+  ``scipy.rvs`` one scalar at a time.  A seed (None / int / RandomState, as in
+  the reference) selects the Philox key, so draws are reproducible under the
+  same seeding discipline but are not MT19937's values.
+* ``in`` checks run the ``ob2_contains`` kernel with bounds resolved once.
+* ``Space.sample_columns`` / ``Space.contains_columns`` are the added
+  tensor-returning fast path; ``Space.sample`` converts the same device result
+  to the reference's list of tuples.
+
+scipy is used on the host only for what is static per dimension (argument
+parsing, ``interval``), exactly the calls the reference makes.
+"""
+from collections import OrderedDict
+
+import numpy
+from scipy._lib._util import check_random_state
+from scipy.stats import distributions
+
+from .columns import ColumnBatch
+from .descriptor import compile_space
+
+_BANNED = {
+    'random_state': "random_state/seed cannot be set in a parameter's definition! Set seed globally!",
+    'seed': "random_state/seed cannot be set in a parameter's definition! Set seed globally!",
+    'discrete': "Do not use kwarg 'discrete' on `Dimension`, use pure `_Discrete` class instead!",
+    'size': "Use 'shape' keyword only instead of 'size'.",
+}
+
+
+def philox_key(seed):
+    """64-bit Philox key from the reference's ``seed`` argument
+    (None -> numpy's global RNG, int -> a fresh RandomState(int),
+    RandomState -> drawn from it, advancing it; space.py:118-127, 482)."""
+    rng = check_random_state(seed)
+    if hasattr(rng, 'randint'):
+        w = rng.randint(0, 2 ** 32, size=2, dtype=numpy.uint64)
+    else:                       # numpy.random.Generator
+        w = rng.integers(0, 2 ** 32, size=2, dtype=numpy.uint64)
+    return int(w[0]) | (int(w[1]) << 32)
+
+
+class _OneDim(OrderedDict):
+    """A throw-away single-dimension space used to compile one Dimension."""
+
+
+class Dimension(object):
+    """Base class for search space dimensions (reference space.py:47-196).
+
+    Attributes
+    ----------
+    name : str or None
+    type : str -- lower-cased class name ('real', 'integer', 'categorical')
+    prior : scipy.stats rv_generic instance
+    shape : tuple
+    """
+
+    def __init__(self, name, prior, *args, **kwargs):
+        self._name = None
+        self.name = name
+        for key in ('random_state', 'seed', 'discrete'):
+            if key in kwargs:
+                raise ValueError(_BANNED[key])
+        if isinstance(prior, str):
+            self._prior_name = prior
+            self.prior = getattr(distributions, prior)
+        else:
+            self._prior_name = prior.name
+            self.prior = prior
+        if 'size' in kwargs:
+            raise ValueError(_BANNED['size'])
+        self._args = args
+        self._kwargs = kwargs
+        self._shape = self._kwargs.pop('shape', None)
+        self._compiled_self = None
+
+    # -- device plumbing ---------------------------------------------------
+    def _compiled(self):
+        """This dimension compiled as a one-dimension space (cached)."""
+        if self._compiled_self is None:
+            solo = _OneDim()
+            solo[self.name or '_'] = self
+            self._compiled_self = compile_space(solo)
+        return self._compiled_self
+
+    def _column_values(self, point):
+        """Flatten one value of this dimension into per-slot scalars, or None
+        when its shape does not fit (``point_.shape != self.shape`` -> False,
+        space.py:162)."""
+        try:
+            arr = numpy.asarray(point, dtype=numpy.float64)
+        except (TypeError, ValueError):
+            return None
+        if arr.shape != self.shape:
+            return None
+        return arr.reshape(-1)
+
+    def _from_columns(self, cols, i):
+        """Value i of this dimension from its host columns (numpy scalars for
+        shape (), ndarrays otherwise -- what scipy's rvs hands back)."""
+        if self.shape == ():
+            return cols[0][i]
+        return numpy.stack([c[i] for c in cols]).reshape(self.shape)
+
+    # -- reference interface ------------------------------------------------
+    def sample(self, n_samples=1, seed=None):
+        """Draw ``n_samples`` values from the prior; returns a list.
+
+        ``seed``: None | int | numpy.random.RandomState, as in the reference
+        (space.py:110-136).  An int re-creates the same key on every call, so
+        the same values come back; pass a RandomState to advance.
+        """
+        compiled = self._compiled()
+        batch = compiled.sample(n_samples, philox_key(seed), with_mask=False)
+        _raise_if_improbable(batch, [self])
+        cols = batch.to_numpy()
+        return [self._from_columns(cols, i) for i in range(n_samples)]
+
+    def interval(self, alpha=1.0):
+        """(low, high) of the prior; low inclusive, high exclusive."""
+        return self.prior.interval(alpha, *self._args, **self._kwargs)
+
+    def __contains__(self, point):
+        vals = self._column_values(point)
+        if vals is None:
+            return False
+        compiled = self._compiled()
+        batch = ColumnBatch.from_numpy(compiled, [numpy.asarray([v]) for v in vals], int_as_f64=True)
+        return bool(compiled.contains(batch, int_as_f64=True)[0].item())
+
+    def __repr__(self):
+        return "{0}(name={1}, prior={{{2}: {3}, {4}}}, shape={5})".format(
+            self.__class__.__name__, self.name, self._prior_name, self._args, self._kwargs, self.shape)
+
+    @property
+    def name(self):
+        return self._name
+
+    @name.setter
+    def name(self, value):
+        if value is not None and not isinstance(value, str):
+            raise TypeError("Dimension's name must be either string or None. "
+                            "Provided: {}, of type: {}".format(value, type(value)))
+        self._name = value
+
+    @property
+    def type(self):
+        return self.__class__.__name__.lower()
+
+    @property
+    def shape(self):
+        size = self.prior._parse_args_rvs(*self._args, size=self._shape, **self._kwargs)[3]  # pylint:disable=protected-access
+        return tuple(int(s) for s in size)
+
+
+class Real(Dimension):
+    """Real-valued dimension with optional ``low`` (inclusive) / ``high``
+    (exclusive) clipping of the prior's support (reference space.py:199-276)."""
+
+    def __init__(self, name, prior, *args, **kwargs):
+        self._low = kwargs.pop('low', -numpy.inf)
+        self._high = kwargs.pop('high', numpy.inf)
+        if self._high <= self._low:
+            raise ValueError("Lower bound {} has to be less than upper bound {}".format(self._low, self._high))
+        super(Real, self).__init__(name, prior, *args, **kwargs)
+
+    def interval(self, alpha=1.0):
+        prior_low, prior_high = super(Real, self).interval(alpha)
+        return (max(prior_low, self._low), min(prior_high, self._high))
+
+
+class _Discrete(Dimension):
+    """Floors draws and widens the interval to integers (space.py:279-319)."""
+
+    def interval(self, alpha=1.0):
+        low, high = super(_Discrete, self).interval(alpha)
+        int_low = int(numpy.floor(low)) if numpy.isfinite(low) else -numpy.inf
+        int_high = int(numpy.floor(high)) if numpy.isfinite(high) else numpy.inf
+        if int_high < high:     # upper bound stays exclusive
+            int_high += 1
+        return (int_low, int_high)
+
+
+class Integer(Real, _Discrete):
+    """Integer dimension: ``floor`` of a draw from any prior, bounds checked on
+    the floored value, membership requires integrality (space.py:322-347).
+    Device dtype int64."""
+
+
+class Categorical(Dimension):
+    """Categorical dimension over arbitrary Python objects (space.py:350-446).
+
+    ``categories`` is an iterable (uniform probabilities) or a dict
+    category -> probability.  On the device a value is its int32 index into
+    ``self.categories``.
+    """
+
+    def __init__(self, name, categories, **kwargs):
+        if isinstance(categories, dict):
+            self.categories = tuple(categories.keys())
+            self._probs = tuple(categories.values())
+        else:
+            self.categories = tuple(categories)
+            self._probs = tuple(numpy.tile(1. / len(self.categories), len(self.categories)))
+        # rv_discrete validates that the probabilities sum to one (ValueError otherwise)
+        prior = distributions.rv_discrete(values=(list(range(len(self.categories))), self._probs))
+        super(Categorical, self).__init__(name, prior, **kwargs)
+
+    def _index_of(self, value):
+        """Position of ``value`` in ``categories`` by ``==`` (so '2' is not 2),
+        -1 when absent."""
+        try:
+            return self.categories.index(value)
+        except ValueError:
+            return -1
+
+    def _column_values(self, point):
+        arr = numpy.asarray(point, dtype=object)
+        if arr.shape != self.shape:
+            return None
+        return numpy.asarray([self._index_of(v) for v in arr.reshape(-1)], dtype=numpy.int32)
+
+    def _from_columns(self, cols, i):
+        if self.shape == ():
+            return self.categories[cols[0][i]]
+        out = numpy.empty(len(cols), dtype=object)
+        for e, c in enumerate(cols):
+            out[e] = self.categories[c[i]]
+        return out.reshape(self.shape)
+
+    def interval(self, alpha=1.0):
+        raise RuntimeError("Categories have no ``interval`` (as they are not ordered).\n"
+                           "Use ``self.categories`` instead.")
+
+    def __repr__(self):
+        pairs = list(zip(self.categories, self._probs))
+        fmt = ['{0}: {1:.2f}'.format(c, p) for c, p in pairs]
+        if len(fmt) > 5:
+            fmt = fmt[:2] + ['...'] + fmt[-2:]
+        return "Categorical(name={0}, prior={{{1}}}, shape={2})".format(self.name, ', '.join(fmt), self.shape)
+
+
+def _raise_if_improbable(batch, dims):
+    """Surface the device's rejection counters as the reference's ValueError
+    (space.py:272-274).  One small device->host read."""
+    failed = batch.n_failed.cpu().numpy()
+    if not failed.any():
+        return
+    first_slot = int(numpy.nonzero(failed)[0][0])
+    d_idx = batch.compiled.dim_first.index(first_slot)
+    dim = dims[d_idx]
+    raise ValueError("Improbable bounds: (low={0}, high={1}). "
+                     "Please make interval larger.".format(dim._low, dim._high))
+
+
+class Space(OrderedDict):
+    """Ordered mapping name -> Dimension (reference space.py:449-550)."""
+
+    def register(self, dimension):
+        self[dimension.name] = dimension
+
+    # -- tensor fast path ---------------------------------------------------
+    def compiled(self, requirement=None, quantize='round'):
+        return compile_space(self, requirement, quantize)
+
+    def sample_columns(self, n_samples=1, seed=None, base_index=0, with_fingerprint=False, check=True):
+        """Device-resident draw: returns a :class:`ColumnBatch` whose ``mask``
+        is the fused ``point in space``.  ``check=False`` skips the
+        synchronising read of the rejection counters."""
+        batch = self.compiled().sample(n_samples, philox_key(seed), base_index=base_index,
+                                       with_mask=True, with_fingerprint=with_fingerprint)
+        if check:
+            _raise_if_improbable(batch, list(self.values()))
+        return batch
+
+    def contains_columns(self, batch):
+        """uint8 device tensor: ``point in space`` for every row of ``batch``."""
+        return self.compiled().contains(batch)
+
+    # -- reference interface ------------------------------------------------
+    def sample(self, n_samples=1, seed=None):
+        """List of ``n_samples`` tuples, one value per dimension in space
+        order (space.py:456-484)."""
+        if not self:
+            return []
+        batch = self.sample_columns(n_samples, seed)
+        return self.rows_from_columns(batch.to_numpy(), n_samples)
+
+    def rows_from_columns(self, host_cols, n):
+        """Host columns -> the reference's list of tuples."""
+        per_dim = []
+        s = 0
+        for dim in self.values():
+            k = int(numpy.prod(dim.shape, dtype=numpy.int64)) if dim.shape else 1
+            cols = host_cols[s:s + k]
+            per_dim.append([dim._from_columns(cols, i) for i in range(n)])
+            s += k
+        return list(zip(*per_dim))
+
+    def columns_from_rows(self, points):
+        """List of tuples -> (host columns, row_ok) where row_ok[i] is False
+        when row i has the wrong arity or a mis-shaped value.  Integer values
+        travel as float64 so the device can check integrality."""
+        dims = list(self.values())
+        widths = [int(numpy.prod(d.shape, dtype=numpy.int64)) if d.shape else 1 for d in dims]
+        n = len(points)
+        row_ok = numpy.ones(n, dtype=bool)
+        cols = [numpy.zeros(n, dtype=numpy.int32 if d.type == 'categorical' else numpy.float64)
+                for d, w in zip(dims, widths) for _ in range(w)]
+        for i, point in enumerate(points):
+            s = 0
+            # zip() semantics of the reference: extra/missing components are ignored
+            for j, dim in enumerate(dims):
+                if j >= len(point):
+                    break
+                vals = dim._column_values(point[j])
+                if vals is None:
+                    row_ok[i] = False
+                else:
+                    for e, v in enumerate(vals):
+                        cols[s + e][i] = v
+                s += widths[j]
+            if len(point) < len(dims):
+                # unchecked dimensions: fill with an always-valid value
+                for j in range(len(point), len(dims)):
+                    off = sum(widths[:j])
+                    low, high = self.compiled().dim_bounds[j]
+                    fill = low if numpy.isfinite(low) else (high - 1 if numpy.isfinite(high) else 0)
+                    for e in range(widths[j]):
+                        cols[off + e][i] = fill
+        return cols, row_ok
+
+    def contains_points(self, points):
+        """Batched ``point in space`` for a list of tuples -> list of bool."""
+        if not self:
+            return [False] * len(points)
+        cols, row_ok = self.columns_from_rows(points)
+        compiled = self.compiled()
+        batch = ColumnBatch.from_numpy(compiled, cols, int_as_f64=True)
+        mask = compiled.contains(batch, int_as_f64=True).cpu().numpy().astype(bool)
+        return list(mask & row_ok)
+
+    def interval(self, alpha=1.0):
+        return [dim.categories if dim.type == 'categorical' else dim.interval(alpha)
+                for dim in self.values()]
+
+    def __getitem__(self, key):
+        if isinstance(key, str):
+            return super(Space, self).__getitem__(key)
+        return list(self.values())[key]
+
+    def __setitem__(self, key, value):
+        if not isinstance(key, str):
+            raise TypeError("Keys registered to Space must be string types. Provided: {}".format(key))
+        if not isinstance(value, Dimension):
+            raise TypeError("Values registered to Space must be Dimension types. Provided: {}".format(value))
+        if key in self:
+            raise ValueError("There is already a Dimension registered with this name. "
+                             "Register it with another name. Provided: {}".format(key))
+        self.__dict__.pop('_ob2_compiled', None)      # descriptor cache is stale now
+        super(Space, self).__setitem__(key, value)
+
+    def __contains__(self, value):
+        """Dimension name registered? / point within the bounds of the space?"""
+        if isinstance(value, str):
+            return super(Space, self).__contains__(value)
+        try:
+            len(value)
+        except TypeError as exc:
+            raise TypeError("Can check only for dimension names or "
+                            "for tuples with parameter values.") from exc
+        if not self:
+            return False
+        return bool(self.contains_points([tuple(value)])[0])
+
+    def __repr__(self):
+        return "Space([{}])".format(',\n       '.join(map(str, self.values())))

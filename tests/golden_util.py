@@ -38,3 +38,37 @@ def load(name):
     out['probes'] = [z[k] for k in sorted(f for f in z.files if f.startswith('probe0') or f.startswith('probe1'))]
     out['probe_verdict'] = z['probe_verdict']
     return out
+
+
+def product_space(dims):
+    """The same fixture spec as an orion_b200 Space (imports the product lazily)."""
+    from collections import OrderedDict
+    from orion_b200.space import Categorical, Integer, Real, Space
+    space = Space()
+    for d in dims:
+        kw = dict(d.get('kwargs', {}))
+        if d.get('shape'):
+            kw['shape'] = tuple(d['shape'])
+        if d['kind'] == 'categorical':
+            cats = [tuple(c) if isinstance(c, list) else c for c in d['categories']]
+            arg = OrderedDict(zip(cats, d['probs'])) if d.get('probs') else cats
+            space.register(Categorical(d['name'], arg, **kw))
+            continue
+        if 'low' in d:
+            kw['low'] = d['low']
+        if 'high' in d:
+            kw['high'] = d['high']
+        klass = Real if d['kind'] == 'real' else Integer
+        space.register(klass(d['name'], d['prior'], *d['args'], **kw))
+    return space
+
+
+def stream_to_U(specs, n, stream):
+    """Dimension-major reference stream (rejection-free) -> U[S][n]."""
+    U = []
+    pos = 0
+    for spec in specs:
+        k = spec.n_slots
+        U.extend(stream[pos:pos + n * k].reshape(n, k).T)
+        pos += n * k
+    return np.stack(U)

@@ -1,0 +1,259 @@
+"""Parity of the CUDA path (through the C ABI) against the reference's golden
+vectors and the numpy oracle.  Bar: bit-exact for Integer / Categorical /
+one-hot / reverse / fingerprints / keep masks and for uniform Real; <= 1e-6
+relative (fp64) for loguniform and normal."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import space_oracle as so
+from tests import golden_util as gu
+from tests.spec_util import specs_from_space
+
+pytestmark = pytest.mark.gpu
+
+RTOL = 1e-6
+
+
+def _pad_U(U):
+    S, n = U.shape
+    ns = (n + 31) // 32 * 32
+    out = np.full((S, ns), 0.5)
+    out[:, :n] = U
+    return torch.from_numpy(out).cuda(), n
+
+
+def _compare_cols(specs, got, want):
+    table = so.slot_table(specs)
+    assert len(got) == len(want) == len(table)
+    for s, (d, _e) in enumerate(table):
+        spec = specs[d]
+        g, w = got[s], want[s]
+        assert g.dtype == w.dtype, (s, g.dtype, w.dtype)
+        if spec.kind == 'real' and spec.prior in ('reciprocal', 'norm'):
+            np.testing.assert_allclose(g, w, rtol=RTOL, atol=0, err_msg='slot %d' % s)
+        else:
+            assert np.array_equal(g, w), 'slot %d (%s %s)' % (s, spec.kind, spec.prior)
+
+
+@pytest.mark.parametrize('name', ['mixed_scalar', 'shaped', 'loc_scale_kwargs'])
+def test_from_uniform_matches_reference_golden(name):
+    g = gu.load(name)
+    space = gu.product_space(g['dims'])
+    U, n = _pad_U(gu.stream_to_U(g['specs'], g['n'], g['stream']))
+    batch = space.compiled().sample_from_uniform(U, n=n)
+    _compare_cols(g['specs'], batch.to_numpy(), g['cols'])
+    assert bool(batch.mask[:n].all().item())
+
+
+def test_from_uniform_integer_with_transcendental_prior_is_exact_here():
+    """Integer over reciprocal/norm: floor() could flip within a few ulp of an
+    integer (SURVEY hard part 2); on the golden streams it must not."""
+    g = gu.load('mixed_scalar')
+    space = gu.product_space(g['dims'])
+    U, n = _pad_U(gu.stream_to_U(g['specs'], g['n'], g['stream']))
+    got = space.compiled().sample_from_uniform(U, n=n).to_numpy()
+    assert np.array_equal(got[5], g['cols'][5])         # 'li': Integer reciprocal(1, 1000)
+
+
+@pytest.mark.parametrize('name', gu.CASES)
+def test_contains_matches_reference_golden(name):
+    from orion_b200.columns import ColumnBatch
+    g = gu.load(name)
+    space = gu.product_space(g['dims'])
+    compiled = space.compiled()
+    batch = ColumnBatch.from_numpy(compiled, g['probes'], int_as_f64=True)
+    got = compiled.contains(batch, int_as_f64=True).cpu().numpy().astype(bool)
+    assert np.array_equal(got, g['probe_verdict'])
+
+
+@pytest.mark.parametrize('n', [1, 2, 31, 33, 1000, 4097])
+def test_philox_matches_oracle_mixed64(n):
+    from orion_b200 import spaces
+    space = spaces.mixed64()
+    specs = specs_from_space(space)
+    seed = 0x1234567890ABCDEF
+    batch = space.compiled().sample(n, seed, base_index=(1 << 40) + 7, with_fingerprint=True)
+    want, failed = so.sample_philox(specs, n, seed, base_index=(1 << 40) + 7)
+    assert not failed.any()
+    got = batch.to_numpy()
+    _compare_cols(specs, got, want)
+    assert bool(batch.mask[:n].all().item())
+    assert int(batch.n_failed.sum().item()) == 0
+    lo, hi = batch.fingerprints_numpy()
+    wlo, whi = so.fingerprint(got)
+    assert np.array_equal(lo, wlo) and np.array_equal(hi, whi)
+
+
+def test_philox_rejection_matches_oracle():
+    """Real.sample's <=4 attempts with whole-value redraw, shaped dims included."""
+    g = gu.load('bounded_reject')
+    space = gu.product_space(g['dims'])
+    n, seed = 5000, 77
+    batch = space.compiled().sample(n, seed)
+    want, failed = so.sample_philox(g['specs'], n, seed)
+    got = batch.to_numpy()
+    _compare_cols(g['specs'], got, want)
+    mask = batch.mask[:n].cpu().numpy().astype(bool)
+    assert np.array_equal(mask, ~failed)
+    assert int(batch.n_failed.sum().item()) == int(failed.sum())
+    # accepted rows are inside the space; rows that used a retry exist
+    assert np.array_equal(so.contains(g['specs'], got), ~failed)
+    first_try, _ = so.sample_from_uniform(
+        g['specs'], np.stack([so.philox_uniform(seed, np.arange(n), s) for s in range(len(got))]))
+    assert any(not np.array_equal(a, b) for a, b in zip(first_try, got))
+
+
+def test_improbable_bounds_raise_like_reference():
+    g = gu.load('improbable')
+    space = gu.product_space(g['dims'])
+    with pytest.raises(ValueError) as exc:
+        space.sample(8, seed=3)
+    assert str(exc.value) == g['error']
+    with pytest.raises(ValueError) as exc:
+        space['yolo'].sample(8)
+    assert 'Improbable bounds' in str(exc.value)
+
+
+@pytest.mark.parametrize('requirement', ['real', 'integer', 'numerical', None])
+@pytest.mark.parametrize('quantize', ['round', 'floor'])
+def test_transform_reverse_match_oracle(requirement, quantize):
+    from orion_b200.transformer import build_required_space
+    g = gu.load('mixed_scalar')
+    dims = g['dims'] + [dict(name='b2', kind='categorical', categories=['x', 'y']),
+                        dict(name='b1', kind='categorical', categories=['only']),
+                        dict(name='sh', kind='categorical', categories=[1, 2, 3], shape=[2])]
+    specs = gu.specs_from_json(dims)
+    space = gu.product_space(dims)
+    n, seed = 777, 5
+    tspace = build_required_space(requirement, space, quantize=quantize)
+    compiled = tspace.compiled()
+    batch = compiled.sample(n, seed)
+    cols = batch.to_numpy()
+    tb = compiled.transform(batch)
+    tgot = tb.to_numpy()
+    twant = so.transform(specs, requirement, cols, quantize=quantize)
+    assert len(tgot) == len(twant)
+    for a, b in zip(tgot, twant):
+        assert a.dtype == b.dtype and np.array_equal(a, b)
+    back = compiled.reverse(tb).to_numpy()
+    bwant = so.reverse(specs, requirement, twant, quantize=quantize)
+    for a, b in zip(back, bwant):
+        assert a.dtype == b.dtype and np.array_equal(a, b)
+    if requirement in ('real', 'numerical', None):
+        for s, (a, b) in enumerate(zip(back, cols)):       # round trip is the identity
+            assert np.array_equal(a, b), s
+
+
+def test_reverse_argmax_ties_and_soft_values():
+    """reverse of arbitrary real vectors: first maximum wins; k == 2 thresholds at 0.5."""
+    from orion_b200.columns import ColumnBatch
+    from orion_b200.transformer import build_required_space
+    dims = [dict(name='c4', kind='categorical', categories=[0, 1, 2, 3]),
+            dict(name='c2', kind='categorical', categories=['a', 'b']),
+            dict(name='c9', kind='categorical', categories=list(range(9)))]
+    specs = gu.specs_from_json(dims)
+    space = gu.product_space(dims)
+    compiled = build_required_space('real', space).compiled()
+    rng = np.random.RandomState(0)
+    n = 300
+    tcols = [np.round(rng.random_sample(n), 1) for _ in range(4 + 1 + 9)]   # rounding forces ties
+    tcols[0][:3], tcols[1][:3], tcols[2][:3], tcols[3][:3] = [.1, .7, .7], [.7, .7, .1], [.7, .1, .7], [0, 0, .7]
+    tb = ColumnBatch.from_numpy(compiled, tcols, transformed=True)
+    got = compiled.reverse(tb).to_numpy()
+    want = so.reverse(specs, 'real', tcols)
+    for a, b in zip(got, want):
+        assert np.array_equal(a, b)
+    assert list(got[0][:3]) == [1, 0, 0]
+
+
+def test_fingerprint_canonicalises_negative_zero_and_matches_oracle():
+    from orion_b200.columns import ColumnBatch
+    dims = [dict(name='a', kind='real', prior='uniform', args=[-1, 2]),
+            dict(name='i', kind='integer', prior='uniform', args=[-5, 10]),
+            dict(name='c', kind='categorical', categories=[0, 1, 2])]
+    space = gu.product_space(dims)
+    compiled = space.compiled()
+    cols = [np.array([0.0, -0.0, 0.5, 0.5]), np.array([1, 1, -2, -2], dtype=np.int64),
+            np.array([2, 2, 0, 1], dtype=np.int32)]
+    batch = ColumnBatch.from_numpy(compiled, cols)
+    compiled.fingerprint(batch)
+    lo, hi = batch.fingerprints_numpy()
+    wlo, whi = so.fingerprint(cols)
+    assert np.array_equal(lo, wlo) and np.array_equal(hi, whi)
+    assert lo[0] == lo[1] and hi[0] == hi[1]
+    assert (lo[2], hi[2]) != (lo[3], hi[3])
+
+
+@pytest.mark.parametrize('n', [3, 1000, 50001])
+def test_dedup_matches_exact_oracle(n):
+    """Planted duplicates: against history, inside the batch, and both."""
+    from orion_b200 import spaces
+    from orion_b200.columns import ColumnBatch
+    from orion_b200.history import TrialHistory
+    space = spaces.mixed64()
+    compiled = space.compiled()
+    seed = 99
+    rng = np.random.RandomState(n)
+    hist_cols = compiled.sample(max(n // 2, 1), seed, base_index=10 ** 6).to_numpy()
+    fresh = compiled.sample(n, seed).to_numpy()
+    # row i: 10 % copy a history row, 5 % copy an earlier batch row (possibly itself a history copy)
+    src_hist = rng.randint(0, len(hist_cols[0]), size=n)
+    pick_hist = rng.random_sample(n) < 0.10
+    cols = [np.where(pick_hist, h[src_hist], f) for h, f in zip(hist_cols, fresh)]
+    for i in np.nonzero(rng.random_sample(n) < 0.05)[0]:
+        if i > 0:
+            j = rng.randint(0, i)
+            for c in cols:
+                c[i] = c[j]
+    oracle = so.ExactHistory()
+    oracle.insert(hist_cols)
+    want = oracle.dedup(cols)
+
+    hist = TrialHistory(space, capacity=4 * n + 64)
+    hist.observe(ColumnBatch.from_numpy(compiled, hist_cols))
+    assert len(hist) == len(hist_cols[0])
+    batch = ColumnBatch.from_numpy(compiled, cols)
+    got = hist.dedup(batch).cpu().numpy().astype(bool)
+    assert np.array_equal(got, want)
+    assert len(hist) == len(hist_cols[0]) + int(want.sum())
+    # idempotence: the same batch again is all duplicates now
+    again = hist.dedup(ColumnBatch.from_numpy(compiled, cols)).cpu().numpy()
+    assert not again.any()
+    # probe agrees with membership
+    found = hist.probe_fingerprints(batch.fp, batch.n)[:n].cpu().numpy()
+    assert found.all()
+
+
+def test_dedup_order_keys_and_padding():
+    """Explicit order keys (the multi-GPU path): the smallest key wins, and
+    entries with fp.lo == 0 are ignored."""
+    from orion_b200 import spaces
+    from orion_b200.history import TrialHistory
+    space = spaces.rosen2()
+    hist = TrialHistory(space, capacity=1024)
+    fp = torch.tensor([[5, 1], [5, 1], [7, 2], [0, 0], [5, 1], [9, 3]], dtype=torch.int64).cuda()
+    order = torch.tensor([30, 10, 5, 1, 20, 2], dtype=torch.int32).cuda()
+    keep = hist.dedup_fingerprints(fp, order=order).cpu().numpy()
+    assert list(keep) == [0, 1, 1, 0, 0, 1]
+    assert len(hist) == 3
+
+
+def test_set_full_is_reported():
+    from orion_b200 import _lib, spaces
+    from orion_b200.history import TrialHistory
+    hist = TrialHistory(spaces.rosen2(), n_slots=64)
+    fp = torch.arange(1, 2 * 100 + 1, dtype=torch.int64).view(100, 2).cuda()
+    with pytest.raises(_lib.Ob2Error) as exc:
+        hist.insert_fingerprints(fp)
+    assert 'full' in str(exc.value)
+
+
+def test_empty_and_bad_batches():
+    from orion_b200 import _lib, spaces
+    compiled = spaces.rosen2().compiled()
+    b = compiled.sample(0, 1)
+    assert b.n == 0 and b.to_numpy()[0].shape == (0,)
+    lib = _lib.load()
+    assert lib.ob2_sample(compiled.handle, 5, 7, 0, 0, b.buf.data_ptr(), None, None, None, None) == -1
+    assert b'n_stride' in lib.ob2_last_error()
