@@ -45,7 +45,7 @@ BYTES_DEDUP = 16 + 32 + 16 + 4 + 4 + 1      # fp read, probe sector, insert, scr
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
-    ap.add_argument('--steps', type=int, default=5)
+    ap.add_argument('--steps', type=int, default=20)
     ap.add_argument('--warmup', type=int, default=3)
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
     ap.add_argument('--cands', type=int, default=CANDS_PER_GPU, help='candidates per GPU per step')
@@ -106,7 +106,7 @@ def cpu_path_rate(n_per_proc, procs, steps=1):
     """candidates/s of the oracle port with `procs` processes; returns
     (rate, total candidates, seconds)."""
     import multiprocessing as mp
-    ctx = mp.get_context('fork')
+    ctx = mp.get_context('spawn')
     jobs = [(n_per_proc, p * n_per_proc, SEED, max(n_per_proc // 4, 16)) for p in range(procs)]
     total_t = 0.0
     total_n = 0
@@ -135,7 +135,7 @@ def run_reference(args):
     if rank != 0:
         return
     procs = host_cores()
-    n_per_proc = 20000
+    n_per_proc = 100000
     for _ in range(args.warmup and 1):
         cpu_path_rate(2000, procs)
     rate, total_n, secs = cpu_path_rate(n_per_proc, procs, steps=args.steps)
@@ -167,6 +167,80 @@ def workload_config(args, world):
 # GPU arm
 # --------------------------------------------------------------------------
 class Clocks(object):
+    """SM clock / throttle-reason sampler (NVML, every few ms) that runs in a
+    thread during the timed region; falls back to an nvidia-smi subprocess."""
+
+    def __init__(self, gpu_index, period_s=0.004):
+        import threading
+        self.gpu = gpu_index
+        self.period = period_s
+        self.rows = []
+        self._stop = threading.Event()
+        self._thread = None
+        self._smi = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            # honour CUDA_VISIBLE_DEVICES: map the CUDA ordinal through the UUID torch reports
+            import torch
+            uuid = str(torch.cuda.get_device_properties(gpu_index).uuid)
+            self.h = None
+            for i in range(pynvml.nvmlDeviceGetCount()):
+                h = pynvml.nvmlDeviceGetHandleByIndex(i)
+                u = pynvml.nvmlDeviceGetUUID(h)
+                u = u.decode() if isinstance(u, bytes) else u
+                if uuid in u:
+                    self.h = h
+            if self.h is None:
+                self.h = pynvml.nvmlDeviceGetHandleByIndex(gpu_index)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+            self._thread = threading.Thread(target=self._loop, daemon=True)
+        except Exception:
+            self.nv = None
+            self._smi = SmiClocks(gpu_index)
+
+    def _loop(self):
+        nv = self.nv
+        while not self._stop.is_set():
+            try:
+                self.rows.append((nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM),
+                                  nv.nvmlDeviceGetCurrentClocksEventReasons(self.h),
+                                  nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0))
+            except Exception:
+                pass
+            time.sleep(self.period)
+
+    def start(self):
+        if self._thread is not None:
+            self._thread.start()
+        elif self._smi is not None:
+            self._smi.start()
+
+    def stop(self):
+        if self._thread is None:
+            return self._smi.stop() if self._smi is not None else {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        self._stop.set()
+        self._thread.join(timeout=2)
+        nv = self.nv
+        if not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": [], "samples": 0}
+        sm = sorted(r[0] for r in self.rows)
+        bits = 0
+        for r in self.rows:
+            bits |= r[1]
+        names = [('hw_slowdown', nv.nvmlClocksEventReasonHwSlowdown),
+                 ('hw_thermal_slowdown', nv.nvmlClocksEventReasonHwThermalSlowdown),
+                 ('sw_thermal_slowdown', nv.nvmlClocksEventReasonSwThermalSlowdown),
+                 ('sw_power_cap', nv.nvmlClocksEventReasonSwPowerCap),
+                 ('hw_power_brake_slowdown', nv.nvmlClocksEventReasonHwPowerBrakeSlowdown)]
+        return {"sm_mhz": float(sm[len(sm) // 2]), "sm_min_mhz": float(sm[0]), "sm_max_mhz": self.max_mhz,
+                "reasons": [n for n, b in names if bits & b], "samples": len(sm),
+                "power_w_max": max(r[2] for r in self.rows), "how": "NVML sampled every %d ms during the timed region"
+                % int(self.period * 1000)}
+
+
+class SmiClocks(object):
     """nvidia-smi sampler running during the timed region."""
 
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
@@ -419,7 +493,7 @@ def run_b200(args):
     }
     if not args.no_cpu_baseline and world == 1:
         procs = host_cores()
-        n_per_proc = 20000
+        n_per_proc = 200000
         rate, total_n, secs = cpu_path_rate(n_per_proc, procs, steps=1)
         line["cpu_baseline"] = {"value": rate, "unit": UNIT, "cores": procs, "kind": "port",
                                 "sample": "%d candidates (%d per process x %d processes, %.1f s) of the same workload "

@@ -94,15 +94,17 @@ int64_t ob2_space_trow_bytes(const ob2_space *space); /* bytes per candidate, tr
  * (space.py:281-294) and Categorical.sample (space.py:392-402), as called by
  * Random.suggest (src/orion/algo/random.py:24-33).  Uniforms come from
  * Philox4x32-10: counter (index_lo, index_hi, slot >> 1, attempt), key = seed,
- * candidate index = base_index + i.  `mask[i]` (nullable) is the fused
+ * candidate index = base_index + i, or index[i] when `index` (device u64[n],
+ * nullable) is given -- replaying chosen candidates from their counters.
+ * `mask[i]` (nullable) is the fused
  * `point in space` of PrimaryAlgo.suggest (src/orion/core/worker/primary_algo.py:53-54);
  * `fp` (nullable, [n_stride][2] u64) receives the row fingerprints;
  * `n_failed` (device u32[n_slots], nullable, zeroed by the caller) counts, at
  * the index of a dimension's first slot, the candidates for which that
  * dimension missed its bounds 4 times (the reference's ValueError). */
 int ob2_sample(const ob2_space *space, int64_t n, int64_t n_stride, uint64_t seed,
-               uint64_t base_index, void *cols, uint8_t *mask, uint64_t *fp,
-               uint32_t *n_failed, void *stream);
+               uint64_t base_index, const uint64_t *index, void *cols, uint8_t *mask,
+               uint64_t *fp, uint32_t *n_failed, void *stream);
 
 /* Parity mode of the same kernel: uniforms are read from U[S][n_stride] (one
  * attempt, no redraw); ok[i] = every Real/Integer slot landed in bounds. */

@@ -49,7 +49,7 @@ template <bool PHILOX, bool WITH_FP>
 __global__ void __launch_bounds__(OB2_BLOCK)
 sample_kernel(const ob2_slot_desc *__restrict__ g_slots, int n_slots, const double *__restrict__ g_cdf,
               int cdf_len, int64_t n, int64_t n_stride, uint32_t k0, uint32_t k1, uint64_t base_index,
-              const double *__restrict__ U, char *__restrict__ cols, uint8_t *__restrict__ mask,
+              const uint64_t *__restrict__ index, const double *__restrict__ U, char *__restrict__ cols, uint8_t *__restrict__ mask,
               uint64_t *__restrict__ fp, uint32_t *__restrict__ n_failed) {
     extern __shared__ __align__(16) unsigned char smem[];
     ob2_slot_desc *s_slots = reinterpret_cast<ob2_slot_desc *>(smem);
@@ -59,7 +59,11 @@ sample_kernel(const ob2_slot_desc *__restrict__ g_slots, int n_slots, const doub
     const int64_t i0 = ((int64_t)blockIdx.x * OB2_BLOCK + threadIdx.x) * OB2_CPT;
     if (i0 >= n) return;
     const bool has1 = i0 + 1 < n;
-    const uint64_t idx0 = base_index + (uint64_t)i0, idx1 = idx0 + 1;
+    uint64_t idx0 = base_index + (uint64_t)i0, idx1 = idx0 + 1;
+    if (PHILOX && index != nullptr) {  // explicit counters (replay / planted duplicates)
+        idx0 = __ldg(index + i0);
+        idx1 = has1 ? __ldg(index + i0 + 1) : idx0;
+    }
 
     FpAcc acc0{0, 0}, acc1{0, 0}, tmp0{0, 0}, tmp1{0, 0};
     bool ok0 = true, ok1 = true;    // current dimension
@@ -200,7 +204,7 @@ int prepare_smem(K kernel, size_t smem) {
 
 template <bool PHILOX>
 int launch_sample(const ob2_space *sp, int64_t n, int64_t n_stride, uint64_t seed, uint64_t base_index,
-                  const double *U, void *cols, uint8_t *mask, uint64_t *fp, uint32_t *n_failed, void *stream) {
+                  const uint64_t *index, const double *U, void *cols, uint8_t *mask, uint64_t *fp, uint32_t *n_failed, void *stream) {
     int rc = ob2_check_batch(sp, n, n_stride);
     if (rc != OB2_OK) return rc;
     if (cols == nullptr || (!PHILOX && U == nullptr)) {
@@ -221,14 +225,14 @@ int launch_sample(const ob2_space *sp, int64_t n, int64_t n_stride, uint64_t see
         rc = prepare_smem(kern, sp->smem_bytes);
         if (rc != OB2_OK) return rc;
         kern<<<(unsigned)blocks, OB2_BLOCK, sp->smem_bytes, st>>>(sp->d_slots, sp->n_slots, sp->d_cdf, sp->cdf_len, n,
-                                                                   n_stride, k0, k1, base_index, U, (char *)cols, mask,
+                                                                   n_stride, k0, k1, base_index, index, U, (char *)cols, mask,
                                                                    fp, n_failed);
     } else {
         auto kern = sample_kernel<PHILOX, false>;
         rc = prepare_smem(kern, sp->smem_bytes);
         if (rc != OB2_OK) return rc;
         kern<<<(unsigned)blocks, OB2_BLOCK, sp->smem_bytes, st>>>(sp->d_slots, sp->n_slots, sp->d_cdf, sp->cdf_len, n,
-                                                                   n_stride, k0, k1, base_index, U, (char *)cols, mask,
+                                                                   n_stride, k0, k1, base_index, index, U, (char *)cols, mask,
                                                                    nullptr, n_failed);
     }
     return ob2_check_cuda(cudaGetLastError(), "sample_kernel launch");
@@ -237,13 +241,14 @@ int launch_sample(const ob2_space *sp, int64_t n, int64_t n_stride, uint64_t see
 }  // namespace
 
 extern "C" int ob2_sample(const ob2_space *space, int64_t n, int64_t n_stride, uint64_t seed, uint64_t base_index,
-                          void *cols, uint8_t *mask, uint64_t *fp, uint32_t *n_failed, void *stream) {
-    return launch_sample<true>(space, n, n_stride, seed, base_index, nullptr, cols, mask, fp, n_failed, stream);
+                          const uint64_t *index, void *cols, uint8_t *mask, uint64_t *fp, uint32_t *n_failed,
+                          void *stream) {
+    return launch_sample<true>(space, n, n_stride, seed, base_index, index, nullptr, cols, mask, fp, n_failed, stream);
 }
 
 extern "C" int ob2_sample_from_uniform(const ob2_space *space, int64_t n, int64_t n_stride, const double *U,
                                        void *cols, uint8_t *ok, uint64_t *fp, void *stream) {
-    return launch_sample<false>(space, n, n_stride, 0, 0, U, cols, ok, fp, nullptr, stream);
+    return launch_sample<false>(space, n, n_stride, 0, 0, nullptr, U, cols, ok, fp, nullptr, stream);
 }
 
 extern "C" int ob2_contains(const ob2_space *space, int64_t n, int64_t n_stride, const void *cols,

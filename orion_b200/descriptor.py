@@ -201,8 +201,9 @@ class CompiledSpace(object):
         return ColumnBatch(self, int(n), n_stride, buf, transformed)
 
     # ------------------------------------------------------------ kernels
-    def sample(self, n, seed, base_index=0, with_mask=True, with_fingerprint=False, out=None):
-        """Philox-mode Space.sample: returns a ColumnBatch (device)."""
+    def sample(self, n, seed, base_index=0, with_mask=True, with_fingerprint=False, out=None, index=None):
+        """Philox-mode Space.sample: returns a ColumnBatch (device).  ``index``
+        (int64 device tensor [n]) replaces the consecutive counters."""
         batch = out if out is not None else self.empty_columns(n)
         assert not batch.transformed and batch.n == n
         ns = batch.n_stride
@@ -215,7 +216,8 @@ class CompiledSpace(object):
         else:
             batch.n_failed.zero_()
         _lib.check(self.lib.ob2_sample(
-            self.handle, n, ns, int(seed) & _M64, int(base_index) & _M64, batch.buf.data_ptr(),
+            self.handle, n, ns, int(seed) & _M64, int(base_index) & _M64,
+            index.data_ptr() if index is not None else None, batch.buf.data_ptr(),
             batch.mask.data_ptr() if with_mask else None,
             batch.fp.data_ptr() if with_fingerprint else None,
             batch.n_failed.data_ptr(), self._stream()))

@@ -85,6 +85,20 @@ def test_philox_matches_oracle_mixed64(n):
     assert np.array_equal(lo, wlo) and np.array_equal(hi, whi)
 
 
+def test_philox_explicit_counters():
+    """index[i] replaces base_index + i: replaying counters reproduces rows."""
+    from orion_b200 import spaces
+    compiled = spaces.mixed64().compiled()
+    seed = 11
+    ref = compiled.sample(1000, seed, base_index=500).to_numpy()
+    idx = torch.tensor([500 + 7, 500 + 7, 500 + 999, 500, 500 + 123], dtype=torch.int64).cuda()
+    got = compiled.sample(5, seed, index=idx, with_fingerprint=True)
+    for g, r in zip(got.to_numpy(), ref):
+        assert np.array_equal(g, r[[7, 7, 999, 0, 123]])
+    lo, hi = got.fingerprints_numpy()
+    assert lo[0] == lo[1] and hi[0] == hi[1]
+
+
 def test_philox_rejection_matches_oracle():
     """Real.sample's <=4 attempts with whole-value redraw, shaped dims included."""
     g = gu.load('bounded_reject')
@@ -255,5 +269,5 @@ def test_empty_and_bad_batches():
     b = compiled.sample(0, 1)
     assert b.n == 0 and b.to_numpy()[0].shape == (0,)
     lib = _lib.load()
-    assert lib.ob2_sample(compiled.handle, 5, 7, 0, 0, b.buf.data_ptr(), None, None, None, None) == -1
+    assert lib.ob2_sample(compiled.handle, 5, 7, 0, 0, None, b.buf.data_ptr(), None, None, None, None) == -1
     assert b'n_stride' in lib.ob2_last_error()
