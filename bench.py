@@ -52,6 +52,7 @@ def parse_args():
     ap.add_argument('--history', type=int, default=HISTORY_PER_GPU, help='history rows per GPU')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--e2e-steps', type=int, default=2)
+    ap.add_argument('--unfused', action='store_true', help='sample and transform as two kernels')
     return ap.parse_args()
 
 
@@ -357,24 +358,31 @@ def run_b200(args):
     tbatch = compiled.empty_columns(n, transformed=True)
     back = compiled.empty_columns(n)
     batch.keep = torch.empty(batch.n_stride, dtype=torch.uint8, device=dev)
-    kernel_names = ['sample', 'transform', 'reverse', 'dedup']
+    fused = not args.unfused
+    kernel_names = ['sample+transform', 'reverse', 'dedup'] if fused else ['sample', 'transform', 'reverse', 'dedup']
     ev = [[torch.cuda.Event(enable_timing=True) for _ in range(len(kernel_names) + 1)] for _ in range(K)]
     launches = [0]
 
     def one_step(step, events=None):
-        compiled.sample(n, SEED, index=index_dev[step], with_mask=True, with_fingerprint=True, out=batch)
+        j = 1
+        if fused:       # TransformedSpace.sample: one kernel draws and transforms
+            compiled.sample(n, SEED, index=index_dev[step], with_mask=True, with_fingerprint=True, out=batch,
+                            transformed_out=tbatch)
+        else:
+            compiled.sample(n, SEED, index=index_dev[step], with_mask=True, with_fingerprint=True, out=batch)
+            if events:
+                events[j].record()
+            j += 1
+            compiled.transform(batch, out=tbatch)
         if events:
-            events[1].record()
-        compiled.transform(batch, out=tbatch)
-        if events:
-            events[2].record()
+            events[j].record()
         compiled.reverse(tbatch, out=back)
         if events:
-            events[3].record()
+            events[j + 1].record()
         sharded.dedup(batch.fp, n, per_rank_n=n, keep=batch.keep, check=False)
         if events:
-            events[4].record()
-        launches[0] += 5 if world == 1 else 8
+            events[j + 2].record()
+        launches[0] += (4 if fused else 5) + (0 if world == 1 else 3)
 
     def sync_all():
         if world > 1:
@@ -425,8 +433,8 @@ def run_b200(args):
 
         def e2e_step(j):
             idx_dev.copy_(host_idx[j], non_blocking=True)                       # H2D: this step's input
-            compiled.sample(n, SEED, index=idx_dev, with_mask=True, with_fingerprint=True, out=batch)
-            compiled.transform(batch, out=tbatch)
+            compiled.sample(n, SEED, index=idx_dev, with_mask=True, with_fingerprint=True, out=batch,
+                            transformed_out=tbatch)
             compiled.reverse(tbatch, out=back)
             sharded.dedup(batch.fp, n, per_rank_n=n, keep=batch.keep, check=False)
             host_cols.copy_(back.buf, non_blocking=True)                        # D2H: the candidates
@@ -463,7 +471,9 @@ def run_b200(args):
         peak_src = "MEASURED_PEAKS.json hbm_gbs (of measured)"
     else:
         peak, peak_src = 6650.0, "B200_PROFILING.md fallback 6.65 TB/s (of fallback)"
-    algo_bytes = {'sample': BYTES_SAMPLE, 'transform': BYTES_TRANSFORM, 'reverse': BYTES_REVERSE, 'dedup': BYTES_DEDUP}
+    algo_bytes = {'sample': BYTES_SAMPLE, 'transform': BYTES_TRANSFORM, 'reverse': BYTES_REVERSE, 'dedup': BYTES_DEDUP,
+                  'sample+transform': BYTES_SAMPLE + BYTES_TRANSFORM}
+    algo_bytes = {k: algo_bytes[k] for k in kernel_names}
     dominant = max(per_kernel_ms, key=per_kernel_ms.get)
     achieved = algo_bytes[dominant] * n / (per_kernel_ms[dominant] * 1e-3) / 1e9
     traffic = None

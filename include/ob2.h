@@ -69,7 +69,7 @@ typedef struct ob2_slot_desc {
     double p0, p1;     /* reciprocal: log(a), log(b) - log(a)                     */
     double loc, scale; /* x = base(u) * scale + loc  (scipy rv_generic.rvs)       */
     double low, high;  /* accepted iff low <= x < high (space.py:160-164)         */
-    uint64_t hk[4];    /* fingerprint keys: xorA, multA(odd), xorB, multB(odd)    */
+    uint64_t hk[4];    /* fingerprint: xor key, odd multiplier, 2 reserved        */
 } ob2_slot_desc;
 
 typedef struct ob2_space ob2_space;
@@ -105,6 +105,16 @@ int64_t ob2_space_trow_bytes(const ob2_space *space); /* bytes per candidate, tr
 int ob2_sample(const ob2_space *space, int64_t n, int64_t n_stride, uint64_t seed,
                uint64_t base_index, const uint64_t *index, void *cols, uint8_t *mask,
                uint64_t *fp, uint32_t *n_failed, void *stream);
+
+/* TransformedSpace.sample = transform(original.sample(...)) in ONE kernel: the
+ * same draw as ob2_sample, and each value is also written through its slot's
+ * transformer into `tcols` (the transformed column set) while it is still in
+ * registers, so the sampled columns are never re-read.  Same arguments as
+ * ob2_sample plus `tcols`.  (Reference: TODO at
+ * src/orion/core/worker/primary_algo.py:54-55) */
+int ob2_sample_transform(const ob2_space *space, int64_t n, int64_t n_stride, uint64_t seed,
+                         uint64_t base_index, const uint64_t *index, void *cols, void *tcols,
+                         uint8_t *mask, uint64_t *fp, uint32_t *n_failed, void *stream);
 
 /* Parity mode of the same kernel: uniforms are read from U[S][n_stride] (one
  * attempt, no redraw); ok[i] = every Real/Integer slot landed in bounds. */

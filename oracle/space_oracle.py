@@ -487,10 +487,10 @@ def canonical_words(cols: Sequence[np.ndarray]) -> List[np.ndarray]:
 def fingerprint(cols: Sequence[np.ndarray]):
     """128-bit row fingerprint as (lo, hi) uint64 arrays.
 
-    Two independent lanes; each is the wrapping sum over slots of
-    ``mum(word ^ key, mult)`` (``mum`` = hi64 ^ lo64 of the 128-bit product),
-    finished with murmur3's ``fmix64``.  ``lo`` is never 0 (0 marks an empty
-    hash-set slot).
+    Per slot one 128-bit product ``(word ^ key) * odd_mult`` (injective in the
+    word); lane a is the wrapping sum over slots of its high 64 bits, lane b of
+    its low 64 bits; each lane is finished with murmur3's ``fmix64``.  ``lo``
+    is never 0 (0 marks an empty hash-set slot).
     """
     S = len(cols)
     keys = slot_hash_keys(S)
@@ -500,9 +500,8 @@ def fingerprint(cols: Sequence[np.ndarray]):
     with np.errstate(over='ignore'):
         for s, w in enumerate(canonical_words(cols)):
             hi, lo = _mul_hi_lo(w ^ keys[s, 0], int(keys[s, 1]))
-            acc_a = acc_a + (hi ^ lo)
-            hi, lo = _mul_hi_lo(w ^ keys[s, 2], int(keys[s, 3]))
-            acc_b = acc_b + (hi ^ lo)
+            acc_a = acc_a + hi
+            acc_b = acc_b + lo
         lo = _fmix64(acc_a ^ U64((S * 0x9E3779B97F4A7C15) & _M64))
         hi = _fmix64(acc_b + U64((S * 0xC2B2AE3D27D4EB4F) & _M64))
     lo = np.where(lo == 0, U64(1), lo)

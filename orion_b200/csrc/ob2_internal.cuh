@@ -62,12 +62,13 @@ __device__ __forceinline__ void ob2_stage_tables(const ob2_slot_desc *__restrict
 struct Philox4 {
     uint32_t x, y, z, w;
 };
+// m0 / m1 must be 0xD2511F53 / 0xCD9E8D57 (see sample_kernel for why they are arguments).
 __device__ __forceinline__ Philox4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
-                                                 uint32_t k0, uint32_t k1) {
+                                                 uint32_t k0, uint32_t k1, uint32_t m0, uint32_t m1) {
 #pragma unroll
     for (int r = 0; r < 10; ++r) {
-        const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
-        const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+        const uint32_t hi0 = __umulhi(m0, c0), lo0 = m0 * c0;
+        const uint32_t hi1 = __umulhi(m1, c2), lo1 = m1 * c2;
         c0 = hi1 ^ c1 ^ k0;
         c2 = hi0 ^ c3 ^ k1;
         c1 = lo1;
@@ -104,14 +105,15 @@ __device__ __forceinline__ double draw_real(const ob2_slot_desc &d, double u) {
 }
 
 // numpy searchsorted(cdf, u, side='right')
+// = #{j : cdf[j] <= u} for a non-decreasing cdf.  Branch-free descent whose trip
+// count depends on k only (warp-uniform), so the warp never diverges here.
 __device__ __forceinline__ int draw_cat(const double *cdf, int k, double u) {
-    int lo = 0, hi = k;
-    while (lo < hi) {
-        const int mid = (lo + hi) >> 1;
-        if (cdf[mid] <= u)
-            lo = mid + 1;
-        else
-            hi = mid;
+    int lo = 0;
+    for (int step = 1 << (31 - __clz(k)); step > 0; step >>= 1) {
+        const int probe = lo + step;
+        const int at = probe <= k ? probe : k;  // clamp the read, not the decision
+        const bool take = (probe <= k) && (cdf[at - 1] <= u);
+        lo = take ? probe : lo;
     }
     return lo;
 }
@@ -135,9 +137,14 @@ __device__ __forceinline__ uint64_t canon_f64(double x) {
 struct FpAcc {
     uint64_t a, b;
 };
+// One 64x64 -> 128-bit product per slot: (word ^ key) * odd multiplier.  The
+// product is injective in the word, its high half feeds lane a and its low
+// half lane b; lanes are wrapping sums over slots, so any partition of the
+// slots over threads gives the same fingerprint.
 __device__ __forceinline__ void fp_add(FpAcc &acc, const ob2_slot_desc &d, uint64_t w) {
-    acc.a += mum64(w ^ d.hk[0], d.hk[1]);
-    acc.b += mum64(w ^ d.hk[2], d.hk[3]);
+    const uint64_t x = w ^ d.hk[0];
+    acc.a += __umul64hi(x, d.hk[1]);
+    acc.b += x * d.hk[1];
 }
 __device__ __forceinline__ void fp_finish(const FpAcc &acc, int n_slots, uint64_t &lo, uint64_t &hi) {
     lo = fmix64(acc.a ^ ((uint64_t)n_slots * 0x9E3779B97F4A7C15ull));

@@ -1,55 +1,120 @@
 // K1: candidate sampling (Philox4x32-10 or injected uniforms -> per-slot
-// inverse CDF), fused with the bounds check, the <=4-attempt rejection and the
-// row fingerprint; and the standalone Space.__contains__ kernel.
+// inverse CDF), fused with the bounds check, the <=4-attempt rejection, the row
+// fingerprint and -- optionally -- the transform chain; and the standalone
+// Space.__contains__ kernel.
 //
 // Mapping: one thread owns OB2_CPT = 2 consecutive candidates and walks the
 // slots in space order.  At any instant a warp therefore works on ONE slot
 // (no divergence on the prior / kind switch) and stores 32 x 16 B = 512
 // contiguous bytes of that slot's column.  Output is columnar [S][n_stride].
+//
+// The sampler is instruction-issue bound (Philox + fp64 inverse CDFs +
+// fingerprint multiplies, ~10k instructions per candidate) while the transform
+// is pure store bandwidth; fusing them (WITH_T) lets the one-hot stores ride
+// under the arithmetic and saves re-reading the sampled columns.
 #include "ob2_internal.cuh"
 
 namespace {
 
+__device__ __forceinline__ long long quantize_ll(double x, int t_flags) {
+    return __double2ll_rz((t_flags & OB2_TFLAG_FLOOR) ? floor(x) : rint(x));
+}
 
-template <bool WITH_FP>
-__device__ __noinline__ bool retry_dim(const ob2_slot_desc *s_slots, int s_last, uint64_t index, int64_t i,
-                                       int64_t n_stride, char *cols, uint32_t k0, uint32_t k1, FpAcc &tmp) {
-    // Real.sample (space.py:263-270): redraw the whole (shaped) value, attempts 1..3
+// ---- transformed-column emission for one slot, both candidates (fused transform)
+__device__ __forceinline__ void emit_real2(const ob2_slot_desc &d, char *tcols, int64_t n_stride, int64_t i0,
+                                           double x0, double x1) {
+    char *dst = tcols + (int64_t)d.t_units * n_stride;
+    if (d.t_op == OB2_OP_QUANTIZE)
+        st_i64x2(reinterpret_cast<long long *>(dst) + i0, quantize_ll(x0, d.t_flags), quantize_ll(x1, d.t_flags));
+    else
+        st_f64x2(reinterpret_cast<double *>(dst) + i0, x0, x1);
+}
+
+// xf = the floored draw as a double (exactly (double)q)
+__device__ __forceinline__ void emit_int2(const ob2_slot_desc &d, char *tcols, int64_t n_stride, int64_t i0,
+                                          long long q0, long long q1, double xf0, double xf1) {
+    char *dst = tcols + (int64_t)d.t_units * n_stride;
+    if (d.t_op == OB2_OP_TO_REAL)
+        st_f64x2(reinterpret_cast<double *>(dst) + i0, xf0, xf1);
+    else
+        st_i64x2(reinterpret_cast<long long *>(dst) + i0, q0, q1);
+}
+
+__device__ __forceinline__ void emit_cat2(const ob2_slot_desc &d, char *tcols, int64_t n_stride, int64_t i0, int c0,
+                                          int c1) {
+    char *dst = tcols + (int64_t)d.t_units * n_stride;
+    if (d.t_op != OB2_OP_ONEHOT) {
+        st_i32x2(reinterpret_cast<int *>(dst) + i0, c0, c1);
+    } else if (d.t_width == 1) {
+        st_f64x2(reinterpret_cast<double *>(dst) + i0, (double)c0, (double)c1);
+    } else {
+        double *out = reinterpret_cast<double *>(dst) + i0;
+        for (int j = 0; j < d.t_width; ++j) {
+            st_f64x2(out, c0 == j ? 1.0 : 0.0, c1 == j ? 1.0 : 0.0);
+            out += n_stride;
+        }
+    }
+}
+
+// Real.sample (space.py:263-270): a draw of dimension [first, s_last] landed
+// outside [low, high): redraw the whole (possibly shaped) value for candidate i,
+// attempts 1..3, overwriting its columns with scalar stores.  Rare path; inlined
+// in a cold branch of the walk so the hot loop carries no redraw state.
+template <bool WITH_FP, bool WITH_T>
+__device__ __forceinline__ bool redraw_dim(const ob2_slot_desc *s_slots, int s_last, uint64_t index, int64_t i,
+                                           int64_t n_stride, char *cols, char *tcols, uint32_t k0, uint32_t k1,
+                                           uint32_t pm0, uint32_t pm1, FpAcc &tmp) {
     const int first = s_slots[s_last].dim_first;
-    const uint32_t ilo = (uint32_t)index, ihi = (uint32_t)(index >> 32);
-    for (uint32_t a = 1; a < 4; ++a) {
-        bool ok = true;
+    bool ok = false;
+    for (uint32_t a = 1; a < 4 && !ok; ++a) {
+        ok = true;
         FpAcc t{0, 0};
         for (int e = first; e <= s_last; ++e) {
             const ob2_slot_desc &d = s_slots[e];
-            const Philox4 r = philox4x32_10(ilo, ihi, (uint32_t)(e >> 1), a, k0, k1);
+            const Philox4 r = philox4x32_10((uint32_t)index, (uint32_t)(index >> 32), (uint32_t)(e >> 1), a, k0, k1, pm0, pm1);
             const double u = (e & 1) ? u53(r.z, r.w) : u53(r.x, r.y);
             double x = draw_real(d, u);
             char *col = cols + (int64_t)d.col_units * n_stride;
+            char *dst = tcols + (int64_t)d.t_units * n_stride;
             uint64_t w;
             if (d.kind == OB2_KIND_INTEGER) {
                 x = floor(x);
-                const long long k = __double2ll_rz(x);
-                reinterpret_cast<long long *>(col)[i] = k;
-                w = (uint64_t)k;
+                const long long q = __double2ll_rz(x);
+                reinterpret_cast<long long *>(col)[i] = q;
+                w = (uint64_t)q;
+                if (WITH_T) {
+                    if (d.t_op == OB2_OP_TO_REAL)
+                        reinterpret_cast<double *>(dst)[i] = x;
+                    else
+                        reinterpret_cast<long long *>(dst)[i] = q;
+                }
             } else {
                 reinterpret_cast<double *>(col)[i] = x;
                 w = canon_f64(x);
+                if (WITH_T) {
+                    if (d.t_op == OB2_OP_QUANTIZE)
+                        reinterpret_cast<long long *>(dst)[i] = quantize_ll(x, d.t_flags);
+                    else
+                        reinterpret_cast<double *>(dst)[i] = x;
+                }
             }
             ok &= (x >= d.low) && (x < d.high);
             if (WITH_FP) fp_add(t, d, w);
         }
         tmp = t;
-        if (ok) return true;
     }
-    return false;
+    return ok;
 }
 
-template <bool PHILOX, bool WITH_FP>
-__global__ void __launch_bounds__(OB2_BLOCK)
+// pm0 / pm1 are the Philox multipliers, passed as kernel parameters so that the
+// multiplies read them straight from the constant bank (as literals the compiler
+// re-materialises them into uniform registers before every round).
+template <bool PHILOX, bool WITH_FP, bool WITH_T>
+__global__ void __launch_bounds__(OB2_BLOCK, 3)
 sample_kernel(const ob2_slot_desc *__restrict__ g_slots, int n_slots, const double *__restrict__ g_cdf,
-              int cdf_len, int64_t n, int64_t n_stride, uint32_t k0, uint32_t k1, uint64_t base_index,
-              const uint64_t *__restrict__ index, const double *__restrict__ U, char *__restrict__ cols, uint8_t *__restrict__ mask,
+              int cdf_len, int64_t n, int64_t n_stride, uint32_t k0, uint32_t k1, uint32_t pm0, uint32_t pm1,
+              uint64_t base_index, const uint64_t *__restrict__ index, const double *__restrict__ U,
+              char *__restrict__ cols, char *__restrict__ tcols, uint8_t *__restrict__ mask,
               uint64_t *__restrict__ fp, uint32_t *__restrict__ n_failed) {
     extern __shared__ __align__(16) unsigned char smem[];
     ob2_slot_desc *s_slots = reinterpret_cast<ob2_slot_desc *>(smem);
@@ -75,8 +140,8 @@ sample_kernel(const ob2_slot_desc *__restrict__ g_slots, int n_slots, const doub
         double u0, u1;
         if (PHILOX) {
             if ((s & 1) == 0) {
-                r0 = philox4x32_10((uint32_t)idx0, (uint32_t)(idx0 >> 32), (uint32_t)(s >> 1), 0u, k0, k1);
-                r1 = philox4x32_10((uint32_t)idx1, (uint32_t)(idx1 >> 32), (uint32_t)(s >> 1), 0u, k0, k1);
+                r0 = philox4x32_10((uint32_t)idx0, (uint32_t)(idx0 >> 32), (uint32_t)(s >> 1), 0u, k0, k1, pm0, pm1);
+                r1 = philox4x32_10((uint32_t)idx1, (uint32_t)(idx1 >> 32), (uint32_t)(s >> 1), 0u, k0, k1, pm0, pm1);
                 u0 = u53(r0.x, r0.y);
                 u1 = u53(r1.x, r1.y);
             } else {
@@ -93,6 +158,7 @@ sample_kernel(const ob2_slot_desc *__restrict__ g_slots, int n_slots, const doub
             const int c0 = draw_cat(cdf, d.n_cats, u0);
             const int c1 = draw_cat(cdf, d.n_cats, u1);
             st_i32x2(reinterpret_cast<int *>(col) + i0, c0, c1);
+            if (WITH_T) emit_cat2(d, tcols, n_stride, i0, c0, c1);
             w0 = (uint64_t)(int64_t)c0;
             w1 = (uint64_t)(int64_t)c1;
             ok0 &= c0 < d.n_cats;
@@ -105,10 +171,12 @@ sample_kernel(const ob2_slot_desc *__restrict__ g_slots, int n_slots, const doub
                 x1 = floor(x1);
                 const long long q0 = __double2ll_rz(x0), q1 = __double2ll_rz(x1);
                 st_i64x2(reinterpret_cast<long long *>(col) + i0, q0, q1);
+                if (WITH_T) emit_int2(d, tcols, n_stride, i0, q0, q1, x0, x1);
                 w0 = (uint64_t)q0;
                 w1 = (uint64_t)q1;
             } else {
                 st_f64x2(reinterpret_cast<double *>(col) + i0, x0, x1);
+                if (WITH_T) emit_real2(d, tcols, n_stride, i0, x0, x1);
                 w0 = canon_f64(x0);
                 w1 = canon_f64(x1);
             }
@@ -120,9 +188,11 @@ sample_kernel(const ob2_slot_desc *__restrict__ g_slots, int n_slots, const doub
             fp_add(tmp1, d, w1);
         }
         if (d.flags & OB2_SLOT_DIM_LAST) {
-            if (PHILOX && d.kind != OB2_KIND_CATEGORICAL) {
-                if (!ok0) ok0 = retry_dim<WITH_FP>(s_slots, s, idx0, i0, n_stride, cols, k0, k1, tmp0);
-                if (!ok1 && has1) ok1 = retry_dim<WITH_FP>(s_slots, s, idx1, i0 + 1, n_stride, cols, k0, k1, tmp1);
+            if (PHILOX && d.kind != OB2_KIND_CATEGORICAL && !(ok0 && (ok1 || !has1))) {  // cold
+                if (!ok0)
+                    ok0 = redraw_dim<WITH_FP, WITH_T>(s_slots, s, idx0, i0, n_stride, cols, tcols, k0, k1, pm0, pm1, tmp0);
+                if (!ok1 && has1)
+                    ok1 = redraw_dim<WITH_FP, WITH_T>(s_slots, s, idx1, i0 + 1, n_stride, cols, tcols, k0, k1, pm0, pm1, tmp1);
                 if (n_failed != nullptr) {  // 4 misses: the reference raises "Improbable bounds"
                     const unsigned bad = (ok0 ? 0u : 1u) + ((ok1 || !has1) ? 0u : 1u);
                     if (bad) atomicAdd(n_failed + d.dim_first, bad);
@@ -202,40 +272,53 @@ int prepare_smem(K kernel, size_t smem) {
     return OB2_OK;
 }
 
-template <bool PHILOX>
-int launch_sample(const ob2_space *sp, int64_t n, int64_t n_stride, uint64_t seed, uint64_t base_index,
-                  const uint64_t *index, const double *U, void *cols, uint8_t *mask, uint64_t *fp, uint32_t *n_failed, void *stream) {
-    int rc = ob2_check_batch(sp, n, n_stride);
+struct SampleArgs {
+    const ob2_space *sp;
+    int64_t n, n_stride;
+    uint64_t seed, base_index;
+    const uint64_t *index;
+    const double *U;
+    void *cols, *tcols;
+    uint8_t *mask;
+    uint64_t *fp;
+    uint32_t *n_failed;
+    void *stream;
+};
+
+template <bool PHILOX, bool WITH_FP, bool WITH_T>
+int launch_one(const SampleArgs &a, unsigned blocks) {
+    auto kern = sample_kernel<PHILOX, WITH_FP, WITH_T>;
+    const ob2_space *sp = a.sp;
+    int rc = prepare_smem(kern, sp->smem_bytes);
     if (rc != OB2_OK) return rc;
-    if (cols == nullptr || (!PHILOX && U == nullptr)) {
+    kern<<<blocks, OB2_BLOCK, sp->smem_bytes, static_cast<cudaStream_t>(a.stream)>>>(
+        sp->d_slots, sp->n_slots, sp->d_cdf, sp->cdf_len, a.n, a.n_stride, (uint32_t)a.seed,
+        (uint32_t)(a.seed >> 32), 0xD2511F53u, 0xCD9E8D57u, a.base_index, a.index, a.U, (char *)a.cols, (char *)a.tcols, a.mask, a.fp,
+        a.n_failed);
+    return ob2_check_cuda(cudaGetLastError(), "sample_kernel launch");
+}
+
+template <bool PHILOX>
+int launch_sample(const SampleArgs &a) {
+    int rc = ob2_check_batch(a.sp, a.n, a.n_stride);
+    if (rc != OB2_OK) return rc;
+    if (a.cols == nullptr || (!PHILOX && a.U == nullptr)) {
         ob2_set_error("sample: null buffer");
         return OB2_EINVAL;
     }
-    if (n == 0) return OB2_OK;
-    const int64_t threads = (n + OB2_CPT - 1) / OB2_CPT;
+    if (a.n == 0) return OB2_OK;
+    const int64_t threads = (a.n + OB2_CPT - 1) / OB2_CPT;
     const int64_t blocks = (threads + OB2_BLOCK - 1) / OB2_BLOCK;
     if (blocks > 0x7FFFFFFFll) {
         ob2_set_error("batch too large for one launch");
         return OB2_ETOOBIG;
     }
-    cudaStream_t st = static_cast<cudaStream_t>(stream);
-    const uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
-    if (fp != nullptr) {
-        auto kern = sample_kernel<PHILOX, true>;
-        rc = prepare_smem(kern, sp->smem_bytes);
-        if (rc != OB2_OK) return rc;
-        kern<<<(unsigned)blocks, OB2_BLOCK, sp->smem_bytes, st>>>(sp->d_slots, sp->n_slots, sp->d_cdf, sp->cdf_len, n,
-                                                                   n_stride, k0, k1, base_index, index, U, (char *)cols, mask,
-                                                                   fp, n_failed);
-    } else {
-        auto kern = sample_kernel<PHILOX, false>;
-        rc = prepare_smem(kern, sp->smem_bytes);
-        if (rc != OB2_OK) return rc;
-        kern<<<(unsigned)blocks, OB2_BLOCK, sp->smem_bytes, st>>>(sp->d_slots, sp->n_slots, sp->d_cdf, sp->cdf_len, n,
-                                                                   n_stride, k0, k1, base_index, index, U, (char *)cols, mask,
-                                                                   nullptr, n_failed);
-    }
-    return ob2_check_cuda(cudaGetLastError(), "sample_kernel launch");
+    const unsigned b = (unsigned)blocks;
+    const bool with_fp = a.fp != nullptr, with_t = a.tcols != nullptr;
+    if (with_fp && with_t) return launch_one<PHILOX, true, true>(a, b);
+    if (with_fp) return launch_one<PHILOX, true, false>(a, b);
+    if (with_t) return launch_one<PHILOX, false, true>(a, b);
+    return launch_one<PHILOX, false, false>(a, b);
 }
 
 }  // namespace
@@ -243,12 +326,25 @@ int launch_sample(const ob2_space *sp, int64_t n, int64_t n_stride, uint64_t see
 extern "C" int ob2_sample(const ob2_space *space, int64_t n, int64_t n_stride, uint64_t seed, uint64_t base_index,
                           const uint64_t *index, void *cols, uint8_t *mask, uint64_t *fp, uint32_t *n_failed,
                           void *stream) {
-    return launch_sample<true>(space, n, n_stride, seed, base_index, index, nullptr, cols, mask, fp, n_failed, stream);
+    const SampleArgs a{space, n, n_stride, seed, base_index, index, nullptr, cols, nullptr, mask, fp, n_failed, stream};
+    return launch_sample<true>(a);
+}
+
+extern "C" int ob2_sample_transform(const ob2_space *space, int64_t n, int64_t n_stride, uint64_t seed,
+                                    uint64_t base_index, const uint64_t *index, void *cols, void *tcols,
+                                    uint8_t *mask, uint64_t *fp, uint32_t *n_failed, void *stream) {
+    if (tcols == nullptr) {
+        ob2_set_error("ob2_sample_transform: null transformed buffer");
+        return OB2_EINVAL;
+    }
+    const SampleArgs a{space, n, n_stride, seed, base_index, index, nullptr, cols, tcols, mask, fp, n_failed, stream};
+    return launch_sample<true>(a);
 }
 
 extern "C" int ob2_sample_from_uniform(const ob2_space *space, int64_t n, int64_t n_stride, const double *U,
                                        void *cols, uint8_t *ok, uint64_t *fp, void *stream) {
-    return launch_sample<false>(space, n, n_stride, 0, 0, nullptr, U, cols, ok, fp, nullptr, stream);
+    const SampleArgs a{space, n, n_stride, 0, 0, nullptr, U, cols, nullptr, ok, fp, nullptr, stream};
+    return launch_sample<false>(a);
 }
 
 extern "C" int ob2_contains(const ob2_space *space, int64_t n, int64_t n_stride, const void *cols,

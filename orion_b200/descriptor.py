@@ -201,12 +201,34 @@ class CompiledSpace(object):
         return ColumnBatch(self, int(n), n_stride, buf, transformed)
 
     # ------------------------------------------------------------ kernels
-    def sample(self, n, seed, base_index=0, with_mask=True, with_fingerprint=False, out=None, index=None):
+    def sample(self, n, seed, base_index=0, with_mask=True, with_fingerprint=False, out=None, index=None,
+               transformed_out=None):
         """Philox-mode Space.sample: returns a ColumnBatch (device).  ``index``
-        (int64 device tensor [n]) replaces the consecutive counters."""
+        (int64 device tensor [n]) replaces the consecutive counters.  With
+        ``transformed_out`` (a transformed ColumnBatch of the same stride) the
+        fused kernel also writes transform(sample) into it."""
         batch = out if out is not None else self.empty_columns(n)
         assert not batch.transformed and batch.n == n
         ns = batch.n_stride
+        if transformed_out is not None:
+            tb = transformed_out
+            assert tb.transformed and tb.n_stride == ns and tb.compiled is self
+            if with_mask and batch.mask is None:
+                batch.mask = torch.empty(ns, dtype=torch.uint8, device=self.device)
+            if with_fingerprint and batch.fp is None:
+                batch.fp = torch.empty((ns, 2), dtype=torch.int64, device=self.device)
+            if batch.n_failed is None:
+                batch.n_failed = torch.zeros(self.n_slots, dtype=torch.int32, device=self.device)
+            else:
+                batch.n_failed.zero_()
+            _lib.check(self.lib.ob2_sample_transform(
+                self.handle, n, ns, int(seed) & _M64, int(base_index) & _M64,
+                index.data_ptr() if index is not None else None, batch.buf.data_ptr(), tb.buf.data_ptr(),
+                batch.mask.data_ptr() if with_mask else None,
+                batch.fp.data_ptr() if with_fingerprint else None,
+                batch.n_failed.data_ptr(), self._stream()))
+            tb.n = n
+            return batch
         if with_mask and batch.mask is None:
             batch.mask = torch.empty(ns, dtype=torch.uint8, device=self.device)
         if with_fingerprint and batch.fp is None:

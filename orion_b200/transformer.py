@@ -238,10 +238,12 @@ class TransformedSpace(Space):
         """``transform(original.sample(...))`` without leaving the device;
         returns (original batch, transformed batch)."""
         compiled = self.compiled()
-        batch = compiled.sample(n_samples, philox_key(seed), base_index=base_index, with_mask=True)
+        tbatch = compiled.empty_columns(n_samples, transformed=True)
+        batch = compiled.sample(n_samples, philox_key(seed), base_index=base_index, with_mask=True,
+                                transformed_out=tbatch)          # one fused kernel
         if check:
             _raise_if_improbable(batch, list(self.original.values()))
-        return batch, compiled.transform(batch)
+        return batch, tbatch
 
     def contains_columns(self, tbatch):
         """``reverse(p) in original`` for every transformed row."""

@@ -159,6 +159,29 @@ def test_transform_reverse_match_oracle(requirement, quantize):
             assert np.array_equal(a, b), s
 
 
+@pytest.mark.parametrize('requirement', ['real', 'integer', 'numerical', None])
+def test_fused_sample_transform_equals_two_kernels(requirement):
+    """ob2_sample_transform == ob2_sample followed by ob2_transform, bit for
+    bit, including rows that went through the rejection path."""
+    from orion_b200.transformer import build_required_space
+    g = gu.load('bounded_reject')
+    extra = [dict(d, name='m_' + d['name']) for d in gu.load('mixed_scalar')['dims'][5:]]
+    dims = g['dims'] + extra + [dict(name='b2', kind='categorical', categories=['x', 'y'])]
+    space = gu.product_space(dims)
+    compiled = build_required_space(requirement, space).compiled()
+    n, seed = 3001, 123
+    plain = compiled.sample(n, seed, with_fingerprint=True)
+    tplain = compiled.transform(plain)
+    tfused = compiled.empty_columns(n, transformed=True)
+    fused = compiled.sample(n, seed, with_fingerprint=True, transformed_out=tfused)
+    for a, b in zip(fused.to_numpy(), plain.to_numpy()):      # (buffers differ only in the stride padding)
+        assert a.dtype == b.dtype and np.array_equal(a, b)
+    assert torch.equal(fused.fp[:n], plain.fp[:n]) and torch.equal(fused.mask[:n], plain.mask[:n])
+    for a, b in zip(tfused.to_numpy(), tplain.to_numpy()):
+        assert a.dtype == b.dtype and np.array_equal(a, b)
+    assert int(fused.n_failed.sum().item()) == int(plain.n_failed.sum().item())
+
+
 def test_reverse_argmax_ties_and_soft_values():
     """reverse of arbitrary real vectors: first maximum wins; k == 2 thresholds at 0.5."""
     from orion_b200.columns import ColumnBatch
