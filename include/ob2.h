@@ -158,6 +158,30 @@ int ob2_set_insert(ob2_set *set, int64_t n, const uint64_t *fp, void *stream);
  * fingerprints stay in the set.  `scratch` is n u32 of caller scratch. */
 int ob2_set_dedup(ob2_set *set, int64_t n, const uint64_t *fp, const uint32_t *order,
                   uint32_t *scratch, uint8_t *keep, void *stream);
+/* Same verdicts as ob2_set_dedup, for callers that cannot allocate device
+ * memory (no counterpart in the reference, which has no device code at all).
+ * Who that is: a plugin inside a process whose framework already owns all of
+ * HBM through its own pool, so a cudaMalloc of its own would fail or fragment
+ * it; a producer loop that must not stall, because cudaMalloc/cudaFree
+ * synchronise the whole device; a minimal binding that only ever holds the
+ * input and output buffers it was given.  The u32-per-entry scratch that
+ * ob2_set_dedup takes from the caller is instead a fixed array inside the
+ * library: every GPU that loads libob2 carries OB2_STATIC_DEDUP_MAX * 4 bytes
+ * (4 MiB) for it until the process exits.  The call itself allocates nothing
+ * (no cudaMalloc/cudaFree, no allocating library routine).
+ *   - n > OB2_STATIC_DEDUP_MAX is refused with OB2_ETOOBIG: split the batch
+ *     into consecutive calls (a row kept by an earlier call beats its copies
+ *     in later ones), or use ob2_set_dedup.
+ *   - the first call on each device looks up the array's device address
+ *     (cudaGetSymbolAddress, with that device current); make that first call
+ *     before any stream capture begins.
+ *   - all calls share the one array per GPU, and it keeps whatever the last
+ *     call wrote.  Nothing in it needs to start at zero (pass 1 writes every
+ *     entry pass 2 reads).  Two calls that overlap on the GPU -- different
+ *     streams, or different sets -- race on it: keep them ordered. */
+#define OB2_STATIC_DEDUP_MAX (1 << 20)
+int ob2_set_dedup_static(ob2_set *set, int64_t n, const uint64_t *fp, const uint32_t *order,
+                         uint8_t *keep, void *stream);
 int ob2_set_probe(const ob2_set *set, int64_t n, const uint64_t *fp, uint8_t *found,
                   void *stream);
 /* number of distinct fingerprints stored; synchronises `stream` */

@@ -17,6 +17,7 @@ TFLAG_FLOOR = 1
 SLOT_DIM_LAST = 1
 SET_SLOT_BYTES = 32
 SET_HEADER_BYTES = 256
+STATIC_DEDUP_MAX = 1 << 20
 
 
 class Ob2Error(RuntimeError):
@@ -67,6 +68,7 @@ SIGNATURES = {
     'ob2_set_destroy': (None, [_vp]),
     'ob2_set_insert': (ctypes.c_int, [_vp, _i64, _vp, _vp]),
     'ob2_set_dedup': (ctypes.c_int, [_vp, _i64, _vp, _vp, _vp, _vp, _vp]),
+    'ob2_set_dedup_static': (ctypes.c_int, [_vp, _i64, _vp, _vp, _vp, _vp]),
     'ob2_set_probe': (ctypes.c_int, [_vp, _i64, _vp, _vp, _vp]),
     'ob2_set_count': (ctypes.c_int, [_vp, ctypes.POINTER(_u64), _vp]),
     'ob2_bucket_by_owner': (ctypes.c_int, [_i64, _vp, _u32, _i32, _i64, _vp, _vp, _vp, _vp, _vp]),

@@ -9,6 +9,7 @@
 // new epoch; pass 1 finds-or-inserts each fingerprint and raises the slot's
 // stamp to max((epoch << 32) | ~order); pass 2 keeps entry i iff the slot was
 // born in this epoch and its stamp is i's own.  No sort, no per-batch clearing.
+#include <mutex>
 #include <new>
 
 #include "ob2_internal.cuh"
@@ -399,6 +400,97 @@ extern "C" int ob2_set_dedup(ob2_set *set, int64_t n, const uint64_t *fp, const 
         return OB2_ETOOBIG;
     }
     const uint32_t epoch = ++set->epoch;
+    set_dedup_pass1<<<blocks, OB2_BLOCK, 0, st>>>(set->header, set->slots, set->n_slots - 1, n, fp, order, epoch, scratch);
+    rc = ob2_check_cuda(cudaGetLastError(), "set_dedup_pass1 launch");
+    if (rc != OB2_OK) return rc;
+    set_dedup_pass2<<<blocks, OB2_BLOCK, 0, st>>>(set->header, set->slots, n, fp, order, epoch, scratch, keep);
+    return ob2_check_cuda(cudaGetLastError(), "set_dedup_pass2 launch");
+}
+
+// ---------------------------------------------------------------------------
+// ob2_set_dedup_static: the same two-pass dedup for callers that must not
+// allocate device memory.
+//
+// ob2_set_dedup needs n u32 of scratch (the slot index pass 1 hands to pass 2)
+// and leaves it to the caller to provide it.  Some callers cannot: a plugin
+// running inside a host process whose framework has already claimed the whole
+// GPU for its own memory pool (a cudaMalloc from the plugin then fails, or
+// fragments the pool); a producer loop that may not stall, since cudaMalloc and
+// cudaFree synchronise the device; a thin binding (cgo/JNI/ctypes) that only
+// ever owns the input and output buffers it was handed.  For them the scratch
+// lives in the library image itself, in the file-scope array below: every GPU
+// that loads libob2 holds OB2_STATIC_DEDUP_MAX * 4 bytes (4 MiB) of it from
+// load until the process exits, whether or not this entry point is used.
+//
+// On the host, `g_static_dedup_scratch` is only a handle for the symbol, not a
+// device address; the address for the current device is looked up once per
+// device with cudaGetSymbolAddress and cached.
+static __device__ __align__(256) uint32_t g_static_dedup_scratch[OB2_STATIC_DEDUP_MAX];
+
+namespace {
+
+constexpr int kMaxDevices = 64;
+uint32_t *g_static_scratch_ptr[kMaxDevices];  // zero-initialised: not looked up yet
+std::mutex g_static_scratch_mutex;
+
+// Device address of the static scratch on the CURRENT device (set-up on first use).
+int static_scratch_for_current_device(uint32_t **out) {
+    int dev = -1;
+    OB2_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevices) {
+        ob2_set_error("ob2_set_dedup_static: device ordinal %d outside [0, %d)", dev, kMaxDevices);
+        return OB2_EINVAL;
+    }
+    std::lock_guard<std::mutex> lock(g_static_scratch_mutex);
+    if (g_static_scratch_ptr[dev] == nullptr) {
+        void *ptr = nullptr;
+        OB2_CUDA(cudaGetSymbolAddress(&ptr, g_static_dedup_scratch));
+        g_static_scratch_ptr[dev] = static_cast<uint32_t *>(ptr);
+    }
+    *out = g_static_scratch_ptr[dev];
+    return OB2_OK;
+}
+
+}  // namespace
+
+extern "C" int ob2_set_dedup_static(ob2_set *set, int64_t n, const uint64_t *fp, const uint32_t *order,
+                                    uint8_t *keep, void *stream) {
+    int rc = check_set_args(set, n, fp);
+    if (rc != OB2_OK) return rc;
+    if (n > (int64_t)OB2_STATIC_DEDUP_MAX) {
+        ob2_set_error("ob2_set_dedup_static: n = %lld exceeds the built-in scratch of %d entries; split the batch "
+                      "or use ob2_set_dedup with caller-provided scratch",
+                      (long long)n, (int)OB2_STATIC_DEDUP_MAX);
+        return OB2_ETOOBIG;
+    }
+    if (n == 0) return OB2_OK;
+    if (keep == nullptr) {
+        ob2_set_error("ob2_set_dedup_static: null keep");
+        return OB2_EINVAL;
+    }
+    int dev = -1;
+    OB2_CUDA(cudaGetDevice(&dev));
+    if (dev != set->device) {
+        ob2_set_error("ob2_set_dedup_static: current device %d is not the set's device %d", dev, set->device);
+        return OB2_EINVAL;
+    }
+    uint32_t *scratch = nullptr;
+    rc = static_scratch_for_current_device(&scratch);
+    if (rc != OB2_OK) return rc;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    rc = reserve(set, n, st);
+    if (rc != OB2_OK) return rc;
+    unsigned blocks;
+    rc = grid_for(n, &blocks);
+    if (rc != OB2_OK) return rc;
+    if (set->epoch == 0xFFFFFFFFu) {
+        ob2_set_error("ob2_set_dedup_static: epoch counter exhausted");
+        return OB2_ETOOBIG;
+    }
+    const uint32_t epoch = ++set->epoch;
+    // Nothing in the scratch has to start at zero: pass 1 writes entry i for
+    // every non-padding fingerprint, and pass 2 only uses entries of non-padding
+    // fingerprints, so whatever an earlier call left behind is never consumed.
     set_dedup_pass1<<<blocks, OB2_BLOCK, 0, st>>>(set->header, set->slots, set->n_slots - 1, n, fp, order, epoch, scratch);
     rc = ob2_check_cuda(cudaGetLastError(), "set_dedup_pass1 launch");
     if (rc != OB2_OK) return rc;

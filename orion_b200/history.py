@@ -74,6 +74,20 @@ class TrialHistory(object):
                                           scratch.data_ptr(), keep.data_ptr(), self._stream()))
         return keep
 
+    def dedup_fingerprints_static(self, fp, keep, n=None, order=None):
+        """``dedup_fingerprints`` for callers that may not allocate on the
+        device: the per-entry scratch is the fixed array built into libob2
+        (``ob2_set_dedup_static``), so the caller passes only ``fp`` in and
+        ``keep`` out, both already allocated.  At most
+        ``_lib.STATIC_DEDUP_MAX`` entries per call; calls must not overlap on
+        the GPU (they share that one array); make the first call on a device
+        before any stream capture (it looks the array's address up)."""
+        n = fp.shape[0] if n is None else n
+        _lib.check(self.lib.ob2_set_dedup_static(self.handle, n, fp.data_ptr(),
+                                                 order.data_ptr() if order is not None else None,
+                                                 keep.data_ptr(), self._stream()))
+        return keep
+
     def probe_fingerprints(self, fp, n=None):
         n = fp.shape[0] if n is None else n
         found = torch.empty(fp.shape[0], dtype=torch.uint8, device=self.device)
