@@ -37,8 +37,10 @@ enum { OB2_OK = 0, OB2_EINVAL = -1, OB2_ECUDA = -2, OB2_ETOOBIG = -3, OB2_ENOMEM
 enum { OB2_KIND_REAL = 0, OB2_KIND_INTEGER = 1, OB2_KIND_CATEGORICAL = 2 };
 
 /* priors with a device inverse CDF (scipy names the reference's DSL maps to,
- * src/orion/core/io/space_builder.py:124-154).  CONST = scale == 0 (rvs returns loc). */
-enum { OB2_DIST_UNIFORM = 0, OB2_DIST_RECIPROCAL = 1, OB2_DIST_NORM = 2, OB2_DIST_CONST = 3 };
+ * src/orion/core/io/space_builder.py:124-154).  CONST = scale == 0 (rvs returns loc).
+ * NONE = any other scipy prior: the space can be checked, transformed, hashed
+ * and deduplicated (only its bounds matter), but ob2_sample* refuse it. */
+enum { OB2_DIST_UNIFORM = 0, OB2_DIST_RECIPROCAL = 1, OB2_DIST_NORM = 2, OB2_DIST_CONST = 3, OB2_DIST_NONE = 4 };
 
 /* per-slot transformer (build_required_space table) */
 enum {

@@ -11,7 +11,7 @@ LIB_PATH = os.path.join(_HERE, 'libob2.so')
 
 OB2_OK = 0
 KIND_REAL, KIND_INTEGER, KIND_CATEGORICAL = 0, 1, 2
-DIST_UNIFORM, DIST_RECIPROCAL, DIST_NORM, DIST_CONST = 0, 1, 2, 3
+DIST_UNIFORM, DIST_RECIPROCAL, DIST_NORM, DIST_CONST, DIST_NONE = 0, 1, 2, 3, 4
 OP_IDENTITY, OP_QUANTIZE, OP_TO_REAL, OP_ENUMERATE, OP_ONEHOT = 0, 1, 2, 3, 4
 TFLAG_FLOOR = 1
 SLOT_DIM_LAST = 1

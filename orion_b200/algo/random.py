@@ -45,7 +45,7 @@ class Random(BaseAlgorithm):
         if not self.dedup:
             return self.space.sample(num, self._rng)
         points = []
-        for _ in range(8):                              # bounded top-up
+        for _ in range(128):                            # bounded top-up (tiny discrete spaces need many rounds)
             need = num - len(points)
             if need <= 0:
                 break

@@ -19,6 +19,7 @@ struct ob2_space {
     ob2_slot_desc *d_slots;
     double *d_cdf;
     bool has_onehot;
+    int unsamplable_slot;  // first slot whose prior has no device inverse CDF, or -1
 };
 
 void ob2_set_error(const char *fmt, ...);

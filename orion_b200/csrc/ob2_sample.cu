@@ -302,6 +302,10 @@ template <bool PHILOX>
 int launch_sample(const SampleArgs &a) {
     int rc = ob2_check_batch(a.sp, a.n, a.n_stride);
     if (rc != OB2_OK) return rc;
+    if (a.sp->unsamplable_slot >= 0) {
+        ob2_set_error("sample: slot %d has a prior without a device inverse CDF (no CPU fallback)", a.sp->unsamplable_slot);
+        return OB2_EINVAL;
+    }
     if (a.cols == nullptr || (!PHILOX && a.U == nullptr)) {
         ob2_set_error("sample: null buffer");
         return OB2_EINVAL;

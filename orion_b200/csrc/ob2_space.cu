@@ -39,13 +39,14 @@ extern "C" int ob2_space_create(const ob2_slot_desc *slots, int32_t n_slots, con
     int64_t units = 0, t_units = 0;
     int32_t t_cols = 0;
     bool has_onehot = false;
+    int unsamplable = -1;
     for (int s = 0; s < n_slots; ++s) {
         const ob2_slot_desc &d = slots[s];
         if (d.kind < OB2_KIND_REAL || d.kind > OB2_KIND_CATEGORICAL) {
             ob2_set_error("slot %d: unknown kind %d", s, d.kind);
             return OB2_EINVAL;
         }
-        if (d.kind != OB2_KIND_CATEGORICAL && (d.dist < OB2_DIST_UNIFORM || d.dist > OB2_DIST_CONST)) {
+        if (d.kind != OB2_KIND_CATEGORICAL && (d.dist < OB2_DIST_UNIFORM || d.dist > OB2_DIST_NONE)) {
             ob2_set_error("slot %d: prior %d has no device inverse CDF", s, d.dist);
             return OB2_EINVAL;
         }
@@ -55,6 +56,7 @@ extern "C" int ob2_space_create(const ob2_slot_desc *slots, int32_t n_slots, con
                           d.cdf_off + d.n_cats, cdf_len);
             return OB2_EINVAL;
         }
+        if (d.kind != OB2_KIND_CATEGORICAL && d.dist == OB2_DIST_NONE && unsamplable < 0) unsamplable = s;
         if (d.dim_first < 0 || d.dim_first > s) {
             ob2_set_error("slot %d: dim_first %d out of order", s, d.dim_first);
             return OB2_EINVAL;
@@ -129,6 +131,7 @@ extern "C" int ob2_space_create(const ob2_slot_desc *slots, int32_t n_slots, con
     sp->t_cols = t_cols;
     sp->smem_bytes = smem;
     sp->has_onehot = has_onehot;
+    sp->unsamplable_slot = unsamplable;
     sp->d_slots = nullptr;
     sp->d_cdf = nullptr;
     int rc = ob2_check_cuda(cudaGetDevice(&sp->device), "cudaGetDevice");

@@ -78,9 +78,8 @@ def _prior_params(dim):
         return _lib.DIST_RECIPROCAL, float(la), float(np.log(b) - la), loc, scale
     if name == 'norm':
         return _lib.DIST_NORM, 0.0, 0.0, loc, scale
-    raise NotImplementedError(
-        "Dimension '{}': prior '{}' has no device inverse CDF yet (supported: uniform, "
-        "reciprocal/loguniform, norm). There is no CPU fallback.".format(dim.name, name))
+    # any other scipy prior: bounds-only (contains / transform / dedup work, sampling refuses)
+    return _lib.DIST_NONE, 0.0, 0.0, loc, scale
 
 
 class CompiledSpace(object):
@@ -101,6 +100,7 @@ class CompiledSpace(object):
         self.dim_kinds = ['real' if d.type == 'dimension' else d.type for d in dims]
         self.dim_shapes = [tuple(d.shape) for d in dims]
         self.dim_categories = [tuple(d.categories) if d.type == 'categorical' else None for d in dims]
+        self.unsamplable = None        # (dimension name, prior) without a device inverse CDF
         self.dim_first = []            # first slot of each dimension
         self.dim_bounds = []
         slots = []
@@ -128,6 +128,8 @@ class CompiledSpace(object):
                 low, high = 0.0, float(n_cats)
             else:
                 dist, p0, p1, loc, scale = _prior_params(dim)
+                if dist == _lib.DIST_NONE and self.unsamplable is None:
+                    self.unsamplable = (dim.name, dim._prior_name)
                 low, high = dim.interval()
                 low, high = float(low), float(high)
                 cdf_off = n_cats = 0
@@ -207,6 +209,7 @@ class CompiledSpace(object):
         (int64 device tensor [n]) replaces the consecutive counters.  With
         ``transformed_out`` (a transformed ColumnBatch of the same stride) the
         fused kernel also writes transform(sample) into it."""
+        self._require_samplable()
         batch = out if out is not None else self.empty_columns(n)
         assert not batch.transformed and batch.n == n
         ns = batch.n_stride
@@ -245,8 +248,15 @@ class CompiledSpace(object):
             batch.n_failed.data_ptr(), self._stream()))
         return batch
 
+    def _require_samplable(self):
+        if self.unsamplable is not None:
+            raise NotImplementedError(
+                "Dimension '{}': prior '{}' has no device inverse CDF yet (supported: uniform, "
+                "reciprocal/loguniform, norm). There is no CPU fallback.".format(*self.unsamplable))
+
     def sample_from_uniform(self, U, n=None, with_fingerprint=False):
         """Parity mode: U is a float64 tensor [n_slots][n_stride] (device)."""
+        self._require_samplable()
         assert U.dtype == torch.float64 and U.is_cuda and U.dim() == 2 and U.shape[0] == self.n_slots
         ns = U.shape[1]
         if ns % 32:

@@ -14,7 +14,10 @@ from .space import Categorical, Integer, Real, Space
 
 
 def _literal_call(expression):
-    node = ast.parse(expression.strip(), mode='eval').body
+    try:
+        node = ast.parse(expression.strip(), mode='eval').body
+    except SyntaxError:
+        node = None
     if not isinstance(node, ast.Call) or not isinstance(node.func, ast.Name):
         raise TypeError("Please provide a valid form for prior: 'distribution(*args, **kwargs)'. "
                         "Provided: '{}'".format(expression))
