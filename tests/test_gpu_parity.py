@@ -294,3 +294,63 @@ def test_empty_and_bad_batches():
     lib = _lib.load()
     assert lib.ob2_sample(compiled.handle, 5, 7, 0, 0, None, b.buf.data_ptr(), None, None, None, None) == -1
     assert b'n_stride' in lib.ob2_last_error()
+
+
+@pytest.mark.parametrize('world', [2, 8])
+def test_exchange_kernels_emulated_on_one_gpu(world):
+    """ob2_bucket_by_owner / ob2_scatter_verdict, and the whole sharded dedup
+    with `world` ranks emulated on ONE device: the all_to_all is a transpose of
+    the [source][owner] bucket grid, each owner has its own hash set.  Result
+    must equal a single set fed the ranks' batches in rank order."""
+    from orion_b200 import spaces
+    from orion_b200.dist import DeviceOps, bucket_capacity
+    from orion_b200.history import TrialHistory
+    space = spaces.rosen2()
+    ops = DeviceOps('cuda')
+    n = 20000
+    rng = np.random.RandomState(world)
+    pool = rng.randint(1, 2 ** 62, size=(world * n // 2, 2), dtype=np.int64)
+    batches = [pool[rng.randint(0, len(pool), size=n)].copy() for _ in range(world)]
+    for b in batches:
+        b[rng.random_sample(n) < 0.02] = 0                      # padding entries are dropped
+    cap = bucket_capacity(n, world)
+    grid = []
+    for r, b in enumerate(batches):
+        out = (torch.full((world, cap, 2), -1, dtype=torch.int64, device='cuda'),
+               torch.zeros((world, cap), dtype=torch.int32, device='cuda'),
+               torch.zeros((world, cap), dtype=torch.int32, device='cuda'),
+               torch.zeros(world, dtype=torch.int32, device='cuda'))
+        ops.bucket(torch.from_numpy(b).cuda(), n, r * n, world, cap, out)
+        out_fp, out_key, out_src, counts = [t.cpu().numpy() for t in out]
+        owner = b[:, 1].view(np.uint64) % np.uint64(world)
+        for o in range(world):
+            rows = np.nonzero((owner == o) & (b[:, 0] != 0))[0]
+            assert counts[o] == len(rows) <= cap
+            got = out_src[o, :len(rows)]
+            assert sorted(got.tolist()) == rows.tolist()         # every row exactly once, any order
+            assert np.array_equal(out_fp[o, :len(rows)], b[got])
+            assert np.array_equal(out_key[o, :len(rows)], r * n + got)
+            assert not out_fp[o, len(rows):].any()               # zero-padded tail
+        grid.append(out)
+    # "all_to_all": owner o receives bucket o of every source, in source order
+    shards = [TrialHistory(space, capacity=4 * n) for _ in range(world)]
+    verdict_back = [[None] * world for _ in range(world)]
+    for o in range(world):
+        in_fp = torch.stack([grid[r][0][o] for r in range(world)]).view(-1, 2).contiguous()
+        in_key = torch.stack([grid[r][1][o] for r in range(world)]).view(-1).contiguous()
+        verdict = torch.zeros(world * cap, dtype=torch.uint8, device='cuda')
+        ops.dedup(shards[o], in_fp, in_key, verdict)
+        for r in range(world):
+            verdict_back[r][o] = verdict[r * cap:(r + 1) * cap]
+    seen = set()
+    for r, b in enumerate(batches):
+        keep = torch.zeros(n, dtype=torch.uint8, device='cuda')
+        back = torch.cat(verdict_back[r]).contiguous()
+        ops.scatter(grid[r][2].view(-1), back, grid[r][0].view(-1, 2), keep)
+        want = np.zeros(n, dtype=np.uint8)
+        for i, (lo, hi) in enumerate(b):
+            if lo != 0 and (int(lo), int(hi)) not in seen:
+                seen.add((int(lo), int(hi)))
+                want[i] = 1
+        assert np.array_equal(keep.cpu().numpy(), want), 'rank %d' % r
+    assert sum(len(s) for s in shards) == len(seen)
