@@ -53,6 +53,7 @@ def parse_args():
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--e2e-steps', type=int, default=2)
     ap.add_argument('--unfused', action='store_true', help='sample and transform as two kernels')
+    ap.add_argument('--serial', action='store_true', help='no stream pipeline: one stream, kernels back to back')
     return ap.parse_args()
 
 
@@ -318,7 +319,7 @@ def run_b200(args):
 
     n = args.cands
     K, W = args.steps, args.warmup
-    total_steps = K + W + args.e2e_steps + 1
+    total_steps = 2 * K + W + args.e2e_steps + 2      # timed + serial pass + e2e (+ its warm-up)
     space = spaces.mixed64()
     tspace = build_required_space('real', space)
     compiled = tspace.compiled()
@@ -326,7 +327,7 @@ def run_b200(args):
     # ---- history shard: rows from counters [2^40 + rank*H, ...), fingerprints only
     H = args.history
     cap_rows = H + int(0.92 * n) * total_steps + n
-    history = TrialHistory(compiled, n_slots=table_slots_for(cap_rows, load=0.5))
+    history = TrialHistory(compiled, n_slots=table_slots_for(cap_rows, load=0.75))
     sharded = ShardedHistory(history, device=dev)
     chunk = n
     hb = compiled.empty_columns(chunk)
@@ -354,10 +355,10 @@ def run_b200(args):
         return idx
 
     index_dev = [step_index(s) for s in range(W + K)]
-    batch = compiled.empty_columns(n)
-    tbatch = compiled.empty_columns(n, transformed=True)
-    back = compiled.empty_columns(n)
-    batch.keep = torch.empty(batch.n_stride, dtype=torch.uint8, device=dev)
+    # two buffer sets (28 GB each) serve the pipeline, the serial pass and the e2e leg
+    from orion_b200.pipeline import CandidatePipeline
+    pipe = CandidatePipeline(compiled, sharded, n, depth=2)
+    batch, tbatch, back = pipe.slots[0].batch, pipe.slots[0].tbatch, pipe.slots[0].back
     fused = not args.unfused
     kernel_names = ['sample+transform', 'reverse', 'dedup'] if fused else ['sample', 'transform', 'reverse', 'dedup']
     ev = [[torch.cuda.Event(enable_timing=True) for _ in range(len(kernel_names) + 1)] for _ in range(K)]
@@ -389,30 +390,72 @@ def run_b200(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    for s in range(W):
-        one_step(s)
-    sync_all()
-    launches[0] = 0
-    clocks = Clocks(local_rank)
-    if rank == 0:
-        clocks.start()
+    def max_over_ranks(ms):
+        if world > 1:
+            t = torch.tensor([ms], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return float(t.item())
+        return ms
+
+    pipelined = fused and not args.serial
     t_begin = torch.cuda.Event(enable_timing=True)
     t_end = torch.cuda.Event(enable_timing=True)
-    t_begin.record()
-    for s in range(K):
-        ev[s][0].record()
-        one_step(W + s, ev[s])
-    t_end.record()
-    sync_all()
-    clock_info = clocks.stop() if rank == 0 else None
-    elapsed_ms = t_begin.elapsed_time(t_end)
-    if world > 1:
-        t = torch.tensor([elapsed_ms], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        elapsed_ms = float(t.item())
-    kept_last = int(batch.keep[:n].sum().item())
-    mask_ok = bool(batch.mask[:n].all().item())
-    round_trip_ok = bool(torch.equal(back.buf, batch.buf))
+    clocks = Clocks(local_rank)
+    contended_ms = None
+    if pipelined:
+        # ---- timed region: K steps through the stream pipeline (sample+transform of step k+1
+        # overlaps reverse and dedup of step k; every result is still materialised)
+        for s in range(W):
+            pipe.submit(SEED, index=index_dev[s])
+        pipe.drain()
+        sync_all()
+        pipe.timed = True
+        if rank == 0:
+            clocks.start()
+        t_begin.record()
+        for s in range(K):
+            slot = pipe.submit(SEED, index=index_dev[W + s])
+        pipe.drain()
+        t_end.record()
+        sync_all()
+        clock_info = clocks.stop() if rank == 0 else None
+        elapsed_ms = max_over_ranks(t_begin.elapsed_time(t_end))
+        timed_launches = K * (4 + (0 if world == 1 else 3))
+        contended_ms = pipe.kernel_ms()
+        pipe.timed = False
+        last_batch, last_back = slot.batch, slot.back
+        kept_last = int(last_batch.keep[:n].sum().item())
+        mask_ok = bool(last_batch.mask[:n].all().item())
+        round_trip_ok = bool(torch.equal(last_back.buf, last_batch.buf))
+        # ---- the same K steps, one stream, no overlap: clean per-kernel durations for the roofline
+        for s in range(K):
+            index_dev[W + s] = step_index(W + K + s)      # fresh counters, same duplicate mix
+        sync_all()
+        for s in range(K):
+            ev[s][0].record()
+            one_step(W + s, ev[s])
+        sync_all()
+        serial_ms = sum(ev[s][0].elapsed_time(ev[s][-1]) for s in range(K)) / K
+    else:
+        for s in range(W):
+            one_step(s)
+        sync_all()
+        launches[0] = 0
+        if rank == 0:
+            clocks.start()
+        t_begin.record()
+        for s in range(K):
+            ev[s][0].record()
+            one_step(W + s, ev[s])
+        t_end.record()
+        sync_all()
+        clock_info = clocks.stop() if rank == 0 else None
+        elapsed_ms = max_over_ranks(t_begin.elapsed_time(t_end))
+        timed_launches = launches[0]
+        serial_ms = elapsed_ms / K
+        kept_last = int(batch.keep[:n].sum().item())
+        mask_ok = bool(batch.mask[:n].all().item())
+        round_trip_ok = bool(torch.equal(back.buf, batch.buf))
     sharded._check_overflow(sharded._buffers(n)) if world > 1 else None
     hist_rows1 = len(history)
 
@@ -424,41 +467,59 @@ def run_b200(args):
     e2e = None
     if args.e2e_steps > 0:
         from orion_b200.algo.random import Random  # noqa: F401  (public entry; the column path below is what it calls)
-        host_idx = [torch.empty(n, dtype=torch.int64).pin_memory() for _ in range(args.e2e_steps + 1)]
+        from orion_b200.pipeline import CandidatePipeline
+        E = args.e2e_steps
+        host_idx = [torch.empty(n, dtype=torch.int64).pin_memory() for _ in range(E + 2)]
         for j, h in enumerate(host_idx):
-            h.copy_(step_index(W + K + j))
-        host_cols = torch.empty(batch.buf.numel(), dtype=torch.uint8).pin_memory()
-        host_keep = torch.empty(batch.n_stride, dtype=torch.uint8).pin_memory()
-        idx_dev = torch.empty(n, dtype=torch.int64, device=dev)
+            h.copy_(step_index(W + 2 * K + j))
+        # two sets of pinned host buffers and device staging: the copies of step j overlap step j+1
+        host_cols = [torch.empty(batch.buf.numel(), dtype=torch.uint8).pin_memory() for _ in range(2)]
+        host_keep = [torch.empty(batch.n_stride, dtype=torch.uint8).pin_memory() for _ in range(2)]
+        idx_dev = [torch.empty(n, dtype=torch.int64, device=dev) for _ in range(2)]
+        copied = [torch.cuda.Event() for _ in range(2)]
+        s_copy = torch.cuda.Stream(device=dev)
+        epipe = pipe
+        epipe.drain()
+        cur = torch.cuda.current_stream()
 
         def e2e_step(j):
-            idx_dev.copy_(host_idx[j], non_blocking=True)                       # H2D: this step's input
-            compiled.sample(n, SEED, index=idx_dev, with_mask=True, with_fingerprint=True, out=batch,
-                            transformed_out=tbatch)
-            compiled.reverse(tbatch, out=back)
-            sharded.dedup(batch.fp, n, per_rank_n=n, keep=batch.keep, check=False)
-            host_cols.copy_(back.buf, non_blocking=True)                        # D2H: the candidates
-            host_keep.copy_(batch.keep, non_blocking=True)                      # D2H: the verdicts
-            torch.cuda.current_stream().synchronize()
-            return int(host_keep[:n].sum())
+            b = j % 2
+            slot = epipe.slots[epipe.k % 2]
+            if slot.busy:
+                cur.wait_event(slot.sampled)                                    # idx_dev[b] no longer read
+            idx_dev[b].copy_(host_idx[j], non_blocking=True)                    # H2D: this step's input
+            slot = epipe.submit(SEED, index=idx_dev[b])
+            with torch.cuda.stream(s_copy):
+                s_copy.wait_event(slot.reversed)
+                s_copy.wait_event(slot.deduped)
+                host_cols[b].copy_(slot.back.buf, non_blocking=True)            # D2H: the candidates
+                host_keep[b].copy_(slot.batch.keep, non_blocking=True)          # D2H: the verdicts
+                copied[b].record()
+            slot.hold = copied[b]                                               # buffers stay put until copied out
+
+        def e2e_finish():
+            epipe.drain()
+            cur.wait_stream(s_copy)
 
         e2e_step(0)
+        e2e_step(1)
+        e2e_finish()
         sync_all()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        for j in range(args.e2e_steps):
-            e2e_step(1 + j)
+        for j in range(E):
+            e2e_step(2 + j)
+        e2e_finish()
         e1.record()
         sync_all()
-        e2e_ms = e0.elapsed_time(e1)
-        if world > 1:
-            t = torch.tensor([e2e_ms], dtype=torch.float64, device=dev)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            e2e_ms = float(t.item())
+        e2e_ms = max_over_ranks(e0.elapsed_time(e1))
+        e2e_kept = int(host_keep[(E + 1) % 2][:n].sum())
         e2e = {"value": world * n * args.e2e_steps / (e2e_ms * 1e-3), "unit": UNIT,
-               "h2d_bytes_per_step": int(n * 8), "d2h_bytes_per_step": int(host_cols.numel() + host_keep.numel()),
-               "steps": args.e2e_steps,
-               "api": "sample(index from pinned host) -> transform -> reverse -> dedup -> columns+keep to pinned host"}
+               "h2d_bytes_per_step": int(n * 8),
+               "d2h_bytes_per_step": int(host_cols[0].numel() + host_keep[0].numel()),
+               "steps": args.e2e_steps, "kept_last_step": e2e_kept,
+               "api": "CandidatePipeline.submit(index copied from pinned host) -> sample+transform -> reverse || dedup "
+                      "-> candidate columns + keep mask copied to pinned host (copies overlap the next step)"}
 
     if rank != 0:
         if world > 1:
@@ -491,12 +552,20 @@ def run_b200(args):
         "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": workload_config(args, world),
         "roofline": {"bound": "hbm", "kernel": dominant, "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                     "how": ("CUDA events around each kernel over K serial steps run right after the timed region "
+                             "(inside it kernels of adjacent steps overlap; those contended durations are in "
+                             "kernels_in_timed_region_ms)" if pipelined else
+                             "CUDA events around each kernel inside the timed region"),
                      "algorithmic_bytes_per_candidate": algo_bytes[dominant]},
         "kernels": kernels,
         "step_roofline": {"algorithmic_bytes_per_candidate": step_bytes,
                           "achieved_GBps": step_bytes * n / (ms_per_step * 1e-3) / 1e9,
                           "frac": step_bytes * n / (ms_per_step * 1e-3) / 1e9 / peak},
-        "e2e": e2e, "gpu_launches": launches[0], "clocks": clock_info,
+        "e2e": e2e, "gpu_launches": timed_launches, "clocks": clock_info,
+        "timed_region": ("K steps through orion_b200.pipeline.CandidatePipeline (3 streams, 2 buffer sets)" if pipelined
+                         else "K steps on one stream, kernels back to back"),
+        "serial_ms_per_step": serial_ms,
+        "kernels_in_timed_region_ms": contended_ms,
         "checks": {"kept_last_step": kept_last, "kept_frac_last_step": kept_last / float(n), "all_in_space": mask_ok,
                    "reverse_of_transform_is_identity": round_trip_ok,
                    "history_rows_before": hist_rows0, "history_rows_after": hist_rows1},

@@ -1,0 +1,121 @@
+"""Stream-pipelined candidate generation: the whole hot path, batch after batch.
+
+One batch goes through three kernels groups with different limits on a B200:
+
+  A  sample + transform   (``ob2_sample_transform``)  instruction-issue bound
+  B  reverse              (``ob2_reverse``)           HBM bound
+  C  dedup (+ exchange)   (``ob2_set_dedup``, NCCL)   DRAM-latency bound
+
+B and C only depend on A, not on each other, and A of the next batch depends on
+neither -- so they run on three CUDA streams with events for the true
+dependencies (and for buffer reuse).  With ``depth`` >= 2 buffer sets, A of
+batch k+1 overlaps B and C of batch k: the issue-bound and the bandwidth-bound
+work share the SMs instead of taking turns.
+
+This is the producer loop of the reference (``Producer.produce`` ->
+``PrimaryAlgo.suggest`` -> ``Random.suggest`` -> ``Space.sample``,
+``src/orion/core/worker/producer.py:42-52``) restated for device-resident
+batches; every result of the unfused path is still materialised.
+"""
+import torch
+
+from .dist import ShardedHistory
+
+
+class BatchSlot(object):
+    """One set of buffers travelling through the pipeline."""
+
+    def __init__(self, compiled, n):
+        dev = compiled.device
+        self.batch = compiled.empty_columns(n)                      # original columns + mask + fp + keep
+        self.tbatch = compiled.empty_columns(n, transformed=True)   # transform(sample)
+        self.back = compiled.empty_columns(n)                       # reverse(transform(sample))
+        self.batch.keep = torch.empty(self.batch.n_stride, dtype=torch.uint8, device=dev)
+        self.sampled = torch.cuda.Event()
+        self.reversed = torch.cuda.Event()
+        self.deduped = torch.cuda.Event()
+        self.busy = False
+        self.hold = None        # event a consumer sets: the slot is not reused before it completes
+
+
+class CandidatePipeline(object):
+    """sample+transform -> (reverse || dedup) over a ring of ``depth`` buffer sets."""
+
+    def __init__(self, compiled, history, n, depth=2, timed=False):
+        self.compiled = compiled
+        self.n = n
+        self.sharded = history if isinstance(history, ShardedHistory) else ShardedHistory(history, device=compiled.device)
+        self.slots = [BatchSlot(compiled, n) for _ in range(depth)]
+        dev = compiled.device
+        self.s_sample = torch.cuda.Stream(device=dev)
+        self.s_reverse = torch.cuda.Stream(device=dev)
+        self.s_dedup = torch.cuda.Stream(device=dev)
+        self.k = 0
+        self.timed = timed
+        self.timings = []          # per step: (sample_ms_events, reverse_events, dedup_events) when timed
+
+    def submit(self, seed, base_index=0, index=None):
+        """Enqueue one batch; returns its BatchSlot (results are valid after
+        ``slot.reversed`` / ``slot.deduped`` have completed)."""
+        slot = self.slots[self.k % len(self.slots)]
+        self.k += 1
+        c, n = self.compiled, self.n
+        caller = torch.cuda.current_stream(c.device)
+        ev = None
+        if self.timed:
+            ev = [torch.cuda.Event(enable_timing=True) for _ in range(6)]
+        with torch.cuda.stream(self.s_sample):
+            self.s_sample.wait_stream(caller)                       # inputs (index) produced by the caller
+            if slot.busy:                                           # buffers still read by B / C of an older batch
+                self.s_sample.wait_event(slot.reversed)
+                self.s_sample.wait_event(slot.deduped)
+            if slot.hold is not None:                               # ... or by a consumer (e.g. a copy to the host)
+                self.s_sample.wait_event(slot.hold)
+                slot.hold = None
+            if ev:
+                ev[0].record()
+            c.sample(n, seed, base_index=base_index, index=index, with_mask=True, with_fingerprint=True,
+                     out=slot.batch, transformed_out=slot.tbatch)
+            if ev:
+                ev[1].record()
+            slot.sampled.record()
+        with torch.cuda.stream(self.s_reverse):
+            self.s_reverse.wait_event(slot.sampled)
+            if ev:
+                ev[2].record()
+            c.reverse(slot.tbatch, out=slot.back)
+            if ev:
+                ev[3].record()
+            slot.reversed.record()
+        with torch.cuda.stream(self.s_dedup):
+            self.s_dedup.wait_event(slot.sampled)
+            if ev:
+                ev[4].record()
+            self.sharded.dedup(slot.batch.fp, n, per_rank_n=n, keep=slot.batch.keep, check=False)
+            if ev:
+                ev[5].record()
+            slot.deduped.record()
+        slot.busy = True
+        if ev:
+            self.timings.append(ev)
+        return slot
+
+    def drain(self):
+        """Make the caller's stream wait for everything submitted so far."""
+        caller = torch.cuda.current_stream(self.compiled.device)
+        caller.wait_stream(self.s_sample)
+        caller.wait_stream(self.s_reverse)
+        caller.wait_stream(self.s_dedup)
+
+    def kernel_ms(self):
+        """Average per-kernel durations (ms) from the on-stream events of timed
+        submissions; durations include contention between overlapped kernels."""
+        if not self.timings:
+            return {}
+        torch.cuda.synchronize(self.compiled.device)
+        k = len(self.timings)
+        return {
+            'sample+transform': sum(e[0].elapsed_time(e[1]) for e in self.timings) / k,
+            'reverse': sum(e[2].elapsed_time(e[3]) for e in self.timings) / k,
+            'dedup': sum(e[4].elapsed_time(e[5]) for e in self.timings) / k,
+        }
