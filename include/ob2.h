@@ -52,6 +52,7 @@ enum {
 };
 #define OB2_TFLAG_FLOOR 1 /* Quantize rounds with floor instead of rint */
 #define OB2_SLOT_DIM_LAST 1
+#define OB2_SLOT_CAT_UNIFORM 2 /* categorical with equal probabilities (a hint: enables the guess-and-walk draw) */
 
 /* One scalar slot of the space (a dimension with shape contributes prod(shape)
  * slots, C order).  Plain data, identical layout on host and device. */

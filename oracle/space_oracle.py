@@ -435,31 +435,23 @@ def _splitmix64(x: int) -> int:
 
 
 def slot_hash_keys(n_slots: int) -> np.ndarray:
-    """[S][4] uint64: (xor key A, odd multiplier A, xor key B, odd multiplier B)."""
-    out = np.zeros((n_slots, 4), dtype=U64)
+    """[S][3] uint64: xor key, lane-a multipliers, lane-b multipliers.  A
+    multiplier word packs two odd 32-bit multipliers: its low half multiplies
+    the low 32 bits of the value, its high half the high 32 bits."""
+    out = np.zeros((n_slots, 3), dtype=U64)
     for s in range(n_slots):
-        for j in range(4):
+        for j in range(3):
             v = _splitmix64((4 * s + j + 1) * 0xD6E8FEB86659FD93 & _M64)
-            if j & 1:
-                v |= 1
+            if j:
+                v |= 0x0000000100000001
             out[s, j] = v
     return out
 
 
-def _mul_hi_lo(x: np.ndarray, m: int):
-    """64x64 -> 128-bit product of a uint64 array with a scalar, via 32-bit limbs."""
+def _lane(x: np.ndarray, mult: int) -> np.ndarray:
+    """lo32(x) * lo32(mult) + hi32(x) * hi32(mult), wrapping at 64 bits."""
     mask = U64(0xFFFFFFFF)
-    sh = U64(32)
-    x0, x1 = x & mask, x >> sh
-    m0, m1 = U64(m & 0xFFFFFFFF), U64(m >> 32)
-    p00 = x0 * m0
-    p01 = x0 * m1
-    p10 = x1 * m0
-    p11 = x1 * m1
-    mid = (p00 >> sh) + (p01 & mask) + (p10 & mask)
-    lo = (p00 & mask) | ((mid & mask) << sh)
-    hi = p11 + (p01 >> sh) + (p10 >> sh) + (mid >> sh)
-    return hi, lo
+    return (x & mask) * U64(mult & 0xFFFFFFFF) + (x >> U64(32)) * U64(mult >> 32)
 
 
 def _fmix64(x: np.ndarray) -> np.ndarray:
@@ -487,10 +479,11 @@ def canonical_words(cols: Sequence[np.ndarray]) -> List[np.ndarray]:
 def fingerprint(cols: Sequence[np.ndarray]):
     """128-bit row fingerprint as (lo, hi) uint64 arrays.
 
-    Per slot one 128-bit product ``(word ^ key) * odd_mult`` (injective in the
-    word); lane a is the wrapping sum over slots of its high 64 bits, lane b of
-    its low 64 bits; each lane is finished with murmur3's ``fmix64``.  ``lo``
-    is never 0 (0 marks an empty hash-set slot).
+    Multilinear hash: each slot's 64-bit word is xored with a per-slot key and
+    split into 32-bit halves; lane a adds ``lo32 * m0 + hi32 * m1``, lane b
+    ``lo32 * m2 + hi32 * m3`` (odd 32-bit multipliers per slot, 64-bit wrapping
+    sums over the slots); each lane is finished with murmur3's ``fmix64``.
+    ``lo`` is never 0 (0 marks an empty hash-set slot).
     """
     S = len(cols)
     keys = slot_hash_keys(S)
@@ -499,9 +492,9 @@ def fingerprint(cols: Sequence[np.ndarray]):
     acc_b = np.zeros(n, dtype=U64)
     with np.errstate(over='ignore'):
         for s, w in enumerate(canonical_words(cols)):
-            hi, lo = _mul_hi_lo(w ^ keys[s, 0], int(keys[s, 1]))
-            acc_a = acc_a + hi
-            acc_b = acc_b + lo
+            x = w ^ keys[s, 0]
+            acc_a = acc_a + _lane(x, int(keys[s, 1]))
+            acc_b = acc_b + _lane(x, int(keys[s, 2]))
         lo = _fmix64(acc_a ^ U64((S * 0x9E3779B97F4A7C15) & _M64))
         hi = _fmix64(acc_b + U64((S * 0xC2B2AE3D27D4EB4F) & _M64))
     lo = np.where(lo == 0, U64(1), lo)

@@ -15,6 +15,7 @@ DIST_UNIFORM, DIST_RECIPROCAL, DIST_NORM, DIST_CONST, DIST_NONE = 0, 1, 2, 3, 4
 OP_IDENTITY, OP_QUANTIZE, OP_TO_REAL, OP_ENUMERATE, OP_ONEHOT = 0, 1, 2, 3, 4
 TFLAG_FLOOR = 1
 SLOT_DIM_LAST = 1
+SLOT_CAT_UNIFORM = 2
 SET_SLOT_BYTES = 32
 SET_HEADER_BYTES = 256
 STATIC_DEDUP_MAX = 1 << 20

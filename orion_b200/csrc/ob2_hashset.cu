@@ -2,13 +2,16 @@
 //
 // The set is an open-addressing table of 32-byte slots -- one DRAM sector per
 // probe -- keyed by the 128-bit fingerprint:
-//     { u64 lo, u64 hi, u64 stamp, u32 born, u32 pad }
+//     { u64 lo, u64 hi, u64 stamp, u32 born, u32 winner }
 // lo == 0 marks an empty slot (fingerprints never have lo == 0).  Keys are
 // claimed with one 128-bit compare-and-swap, so a slot is either empty or holds
-// a complete key.  Deterministic first-wins inside a batch: every call gets a
-// new epoch; pass 1 finds-or-inserts each fingerprint and raises the slot's
-// stamp to max((epoch << 32) | ~order); pass 2 keeps entry i iff the slot was
-// born in this epoch and its stamp is i's own.  No sort, no per-batch clearing.
+// a complete key.  Deterministic first-wins inside a batch: every dedup call
+// gets a new epoch.  Pass 1 finds-or-inserts each fingerprint: a key that was
+// there before the call is a duplicate (final, no atomic); a key it inserts is
+// kept provisionally; a key inserted by ANOTHER entry of the same call (`born`
+// == epoch) makes both compete through atomicMax on the slot's stamp
+// ((epoch << 32) | ~order).  Pass 2 revisits only those in-batch duplicates and
+// gives the slot to the smallest order key.  No sort, no per-batch clearing.
 #include <mutex>
 #include <new>
 
@@ -19,8 +22,8 @@ namespace {
 struct __align__(32) SetSlot {
     uint64_t lo, hi;
     unsigned long long stamp;
-    uint32_t born;
-    uint32_t pad;
+    uint32_t born;    // 0 = never completed an insert; epoch of the dedup call that inserted it; or OB2_BORN_HISTORY
+    uint32_t winner;  // batch position of the entry whose CAS inserted the key (meaningful within its epoch)
 };
 static_assert(sizeof(SetSlot) == OB2_SET_SLOT_BYTES, "slot size");
 
@@ -107,6 +110,9 @@ __device__ __forceinline__ void warp_count_add(unsigned long long *counter, bool
     if (flag && (threadIdx.x & 31) == (__ffs(ballot) - 1)) atomicAdd(counter, (unsigned long long)__popc(ballot));
 }
 
+#define OB2_BORN_HISTORY 0xFFFFFFFFu  // inserted by ob2_set_insert (not by a dedup call)
+#define OB2_NO_CONFLICT 0xFFFFFFFFu   // scratch marker: verdict already final after pass 1
+
 __global__ void __launch_bounds__(OB2_BLOCK)
 set_insert_kernel(SetHeader *hdr, SetSlot *slots, uint64_t mask, int64_t n, const uint64_t *__restrict__ fp) {
     const int64_t i = (int64_t)blockIdx.x * OB2_BLOCK + threadIdx.x;
@@ -117,51 +123,80 @@ set_insert_kernel(SetHeader *hdr, SetSlot *slots, uint64_t mask, int64_t n, cons
             uint64_t pos;
             const int r = find_or_insert(slots, mask, key.x, key.y, pos);
             inserted = r == INSERTED;
+            if (inserted) slots[pos].born = OB2_BORN_HISTORY;  // every completed insert has born != 0
             if (r == OVERFLOW) hdr->overflow = 1;
         }
     }
     warp_count_add(&hdr->count, inserted);
 }
 
-__global__ void __launch_bounds__(OB2_BLOCK)
-set_dedup_pass1(SetHeader *hdr, SetSlot *slots, uint64_t mask, int64_t n, const uint64_t *__restrict__ fp,
-                const uint32_t *__restrict__ order, uint32_t epoch, uint32_t *__restrict__ scratch) {
-    const int64_t i = (int64_t)blockIdx.x * OB2_BLOCK + threadIdx.x;
-    if (i >= n) return;
-    const ulonglong2 key = __ldg(reinterpret_cast<const ulonglong2 *>(fp) + i);
-    if (key.x == 0) return;  // padding
-    uint64_t pos;
-    const int r = find_or_insert(slots, mask, key.x, key.y, pos);
-    if (r == OVERFLOW) {
-        hdr->overflow = 1;
-        scratch[i] = 0xFFFFFFFFu;
-        return;
-    }
-    SetSlot *slot = slots + pos;
-    if (r == INSERTED) slot->born = epoch;  // read only by pass 2, after this grid retires
-    const uint32_t ord = order ? __ldg(order + i) : (uint32_t)i;
-    atomicMax(&slot->stamp, ((unsigned long long)epoch << 32) | (unsigned long long)(0xFFFFFFFFu - ord));
-    scratch[i] = (uint32_t)pos;
+__device__ __forceinline__ unsigned long long dedup_tag(uint32_t epoch, uint32_t ord) {
+    return ((unsigned long long)epoch << 32) | (unsigned long long)(0xFFFFFFFFu - ord);  // max tag = smallest order key
 }
 
+// Pass 1 settles almost every entry with ONE probe:
+//   - key absent  -> insert it (128-bit CAS), keep = 1 for now, remember who won the slot;
+//   - key present since an earlier call (born != 0 and != epoch) -> keep = 0, no atomic at all;
+//   - key present and inserted during THIS call (born == epoch, or 0 = the winner's store is
+//     still in flight) -> a duplicate inside the batch: compete for the slot's stamp and leave
+//     the verdict to pass 2 (scratch[i] = slot index).
+// Only the last class -- the rows that really are duplicated inside the batch -- touches the
+// table a second time.
 __global__ void __launch_bounds__(OB2_BLOCK)
-set_dedup_pass2(SetHeader *hdr, const SetSlot *__restrict__ slots, int64_t n, const uint64_t *__restrict__ fp,
-                const uint32_t *__restrict__ order, uint32_t epoch, const uint32_t *__restrict__ scratch,
+set_dedup_pass1(SetHeader *hdr, SetSlot *slots, uint64_t mask, int64_t n, const uint64_t *__restrict__ fp,
+                const uint32_t *__restrict__ order, uint32_t epoch, uint32_t *__restrict__ scratch,
                 uint8_t *__restrict__ keep) {
     const int64_t i = (int64_t)blockIdx.x * OB2_BLOCK + threadIdx.x;
-    bool kept = false;
+    bool inserted = false;
     if (i < n) {
-        const uint64_t lo = __ldg(fp + 2 * i);
-        const uint32_t pos = scratch[i];
-        if (lo != 0 && pos != 0xFFFFFFFFu) {
-            const SetSlot *slot = slots + pos;
+        uint8_t verdict = 0;
+        uint32_t conflict = OB2_NO_CONFLICT;
+        const ulonglong2 key = __ldg(reinterpret_cast<const ulonglong2 *>(fp) + i);
+        if (key.x != 0) {  // lo == 0 is padding
+            uint64_t pos;
+            const int r = find_or_insert(slots, mask, key.x, key.y, pos);
+            SetSlot *slot = slots + pos;
             const uint32_t ord = order ? __ldg(order + i) : (uint32_t)i;
-            const unsigned long long mine = ((unsigned long long)epoch << 32) | (unsigned long long)(0xFFFFFFFFu - ord);
-            kept = (slot->born == epoch) && (slot->stamp == mine);
+            if (r == INSERTED) {
+                inserted = true;
+                slot->winner = (uint32_t)i;  // read by pass 2 only
+                slot->born = epoch;
+                atomicMax(&slot->stamp, dedup_tag(epoch, ord));
+                verdict = 1;
+            } else if (r == FOUND) {
+                uint32_t born;
+                asm volatile("ld.global.cg.u32 %0, [%1];" : "=r"(born) : "l"(&slot->born));
+                if (born == 0 || born == epoch) {
+                    atomicMax(&slot->stamp, dedup_tag(epoch, ord));
+                    conflict = (uint32_t)pos;
+                }
+            } else {
+                hdr->overflow = 1;
+            }
         }
-        keep[i] = kept ? 1 : 0;
+        keep[i] = verdict;
+        scratch[i] = conflict;
     }
-    warp_count_add(&hdr->count, kept);
+    warp_count_add(&hdr->count, inserted);
+}
+
+// Pass 2: only entries that met a key inserted by this same call.  The smallest order key
+// wins the slot; if that is not the entry that physically inserted the key, the inserter's
+// provisional keep = 1 is withdrawn (every loser writes the same 0, so the race is benign).
+__global__ void __launch_bounds__(OB2_BLOCK)
+set_dedup_pass2(const SetSlot *__restrict__ slots, int64_t n, const uint32_t *__restrict__ order, uint32_t epoch,
+                const uint32_t *__restrict__ scratch, uint8_t *__restrict__ keep) {
+    const int64_t i = (int64_t)blockIdx.x * OB2_BLOCK + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t pos = scratch[i];
+    if (pos == OB2_NO_CONFLICT) return;
+    const SetSlot *slot = slots + pos;
+    const unsigned long long stamp = slot->stamp;
+    const uint32_t ord = order ? __ldg(order + i) : (uint32_t)i;
+    if (stamp == dedup_tag(epoch, ord)) keep[i] = 1;
+    const uint32_t w = slot->winner;
+    const uint32_t ord_w = order ? __ldg(order + w) : w;
+    if (stamp != dedup_tag(epoch, ord_w)) keep[w] = 0;
 }
 
 __global__ void __launch_bounds__(OB2_BLOCK)
@@ -332,8 +367,8 @@ extern "C" int ob2_fingerprint(const ob2_space *space, int64_t n, int64_t n_stri
 }
 
 extern "C" int ob2_set_create(void *mem, uint64_t n_slots, void *stream, ob2_set **out) {
-    if (out == nullptr || mem == nullptr || n_slots < 64 || (n_slots & (n_slots - 1)) != 0 || n_slots > (1ull << 32)) {
-        ob2_set_error("ob2_set_create: n_slots must be a power of two in [64, 2^32] (got %llu)", (unsigned long long)n_slots);
+    if (out == nullptr || mem == nullptr || n_slots < 64 || (n_slots & (n_slots - 1)) != 0 || n_slots > (1ull << 31)) {
+        ob2_set_error("ob2_set_create: n_slots must be a power of two in [64, 2^31] (got %llu)", (unsigned long long)n_slots);
         return OB2_EINVAL;
     }
     if ((reinterpret_cast<uintptr_t>(mem) & 255) != 0) {
@@ -400,10 +435,10 @@ extern "C" int ob2_set_dedup(ob2_set *set, int64_t n, const uint64_t *fp, const 
         return OB2_ETOOBIG;
     }
     const uint32_t epoch = ++set->epoch;
-    set_dedup_pass1<<<blocks, OB2_BLOCK, 0, st>>>(set->header, set->slots, set->n_slots - 1, n, fp, order, epoch, scratch);
+    set_dedup_pass1<<<blocks, OB2_BLOCK, 0, st>>>(set->header, set->slots, set->n_slots - 1, n, fp, order, epoch, scratch, keep);
     rc = ob2_check_cuda(cudaGetLastError(), "set_dedup_pass1 launch");
     if (rc != OB2_OK) return rc;
-    set_dedup_pass2<<<blocks, OB2_BLOCK, 0, st>>>(set->header, set->slots, n, fp, order, epoch, scratch, keep);
+    set_dedup_pass2<<<blocks, OB2_BLOCK, 0, st>>>(set->slots, n, order, epoch, scratch, keep);
     return ob2_check_cuda(cudaGetLastError(), "set_dedup_pass2 launch");
 }
 
@@ -489,12 +524,12 @@ extern "C" int ob2_set_dedup_static(ob2_set *set, int64_t n, const uint64_t *fp,
     }
     const uint32_t epoch = ++set->epoch;
     // Nothing in the scratch has to start at zero: pass 1 writes entry i for
-    // every non-padding fingerprint, and pass 2 only uses entries of non-padding
-    // fingerprints, so whatever an earlier call left behind is never consumed.
-    set_dedup_pass1<<<blocks, OB2_BLOCK, 0, st>>>(set->header, set->slots, set->n_slots - 1, n, fp, order, epoch, scratch);
+    // every i < n (a slot index, or the "settled" marker) and pass 2 reads only
+    // those n entries, so whatever an earlier call left behind is never consumed.
+    set_dedup_pass1<<<blocks, OB2_BLOCK, 0, st>>>(set->header, set->slots, set->n_slots - 1, n, fp, order, epoch, scratch, keep);
     rc = ob2_check_cuda(cudaGetLastError(), "set_dedup_pass1 launch");
     if (rc != OB2_OK) return rc;
-    set_dedup_pass2<<<blocks, OB2_BLOCK, 0, st>>>(set->header, set->slots, n, fp, order, epoch, scratch, keep);
+    set_dedup_pass2<<<blocks, OB2_BLOCK, 0, st>>>(set->slots, n, order, epoch, scratch, keep);
     return ob2_check_cuda(cudaGetLastError(), "set_dedup_pass2 launch");
 }
 

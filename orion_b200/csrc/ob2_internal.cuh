@@ -138,14 +138,17 @@ __device__ __forceinline__ uint64_t canon_f64(double x) {
 struct FpAcc {
     uint64_t a, b;
 };
-// One 64x64 -> 128-bit product per slot: (word ^ key) * odd multiplier.  The
-// product is injective in the word, its high half feeds lane a and its low
-// half lane b; lanes are wrapping sums over slots, so any partition of the
-// slots over threads gives the same fingerprint.
+// Multilinear hash over the 32-bit halves of (word ^ key): each lane adds
+// lo32 * m + hi32 * m' with its own pair of odd 32-bit multipliers, i.e. two
+// 32x32 -> 64-bit multiply-accumulates per lane (IMAD.WIDE) instead of a full
+// 64x64 -> 128-bit product.  Lanes are wrapping sums over slots, so any partition
+// of the slots over threads gives the same fingerprint, and a contribution can
+// be subtracted again (the redraw path does).
 __device__ __forceinline__ void fp_add(FpAcc &acc, const ob2_slot_desc &d, uint64_t w) {
     const uint64_t x = w ^ d.hk[0];
-    acc.a += __umul64hi(x, d.hk[1]);
-    acc.b += x * d.hk[1];
+    const uint32_t xl = (uint32_t)x, xh = (uint32_t)(x >> 32);
+    acc.a += (uint64_t)xl * (uint32_t)d.hk[1] + (uint64_t)xh * (uint32_t)(d.hk[1] >> 32);
+    acc.b += (uint64_t)xl * (uint32_t)d.hk[2] + (uint64_t)xh * (uint32_t)(d.hk[2] >> 32);
 }
 __device__ __forceinline__ void fp_finish(const FpAcc &acc, int n_slots, uint64_t &lo, uint64_t &hi) {
     lo = fmix64(acc.a ^ ((uint64_t)n_slots * 0x9E3779B97F4A7C15ull));

@@ -20,55 +20,55 @@ __device__ __forceinline__ long long quantize_ll(double x, int t_flags) {
     return __double2ll_rz((t_flags & OB2_TFLAG_FLOOR) ? floor(x) : rint(x));
 }
 
-// ---- transformed-column emission for one slot, both candidates (fused transform)
-__device__ __forceinline__ void emit_real2(const ob2_slot_desc &d, char *tcols, int64_t n_stride, int64_t i0,
-                                           double x0, double x1) {
-    char *dst = tcols + (int64_t)d.t_units * n_stride;
-    if (d.t_op == OB2_OP_QUANTIZE)
-        st_i64x2(reinterpret_cast<long long *>(dst) + i0, quantize_ll(x0, d.t_flags), quantize_ll(x1, d.t_flags));
-    else
-        st_f64x2(reinterpret_cast<double *>(dst) + i0, x0, x1);
+// One-hot pair: 1.0 = 0x3FF00000'00000000, so only the high words are selected.
+__device__ __forceinline__ void st_onehot2(double *p, int c0, int c1, int j) {
+    const unsigned h0 = c0 == j ? 0x3FF00000u : 0u, h1 = c1 == j ? 0x3FF00000u : 0u;
+    asm volatile("st.global.cs.v4.u32 [%0], {%1, %2, %1, %3};" ::"l"(p), "r"(0u), "r"(h0), "r"(h1) : "memory");
 }
 
-// xf = the floored draw as a double (exactly (double)q)
-__device__ __forceinline__ void emit_int2(const ob2_slot_desc &d, char *tcols, int64_t n_stride, int64_t i0,
-                                          long long q0, long long q1, double xf0, double xf1) {
-    char *dst = tcols + (int64_t)d.t_units * n_stride;
-    if (d.t_op == OB2_OP_TO_REAL)
-        st_f64x2(reinterpret_cast<double *>(dst) + i0, xf0, xf1);
-    else
-        st_i64x2(reinterpret_cast<long long *>(dst) + i0, q0, q1);
-}
-
-__device__ __forceinline__ void emit_cat2(const ob2_slot_desc &d, char *tcols, int64_t n_stride, int64_t i0, int c0,
-                                          int c1) {
-    char *dst = tcols + (int64_t)d.t_units * n_stride;
-    if (d.t_op != OB2_OP_ONEHOT) {
-        st_i32x2(reinterpret_cast<int *>(dst) + i0, c0, c1);
-    } else if (d.t_width == 1) {
-        st_f64x2(reinterpret_cast<double *>(dst) + i0, (double)c0, (double)c1);
-    } else {
-        double *out = reinterpret_cast<double *>(dst) + i0;
-        for (int j = 0; j < d.t_width; ++j) {
-            st_f64x2(out, c0 == j ? 1.0 : 0.0, c1 == j ? 1.0 : 0.0);
-            out += n_stride;
-        }
-    }
+// Categorical draw = #{j : cdf[j] <= u}.  With equal probabilities floor(u * k)
+// is within one of the answer, so start there and walk to the exact index
+// (exact for ANY non-decreasing cdf; the guess only decides how far the walk is).
+// Otherwise the branch-free descent.
+__device__ __forceinline__ int draw_cat_fast(const double *cdf, int k, double u, bool uniform) {
+    if (!uniform) return draw_cat(cdf, k, u);
+    int idx = __double2int_rz(u * (double)k);
+    idx = min(max(idx, 0), k);
+    while (idx > 0 && cdf[idx - 1] > u) --idx;
+    while (idx < k && cdf[idx] <= u) ++idx;
+    return idx;
 }
 
 // Real.sample (space.py:263-270): a draw of dimension [first, s_last] landed
 // outside [low, high): redraw the whole (possibly shaped) value for candidate i,
-// attempts 1..3, overwriting its columns with scalar stores.  Rare path; inlined
-// in a cold branch of the walk so the hot loop carries no redraw state.
+// attempts 1..3, overwriting its columns with scalar stores.  Rare path, inlined
+// in a cold branch of the walk: the hot loop carries no redraw state at all --
+// the fingerprint lanes are wrapping sums, so the contribution of the rejected
+// values (read back from the columns this thread just wrote) is subtracted and
+// the redrawn one added.
 template <bool WITH_FP, bool WITH_T>
 __device__ __forceinline__ bool redraw_dim(const ob2_slot_desc *s_slots, int s_last, uint64_t index, int64_t i,
                                            int64_t n_stride, char *cols, char *tcols, uint32_t k0, uint32_t k1,
-                                           uint32_t pm0, uint32_t pm1, FpAcc &tmp) {
+                                           uint32_t pm0, uint32_t pm1, FpAcc &acc) {
     const int first = s_slots[s_last].dim_first;
+    if (WITH_FP) {
+        FpAcc old{0, 0};
+        for (int e = first; e <= s_last; ++e) {
+            const ob2_slot_desc &d = s_slots[e];
+            const char *col = cols + (int64_t)d.col_units * n_stride;
+            const uint64_t w = d.kind == OB2_KIND_INTEGER
+                                   ? (uint64_t) reinterpret_cast<const volatile long long *>(col)[i]
+                                   : canon_f64(reinterpret_cast<const volatile double *>(col)[i]);
+            fp_add(old, d, w);
+        }
+        acc.a -= old.a;
+        acc.b -= old.b;
+    }
     bool ok = false;
+    FpAcc t{0, 0};
     for (uint32_t a = 1; a < 4 && !ok; ++a) {
         ok = true;
-        FpAcc t{0, 0};
+        t = FpAcc{0, 0};
         for (int e = first; e <= s_last; ++e) {
             const ob2_slot_desc &d = s_slots[e];
             const Philox4 r = philox4x32_10((uint32_t)index, (uint32_t)(index >> 32), (uint32_t)(e >> 1), a, k0, k1, pm0, pm1);
@@ -101,14 +101,22 @@ __device__ __forceinline__ bool redraw_dim(const ob2_slot_desc *s_slots, int s_l
             ok &= (x >= d.low) && (x < d.high);
             if (WITH_FP) fp_add(t, d, w);
         }
-        tmp = t;
+    }
+    if (WITH_FP) {
+        acc.a += t.a;
+        acc.b += t.b;
     }
     return ok;
 }
 
 // pm0 / pm1 are the Philox multipliers, passed as kernel parameters so that the
-// multiplies read them straight from the constant bank (as literals the compiler
-// re-materialises them into uniform registers before every round).
+// multiplies read them straight from the constant bank.
+//
+// Hot-loop economy (the kernel is issue bound): column pointers are running
+// pointers advanced by 4*n_stride / 8*n_stride instead of being recomputed from
+// the descriptor; the fingerprint accumulates straight into its lanes; the
+// second candidate of a trailing odd pair replays the first (no `has1` tests
+// until the final stores).
 template <bool PHILOX, bool WITH_FP, bool WITH_T>
 __global__ void __launch_bounds__(OB2_BLOCK, 3)
 sample_kernel(const ob2_slot_desc *__restrict__ g_slots, int n_slots, const double *__restrict__ g_cdf,
@@ -129,11 +137,16 @@ sample_kernel(const ob2_slot_desc *__restrict__ g_slots, int n_slots, const doub
         idx0 = __ldg(index + i0);
         idx1 = has1 ? __ldg(index + i0 + 1) : idx0;
     }
+    if (!has1) idx1 = idx0;  // the padding candidate replays its neighbour: always well defined
 
-    FpAcc acc0{0, 0}, acc1{0, 0}, tmp0{0, 0}, tmp1{0, 0};
+    FpAcc acc0{0, 0}, acc1{0, 0};
     bool ok0 = true, ok1 = true;    // current dimension
     bool all0 = true, all1 = true;  // whole candidate
     Philox4 r0{0, 0, 0, 0}, r1{0, 0, 0, 0};
+    const int64_t stride4 = 4 * n_stride, stride8 = 8 * n_stride;
+    char *col = cols + i0 * 8;                          // running pointers: element i0 of the current column
+    char *tcol = WITH_T ? tcols + i0 * 8 : nullptr;     // (a 4-byte column is addressed at half the offset)
+    const double *ucol = PHILOX ? nullptr : U + i0;
 
     for (int s = 0; s < n_slots; ++s) {
         const ob2_slot_desc &d = s_slots[s];
@@ -149,20 +162,40 @@ sample_kernel(const ob2_slot_desc *__restrict__ g_slots, int n_slots, const doub
                 u1 = u53(r1.z, r1.w);
             }
         } else {
-            ld_f64x2(U + (int64_t)s * n_stride + i0, u0, u1);
+            ld_f64x2(ucol, u0, u1);
+            ucol += n_stride;
         }
-        char *col = cols + (int64_t)d.col_units * n_stride;
         uint64_t w0, w1;
         if (d.kind == OB2_KIND_CATEGORICAL) {
             const double *cdf = s_cdf + d.cdf_off;
-            const int c0 = draw_cat(cdf, d.n_cats, u0);
-            const int c1 = draw_cat(cdf, d.n_cats, u1);
-            st_i32x2(reinterpret_cast<int *>(col) + i0, c0, c1);
-            if (WITH_T) emit_cat2(d, tcols, n_stride, i0, c0, c1);
+            const bool uni = (d.flags & OB2_SLOT_CAT_UNIFORM) != 0;
+            const int c0 = draw_cat_fast(cdf, d.n_cats, u0, uni);
+            const int c1 = draw_cat_fast(cdf, d.n_cats, u1, uni);
+            st_i32x2(reinterpret_cast<int *>(col - i0 * 4), c0, c1);
+            col += stride4;
+            if (WITH_T) {
+                if (d.t_op != OB2_OP_ONEHOT) {
+                    st_i32x2(reinterpret_cast<int *>(tcol - i0 * 4), c0, c1);
+                    tcol += stride4;
+                } else if (d.t_width == 1) {
+                    st_f64x2(reinterpret_cast<double *>(tcol), (double)c0, (double)c1);
+                    tcol += stride8;
+                } else {
+                    // column j is at tcol + j * stride8; the launcher guarantees stride8 < 2^32,
+                    // so each address is ONE 32x32+64 multiply-add (IMAD.WIDE.U32)
+                    const uint32_t s8 = (uint32_t)stride8, k = (uint32_t)d.t_width;
+#pragma unroll 4
+                    for (uint32_t j = 0; j < k; ++j)
+                        st_onehot2(reinterpret_cast<double *>(tcol + (uint64_t)j * s8), c0, c1, (int)j);
+                    tcol += (uint64_t)k * s8;
+                }
+            }
             w0 = (uint64_t)(int64_t)c0;
             w1 = (uint64_t)(int64_t)c1;
-            ok0 &= c0 < d.n_cats;
-            ok1 &= c1 < d.n_cats;
+            if (!PHILOX) {  // an injected u >= 1 can run off the table; a Philox u cannot
+                ok0 &= c0 < d.n_cats;
+                ok1 &= c1 < d.n_cats;
+            }
         } else {
             double x0 = draw_real(d, u0);
             double x1 = draw_real(d, u1);
@@ -170,45 +203,52 @@ sample_kernel(const ob2_slot_desc *__restrict__ g_slots, int n_slots, const doub
                 x0 = floor(x0);  // _Discrete.sample, space.py:294
                 x1 = floor(x1);
                 const long long q0 = __double2ll_rz(x0), q1 = __double2ll_rz(x1);
-                st_i64x2(reinterpret_cast<long long *>(col) + i0, q0, q1);
-                if (WITH_T) emit_int2(d, tcols, n_stride, i0, q0, q1, x0, x1);
+                st_i64x2(reinterpret_cast<long long *>(col), q0, q1);
+                if (WITH_T) {
+                    if (d.t_op == OB2_OP_TO_REAL)  // the floored double is exactly (double)q
+                        st_f64x2(reinterpret_cast<double *>(tcol), x0, x1);
+                    else
+                        st_i64x2(reinterpret_cast<long long *>(tcol), q0, q1);
+                    tcol += stride8;
+                }
                 w0 = (uint64_t)q0;
                 w1 = (uint64_t)q1;
             } else {
-                st_f64x2(reinterpret_cast<double *>(col) + i0, x0, x1);
-                if (WITH_T) emit_real2(d, tcols, n_stride, i0, x0, x1);
+                st_f64x2(reinterpret_cast<double *>(col), x0, x1);
+                if (WITH_T) {
+                    if (d.t_op == OB2_OP_QUANTIZE)
+                        st_i64x2(reinterpret_cast<long long *>(tcol), quantize_ll(x0, d.t_flags), quantize_ll(x1, d.t_flags));
+                    else
+                        st_f64x2(reinterpret_cast<double *>(tcol), x0, x1);
+                    tcol += stride8;
+                }
                 w0 = canon_f64(x0);
                 w1 = canon_f64(x1);
             }
-            ok0 &= (x0 >= d.low) && (x0 < d.high);  // half-open, space.py:164
-            ok1 &= (x1 >= d.low) && (x1 < d.high);
+            col += stride8;
+            ok0 &= (x0 >= d.low) & (x0 < d.high);  // half-open, space.py:164
+            ok1 &= (x1 >= d.low) & (x1 < d.high);
         }
         if (WITH_FP) {
-            fp_add(tmp0, d, w0);
-            fp_add(tmp1, d, w1);
+            fp_add(acc0, d, w0);
+            fp_add(acc1, d, w1);
         }
         if (d.flags & OB2_SLOT_DIM_LAST) {
-            if (PHILOX && d.kind != OB2_KIND_CATEGORICAL && !(ok0 && (ok1 || !has1))) {  // cold
-                if (!ok0)
-                    ok0 = redraw_dim<WITH_FP, WITH_T>(s_slots, s, idx0, i0, n_stride, cols, tcols, k0, k1, pm0, pm1, tmp0);
-                if (!ok1 && has1)
-                    ok1 = redraw_dim<WITH_FP, WITH_T>(s_slots, s, idx1, i0 + 1, n_stride, cols, tcols, k0, k1, pm0, pm1, tmp1);
-                if (n_failed != nullptr) {  // 4 misses: the reference raises "Improbable bounds"
-                    const unsigned bad = (ok0 ? 0u : 1u) + ((ok1 || !has1) ? 0u : 1u);
-                    if (bad) atomicAdd(n_failed + d.dim_first, bad);
+            if (!(ok0 & ok1)) {  // cold: only Real/Integer slots can clear ok
+                if (PHILOX) {
+                    if (!ok0)
+                        ok0 = redraw_dim<WITH_FP, WITH_T>(s_slots, s, idx0, i0, n_stride, cols, tcols, k0, k1, pm0, pm1, acc0);
+                    if (!ok1)
+                        ok1 = redraw_dim<WITH_FP, WITH_T>(s_slots, s, idx1, i0 + 1, n_stride, cols, tcols, k0, k1, pm0, pm1, acc1);
+                    if (n_failed != nullptr) {  // 4 misses: the reference raises "Improbable bounds"
+                        const unsigned bad = (ok0 ? 0u : 1u) + ((ok1 || !has1) ? 0u : 1u);
+                        if (bad) atomicAdd(n_failed + d.dim_first, bad);
+                    }
                 }
+                all0 &= ok0;
+                all1 &= ok1;
+                ok0 = ok1 = true;
             }
-            all0 &= ok0;
-            all1 &= ok1;
-            if (WITH_FP) {
-                acc0.a += tmp0.a;
-                acc0.b += tmp0.b;
-                acc1.a += tmp1.a;
-                acc1.b += tmp1.b;
-                tmp0 = FpAcc{0, 0};
-                tmp1 = FpAcc{0, 0};
-            }
-            ok0 = ok1 = true;
         }
     }
     if (mask != nullptr) {
@@ -311,6 +351,11 @@ int launch_sample(const SampleArgs &a) {
         return OB2_EINVAL;
     }
     if (a.n == 0) return OB2_OK;
+    if (a.n_stride >= (1ll << 29)) {  // the kernel steps through columns with 32-bit byte strides
+        ob2_set_error("sample: n_stride %lld too large for one launch (limit 2^29 - 1); split the batch",
+                      (long long)a.n_stride);
+        return OB2_ETOOBIG;
+    }
     const int64_t threads = (a.n + OB2_CPT - 1) / OB2_CPT;
     const int64_t blocks = (threads + OB2_BLOCK - 1) / OB2_BLOCK;
     if (blocks > 0x7FFFFFFFll) {

@@ -44,14 +44,11 @@ def _splitmix64(x):
 
 
 def _hash_keys(slot):
-    """Per-slot fingerprint constants (xor key, odd multiplier) x 2 lanes."""
-    out = []
-    for j in range(4):
-        v = _splitmix64((4 * slot + j + 1) * 0xD6E8FEB86659FD93 & _M64)
-        if j & 1:
-            v |= 1
-        out.append(v)
-    return out
+    """Per-slot fingerprint constants: [xor key, lane-a multipliers, lane-b
+    multipliers, 0]; a multiplier word packs two odd 32-bit multipliers (for
+    the low and the high half of the value)."""
+    k = [_splitmix64((4 * slot + j + 1) * 0xD6E8FEB86659FD93 & _M64) for j in range(3)]
+    return [k[0], k[1] | 0x0000000100000001, k[2] | 0x0000000100000001, 0]
 
 
 def round_up(n, m=32):
@@ -153,6 +150,8 @@ class CompiledSpace(object):
                 sd.kind, sd.dist = _KIND[kind], dist
                 sd.dim_first = first
                 sd.flags = _lib.SLOT_DIM_LAST if e == k - 1 else 0
+                if kind == 'categorical' and len(set(dim._probs)) == 1:
+                    sd.flags |= _lib.SLOT_CAT_UNIFORM
                 sd.n_cats, sd.cdf_off = n_cats, cdf_off
                 sd.col_units, sd.t_units = col_units, t_units
                 sd.t_op = op

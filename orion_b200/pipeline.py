@@ -47,9 +47,13 @@ class CandidatePipeline(object):
         self.sharded = history if isinstance(history, ShardedHistory) else ShardedHistory(history, device=compiled.device)
         self.slots = [BatchSlot(compiled, n) for _ in range(depth)]
         dev = compiled.device
-        self.s_sample = torch.cuda.Stream(device=dev)
-        self.s_reverse = torch.cuda.Stream(device=dev)
-        self.s_dedup = torch.cuda.Stream(device=dev)
+        # The dedup kernels are latency bound (random 32-byte probes) and tiny next to the
+        # streaming ones; at equal priority their blocks queue behind the ~24k blocks of
+        # sample / reverse and the three groups run back to back.  With the higher priority
+        # they are dispatched as soon as SM slots free up and really co-reside.
+        self.s_sample = torch.cuda.Stream(device=dev, priority=0)
+        self.s_reverse = torch.cuda.Stream(device=dev, priority=0)
+        self.s_dedup = torch.cuda.Stream(device=dev, priority=-1)
         self.k = 0
         self.timed = timed
         self.timings = []          # per step: (sample_ms_events, reverse_events, dedup_events) when timed
