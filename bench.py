@@ -151,7 +151,7 @@ def run_reference(args):
         "cpu_baseline": {"value": rate, "unit": UNIT, "cores": procs, "kind": "port", "sample": sample},
         "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
-    print(json.dumps(line))
+    emit(line)
 
 
 def workload_config(args, world):
@@ -577,13 +577,32 @@ def run_b200(args):
         line["cpu_baseline"] = {"value": rate, "unit": UNIT, "cores": procs, "kind": "port",
                                 "sample": "%d candidates (%d per process x %d processes, %.1f s) of the same workload "
                                           "through the numpy oracle" % (total_n, n_per_proc, procs, secs)}
-    print(json.dumps(line))
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
+_REAL_STDOUT = None
+
+
+def emit(line):
+    """The ONE JSON line, on the process's real stdout."""
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 def main():
+    global _REAL_STDOUT
     args = parse_args()
+    # Libraries chat on stdout (NCCL prints its version banner there): park fd 1 on stderr for
+    # the duration of the run so that stdout carries exactly the JSON line.
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     if args.impl == 'reference':
         run_reference(args)
     else:

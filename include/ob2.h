@@ -146,7 +146,7 @@ int ob2_reverse(const ob2_space *space, int64_t n, int64_t n_stride, const void 
 int ob2_fingerprint(const ob2_space *space, int64_t n, int64_t n_stride, const void *cols,
                     uint64_t *fp, void *stream);
 
-/* History hash set over caller-owned memory: n_slots (power of two) slots of
+/* History hash set over caller-owned memory: n_slots (power of two, <= 2^31) slots of
  * OB2_SET_SLOT_BYTES, preceded by an OB2_SET_HEADER_BYTES header.  create
  * zeroes the memory on `stream`. */
 #define OB2_SET_SLOT_BYTES 32
