@@ -190,6 +190,19 @@ int ob2_set_probe(const ob2_set *set, int64_t n, const uint64_t *fp, uint8_t *fo
 /* number of distinct fingerprints stored; synchronises `stream` */
 int ob2_set_count(const ob2_set *set, uint64_t *count, void *stream);
 
+/* Order-preserving gather of the rows with keep[i] != 0 into a dense column
+ * block of the same layout with stride out_stride; *n_kept (device u64)
+ * receives their number.  The device half of Producer.produce's
+ * suggest -> tuple_to_trial -> register_trials hand-over
+ * (src/orion/core/worker/producer.py:45-51, src/orion/core/utils/format_trials.py:28-42):
+ * only surviving candidates are copied to the host and turned into trials.
+ * `transformed` != 0 compacts a transformed column set.  `scratch` is
+ * ob2_compact_scratch_bytes(n) bytes of caller scratch. */
+int64_t ob2_compact_scratch_bytes(int64_t n);
+int ob2_compact(const ob2_space *space, int64_t n, int64_t n_stride, const void *cols,
+                const uint8_t *keep, int32_t transformed, int64_t out_stride, void *out_cols,
+                void *scratch, uint64_t *n_kept, void *stream);
+
 /* Multi-GPU exchange helpers: owner rank of a fingerprint is
  * fp.hi % n_ranks.  bucket writes (fp, global order key) into
  * out_fp[n_ranks][cap][2] / out_key[n_ranks][cap], zero-pads each bucket's

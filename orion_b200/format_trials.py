@@ -1,0 +1,59 @@
+"""Points <-> trial records, batch-first.
+
+Mirror of ``src/orion/core/utils/format_trials.py:16-55`` (``trial_to_tuple``,
+``tuple_to_trial``) for the step right after the hot path:
+``Producer.produce`` maps every suggested point to a ``Trial`` and registers it
+(``src/orion/core/worker/producer.py:47-51``), one Python object per parameter.
+Here the deduplicated survivors are gathered on the device (``ob2_compact``),
+copied to the host once, and expanded into the same ``params`` records --
+``{'name', 'type', 'value'}`` per dimension, the shape ``Trial.to_dict()``
+stores (``src/orion/core/worker/trial.py:136-141, 170-191``).
+
+The reference's ``Trial`` class belongs to its storage layer (out of scope
+here); a trial is represented by the plain dict that class serialises to.
+"""
+import numpy
+
+
+def tuple_to_trial(data, space):
+    """One point (tuple in space order) -> trial record with only ``params`` filled."""
+    assert len(data) == len(space)
+    dims = list(space.values())
+    return {'params': [dict(name=dims[j].name, type=dims[j].type, value=data[j]) for j in range(len(dims))]}
+
+
+def trial_to_tuple(trial, space):
+    """Trial record -> point; parameter order must be the space's."""
+    params = trial['params']
+    assert len(params) == len(space)
+    for j, param in enumerate(params):
+        assert space[j].name == param['name']
+    return tuple(param['value'] for param in params)
+
+
+def batch_to_trials(space, batch, keep=None):
+    """Surviving rows of a device ColumnBatch -> list of trial records.
+
+    ``keep`` defaults to ``batch.keep`` when the batch went through dedup, and
+    to every row otherwise.  Survivors are compacted on the device and cross
+    PCIe once.
+    """
+    keep = batch.keep if keep is None else keep
+    dense = batch.compact(keep) if keep is not None else batch
+    rows = space.rows_from_columns(dense.to_numpy(), dense.n)
+    return [tuple_to_trial(row, space) for row in rows]
+
+
+def trials_to_batch(space, trials):
+    """Completed trials -> device ColumnBatch (history ingestion:
+    ``Producer.update`` -> ``trial_to_tuple`` -> ``observe``,
+    ``src/orion/core/worker/producer.py:54-67``)."""
+    from .columns import ColumnBatch
+    points = [trial_to_tuple(t, space) for t in trials]
+    cols, row_ok = space.columns_from_rows(points)
+    if not row_ok.all():
+        raise ValueError("a trial does not match the shape of the space")
+    compiled = space.compiled()
+    typed = [numpy.asarray(c, dtype={'f8': numpy.float64, 'i8': numpy.int64, 'i4': numpy.int32}[dt])
+             for c, (_u, dt) in zip(cols, compiled.col_meta)]
+    return ColumnBatch.from_numpy(compiled, typed)

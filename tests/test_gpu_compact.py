@@ -1,0 +1,63 @@
+"""ob2_compact (survivor gather) and the trial-record encoder built on it
+(src/orion/core/utils/format_trials.py:16-42 applied to whole batches)."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize('n', [1, 2, 511, 512, 513, 100_003])
+@pytest.mark.parametrize('transformed', [False, True])
+def test_compact_matches_boolean_indexing(n, transformed):
+    from orion_b200 import spaces
+    from orion_b200.transformer import build_required_space
+    space = spaces.mixed64()
+    compiled = build_required_space('real', space).compiled()
+    tb = compiled.empty_columns(n, transformed=True)
+    batch = compiled.sample(n, 9, transformed_out=tb)
+    src = tb if transformed else batch
+    rng = np.random.RandomState(n)
+    for frac in (0.0, 0.5, 0.89, 1.0):
+        keep_host = (rng.random_sample(n) < frac).astype(np.uint8)
+        keep = torch.from_numpy(keep_host).cuda()
+        dense = src.compact(keep)
+        assert dense.n == int(keep_host.sum())
+        for got, want in zip(dense.to_numpy(), src.to_numpy()):
+            assert got.dtype == want.dtype and np.array_equal(got, want[keep_host.astype(bool)])
+
+
+def test_batch_to_trials_round_trip():
+    from collections import OrderedDict
+    from orion_b200 import format_trials
+    from orion_b200.history import TrialHistory
+    from orion_b200.space import Categorical, Integer, Real, Space
+    space = Space()
+    space.register(Categorical('yolo', OrderedDict(zip(('asdfa', 2, 3, 4), (0.1, 0.2, 0.3, 0.4))), shape=2))
+    space.register(Integer('yolo2', 'uniform', -3, 6))
+    space.register(Real('yolo3', 'norm', 0.9))
+    # tuple_to_trial / trial_to_tuple: tests/unittests/core/test_utils_format.py
+    point = (np.array(['asdfa', 2], dtype=object), 0, 3.5)
+    trial = format_trials.tuple_to_trial(point, space)
+    assert [p['name'] for p in trial['params']] == ['yolo', 'yolo2', 'yolo3']
+    assert [p['type'] for p in trial['params']] == ['categorical', 'integer', 'real']
+    assert format_trials.trial_to_tuple(trial, space)[1:] == (0, 3.5)
+    with pytest.raises(AssertionError):
+        format_trials.tuple_to_trial(point[:2], space)
+    # batch path: dedup -> compact -> one host copy -> records
+    hist = TrialHistory(space, capacity=4096)
+    counters = torch.from_numpy(np.random.RandomState(0).randint(0, 300, size=500).astype(np.int64)).cuda()
+    batch = space.compiled().sample(500, 3, index=counters, with_fingerprint=True)    # repeated counters = repeated rows
+    hist.dedup(batch)
+    trials = format_trials.batch_to_trials(space, batch)
+    kept = int(batch.keep[:500].sum().item())
+    assert len(trials) == kept == len(np.unique(counters.cpu().numpy()))
+    rows = space.rows_from_columns(batch.to_numpy(), 500)
+    keep = batch.keep[:500].cpu().numpy().astype(bool)
+    want = [r for r, k in zip(rows, keep) if k]
+    for t, w in zip(trials, want):
+        got = format_trials.trial_to_tuple(t, space)
+        assert np.all(got[0] == w[0]) and got[1:] == w[1:]
+    # history ingestion of stored trials: they are all known now
+    again = format_trials.trials_to_batch(space, trials)
+    assert not bool(hist.dedup(again).any().item())
