@@ -118,7 +118,7 @@ __device__ __forceinline__ bool redraw_dim(const ob2_slot_desc *s_slots, int s_l
 // second candidate of a trailing odd pair replays the first (no `has1` tests
 // until the final stores).
 template <bool PHILOX, bool WITH_FP, bool WITH_T>
-__global__ void __launch_bounds__(OB2_BLOCK, 3)
+__global__ void __launch_bounds__(OB2_BLOCK, 4)
 sample_kernel(const ob2_slot_desc *__restrict__ g_slots, int n_slots, const double *__restrict__ g_cdf,
               int cdf_len, int64_t n, int64_t n_stride, uint32_t k0, uint32_t k1, uint32_t pm0, uint32_t pm1,
               uint64_t base_index, const uint64_t *__restrict__ index, const double *__restrict__ U,
