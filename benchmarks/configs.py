@@ -1,0 +1,72 @@
+#!/usr/bin/env python
+"""Side measurements for the BASELINE.json configs that are not the bench line
+(config 1: small-n latency through the list-of-tuples API; config 2: real16
+sampling; config 4: cat32x100 one-hot transform + reverse, chunked).  Prints one
+JSON object; numbers go to DESIGN.md, not to the driver."""
+import json
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+from orion_b200 import spaces  # noqa: E402
+from orion_b200.primary_algo import PrimaryAlgo  # noqa: E402
+from orion_b200.transformer import build_required_space  # noqa: E402
+
+
+def timed(fn, reps, warm=3):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / reps
+
+
+def main():
+    out = {}
+    # config 1: random search on 2-dim Rosenbrock, suggest(10) x 100, in process
+    algo = PrimaryAlgo(spaces.rosen2(), {'random': {'seed': 1}})
+    algo.suggest(10)
+    t0 = time.perf_counter()
+    best = float('inf')
+    for _ in range(100):
+        pts = algo.suggest(10)
+        best = min(best, min((1 - x) ** 2 + 100 * (y - x ** 2) ** 2 for x, y in pts))
+    dt = time.perf_counter() - t0
+    out['config1_rosen2_suggest10_x100'] = {'seconds': dt, 'candidates_per_s': 1000 / dt, 'best_objective': best,
+                                            'note': 'list-of-tuples API: launch + D2H + Python tuples per call'}
+    # config 2: Space.sample 1M points, real16
+    c = spaces.real16().compiled()
+    for n in (1_000_000, 100_000_000):
+        b = c.empty_columns(n)
+        ms = timed(lambda: c.sample(n, 20240002, with_mask=True, out=b), 20 if n < 10 ** 7 else 5)
+        out['config2_real16_n%d' % n] = {'ms': ms, 'candidates_per_s': n / ms * 1e3, 'GBps_written': 128 * n / ms / 1e6}
+        del b
+    # config 4: cat32x100 transform + reverse, 10 chunks of 1M
+    c = build_required_space('real', spaces.cat32x100()).compiled()
+    n = 1_000_000
+    b = c.sample(n, 20240004)
+    tb = c.empty_columns(n, transformed=True)
+    back = c.empty_columns(n)
+    t_ms = timed(lambda: c.transform(b, out=tb), 10)
+    r_ms = timed(lambda: c.reverse(tb, out=back), 10)
+    f_ms = timed(lambda: c.sample(n, 20240004, out=b, transformed_out=tb), 10)
+    out['config4_cat32x100_per_1M_chunk'] = {
+        'transform_ms': t_ms, 'reverse_ms': r_ms, 'fused_sample_transform_ms': f_ms,
+        'points_per_s_transform_plus_reverse': n / (t_ms + r_ms) * 1e3,
+        'transform_GBps': (128 + 25600) * n / t_ms / 1e6, 'reverse_GBps': (25600 + 128) * n / r_ms / 1e6,
+        'round_trip_ok': bool(torch.equal(back.buf, b.buf))}
+    print(json.dumps(out, indent=1))
+
+
+if __name__ == '__main__':
+    main()
