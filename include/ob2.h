@@ -40,7 +40,12 @@ enum { OB2_KIND_REAL = 0, OB2_KIND_INTEGER = 1, OB2_KIND_CATEGORICAL = 2 };
  * src/orion/core/io/space_builder.py:124-154).  CONST = scale == 0 (rvs returns loc).
  * NONE = any other scipy prior: the space can be checked, transformed, hashed
  * and deduplicated (only its bounds matter), but ob2_sample* refuse it. */
-enum { OB2_DIST_UNIFORM = 0, OB2_DIST_RECIPROCAL = 1, OB2_DIST_NORM = 2, OB2_DIST_CONST = 3, OB2_DIST_NONE = 4 };
+enum { OB2_DIST_UNIFORM = 0, OB2_DIST_RECIPROCAL = 1, OB2_DIST_NORM = 2, OB2_DIST_CONST = 3, OB2_DIST_NONE = 4,
+       /* further scipy priors with a closed-form _ppf (any name DimensionBuilder._build accepts,
+        * space_builder.py:156-186); p0 / p1 carry the shape parameter and its reciprocal */
+       OB2_DIST_EXPON = 5, OB2_DIST_LOGNORM = 6, OB2_DIST_LOGISTIC = 7, OB2_DIST_LAPLACE = 8, OB2_DIST_GUMBEL_R = 9,
+       OB2_DIST_WEIBULL_MIN = 10, OB2_DIST_PARETO = 11, OB2_DIST_RAYLEIGH = 12, OB2_DIST_HALFNORM = 13,
+       OB2_DIST_POWERLAW = 14, OB2_DIST_LAST = 14 };
 
 /* per-slot transformer (build_required_space table) */
 enum {

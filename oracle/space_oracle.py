@@ -178,6 +178,10 @@ def slot_table(specs: Sequence[DimSpec]) -> List[Tuple[int, int]]:
     return out
 
 
+CLOSED_FORM_PRIORS = ('expon', 'lognorm', 'logistic', 'laplace', 'gumbel_r', 'weibull_min', 'pareto',
+                      'rayleigh', 'halfnorm', 'powerlaw')
+
+
 def _draw(spec: DimSpec, u: np.ndarray) -> np.ndarray:
     """Inverse-CDF draw of one scalar slot from uniforms (Appendix A.1/A.2)."""
     if spec.kind == 'categorical':
@@ -195,6 +199,9 @@ def _draw(spec: DimSpec, u: np.ndarray) -> np.ndarray:
             base = np.exp(np.log(a) + u * (np.log(b) - np.log(a)))
         elif name == 'norm':
             base = _sc.ndtri(u)
+        elif name in CLOSED_FORM_PRIORS:
+            # scipy's own inverse CDF of the standardised distribution
+            base = dist._ppf(u, *[np.float64(a) for a in args])
         else:
             raise NotImplementedError(name)
         x = base * scale + loc          # rounded mul, then rounded add

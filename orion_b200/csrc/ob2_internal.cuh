@@ -99,6 +99,37 @@ __device__ __forceinline__ double draw_real(const ob2_slot_desc &d, double u) {
         case OB2_DIST_NORM:
             b = normcdfinv(u);
             break;
+        // closed-form inverse CDFs of further scipy priors (scipy's own _ppf formulas)
+        case OB2_DIST_EXPON:
+            b = -log1p(-u);
+            break;
+        case OB2_DIST_LOGNORM:  // p0 = s
+            b = exp(__dmul_rn(d.p0, normcdfinv(u)));
+            break;
+        case OB2_DIST_LOGISTIC:
+            b = log(u / (1.0 - u));
+            break;
+        case OB2_DIST_LAPLACE:
+            b = u > 0.5 ? -log(2.0 * (1.0 - u)) : log(2.0 * u);
+            break;
+        case OB2_DIST_GUMBEL_R:
+            b = -log(-log(u));
+            break;
+        case OB2_DIST_WEIBULL_MIN:  // p0 = c, p1 = 1 / c
+            b = pow(-log1p(-u), d.p1);
+            break;
+        case OB2_DIST_PARETO:  // p0 = b, p1 = -1 / b
+            b = pow(1.0 - u, d.p1);
+            break;
+        case OB2_DIST_RAYLEIGH:
+            b = sqrt(-2.0 * log1p(-u));
+            break;
+        case OB2_DIST_HALFNORM:
+            b = normcdfinv(0.5 * (1.0 + u));
+            break;
+        case OB2_DIST_POWERLAW:  // p0 = a, p1 = 1 / a
+            b = pow(u, d.p1);
+            break;
         default:
             return d.loc;  // scale == 0
     }

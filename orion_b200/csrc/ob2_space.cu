@@ -46,7 +46,7 @@ extern "C" int ob2_space_create(const ob2_slot_desc *slots, int32_t n_slots, con
             ob2_set_error("slot %d: unknown kind %d", s, d.kind);
             return OB2_EINVAL;
         }
-        if (d.kind != OB2_KIND_CATEGORICAL && (d.dist < OB2_DIST_UNIFORM || d.dist > OB2_DIST_NONE)) {
+        if (d.kind != OB2_KIND_CATEGORICAL && (d.dist < OB2_DIST_UNIFORM || d.dist > OB2_DIST_LAST)) {
             ob2_set_error("slot %d: prior %d has no device inverse CDF", s, d.dist);
             return OB2_EINVAL;
         }

@@ -55,6 +55,15 @@ def round_up(n, m=32):
     return (int(n) + m - 1) // m * m
 
 
+# scipy priors with a closed-form inverse CDF on the device:
+# name -> (dist code, number of shape parameters, sign of the reciprocal stored in p1 or 0)
+_CLOSED_FORM = {
+    'expon': (5, 0, 0), 'lognorm': (6, 1, 0), 'logistic': (7, 0, 0), 'laplace': (8, 0, 0), 'gumbel_r': (9, 0, 0),
+    'weibull_min': (10, 1, 1.0), 'pareto': (11, 1, -1.0), 'rayleigh': (12, 0, 0), 'halfnorm': (13, 0, 0),
+    'powerlaw': (14, 1, 1.0),
+}
+
+
 def _prior_params(dim):
     """(dist code, p0, p1, loc, scale) of a Real/Integer dimension."""
     name = dim._prior_name
@@ -75,6 +84,13 @@ def _prior_params(dim):
         return _lib.DIST_RECIPROCAL, float(la), float(np.log(b) - la), loc, scale
     if name == 'norm':
         return _lib.DIST_NORM, 0.0, 0.0, loc, scale
+    if name in _CLOSED_FORM:
+        code, n_shape, reciprocal_sign = _CLOSED_FORM[name]
+        if len(args) != n_shape:
+            raise TypeError("Parameter '{}': prior '{}' takes {} shape parameter(s)".format(dim.name, name, n_shape))
+        p0 = float(args[0]) if n_shape else 0.0
+        p1 = reciprocal_sign / p0 if (n_shape and reciprocal_sign) else 0.0
+        return code, p0, p1, loc, scale
     # any other scipy prior: bounds-only (contains / transform / dedup work, sampling refuses)
     return _lib.DIST_NONE, 0.0, 0.0, loc, scale
 

@@ -1,0 +1,78 @@
+"""Further scipy priors with a closed-form inverse CDF on the device
+(anything `DimensionBuilder._build` accepts,
+reference space_builder.py:156-186).  Parity: the device draw from an injected
+uniform equals scipy's own ppf within 1e-6 relative; Philox-mode marginals pass
+a KS test against scipy's distribution; Integer variants floor exactly."""
+import numpy as np
+import pytest
+import torch
+from scipy import stats
+
+from oracle import space_oracle as so
+from tests import golden_util as gu
+
+pytestmark = pytest.mark.gpu
+
+PRIORS = [
+    ('expon', []), ('expon', [2.0, 3.0]), ('lognorm', [0.5]), ('lognorm', [1.25, 1.0, 2.0]),
+    ('logistic', []), ('logistic', [1.0, 0.5]), ('laplace', []), ('gumbel_r', [0.5, 2.0]),
+    ('weibull_min', [1.5]), ('weibull_min', [0.7, 1.0, 3.0]), ('pareto', [2.5]), ('rayleigh', []),
+    ('rayleigh', [0.0, 4.0]), ('halfnorm', []), ('powerlaw', [3.0]), ('powerlaw', [0.5, -1.0, 2.0]),
+]
+
+
+def _space(kind='real'):
+    dims = [dict(name='d%d' % j, kind=kind, prior=p, args=a) for j, (p, a) in enumerate(PRIORS)]
+    return dims, gu.specs_from_json(dims), gu.product_space(dims)
+
+
+def test_from_uniform_matches_scipy_ppf():
+    dims, specs, space = _space()
+    rng = np.random.RandomState(0)
+    n = 4096
+    U = rng.random_sample((len(dims), n))
+    U[:, :4] = [1e-300, 2.0 ** -53, 0.5, 1 - 2.0 ** -53]
+    batch = space.compiled().sample_from_uniform(torch.from_numpy(U).cuda())
+    got = batch.to_numpy()
+    want, ok = so.sample_from_uniform(specs, U)
+    for j, (g, w) in enumerate(zip(got, want)):
+        np.testing.assert_allclose(g, w, rtol=1e-6, atol=1e-13, err_msg='%s%r' % PRIORS[j])
+        direct = getattr(stats, PRIORS[j][0]).ppf(U[j], *PRIORS[j][1])
+        np.testing.assert_allclose(g, direct, rtol=1e-6, atol=1e-13, err_msg='%s%r' % PRIORS[j])
+    assert np.array_equal(batch.mask.cpu().numpy().astype(bool), ok)
+
+
+def test_philox_marginals_pass_ks():
+    dims, specs, space = _space()
+    n = 400_000
+    cols = space.compiled().sample(n, 31337).to_numpy()
+    for j, x in enumerate(cols):
+        dist = getattr(stats, PRIORS[j][0])(*PRIORS[j][1])
+        p = stats.kstest(x, dist.cdf).pvalue
+        assert p > 1e-3 / len(cols), '%s%r: p = %g' % (PRIORS[j] + (p,))
+
+
+def test_integer_variants_and_bounds():
+    """discrete=True over these priors: floor of the continuous draw, checked
+    against the floored interval (reference space.py:281-319)."""
+    dims, specs, space = _space('integer')
+    n = 50_000
+    batch = space.compiled().sample(n, 5)
+    got = batch.to_numpy()
+    want, failed = so.sample_philox(specs, n, 5)
+    flips = 0
+    for j, (g, w) in enumerate(zip(got, want)):
+        assert g.dtype == np.int64
+        flips += int((g != w).sum())        # floor can flip only when the draw is within ulps of an integer
+    assert flips <= 2
+    assert bool(batch.mask[:n].all().item()) and not failed.any()
+    assert np.array_equal(so.contains(specs, got), np.ones(n, dtype=bool))
+
+
+def test_unsupported_prior_still_refuses():
+    from orion_b200.space import Real, Space
+    space = Space()
+    space.register(Real('a', 'alpha', 0.9))
+    assert (3.5,) in space
+    with pytest.raises(NotImplementedError):
+        space.sample(1)
