@@ -54,6 +54,8 @@ def parse_args():
     ap.add_argument('--e2e-steps', type=int, default=2)
     ap.add_argument('--unfused', action='store_true', help='sample and transform as two kernels')
     ap.add_argument('--serial', action='store_true', help='no stream pipeline: one stream, kernels back to back')
+    ap.add_argument('--exchange', default='nccl', choices=['nccl', 'peer'],
+                    help='multi-GPU dedup exchange: NCCL all-to-all, or peer-memory stores from inside the kernels')
     return ap.parse_args()
 
 
@@ -328,7 +330,11 @@ def run_b200(args):
     H = args.history
     cap_rows = H + int(0.92 * n) * total_steps + n
     history = TrialHistory(compiled, n_slots=table_slots_for(cap_rows, load=0.75))
-    sharded = ShardedHistory(history, device=dev)
+    if world > 1 and args.exchange == 'peer':
+        from orion_b200.dist import PeerShardedHistory
+        sharded = PeerShardedHistory(history, max_n=n)      # kernels store straight into the owners' HBM
+    else:
+        sharded = ShardedHistory(history, device=dev)       # NCCL all-to-all
     chunk = n
     hb = compiled.empty_columns(chunk)
     done = 0
@@ -360,6 +366,8 @@ def run_b200(args):
     pipe = CandidatePipeline(compiled, sharded, n, depth=2)
     batch, tbatch, back = pipe.slots[0].batch, pipe.slots[0].tbatch, pipe.slots[0].back
     fused = not args.unfused
+    # extra kernels of mine per step for the exchange: NCCL path bucket+pad+scatter; peer path send+counts+pad+return+collect
+    exchange_launches = 0 if world == 1 else (5 if args.exchange == 'peer' else 3)
     kernel_names = ['sample+transform', 'reverse', 'dedup'] if fused else ['sample', 'transform', 'reverse', 'dedup']
     ev = [[torch.cuda.Event(enable_timing=True) for _ in range(len(kernel_names) + 1)] for _ in range(K)]
     launches = [0]
@@ -383,7 +391,7 @@ def run_b200(args):
         sharded.dedup(batch.fp, n, per_rank_n=n, keep=batch.keep, check=False)
         if events:
             events[j + 2].record()
-        launches[0] += (4 if fused else 5) + (0 if world == 1 else 3)
+        launches[0] += (4 if fused else 5) + exchange_launches
 
     def sync_all():
         if world > 1:
@@ -420,7 +428,7 @@ def run_b200(args):
         sync_all()
         clock_info = clocks.stop() if rank == 0 else None
         elapsed_ms = max_over_ranks(t_begin.elapsed_time(t_end))
-        timed_launches = K * (4 + (0 if world == 1 else 3))
+        timed_launches = K * (4 + exchange_launches)
         contended_ms = pipe.kernel_ms()
         pipe.timed = False
         last_batch, last_back = slot.batch, slot.back
@@ -456,7 +464,8 @@ def run_b200(args):
         kept_last = int(batch.keep[:n].sum().item())
         mask_ok = bool(batch.mask[:n].all().item())
         round_trip_ok = bool(torch.equal(back.buf, batch.buf))
-    sharded._check_overflow(sharded._buffers(n)) if world > 1 else None
+    if world > 1:        # did any (source, owner) lane overflow during the run?
+        sharded.check_overflow() if args.exchange == 'peer' else sharded._check_overflow(sharded._buffers(n))
     hist_rows1 = len(history)
 
     per_kernel_ms = {}

@@ -219,6 +219,34 @@ int ob2_bucket_by_owner(int64_t n, const uint64_t *fp, uint32_t key_base, int32_
 int ob2_scatter_verdict(int64_t n_entries, const uint32_t *src_index, const uint8_t *verdict,
                         const uint64_t *fp, uint8_t *keep, void *stream);
 
+/* Peer-memory exchange: the same sharded dedup with the transfers done by the
+ * kernels themselves over NVLink (no counterpart in the reference).
+ * Every rank creates an exchange (it owns an inbox region in its HBM -- the one
+ * place where the library allocates, because CUDA IPC shares whole
+ * allocations), publishes its 64-byte IPC handle, and opens everybody else's.
+ * Per batch, on one stream:
+ *     ob2_xchg_send     bucket by owner, storing (fp, order key) straight into
+ *                       the owners' inboxes
+ *     <barrier>         any stream-ordered collective (e.g. a 1-element all-reduce)
+ *     ob2_xchg_dedup    dedup my inbox against my shard, store the verdicts
+ *                       straight into the sources' verdict inboxes
+ *                       (insert_only != 0: history load, no verdicts)
+ *     <barrier>
+ *     ob2_xchg_collect  scatter the verdicts I received into keep[0..n)
+ * `cap` = capacity of one (source, owner) lane; ob2_xchg_send_counts reads back
+ * how many entries went to each owner (a count above cap means dropped entries). */
+typedef struct ob2_xchg ob2_xchg;
+int ob2_xchg_create(int32_t rank, int32_t world, int64_t cap, ob2_xchg **out);
+void ob2_xchg_destroy(ob2_xchg *x);
+int ob2_xchg_ipc_handle(const ob2_xchg *x, void *handle64);
+int ob2_xchg_open_peers(ob2_xchg *x, const void *handles /* [world][64] */);
+int ob2_xchg_set_peers(ob2_xchg *x, void *const *regions /* same-process ranks */);
+void *ob2_xchg_region(const ob2_xchg *x);
+int ob2_xchg_send(ob2_xchg *x, int64_t n, const uint64_t *fp, uint32_t key_base, void *stream);
+int ob2_xchg_dedup(ob2_xchg *x, ob2_set *set, int32_t insert_only, void *stream);
+int ob2_xchg_collect(ob2_xchg *x, int64_t n, uint8_t *keep, void *stream);
+int ob2_xchg_send_counts(const ob2_xchg *x, uint32_t *counts_host, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -76,6 +76,16 @@ SIGNATURES = {
     'ob2_compact': (ctypes.c_int, [_vp, _i64, _i64, _vp, _vp, _i32, _i64, _vp, _vp, _vp, _vp]),
     'ob2_bucket_by_owner': (ctypes.c_int, [_i64, _vp, _u32, _i32, _i64, _vp, _vp, _vp, _vp, _vp]),
     'ob2_scatter_verdict': (ctypes.c_int, [_i64, _vp, _vp, _vp, _vp, _vp]),
+    'ob2_xchg_create': (ctypes.c_int, [_i32, _i32, _i64, ctypes.POINTER(_vp)]),
+    'ob2_xchg_destroy': (None, [_vp]),
+    'ob2_xchg_ipc_handle': (ctypes.c_int, [_vp, _vp]),
+    'ob2_xchg_open_peers': (ctypes.c_int, [_vp, _vp]),
+    'ob2_xchg_set_peers': (ctypes.c_int, [_vp, ctypes.POINTER(_vp)]),
+    'ob2_xchg_region': (_vp, [_vp]),
+    'ob2_xchg_send': (ctypes.c_int, [_vp, _i64, _vp, _u32, _vp]),
+    'ob2_xchg_dedup': (ctypes.c_int, [_vp, _vp, _i32, _vp]),
+    'ob2_xchg_collect': (ctypes.c_int, [_vp, _i64, _vp, _vp]),
+    'ob2_xchg_send_counts': (ctypes.c_int, [_vp, ctypes.POINTER(_u32), _vp]),
 }
 
 _lib = None

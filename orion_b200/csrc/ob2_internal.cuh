@@ -19,6 +19,7 @@ struct ob2_space {
     ob2_slot_desc *d_slots;
     double *d_cdf;
     bool has_onehot;
+    bool has_extended_prior;  // a slot uses one of the OB2_DIST_EXPON.. priors
     int unsamplable_slot;  // first slot whose prior has no device inverse CDF, or -1
 };
 
@@ -86,7 +87,35 @@ __device__ __forceinline__ double u53(uint32_t w0, uint32_t w1) {
     return __ull2double_rn(v) * 1.1102230246251565e-16;  // 2^-53
 }
 
+// The ten extra closed-form priors, out of line and out of the common kernel (EXT = false
+// never references it).
+static __device__ __noinline__ double draw_extended(int dist, double p0, double p1, double u) {
+    switch (dist) {
+        case OB2_DIST_EXPON:
+            return -log1p(-u);
+        case OB2_DIST_LOGNORM:  // p0 = s
+            return exp(__dmul_rn(p0, normcdfinv(u)));
+        case OB2_DIST_LOGISTIC:
+            return log(u / (1.0 - u));
+        case OB2_DIST_LAPLACE:
+            return u > 0.5 ? -log(2.0 * (1.0 - u)) : log(2.0 * u);
+        case OB2_DIST_GUMBEL_R:
+            return -log(-log(u));
+        case OB2_DIST_WEIBULL_MIN:  // p1 = 1 / c
+            return pow(-log1p(-u), p1);
+        case OB2_DIST_PARETO:  // p1 = -1 / b
+            return pow(1.0 - u, p1);
+        case OB2_DIST_RAYLEIGH:
+            return sqrt(-2.0 * log1p(-u));
+        case OB2_DIST_HALFNORM:
+            return normcdfinv(0.5 * (1.0 + u));
+        default:  // OB2_DIST_POWERLAW, p1 = 1 / a
+            return pow(u, p1);
+    }
+}
+
 // base(u) * scale + loc, rounded multiply then rounded add (scipy rv_generic.rvs)
+template <bool EXT>
 __device__ __forceinline__ double draw_real(const ob2_slot_desc &d, double u) {
     double b;
     switch (d.dist) {
@@ -99,39 +128,12 @@ __device__ __forceinline__ double draw_real(const ob2_slot_desc &d, double u) {
         case OB2_DIST_NORM:
             b = normcdfinv(u);
             break;
-        // closed-form inverse CDFs of further scipy priors (scipy's own _ppf formulas)
-        case OB2_DIST_EXPON:
-            b = -log1p(-u);
-            break;
-        case OB2_DIST_LOGNORM:  // p0 = s
-            b = exp(__dmul_rn(d.p0, normcdfinv(u)));
-            break;
-        case OB2_DIST_LOGISTIC:
-            b = log(u / (1.0 - u));
-            break;
-        case OB2_DIST_LAPLACE:
-            b = u > 0.5 ? -log(2.0 * (1.0 - u)) : log(2.0 * u);
-            break;
-        case OB2_DIST_GUMBEL_R:
-            b = -log(-log(u));
-            break;
-        case OB2_DIST_WEIBULL_MIN:  // p0 = c, p1 = 1 / c
-            b = pow(-log1p(-u), d.p1);
-            break;
-        case OB2_DIST_PARETO:  // p0 = b, p1 = -1 / b
-            b = pow(1.0 - u, d.p1);
-            break;
-        case OB2_DIST_RAYLEIGH:
-            b = sqrt(-2.0 * log1p(-u));
-            break;
-        case OB2_DIST_HALFNORM:
-            b = normcdfinv(0.5 * (1.0 + u));
-            break;
-        case OB2_DIST_POWERLAW:  // p0 = a, p1 = 1 / a
-            b = pow(u, d.p1);
-            break;
-        default:
+        case OB2_DIST_CONST:
             return d.loc;  // scale == 0
+        default:  // closed-form inverse CDFs of further scipy priors (scipy's own _ppf formulas)
+            if (!EXT) return d.loc;
+            b = draw_extended(d.dist, d.p0, d.p1, u);
+            break;
     }
     return __dadd_rn(__dmul_rn(b, d.scale), d.loc);
 }

@@ -46,7 +46,7 @@ __device__ __forceinline__ int draw_cat_fast(const double *cdf, int k, double u,
 // the fingerprint lanes are wrapping sums, so the contribution of the rejected
 // values (read back from the columns this thread just wrote) is subtracted and
 // the redrawn one added.
-template <bool WITH_FP, bool WITH_T>
+template <bool WITH_FP, bool WITH_T, bool EXT>
 __device__ __forceinline__ bool redraw_dim(const ob2_slot_desc *s_slots, int s_last, uint64_t index, int64_t i,
                                            int64_t n_stride, char *cols, char *tcols, uint32_t k0, uint32_t k1,
                                            uint32_t pm0, uint32_t pm1, FpAcc &acc) {
@@ -73,7 +73,7 @@ __device__ __forceinline__ bool redraw_dim(const ob2_slot_desc *s_slots, int s_l
             const ob2_slot_desc &d = s_slots[e];
             const Philox4 r = philox4x32_10((uint32_t)index, (uint32_t)(index >> 32), (uint32_t)(e >> 1), a, k0, k1, pm0, pm1);
             const double u = (e & 1) ? u53(r.z, r.w) : u53(r.x, r.y);
-            double x = draw_real(d, u);
+            double x = draw_real<EXT>(d, u);
             char *col = cols + (int64_t)d.col_units * n_stride;
             char *dst = tcols + (int64_t)d.t_units * n_stride;
             uint64_t w;
@@ -117,7 +117,7 @@ __device__ __forceinline__ bool redraw_dim(const ob2_slot_desc *s_slots, int s_l
 // the descriptor; the fingerprint accumulates straight into its lanes; the
 // second candidate of a trailing odd pair replays the first (no `has1` tests
 // until the final stores).
-template <bool PHILOX, bool WITH_FP, bool WITH_T>
+template <bool PHILOX, bool WITH_FP, bool WITH_T, bool EXT>
 __global__ void __launch_bounds__(OB2_BLOCK, 4)
 sample_kernel(const ob2_slot_desc *__restrict__ g_slots, int n_slots, const double *__restrict__ g_cdf,
               int cdf_len, int64_t n, int64_t n_stride, uint32_t k0, uint32_t k1, uint32_t pm0, uint32_t pm1,
@@ -197,8 +197,8 @@ sample_kernel(const ob2_slot_desc *__restrict__ g_slots, int n_slots, const doub
                 ok1 &= c1 < d.n_cats;
             }
         } else {
-            double x0 = draw_real(d, u0);
-            double x1 = draw_real(d, u1);
+            double x0 = draw_real<EXT>(d, u0);
+            double x1 = draw_real<EXT>(d, u1);
             if (d.kind == OB2_KIND_INTEGER) {
                 x0 = floor(x0);  // _Discrete.sample, space.py:294
                 x1 = floor(x1);
@@ -237,9 +237,9 @@ sample_kernel(const ob2_slot_desc *__restrict__ g_slots, int n_slots, const doub
             if (!(ok0 & ok1)) {  // cold: only Real/Integer slots can clear ok
                 if (PHILOX) {
                     if (!ok0)
-                        ok0 = redraw_dim<WITH_FP, WITH_T>(s_slots, s, idx0, i0, n_stride, cols, tcols, k0, k1, pm0, pm1, acc0);
+                        ok0 = redraw_dim<WITH_FP, WITH_T, EXT>(s_slots, s, idx0, i0, n_stride, cols, tcols, k0, k1, pm0, pm1, acc0);
                     if (!ok1)
-                        ok1 = redraw_dim<WITH_FP, WITH_T>(s_slots, s, idx1, i0 + 1, n_stride, cols, tcols, k0, k1, pm0, pm1, acc1);
+                        ok1 = redraw_dim<WITH_FP, WITH_T, EXT>(s_slots, s, idx1, i0 + 1, n_stride, cols, tcols, k0, k1, pm0, pm1, acc1);
                     if (n_failed != nullptr) {  // 4 misses: the reference raises "Improbable bounds"
                         const unsigned bad = (ok0 ? 0u : 1u) + ((ok1 || !has1) ? 0u : 1u);
                         if (bad) atomicAdd(n_failed + d.dim_first, bad);
@@ -325,9 +325,9 @@ struct SampleArgs {
     void *stream;
 };
 
-template <bool PHILOX, bool WITH_FP, bool WITH_T>
+template <bool PHILOX, bool WITH_FP, bool WITH_T, bool EXT>
 int launch_one(const SampleArgs &a, unsigned blocks) {
-    auto kern = sample_kernel<PHILOX, WITH_FP, WITH_T>;
+    auto kern = sample_kernel<PHILOX, WITH_FP, WITH_T, EXT>;
     const ob2_space *sp = a.sp;
     int rc = prepare_smem(kern, sp->smem_bytes);
     if (rc != OB2_OK) return rc;
@@ -364,10 +364,18 @@ int launch_sample(const SampleArgs &a) {
     }
     const unsigned b = (unsigned)blocks;
     const bool with_fp = a.fp != nullptr, with_t = a.tcols != nullptr;
-    if (with_fp && with_t) return launch_one<PHILOX, true, true>(a, b);
-    if (with_fp) return launch_one<PHILOX, true, false>(a, b);
-    if (with_t) return launch_one<PHILOX, false, true>(a, b);
-    return launch_one<PHILOX, false, false>(a, b);
+    // EXT = the space uses one of the extra closed-form priors: those inverse CDFs live in a
+    // separate instantiation so that the common kernel keeps its registers and code size
+    if (a.sp->has_extended_prior) {
+        if (with_fp && with_t) return launch_one<PHILOX, true, true, true>(a, b);
+        if (with_fp) return launch_one<PHILOX, true, false, true>(a, b);
+        if (with_t) return launch_one<PHILOX, false, true, true>(a, b);
+        return launch_one<PHILOX, false, false, true>(a, b);
+    }
+    if (with_fp && with_t) return launch_one<PHILOX, true, true, false>(a, b);
+    if (with_fp) return launch_one<PHILOX, true, false, false>(a, b);
+    if (with_t) return launch_one<PHILOX, false, true, false>(a, b);
+    return launch_one<PHILOX, false, false, false>(a, b);
 }
 
 }  // namespace

@@ -40,6 +40,7 @@ extern "C" int ob2_space_create(const ob2_slot_desc *slots, int32_t n_slots, con
     int32_t t_cols = 0;
     bool has_onehot = false;
     int unsamplable = -1;
+    bool extended = false;
     for (int s = 0; s < n_slots; ++s) {
         const ob2_slot_desc &d = slots[s];
         if (d.kind < OB2_KIND_REAL || d.kind > OB2_KIND_CATEGORICAL) {
@@ -57,6 +58,7 @@ extern "C" int ob2_space_create(const ob2_slot_desc *slots, int32_t n_slots, con
             return OB2_EINVAL;
         }
         if (d.kind != OB2_KIND_CATEGORICAL && d.dist == OB2_DIST_NONE && unsamplable < 0) unsamplable = s;
+        if (d.kind != OB2_KIND_CATEGORICAL && d.dist > OB2_DIST_NONE) extended = true;
         if (d.dim_first < 0 || d.dim_first > s) {
             ob2_set_error("slot %d: dim_first %d out of order", s, d.dim_first);
             return OB2_EINVAL;
@@ -132,6 +134,7 @@ extern "C" int ob2_space_create(const ob2_slot_desc *slots, int32_t n_slots, con
     sp->smem_bytes = smem;
     sp->has_onehot = has_onehot;
     sp->unsamplable_slot = unsamplable;
+    sp->has_extended_prior = extended;
     sp->d_slots = nullptr;
     sp->d_cdf = nullptr;
     int rc = ob2_check_cuda(cudaGetDevice(&sp->device), "cudaGetDevice");

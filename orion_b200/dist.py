@@ -138,3 +138,121 @@ class ShardedHistory(object):
         self.ops.insert(self.history, b['in_fp'].view(-1, 2))
         if check:
             self._check_overflow(b)
+
+
+class PeerExchange(object):
+    """ctypes wrapper of one rank's ``ob2_xchg`` (inbox region + kernels)."""
+
+    def __init__(self, rank, world, cap, device):
+        self.lib = _lib.load()
+        self.rank, self.world, self.cap = rank, world, cap
+        self.device = torch.device(device)
+        handle = ctypes.c_void_p()
+        with torch.cuda.device(self.device):
+            _lib.check(self.lib.ob2_xchg_create(rank, world, cap, ctypes.byref(handle)))
+        self.handle = handle
+
+    def __del__(self):
+        handle = getattr(self, 'handle', None)
+        if handle:
+            try:
+                self.lib.ob2_xchg_destroy(handle)
+            except Exception:
+                pass
+            self.handle = None
+
+    def _stream(self):
+        return ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def ipc_handle(self):
+        buf = ctypes.create_string_buffer(64)
+        _lib.check(self.lib.ob2_xchg_ipc_handle(self.handle, buf))
+        return buf.raw
+
+    def open_peers(self, handles):
+        """handles: list of the 64-byte IPC handles of every rank, in rank order."""
+        blob = b''.join(handles)
+        assert len(blob) == 64 * self.world
+        _lib.check(self.lib.ob2_xchg_open_peers(self.handle, blob))
+
+    def set_peers(self, regions):
+        """Same-process ranks: raw region addresses in rank order."""
+        arr = (ctypes.c_void_p * self.world)(*regions)
+        _lib.check(self.lib.ob2_xchg_set_peers(self.handle, arr))
+
+    def region(self):
+        return self.lib.ob2_xchg_region(self.handle)
+
+    def send(self, fp, n, key_base):
+        _lib.check(self.lib.ob2_xchg_send(self.handle, n, fp.data_ptr(), key_base, self._stream()))
+
+    def dedup(self, history, insert_only=False):
+        _lib.check(self.lib.ob2_xchg_dedup(self.handle, history.handle, 1 if insert_only else 0, self._stream()))
+
+    def collect(self, n, keep):
+        _lib.check(self.lib.ob2_xchg_collect(self.handle, n, keep.data_ptr(), self._stream()))
+
+    def send_counts(self):
+        out = (ctypes.c_uint32 * self.world)()
+        _lib.check(self.lib.ob2_xchg_send_counts(self.handle, out, self._stream()))
+        return list(out)
+
+
+class PeerShardedHistory(object):
+    """Sharded dedup whose exchange runs over peer memory (NVLink stores from
+    inside the kernels) instead of NCCL all-to-alls; same results as
+    :class:`ShardedHistory`.  Cross-rank ordering uses two 1-element all-reduces
+    per batch as stream-ordered barriers."""
+
+    def __init__(self, history, max_n, group=None):
+        self.history = history
+        self.group = group
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.device = history.device
+        self.max_n = int(max_n)
+        self.cap = bucket_capacity(self.max_n, self.world)
+        self.xchg = PeerExchange(self.rank, self.world, self.cap, self.device)
+        self._token = torch.zeros(1, dtype=torch.int32, device=self.device)
+        if self.world > 1:
+            mine = torch.tensor(list(self.xchg.ipc_handle()), dtype=torch.uint8, device=self.device)
+            everyone = [torch.empty(64, dtype=torch.uint8, device=self.device) for _ in range(self.world)]
+            dist.all_gather(everyone, mine, group=group)
+            self.xchg.open_peers([bytes(t.cpu().tolist()) for t in everyone])
+            dist.barrier(group=group)
+
+    def _barrier(self):
+        if self.world > 1:
+            dist.all_reduce(self._token, group=self.group)     # stream-ordered; no host sync
+
+    def dedup(self, fp, n, per_rank_n=None, keep=None, check=True):
+        per_rank_n = n if per_rank_n is None else per_rank_n
+        if n > self.max_n:
+            raise ValueError("batch of %d exceeds the exchange capacity sized for %d" % (n, self.max_n))
+        if (self.world - 1) * per_rank_n + n >= 2 ** 32 - 1:
+            raise ValueError("global candidate index does not fit the 32-bit order key")
+        if keep is None:
+            keep = torch.empty(fp.shape[0], dtype=torch.uint8, device=self.device)
+        self.xchg.send(fp, n, self.rank * per_rank_n)
+        self._barrier()
+        self.xchg.dedup(self.history)
+        self._barrier()
+        self.xchg.collect(n, keep)
+        if check:
+            self.check_overflow()
+        return keep
+
+    def insert(self, fp, n, check=True):
+        if n > self.max_n:
+            raise ValueError("batch of %d exceeds the exchange capacity sized for %d" % (n, self.max_n))
+        self.xchg.send(fp, n, 0)
+        self._barrier()
+        self.xchg.dedup(self.history, insert_only=True)
+        self._barrier()
+        if check:
+            self.check_overflow()
+
+    def check_overflow(self):
+        worst = max(self.xchg.send_counts())
+        if worst > self.cap:
+            raise RuntimeError("exchange lane overflow: %d fingerprints for one owner, capacity %d" % (worst, self.cap))

@@ -44,7 +44,8 @@ class CandidatePipeline(object):
     def __init__(self, compiled, history, n, depth=2, timed=False):
         self.compiled = compiled
         self.n = n
-        self.sharded = history if isinstance(history, ShardedHistory) else ShardedHistory(history, device=compiled.device)
+        # a ShardedHistory / PeerShardedHistory is used as is; a bare TrialHistory is wrapped
+        self.sharded = history if hasattr(history, 'world') else ShardedHistory(history, device=compiled.device)
         self.slots = [BatchSlot(compiled, n) for _ in range(depth)]
         dev = compiled.device
         # The dedup kernels are latency bound (random 32-byte probes) and tiny next to the
