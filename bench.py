@@ -51,7 +51,7 @@ def parse_args():
     ap.add_argument('--cands', type=int, default=CANDS_PER_GPU, help='candidates per GPU per step')
     ap.add_argument('--history', type=int, default=HISTORY_PER_GPU, help='history rows per GPU')
     ap.add_argument('--no-cpu-baseline', action='store_true')
-    ap.add_argument('--e2e-steps', type=int, default=2)
+    ap.add_argument('--e2e-steps', type=int, default=4)
     ap.add_argument('--unfused', action='store_true', help='sample and transform as two kernels')
     ap.add_argument('--serial', action='store_true', help='no stream pipeline: one stream, kernels back to back')
     ap.add_argument('--exchange', default='nccl', choices=['nccl', 'peer'],
@@ -481,15 +481,37 @@ def run_b200(args):
         host_idx = [torch.empty(n, dtype=torch.int64).pin_memory() for _ in range(E + 2)]
         for j, h in enumerate(host_idx):
             h.copy_(step_index(W + 2 * K + j))
-        # two sets of pinned host buffers and device staging: the copies of step j overlap step j+1
+        # Survivors only cross PCIe: after dedup the kept rows are gathered into a dense block on
+        # the device (ob2_compact) and each column's first n_kept elements are copied to pinned
+        # host memory.  Two buffer sets: compaction and copies of step j overlap step j+1.
+        from orion_b200.columns import _SIZE
+        ns = batch.n_stride
         host_cols = [torch.empty(batch.buf.numel(), dtype=torch.uint8).pin_memory() for _ in range(2)]
-        host_keep = [torch.empty(batch.n_stride, dtype=torch.uint8).pin_memory() for _ in range(2)]
+        host_cnt = [torch.zeros(1, dtype=torch.int64).pin_memory() for _ in range(2)]
+        dense = [compiled.empty_columns(n) for _ in range(2)]
+        cnt_dev = [torch.zeros(1, dtype=torch.int64, device=dev) for _ in range(2)]
+        cscratch = [torch.empty(max(int(compiled.lib.ob2_compact_scratch_bytes(n)), 8), dtype=torch.uint8, device=dev)
+                    for _ in range(2)]
         idx_dev = [torch.empty(n, dtype=torch.int64, device=dev) for _ in range(2)]
+        compacted = [torch.cuda.Event() for _ in range(2)]
         copied = [torch.cuda.Event() for _ in range(2)]
+        s_comp = torch.cuda.Stream(device=dev)
         s_copy = torch.cuda.Stream(device=dev)
         epipe = pipe
         epipe.drain()
         cur = torch.cuda.current_stream()
+        state = {'pending': None, 'd2h': 0, 'kept': 0, 'used': [False, False]}
+
+        def copy_out(b):
+            compacted[b].synchronize()              # the host needs n_kept; the GPU already works on the next step
+            k = int(host_cnt[b][0])
+            with torch.cuda.stream(s_copy):
+                for units, dt in compiled.col_meta:
+                    start, nbytes = units * ns, k * _SIZE[dt]
+                    host_cols[b][start:start + nbytes].copy_(dense[b].buf[start:start + nbytes], non_blocking=True)
+                copied[b].record()
+            state['d2h'] += k * compiled.row_bytes + 8
+            state['kept'] = k
 
         def e2e_step(j):
             b = j % 2
@@ -498,22 +520,33 @@ def run_b200(args):
                 cur.wait_event(slot.sampled)                                    # idx_dev[b] no longer read
             idx_dev[b].copy_(host_idx[j], non_blocking=True)                    # H2D: this step's input
             slot = epipe.submit(SEED, index=idx_dev[b])
-            with torch.cuda.stream(s_copy):
-                s_copy.wait_event(slot.reversed)
-                s_copy.wait_event(slot.deduped)
-                host_cols[b].copy_(slot.back.buf, non_blocking=True)            # D2H: the candidates
-                host_keep[b].copy_(slot.batch.keep, non_blocking=True)          # D2H: the verdicts
-                copied[b].record()
-            slot.hold = copied[b]                                               # buffers stay put until copied out
+            with torch.cuda.stream(s_comp):
+                s_comp.wait_event(slot.reversed)
+                s_comp.wait_event(slot.deduped)
+                if state['used'][b]:
+                    s_comp.wait_event(copied[b])                                # dense[b] has been copied out
+                slot.back.compact(keep=slot.batch.keep, out=dense[b], count=cnt_dev[b], scratch=cscratch[b])
+                host_cnt[b].copy_(cnt_dev[b], non_blocking=True)                # D2H: how many survived
+                compacted[b].record()
+            state['used'][b] = True
+            slot.hold = compacted[b]                                            # slot buffers are free once gathered
+            if state['pending'] is not None:
+                copy_out(state['pending'])                                      # D2H: the previous step's survivors
+            state['pending'] = b
 
         def e2e_finish():
+            if state['pending'] is not None:
+                copy_out(state['pending'])
+                state['pending'] = None
             epipe.drain()
+            cur.wait_stream(s_comp)
             cur.wait_stream(s_copy)
 
         e2e_step(0)
         e2e_step(1)
         e2e_finish()
         sync_all()
+        state['d2h'] = 0
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         for j in range(E):
@@ -522,13 +555,12 @@ def run_b200(args):
         e1.record()
         sync_all()
         e2e_ms = max_over_ranks(e0.elapsed_time(e1))
-        e2e_kept = int(host_keep[(E + 1) % 2][:n].sum())
         e2e = {"value": world * n * args.e2e_steps / (e2e_ms * 1e-3), "unit": UNIT,
                "h2d_bytes_per_step": int(n * 8),
-               "d2h_bytes_per_step": int(host_cols[0].numel() + host_keep[0].numel()),
-               "steps": args.e2e_steps, "kept_last_step": e2e_kept,
-               "api": "CandidatePipeline.submit(index copied from pinned host) -> sample+transform -> reverse || dedup "
-                      "-> candidate columns + keep mask copied to pinned host (copies overlap the next step)"}
+               "d2h_bytes_per_step": int(state['d2h'] // max(E, 1)),
+               "steps": args.e2e_steps, "kept_last_step": state['kept'],
+               "api": "CandidatePipeline.submit(counters copied from pinned host) -> sample+transform -> reverse || dedup "
+                      "-> ob2_compact -> surviving candidates' columns copied to pinned host (copies overlap the next step)"}
 
     if rank != 0:
         if world > 1:

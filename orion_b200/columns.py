@@ -74,10 +74,12 @@ class ColumnBatch(object):
         batch.buf.copy_(torch.from_numpy(host))
         return batch
 
-    def compact(self, keep=None, out=None):
+    def compact(self, keep=None, out=None, count=None, scratch=None):
         """Dense ColumnBatch of the rows with ``keep != 0`` (default: the
         batch's own dedup verdicts), original order preserved
-        (``ob2_compact``).  Reads the survivor count back (one sync)."""
+        (``ob2_compact``).  Reads the survivor count back (one sync) unless a
+        device ``count`` tensor (int64[1]) is passed, in which case nothing
+        synchronises and ``dest.n`` is left for the caller to set."""
         import ctypes
         from . import _lib
         c = self.compiled
@@ -85,13 +87,18 @@ class ColumnBatch(object):
         assert keep is not None and keep.dtype == torch.uint8
         dest = out if out is not None else c.empty_columns(self.n, self.transformed)
         nbytes = c.lib.ob2_compact_scratch_bytes(self.n)
-        scratch = torch.empty(max(nbytes, 8), dtype=torch.uint8, device=c.device)
-        count = torch.zeros(1, dtype=torch.int64, device=c.device)
+        if scratch is None:
+            scratch = torch.empty(max(nbytes, 8), dtype=torch.uint8, device=c.device)
+        assert scratch.numel() * scratch.element_size() >= nbytes
+        lazy = count is not None
+        if count is None:
+            count = torch.zeros(1, dtype=torch.int64, device=c.device)
         _lib.check(c.lib.ob2_compact(c.handle, self.n, self.n_stride, self.buf.data_ptr(), keep.data_ptr(),
                                      1 if self.transformed else 0, dest.n_stride, dest.buf.data_ptr(),
                                      scratch.data_ptr(), count.data_ptr(),
                                      ctypes.c_void_p(torch.cuda.current_stream(c.device).cuda_stream)))
-        dest.n = int(count.item())
+        if not lazy:
+            dest.n = int(count.item())
         return dest
 
     def fingerprints_numpy(self):
