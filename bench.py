@@ -17,7 +17,6 @@ Prints ONE JSON line (rank 0).
 """
 import argparse
 import json
-import math
 import os
 import subprocess
 import sys
@@ -66,14 +65,12 @@ def _cpu_worker(job):
     """One process: the whole path on `n` candidates with numpy (oracle port)."""
     import numpy as np
     from oracle import space_oracle as so
-    from tests.spec_util import specs_from_space  # noqa: F401  (kept importable on the box)
     n, base, seed, n_hist = job
     specs = _mixed64_specs()
     hist_cols, _ = so.sample_philox(specs, n_hist, seed, base_index=HISTORY_BASE + base)
     history = set(zip(*[x.tolist() for x in so.fingerprint(hist_cols)]))
     t0 = time.perf_counter()
     # planted duplicates: 10 % history counters, 1 % repeat an earlier counter
-    idx = np.arange(n, dtype=np.uint64) + np.uint64(base)
     cols, failed = so.sample_philox(specs, n, seed, base_index=base)
     dup = np.arange(n) % 10 == 3
     for c, h in zip(cols, hist_cols):
@@ -84,7 +81,7 @@ def _cpu_worker(job):
     lo, hi = so.fingerprint(back)
     keep = so.dedup_fingerprints(history, lo, hi)
     dt = time.perf_counter() - t0
-    assert ok.all() and not failed.any() and len(idx) == n
+    assert ok.all() and not failed.any() and len(keep) == n
     return dt, int(keep.sum())
 
 
@@ -475,7 +472,6 @@ def run_b200(args):
     # ---- end to end through the public API with host buffers
     e2e = None
     if args.e2e_steps > 0:
-        from orion_b200.algo.random import Random  # noqa: F401  (public entry; the column path below is what it calls)
         from orion_b200.pipeline import CandidatePipeline
         E = args.e2e_steps
         host_idx = [torch.empty(n, dtype=torch.int64).pin_memory() for _ in range(E + 2)]

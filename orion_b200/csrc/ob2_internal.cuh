@@ -153,9 +153,6 @@ __device__ __forceinline__ int draw_cat(const double *cdf, int k, double u) {
 }
 
 // ---- fingerprint pieces
-__device__ __forceinline__ uint64_t mum64(uint64_t x, uint64_t m) {
-    return __umul64hi(x, m) ^ (x * m);
-}
 __device__ __forceinline__ uint64_t fmix64(uint64_t x) {
     x ^= x >> 33;
     x *= 0xFF51AFD7ED558CCDull;

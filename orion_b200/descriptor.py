@@ -29,8 +29,6 @@ _OPS = {
     'numerical': {'real': _lib.OP_IDENTITY, 'integer': _lib.OP_IDENTITY, 'categorical': _lib.OP_ONEHOT},
     None: {'real': _lib.OP_IDENTITY, 'integer': _lib.OP_IDENTITY, 'categorical': _lib.OP_IDENTITY},
 }
-_NP_DTYPE = {8: {'f': np.float64, 'i': np.int64}, 4: {'i': np.int32}}
-_TORCH_DTYPE = {'f8': torch.float64, 'i8': torch.int64, 'i4': torch.int32}
 
 _M64 = (1 << 64) - 1
 

@@ -10,11 +10,13 @@ device op it lowers to); the arithmetic itself runs in ``ob2_transform`` /
 ``ob2_reverse`` for whole batches.  Per-point calls go through the same kernels
 with a batch of one -- there is no host implementation to fall back on.
 """
+from collections import OrderedDict
+
 import numpy
 
 from . import _lib
 from .columns import ColumnBatch
-from .descriptor import compile_space
+from .descriptor import _OPS, compile_space
 from .space import Space, _raise_if_improbable, philox_key
 
 
@@ -162,11 +164,21 @@ _REQUIRED = {
 class TransformedDimension(object):
     """An original dimension seen through a transformer."""
 
-    def __init__(self, transformer, original_dimension, owner=None, index=None):
+    def __init__(self, transformer, original_dimension, requirement=None, quantize='round'):
         self.transformer = transformer
         self.original_dimension = original_dimension
-        self._owner = owner
-        self._index = index
+        self._requirement = requirement
+        self._quantize = quantize
+        self._solo = None
+
+    def _solo_space(self):
+        """This dimension alone as a one-dimension TransformedSpace (the device
+        path works on spaces); built on first use."""
+        if self._solo is None:
+            solo = Space()
+            OrderedDict.__setitem__(solo, self.original_dimension.name or '_', self.original_dimension)
+            self._solo = TransformedSpace(solo, self._requirement, self._quantize)
+        return self._solo
 
     @property
     def name(self):
@@ -186,10 +198,10 @@ class TransformedDimension(object):
         return self.transformer.interval(*self.original_dimension.interval(alpha))
 
     def transform(self, point):
-        return self._owner.transform(self._owner._pad_point(self._index, point))[self._index]
+        return self._solo_space().transform((point,))[0]
 
     def reverse(self, transformed_point):
-        return self._owner.reverse(self._owner._pad_tpoint(self._index, transformed_point))[self._index]
+        return self._solo_space().reverse((transformed_point,))[0]
 
     def sample(self, n_samples=1, seed=None):
         return [self.transform(p) for p in self.original_dimension.sample(n_samples, seed)]
@@ -210,17 +222,13 @@ class TransformedSpace(Space):
         self.original = original_space
         self.requirement = requirement
         self.quantize = quantize
-        for j, dim in enumerate(original_space.values()):
+        for dim in original_space.values():
             kind = 'real' if dim.type == 'dimension' else dim.type
             t = _REQUIRED[requirement][kind](dim)
-            tdim = TransformedDimension(t, dim, owner=self, index=j)
-            if _device_op(t, kind) != self._expected_op(kind):
+            if _device_op(t, kind) != _OPS[requirement][kind]:
                 raise NotImplementedError("no device lowering for {!r}".format(t))
-            OrderedDictSet(self, dim.name, tdim)
-
-    def _expected_op(self, kind):
-        from .descriptor import _OPS
-        return _OPS[self.requirement][kind]
+            # (Space.__setitem__ only admits Dimension instances)
+            OrderedDict.__setitem__(self, dim.name, TransformedDimension(t, dim, requirement, quantize))
 
     def compiled(self, requirement=None, quantize=None):
         return compile_space(self.original, self.requirement, self.quantize)
@@ -322,16 +330,6 @@ class TransformedSpace(Space):
     def reverse(self, transformed_point):
         return self.reverse_points([tuple(transformed_point)])[0]
 
-    def _pad_point(self, index, value):
-        """A full original point whose component ``index`` is ``value`` (other
-        components: any in-bounds filler)."""
-        filler = self.original.sample(1, seed=0)[0]
-        return tuple(value if j == index else filler[j] for j in range(len(filler)))
-
-    def _pad_tpoint(self, index, value):
-        filler = self.transform(self.original.sample(1, seed=0)[0])
-        return tuple(value if j == index else filler[j] for j in range(len(filler)))
-
     def sample(self, n_samples=1, seed=None):
         """``[transform(p) for p in original.sample(n, seed)]`` -- computed as
         one device batch."""
@@ -359,12 +357,6 @@ class TransformedSpace(Space):
 
     def interval(self, alpha=1.0):
         return [tdim.interval(alpha) for tdim in self.values()]
-
-
-def OrderedDictSet(space, key, value):
-    """Bypass Space.__setitem__'s Dimension type check for TransformedDimension."""
-    from collections import OrderedDict
-    OrderedDict.__setitem__(space, key, value)
 
 
 def build_required_space(requirement, original_space, quantize='round'):
