@@ -462,7 +462,7 @@ def run_b200(args):
         mask_ok = bool(batch.mask[:n].all().item())
         round_trip_ok = bool(torch.equal(back.buf, batch.buf))
     if world > 1:        # did any (source, owner) lane overflow during the run?
-        sharded.check_overflow() if args.exchange == 'peer' else sharded._check_overflow(sharded._buffers(n))
+        sharded.check_overflow() if args.exchange == 'peer' else sharded.check_overflow(n)
     hist_rows1 = len(history)
 
     per_kernel_ms = {}

@@ -75,8 +75,8 @@ class ShardedHistory(object):
         self.ops = ops if ops is not None else DeviceOps(self.device)
         self._bufs = {}
 
-    def _buffers(self, n):
-        cap = bucket_capacity(n, self.world)
+    def _buffers(self, n, cap=None):
+        cap = bucket_capacity(n, self.world) if cap is None else cap
         key = (n, cap)
         if key not in self._bufs:
             w, dev = self.world, self.device
@@ -93,13 +93,27 @@ class ShardedHistory(object):
             )}
         return self._bufs[key]
 
-    def _route(self, fp, n, per_rank_n):
-        """Steps 1-2: returns the buffers with ``in_fp`` / ``in_key`` filled."""
+    def _route(self, fp, n, per_rank_n, check):
+        """Steps 1-2: returns the buffers with ``in_fp`` / ``in_key`` filled.
+
+        With ``check`` the bucket counts are inspected BEFORE anything is sent:
+        if any rank has a lane that does not fit (many copies of few rows, e.g.
+        a small discrete space -- equal rows share an owner), every rank
+        re-buckets into worst-case lanes (capacity n).  Costs one small
+        all-reduce and a host sync per batch; ``check=False`` skips it and
+        leaves overflow detection to the caller (``_check_overflow``)."""
         b = self._buffers(n)
         key_base = self.rank * per_rank_n
         if (self.world - 1) * per_rank_n + n >= 2 ** 32 - 1:
             raise ValueError("global candidate index does not fit the 32-bit order key")
         self.ops.bucket(fp, n, key_base, self.world, b['cap'], (b['out_fp'], b['out_key'], b['out_src'], b['counts']))
+        if check:
+            worst = b['counts'].max().to(torch.int64).reshape(1)
+            dist.all_reduce(worst, op=dist.ReduceOp.MAX, group=self.group)
+            if int(worst.item()) > b['cap']:
+                b = self._buffers(n, cap=n)
+                self.ops.bucket(fp, n, key_base, self.world, b['cap'],
+                                (b['out_fp'], b['out_key'], b['out_src'], b['counts']))
         dist.all_to_all_single(b['in_fp'], b['out_fp'], group=self.group)
         dist.all_to_all_single(b['in_key'], b['out_key'], group=self.group)
         return b
@@ -120,13 +134,11 @@ class ShardedHistory(object):
         if self.world == 1:
             self.ops.dedup(self.history, fp[:n], None, keep)
             return keep
-        b = self._route(fp, n, per_rank_n)
+        b = self._route(fp, n, per_rank_n, check)
         self.ops.dedup(self.history, b['in_fp'].view(-1, 2), b['in_key'].view(-1), b['verdict'])
         dist.all_to_all_single(b['back'], b['verdict'], group=self.group)
         keep.zero_()
         self.ops.scatter(b['out_src'].view(-1), b['back'], b['out_fp'].view(-1, 2), keep)
-        if check:
-            self._check_overflow(b)
         return keep
 
     def insert(self, fp, n, check=True):
@@ -134,10 +146,14 @@ class ShardedHistory(object):
         if self.world == 1:
             self.ops.insert(self.history, fp[:n])
             return
-        b = self._route(fp, n, n)
+        b = self._route(fp, n, n, check)
         self.ops.insert(self.history, b['in_fp'].view(-1, 2))
-        if check:
-            self._check_overflow(b)
+
+    def check_overflow(self, n):
+        """After a run of ``check=False`` calls with batches of ``n``: raise if
+        the last one dropped fingerprints."""
+        if self.world > 1:
+            self._check_overflow(self._buffers(n))
 
 
 class PeerExchange(object):

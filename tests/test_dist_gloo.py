@@ -65,12 +65,14 @@ class FakeShard(object):
         self.rows = set()
 
 
-def _make_batches(world, n, seed=0):
+def _make_batches(world, n, seed=0, distinct=None):
     """Per-rank fingerprints with duplicates inside a rank, across ranks and
-    against the history."""
+    against the history.  ``distinct`` caps the number of different rows (a
+    small discrete space): equal rows share an owner, so lanes overflow their
+    nominal capacity."""
     rng = np.random.RandomState(seed)
     history = rng.randint(1, 2 ** 62, size=(n, 2), dtype=np.int64)
-    pool = rng.randint(1, 2 ** 62, size=(world * n // 2, 2), dtype=np.int64)      # forces repeats
+    pool = rng.randint(1, 2 ** 62, size=(distinct or world * n // 2, 2), dtype=np.int64)      # forces repeats
     batches = []
     for _ in range(world):
         b = pool[rng.randint(0, len(pool), size=n)].copy()
@@ -94,10 +96,10 @@ def _expected(history, batches):
     return out
 
 
-def _worker(rank, world, init_file, n, result_dir):
+def _worker(rank, world, init_file, n, result_dir, distinct=None):
     dist.init_process_group('gloo', init_method='file://' + init_file, rank=rank, world_size=world)
     try:
-        history, batches = _make_batches(world, n)
+        history, batches = _make_batches(world, n, distinct=distinct)
         sharded = ShardedHistory(FakeShard(), ops=NumpyOps(), device='cpu')
         assert sharded.world == world and sharded.rank == rank
         # history load: every rank contributes a slice, rows land on their owners
@@ -135,6 +137,21 @@ def test_sharded_dedup_world2_matches_single_set():
             owned += int(np.load(os.path.join(tmp, 'owned_%d.npy' % r)))
         assert owned == len(set(map(tuple, history.tolist())))
         assert 0 < sum(int(w.sum()) for w in want) < world * n
+
+
+@pytest.mark.timeout(180)
+def test_sharded_dedup_world2_skewed_owners_fall_back_to_worst_case_lanes():
+    """Three distinct rows: one owner receives far more than mean + slack."""
+    world, n, distinct = 2, 400, 3
+    with tempfile.TemporaryDirectory() as tmp:
+        init_file = os.path.join(tmp, 'rendezvous')
+        mp.spawn(_worker, args=(world, init_file, n, tmp, distinct), nprocs=world, join=True)
+        history, batches = _make_batches(world, n, distinct=distinct)
+        want = _expected(history, batches)
+        for r in range(world):
+            keep1 = np.load(os.path.join(tmp, 'keep1_%d.npy' % r))
+            assert np.array_equal(keep1[:n], want[r]), 'rank %d' % r
+        assert sum(int(w.sum()) for w in want) <= distinct
 
 
 def test_single_rank_path_skips_the_exchange():
