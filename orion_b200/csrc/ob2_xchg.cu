@@ -8,10 +8,10 @@
 //   send     the bucketing kernel stores each (fingerprint, order key) straight
 //            into the owner's inbox -- the "all-to-all" happens store by store
 //            while the kernel is still bucketing;
-//   dedup    the owner dedups its inbox against its shard (ob2_set_dedup) and a
-//            small kernel stores the 1-byte verdicts straight into each source's
-//            verdict inbox;
-//   collect  the source scatters the verdicts into its keep mask.
+//   dedup    the owner dedups its inbox against its shard (ob2_set_dedup); the
+//            verdicts stay in its region, lane by source;
+//   collect  the source pulls its verdict lanes out of the owners' regions
+//            (128-bit loads over NVLink) and scatters them into its keep mask.
 //
 // The caller orders the three phases across ranks with two stream-ordered
 // barriers per batch (any tiny collective on the same stream): one after send,
@@ -63,42 +63,80 @@ struct ob2_xchg {
     uint32_t *out_src;     // [world][cap] local index of what I sent to each owner
     uint32_t *send_cnt;    // [world]
     uint32_t *scratch;     // [world * cap] dedup scratch
-    uint8_t *verdict;      // [world * cap] verdicts of my inbox before they are returned
     bool peers_ready;
 };
 
 namespace {
 
+constexpr int kSendPerThread = 4;
+constexpr int kSendTile = OB2_BLOCK * kSendPerThread;  // 1024 fingerprints per block
+
+// Bucket-and-push.  A block takes a tile of 1024 fingerprints, counting-sorts it by owner in
+// shared memory, reserves one contiguous run per owner in that owner's inbox lane, and then
+// writes the runs out with consecutive threads on consecutive addresses: every owner receives
+// ~2 KB (8 ranks) of contiguous 16-byte stores per block instead of scattered single entries,
+// which is what NVLink wants.
 __global__ void __launch_bounds__(OB2_BLOCK)
 xchg_send_kernel(int64_t n, const uint64_t *__restrict__ fp, uint32_t key_base, int rank, int world, int64_t cap,
                  const PeerTable *__restrict__ peers, size_t fp_off, size_t key_off, uint32_t *__restrict__ out_src,
                  uint32_t *__restrict__ send_cnt) {
-    __shared__ uint32_t s_cnt[OB2_XCHG_MAX_RANKS];
-    __shared__ uint32_t s_base[OB2_XCHG_MAX_RANKS];
-    if (threadIdx.x < world) s_cnt[threadIdx.x] = 0;
+    __shared__ uint32_t s_cnt[OB2_XCHG_MAX_RANKS];   // entries of this tile per owner
+    __shared__ uint32_t s_off[OB2_XCHG_MAX_RANKS];   // where the owner's run starts in the staging arrays
+    __shared__ uint32_t s_base[OB2_XCHG_MAX_RANKS];  // where it starts in the owner's inbox lane
+    __shared__ ulonglong2 s_fp[kSendTile];
+    __shared__ uint32_t s_idx[kSendTile];
+    const int tid = threadIdx.x;
+    if (tid < world) s_cnt[tid] = 0;
     __syncthreads();
-    const int64_t i = (int64_t)blockIdx.x * OB2_BLOCK + threadIdx.x;
-    int owner = -1;
-    uint32_t rank_in_block = 0;
-    ulonglong2 key = make_ulonglong2(0, 0);
-    if (i < n) {
-        key = __ldg(reinterpret_cast<const ulonglong2 *>(fp) + i);
-        if (key.x != 0) {
-            owner = (int)(key.y % (uint64_t)world);
-            rank_in_block = atomicAdd(&s_cnt[owner], 1u);
+    const int64_t tile0 = (int64_t)blockIdx.x * kSendTile;
+    ulonglong2 key[kSendPerThread];
+    int owner[kSendPerThread];
+    uint32_t local_rank[kSendPerThread];
+#pragma unroll
+    for (int q = 0; q < kSendPerThread; ++q) {
+        const int64_t i = tile0 + q * OB2_BLOCK + tid;
+        owner[q] = -1;
+        local_rank[q] = 0;
+        key[q] = make_ulonglong2(0, 0);
+        if (i < n) {
+            key[q] = __ldg(reinterpret_cast<const ulonglong2 *>(fp) + i);
+            if (key[q].x != 0) {
+                owner[q] = (int)(key[q].y % (uint64_t)world);
+                local_rank[q] = atomicAdd(&s_cnt[owner[q]], 1u);
+            }
         }
     }
     __syncthreads();
-    if (threadIdx.x < world) s_base[threadIdx.x] = s_cnt[threadIdx.x] ? atomicAdd(&send_cnt[threadIdx.x], s_cnt[threadIdx.x]) : 0;
+    if (tid == 0) {
+        uint32_t off = 0;
+        for (int o = 0; o < world; ++o) {
+            s_off[o] = off;
+            off += s_cnt[o];
+        }
+    }
+    if (tid < world) s_base[tid] = s_cnt[tid] ? atomicAdd(&send_cnt[tid], s_cnt[tid]) : 0;
     __syncthreads();
-    if (owner >= 0) {
-        const int64_t pos = (int64_t)s_base[owner] + rank_in_block;
+#pragma unroll
+    for (int q = 0; q < kSendPerThread; ++q) {
+        if (owner[q] >= 0) {
+            const uint32_t slot = s_off[owner[q]] + local_rank[q];
+            s_fp[slot] = key[q];
+            s_idx[slot] = (uint32_t)(q * OB2_BLOCK + tid);
+        }
+    }
+    __syncthreads();
+    const uint32_t total = s_off[world - 1] + s_cnt[world - 1];
+    for (uint32_t t = tid; t < total; t += OB2_BLOCK) {
+        int o = 0;
+        while (o + 1 < world && t >= s_off[o + 1]) ++o;           // which owner's run holds staged entry t
+        const int64_t pos = (int64_t)s_base[o] + (t - s_off[o]);
         if (pos < cap) {
-            char *dst = peers->base[owner];                       // the OWNER's region: a store over NVLink
-            const int64_t o = (int64_t)rank * cap + pos;          // my lane of its inbox
-            reinterpret_cast<ulonglong2 *>(dst + fp_off)[o] = key;
-            reinterpret_cast<uint32_t *>(dst + key_off)[o] = key_base + (uint32_t)i;
-            out_src[(int64_t)owner * cap + pos] = (uint32_t)i;
+            char *dst = peers->base[o];                            // the OWNER's region: stores over NVLink
+            const int64_t lane = (int64_t)rank * cap + pos;        // my lane of its inbox
+            const uint32_t local = (uint32_t)(tile0 + s_idx[t]);
+            reinterpret_cast<ulonglong2 *>(dst + fp_off)[lane] = s_fp[t];
+            reinterpret_cast<uint32_t *>(dst + key_off)[lane] = key_base + local;
+            out_src[(int64_t)o * cap + pos] = local;
         }
     }
 }
@@ -119,25 +157,22 @@ xchg_pad_kernel(int64_t cap, const uint32_t *__restrict__ cnt, uint64_t *__restr
         reinterpret_cast<ulonglong2 *>(inbox_fp)[(int64_t)src * cap + p] = make_ulonglong2(0, 0);
 }
 
-// owner side: hand every verdict back to the rank that sent the entry
+// source side: PULL the verdicts of what I sent to owner `blockIdx.y` out of that owner's
+// region (16 verdicts per 128-bit load over NVLink) and scatter them into my keep mask
 __global__ void __launch_bounds__(OB2_BLOCK)
-xchg_return_kernel(int rank, int64_t cap, const uint32_t *__restrict__ cnt, const uint8_t *__restrict__ verdict,
-                   const PeerTable *__restrict__ peers, size_t verdict_off) {
-    const int src = blockIdx.y;
-    const int64_t used = min((int64_t)cnt[src], cap);
-    uint8_t *dst = reinterpret_cast<uint8_t *>(peers->base[src] + verdict_off) + (int64_t)rank * cap;
-    for (int64_t p = (int64_t)blockIdx.x * OB2_BLOCK + threadIdx.x; p < used; p += (int64_t)gridDim.x * OB2_BLOCK)
-        dst[p] = verdict[(int64_t)src * cap + p];
-}
-
-// source side: verdicts of what I sent to owner `blockIdx.y` -> my keep mask
-__global__ void __launch_bounds__(OB2_BLOCK)
-xchg_collect_kernel(int64_t cap, const uint32_t *__restrict__ send_cnt, const uint32_t *__restrict__ out_src,
-                    const uint8_t *__restrict__ verdict_in, uint8_t *__restrict__ keep) {
+xchg_collect_kernel(int rank, int64_t cap, const uint32_t *__restrict__ send_cnt, const uint32_t *__restrict__ out_src,
+                    const PeerTable *__restrict__ peers, size_t verdict_off, uint8_t *__restrict__ keep) {
     const int owner = blockIdx.y;
     const int64_t used = min((int64_t)send_cnt[owner], cap);
-    for (int64_t p = (int64_t)blockIdx.x * OB2_BLOCK + threadIdx.x; p < used; p += (int64_t)gridDim.x * OB2_BLOCK)
-        keep[out_src[(int64_t)owner * cap + p]] = verdict_in[(int64_t)owner * cap + p];
+    const uint8_t *src = reinterpret_cast<const uint8_t *>(peers->base[owner] + verdict_off) + (int64_t)rank * cap;
+    const uint32_t *idx = out_src + (int64_t)owner * cap;
+    for (int64_t p0 = ((int64_t)blockIdx.x * OB2_BLOCK + threadIdx.x) * 16; p0 < used; p0 += (int64_t)gridDim.x * OB2_BLOCK * 16) {
+        const uint4 v = *reinterpret_cast<const uint4 *>(src + p0);   // cap is a multiple of 16: aligned
+        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int q = 0; q < 16; ++q)
+            if (p0 + q < used) keep[idx[p0 + q]] = (uint8_t)((w[q >> 2] >> (8 * (q & 3))) & 0xFFu);
+    }
 }
 
 int upload_peers(ob2_xchg *x) {
@@ -177,6 +212,7 @@ extern "C" int ob2_xchg_create(int32_t rank, int32_t world, int64_t cap, ob2_xch
     }
     x->rank = rank;
     x->world = world;
+    cap = (cap + 15) / 16 * 16;  // verdict lanes are read back 16 bytes at a time
     x->cap = cap;
     x->lay = region_layout(world, cap);
     x->peers_ready = false;
@@ -192,7 +228,6 @@ extern "C" int ob2_xchg_create(int32_t rank, int32_t world, int64_t cap, ob2_xch
     if (rc == OB2_OK) rc = ob2_check_cuda(cudaMalloc(&x->out_src, lanes * 4), "cudaMalloc(out_src)");
     if (rc == OB2_OK) rc = ob2_check_cuda(cudaMalloc(&x->send_cnt, 256), "cudaMalloc(send_cnt)");
     if (rc == OB2_OK) rc = ob2_check_cuda(cudaMalloc(&x->scratch, lanes * 4), "cudaMalloc(scratch)");
-    if (rc == OB2_OK) rc = ob2_check_cuda(cudaMalloc(&x->verdict, lanes), "cudaMalloc(verdict)");
     if (rc != OB2_OK) {
         ob2_xchg_destroy(x);
         return rc;
@@ -216,7 +251,6 @@ extern "C" void ob2_xchg_destroy(ob2_xchg *x) {
     if (x->out_src) cudaFree(x->out_src);
     if (x->send_cnt) cudaFree(x->send_cnt);
     if (x->scratch) cudaFree(x->scratch);
-    if (x->verdict) cudaFree(x->verdict);
     delete x;
 }
 
@@ -272,7 +306,7 @@ extern "C" int ob2_xchg_send(ob2_xchg *x, int64_t n, const uint64_t *fp, uint32_
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     OB2_CUDA(cudaMemsetAsync(x->send_cnt, 0, sizeof(uint32_t) * x->world, st));
     if (n > 0) {
-        const int64_t blocks = (n + OB2_BLOCK - 1) / OB2_BLOCK;
+        const int64_t blocks = (n + kSendTile - 1) / kSendTile;
         xchg_send_kernel<<<(unsigned)blocks, OB2_BLOCK, 0, st>>>(n, fp, key_base, x->rank, x->world, x->cap, x->d_peers,
                                                                   x->lay.fp_off, x->lay.key_off, x->out_src, x->send_cnt);
         rc = ob2_check_cuda(cudaGetLastError(), "xchg_send_kernel launch");
@@ -299,10 +333,9 @@ extern "C" int ob2_xchg_dedup(ob2_xchg *x, ob2_set *set, int32_t insert_only, vo
     if (rc != OB2_OK) return rc;
     const int64_t lanes = (int64_t)x->world * x->cap;
     if (insert_only) return ob2_set_insert(set, lanes, inbox_fp, stream);
-    rc = ob2_set_dedup(set, lanes, inbox_fp, inbox_key, x->scratch, x->verdict, stream);
-    if (rc != OB2_OK) return rc;
-    xchg_return_kernel<<<grid, OB2_BLOCK, 0, st>>>(x->rank, x->cap, cnt, x->verdict, x->d_peers, x->lay.verdict_off);
-    return ob2_check_cuda(cudaGetLastError(), "xchg_return_kernel launch");
+    // verdicts stay in MY region, lane by source; the sources pull them (ob2_xchg_collect)
+    return ob2_set_dedup(set, lanes, inbox_fp, inbox_key, x->scratch,
+                         reinterpret_cast<uint8_t *>(x->region + x->lay.verdict_off), stream);
 }
 
 extern "C" int ob2_xchg_collect(ob2_xchg *x, int64_t n, uint8_t *keep, void *stream) {
@@ -314,9 +347,9 @@ extern "C" int ob2_xchg_collect(ob2_xchg *x, int64_t n, uint8_t *keep, void *str
     }
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     OB2_CUDA(cudaMemsetAsync(keep, 0, (size_t)n, st));     // padding entries and bucket overflow stay 0
-    const uint8_t *verdict_in = reinterpret_cast<const uint8_t *>(x->region + x->lay.verdict_off);
-    const dim3 grid(lane_blocks(x->cap), (unsigned)x->world);
-    xchg_collect_kernel<<<grid, OB2_BLOCK, 0, st>>>(x->cap, x->send_cnt, x->out_src, verdict_in, keep);
+    const dim3 grid(lane_blocks((x->cap + 15) / 16), (unsigned)x->world);
+    xchg_collect_kernel<<<grid, OB2_BLOCK, 0, st>>>(x->rank, x->cap, x->send_cnt, x->out_src, x->d_peers,
+                                                    x->lay.verdict_off, keep);
     return ob2_check_cuda(cudaGetLastError(), "xchg_collect_kernel launch");
 }
 
