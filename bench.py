@@ -53,8 +53,9 @@ def parse_args():
     ap.add_argument('--e2e-steps', type=int, default=4)
     ap.add_argument('--unfused', action='store_true', help='sample and transform as two kernels')
     ap.add_argument('--serial', action='store_true', help='no stream pipeline: one stream, kernels back to back')
-    ap.add_argument('--exchange', default='nccl', choices=['nccl', 'peer'],
-                    help='multi-GPU dedup exchange: NCCL all-to-all, or peer-memory stores from inside the kernels')
+    ap.add_argument('--exchange', default='auto', choices=['auto', 'nccl', 'peer'],
+                    help='multi-GPU dedup exchange: peer-memory stores from inside the kernels, NCCL all-to-all, '
+                         'or auto (peer where the ranks can map each other, else NCCL)')
     return ap.parse_args()
 
 
@@ -327,11 +328,11 @@ def run_b200(args):
     H = args.history
     cap_rows = H + int(0.92 * n) * total_steps + n
     history = TrialHistory(compiled, n_slots=table_slots_for(cap_rows, load=0.75))
-    if world > 1 and args.exchange == 'peer':
-        from orion_b200.dist import PeerShardedHistory
-        sharded = PeerShardedHistory(history, max_n=n)      # kernels store straight into the owners' HBM
-    else:
-        sharded = ShardedHistory(history, device=dev)       # NCCL all-to-all
+    # 'auto': peer-memory inboxes (kernels store straight into the owners' HBM over NVLink) where the
+    # ranks can map each other's memory, NCCL all-to-all otherwise
+    from orion_b200.dist import PeerShardedHistory, make_sharded_history
+    sharded = make_sharded_history(history, max_n=n, exchange=args.exchange)
+    peer_exchange = isinstance(sharded, PeerShardedHistory)
     chunk = n
     hb = compiled.empty_columns(chunk)
     done = 0
@@ -364,7 +365,7 @@ def run_b200(args):
     batch, tbatch, back = pipe.slots[0].batch, pipe.slots[0].tbatch, pipe.slots[0].back
     fused = not args.unfused
     # extra kernels of mine per step for the exchange: NCCL path bucket+pad+scatter; peer path send+counts+pad+return+collect
-    exchange_launches = 0 if world == 1 else (5 if args.exchange == 'peer' else 3)
+    exchange_launches = 0 if world == 1 else (4 if peer_exchange else 3)
     kernel_names = ['sample+transform', 'reverse', 'dedup'] if fused else ['sample', 'transform', 'reverse', 'dedup']
     ev = [[torch.cuda.Event(enable_timing=True) for _ in range(len(kernel_names) + 1)] for _ in range(K)]
     launches = [0]
@@ -462,7 +463,7 @@ def run_b200(args):
         mask_ok = bool(batch.mask[:n].all().item())
         round_trip_ok = bool(torch.equal(back.buf, batch.buf))
     if world > 1:        # did any (source, owner) lane overflow during the run?
-        sharded.check_overflow() if args.exchange == 'peer' else sharded.check_overflow(n)
+        sharded.check_overflow() if peer_exchange else sharded.check_overflow(n)
     hist_rows1 = len(history)
 
     per_kernel_ms = {}
@@ -589,6 +590,10 @@ def run_b200(args):
         "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": workload_config(args, world),
         "roofline": {"bound": "hbm", "kernel": dominant, "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                     # the yard-stick counts the 448 B/candidate re-read that fusing transform into the
+                     # sampler removes; measured DRAM traffic (ncu, profiles/traffic.json) over the same time:
+                     "traffic_frac": (traffic * n / 12_500_000 / (per_kernel_ms[dominant] * 1e-3) / 1e9 / peak
+                                      if traffic else None),
                      "how": ("CUDA events around each kernel over K serial steps run right after the timed region "
                              "(inside it kernels of adjacent steps overlap; those contended durations are in "
                              "kernels_in_timed_region_ms)" if pipelined else
@@ -607,6 +612,8 @@ def run_b200(args):
                    "reverse_of_transform_is_identity": round_trip_ok,
                    "history_rows_before": hist_rows0, "history_rows_after": hist_rows1},
     }
+    line["config"]["exchange"] = ("none (1 GPU)" if world == 1 else
+                                  "peer-memory inboxes over CUDA IPC (ob2_xchg_*)" if peer_exchange else "NCCL all-to-all")
     if not args.no_cpu_baseline and world == 1:
         procs = host_cores()
         n_per_proc = 200000

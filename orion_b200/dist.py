@@ -214,6 +214,25 @@ class PeerExchange(object):
         return list(out)
 
 
+class PeerExchangeUnavailable(RuntimeError):
+    """The ranks cannot map each other's inboxes (raised on EVERY rank together)."""
+
+
+def make_sharded_history(history, max_n, exchange='auto', group=None):
+    """The sharded history for this process group: ``'peer'`` (peer-memory
+    inboxes), ``'nccl'`` (all-to-all), or ``'auto'`` = peer where the ranks can
+    map each other's memory, NCCL otherwise.  Collective: call on every rank."""
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    if world == 1 or exchange == 'nccl':
+        return ShardedHistory(history, group=group)
+    try:
+        return PeerShardedHistory(history, max_n, group=group)
+    except PeerExchangeUnavailable:
+        if exchange == 'peer':
+            raise
+        return ShardedHistory(history, group=group)
+
+
 class PeerShardedHistory(object):
     """Sharded dedup whose exchange runs over peer memory (NVLink stores from
     inside the kernels) instead of NCCL all-to-alls; same results as
@@ -234,8 +253,16 @@ class PeerShardedHistory(object):
             mine = torch.tensor(list(self.xchg.ipc_handle()), dtype=torch.uint8, device=self.device)
             everyone = [torch.empty(64, dtype=torch.uint8, device=self.device) for _ in range(self.world)]
             dist.all_gather(everyone, mine, group=group)
-            self.xchg.open_peers([bytes(t.cpu().tolist()) for t in everyone])
-            dist.barrier(group=group)
+            error = None
+            try:
+                self.xchg.open_peers([bytes(t.cpu().tolist()) for t in everyone])
+            except _lib.Ob2Error as exc:       # no peer access / IPC between these processes
+                error = exc
+            # every rank must reach the same conclusion, or the next collective deadlocks
+            ok = torch.tensor([0 if error else 1], dtype=torch.int32, device=self.device)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
+            if int(ok.item()) == 0:
+                raise PeerExchangeUnavailable(str(error) if error else "a peer rank could not map the inboxes")
 
     def _barrier(self):
         if self.world > 1:
