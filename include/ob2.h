@@ -192,6 +192,16 @@ int ob2_set_dedup_static(ob2_set *set, int64_t n, const uint64_t *fp, const uint
                          uint8_t *keep, void *stream);
 int ob2_set_probe(const ob2_set *set, int64_t n, const uint64_t *fp, uint8_t *found,
                   void *stream);
+/* Table growth: move every fingerprint of `src` into `dst`, a freshly created
+ * (larger) set; they count as history for later dedup calls.  Synchronises
+ * `stream`.  The reference rebuilds algorithm state by re-observing stored
+ * trials (src/orion/core/worker/experiment.py:230-247); this avoids that. */
+int ob2_set_rehash(const ob2_set *src, ob2_set *dst, void *stream);
+/* Snapshot (checkpoint / resume): write the stored fingerprints, in no
+ * particular order, to out_fp[max_out][2]; *n_out (device u64) receives their
+ * number (entries beyond max_out are counted but not written). */
+int ob2_set_export(const ob2_set *set, uint64_t max_out, uint64_t *out_fp, uint64_t *n_out,
+                   void *stream);
 /* number of distinct fingerprints stored; synchronises `stream` */
 int ob2_set_count(const ob2_set *set, uint64_t *count, void *stream);
 

@@ -71,6 +71,8 @@ SIGNATURES = {
     'ob2_set_dedup': (ctypes.c_int, [_vp, _i64, _vp, _vp, _vp, _vp, _vp]),
     'ob2_set_dedup_static': (ctypes.c_int, [_vp, _i64, _vp, _vp, _vp, _vp]),
     'ob2_set_probe': (ctypes.c_int, [_vp, _i64, _vp, _vp, _vp]),
+    'ob2_set_rehash': (ctypes.c_int, [_vp, _vp, _vp]),
+    'ob2_set_export': (ctypes.c_int, [_vp, _u64, _vp, _vp, _vp]),
     'ob2_set_count': (ctypes.c_int, [_vp, ctypes.POINTER(_u64), _vp]),
     'ob2_compact_scratch_bytes': (_i64, [_i64]),
     'ob2_compact': (ctypes.c_int, [_vp, _i64, _i64, _vp, _vp, _i32, _i64, _vp, _vp, _vp, _vp]),

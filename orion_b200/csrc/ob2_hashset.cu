@@ -548,6 +548,87 @@ extern "C" int ob2_set_probe(const ob2_set *set, int64_t n, const uint64_t *fp, 
     return ob2_check_cuda(cudaGetLastError(), "set_probe_kernel launch");
 }
 
+namespace {
+
+// table growth: every stored key moves to the new table as history
+__global__ void __launch_bounds__(OB2_BLOCK)
+set_rehash_kernel(const SetSlot *__restrict__ old_slots, uint64_t old_n, SetHeader *hdr, SetSlot *slots, uint64_t mask) {
+    const uint64_t i = (uint64_t)blockIdx.x * OB2_BLOCK + threadIdx.x;
+    bool inserted = false;
+    if (i < old_n) {
+        const ulonglong2 key = *reinterpret_cast<const ulonglong2 *>(old_slots + i);
+        if (key.x != 0) {
+            uint64_t pos;
+            const int r = find_or_insert(slots, mask, key.x, key.y, pos);
+            inserted = r == INSERTED;
+            if (inserted) slots[pos].born = OB2_BORN_HISTORY;
+            if (r == OVERFLOW) hdr->overflow = 1;
+        }
+    }
+    warp_count_add(&hdr->count, inserted);
+}
+
+// snapshot: the stored fingerprints, in no particular order
+__global__ void __launch_bounds__(OB2_BLOCK)
+set_export_kernel(const SetSlot *__restrict__ slots, uint64_t n_slots, uint64_t max_out, uint64_t *__restrict__ out,
+                  unsigned long long *__restrict__ n_out) {
+    const uint64_t i = (uint64_t)blockIdx.x * OB2_BLOCK + threadIdx.x;
+    ulonglong2 key = make_ulonglong2(0, 0);
+    if (i < n_slots) key = *reinterpret_cast<const ulonglong2 *>(slots + i);
+    const bool live = key.x != 0;
+    const unsigned ballot = __ballot_sync(0xFFFFFFFFu, live);
+    if (ballot == 0) return;
+    const unsigned lane = threadIdx.x & 31, leader = __ffs(ballot) - 1;
+    unsigned long long base = 0;
+    if (lane == leader) base = atomicAdd(n_out, (unsigned long long)__popc(ballot));
+    base = __shfl_sync(0xFFFFFFFFu, base, leader);
+    if (live) {
+        const unsigned long long at = base + __popc(ballot & ((1u << lane) - 1));
+        if (at < max_out) reinterpret_cast<ulonglong2 *>(out)[at] = key;
+    }
+}
+
+}  // namespace
+
+extern "C" int ob2_set_rehash(const ob2_set *src, ob2_set *dst, void *stream) {
+    if (src == nullptr || dst == nullptr || src == dst) {
+        ob2_set_error("ob2_set_rehash: bad arguments");
+        return OB2_EINVAL;
+    }
+    if (dst->upper_bound != 0) {
+        ob2_set_error("ob2_set_rehash: the destination set must be freshly created");
+        return OB2_EINVAL;
+    }
+    unsigned blocks;
+    int rc = grid_for((int64_t)src->n_slots, &blocks);
+    if (rc != OB2_OK) return rc;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    set_rehash_kernel<<<blocks, OB2_BLOCK, 0, st>>>(src->slots, src->n_slots, dst->header, dst->slots, dst->n_slots - 1);
+    rc = ob2_check_cuda(cudaGetLastError(), "set_rehash_kernel launch");
+    if (rc != OB2_OK) return rc;
+    unsigned long long moved = 0;
+    OB2_CUDA(cudaMemcpyAsync(&moved, &dst->header->count, sizeof(moved), cudaMemcpyDeviceToHost, st));
+    OB2_CUDA(cudaStreamSynchronize(st));
+    dst->upper_bound = moved;
+    dst->epoch = src->epoch;  // later dedup calls keep distinguishing "this call" from everything before
+    return OB2_OK;
+}
+
+extern "C" int ob2_set_export(const ob2_set *set, uint64_t max_out, uint64_t *out_fp, uint64_t *n_out, void *stream) {
+    if (set == nullptr || n_out == nullptr || (max_out > 0 && out_fp == nullptr)) {
+        ob2_set_error("ob2_set_export: bad arguments");
+        return OB2_EINVAL;
+    }
+    unsigned blocks;
+    int rc = grid_for((int64_t)set->n_slots, &blocks);
+    if (rc != OB2_OK) return rc;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    OB2_CUDA(cudaMemsetAsync(n_out, 0, sizeof(uint64_t), st));
+    set_export_kernel<<<blocks, OB2_BLOCK, 0, st>>>(set->slots, set->n_slots, max_out, out_fp,
+                                                    reinterpret_cast<unsigned long long *>(n_out));
+    return ob2_check_cuda(cudaGetLastError(), "set_export_kernel launch");
+}
+
 extern "C" int ob2_set_count(const ob2_set *set, uint64_t *count, void *stream) {
     if (set == nullptr || count == nullptr) {
         ob2_set_error("ob2_set_count: bad arguments");

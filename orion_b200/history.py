@@ -26,19 +26,61 @@ def table_slots_for(capacity, load=0.5):
 class TrialHistory(object):
     """Hash set of row fingerprints in HBM + the dedup operations on it."""
 
-    def __init__(self, space, capacity=1 << 20, n_slots=None, device=None):
+    def __init__(self, space, capacity=1 << 20, n_slots=None, device=None, auto_grow=False):
         self.lib = _lib.load()
         self.space = space
         self.compiled = space.compiled() if hasattr(space, 'compiled') else space
         self.device = self.compiled.device if device is None else torch.device(device)
+        self.auto_grow = auto_grow
         self.n_slots = int(n_slots) if n_slots else table_slots_for(capacity)
-        nbytes = _lib.SET_HEADER_BYTES + self.n_slots * _lib.SET_SLOT_BYTES
-        self.table = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
-        assert self.table.data_ptr() % 256 == 0
-        handle = ctypes.c_void_p()
-        _lib.check(self.lib.ob2_set_create(self.table.data_ptr(), self.n_slots, self._stream(), ctypes.byref(handle)))
-        self.handle = handle
+        self.table, self.handle = self._new_table(self.n_slots)
         self._scratch = None
+
+    def _new_table(self, n_slots):
+        nbytes = _lib.SET_HEADER_BYTES + n_slots * _lib.SET_SLOT_BYTES
+        table = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
+        assert table.data_ptr() % 256 == 0
+        handle = ctypes.c_void_p()
+        _lib.check(self.lib.ob2_set_create(table.data_ptr(), n_slots, self._stream(), ctypes.byref(handle)))
+        return table, handle
+
+    def grow(self, n_slots=None):
+        """Move the history into a table of ``n_slots`` (default: twice as many);
+        everything stored so far stays a duplicate for future batches."""
+        n_slots = int(n_slots) if n_slots else 2 * self.n_slots
+        if n_slots <= self.n_slots or n_slots & (n_slots - 1):
+            raise ValueError("grow() needs a larger power-of-two slot count")
+        table, handle = self._new_table(n_slots)
+        _lib.check(self.lib.ob2_set_rehash(self.handle, handle, self._stream()))
+        self.lib.ob2_set_destroy(self.handle)
+        self.table, self.handle, self.n_slots = table, handle, n_slots
+
+    def _guarded(self, call):
+        """Run a set operation; with ``auto_grow`` a full table is doubled and
+        the operation retried (the library refuses BEFORE touching the table)."""
+        while True:
+            rc = call()
+            if rc == -4 and self.auto_grow and self.n_slots < (1 << 31):      # OB2_ENOMEM: set full
+                self.grow()
+                continue
+            _lib.check(rc)
+            return
+
+    # -- snapshot / restore ----------------------------------------------------
+    def state_dict(self):
+        """The stored fingerprints as a host tensor (int64 [count][2]): enough
+        to rebuild the history in a table of any size."""
+        count = len(self)
+        out = torch.empty((max(count, 1), 2), dtype=torch.int64, device=self.device)
+        n_out = torch.zeros(1, dtype=torch.int64, device=self.device)
+        _lib.check(self.lib.ob2_set_export(self.handle, count, out.data_ptr(), n_out.data_ptr(), self._stream()))
+        assert int(n_out.item()) == count
+        return {'fingerprints': out[:count].cpu(), 'n_slots': self.n_slots}
+
+    def load_state_dict(self, state):
+        fp = state['fingerprints'].to(self.device)
+        if fp.shape[0]:
+            self.insert_fingerprints(fp.contiguous())
 
     def __del__(self):
         handle = getattr(self, 'handle', None)
@@ -61,7 +103,7 @@ class TrialHistory(object):
     def insert_fingerprints(self, fp, n=None):
         """History load: ``fp`` is an int64 [m][2] device tensor."""
         n = fp.shape[0] if n is None else n
-        _lib.check(self.lib.ob2_set_insert(self.handle, n, fp.data_ptr(), self._stream()))
+        self._guarded(lambda: self.lib.ob2_set_insert(self.handle, n, fp.data_ptr(), self._stream()))
 
     def dedup_fingerprints(self, fp, n=None, order=None, keep=None):
         """uint8 keep mask for ``fp`` (first occurrence by ``order`` wins)."""
@@ -69,9 +111,9 @@ class TrialHistory(object):
         if keep is None:
             keep = torch.empty(fp.shape[0], dtype=torch.uint8, device=self.device)
         scratch = self._scratch_for(n)
-        _lib.check(self.lib.ob2_set_dedup(self.handle, n, fp.data_ptr(),
-                                          order.data_ptr() if order is not None else None,
-                                          scratch.data_ptr(), keep.data_ptr(), self._stream()))
+        self._guarded(lambda: self.lib.ob2_set_dedup(self.handle, n, fp.data_ptr(),
+                                                     order.data_ptr() if order is not None else None,
+                                                     scratch.data_ptr(), keep.data_ptr(), self._stream()))
         return keep
 
     def dedup_fingerprints_static(self, fp, keep, n=None, order=None):
