@@ -120,7 +120,8 @@ __device__ __forceinline__ bool redraw_dim(const ob2_slot_desc *s_slots, int s_l
 template <bool PHILOX, bool WITH_FP, bool WITH_T, bool EXT>
 __global__ void __launch_bounds__(OB2_BLOCK, 4)
 sample_kernel(const ob2_slot_desc *__restrict__ g_slots, int n_slots, const double *__restrict__ g_cdf,
-              int cdf_len, int64_t n, int64_t n_stride, uint32_t k0, uint32_t k1, uint32_t pm0, uint32_t pm1,
+              int cdf_len, int64_t n, int64_t n_stride, int64_t stride4, int64_t stride8, uint32_t k0, uint32_t k1,
+              uint32_t pm0, uint32_t pm1,
               uint64_t base_index, const uint64_t *__restrict__ index, const double *__restrict__ U,
               char *__restrict__ cols, char *__restrict__ tcols, uint8_t *__restrict__ mask,
               uint64_t *__restrict__ fp, uint32_t *__restrict__ n_failed) {
@@ -143,7 +144,8 @@ sample_kernel(const ob2_slot_desc *__restrict__ g_slots, int n_slots, const doub
     bool ok0 = true, ok1 = true;    // current dimension
     bool all0 = true, all1 = true;  // whole candidate
     Philox4 r0{0, 0, 0, 0}, r1{0, 0, 0, 0};
-    const int64_t stride4 = 4 * n_stride, stride8 = 8 * n_stride;
+    // stride4 / stride8 = 4 * n_stride / 8 * n_stride arrive as kernel parameters: the pointer bumps then
+    // take them straight from the constant bank instead of re-deriving them every slot
     char *col = cols + i0 * 8;                          // running pointers: element i0 of the current column
     char *tcol = WITH_T ? tcols + i0 * 8 : nullptr;     // (a 4-byte column is addressed at half the offset)
     const double *ucol = PHILOX ? nullptr : U + i0;
@@ -332,7 +334,7 @@ int launch_one(const SampleArgs &a, unsigned blocks) {
     int rc = prepare_smem(kern, sp->smem_bytes);
     if (rc != OB2_OK) return rc;
     kern<<<blocks, OB2_BLOCK, sp->smem_bytes, static_cast<cudaStream_t>(a.stream)>>>(
-        sp->d_slots, sp->n_slots, sp->d_cdf, sp->cdf_len, a.n, a.n_stride, (uint32_t)a.seed,
+        sp->d_slots, sp->n_slots, sp->d_cdf, sp->cdf_len, a.n, a.n_stride, 4 * a.n_stride, 8 * a.n_stride, (uint32_t)a.seed,
         (uint32_t)(a.seed >> 32), 0xD2511F53u, 0xCD9E8D57u, a.base_index, a.index, a.U, (char *)a.cols, (char *)a.tcols, a.mask, a.fp,
         a.n_failed);
     return ob2_check_cuda(cudaGetLastError(), "sample_kernel launch");
