@@ -321,6 +321,15 @@ int check_set_args(const ob2_set *set, int64_t n, const void *fp) {
         ob2_set_error("hash set: at most 2^32 - 2 entries per call");
         return OB2_ETOOBIG;
     }
+    if ((reinterpret_cast<uintptr_t>(fp) & 15) != 0) {
+        ob2_set_error("hash set: the fingerprint array must be 16-byte aligned (it is read as 128-bit words)");
+        return OB2_EINVAL;
+    }
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev != set->device) {
+        ob2_set_error("current device %d is not the device %d this set lives on", dev, set->device);
+        return OB2_EINVAL;
+    }
     return OB2_OK;
 }
 

@@ -41,6 +41,11 @@ static inline int ob2_check_batch(const ob2_space *sp, int64_t n, int64_t n_stri
                       (long long)n, (long long)n_stride);
         return OB2_EINVAL;
     }
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev != sp->device) {  // its tables live on sp->device
+        ob2_set_error("current device %d is not the device %d this space was compiled on", dev, sp->device);
+        return OB2_EINVAL;
+    }
     return OB2_OK;
 }
 
