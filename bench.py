@@ -52,6 +52,8 @@ def parse_args():
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--e2e-steps', type=int, default=4)
     ap.add_argument('--unfused', action='store_true', help='sample and transform as two kernels')
+    ap.add_argument('--fp-in-sampler', action='store_true',
+                    help='compute the row fingerprints in the sampler instead of the reverse kernel')
     ap.add_argument('--serial', action='store_true', help='no stream pipeline: one stream, kernels back to back')
     ap.add_argument('--exchange', default='auto', choices=['auto', 'nccl', 'peer'],
                     help='multi-GPU dedup exchange: peer-memory stores from inside the kernels, NCCL all-to-all, '
@@ -361,20 +363,23 @@ def run_b200(args):
     index_dev = [step_index(s) for s in range(W + K)]
     # two buffer sets (28 GB each) serve the pipeline, the serial pass and the e2e leg
     from orion_b200.pipeline import CandidatePipeline
-    pipe = CandidatePipeline(compiled, sharded, n, depth=2)
+    pipe = CandidatePipeline(compiled, sharded, n, depth=2,
+                             fingerprint_in='sample' if args.fp_in_sampler else 'reverse')
     batch, tbatch, back = pipe.slots[0].batch, pipe.slots[0].tbatch, pipe.slots[0].back
     fused = not args.unfused
     # extra kernels of mine per step for the exchange: NCCL path bucket+pad+scatter; peer path send+counts+pad+return+collect
     exchange_launches = 0 if world == 1 else (4 if peer_exchange else 3)
-    kernel_names = ['sample+transform', 'reverse', 'dedup'] if fused else ['sample', 'transform', 'reverse', 'dedup']
+    fp_in_reverse = fused and not args.fp_in_sampler     # fingerprints computed by the reverse kernel (default)
+    rev = 'reverse+fingerprint' if fp_in_reverse else 'reverse'
+    kernel_names = ['sample+transform', rev, 'dedup'] if fused else ['sample', 'transform', rev, 'dedup']
     ev = [[torch.cuda.Event(enable_timing=True) for _ in range(len(kernel_names) + 1)] for _ in range(K)]
     launches = [0]
 
     def one_step(step, events=None):
         j = 1
         if fused:       # TransformedSpace.sample: one kernel draws and transforms
-            compiled.sample(n, SEED, index=index_dev[step], with_mask=True, with_fingerprint=True, out=batch,
-                            transformed_out=tbatch)
+            compiled.sample(n, SEED, index=index_dev[step], with_mask=True, with_fingerprint=not fp_in_reverse,
+                            out=batch, transformed_out=tbatch)
         else:
             compiled.sample(n, SEED, index=index_dev[step], with_mask=True, with_fingerprint=True, out=batch)
             if events:
@@ -383,10 +388,10 @@ def run_b200(args):
             compiled.transform(batch, out=tbatch)
         if events:
             events[j].record()
-        compiled.reverse(tbatch, out=back)
+        compiled.reverse(tbatch, out=back, with_fingerprint=fp_in_reverse)
         if events:
             events[j + 1].record()
-        sharded.dedup(batch.fp, n, per_rank_n=n, keep=batch.keep, check=False)
+        sharded.dedup(back.fp if fp_in_reverse else batch.fp, n, per_rank_n=n, keep=batch.keep, check=False)
         if events:
             events[j + 2].record()
         launches[0] += (4 if fused else 5) + exchange_launches
@@ -571,7 +576,8 @@ def run_b200(args):
     else:
         peak, peak_src = 6650.0, "B200_PROFILING.md fallback 6.65 TB/s (of fallback)"
     algo_bytes = {'sample': BYTES_SAMPLE, 'transform': BYTES_TRANSFORM, 'reverse': BYTES_REVERSE, 'dedup': BYTES_DEDUP,
-                  'sample+transform': BYTES_SAMPLE + BYTES_TRANSFORM}
+                  'sample+transform': BYTES_SAMPLE + BYTES_TRANSFORM,
+                  'reverse+fingerprint': BYTES_REVERSE}
     algo_bytes = {k: algo_bytes[k] for k in kernel_names}
     dominant = max(per_kernel_ms, key=per_kernel_ms.get)
     achieved = algo_bytes[dominant] * n / (per_kernel_ms[dominant] * 1e-3) / 1e9

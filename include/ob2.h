@@ -144,6 +144,13 @@ int ob2_transform(const ob2_space *space, int64_t n, int64_t n_stride, const voi
                   void *tcols, void *stream);
 int ob2_reverse(const ob2_space *space, int64_t n, int64_t n_stride, const void *tcols,
                 void *cols, void *stream);
+/* ob2_reverse that also fingerprints the rows it writes (fp[n_stride][2]), i.e.
+ * the candidates as they are handed out.  The reverse is bandwidth bound with
+ * idle issue slots, so this is where the dedup fingerprint is cheapest; under
+ * the 'real' / 'numerical' / None requirements reverse(transform(x)) == x and it
+ * equals the fingerprint ob2_sample would have produced. */
+int ob2_reverse_fingerprint(const ob2_space *space, int64_t n, int64_t n_stride,
+                            const void *tcols, void *cols, uint64_t *fp, void *stream);
 
 /* 128-bit row fingerprint of existing columns (history ingestion); the trial
  * identity the producer dedups on.  No counterpart in the snapshot

@@ -64,6 +64,7 @@ SIGNATURES = {
     'ob2_contains': (ctypes.c_int, [_vp, _i64, _i64, _vp, _i32, _vp, _vp]),
     'ob2_transform': (ctypes.c_int, [_vp, _i64, _i64, _vp, _vp, _vp]),
     'ob2_reverse': (ctypes.c_int, [_vp, _i64, _i64, _vp, _vp, _vp]),
+    'ob2_reverse_fingerprint': (ctypes.c_int, [_vp, _i64, _i64, _vp, _vp, _vp, _vp]),
     'ob2_fingerprint': (ctypes.c_int, [_vp, _i64, _i64, _vp, _vp, _vp]),
     'ob2_set_create': (ctypes.c_int, [_vp, _u64, _vp, ctypes.POINTER(_vp)]),
     'ob2_set_destroy': (None, [_vp]),

@@ -70,18 +70,24 @@ transform_kernel(const ob2_slot_desc *__restrict__ g_slots, int n_slots, int64_t
     }
 }
 
+// WITH_FP: also fingerprint the rows it writes.  reverse is bandwidth bound with ~3/4 of its
+// issue slots idle, so the fingerprint arithmetic (which costs the issue-bound sampler 17 %)
+// rides along for free here.
+template <bool WITH_FP>
 __global__ void __launch_bounds__(OB2_BLOCK)
 reverse_kernel(const ob2_slot_desc *__restrict__ g_slots, int n_slots, int64_t n, int64_t n_stride,
-               const char *__restrict__ tcols, char *__restrict__ cols) {
+               const char *__restrict__ tcols, char *__restrict__ cols, uint64_t *__restrict__ fp) {
     extern __shared__ __align__(16) unsigned char smem[];
     ob2_slot_desc *s_slots = reinterpret_cast<ob2_slot_desc *>(smem);
     ob2_stage_tables(g_slots, n_slots, nullptr, 0, s_slots, nullptr);
     const int64_t i0 = ((int64_t)blockIdx.x * OB2_BLOCK + threadIdx.x) * OB2_CPT;
     if (i0 >= n) return;
+    FpAcc acc0{0, 0}, acc1{0, 0};
     for (int s = 0; s < n_slots; ++s) {
         const ob2_slot_desc &d = s_slots[s];
         const char *src = tcols + (int64_t)d.t_units * n_stride;
         char *dst = cols + (int64_t)d.col_units * n_stride;
+        uint64_t w0, w1;  // the values written, as canonical fingerprint words
         switch (d.t_op) {
             case OB2_OP_ONEHOT: {
                 int c0 = 0, c1 = 0;
@@ -128,18 +134,26 @@ reverse_kernel(const ob2_slot_desc *__restrict__ g_slots, int n_slots, int64_t n
                     }
                 }
                 st_i32x2(reinterpret_cast<int *>(dst) + i0, c0, c1);
+                w0 = (uint64_t)(int64_t)c0;
+                w1 = (uint64_t)(int64_t)c1;
                 break;
             }
             case OB2_OP_QUANTIZE: {  // Quantize.reverse: cast back to float
                 long long q0, q1;
                 ld_i64x2(reinterpret_cast<const long long *>(src) + i0, q0, q1);
-                st_f64x2(reinterpret_cast<double *>(dst) + i0, __ll2double_rn(q0), __ll2double_rn(q1));
+                const double x0 = __ll2double_rn(q0), x1 = __ll2double_rn(q1);
+                st_f64x2(reinterpret_cast<double *>(dst) + i0, x0, x1);
+                w0 = canon_f64(x0);
+                w1 = canon_f64(x1);
                 break;
             }
             case OB2_OP_TO_REAL: {  // Reverse(Quantize).reverse = Quantize.transform
                 double x0, x1;
                 ld_f64x2(reinterpret_cast<const double *>(src) + i0, x0, x1);
-                st_i64x2(reinterpret_cast<long long *>(dst) + i0, quantize(x0, d.t_flags), quantize(x1, d.t_flags));
+                const long long q0 = quantize(x0, d.t_flags), q1 = quantize(x1, d.t_flags);
+                st_i64x2(reinterpret_cast<long long *>(dst) + i0, q0, q1);
+                w0 = (uint64_t)q0;
+                w1 = (uint64_t)q1;
                 break;
             }
             default: {
@@ -147,20 +161,40 @@ reverse_kernel(const ob2_slot_desc *__restrict__ g_slots, int n_slots, int64_t n
                     int c0, c1;
                     ld_i32x2(reinterpret_cast<const int *>(src) + i0, c0, c1);
                     st_i32x2(reinterpret_cast<int *>(dst) + i0, c0, c1);
+                    w0 = (uint64_t)(int64_t)c0;
+                    w1 = (uint64_t)(int64_t)c1;
                 } else {
                     long long q0, q1;
                     ld_i64x2(reinterpret_cast<const long long *>(src) + i0, q0, q1);
                     st_i64x2(reinterpret_cast<long long *>(dst) + i0, q0, q1);
+                    if (d.kind == OB2_KIND_REAL) {
+                        w0 = canon_f64(__longlong_as_double(q0));
+                        w1 = canon_f64(__longlong_as_double(q1));
+                    } else {
+                        w0 = (uint64_t)q0;
+                        w1 = (uint64_t)q1;
+                    }
                 }
                 break;
             }
         }
+        if (WITH_FP) {
+            fp_add(acc0, d, w0);
+            fp_add(acc1, d, w1);
+        }
+    }
+    if (WITH_FP) {
+        uint64_t lo0, hi0, lo1, hi1;
+        fp_finish(acc0, n_slots, lo0, hi0);
+        fp_finish(acc1, n_slots, lo1, hi1);
+        if (i0 + 1 >= n) lo1 = hi1 = 0;  // padding entry
+        st_u64x4(fp + 2 * i0, lo0, hi0, lo1, hi1);
     }
 }
 
-template <typename K>
+template <typename K, typename... Extra>
 int launch_codec(K kernel, const char *what, const ob2_space *sp, int64_t n, int64_t n_stride, const void *in,
-                 void *out, void *stream) {
+                 void *out, void *stream, Extra... extra) {
     int rc = ob2_check_batch(sp, n, n_stride);
     if (rc != OB2_OK) return rc;
     if (in == nullptr || out == nullptr) {
@@ -177,7 +211,7 @@ int launch_codec(K kernel, const char *what, const ob2_space *sp, int64_t n, int
         if (rc != OB2_OK) return rc;
     }
     kernel<<<(unsigned)blocks, OB2_BLOCK, smem, static_cast<cudaStream_t>(stream)>>>(
-        sp->d_slots, sp->n_slots, n, n_stride, (const char *)in, (char *)out);
+        sp->d_slots, sp->n_slots, n, n_stride, (const char *)in, (char *)out, extra...);
     return ob2_check_cuda(cudaGetLastError(), what);
 }
 
@@ -190,5 +224,15 @@ extern "C" int ob2_transform(const ob2_space *space, int64_t n, int64_t n_stride
 
 extern "C" int ob2_reverse(const ob2_space *space, int64_t n, int64_t n_stride, const void *tcols, void *cols,
                            void *stream) {
-    return launch_codec(reverse_kernel, "reverse_kernel", space, n, n_stride, tcols, cols, stream);
+    return launch_codec(reverse_kernel<false>, "reverse_kernel", space, n, n_stride, tcols, cols, stream,
+                        static_cast<uint64_t *>(nullptr));
+}
+
+extern "C" int ob2_reverse_fingerprint(const ob2_space *space, int64_t n, int64_t n_stride, const void *tcols,
+                                       void *cols, uint64_t *fp, void *stream) {
+    if (fp == nullptr) {
+        ob2_set_error("ob2_reverse_fingerprint: null fingerprint buffer");
+        return OB2_EINVAL;
+    }
+    return launch_codec(reverse_kernel<true>, "reverse_kernel", space, n, n_stride, tcols, cols, stream, fp);
 }

@@ -301,12 +301,22 @@ class CompiledSpace(object):
                                           tb.buf.data_ptr(), self._stream()))
         return tb
 
-    def reverse(self, tbatch, out=None):
+    def reverse(self, tbatch, out=None, with_fingerprint=False):
+        """Transformed batch -> original batch.  ``with_fingerprint`` also fills
+        ``out.fp`` with the fingerprints of the rows written (fused into the
+        same bandwidth-bound kernel)."""
         assert tbatch.transformed
         b = out if out is not None else self.empty_columns(tbatch.n)
         assert not b.transformed and b.n_stride == tbatch.n_stride
-        _lib.check(self.lib.ob2_reverse(self.handle, tbatch.n, tbatch.n_stride, tbatch.buf.data_ptr(),
-                                        b.buf.data_ptr(), self._stream()))
+        b.n = tbatch.n
+        if with_fingerprint:
+            if b.fp is None:
+                b.fp = torch.empty((b.n_stride, 2), dtype=torch.int64, device=self.device)
+            _lib.check(self.lib.ob2_reverse_fingerprint(self.handle, tbatch.n, tbatch.n_stride, tbatch.buf.data_ptr(),
+                                                        b.buf.data_ptr(), b.fp.data_ptr(), self._stream()))
+        else:
+            _lib.check(self.lib.ob2_reverse(self.handle, tbatch.n, tbatch.n_stride, tbatch.buf.data_ptr(),
+                                            b.buf.data_ptr(), self._stream()))
         return b
 
     def fingerprint(self, batch):

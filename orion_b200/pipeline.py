@@ -2,13 +2,15 @@
 
 One batch goes through three kernels groups with different limits on a B200:
 
-  A  sample + transform   (``ob2_sample_transform``)  instruction-issue bound
-  B  reverse              (``ob2_reverse``)           HBM bound
-  C  dedup (+ exchange)   (``ob2_set_dedup``, NCCL)   DRAM-latency bound
+  A  sample + transform       (``ob2_sample_transform``)       instruction-issue bound
+  B  reverse + fingerprint    (``ob2_reverse_fingerprint``)    HBM bound
+  C  dedup (+ exchange)       (``ob2_set_dedup``, NCCL / peer)  DRAM-latency bound
 
-B and C only depend on A, not on each other, and A of the next batch depends on
-neither -- so they run on three CUDA streams with events for the true
-dependencies (and for buffer reuse).  With ``depth`` >= 2 buffer sets, A of
+The fingerprint arithmetic costs the issue-bound sampler 17 % but is free in
+the bandwidth-bound reverse, so by default B computes it (over the rows it
+writes: the candidates as they are handed out) and C follows B.  A of the next
+batch depends on neither, so the three groups run on three CUDA streams with
+events for the true dependencies (and for buffer reuse).  With ``depth`` >= 2 buffer sets, A of
 batch k+1 overlaps B and C of batch k: the issue-bound and the bandwidth-bound
 work share the SMs instead of taking turns.
 
@@ -41,7 +43,11 @@ class BatchSlot(object):
 class CandidatePipeline(object):
     """sample+transform -> (reverse || dedup) over a ring of ``depth`` buffer sets."""
 
-    def __init__(self, compiled, history, n, depth=2, timed=False):
+    def __init__(self, compiled, history, n, depth=2, timed=False, fingerprint_in='reverse'):
+        # 'reverse': the fingerprints are computed by the (bandwidth-bound) reverse kernel over the rows it
+        # writes -- the candidates as handed out; 'sample': by the (issue-bound) sampler over its draws
+        assert fingerprint_in in ('reverse', 'sample')
+        self.fp_in_reverse = fingerprint_in == 'reverse'
         self.compiled = compiled
         self.n = n
         # a ShardedHistory / PeerShardedHistory is used as is; a bare TrialHistory is wrapped
@@ -79,7 +85,8 @@ class CandidatePipeline(object):
                 slot.hold = None
             if ev:
                 ev[0].record()
-            c.sample(n, seed, base_index=base_index, index=index, with_mask=True, with_fingerprint=True,
+            c.sample(n, seed, base_index=base_index, index=index, with_mask=True,
+                     with_fingerprint=not self.fp_in_reverse,
                      out=slot.batch, transformed_out=slot.tbatch)
             if ev:
                 ev[1].record()
@@ -88,15 +95,16 @@ class CandidatePipeline(object):
             self.s_reverse.wait_event(slot.sampled)
             if ev:
                 ev[2].record()
-            c.reverse(slot.tbatch, out=slot.back)
+            c.reverse(slot.tbatch, out=slot.back, with_fingerprint=self.fp_in_reverse)
             if ev:
                 ev[3].record()
             slot.reversed.record()
         with torch.cuda.stream(self.s_dedup):
-            self.s_dedup.wait_event(slot.sampled)
+            self.s_dedup.wait_event(slot.reversed if self.fp_in_reverse else slot.sampled)
             if ev:
                 ev[4].record()
-            self.sharded.dedup(slot.batch.fp, n, per_rank_n=n, keep=slot.batch.keep, check=False)
+            fp = slot.back.fp if self.fp_in_reverse else slot.batch.fp
+            self.sharded.dedup(fp, n, per_rank_n=n, keep=slot.batch.keep, check=False)
             if ev:
                 ev[5].record()
             slot.deduped.record()
