@@ -51,6 +51,9 @@ def parse_args():
     ap.add_argument('--history', type=int, default=HISTORY_PER_GPU, help='history rows per GPU')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--e2e-steps', type=int, default=4)
+    ap.add_argument('--staged', action='store_true',
+                    help='sample+transform, reverse+fingerprint and dedup as separate kernels (the path of an '
+                         'algorithm that computes in the transformed space) instead of the one-kernel ob2_suggest')
     ap.add_argument('--unfused', action='store_true', help='sample and transform as two kernels')
     ap.add_argument('--fp-in-sampler', action='store_true',
                     help='compute the row fingerprints in the sampler instead of the reverse kernel')
@@ -321,7 +324,8 @@ def run_b200(args):
 
     n = args.cands
     K, W = args.steps, args.warmup
-    total_steps = 2 * K + W + args.e2e_steps + 2      # timed + serial pass + e2e (+ its warm-up)
+    KS = min(K, 5)                                    # steps of the staged-kernels comparison pass
+    total_steps = 2 * K + KS + W + args.e2e_steps + 2   # timed + serial pass + staged pass + e2e (+ its warm-up)
     space = spaces.mixed64()
     tspace = build_required_space('real', space)
     compiled = tspace.compiled()
@@ -363,8 +367,10 @@ def run_b200(args):
     index_dev = [step_index(s) for s in range(W + K)]
     # two buffer sets (28 GB each) serve the pipeline, the serial pass and the e2e leg
     from orion_b200.pipeline import CandidatePipeline
+    # default: ob2_suggest, ONE kernel for sample -> transform -> reverse -> fingerprint (Random.suggest fast path)
+    one_kernel = not (args.staged or args.unfused or args.fp_in_sampler)
     pipe = CandidatePipeline(compiled, sharded, n, depth=2,
-                             fingerprint_in='sample' if args.fp_in_sampler else 'reverse')
+                             fingerprint_in='suggest' if one_kernel else 'sample' if args.fp_in_sampler else 'reverse')
     batch, tbatch, back = pipe.slots[0].batch, pipe.slots[0].tbatch, pipe.slots[0].back
     fused = not args.unfused
     # extra kernels of mine per step for the exchange: NCCL path bucket+pad+scatter; peer path send+counts+pad+return+collect
@@ -372,11 +378,24 @@ def run_b200(args):
     fp_in_reverse = fused and not args.fp_in_sampler     # fingerprints computed by the reverse kernel (default)
     rev = 'reverse+fingerprint' if fp_in_reverse else 'reverse'
     kernel_names = ['sample+transform', rev, 'dedup'] if fused else ['sample', 'transform', rev, 'dedup']
+    staged_names = list(kernel_names)
+    if one_kernel:
+        kernel_names = ['suggest', 'dedup']
+    step_launches = (3 if one_kernel else 4 if fused else 5) + exchange_launches    # dedup = 2 launches
     ev = [[torch.cuda.Event(enable_timing=True) for _ in range(len(kernel_names) + 1)] for _ in range(K)]
     launches = [0]
 
-    def one_step(step, events=None):
+    def one_step(step, events=None, staged=False):
         j = 1
+        if one_kernel and not staged:
+            compiled.suggest(n, SEED, index=index_dev[step], out=batch, transformed_out=tbatch, back_out=back)
+            if events:
+                events[1].record()
+            sharded.dedup(back.fp, n, per_rank_n=n, keep=batch.keep, check=False)
+            if events:
+                events[2].record()
+            launches[0] += step_launches
+            return
         if fused:       # TransformedSpace.sample: one kernel draws and transforms
             compiled.sample(n, SEED, index=index_dev[step], with_mask=True, with_fingerprint=not fp_in_reverse,
                             out=batch, transformed_out=tbatch)
@@ -431,7 +450,7 @@ def run_b200(args):
         sync_all()
         clock_info = clocks.stop() if rank == 0 else None
         elapsed_ms = max_over_ranks(t_begin.elapsed_time(t_end))
-        timed_launches = K * (4 + exchange_launches)
+        timed_launches = K * step_launches
         contended_ms = pipe.kernel_ms()
         pipe.timed = False
         last_batch, last_back = slot.batch, slot.back
@@ -475,6 +494,24 @@ def run_b200(args):
     for j, name in enumerate(kernel_names):
         per_kernel_ms[name] = sum(ev[s][j].elapsed_time(ev[s][j + 1]) for s in range(K)) / K
 
+    # ---- for comparison: the same K steps through the separate kernels (what an algorithm that works in the
+    # transformed space pays: the transformed columns are read back by reverse), one stream
+    staged_info = None
+    if one_kernel:
+        sev = [[torch.cuda.Event(enable_timing=True) for _ in range(len(staged_names) + 1)] for _ in range(KS)]
+        for s in range(KS):
+            index_dev[W + s] = step_index(W + 2 * K + s)
+        sync_all()
+        for s in range(KS):
+            sev[s][0].record()
+            one_step(W + s, sev[s], staged=True)
+        sync_all()
+        staged_info = {"steps": KS, "ms_per_step": sum(e[0].elapsed_time(e[-1]) for e in sev) / KS,
+                       "kernels_ms": {name: sum(e[j].elapsed_time(e[j + 1]) for e in sev) / KS
+                                      for j, name in enumerate(staged_names)},
+                       "note": "same workload through ob2_sample_transform -> ob2_reverse_fingerprint -> ob2_set_dedup, "
+                               "one stream, run after the timed region"}
+
     # ---- end to end through the public API with host buffers
     e2e = None
     if args.e2e_steps > 0:
@@ -482,7 +519,7 @@ def run_b200(args):
         E = args.e2e_steps
         host_idx = [torch.empty(n, dtype=torch.int64).pin_memory() for _ in range(E + 2)]
         for j, h in enumerate(host_idx):
-            h.copy_(step_index(W + 2 * K + j))
+            h.copy_(step_index(W + 2 * K + KS + j))
         # Survivors only cross PCIe: after dedup the kept rows are gathered into a dense block on
         # the device (ob2_compact) and each column's first n_kept elements are copied to pinned
         # host memory.  Two buffer sets: compaction and copies of step j overlap step j+1.
@@ -561,7 +598,8 @@ def run_b200(args):
                "h2d_bytes_per_step": int(n * 8),
                "d2h_bytes_per_step": int(state['d2h'] // max(E, 1)),
                "steps": args.e2e_steps, "kept_last_step": state['kept'],
-               "api": "CandidatePipeline.submit(counters copied from pinned host) -> sample+transform -> reverse || dedup "
+               "api": "CandidatePipeline.submit(counters copied from pinned host) -> "
+                      + ("suggest (one kernel) -> dedup " if one_kernel else "sample+transform -> reverse || dedup ") +
                       "-> ob2_compact -> surviving candidates' columns copied to pinned host (copies overlap the next step)"}
 
     if rank != 0:
@@ -577,7 +615,9 @@ def run_b200(args):
         peak, peak_src = 6650.0, "B200_PROFILING.md fallback 6.65 TB/s (of fallback)"
     algo_bytes = {'sample': BYTES_SAMPLE, 'transform': BYTES_TRANSFORM, 'reverse': BYTES_REVERSE, 'dedup': BYTES_DEDUP,
                   'sample+transform': BYTES_SAMPLE + BYTES_TRANSFORM,
-                  'reverse+fingerprint': BYTES_REVERSE}
+                  'reverse+fingerprint': BYTES_REVERSE,
+                  # the yard-stick stays the table's figure: fusion shows up as frac > naive
+                  'suggest': BYTES_SAMPLE + BYTES_TRANSFORM + BYTES_REVERSE}
     algo_bytes = {k: algo_bytes[k] for k in kernel_names}
     dominant = max(per_kernel_ms, key=per_kernel_ms.get)
     achieved = algo_bytes[dominant] * n / (per_kernel_ms[dominant] * 1e-3) / 1e9
@@ -610,10 +650,12 @@ def run_b200(args):
                           "achieved_GBps": step_bytes * n / (ms_per_step * 1e-3) / 1e9,
                           "frac": step_bytes * n / (ms_per_step * 1e-3) / 1e9 / peak},
         "e2e": e2e, "gpu_launches": timed_launches, "clocks": clock_info,
-        "timed_region": ("K steps through orion_b200.pipeline.CandidatePipeline (3 streams, 2 buffer sets)" if pipelined
+        "timed_region": ("K steps through orion_b200.pipeline.CandidatePipeline (%s, 2 buffer sets)"
+                         % ("suggest and dedup on 2 streams" if one_kernel else "3 streams") if pipelined
                          else "K steps on one stream, kernels back to back"),
         "serial_ms_per_step": serial_ms,
         "kernels_in_timed_region_ms": contended_ms,
+        "staged_path": staged_info,
         "checks": {"kept_last_step": kept_last, "kept_frac_last_step": kept_last / float(n), "all_in_space": mask_ok,
                    "reverse_of_transform_is_identity": round_trip_ok,
                    "history_rows_before": hist_rows0, "history_rows_after": hist_rows1},

@@ -124,6 +124,18 @@ int ob2_sample_transform(const ob2_space *space, int64_t n, int64_t n_stride, ui
                          uint64_t base_index, const uint64_t *index, void *cols, void *tcols,
                          uint8_t *mask, uint64_t *fp, uint32_t *n_failed, void *stream);
 
+/* Random.suggest behind PrimaryAlgo in ONE kernel (src/orion/algo/random.py:24-33 called
+ * through src/orion/core/worker/primary_algo.py:44-56): the draw and transform of
+ * ob2_sample_transform, plus reverse() of every transformed value while it is still in
+ * registers -- written to `back` (the handed-out rows; same layout as `cols`, a distinct
+ * 16-byte aligned buffer) -- plus the fingerprint of the `back` rows into `fp` (required).
+ * Results are bit-identical to ob2_sample_transform followed by ob2_reverse_fingerprint;
+ * what is saved is re-reading the transformed columns (the widest stream of the path).
+ * Algorithms that compute in the transformed space keep using the separate kernels. */
+int ob2_suggest(const ob2_space *space, int64_t n, int64_t n_stride, uint64_t seed,
+                uint64_t base_index, const uint64_t *index, void *cols, void *tcols, void *back,
+                uint8_t *mask, uint64_t *fp, uint32_t *n_failed, void *stream);
+
 /* Parity mode of the same kernel: uniforms are read from U[S][n_stride] (one
  * attempt, no redraw); ok[i] = every Real/Integer slot landed in bounds. */
 int ob2_sample_from_uniform(const ob2_space *space, int64_t n, int64_t n_stride,

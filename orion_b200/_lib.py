@@ -60,6 +60,7 @@ SIGNATURES = {
     'ob2_space_trow_bytes': (_i64, [_vp]),
     'ob2_sample': (ctypes.c_int, [_vp, _i64, _i64, _u64, _u64, _vp, _vp, _vp, _vp, _vp, _vp]),
     'ob2_sample_transform': (ctypes.c_int, [_vp, _i64, _i64, _u64, _u64, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    'ob2_suggest': (ctypes.c_int, [_vp, _i64, _i64, _u64, _u64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     'ob2_sample_from_uniform': (ctypes.c_int, [_vp, _i64, _i64, _vp, _vp, _vp, _vp, _vp]),
     'ob2_contains': (ctypes.c_int, [_vp, _i64, _i64, _vp, _i32, _vp, _vp]),
     'ob2_transform': (ctypes.c_int, [_vp, _i64, _i64, _vp, _vp, _vp]),

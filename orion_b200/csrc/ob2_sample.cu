@@ -14,6 +14,10 @@
 // under the arithmetic and saves re-reading the sampled columns.
 #include "ob2_internal.cuh"
 
+#ifndef OB2_SUGGEST_CTAS
+#define OB2_SUGGEST_CTAS 4  // resident CTAs per SM the fused suggest kernel is compiled for
+#endif
+
 namespace {
 
 __device__ __forceinline__ long long quantize_ll(double x, int t_flags) {
@@ -46,16 +50,17 @@ __device__ __forceinline__ int draw_cat_fast(const double *cdf, int k, double u,
 // the fingerprint lanes are wrapping sums, so the contribution of the rejected
 // values (read back from the columns this thread just wrote) is subtracted and
 // the redrawn one added.
-template <bool WITH_FP, bool WITH_T, bool EXT>
+// WITH_B: the fingerprint is over the handed-out row (`back`, at cols + bdelta), which is also rewritten.
+template <bool WITH_FP, bool WITH_T, bool WITH_B, bool EXT>
 __device__ __forceinline__ bool redraw_dim(const ob2_slot_desc *s_slots, int s_last, uint64_t index, int64_t i,
-                                           int64_t n_stride, char *cols, char *tcols, uint32_t k0, uint32_t k1,
-                                           uint32_t pm0, uint32_t pm1, FpAcc &acc) {
+                                           int64_t n_stride, char *cols, char *tcols, int64_t bdelta, uint32_t k0,
+                                           uint32_t k1, uint32_t pm0, uint32_t pm1, FpAcc &acc) {
     const int first = s_slots[s_last].dim_first;
     if (WITH_FP) {
         FpAcc old{0, 0};
         for (int e = first; e <= s_last; ++e) {
             const ob2_slot_desc &d = s_slots[e];
-            const char *col = cols + (int64_t)d.col_units * n_stride;
+            const char *col = cols + (int64_t)d.col_units * n_stride + (WITH_B ? bdelta : 0);
             const uint64_t w = d.kind == OB2_KIND_INTEGER
                                    ? (uint64_t) reinterpret_cast<const volatile long long *>(col)[i]
                                    : canon_f64(reinterpret_cast<const volatile double *>(col)[i]);
@@ -81,6 +86,7 @@ __device__ __forceinline__ bool redraw_dim(const ob2_slot_desc *s_slots, int s_l
                 x = floor(x);
                 const long long q = __double2ll_rz(x);
                 reinterpret_cast<long long *>(col)[i] = q;
+                if (WITH_B) reinterpret_cast<long long *>(col + bdelta)[i] = q;
                 w = (uint64_t)q;
                 if (WITH_T) {
                     if (d.t_op == OB2_OP_TO_REAL)
@@ -90,13 +96,18 @@ __device__ __forceinline__ bool redraw_dim(const ob2_slot_desc *s_slots, int s_l
                 }
             } else {
                 reinterpret_cast<double *>(col)[i] = x;
-                w = canon_f64(x);
+                double bx = x;
                 if (WITH_T) {
-                    if (d.t_op == OB2_OP_QUANTIZE)
-                        reinterpret_cast<long long *>(dst)[i] = quantize_ll(x, d.t_flags);
-                    else
+                    if (d.t_op == OB2_OP_QUANTIZE) {
+                        const long long t = quantize_ll(x, d.t_flags);
+                        reinterpret_cast<long long *>(dst)[i] = t;
+                        bx = __ll2double_rn(t);
+                    } else {
                         reinterpret_cast<double *>(dst)[i] = x;
+                    }
                 }
+                if (WITH_B) reinterpret_cast<double *>(col + bdelta)[i] = bx;
+                w = canon_f64(WITH_B ? bx : x);
             }
             ok &= (x >= d.low) && (x < d.high);
             if (WITH_FP) fp_add(t, d, w);
@@ -117,13 +128,21 @@ __device__ __forceinline__ bool redraw_dim(const ob2_slot_desc *s_slots, int s_l
 // the descriptor; the fingerprint accumulates straight into its lanes; the
 // second candidate of a trailing odd pair replays the first (no `has1` tests
 // until the final stores).
-template <bool PHILOX, bool WITH_FP, bool WITH_T, bool EXT>
-__global__ void __launch_bounds__(OB2_BLOCK, 4)
+//
+// WITH_B (Random.suggest behind PrimaryAlgo, in one pass): also evaluate reverse() on the
+// transformed values while they are still in registers and store the handed-out row to
+// `back` = cols + bdelta (same column layout); the fingerprint is then that of the `back`
+// row, exactly what reverse_kernel<true> computes from the materialised tcols.  Per op:
+// Identity / Enumerate pass the value through; Reverse(Quantize) then Quantize of an exact
+// integer is that integer; argmax (or > 0.5) of the one-hot encoding of an in-range index
+// is that index; Quantize then its cast back is NOT the identity and is computed.
+template <bool PHILOX, bool WITH_FP, bool WITH_T, bool WITH_B, bool EXT>
+__global__ void __launch_bounds__(OB2_BLOCK, WITH_B ? OB2_SUGGEST_CTAS : 4)
 sample_kernel(const ob2_slot_desc *__restrict__ g_slots, int n_slots, const double *__restrict__ g_cdf,
               int cdf_len, int64_t n, int64_t n_stride, int64_t stride4, int64_t stride8, uint32_t k0, uint32_t k1,
               uint32_t pm0, uint32_t pm1,
               uint64_t base_index, const uint64_t *__restrict__ index, const double *__restrict__ U,
-              char *__restrict__ cols, char *__restrict__ tcols, uint8_t *__restrict__ mask,
+              char *__restrict__ cols, char *__restrict__ tcols, int64_t bdelta, uint8_t *__restrict__ mask,
               uint64_t *__restrict__ fp, uint32_t *__restrict__ n_failed) {
     extern __shared__ __align__(16) unsigned char smem[];
     ob2_slot_desc *s_slots = reinterpret_cast<ob2_slot_desc *>(smem);
@@ -174,6 +193,7 @@ sample_kernel(const ob2_slot_desc *__restrict__ g_slots, int n_slots, const doub
             const int c0 = draw_cat_fast(cdf, d.n_cats, u0, uni);
             const int c1 = draw_cat_fast(cdf, d.n_cats, u1, uni);
             st_i32x2(reinterpret_cast<int *>(col - i0 * 4), c0, c1);
+            if (WITH_B) st_i32x2(reinterpret_cast<int *>(col - i0 * 4 + bdelta), c0, c1);
             col += stride4;
             if (WITH_T) {
                 if (d.t_op != OB2_OP_ONEHOT) {
@@ -206,6 +226,7 @@ sample_kernel(const ob2_slot_desc *__restrict__ g_slots, int n_slots, const doub
                 x1 = floor(x1);
                 const long long q0 = __double2ll_rz(x0), q1 = __double2ll_rz(x1);
                 st_i64x2(reinterpret_cast<long long *>(col), q0, q1);
+                if (WITH_B) st_i64x2(reinterpret_cast<long long *>(col + bdelta), q0, q1);
                 if (WITH_T) {
                     if (d.t_op == OB2_OP_TO_REAL)  // the floored double is exactly (double)q
                         st_f64x2(reinterpret_cast<double *>(tcol), x0, x1);
@@ -217,15 +238,23 @@ sample_kernel(const ob2_slot_desc *__restrict__ g_slots, int n_slots, const doub
                 w1 = (uint64_t)q1;
             } else {
                 st_f64x2(reinterpret_cast<double *>(col), x0, x1);
+                double bx0 = x0, bx1 = x1;
                 if (WITH_T) {
-                    if (d.t_op == OB2_OP_QUANTIZE)
-                        st_i64x2(reinterpret_cast<long long *>(tcol), quantize_ll(x0, d.t_flags), quantize_ll(x1, d.t_flags));
-                    else
+                    if (d.t_op == OB2_OP_QUANTIZE) {
+                        const long long t0 = quantize_ll(x0, d.t_flags), t1 = quantize_ll(x1, d.t_flags);
+                        st_i64x2(reinterpret_cast<long long *>(tcol), t0, t1);
+                        if (WITH_B) {
+                            bx0 = __ll2double_rn(t0);
+                            bx1 = __ll2double_rn(t1);
+                        }
+                    } else {
                         st_f64x2(reinterpret_cast<double *>(tcol), x0, x1);
+                    }
                     tcol += stride8;
                 }
-                w0 = canon_f64(x0);
-                w1 = canon_f64(x1);
+                if (WITH_B) st_f64x2(reinterpret_cast<double *>(col + bdelta), bx0, bx1);
+                w0 = canon_f64(bx0);
+                w1 = canon_f64(bx1);
             }
             col += stride8;
             ok0 &= (x0 >= d.low) & (x0 < d.high);  // half-open, space.py:164
@@ -239,9 +268,9 @@ sample_kernel(const ob2_slot_desc *__restrict__ g_slots, int n_slots, const doub
             if (!(ok0 & ok1)) {  // cold: only Real/Integer slots can clear ok
                 if (PHILOX) {
                     if (!ok0)
-                        ok0 = redraw_dim<WITH_FP, WITH_T, EXT>(s_slots, s, idx0, i0, n_stride, cols, tcols, k0, k1, pm0, pm1, acc0);
+                        ok0 = redraw_dim<WITH_FP, WITH_T, WITH_B, EXT>(s_slots, s, idx0, i0, n_stride, cols, tcols, bdelta, k0, k1, pm0, pm1, acc0);
                     if (!ok1)
-                        ok1 = redraw_dim<WITH_FP, WITH_T, EXT>(s_slots, s, idx1, i0 + 1, n_stride, cols, tcols, k0, k1, pm0, pm1, acc1);
+                        ok1 = redraw_dim<WITH_FP, WITH_T, WITH_B, EXT>(s_slots, s, idx1, i0 + 1, n_stride, cols, tcols, bdelta, k0, k1, pm0, pm1, acc1);
                     if (n_failed != nullptr) {  // 4 misses: the reference raises "Improbable bounds"
                         const unsigned bad = (ok0 ? 0u : 1u) + ((ok1 || !has1) ? 0u : 1u);
                         if (bad) atomicAdd(n_failed + d.dim_first, bad);
@@ -320,22 +349,23 @@ struct SampleArgs {
     uint64_t seed, base_index;
     const uint64_t *index;
     const double *U;
-    void *cols, *tcols;
+    void *cols, *tcols, *back;
     uint8_t *mask;
     uint64_t *fp;
     uint32_t *n_failed;
     void *stream;
 };
 
-template <bool PHILOX, bool WITH_FP, bool WITH_T, bool EXT>
+template <bool PHILOX, bool WITH_FP, bool WITH_T, bool EXT, bool WITH_B = false>
 int launch_one(const SampleArgs &a, unsigned blocks) {
-    auto kern = sample_kernel<PHILOX, WITH_FP, WITH_T, EXT>;
+    auto kern = sample_kernel<PHILOX, WITH_FP, WITH_T, WITH_B, EXT>;
+    const int64_t bdelta = WITH_B ? (const char *)a.back - (const char *)a.cols : 0;
     const ob2_space *sp = a.sp;
     int rc = prepare_smem(kern, sp->smem_bytes);
     if (rc != OB2_OK) return rc;
     kern<<<blocks, OB2_BLOCK, sp->smem_bytes, static_cast<cudaStream_t>(a.stream)>>>(
         sp->d_slots, sp->n_slots, sp->d_cdf, sp->cdf_len, a.n, a.n_stride, 4 * a.n_stride, 8 * a.n_stride, (uint32_t)a.seed,
-        (uint32_t)(a.seed >> 32), 0xD2511F53u, 0xCD9E8D57u, a.base_index, a.index, a.U, (char *)a.cols, (char *)a.tcols, a.mask, a.fp,
+        (uint32_t)(a.seed >> 32), 0xD2511F53u, 0xCD9E8D57u, a.base_index, a.index, a.U, (char *)a.cols, (char *)a.tcols, bdelta, a.mask, a.fp,
         a.n_failed);
     return ob2_check_cuda(cudaGetLastError(), "sample_kernel launch");
 }
@@ -366,6 +396,10 @@ int launch_sample(const SampleArgs &a) {
     }
     const unsigned b = (unsigned)blocks;
     const bool with_fp = a.fp != nullptr, with_t = a.tcols != nullptr;
+    if (a.back != nullptr) {  // ob2_suggest: Philox, transform, reverse and fingerprint, all in the one pass
+        if (a.sp->has_extended_prior) return launch_one<PHILOX, true, true, true, PHILOX>(a, b);
+        return launch_one<PHILOX, true, true, false, PHILOX>(a, b);
+    }
     // EXT = the space uses one of the extra closed-form priors: those inverse CDFs live in a
     // separate instantiation so that the common kernel keeps its registers and code size
     if (a.sp->has_extended_prior) {
@@ -385,7 +419,7 @@ int launch_sample(const SampleArgs &a) {
 extern "C" int ob2_sample(const ob2_space *space, int64_t n, int64_t n_stride, uint64_t seed, uint64_t base_index,
                           const uint64_t *index, void *cols, uint8_t *mask, uint64_t *fp, uint32_t *n_failed,
                           void *stream) {
-    const SampleArgs a{space, n, n_stride, seed, base_index, index, nullptr, cols, nullptr, mask, fp, n_failed, stream};
+    const SampleArgs a{space, n, n_stride, seed, base_index, index, nullptr, cols, nullptr, nullptr, mask, fp, n_failed, stream};
     return launch_sample<true>(a);
 }
 
@@ -396,13 +430,28 @@ extern "C" int ob2_sample_transform(const ob2_space *space, int64_t n, int64_t n
         ob2_set_error("ob2_sample_transform: null transformed buffer");
         return OB2_EINVAL;
     }
-    const SampleArgs a{space, n, n_stride, seed, base_index, index, nullptr, cols, tcols, mask, fp, n_failed, stream};
+    const SampleArgs a{space, n, n_stride, seed, base_index, index, nullptr, cols, tcols, nullptr, mask, fp, n_failed, stream};
+    return launch_sample<true>(a);
+}
+
+extern "C" int ob2_suggest(const ob2_space *space, int64_t n, int64_t n_stride, uint64_t seed, uint64_t base_index,
+                           const uint64_t *index, void *cols, void *tcols, void *back, uint8_t *mask, uint64_t *fp,
+                           uint32_t *n_failed, void *stream) {
+    if (tcols == nullptr || back == nullptr || fp == nullptr) {
+        ob2_set_error("ob2_suggest: null transformed / handed-out / fingerprint buffer");
+        return OB2_EINVAL;
+    }
+    if (back == cols || ((uintptr_t)back & 15) != 0) {
+        ob2_set_error("ob2_suggest: `back` must be a 16-byte aligned buffer distinct from `cols`");
+        return OB2_EINVAL;
+    }
+    const SampleArgs a{space, n, n_stride, seed, base_index, index, nullptr, cols, tcols, back, mask, fp, n_failed, stream};
     return launch_sample<true>(a);
 }
 
 extern "C" int ob2_sample_from_uniform(const ob2_space *space, int64_t n, int64_t n_stride, const double *U,
                                        void *cols, uint8_t *ok, uint64_t *fp, void *stream) {
-    const SampleArgs a{space, n, n_stride, 0, 0, nullptr, U, cols, nullptr, ok, fp, nullptr, stream};
+    const SampleArgs a{space, n, n_stride, 0, 0, nullptr, U, cols, nullptr, nullptr, ok, fp, nullptr, stream};
     return launch_sample<false>(a);
 }
 

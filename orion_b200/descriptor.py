@@ -261,6 +261,36 @@ class CompiledSpace(object):
             batch.n_failed.data_ptr(), self._stream()))
         return batch
 
+    def suggest(self, n, seed, base_index=0, index=None, out=None, transformed_out=None, back_out=None):
+        """Random.suggest behind PrimaryAlgo as one kernel (``ob2_suggest``):
+        sample -> transform -> reverse -> fingerprint.  Returns ``(batch, tbatch,
+        back)``; ``back.fp`` holds the fingerprints of the handed-out rows and
+        ``batch.mask`` the fused ``point in space``.  Bit-identical to
+        ``sample(transformed_out=...)`` followed by ``reverse(with_fingerprint=True)``."""
+        self._require_samplable()
+        batch = out if out is not None else self.empty_columns(n)
+        tb = transformed_out if transformed_out is not None else self.empty_columns(n, transformed=True)
+        back = back_out if back_out is not None else self.empty_columns(n)
+        ns = batch.n_stride
+        assert not batch.transformed and tb.transformed and not back.transformed
+        assert batch.n == n and tb.n_stride == ns and back.n_stride == ns
+        if batch.mask is None:
+            batch.mask = torch.empty(ns, dtype=torch.uint8, device=self.device)
+        if back.fp is None:
+            back.fp = torch.empty((ns, 2), dtype=torch.int64, device=self.device)
+        if batch.n_failed is None:
+            batch.n_failed = torch.zeros(self.n_slots, dtype=torch.int32, device=self.device)
+        else:
+            batch.n_failed.zero_()
+        _lib.check(self.lib.ob2_suggest(
+            self.handle, n, ns, int(seed) & _M64, int(base_index) & _M64,
+            index.data_ptr() if index is not None else None, batch.buf.data_ptr(), tb.buf.data_ptr(),
+            back.buf.data_ptr(), batch.mask.data_ptr(), back.fp.data_ptr(), batch.n_failed.data_ptr(),
+            self._stream()))
+        tb.n = n
+        back.n = n
+        return batch, tb, back
+
     def _require_samplable(self):
         if self.unsamplable is not None:
             raise NotImplementedError(

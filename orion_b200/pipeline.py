@@ -46,8 +46,11 @@ class CandidatePipeline(object):
     def __init__(self, compiled, history, n, depth=2, timed=False, fingerprint_in='reverse'):
         # 'reverse': the fingerprints are computed by the (bandwidth-bound) reverse kernel over the rows it
         # writes -- the candidates as handed out; 'sample': by the (issue-bound) sampler over its draws
-        assert fingerprint_in in ('reverse', 'sample')
-        self.fp_in_reverse = fingerprint_in == 'reverse'
+        # 'suggest': ONE kernel (ob2_suggest) samples, transforms, reverses in registers and fingerprints --
+        # the Random.suggest fast path; the transformed columns are written but never read back
+        assert fingerprint_in in ('reverse', 'sample', 'suggest')
+        self.fused = fingerprint_in == 'suggest'
+        self.fp_in_reverse = fingerprint_in in ('reverse', 'suggest')
         self.compiled = compiled
         self.n = n
         # a ShardedHistory / PeerShardedHistory is used as is; a bare TrialHistory is wrapped
@@ -85,20 +88,27 @@ class CandidatePipeline(object):
                 slot.hold = None
             if ev:
                 ev[0].record()
-            c.sample(n, seed, base_index=base_index, index=index, with_mask=True,
-                     with_fingerprint=not self.fp_in_reverse,
-                     out=slot.batch, transformed_out=slot.tbatch)
+            if self.fused:
+                c.suggest(n, seed, base_index=base_index, index=index,
+                          out=slot.batch, transformed_out=slot.tbatch, back_out=slot.back)
+            else:
+                c.sample(n, seed, base_index=base_index, index=index, with_mask=True,
+                         with_fingerprint=not self.fp_in_reverse,
+                         out=slot.batch, transformed_out=slot.tbatch)
             if ev:
                 ev[1].record()
             slot.sampled.record()
-        with torch.cuda.stream(self.s_reverse):
-            self.s_reverse.wait_event(slot.sampled)
-            if ev:
-                ev[2].record()
-            c.reverse(slot.tbatch, out=slot.back, with_fingerprint=self.fp_in_reverse)
-            if ev:
-                ev[3].record()
-            slot.reversed.record()
+            if self.fused:
+                slot.reversed.record()
+        if not self.fused:
+            with torch.cuda.stream(self.s_reverse):
+                self.s_reverse.wait_event(slot.sampled)
+                if ev:
+                    ev[2].record()
+                c.reverse(slot.tbatch, out=slot.back, with_fingerprint=self.fp_in_reverse)
+                if ev:
+                    ev[3].record()
+                slot.reversed.record()
         with torch.cuda.stream(self.s_dedup):
             self.s_dedup.wait_event(slot.reversed if self.fp_in_reverse else slot.sampled)
             if ev:
@@ -127,6 +137,11 @@ class CandidatePipeline(object):
             return {}
         torch.cuda.synchronize(self.compiled.device)
         k = len(self.timings)
+        if self.fused:
+            return {
+                'suggest': sum(e[0].elapsed_time(e[1]) for e in self.timings) / k,
+                'dedup': sum(e[4].elapsed_time(e[5]) for e in self.timings) / k,
+            }
         return {
             'sample+transform': sum(e[0].elapsed_time(e[1]) for e in self.timings) / k,
             'reverse': sum(e[2].elapsed_time(e[3]) for e in self.timings) / k,

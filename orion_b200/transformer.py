@@ -253,6 +253,17 @@ class TransformedSpace(Space):
             _raise_if_improbable(batch, list(self.original.values()))
         return batch, tbatch
 
+    def suggest_columns(self, n_samples=1, seed=None, base_index=0, check=True):
+        """What ``Random`` behind ``PrimaryAlgo`` produces, from one kernel
+        (``ob2_suggest``): returns (original batch, transformed batch, handed-out
+        batch = reverse(transformed)); the last carries the row fingerprints
+        (``.fp``) the history dedups on, the first the fused in-space mask."""
+        compiled = self.compiled()
+        batch, tbatch, back = compiled.suggest(n_samples, philox_key(seed), base_index=base_index)
+        if check:
+            _raise_if_improbable(batch, list(self.original.values()))
+        return batch, tbatch, back
+
     def contains_columns(self, tbatch):
         """``reverse(p) in original`` for every transformed row."""
         compiled = self.compiled()
