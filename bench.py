@@ -57,6 +57,9 @@ def parse_args():
     ap.add_argument('--unfused', action='store_true', help='sample and transform as two kernels')
     ap.add_argument('--fp-in-sampler', action='store_true',
                     help='compute the row fingerprints in the sampler instead of the reverse kernel')
+    ap.add_argument('--e2e-natural', action='store_true',
+                    help='e2e leg: copy the survivors out at the natural column widths (int64 / int32) instead of '
+                         'the narrowed wire layout')
     ap.add_argument('--serial', action='store_true', help='no stream pipeline: one stream, kernels back to back')
     ap.add_argument('--exchange', default='auto', choices=['auto', 'nccl', 'peer'],
                     help='multi-GPU dedup exchange: peer-memory stores from inside the kernels, NCCL all-to-all, '
@@ -525,9 +528,14 @@ def run_b200(args):
         # host memory.  Two buffer sets: compaction and copies of step j overlap step j+1.
         from orion_b200.columns import _SIZE
         ns = batch.n_stride
-        host_cols = [torch.empty(batch.buf.numel(), dtype=torch.uint8).pin_memory() for _ in range(2)]
+        # ... in the wire layout: Integer / Categorical columns at their narrowest lossless width
+        # (mixed64: 288 instead of 448 bytes per candidate)
+        wire = not args.e2e_natural
+        out_meta = compiled.wire_meta if wire else compiled.col_meta
+        out_row = compiled.wire_row_bytes if wire else compiled.row_bytes
+        host_cols = [torch.empty(out_row * ns, dtype=torch.uint8).pin_memory() for _ in range(2)]
         host_cnt = [torch.zeros(1, dtype=torch.int64).pin_memory() for _ in range(2)]
-        dense = [compiled.empty_columns(n) for _ in range(2)]
+        dense = [compiled.empty_columns(n, wire=wire) for _ in range(2)]
         cnt_dev = [torch.zeros(1, dtype=torch.int64, device=dev) for _ in range(2)]
         cscratch = [torch.empty(max(int(compiled.lib.ob2_compact_scratch_bytes(n)), 8), dtype=torch.uint8, device=dev)
                     for _ in range(2)]
@@ -545,11 +553,11 @@ def run_b200(args):
             compacted[b].synchronize()              # the host needs n_kept; the GPU already works on the next step
             k = int(host_cnt[b][0])
             with torch.cuda.stream(s_copy):
-                for units, dt in compiled.col_meta:
+                for units, dt in out_meta:
                     start, nbytes = units * ns, k * _SIZE[dt]
                     host_cols[b][start:start + nbytes].copy_(dense[b].buf[start:start + nbytes], non_blocking=True)
                 copied[b].record()
-            state['d2h'] += k * compiled.row_bytes + 8
+            state['d2h'] += k * out_row + 8
             state['kept'] = k
 
         def e2e_step(j):
@@ -564,7 +572,7 @@ def run_b200(args):
                 s_comp.wait_event(slot.deduped)
                 if state['used'][b]:
                     s_comp.wait_event(copied[b])                                # dense[b] has been copied out
-                slot.back.compact(keep=slot.batch.keep, out=dense[b], count=cnt_dev[b], scratch=cscratch[b])
+                slot.back.compact(keep=slot.batch.keep, out=dense[b], count=cnt_dev[b], scratch=cscratch[b], wire=wire)
                 host_cnt[b].copy_(cnt_dev[b], non_blocking=True)                # D2H: how many survived
                 compacted[b].record()
             state['used'][b] = True
@@ -600,7 +608,7 @@ def run_b200(args):
                "steps": args.e2e_steps, "kept_last_step": state['kept'],
                "api": "CandidatePipeline.submit(counters copied from pinned host) -> "
                       + ("suggest (one kernel) -> dedup " if one_kernel else "sample+transform -> reverse || dedup ") +
-                      "-> ob2_compact -> surviving candidates' columns copied to pinned host (copies overlap the next step)"}
+                      "-> ob2_compact" + ("_wire" if wire else "") + " -> surviving candidates' columns copied to pinned host (copies overlap the next step)"}
 
     if rank != 0:
         if world > 1:

@@ -73,7 +73,7 @@ typedef struct ob2_slot_desc {
     int32_t t_units;   /* same as col_units, in the transformed column set        */
     int32_t t_flags;   /* OB2_TFLAG_*                                             */
     int32_t t_width;   /* number of transformed columns this slot expands to      */
-    int32_t reserved;  /* keeps the struct at 128 bytes                           */
+    int32_t reserved;  /* ignored on input (the library keeps the wire layout here) */
     double p0, p1;     /* reciprocal: log(a), log(b) - log(a)                     */
     double loc, scale; /* x = base(u) * scale + loc  (scipy rv_generic.rvs)       */
     double low, high;  /* accepted iff low <= x < high (space.py:160-164)         */
@@ -96,6 +96,14 @@ int ob2_space_create(const ob2_slot_desc *slots, int32_t n_slots, const double *
 void ob2_space_destroy(ob2_space *space);
 int64_t ob2_space_row_bytes(const ob2_space *space);  /* bytes per candidate, original set   */
 int64_t ob2_space_trow_bytes(const ob2_space *space); /* bytes per candidate, transformed set */
+/* The "wire" layout used to hand candidates to the host (ob2_compact_wire): same columnar
+ * scheme, but every Integer / Categorical column is stored in the narrowest integer type
+ * that holds the slot's whole interval (Integer: signed 1/2/4/8 bytes from [low, high);
+ * Categorical index: unsigned 1/2 bytes, else int32); Real columns stay float64.  Lossless
+ * for every row that is in the space.  units[s] * stride = byte offset of slot s's column,
+ * elem_bytes[s] its element size; both are host arrays of n_slots entries. */
+int64_t ob2_space_wire_row_bytes(const ob2_space *space);
+int ob2_space_wire_layout(const ob2_space *space, int32_t *units, int32_t *elem_bytes);
 
 /* Space.sample(n, seed) -- src/orion/algo/space.py:456-484, with Real.sample's
  * <=4-attempt rejection (space.py:256-276), _Discrete.sample's floor
@@ -236,6 +244,14 @@ int64_t ob2_compact_scratch_bytes(int64_t n);
 int ob2_compact(const ob2_space *space, int64_t n, int64_t n_stride, const void *cols,
                 const uint8_t *keep, int32_t transformed, int64_t out_stride, void *out_cols,
                 void *scratch, uint64_t *n_kept, void *stream);
+/* The same gather of an ORIGINAL column set, written in the wire layout above: what crosses
+ * PCIe on the way to tuple_to_trial (src/orion/core/utils/format_trials.py:28-42) is the
+ * survivors' values at their narrowest lossless width (mixed64: 288 instead of 448 bytes
+ * per candidate).  Rows that are not in the space (an "Improbable bounds" failure the host
+ * raises on anyway) may be truncated. */
+int ob2_compact_wire(const ob2_space *space, int64_t n, int64_t n_stride, const void *cols,
+                     const uint8_t *keep, int64_t out_stride, void *out_cols, void *scratch,
+                     uint64_t *n_kept, void *stream);
 
 /* Multi-GPU exchange helpers: owner rank of a fingerprint is
  * fp.hi % n_ranks.  bucket writes (fp, global order key) into

@@ -77,6 +77,9 @@ SIGNATURES = {
     'ob2_set_export': (ctypes.c_int, [_vp, _u64, _vp, _vp, _vp]),
     'ob2_set_count': (ctypes.c_int, [_vp, ctypes.POINTER(_u64), _vp]),
     'ob2_compact_scratch_bytes': (_i64, [_i64]),
+    'ob2_space_wire_row_bytes': (_i64, [_vp]),
+    'ob2_space_wire_layout': (ctypes.c_int, [_vp, ctypes.POINTER(_i32), ctypes.POINTER(_i32)]),
+    'ob2_compact_wire': (ctypes.c_int, [_vp, _i64, _i64, _vp, _vp, _i64, _vp, _vp, _vp, _vp]),
     'ob2_compact': (ctypes.c_int, [_vp, _i64, _i64, _vp, _vp, _i32, _i64, _vp, _vp, _vp, _vp]),
     'ob2_bucket_by_owner': (ctypes.c_int, [_i64, _vp, _u32, _i32, _i64, _vp, _vp, _vp, _vp, _vp]),
     'ob2_scatter_verdict': (ctypes.c_int, [_i64, _vp, _vp, _vp, _vp, _vp]),

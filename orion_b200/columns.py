@@ -8,20 +8,23 @@ form held in device memory: one contiguous block, the column of scalar slot
 import numpy as np
 import torch
 
-_TORCH = {'f8': torch.float64, 'i8': torch.int64, 'i4': torch.int32}
-_NUMPY = {'f8': np.float64, 'i8': np.int64, 'i4': np.int32}
-_SIZE = {'f8': 8, 'i8': 8, 'i4': 4}
+_TORCH = {'f8': torch.float64, 'i8': torch.int64, 'i4': torch.int32, 'i2': torch.int16, 'i1': torch.int8,
+          'u2': torch.uint16, 'u1': torch.uint8}
+_NUMPY = {'f8': np.float64, 'i8': np.int64, 'i4': np.int32, 'i2': np.int16, 'i1': np.int8,
+          'u2': np.uint16, 'u1': np.uint8}
+_SIZE = {'f8': 8, 'i8': 8, 'i4': 4, 'i2': 2, 'i1': 1, 'u2': 2, 'u1': 1}
 
 
 class ColumnBatch(object):
     """n candidates (or transformed points) as device columns."""
 
-    def __init__(self, compiled, n, n_stride, buf, transformed=False):
+    def __init__(self, compiled, n, n_stride, buf, transformed=False, wire=False):
         self.compiled = compiled
         self.n = n
         self.n_stride = n_stride
         self.buf = buf
         self.transformed = transformed
+        self.wire = wire        # narrowed hand-off layout: same values, narrowest lossless integer widths
         self.mask = None        # uint8 [n_stride]: point in space (fused contains)
         self.fp = None          # int64 [n_stride][2]: row fingerprints (bit pattern of u64)
         self.keep = None        # uint8 [n_stride]: survived dedup
@@ -30,6 +33,8 @@ class ColumnBatch(object):
     @property
     def _meta(self):
         c = self.compiled
+        if self.wire:
+            return c.wire_meta
         return [(u, dt) for (u, dt, _s) in c.tcol_meta] if self.transformed else c.col_meta
 
     def column(self, j):
@@ -47,13 +52,19 @@ class ColumnBatch(object):
         return self.n
 
     # ---- host round trips (compatibility path and tests)
-    def to_numpy(self):
-        """One numpy array per column (a single device->host copy)."""
+    def to_numpy(self, natural=True):
+        """One numpy array per column (a single device->host copy).  A wire
+        batch is widened on the host to the natural dtypes (int64 / int32)
+        unless ``natural`` is False."""
         host = self.buf.cpu().numpy()
         out = []
-        for units, dt in self._meta:
+        for j, (units, dt) in enumerate(self._meta):
             start = units * self.n_stride
-            out.append(host[start:start + _SIZE[dt] * self.n_stride].view(_NUMPY[dt])[:self.n].copy())
+            col = host[start:start + _SIZE[dt] * self.n_stride].view(_NUMPY[dt])[:self.n]
+            if self.wire and natural:
+                out.append(col.astype(_NUMPY[self.compiled.col_meta[j][1]]))
+            else:
+                out.append(col.copy())
         return out
 
     @classmethod
@@ -74,18 +85,22 @@ class ColumnBatch(object):
         batch.buf.copy_(torch.from_numpy(host))
         return batch
 
-    def compact(self, keep=None, out=None, count=None, scratch=None):
+    def compact(self, keep=None, out=None, count=None, scratch=None, wire=False):
         """Dense ColumnBatch of the rows with ``keep != 0`` (default: the
         batch's own dedup verdicts), original order preserved
         (``ob2_compact``).  Reads the survivor count back (one sync) unless a
         device ``count`` tensor (int64[1]) is passed, in which case nothing
-        synchronises and ``dest.n`` is left for the caller to set."""
+        synchronises and ``dest.n`` is left for the caller to set.  ``wire``:
+        the result is in the narrowed hand-off layout (``ob2_compact_wire``;
+        original column sets only) -- fewer bytes to copy to the host."""
         import ctypes
         from . import _lib
         c = self.compiled
         keep = self.keep if keep is None else keep
         assert keep is not None and keep.dtype == torch.uint8
-        dest = out if out is not None else c.empty_columns(self.n, self.transformed)
+        assert not self.wire and not (wire and self.transformed)
+        dest = out if out is not None else c.empty_columns(self.n, self.transformed, wire=wire)
+        assert dest.wire == wire and dest.transformed == self.transformed
         nbytes = c.lib.ob2_compact_scratch_bytes(self.n)
         if scratch is None:
             scratch = torch.empty(max(nbytes, 8), dtype=torch.uint8, device=c.device)
@@ -93,10 +108,15 @@ class ColumnBatch(object):
         lazy = count is not None
         if count is None:
             count = torch.zeros(1, dtype=torch.int64, device=c.device)
-        _lib.check(c.lib.ob2_compact(c.handle, self.n, self.n_stride, self.buf.data_ptr(), keep.data_ptr(),
-                                     1 if self.transformed else 0, dest.n_stride, dest.buf.data_ptr(),
-                                     scratch.data_ptr(), count.data_ptr(),
-                                     ctypes.c_void_p(torch.cuda.current_stream(c.device).cuda_stream)))
+        stream = ctypes.c_void_p(torch.cuda.current_stream(c.device).cuda_stream)
+        if wire:
+            _lib.check(c.lib.ob2_compact_wire(c.handle, self.n, self.n_stride, self.buf.data_ptr(), keep.data_ptr(),
+                                              dest.n_stride, dest.buf.data_ptr(), scratch.data_ptr(),
+                                              count.data_ptr(), stream))
+        else:
+            _lib.check(c.lib.ob2_compact(c.handle, self.n, self.n_stride, self.buf.data_ptr(), keep.data_ptr(),
+                                         1 if self.transformed else 0, dest.n_stride, dest.buf.data_ptr(),
+                                         scratch.data_ptr(), count.data_ptr(), stream))
         if not lazy:
             dest.n = int(count.item())
         return dest

@@ -78,6 +78,9 @@ compact_scan_kernel(int64_t n_blocks, uint32_t *__restrict__ block_counts, unsig
     if (t == 1023) *n_kept = s_part[1023];
 }
 
+// WIRE: original columns only, each written at the slot's narrowed width (descriptor `reserved`
+// = (offset units << 4) | element bytes, filled in by ob2_space_create).
+template <bool WIRE>
 __global__ void __launch_bounds__(OB2_BLOCK)
 compact_gather_kernel(const ob2_slot_desc *__restrict__ g_slots, int n_slots, int transformed, int64_t n,
                       int64_t n_stride, const char *__restrict__ cols, const uint8_t *__restrict__ keep,
@@ -96,7 +99,37 @@ compact_gather_kernel(const ob2_slot_desc *__restrict__ g_slots, int n_slots, in
     if (mine == 0) return;
     for (int s = 0; s < n_slots; ++s) {
         const ob2_slot_desc &d = s_slots[s];
-        if (!transformed) {
+        if (WIRE) {
+            const char *src = cols + (int64_t)d.col_units * n_stride;
+            char *dst = out + (int64_t)(d.reserved >> 4) * out_stride;
+            long long a, b;
+            if (d.kind == OB2_KIND_CATEGORICAL) {
+                int a4, b4;
+                ld_i32x2(reinterpret_cast<const int *>(src) + i0, a4, b4);
+                a = a4;
+                b = b4;
+            } else {
+                ld_i64x2(reinterpret_cast<const long long *>(src) + i0, a, b);
+            }
+            switch (d.reserved & 15) {  // truncation keeps the value: it lies in the slot's interval
+                case 1:
+                    if (k0) reinterpret_cast<signed char *>(dst)[r0] = (signed char)a;
+                    if (k1) reinterpret_cast<signed char *>(dst)[r1] = (signed char)b;
+                    break;
+                case 2:
+                    if (k0) reinterpret_cast<short *>(dst)[r0] = (short)a;
+                    if (k1) reinterpret_cast<short *>(dst)[r1] = (short)b;
+                    break;
+                case 4:
+                    if (k0) reinterpret_cast<int *>(dst)[r0] = (int)a;
+                    if (k1) reinterpret_cast<int *>(dst)[r1] = (int)b;
+                    break;
+                default:
+                    if (k0) reinterpret_cast<long long *>(dst)[r0] = a;
+                    if (k1) reinterpret_cast<long long *>(dst)[r1] = b;
+                    break;
+            }
+        } else if (!transformed) {
             const char *src = cols + (int64_t)d.col_units * n_stride;
             char *dst = out + (int64_t)d.col_units * out_stride;
             if (d.kind == OB2_KIND_CATEGORICAL) {
@@ -141,9 +174,10 @@ extern "C" int64_t ob2_compact_scratch_bytes(int64_t n) {
     return (blocks + 1) * (int64_t)sizeof(uint32_t);
 }
 
-extern "C" int ob2_compact(const ob2_space *space, int64_t n, int64_t n_stride, const void *cols,
-                           const uint8_t *keep, int32_t transformed, int64_t out_stride, void *out_cols,
-                           void *scratch, uint64_t *n_kept, void *stream) {
+namespace {
+int compact_impl(const ob2_space *space, int64_t n, int64_t n_stride, const void *cols, const uint8_t *keep,
+                 int32_t transformed, bool wire, int64_t out_stride, void *out_cols, void *scratch, uint64_t *n_kept,
+                 void *stream) {
     int rc = ob2_check_batch(space, n, n_stride);
     if (rc != OB2_OK) return rc;
     if (cols == nullptr || keep == nullptr || out_cols == nullptr || scratch == nullptr || n_kept == nullptr ||
@@ -166,13 +200,26 @@ extern "C" int ob2_compact(const ob2_space *space, int64_t n, int64_t n_stride, 
     rc = ob2_check_cuda(cudaGetLastError(), "compact_scan_kernel launch");
     if (rc != OB2_OK) return rc;
     const size_t smem = (size_t)space->n_slots * sizeof(ob2_slot_desc);
+    auto kern = wire ? compact_gather_kernel<true> : compact_gather_kernel<false>;
     if (smem > 48 * 1024) {
-        rc = ob2_check_cuda(cudaFuncSetAttribute(compact_gather_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
+        rc = ob2_check_cuda(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
                             "cudaFuncSetAttribute(smem)");
         if (rc != OB2_OK) return rc;
     }
-    compact_gather_kernel<<<(unsigned)blocks, OB2_BLOCK, smem, st>>>(space->d_slots, space->n_slots, transformed, n,
-                                                                     n_stride, (const char *)cols, keep, counts,
-                                                                     out_stride, (char *)out_cols);
+    kern<<<(unsigned)blocks, OB2_BLOCK, smem, st>>>(space->d_slots, space->n_slots, transformed, n, n_stride,
+                                                    (const char *)cols, keep, counts, out_stride, (char *)out_cols);
     return ob2_check_cuda(cudaGetLastError(), "compact_gather_kernel launch");
+}
+}  // namespace
+
+extern "C" int ob2_compact(const ob2_space *space, int64_t n, int64_t n_stride, const void *cols,
+                           const uint8_t *keep, int32_t transformed, int64_t out_stride, void *out_cols,
+                           void *scratch, uint64_t *n_kept, void *stream) {
+    return compact_impl(space, n, n_stride, cols, keep, transformed, false, out_stride, out_cols, scratch, n_kept, stream);
+}
+
+extern "C" int ob2_compact_wire(const ob2_space *space, int64_t n, int64_t n_stride, const void *cols,
+                                const uint8_t *keep, int64_t out_stride, void *out_cols, void *scratch,
+                                uint64_t *n_kept, void *stream) {
+    return compact_impl(space, n, n_stride, cols, keep, 0, true, out_stride, out_cols, scratch, n_kept, stream);
 }

@@ -14,6 +14,9 @@ struct ob2_space {
     int32_t cdf_len;
     int64_t row_bytes;   // bytes per candidate in the original column set
     int64_t trow_bytes;  // bytes per candidate in the transformed column set
+    int64_t wire_row_bytes;  // bytes per candidate in the narrowed host hand-off layout (ob2_compact_wire)
+    int32_t *wire_units;     // host: per slot, byte offset per row of its wire column
+    int32_t *wire_bytes;     // host: per slot, element size of its wire column (1, 2, 4 or 8)
     int32_t t_cols;      // number of transformed columns
     size_t smem_bytes;   // descriptor + cdf staging size
     ob2_slot_desc *d_slots;

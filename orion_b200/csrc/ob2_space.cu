@@ -29,6 +29,19 @@ extern "C" int ob2_version(void) { return OB2_VERSION; }
 
 static int elem_bytes_orig(const ob2_slot_desc &d) { return d.kind == OB2_KIND_CATEGORICAL ? 4 : 8; }
 
+// Element size of a slot in the wire layout: the narrowest integer type that holds every value
+// of the slot's interval (Integer: signed, [low, high) inside [-2^(8w-1), 2^(8w-1)); Categorical:
+// the index, unsigned for w < 4).  Real slots stay 8-byte doubles.
+static int elem_bytes_wire(const ob2_slot_desc &d) {
+    if (d.kind == OB2_KIND_REAL) return 8;
+    if (d.kind == OB2_KIND_CATEGORICAL) return d.n_cats <= 256 ? 1 : d.n_cats <= 65536 ? 2 : 4;
+    for (int w = 1; w <= 4; w *= 2) {
+        const double lim = (double)(1ll << (8 * w - 1));
+        if (d.low >= -lim && d.high <= lim) return w;  // (false for NaN / infinite bounds)
+    }
+    return 8;
+}
+
 extern "C" int ob2_space_create(const ob2_slot_desc *slots, int32_t n_slots, const double *cdf,
                                 int32_t cdf_len, ob2_space **out) {
     if (out == nullptr || slots == nullptr || n_slots <= 0 || cdf_len < 0 || (cdf_len > 0 && cdf == nullptr)) {
@@ -137,11 +150,32 @@ extern "C" int ob2_space_create(const ob2_slot_desc *slots, int32_t n_slots, con
     sp->has_extended_prior = extended;
     sp->d_slots = nullptr;
     sp->d_cdf = nullptr;
+    // the device copy of the table carries the wire layout in `reserved`: (offset units << 4) | element bytes
+    ob2_slot_desc *staged = new (std::nothrow) ob2_slot_desc[n_slots];
+    sp->wire_units = new (std::nothrow) int32_t[n_slots];
+    sp->wire_bytes = new (std::nothrow) int32_t[n_slots];
+    if (staged == nullptr || sp->wire_units == nullptr || sp->wire_bytes == nullptr) {
+        delete[] staged;
+        ob2_space_destroy(sp);
+        ob2_set_error("out of host memory");
+        return OB2_ENOMEM;
+    }
+    int64_t wire = 0;
+    for (int s = 0; s < n_slots; ++s) {
+        staged[s] = slots[s];
+        const int w = elem_bytes_wire(slots[s]);
+        sp->wire_units[s] = (int32_t)wire;
+        sp->wire_bytes[s] = w;
+        staged[s].reserved = (int32_t)((wire << 4) | w);  // wire <= row_bytes < 2^27 (smem limit on n_slots)
+        wire += w;
+    }
+    sp->wire_row_bytes = wire;
     int rc = ob2_check_cuda(cudaGetDevice(&sp->device), "cudaGetDevice");
     if (rc == OB2_OK) rc = ob2_check_cuda(cudaMalloc(&sp->d_slots, (size_t)n_slots * sizeof(ob2_slot_desc)), "cudaMalloc(slots)");
     if (rc == OB2_OK)
-        rc = ob2_check_cuda(cudaMemcpy(sp->d_slots, slots, (size_t)n_slots * sizeof(ob2_slot_desc), cudaMemcpyHostToDevice),
+        rc = ob2_check_cuda(cudaMemcpy(sp->d_slots, staged, (size_t)n_slots * sizeof(ob2_slot_desc), cudaMemcpyHostToDevice),
                             "cudaMemcpy(slots)");
+    delete[] staged;
     // always allocate at least one element so kernels get a valid pointer
     if (rc == OB2_OK) rc = ob2_check_cuda(cudaMalloc(&sp->d_cdf, (size_t)(cdf_len > 0 ? cdf_len : 1) * sizeof(double)), "cudaMalloc(cdf)");
     if (rc == OB2_OK && cdf_len > 0)
@@ -158,8 +192,21 @@ extern "C" void ob2_space_destroy(ob2_space *sp) {
     if (sp == nullptr) return;
     if (sp->d_slots) cudaFree(sp->d_slots);
     if (sp->d_cdf) cudaFree(sp->d_cdf);
+    delete[] sp->wire_units;
+    delete[] sp->wire_bytes;
     delete sp;
 }
 
 extern "C" int64_t ob2_space_row_bytes(const ob2_space *sp) { return sp ? sp->row_bytes : -1; }
 extern "C" int64_t ob2_space_trow_bytes(const ob2_space *sp) { return sp ? sp->trow_bytes : -1; }
+extern "C" int64_t ob2_space_wire_row_bytes(const ob2_space *sp) { return sp ? sp->wire_row_bytes : -1; }
+
+extern "C" int ob2_space_wire_layout(const ob2_space *sp, int32_t *units, int32_t *elem_bytes) {
+    if (sp == nullptr || units == nullptr || elem_bytes == nullptr) {
+        ob2_set_error("ob2_space_wire_layout: null argument");
+        return OB2_EINVAL;
+    }
+    memcpy(units, sp->wire_units, (size_t)sp->n_slots * sizeof(int32_t));
+    memcpy(elem_bytes, sp->wire_bytes, (size_t)sp->n_slots * sizeof(int32_t));
+    return OB2_OK;
+}

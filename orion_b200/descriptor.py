@@ -193,6 +193,16 @@ class CompiledSpace(object):
         self.handle = handle
         assert self.lib.ob2_space_row_bytes(handle) == self.row_bytes
         assert self.lib.ob2_space_trow_bytes(handle) == self.trow_bytes
+        # the narrowed host hand-off layout (ob2_compact_wire): the library decides it, we only read it
+        units = (ctypes.c_int32 * self.n_slots)()
+        widths = (ctypes.c_int32 * self.n_slots)()
+        _lib.check(self.lib.ob2_space_wire_layout(handle, units, widths))
+        self.wire_row_bytes = int(self.lib.ob2_space_wire_row_bytes(handle))
+        self.wire_meta = []
+        for s, (_u, dt) in enumerate(self.col_meta):
+            w = int(widths[s])
+            wdt = 'f8' if dt == 'f8' else ('i%d' % w) if dt == 'i8' else ('u%d' % w if w < 4 else 'i4')
+            self.wire_meta.append((int(units[s]), wdt))
 
     def __del__(self):
         handle = getattr(self, 'handle', None)
@@ -207,13 +217,15 @@ class CompiledSpace(object):
     def _stream(self):
         return ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
 
-    def empty_columns(self, n, transformed=False):
-        """Uninitialised column block for n candidates."""
+    def empty_columns(self, n, transformed=False, wire=False):
+        """Uninitialised column block for n candidates (``wire``: the narrowed
+        host hand-off layout of ``ob2_compact_wire``)."""
         from .columns import ColumnBatch
+        assert not (transformed and wire)
         n_stride = round_up(max(int(n), 1))
-        row = self.trow_bytes if transformed else self.row_bytes
+        row = self.wire_row_bytes if wire else self.trow_bytes if transformed else self.row_bytes
         buf = torch.empty(row * n_stride, dtype=torch.uint8, device=self.device)
-        return ColumnBatch(self, int(n), n_stride, buf, transformed)
+        return ColumnBatch(self, int(n), n_stride, buf, transformed, wire=wire)
 
     # ------------------------------------------------------------ kernels
     def sample(self, n, seed, base_index=0, with_mask=True, with_fingerprint=False, out=None, index=None,

@@ -39,7 +39,8 @@ def batch_to_trials(space, batch, keep=None):
     PCIe once.
     """
     keep = batch.keep if keep is None else keep
-    dense = batch.compact(keep) if keep is not None else batch
+    # (wire: Integer / Categorical columns cross PCIe at their narrowest lossless width)
+    dense = batch.compact(keep, wire=not batch.transformed) if keep is not None else batch
     rows = space.rows_from_columns(dense.to_numpy(), dense.n)
     return [tuple_to_trial(row, space) for row in rows]
 

@@ -61,3 +61,53 @@ def test_batch_to_trials_round_trip():
     # history ingestion of stored trials: they are all known now
     again = format_trials.trials_to_batch(space, trials)
     assert not bool(hist.dedup(again).any().item())
+
+
+def _width_space():
+    from orion_b200.space import Categorical, Integer, Real, Space
+    space = Space()
+    space.register(Integer('i1', 'uniform', -128, 256))            # [-128, 128)   -> int8
+    space.register(Integer('i2a', 'uniform', -128, 257))           # [-128, 129)   -> int16
+    space.register(Integer('i2b', 'reciprocal', 1, 1000))          # [1, 1000)     -> int16
+    space.register(Real('x', 'uniform', -1, 2))
+    space.register(Integer('i4', 'uniform', 0, 1000000))           # -> int32
+    space.register(Integer('i8', 'norm', 0, 1e12))                 # unbounded     -> int64
+    space.register(Categorical('c1', list(range(256))))            # -> uint8
+    space.register(Categorical('c2', list(range(257)), shape=2))   # -> uint16
+    space.register(Integer('neg', 'uniform', -40000, 10))          # [-40000, -39990) -> int32
+    return space
+
+
+def test_wire_layout_is_the_narrowest_lossless_one():
+    compiled = _width_space().compiled()
+    assert [dt for _u, dt in compiled.wire_meta] == ['i1', 'i2', 'i2', 'f8', 'i4', 'i8', 'u1', 'u2', 'u2', 'i4']
+    assert compiled.wire_row_bytes == 1 + 2 + 2 + 8 + 4 + 8 + 1 + 2 + 2 + 4
+    units = [u for u, _dt in compiled.wire_meta]
+    assert units == [0, 1, 3, 5, 13, 17, 25, 26, 28, 30]
+    from orion_b200 import spaces
+    assert spaces.mixed64().compiled().wire_row_bytes == 32 * 8 + 16 + 16       # 288 instead of 448
+
+
+@pytest.mark.parametrize('n', [1, 2, 513, 100_003])
+def test_compact_wire_matches_natural_compaction(n):
+    from orion_b200 import spaces
+    for space in (_width_space(), spaces.mixed64()):
+        compiled = space.compiled()
+        batch = compiled.sample(n, 17)
+        assert bool(batch.mask[:n].all())
+        rng = np.random.RandomState(n)
+        for frac in (0.0, 0.89, 1.0):
+            keep_host = (rng.random_sample(n) < frac).astype(np.uint8)
+            keep = torch.from_numpy(keep_host).cuda()
+            wide = batch.compact(keep)
+            wire = batch.compact(keep, wire=True)
+            assert wire.wire and wire.n == wide.n == int(keep_host.sum())
+            assert wire.buf.numel() == compiled.wire_row_bytes * wire.n_stride
+            raw = wire.to_numpy(natural=False)
+            for (u, dt), col in zip(compiled.wire_meta, raw):
+                assert col.dtype == np.dtype(dt)
+            for got, want, narrow in zip(wire.to_numpy(), wide.to_numpy(), raw):
+                assert got.dtype == want.dtype and np.array_equal(got, want)
+                assert np.array_equal(narrow.astype(want.dtype), want)            # lossless
+            for j in range(len(raw)):                                             # typed device views too
+                assert np.array_equal(wire.column(j).cpu().numpy(), raw[j])
