@@ -45,7 +45,12 @@ enum { OB2_DIST_UNIFORM = 0, OB2_DIST_RECIPROCAL = 1, OB2_DIST_NORM = 2, OB2_DIS
         * space_builder.py:156-186); p0 / p1 carry the shape parameter and its reciprocal */
        OB2_DIST_EXPON = 5, OB2_DIST_LOGNORM = 6, OB2_DIST_LOGISTIC = 7, OB2_DIST_LAPLACE = 8, OB2_DIST_GUMBEL_R = 9,
        OB2_DIST_WEIBULL_MIN = 10, OB2_DIST_PARETO = 11, OB2_DIST_RAYLEIGH = 12, OB2_DIST_HALFNORM = 13,
-       OB2_DIST_POWERLAW = 14, OB2_DIST_LAST = 14 };
+       OB2_DIST_POWERLAW = 14,
+       /* the priors of the reference's own DSL examples (space_builder.py:84,98-99: `alpha(.9)`,
+        * `randint(-3, 5)`, `poisson(mu=3)`).  ALPHA: p0 = a, p1 = ndtr(a).  RANDINT: p0 = low,
+        * p1 = high - low, scipy's _ppf verbatim.  POISSON: p0 = mu (<= 500), p1 = exp(-mu); the
+        * smallest k with cdf(k) >= u by summing the pmf. */
+       OB2_DIST_ALPHA = 15, OB2_DIST_RANDINT = 16, OB2_DIST_POISSON = 17, OB2_DIST_LAST = 17 };
 
 /* per-slot transformer (build_required_space table) */
 enum {

@@ -179,7 +179,10 @@ def slot_table(specs: Sequence[DimSpec]) -> List[Tuple[int, int]]:
 
 
 CLOSED_FORM_PRIORS = ('expon', 'lognorm', 'logistic', 'laplace', 'gumbel_r', 'weibull_min', 'pareto',
-                      'rayleigh', 'halfnorm', 'powerlaw')
+                      'rayleigh', 'halfnorm', 'powerlaw',
+                      # the reference's DSL examples (space_builder.py:84,98-99); poisson and randint are
+                      # rv_discrete: rvs adds loc only (scale is 1)
+                      'alpha', 'randint', 'poisson')
 
 
 def _draw(spec: DimSpec, u: np.ndarray) -> np.ndarray:

@@ -95,7 +95,7 @@ __device__ __forceinline__ double u53(uint32_t w0, uint32_t w1) {
     return __ull2double_rn(v) * 1.1102230246251565e-16;  // 2^-53
 }
 
-// The ten extra closed-form priors, out of line and out of the common kernel (EXT = false
+// The extra priors, out of line and out of the common kernel (EXT = false
 // never references it).
 static __device__ __noinline__ double draw_extended(int dist, double p0, double p1, double u) {
     switch (dist) {
@@ -117,8 +117,26 @@ static __device__ __noinline__ double draw_extended(int dist, double p0, double 
             return sqrt(-2.0 * log1p(-u));
         case OB2_DIST_HALFNORM:
             return normcdfinv(0.5 * (1.0 + u));
-        default:  // OB2_DIST_POWERLAW, p1 = 1 / a
+        case OB2_DIST_POWERLAW:  // p1 = 1 / a
             return pow(u, p1);
+        case OB2_DIST_ALPHA:  // p0 = a, p1 = ndtr(a): 1 / (a - ndtri(q * ndtr(a)))
+            return 1.0 / (p0 - normcdfinv(__dmul_rn(u, p1)));
+        case OB2_DIST_RANDINT: {  // p0 = low, p1 = high - low; randint_gen._ppf, operation for operation
+            const double vals = ceil(__dadd_rn(__dmul_rn(u, p1), p0)) - 1.0;
+            const double vals1 = fmin(fmax(vals - 1.0, p0), p0 + p1);
+            const double temp = (floor(vals1) - p0 + 1.0) / p1;
+            return temp >= u ? vals1 : vals;
+        }
+        default: {  // OB2_DIST_POISSON, p0 = mu, p1 = exp(-mu): smallest k with cdf(k) >= u
+            double k = 0.0, pmf = p1, cdf = p1;
+            const double k_max = p0 + 40.0 * sqrt(p0) + 60.0;  // the tail beyond is < 1e-300
+            while (cdf < u && k < k_max) {
+                k += 1.0;
+                pmf *= p0 / k;
+                cdf += pmf;
+            }
+            return k;
+        }
     }
 }
 

@@ -89,6 +89,16 @@ def _prior_params(dim):
         p0 = float(args[0]) if n_shape else 0.0
         p1 = reciprocal_sign / p0 if (n_shape and reciprocal_sign) else 0.0
         return code, p0, p1, loc, scale
+    if name == 'alpha' and len(args) == 1:
+        from scipy.special import ndtr
+        a = float(args[0])
+        return 15, a, float(ndtr(a)), loc, scale
+    if name == 'randint' and len(args) == 2:
+        low, high = float(args[0]), float(args[1])
+        return 16, low, high - low, loc, scale
+    if name == 'poisson' and len(args) == 1 and float(args[0]) <= 500.0:
+        mu = float(args[0])
+        return 17, mu, float(np.exp(-mu)), loc, scale
     # any other scipy prior: bounds-only (contains / transform / dedup work, sampling refuses)
     return _lib.DIST_NONE, 0.0, 0.0, loc, scale
 

@@ -69,10 +69,81 @@ def test_integer_variants_and_bounds():
     assert np.array_equal(so.contains(specs, got), np.ones(n, dtype=bool))
 
 
+DSL_EXAMPLES = [      # the priors of the reference's own DSL examples (space_builder.py:84,98-99)
+    dict(name='a', kind='real', prior='alpha', args=[0.9]),
+    dict(name='a2', kind='real', prior='alpha', args=[2.5, 1.0, 3.0]),
+    dict(name='r', kind='integer', prior='randint', args=[-3, 5]),
+    dict(name='r2', kind='integer', prior='randint', args=[0, 1000], kwargs=dict(loc=7)),
+    dict(name='p', kind='integer', prior='poisson', args=[], kwargs=dict(mu=3)),
+    dict(name='p2', kind='integer', prior='poisson', args=[0.5], kwargs=dict(loc=2)),
+    dict(name='p3', kind='integer', prior='poisson', args=[120.0]),
+]
+
+
+def test_dsl_example_priors_from_uniform():
+    """alpha within 1e-6 of scipy's ppf; randint (scipy's _ppf operation for
+    operation) exact; poisson exact up to pmf-summation ulps at a cdf step."""
+    specs = gu.specs_from_json(DSL_EXAMPLES)
+    space = gu.product_space(DSL_EXAMPLES)
+    rng = np.random.RandomState(1)
+    n = 8192
+    U = rng.random_sample((len(specs), n))
+    U[:, :4] = [0.0, 2.0 ** -53, 0.5, 1 - 2.0 ** -53]
+    U[0:2, 0] = 1e-300                                        # alpha.ppf(0) = 1/inf
+    U[0:2, 3] = 1 - 1e-9      # (beyond that scipy's own formula 1/(a - ndtri(q ndtr(a))) cancels catastrophically)
+    batch = space.compiled().sample_from_uniform(torch.from_numpy(U).cuda())
+    got = batch.to_numpy()
+    want, ok = so.sample_from_uniform(specs, U)
+    for j in (0, 1):
+        np.testing.assert_allclose(got[j], want[j], rtol=1e-6, atol=1e-300)
+        np.testing.assert_allclose(got[j], stats.alpha.ppf(U[j], *DSL_EXAMPLES[j]['args']), rtol=1e-6, atol=1e-300)
+    for j in (2, 3):
+        assert got[j].dtype == np.int64 and np.array_equal(got[j], want[j])
+    for j in (4, 5, 6):
+        assert int((got[j] != want[j]).sum()) <= 1
+    assert int((batch.mask.cpu().numpy().astype(bool) != ok).sum()) <= 1
+
+
+def test_dsl_example_priors_philox_marginals():
+    """Philox mode: the accepted draws follow scipy's distribution conditioned
+    on the dimension's interval (randint(-3, 5) -> [-4, 4): the reference's own
+    interval excludes the top value, space.py:296-319)."""
+    specs = gu.specs_from_json(DSL_EXAMPLES)
+    space = gu.product_space(DSL_EXAMPLES)
+    n = 400_000
+    batch = space.compiled().sample(n, 2024)
+    ok = batch.mask[:n].cpu().numpy().astype(bool)
+    cols = batch.to_numpy()
+    want, failed = so.sample_philox(specs, n, 2024)
+    assert np.array_equal(ok, ~failed)
+    for j, spec in enumerate(DSL_EXAMPLES):
+        args, kw = spec['args'], spec.get('kwargs', {})
+        dist = getattr(stats, spec['prior'])(*args, **kw)
+        x = cols[j][ok]
+        if spec['kind'] == 'real':
+            p = stats.kstest(x, dist.cdf).pvalue
+        else:
+            lo, hi = so.dim_interval(specs[j])
+            top = min(hi, dist.ppf(1 - 1e-12) + 1)
+            ks = np.arange(max(lo, dist.ppf(0) + 1 if np.isinf(lo) else lo), top)
+            pmf = dist.pmf(ks)
+            ks, pmf = ks[pmf > 0], pmf[pmf > 0]
+            exp = pmf / pmf.sum() * len(x)                              # conditioned on the interval
+            obs = np.array([(x == k).sum() for k in ks], dtype=np.float64)
+            assert obs.sum() == len(x)                                   # nothing outside the interval
+            big = exp >= 5                                               # pool the sparse tail
+            if (~big).any():
+                obs = np.append(obs[big], obs[~big].sum())
+                exp = np.append(exp[big], exp[~big].sum())
+            p = stats.chisquare(obs, exp).pvalue
+            assert int((cols[j] != want[j]).sum()) <= 1
+        assert p > 1e-3 / len(DSL_EXAMPLES), '%s: p = %g' % (spec['name'], p)
+
+
 def test_unsupported_prior_still_refuses():
     from orion_b200.space import Real, Space
     space = Space()
-    space.register(Real('a', 'alpha', 0.9))
+    space.register(Real('a', 'gamma', 2.0))
     assert (3.5,) in space
     with pytest.raises(NotImplementedError):
         space.sample(1)
