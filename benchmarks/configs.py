@@ -44,6 +44,16 @@ def main():
     dt = time.perf_counter() - t0
     out['config1_rosen2_suggest10_x100'] = {'seconds': dt, 'candidates_per_s': 1000 / dt, 'best_objective': best,
                                             'note': 'list-of-tuples API: launch + D2H + Python tuples per call'}
+    space = spaces.rosen2()
+    for label, fn in (('space.sample(10)', lambda: space.sample(10)),
+                      ('space.sample(1)', lambda: space.sample(1)),
+                      ('points in space (10)', lambda: space.contains_points(pts)),
+                      ('mixed64.sample(10)', lambda m=spaces.mixed64(): m.sample(10))):
+        fn()
+        t0 = time.perf_counter()
+        for _ in range(300):
+            fn()
+        out['config1_us_per_call ' + label] = (time.perf_counter() - t0) / 300 * 1e6
     # config 2: Space.sample 1M points, real16
     c = spaces.real16().compiled()
     for n in (1_000_000, 100_000_000):

@@ -149,6 +149,25 @@ int ob2_suggest(const ob2_space *space, int64_t n, int64_t n_stride, uint64_t se
                 uint64_t base_index, const uint64_t *index, void *cols, void *tcols, void *back,
                 uint8_t *mask, uint64_t *fp, uint32_t *n_failed, void *stream);
 
+/* Space.sample(n) for the small n the reference's own callers ask for (Producer.produce ->
+ * suggest(pool_size), src/orion/core/worker/producer.py:45; DimensionBuilder's warm-up draw,
+ * src/orion/core/io/space_builder.py:205): the same draw as ob2_sample, delivered into HOST
+ * memory.  host_cols receives the column block with n_stride = n rounded up to 32
+ * (ob2_space_row_bytes * n_stride bytes); host_n_failed the n_slots rejection counters.
+ * Synchronous.  The first call on a space allocates a staging block (device + pinned host,
+ * row_bytes * OB2_HOST_SAMPLE_MAX bytes each) that lives until ob2_space_destroy; concurrent
+ * calls on one space serialise. */
+#define OB2_HOST_SAMPLE_MAX 4096
+int ob2_sample_host(ob2_space *space, int64_t n, uint64_t seed, uint64_t base_index, void *host_cols,
+                    uint32_t *host_n_failed, void *stream);
+
+/* Space.__contains__ for a handful of HOST points (PrimaryAlgo.suggest / observe / score /
+ * judge check every point, src/orion/core/worker/primary_algo.py:53-54,64-66,78-84):
+ * host_cols is a column block with n_stride = n rounded up to 32 (as ob2_contains takes it on
+ * the device), host_mask receives n verdicts.  Same staging block and limits as ob2_sample_host. */
+int ob2_contains_host(ob2_space *space, int64_t n, const void *host_cols, int32_t int_as_f64,
+                      uint8_t *host_mask, void *stream);
+
 /* Parity mode of the same kernel: uniforms are read from U[S][n_stride] (one
  * attempt, no redraw); ok[i] = every Real/Integer slot landed in bounds. */
 int ob2_sample_from_uniform(const ob2_space *space, int64_t n, int64_t n_stride,

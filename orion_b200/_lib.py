@@ -19,6 +19,7 @@ SLOT_CAT_UNIFORM = 2
 SET_SLOT_BYTES = 32
 SET_HEADER_BYTES = 256
 STATIC_DEDUP_MAX = 1 << 20
+HOST_SAMPLE_MAX = 4096
 
 
 class Ob2Error(RuntimeError):
@@ -61,6 +62,8 @@ SIGNATURES = {
     'ob2_sample': (ctypes.c_int, [_vp, _i64, _i64, _u64, _u64, _vp, _vp, _vp, _vp, _vp, _vp]),
     'ob2_sample_transform': (ctypes.c_int, [_vp, _i64, _i64, _u64, _u64, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     'ob2_suggest': (ctypes.c_int, [_vp, _i64, _i64, _u64, _u64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    'ob2_sample_host': (ctypes.c_int, [_vp, _i64, _u64, _u64, _vp, _vp, _vp]),
+    'ob2_contains_host': (ctypes.c_int, [_vp, _i64, _vp, _i32, _vp, _vp]),
     'ob2_sample_from_uniform': (ctypes.c_int, [_vp, _i64, _i64, _vp, _vp, _vp, _vp, _vp]),
     'ob2_contains': (ctypes.c_int, [_vp, _i64, _i64, _vp, _i32, _vp, _vp]),
     'ob2_transform': (ctypes.c_int, [_vp, _i64, _i64, _vp, _vp, _vp]),

@@ -5,6 +5,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <mutex>
+
 #include "ob2.h"
 
 // ---------------------------------------------------------------- host side
@@ -17,6 +19,10 @@ struct ob2_space {
     int64_t wire_row_bytes;  // bytes per candidate in the narrowed host hand-off layout (ob2_compact_wire)
     int32_t *wire_units;     // host: per slot, byte offset per row of its wire column
     int32_t *wire_bytes;     // host: per slot, element size of its wire column (1, 2, 4 or 8)
+    // ob2_sample_host: one device block and its pinned mirror, allocated on first use
+    // ([columns: row_bytes * OB2_HOST_SAMPLE_MAX][n_failed: n_slots u32]); calls serialise on the mutex
+    void *d_stage, *h_stage;
+    std::mutex *stage_mutex;
     int32_t t_cols;      // number of transformed columns
     size_t smem_bytes;   // descriptor + cdf staging size
     ob2_slot_desc *d_slots;

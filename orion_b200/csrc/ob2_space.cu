@@ -150,11 +150,13 @@ extern "C" int ob2_space_create(const ob2_slot_desc *slots, int32_t n_slots, con
     sp->has_extended_prior = extended;
     sp->d_slots = nullptr;
     sp->d_cdf = nullptr;
+    sp->d_stage = sp->h_stage = nullptr;
+    sp->stage_mutex = new (std::nothrow) std::mutex();
     // the device copy of the table carries the wire layout in `reserved`: (offset units << 4) | element bytes
     ob2_slot_desc *staged = new (std::nothrow) ob2_slot_desc[n_slots];
     sp->wire_units = new (std::nothrow) int32_t[n_slots];
     sp->wire_bytes = new (std::nothrow) int32_t[n_slots];
-    if (staged == nullptr || sp->wire_units == nullptr || sp->wire_bytes == nullptr) {
+    if (staged == nullptr || sp->wire_units == nullptr || sp->wire_bytes == nullptr || sp->stage_mutex == nullptr) {
         delete[] staged;
         ob2_space_destroy(sp);
         ob2_set_error("out of host memory");
@@ -192,6 +194,9 @@ extern "C" void ob2_space_destroy(ob2_space *sp) {
     if (sp == nullptr) return;
     if (sp->d_slots) cudaFree(sp->d_slots);
     if (sp->d_cdf) cudaFree(sp->d_cdf);
+    if (sp->d_stage) cudaFree(sp->d_stage);
+    if (sp->h_stage) cudaFreeHost(sp->h_stage);
+    delete sp->stage_mutex;
     delete[] sp->wire_units;
     delete[] sp->wire_bytes;
     delete sp;

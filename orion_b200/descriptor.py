@@ -31,6 +31,7 @@ _OPS = {
 }
 
 _M64 = (1 << 64) - 1
+_ELEM = {'f8': 8, 'i8': 8, 'i4': 4}
 
 
 def _splitmix64(x):
@@ -192,6 +193,13 @@ class CompiledSpace(object):
                 col_units += elem
                 t_units += t_elem * width
         self.n_slots = len(slots)
+        self.dim_widths = [b - a for a, b in zip(self.dim_first, self.dim_first[1:] + [len(slots)])]
+        self._col_runs = []                                 # (first column's units, dtype, number of columns)
+        for units, dt in self.col_meta:
+            if self._col_runs and self._col_runs[-1][1] == dt:
+                self._col_runs[-1][2] += 1
+            else:
+                self._col_runs.append([units, dt, 1])
         self.n_tcols = len(self.tcol_meta)
         self.row_bytes = col_units
         self.trow_bytes = t_units
@@ -201,6 +209,7 @@ class CompiledSpace(object):
         with torch.cuda.device(self.device):
             _lib.check(self.lib.ob2_space_create(arr, self.n_slots, cdf_arr, len(cdf), ctypes.byref(handle)))
         self.handle = handle
+        self._host_cols = self._host_failed = None      # sample_host's reusable host block
         assert self.lib.ob2_space_row_bytes(handle) == self.row_bytes
         assert self.lib.ob2_space_trow_bytes(handle) == self.trow_bytes
         # the narrowed host hand-off layout (ob2_compact_wire): the library decides it, we only read it
@@ -312,6 +321,41 @@ class CompiledSpace(object):
         tb.n = n
         back.n = n
         return batch, tb, back
+
+    def sample_host(self, n, seed, base_index=0):
+        """Small draws (n <= ``_lib.HOST_SAMPLE_MAX``) delivered as host columns
+        by ONE library call (``ob2_sample_host``: kernel, copy and sync inside).
+        Returns (list of numpy columns, n_failed numpy array)."""
+        self._require_samplable()
+        n = int(n)
+        ns = round_up(max(n, 1))
+        if self._host_cols is None:
+            self._host_cols = np.empty(self.row_bytes * _lib.HOST_SAMPLE_MAX, dtype=np.uint8)
+            self._host_failed = np.empty(self.n_slots, dtype=np.uint32)
+        host = self._host_cols
+        _lib.check(self.lib.ob2_sample_host(self.handle, n, int(seed) & _M64, int(base_index) & _M64,
+                                            host.ctypes.data, self._host_failed.ctypes.data, self._stream()))
+        blk = host[:self.row_bytes * ns].copy()             # the caller's own copy; the columns are views of it
+        cols = []
+        for units, dt, count in self._col_runs:             # adjacent columns of one dtype: one 2-D view per run
+            e = _ELEM[dt]
+            cols.extend(blk[units * ns:(units + e * count) * ns].view(dt).reshape(count, ns)[:, :n])
+        return cols, self._host_failed
+
+    def contains_host(self, cols, n, int_as_f64=True):
+        """``point in space`` for n <= ``_lib.HOST_SAMPLE_MAX`` host rows given as
+        columns (Integer columns as float64 when ``int_as_f64``), by ONE library
+        call (``ob2_contains_host``).  Returns a bool numpy array [n]."""
+        ns = round_up(max(int(n), 1))
+        host = np.zeros(self.row_bytes * ns, dtype=np.uint8)
+        for (units, dt), col in zip(self.col_meta, cols):
+            want = np.float64 if (int_as_f64 and dt == 'i8') else dt
+            arr = np.ascontiguousarray(col, dtype=want)
+            host[units * ns:units * ns + arr.nbytes] = arr.view(np.uint8)
+        mask = np.empty(max(int(n), 1), dtype=np.uint8)
+        _lib.check(self.lib.ob2_contains_host(self.handle, int(n), host.ctypes.data, 1 if int_as_f64 else 0,
+                                              mask.ctypes.data, self._stream()))
+        return mask[:n].astype(bool)
 
     def _require_samplable(self):
         if self.unsamplable is not None:

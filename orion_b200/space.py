@@ -24,6 +24,7 @@ import numpy
 from scipy._lib._util import check_random_state
 from scipy.stats import distributions
 
+from ._lib import HOST_SAMPLE_MAX
 from .columns import ColumnBatch
 from .descriptor import compile_space
 
@@ -118,9 +119,13 @@ class Dimension(object):
         the same values come back; pass a RandomState to advance.
         """
         compiled = self._compiled()
-        batch = compiled.sample(n_samples, philox_key(seed), with_mask=False)
-        _raise_if_improbable(batch, [self])
-        cols = batch.to_numpy()
+        if n_samples <= HOST_SAMPLE_MAX:            # one library call: kernel + copy + sync
+            cols, failed = compiled.sample_host(n_samples, philox_key(seed))
+            _raise_if_failed(failed, compiled, [self])
+        else:
+            batch = compiled.sample(n_samples, philox_key(seed), with_mask=False)
+            _raise_if_improbable(batch, [self])
+            cols = batch.to_numpy()
         return [self._from_columns(cols, i) for i in range(n_samples)]
 
     def interval(self, alpha=1.0):
@@ -132,8 +137,7 @@ class Dimension(object):
         if vals is None:
             return False
         compiled = self._compiled()
-        batch = ColumnBatch.from_numpy(compiled, [numpy.asarray([v]) for v in vals], int_as_f64=True)
-        return bool(compiled.contains(batch, int_as_f64=True)[0].item())
+        return bool(compiled.contains_host([numpy.asarray([v]) for v in vals], 1, int_as_f64=True)[0])
 
     def __repr__(self):
         return "{0}(name={1}, prior={{{2}: {3}, {4}}}, shape={5})".format(
@@ -250,11 +254,14 @@ class Categorical(Dimension):
 def _raise_if_improbable(batch, dims):
     """Surface the device's rejection counters as the reference's ValueError
     (space.py:272-274).  One small device->host read."""
-    failed = batch.n_failed.cpu().numpy()
+    _raise_if_failed(batch.n_failed.cpu().numpy(), batch.compiled, dims)
+
+
+def _raise_if_failed(failed, compiled, dims):
     if not failed.any():
         return
     first_slot = int(numpy.nonzero(failed)[0][0])
-    d_idx = batch.compiled.dim_first.index(first_slot)
+    d_idx = compiled.dim_first.index(first_slot)
     dim = dims[d_idx]
     raise ValueError("Improbable bounds: (low={0}, high={1}). "
                      "Please make interval larger.".format(dim._low, dim._high))
@@ -290,6 +297,11 @@ class Space(OrderedDict):
         order (space.py:456-484)."""
         if not self:
             return []
+        if n_samples <= HOST_SAMPLE_MAX:            # one library call: kernel + copy + sync
+            compiled = self.compiled()
+            cols, failed = compiled.sample_host(n_samples, philox_key(seed))
+            _raise_if_failed(failed, compiled, list(self.values()))
+            return self.rows_from_columns(cols, n_samples)
         batch = self.sample_columns(n_samples, seed)
         return self.rows_from_columns(batch.to_numpy(), n_samples)
 
@@ -298,19 +310,55 @@ class Space(OrderedDict):
         per_dim = []
         s = 0
         for dim in self.values():
-            k = int(numpy.prod(dim.shape, dtype=numpy.int64)) if dim.shape else 1
+            if dim.shape == ():                 # a whole column at once (numpy scalars, like scipy's rvs)
+                col = host_cols[s][:n]
+                if dim.type == 'categorical':
+                    cats = dim.categories
+                    per_dim.append([cats[c] for c in col.tolist()])
+                else:
+                    per_dim.append(list(col))
+                s += 1
+                continue
+            k = int(numpy.prod(dim.shape, dtype=numpy.int64))
             cols = host_cols[s:s + k]
             per_dim.append([dim._from_columns(cols, i) for i in range(n)])
             s += k
         return list(zip(*per_dim))
+
+    @staticmethod
+    def _columns_of_scalar_rows(dims, points, n):
+        """The common case -- every dimension scalar, every point a full row of
+        plain scalars -- column by column; None when anything is unusual (the
+        general loop then decides row by row)."""
+        if any(d.shape != () for d in dims) or any(len(p) != len(dims) for p in points):
+            return None
+        cols = []
+        for j, dim in enumerate(dims):
+            vals = [p[j] for p in points]
+            if dim.type == 'categorical':
+                if any(isinstance(v, (numpy.ndarray, list, tuple)) for v in vals):
+                    return None
+                cols.append(numpy.fromiter((dim._index_of(v) for v in vals), dtype=numpy.int32, count=n))
+            else:
+                try:
+                    col = numpy.asarray(vals, dtype=numpy.float64)
+                except (TypeError, ValueError):
+                    return None
+                if col.shape != (n,):
+                    return None
+                cols.append(col)
+        return cols
 
     def columns_from_rows(self, points):
         """List of tuples -> (host columns, row_ok) where row_ok[i] is False
         when row i has the wrong arity or a mis-shaped value.  Integer values
         travel as float64 so the device can check integrality."""
         dims = list(self.values())
-        widths = [int(numpy.prod(d.shape, dtype=numpy.int64)) if d.shape else 1 for d in dims]
         n = len(points)
+        fast = self._columns_of_scalar_rows(dims, points, n)
+        if fast is not None:
+            return fast, numpy.ones(n, dtype=bool)
+        widths = [int(numpy.prod(d.shape, dtype=numpy.int64)) if d.shape else 1 for d in dims]
         row_ok = numpy.ones(n, dtype=bool)
         cols = [numpy.zeros(n, dtype=numpy.int32 if d.type == 'categorical' else numpy.float64)
                 for d, w in zip(dims, widths) for _ in range(w)]
@@ -343,8 +391,11 @@ class Space(OrderedDict):
             return [False] * len(points)
         cols, row_ok = self.columns_from_rows(points)
         compiled = self.compiled()
-        batch = ColumnBatch.from_numpy(compiled, cols, int_as_f64=True)
-        mask = compiled.contains(batch, int_as_f64=True).cpu().numpy().astype(bool)
+        if len(points) <= HOST_SAMPLE_MAX:          # one library call: copy in, kernel, copy out, sync
+            mask = compiled.contains_host(cols, len(points), int_as_f64=True)
+        else:
+            batch = ColumnBatch.from_numpy(compiled, cols, int_as_f64=True)
+            mask = compiled.contains(batch, int_as_f64=True).cpu().numpy().astype(bool)
         return list(mask & row_ok)
 
     def interval(self, alpha=1.0):

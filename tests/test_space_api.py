@@ -213,9 +213,12 @@ class TestInteger(object):
 
     @gpu
     def test_unsupported_prior_has_no_cpu_fallback(self):
-        dim = Integer('yolo', 'poisson', 5)
+        dim = Integer('yolo', 'binom', 10, 0.5)
+        assert 3 in dim
         with pytest.raises(NotImplementedError):
             dim.sample()
+        draws = Integer('yolo', 'poisson', 5).sample(50, seed=1)         # this one has a device inverse CDF
+        assert all(int(x) == x and x >= 0 for x in draws) and len(set(draws)) > 3
 
 
 class TestCategorical(object):
