@@ -161,6 +161,12 @@ int ob2_suggest(const ob2_space *space, int64_t n, int64_t n_stride, uint64_t se
 int ob2_sample_host(ob2_space *space, int64_t n, uint64_t seed, uint64_t base_index, void *host_cols,
                     uint32_t *host_n_failed, void *stream);
 
+/* ob2_sample_host plus the producer's dedup: the drawn rows are
+ * fingerprinted and deduplicated against `set` (ob2_set_dedup semantics: kept rows join the
+ * set); host_keep receives n verdicts.  One kernel sequence, one copy, one synchronisation. */
+int ob2_sample_dedup_host(ob2_space *space, ob2_set *set, int64_t n, uint64_t seed, uint64_t base_index,
+                          void *host_cols, uint8_t *host_keep, uint32_t *host_n_failed, void *stream);
+
 /* Space.__contains__ for a handful of HOST points (PrimaryAlgo.suggest / observe / score /
  * judge check every point, src/orion/core/worker/primary_algo.py:53-54,64-66,78-84):
  * host_cols is a column block with n_stride = n rounded up to 32 (as ob2_contains takes it on

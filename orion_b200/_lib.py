@@ -63,6 +63,7 @@ SIGNATURES = {
     'ob2_sample_transform': (ctypes.c_int, [_vp, _i64, _i64, _u64, _u64, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     'ob2_suggest': (ctypes.c_int, [_vp, _i64, _i64, _u64, _u64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     'ob2_sample_host': (ctypes.c_int, [_vp, _i64, _u64, _u64, _vp, _vp, _vp]),
+    'ob2_sample_dedup_host': (ctypes.c_int, [_vp, _vp, _i64, _u64, _u64, _vp, _vp, _vp, _vp]),
     'ob2_contains_host': (ctypes.c_int, [_vp, _i64, _vp, _i32, _vp, _vp]),
     'ob2_sample_from_uniform': (ctypes.c_int, [_vp, _i64, _i64, _vp, _vp, _vp, _vp, _vp]),
     'ob2_contains': (ctypes.c_int, [_vp, _i64, _i64, _vp, _i32, _vp, _vp]),

@@ -11,6 +11,8 @@ Mirror of ``src/orion/algo/random.py:15-41`` (``suggest(num)`` =
 """
 import numpy
 
+from .._lib import HOST_SAMPLE_MAX
+from ..space import _raise_if_failed, philox_key
 from .base import BaseAlgorithm
 
 
@@ -49,9 +51,15 @@ class Random(BaseAlgorithm):
             need = num - len(points)
             if need <= 0:
                 break
-            batch = self.suggest_columns(need)
-            keep = batch.keep[:batch.n].cpu().numpy().astype(bool)
-            rows = self.space.rows_from_columns(batch.to_numpy(), batch.n)
+            if need <= HOST_SAMPLE_MAX:                 # draw + dedup + copy + sync in one library call
+                compiled = self.space.compiled()
+                cols, failed, keep = compiled.sample_host(need, philox_key(self._rng), history=self.history)
+                _raise_if_failed(failed, compiled, list(self.space.values()))
+                rows = self.space.rows_from_columns(cols, need)
+            else:
+                batch = self.suggest_columns(need)
+                keep = batch.keep[:batch.n].cpu().numpy().astype(bool)
+                rows = self.space.rows_from_columns(batch.to_numpy(), batch.n)
             points.extend(r for r, k in zip(rows, keep) if k)
         return points[:num]
 

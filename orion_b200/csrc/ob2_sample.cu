@@ -452,13 +452,16 @@ extern "C" int ob2_suggest(const ob2_space *space, int64_t n, int64_t n_stride, 
 }
 
 namespace {
+size_t stage_counter_bytes(const ob2_space *space) {
+    return ((size_t)space->n_slots * sizeof(uint32_t) + 255) / 256 * 256;
+}
+
 // staging block of the *_host entry points: [columns of up to OB2_HOST_SAMPLE_MAX rows][counters or mask]
 int ensure_stage(ob2_space *space) {
     if (space->d_stage != nullptr) return OB2_OK;
-    const size_t tail = (size_t)space->n_slots * sizeof(uint32_t) > OB2_HOST_SAMPLE_MAX
-                            ? (size_t)space->n_slots * sizeof(uint32_t)
-                            : (size_t)OB2_HOST_SAMPLE_MAX;
-    const size_t bytes = (size_t)space->row_bytes * OB2_HOST_SAMPLE_MAX + tail;
+    // behind the columns: rejection counters, then per row a verdict byte, a fingerprint and a scratch word
+    const size_t bytes = (size_t)space->row_bytes * OB2_HOST_SAMPLE_MAX + stage_counter_bytes(space) +
+                         (size_t)OB2_HOST_SAMPLE_MAX * (1 + 16 + 4);
     OB2_CUDA(cudaMalloc(&space->d_stage, bytes));
     const int rc = ob2_check_cuda(cudaMallocHost(&space->h_stage, bytes), "cudaMallocHost(stage)");
     if (rc != OB2_OK) {
@@ -506,6 +509,51 @@ extern "C" int ob2_sample_host(ob2_space *space, int64_t n, uint64_t seed, uint6
     OB2_CUDA(cudaStreamSynchronize(st));
     memcpy(host_cols, h, used);
     memcpy(host_n_failed, h + used, fail_bytes);
+    return OB2_OK;
+}
+
+// Random.suggest with the producer's dedup for a handful of points: draw, fingerprint, dedup
+// against the history set, and bring columns + verdicts + counters back with ONE copy.
+extern "C" int ob2_sample_dedup_host(ob2_space *space, ob2_set *set, int64_t n, uint64_t seed, uint64_t base_index,
+                                     void *host_cols, uint8_t *host_keep, uint32_t *host_n_failed, void *stream) {
+    if (space == nullptr || set == nullptr || host_cols == nullptr || host_keep == nullptr || host_n_failed == nullptr) {
+        ob2_set_error("ob2_sample_dedup_host: null argument");
+        return OB2_EINVAL;
+    }
+    if (n < 0 || n > OB2_HOST_SAMPLE_MAX) {
+        ob2_set_error("ob2_sample_dedup_host: n = %lld outside [0, %d]; use ob2_sample + ob2_set_dedup for bulk",
+                      (long long)n, (int)OB2_HOST_SAMPLE_MAX);
+        return OB2_ETOOBIG;
+    }
+    const size_t fail_bytes = (size_t)space->n_slots * sizeof(uint32_t);
+    if (n == 0) {
+        memset(host_n_failed, 0, fail_bytes);
+        return OB2_OK;
+    }
+    const int64_t n_stride = (n + 31) / 32 * 32;
+    int rc = ob2_check_batch(space, n, n_stride);
+    if (rc != OB2_OK) return rc;
+    std::lock_guard<std::mutex> lock(*space->stage_mutex);
+    rc = ensure_stage(space);
+    if (rc != OB2_OK) return rc;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    char *d = static_cast<char *>(space->d_stage), *h = static_cast<char *>(space->h_stage);
+    const size_t used = (size_t)space->row_bytes * n_stride, counters = stage_counter_bytes(space);
+    uint32_t *d_failed = reinterpret_cast<uint32_t *>(d + used);
+    uint8_t *d_keep = reinterpret_cast<uint8_t *>(d + used + counters);
+    uint64_t *d_fp = reinterpret_cast<uint64_t *>(d + used + counters + n_stride);
+    uint32_t *d_scratch = reinterpret_cast<uint32_t *>(d + used + counters + n_stride + 16 * n_stride);
+    OB2_CUDA(cudaMemsetAsync(d_failed, 0, fail_bytes, st));
+    const SampleArgs a{space, n, n_stride, seed, base_index, nullptr, nullptr, d, nullptr, nullptr, nullptr, d_fp, d_failed, st};
+    rc = launch_sample<true>(a);
+    if (rc != OB2_OK) return rc;
+    rc = ob2_set_dedup(set, n, d_fp, nullptr, d_scratch, d_keep, st);
+    if (rc != OB2_OK) return rc;
+    OB2_CUDA(cudaMemcpyAsync(h, d, used + counters + (size_t)n_stride, cudaMemcpyDeviceToHost, st));
+    OB2_CUDA(cudaStreamSynchronize(st));
+    memcpy(host_cols, h, used);
+    memcpy(host_n_failed, h + used, fail_bytes);
+    memcpy(host_keep, h + used + counters, (size_t)n);
     return OB2_OK;
 }
 

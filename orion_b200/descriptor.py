@@ -322,10 +322,12 @@ class CompiledSpace(object):
         back.n = n
         return batch, tb, back
 
-    def sample_host(self, n, seed, base_index=0):
+    def sample_host(self, n, seed, base_index=0, history=None):
         """Small draws (n <= ``_lib.HOST_SAMPLE_MAX``) delivered as host columns
         by ONE library call (``ob2_sample_host``: kernel, copy and sync inside).
-        Returns (list of numpy columns, n_failed numpy array)."""
+        Returns (list of numpy columns, n_failed numpy array); with ``history``
+        (a TrialHistory) the rows are also deduplicated against it
+        (``ob2_sample_dedup_host``) and a bool keep array is returned third."""
         self._require_samplable()
         n = int(n)
         ns = round_up(max(n, 1))
@@ -333,13 +335,27 @@ class CompiledSpace(object):
             self._host_cols = np.empty(self.row_bytes * _lib.HOST_SAMPLE_MAX, dtype=np.uint8)
             self._host_failed = np.empty(self.n_slots, dtype=np.uint32)
         host = self._host_cols
-        _lib.check(self.lib.ob2_sample_host(self.handle, n, int(seed) & _M64, int(base_index) & _M64,
-                                            host.ctypes.data, self._host_failed.ctypes.data, self._stream()))
+        keep = None
+        if history is not None:         # draw + fingerprint + dedup against the history, still one call
+            keep = np.empty(max(n, 1), dtype=np.uint8)
+            rc = self.lib.ob2_sample_dedup_host(self.handle, history.handle, n, int(seed) & _M64,
+                                                int(base_index) & _M64, host.ctypes.data, keep.ctypes.data,
+                                                self._host_failed.ctypes.data, self._stream())
+            if rc == -4 and history.auto_grow:      # set full (refused before anything was touched)
+                history.grow()
+                return self.sample_host(n, seed, base_index, history)
+            _lib.check(rc)
+            keep = keep[:n].astype(bool)
+        else:
+            _lib.check(self.lib.ob2_sample_host(self.handle, n, int(seed) & _M64, int(base_index) & _M64,
+                                                host.ctypes.data, self._host_failed.ctypes.data, self._stream()))
         blk = host[:self.row_bytes * ns].copy()             # the caller's own copy; the columns are views of it
         cols = []
         for units, dt, count in self._col_runs:             # adjacent columns of one dtype: one 2-D view per run
             e = _ELEM[dt]
             cols.extend(blk[units * ns:(units + e * count) * ns].view(dt).reshape(count, ns)[:, :n])
+        if history is not None:
+            return cols, self._host_failed, keep
         return cols, self._host_failed
 
     def contains_host(self, cols, n, int_as_f64=True):

@@ -90,3 +90,43 @@ def test_points_in_space_small_and_bulk_agree():
     assert space.contains_points(many) == small * ((_lib.HOST_SAMPLE_MAX // 40) + 2)
     assert pts[0] in space and pts[3] not in space
     assert pts[0][0] in space['u0'] if 'u0' in space else True
+
+
+def test_sample_dedup_host_equals_tensor_path():
+    """ob2_sample_dedup_host == sample + fingerprint + TrialHistory.dedup."""
+    from orion_b200.history import TrialHistory
+    from orion_b200.space import Categorical, Integer, Space
+    space = Space()                                  # small discrete space: duplicates are certain
+    space.register(Integer('i', 'uniform', 0, 6))
+    space.register(Categorical('c', ['a', 'b', 'c']))
+    compiled = space.compiled()
+    h_host, h_dev = TrialHistory(space, capacity=4096), TrialHistory(space, capacity=4096)
+    for call, n in enumerate([1, 7, 64, 500]):
+        cols, failed, keep = compiled.sample_host(n, 100 + call, history=h_host)
+        batch = compiled.sample(n, 100 + call, with_fingerprint=True)
+        want_keep = h_dev.dedup(batch).cpu().numpy().astype(bool)
+        assert keep.dtype == bool and np.array_equal(keep, want_keep)
+        for a, b in zip(cols, batch.to_numpy()):
+            assert np.array_equal(a, b)
+        assert not failed.any()
+        assert len(h_host) == len(h_dev)
+    assert len(h_host) == 18                         # every (i, c) pair seen, each kept exactly once
+
+
+def test_random_suggest_with_dedup_small_calls():
+    from orion_b200.algo.random import Random
+    from orion_b200.space import Categorical, Integer, Space
+    space = Space()
+    space.register(Integer('i', 'uniform', 0, 6))
+    space.register(Categorical('c', ['a', 'b', 'c']))
+    algo = Random(space, seed=5, dedup=True)
+    seen = []
+    for _ in range(6):
+        pts = algo.suggest(3)
+        assert len(pts) == 3 and all(p in space for p in pts)
+        seen.extend((int(p[0]), p[1]) for p in pts)
+    assert len(set(seen)) == 18                      # never the same point twice: the space is exhausted exactly
+    assert algo.suggest(1) == []                     # nothing new left (bounded top-up gives up)
+    auto = Random(space, seed=5, dedup=True, history_capacity=8)
+    auto.history.auto_grow = True
+    assert len(auto.suggest(12)) == 12               # the tiny table grows instead of failing
