@@ -5,9 +5,12 @@
     python bench.py --impl reference --gpus N --steps K ...  # CPU arm (oracle port of the reference path)
 
 One "step" = one pass of the whole path over one batch of synthetic candidates
-of the `mixed64` space: sample (Philox, fused bounds check and
-fingerprint) -> transform('real') -> reverse -> dedup against the history
-shard.  Per GPU a step processes CANDS_PER_GPU candidates against a history
+of the `mixed64` space: sample (Philox, fused bounds check) ->
+transform('real') -> reverse -> fingerprint -> dedup against the history shard.
+By default the first four stages are ONE kernel (ob2_suggest: every stage's
+result is still written to HBM, nothing is read back); `--staged` runs them as
+separate kernels, and the default JSON line carries that path's timings too
+(`staged_path`).  Per GPU a step processes CANDS_PER_GPU candidates against a history
 shard of HISTORY_PER_GPU rows; at 8 GPUs that is exactly BASELINE.json config 5
 (1e8 candidates vs 1e9-row history) with config 3's transform chain on top.
 10 % of each batch are planted duplicates of history rows and 1 % duplicates of

@@ -1,18 +1,24 @@
 """Stream-pipelined candidate generation: the whole hot path, batch after batch.
 
-One batch goes through three kernels groups with different limits on a B200:
+``fingerprint_in='suggest'`` (what ``bench.py`` times): one kernel per batch
+(``ob2_suggest``: sample + contains + transform + reverse + fingerprint, at the
+HBM write ceiling) on one stream, dedup (+ exchange) on a second one.
 
-  A  sample + transform       (``ob2_sample_transform``)       instruction-issue bound
+The staged modes are for algorithms that compute in the transformed space
+between transform and reverse; a batch then goes through three kernel groups
+with different limits on a B200:
+
+  A  sample + transform       (``ob2_sample_transform``)       HBM writes / instruction issue
   B  reverse + fingerprint    (``ob2_reverse_fingerprint``)    HBM bound
-  C  dedup (+ exchange)       (``ob2_set_dedup``, NCCL / peer)  DRAM-latency bound
+  C  dedup (+ exchange)       (``ob2_set_dedup``, NCCL / peer)  random DRAM access
 
-The fingerprint arithmetic costs the issue-bound sampler 17 % but is free in
-the bandwidth-bound reverse, so by default B computes it (over the rows it
+The fingerprint arithmetic costs the sampler 17 % but is free in the
+bandwidth-bound reverse, so with ``'reverse'`` B computes it (over the rows it
 writes: the candidates as they are handed out) and C follows B.  A of the next
-batch depends on neither, so the three groups run on three CUDA streams with
-events for the true dependencies (and for buffer reuse).  With ``depth`` >= 2 buffer sets, A of
-batch k+1 overlaps B and C of batch k: the issue-bound and the bandwidth-bound
-work share the SMs instead of taking turns.
+batch depends on neither, so the groups run on three CUDA streams with events
+for the true dependencies (and for buffer reuse).  With ``depth`` >= 2 buffer
+sets, A of batch k+1 overlaps B and C of batch k -- which buys little: all of
+them saturate the same memory system.
 
 This is the producer loop of the reference (``Producer.produce`` ->
 ``PrimaryAlgo.suggest`` -> ``Random.suggest`` -> ``Space.sample``,
