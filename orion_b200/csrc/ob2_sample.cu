@@ -1,17 +1,19 @@
 // K1: candidate sampling (Philox4x32-10 or injected uniforms -> per-slot
 // inverse CDF), fused with the bounds check, the <=4-attempt rejection, the row
-// fingerprint and -- optionally -- the transform chain; and the standalone
-// Space.__contains__ kernel.
+// fingerprint and -- optionally -- the transform chain and its reverse (the
+// one-kernel ob2_suggest); the standalone Space.__contains__ kernel; and the
+// *_host entry points for the small calls the reference's callers make.
 //
 // Mapping: one thread owns OB2_CPT = 2 consecutive candidates and walks the
 // slots in space order.  At any instant a warp therefore works on ONE slot
 // (no divergence on the prior / kind switch) and stores 32 x 16 B = 512
 // contiguous bytes of that slot's column.  Output is columnar [S][n_stride].
 //
-// The sampler is instruction-issue bound (Philox + fp64 inverse CDFs +
-// fingerprint multiplies, ~10k instructions per candidate) while the transform
-// is pure store bandwidth; fusing them (WITH_T) lets the one-hot stores ride
-// under the arithmetic and saves re-reading the sampled columns.
+// On its own the sampler is instruction-issue bound (Philox + fp64 inverse CDFs
+// + fingerprint multiplies, ~8-10k instructions per candidate of mixed64) while
+// transform and reverse are pure memory traffic; fusing them in (WITH_T, WITH_B)
+// lets the stores ride under the arithmetic and removes every re-read: the fused
+// kernel ends up at the HBM write ceiling (profiles/r1g_full_suggest.md).
 #include <cstring>
 
 #include "ob2_internal.cuh"
