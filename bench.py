@@ -53,6 +53,8 @@ def parse_args():
     ap.add_argument('--cands', type=int, default=CANDS_PER_GPU, help='candidates per GPU per step')
     ap.add_argument('--history', type=int, default=HISTORY_PER_GPU, help='history rows per GPU')
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--ref-cands', type=int, default=100000,
+                    help='--impl reference: candidates per process per step (a bounded sample of the workload)')
     ap.add_argument('--e2e-steps', type=int, default=4)
     ap.add_argument('--staged', action='store_true',
                     help='sample+transform, reverse+fingerprint and dedup as separate kernels (the path of an '
@@ -148,7 +150,7 @@ def run_reference(args):
     if rank != 0:
         return
     procs = host_cores()
-    n_per_proc = 100000
+    n_per_proc = args.ref_cands
     for _ in range(args.warmup and 1):
         cpu_path_rate(2000, procs)
     rate, total_n, secs = cpu_path_rate(n_per_proc, procs, steps=args.steps)
@@ -158,7 +160,7 @@ def run_reference(args):
         "impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * secs / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
-        "data": "synthetic", "config": workload_config(args, 1),
+        "data": "synthetic", "config": workload_config(args, args.gpus),
         "cpu_baseline": {"value": rate, "unit": UNIT, "cores": procs, "kind": "port", "sample": sample},
         "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
