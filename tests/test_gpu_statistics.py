@@ -128,3 +128,58 @@ def test_cat32x100_chunked_one_hot_round_trip():
             idx = batch.columns[0].long()
             picked = torch.stack(tcols[:100], dim=1).gather(1, idx[:, None])[:, 0]
             assert bool((picked == 1.0).all().item())
+
+
+def test_full_size_suggest_and_dedup_exact_keep_mask():
+    """BASELINE.json config 5's per-GPU batch (1.25e7 candidates of mixed64)
+    through the one-kernel suggest and the history dedup, with planted
+    duplicates: the keep mask must equal the one derived from counter equality
+    (candidates are a function of their Philox counter; continuous dimensions
+    never collide otherwise), the staged kernels must produce the same bytes,
+    and a second pass over the same counters must keep nothing."""
+    from orion_b200 import spaces
+    from orion_b200.history import TrialHistory
+    from orion_b200.transformer import build_required_space
+    compiled = build_required_space('real', spaces.mixed64()).compiled()
+    n, n_hist, seed = 12_500_000, 25_000_000, 20240005
+    hist_base = 1 << 40
+    history = TrialHistory(compiled, capacity=n_hist + 2 * n)
+    hb = compiled.empty_columns(n)
+    for start in range(0, n_hist, n):
+        m = min(n, n_hist - start)
+        b = compiled.sample(m, seed, base_index=hist_base + start, with_mask=False, with_fingerprint=True,
+                            out=hb if m == n else None)
+        history.insert_fingerprints(b.fp, m)
+    assert len(history) == n_hist
+    g = torch.Generator(device='cuda')
+    g.manual_seed(1)
+    idx = torch.arange(n, dtype=torch.int64, device='cuda')
+    r = torch.rand(n, generator=g, device='cuda')
+    idx = torch.where(r < 0.10, hist_base + torch.randint(0, n_hist, (n,), generator=g, device='cuda'), idx)
+    early = torch.randint(0, n // 100, (n,), generator=g, device='cuda')
+    idx = torch.where((r >= 0.10) & (r < 0.11), early, idx)
+    # expected verdicts from the counters alone: not a history counter, and the first row with this counter
+    order = torch.argsort(idx, stable=True)
+    s = idx[order]
+    first_sorted = torch.ones(n, dtype=torch.bool, device='cuda')
+    first_sorted[1:] = s[1:] != s[:-1]
+    first = torch.empty(n, dtype=torch.bool, device='cuda')
+    first[order] = first_sorted
+    want = first & (idx < hist_base)
+
+    batch, tb, back = compiled.suggest(n, seed, index=idx)
+    assert bool(batch.mask[:n].all().item())
+    assert torch.equal(back.buf, batch.buf)                      # 'real': the round trip is the identity, byte for byte
+    keep = history.dedup_fingerprints(back.fp, n)
+    assert torch.equal(keep[:n].bool(), want)
+    assert len(history) == n_hist + int(want.sum().item())
+    # the staged kernels write the same bytes
+    tb2 = compiled.empty_columns(n, transformed=True)
+    b2 = compiled.sample(n, seed, index=idx, transformed_out=tb2)
+    assert torch.equal(b2.buf, batch.buf) and torch.equal(tb2.buf, tb.buf)
+    del tb
+    k2 = compiled.reverse(tb2, out=b2, with_fingerprint=True)    # (reverse may overwrite the sampled columns)
+    assert torch.equal(k2.fp[:n], back.fp[:n]) and torch.equal(k2.buf, back.buf)
+    # idempotence: everything is history now
+    again = history.dedup_fingerprints(back.fp, n)
+    assert int(again[:n].sum().item()) == 0
