@@ -333,7 +333,8 @@ def run_b200(args):
     n = args.cands
     K, W = args.steps, args.warmup
     KS = min(K, 5)                                    # steps of the staged-kernels comparison pass
-    total_steps = 2 * K + KS + W + args.e2e_steps + 2   # timed + serial pass + staged pass + e2e (+ its warm-up)
+    KR = min(K, 20)                                   # steps of the serial per-kernel pass behind the timed region
+    total_steps = K + KR + KS + W + args.e2e_steps + 2  # timed + serial pass + staged pass + e2e (+ its warm-up)
     space = spaces.mixed64()
     tspace = build_required_space('real', space)
     compiled = tspace.compiled()
@@ -341,6 +342,9 @@ def run_b200(args):
     # ---- history shard: rows from counters [2^40 + rank*H, ...), fingerprints only
     H = args.history
     cap_rows = H + int(0.92 * n) * total_steps + n
+    if table_slots_for(cap_rows, load=0.75) > (1 << 31):
+        raise SystemExit("bench.py: %d steps of %d candidates on top of %d history rows need more than the 2^31 slots "
+                         "one history table holds; use fewer --steps or --cands" % (total_steps, n, H))
     history = TrialHistory(compiled, n_slots=table_slots_for(cap_rows, load=0.75))
     # 'auto': peer-memory inboxes (kernels store straight into the owners' HBM over NVLink) where the
     # ranks can map each other's memory, NCCL all-to-all otherwise
@@ -436,6 +440,7 @@ def run_b200(args):
         return ms
 
     pipelined = fused and not args.serial
+    n_ev = K                      # steps whose per-kernel events are averaged
     t_begin = torch.cuda.Event(enable_timing=True)
     t_end = torch.cuda.Event(enable_timing=True)
     clocks = Clocks(local_rank)
@@ -465,15 +470,16 @@ def run_b200(args):
         kept_last = int(last_batch.keep[:n].sum().item())
         mask_ok = bool(last_batch.mask[:n].all().item())
         round_trip_ok = bool(torch.equal(last_back.buf, last_batch.buf))
-        # ---- the same K steps, one stream, no overlap: clean per-kernel durations for the roofline
-        for s in range(K):
+        # ---- the same steps (at most 20), one stream, no overlap: clean per-kernel durations for the roofline
+        n_ev = KR
+        for s in range(KR):
             index_dev[W + s] = step_index(W + K + s)      # fresh counters, same duplicate mix
         sync_all()
-        for s in range(K):
+        for s in range(KR):
             ev[s][0].record()
             one_step(W + s, ev[s])
         sync_all()
-        serial_ms = sum(ev[s][0].elapsed_time(ev[s][-1]) for s in range(K)) / K
+        serial_ms = sum(ev[s][0].elapsed_time(ev[s][-1]) for s in range(KR)) / KR
     else:
         for s in range(W):
             one_step(s)
@@ -500,7 +506,7 @@ def run_b200(args):
 
     per_kernel_ms = {}
     for j, name in enumerate(kernel_names):
-        per_kernel_ms[name] = sum(ev[s][j].elapsed_time(ev[s][j + 1]) for s in range(K)) / K
+        per_kernel_ms[name] = sum(ev[s][j].elapsed_time(ev[s][j + 1]) for s in range(n_ev)) / n_ev
 
     # ---- for comparison: the same K steps through the separate kernels (what an algorithm that works in the
     # transformed space pays: the transformed columns are read back by reverse), one stream
@@ -508,7 +514,7 @@ def run_b200(args):
     if one_kernel:
         sev = [[torch.cuda.Event(enable_timing=True) for _ in range(len(staged_names) + 1)] for _ in range(KS)]
         for s in range(KS):
-            index_dev[W + s] = step_index(W + 2 * K + s)
+            index_dev[W + s] = step_index(W + K + KR + s)
         sync_all()
         for s in range(KS):
             sev[s][0].record()
@@ -527,7 +533,7 @@ def run_b200(args):
         E = args.e2e_steps
         host_idx = [torch.empty(n, dtype=torch.int64).pin_memory() for _ in range(E + 2)]
         for j, h in enumerate(host_idx):
-            h.copy_(step_index(W + 2 * K + KS + j))
+            h.copy_(step_index(W + K + KR + KS + j))
         # Survivors only cross PCIe: after dedup the kept rows are gathered into a dense block on
         # the device (ob2_compact) and each column's first n_kept elements are copied to pinned
         # host memory.  Two buffer sets: compaction and copies of step j overlap step j+1.
@@ -653,7 +659,7 @@ def run_b200(args):
                      # sampler removes; measured DRAM traffic (ncu, profiles/traffic.json) over the same time:
                      "traffic_frac": (traffic * n / 12_500_000 / (per_kernel_ms[dominant] * 1e-3) / 1e9 / peak
                                       if traffic else None),
-                     "how": ("CUDA events around each kernel over K serial steps run right after the timed region "
+                     "how": ("CUDA events around each kernel over min(K, 20) serial steps run right after the timed region "
                              "(inside it kernels of adjacent steps overlap; those contended durations are in "
                              "kernels_in_timed_region_ms)" if pipelined else
                              "CUDA events around each kernel inside the timed region"),
