@@ -29,8 +29,7 @@ __device__ __forceinline__ long long quantize_ll(double x, int t_flags) {
 }
 
 // One-hot pair: 1.0 = 0x3FF00000'00000000, so only the high words are selected.
-__device__ __forceinline__ void st_onehot2(double *p, int c0, int c1, int j) {
-    const unsigned h0 = c0 == j ? 0x3FF00000u : 0u, h1 = c1 == j ? 0x3FF00000u : 0u;
+__device__ __forceinline__ void st_onehot_hi(double *p, unsigned h0, unsigned h1) {
     asm volatile("st.global.cs.v4.u32 [%0], {%1, %2, %1, %3};" ::"l"(p), "r"(0u), "r"(h0), "r"(h1) : "memory");
 }
 
@@ -90,14 +89,17 @@ __device__ __forceinline__ bool redraw_dim(const ob2_slot_desc *s_slots, int s_l
                 x = floor(x);
                 const long long q = __double2ll_rz(x);
                 reinterpret_cast<long long *>(col)[i] = q;
-                if (WITH_B) reinterpret_cast<long long *>(col + bdelta)[i] = q;
-                w = (uint64_t)q;
+                long long bq = q;
                 if (WITH_T) {
-                    if (d.t_op == OB2_OP_TO_REAL)
+                    if (d.t_op == OB2_OP_TO_REAL) {
                         reinterpret_cast<double *>(dst)[i] = x;
-                    else
+                        if (WITH_B) bq = quantize_ll(x, d.t_flags);
+                    } else {
                         reinterpret_cast<long long *>(dst)[i] = q;
+                    }
                 }
+                if (WITH_B) reinterpret_cast<long long *>(col + bdelta)[i] = bq;
+                w = (uint64_t)bq;
             } else {
                 reinterpret_cast<double *>(col)[i] = x;
                 double bx = x;
@@ -137,9 +139,9 @@ __device__ __forceinline__ bool redraw_dim(const ob2_slot_desc *s_slots, int s_l
 // transformed values while they are still in registers and store the handed-out row to
 // `back` = cols + bdelta (same column layout); the fingerprint is then that of the `back`
 // row, exactly what reverse_kernel<true> computes from the materialised tcols.  Per op:
-// Identity / Enumerate pass the value through; Reverse(Quantize) then Quantize of an exact
-// integer is that integer; argmax (or > 0.5) of the one-hot encoding of an in-range index
-// is that index; Quantize then its cast back is NOT the identity and is computed.
+// Quantize of the stored double, the cast back of the stored integer and (v > 0.5) for k = 2
+// are evaluated on the transformed value; Identity / Enumerate pass the value through; the
+// argmax over a k > 2 one-hot block is the position of its single 1.0, the drawn index.
 template <bool PHILOX, bool WITH_FP, bool WITH_T, bool WITH_B, bool EXT>
 __global__ void __launch_bounds__(OB2_BLOCK, WITH_B ? OB2_SUGGEST_CTAS : 4)
 sample_kernel(const ob2_slot_desc *__restrict__ g_slots, int n_slots, const double *__restrict__ g_cdf,
@@ -197,27 +199,41 @@ sample_kernel(const ob2_slot_desc *__restrict__ g_slots, int n_slots, const doub
             const int c0 = draw_cat_fast(cdf, d.n_cats, u0, uni);
             const int c1 = draw_cat_fast(cdf, d.n_cats, u1, uni);
             st_i32x2(reinterpret_cast<int *>(col - i0 * 4), c0, c1);
-            if (WITH_B) st_i32x2(reinterpret_cast<int *>(col - i0 * 4 + bdelta), c0, c1);
+            int *bcol = reinterpret_cast<int *>(col - i0 * 4 + bdelta);
             col += stride4;
+            int b0 = c0, b1 = c1;  // WITH_B: reverse() of the transformed value, evaluated on what is stored
             if (WITH_T) {
-                if (d.t_op != OB2_OP_ONEHOT) {
+                if (d.t_op != OB2_OP_ONEHOT) {  // Enumerate / Identity: the index both ways
                     st_i32x2(reinterpret_cast<int *>(tcol - i0 * 4), c0, c1);
                     tcol += stride4;
                 } else if (d.t_width == 1) {
-                    st_f64x2(reinterpret_cast<double *>(tcol), (double)c0, (double)c1);
+                    const double t0 = (double)c0, t1 = (double)c1;
+                    st_f64x2(reinterpret_cast<double *>(tcol), t0, t1);
                     tcol += stride8;
+                    if (WITH_B) {  // k == 2: (v > 0.5); k == 1: always category 0
+                        b0 = (d.n_cats == 2 && t0 > 0.5) ? 1 : 0;
+                        b1 = (d.n_cats == 2 && t1 > 0.5) ? 1 : 0;
+                    }
                 } else {
                     // column j is at tcol + j * stride8; the launcher guarantees stride8 < 2^32,
                     // so each address is ONE 32x32+64 multiply-add (IMAD.WIDE.U32)
                     const uint32_t s8 = (uint32_t)stride8, k = (uint32_t)d.t_width;
+                    // WITH_B: reverse_kernel's argmax (first maximum) over these k values is the position
+                    // of the single 1.0 stored below, i.e. the index itself: the Philox draw is always in
+                    // [0, k).  Tracking the maximum while storing (tried: 6 more instructions per column
+                    // pair) costs the kernel 4.5 % for the same bytes, so the identity is used; the staged
+                    // kernels and tests/test_gpu_suggest_fused.py hold it to account.
 #pragma unroll 4
-                    for (uint32_t j = 0; j < k; ++j)
-                        st_onehot2(reinterpret_cast<double *>(tcol + (uint64_t)j * s8), c0, c1, (int)j);
+                    for (uint32_t j = 0; j < k; ++j) {
+                        const unsigned h0 = c0 == (int)j ? 0x3FF00000u : 0u, h1 = c1 == (int)j ? 0x3FF00000u : 0u;
+                        st_onehot_hi(reinterpret_cast<double *>(tcol + (uint64_t)j * s8), h0, h1);
+                    }
                     tcol += (uint64_t)k * s8;
                 }
             }
-            w0 = (uint64_t)(int64_t)c0;
-            w1 = (uint64_t)(int64_t)c1;
+            if (WITH_B) st_i32x2(bcol, b0, b1);
+            w0 = (uint64_t)(int64_t)b0;
+            w1 = (uint64_t)(int64_t)b1;
             if (!PHILOX) {  // an injected u >= 1 can run off the table; a Philox u cannot
                 ok0 &= c0 < d.n_cats;
                 ok1 &= c1 < d.n_cats;
@@ -230,16 +246,22 @@ sample_kernel(const ob2_slot_desc *__restrict__ g_slots, int n_slots, const doub
                 x1 = floor(x1);
                 const long long q0 = __double2ll_rz(x0), q1 = __double2ll_rz(x1);
                 st_i64x2(reinterpret_cast<long long *>(col), q0, q1);
-                if (WITH_B) st_i64x2(reinterpret_cast<long long *>(col + bdelta), q0, q1);
+                long long bq0 = q0, bq1 = q1;
                 if (WITH_T) {
-                    if (d.t_op == OB2_OP_TO_REAL)  // the floored double is exactly (double)q
+                    if (d.t_op == OB2_OP_TO_REAL) {  // the floored double is exactly (double)q
                         st_f64x2(reinterpret_cast<double *>(tcol), x0, x1);
-                    else
+                        if (WITH_B) {  // Reverse(Quantize).reverse = Quantize.transform of the stored double
+                            bq0 = quantize_ll(x0, d.t_flags);
+                            bq1 = quantize_ll(x1, d.t_flags);
+                        }
+                    } else {
                         st_i64x2(reinterpret_cast<long long *>(tcol), q0, q1);
+                    }
                     tcol += stride8;
                 }
-                w0 = (uint64_t)q0;
-                w1 = (uint64_t)q1;
+                if (WITH_B) st_i64x2(reinterpret_cast<long long *>(col + bdelta), bq0, bq1);
+                w0 = (uint64_t)bq0;
+                w1 = (uint64_t)bq1;
             } else {
                 st_f64x2(reinterpret_cast<double *>(col), x0, x1);
                 double bx0 = x0, bx1 = x1;
