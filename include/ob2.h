@@ -50,7 +50,11 @@ enum { OB2_DIST_UNIFORM = 0, OB2_DIST_RECIPROCAL = 1, OB2_DIST_NORM = 2, OB2_DIS
         * `randint(-3, 5)`, `poisson(mu=3)`).  ALPHA: p0 = a, p1 = ndtr(a).  RANDINT: p0 = low,
         * p1 = high - low, scipy's _ppf verbatim.  POISSON: p0 = mu (<= 500), p1 = exp(-mu); the
         * smallest k with cdf(k) >= u by summing the pmf. */
-       OB2_DIST_ALPHA = 15, OB2_DIST_RANDINT = 16, OB2_DIST_POISSON = 17, OB2_DIST_LAST = 17 };
+       OB2_DIST_ALPHA = 15, OB2_DIST_RANDINT = 16, OB2_DIST_POISSON = 17,
+       /* GAMMA (also erlang): p0 = a, p1 = lgamma(a).  BETA: p0 = a, p1 = b, hk[3] = bit pattern of
+        * the double lbeta(a, b).  Inverse of the regularised incomplete gamma / beta function by
+        * Halley steps from a closed-form first guess (scipy: special.gammaincinv / betaincinv). */
+       OB2_DIST_GAMMA = 18, OB2_DIST_BETA = 19, OB2_DIST_LAST = 19 };
 
 /* per-slot transformer (build_required_space table) */
 enum {
@@ -82,7 +86,7 @@ typedef struct ob2_slot_desc {
     double p0, p1;     /* reciprocal: log(a), log(b) - log(a)                     */
     double loc, scale; /* x = base(u) * scale + loc  (scipy rv_generic.rvs)       */
     double low, high;  /* accepted iff low <= x < high (space.py:160-164)         */
-    uint64_t hk[4];    /* fingerprint: xor key, odd multiplier, 2 reserved        */
+    uint64_t hk[4];    /* fingerprint: xor key, 2 x packed odd multipliers; hk[3]: third prior parameter (BETA) */
 } ob2_slot_desc;
 
 typedef struct ob2_space ob2_space;

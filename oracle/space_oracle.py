@@ -182,7 +182,9 @@ CLOSED_FORM_PRIORS = ('expon', 'lognorm', 'logistic', 'laplace', 'gumbel_r', 'we
                       'rayleigh', 'halfnorm', 'powerlaw',
                       # the reference's DSL examples (space_builder.py:84,98-99); poisson and randint are
                       # rv_discrete: rvs adds loc only (scale is 1)
-                      'alpha', 'randint', 'poisson')
+                      'alpha', 'randint', 'poisson',
+                      # special.gammaincinv / betaincinv
+                      'gamma', 'erlang', 'beta')
 
 
 def _draw(spec: DimSpec, u: np.ndarray) -> np.ndarray:

@@ -101,9 +101,148 @@ __device__ __forceinline__ double u53(uint32_t w0, uint32_t w1) {
     return __ull2double_rn(v) * 1.1102230246251565e-16;  // 2^-53
 }
 
+// ---- regularised incomplete gamma / beta and their inverses (gamma, erlang, beta priors).
+// scipy's ppf for these is special.gammaincinv / betaincinv; here: series / modified-Lentz
+// continued fractions for the functions, a closed-form first guess and Halley steps on the
+// lower tail (P - p) or the upper one (q - Q), whichever is the small one, to ~1e-14.
+__device__ __forceinline__ void gamma_pq(double a, double x, double lga, double &P, double &Q) {
+    const double front = exp(-x + a * log(x) - lga);
+    if (x < a + 1.0) {  // series for P
+        double ap = a, del = 1.0 / a, sum = del;
+        for (int n = 0; n < 2000; ++n) {
+            ap += 1.0;
+            del *= x / ap;
+            sum += del;
+            if (fabs(del) < fabs(sum) * 1e-16) break;
+        }
+        P = sum * front;
+        Q = 1.0 - P;
+    } else {  // continued fraction for Q
+        const double tiny = 1e-300;
+        double b = x + 1.0 - a, c = 1.0 / tiny, d = 1.0 / b, h = d;
+        for (int i = 1; i < 2000; ++i) {
+            const double an = -(double)i * ((double)i - a);
+            b += 2.0;
+            d = an * d + b;
+            if (fabs(d) < tiny) d = tiny;
+            c = b + an / c;
+            if (fabs(c) < tiny) c = tiny;
+            d = 1.0 / d;
+            const double del = d * c;
+            h *= del;
+            if (fabs(del - 1.0) < 1e-16) break;
+        }
+        Q = front * h;
+        P = 1.0 - Q;
+    }
+}
+
+static __device__ __noinline__ double gamma_ppf(double a, double lga, double p) {
+    if (p <= 0.0) return 0.0;
+    const double q = 1.0 - p;
+    double x;
+    if (a > 1.0) {  // Wilson-Hilferty
+        const double t = normcdfinv(p), s = 1.0 - 1.0 / (9.0 * a) + t / (3.0 * sqrt(a));
+        x = a * s * s * s;
+        if (!(x > 0.0)) x = exp((log(p) + lga + log(a)) / a);  // far lower tail: P ~ x^a / Gamma(a + 1)
+    } else {
+        const double t = 1.0 - a * (0.253 + 0.12 * a);
+        x = p < t ? pow(p / t, 1.0 / a) : 1.0 - log1p(-(p - t) / (1.0 - t));
+    }
+    for (int it = 0; it < 40; ++it) {
+        if (!(x > 0.0)) return 0.0;
+        double P, Q;
+        gamma_pq(a, x, lga, P, Q);
+        const double err = p <= 0.5 ? P - p : q - Q;
+        const double pdf = exp(-x + (a - 1.0) * log(x) - lga);
+        if (!(pdf > 0.0)) break;
+        const double u = err / pdf;
+        const double dx = u / (1.0 - 0.5 * fmin(1.0, u * ((a - 1.0) / x - 1.0)));
+        x -= dx;
+        if (x <= 0.0) x = 0.5 * (x + dx);
+        if (fabs(dx) < 1e-14 * x) break;
+    }
+    return x;
+}
+
+// continued fraction of the incomplete beta function (modified Lentz)
+__device__ __forceinline__ double beta_cf(double a, double b, double x) {
+    const double tiny = 1e-300, qab = a + b, qap = a + 1.0, qam = a - 1.0;
+    double c = 1.0, d = 1.0 - qab * x / qap;
+    if (fabs(d) < tiny) d = tiny;
+    d = 1.0 / d;
+    double h = d;
+    for (int m = 1; m < 3000; ++m) {
+        const double m2 = 2.0 * m;
+        double aa = m * (b - m) * x / ((qam + m2) * (a + m2));
+        d = 1.0 + aa * d;
+        if (fabs(d) < tiny) d = tiny;
+        c = 1.0 + aa / c;
+        if (fabs(c) < tiny) c = tiny;
+        d = 1.0 / d;
+        h *= d * c;
+        aa = -(a + m) * (qab + m) * x / ((a + m2) * (qap + m2));
+        d = 1.0 + aa * d;
+        if (fabs(d) < tiny) d = tiny;
+        c = 1.0 + aa / c;
+        if (fabs(c) < tiny) c = tiny;
+        d = 1.0 / d;
+        const double del = d * c;
+        h *= del;
+        if (fabs(del - 1.0) < 1e-16) break;
+    }
+    return h;
+}
+
+__device__ __forceinline__ void beta_pq(double a, double b, double lbeta, double x, double &P, double &Q) {
+    const double front = exp(a * log(x) + b * log1p(-x) - lbeta);
+    if (x < (a + 1.0) / (a + b + 2.0)) {
+        P = front * beta_cf(a, b, x) / a;
+        Q = 1.0 - P;
+    } else {
+        Q = front * beta_cf(b, a, 1.0 - x) / b;
+        P = 1.0 - Q;
+    }
+}
+
+static __device__ __noinline__ double beta_ppf(double a, double b, double lbeta, double p) {
+    if (p <= 0.0) return 0.0;
+    const double q = 1.0 - p;
+    double x;
+    if (a >= 1.0 && b >= 1.0) {  // Abramowitz & Stegun 26.5.22
+        const double t = -normcdfinv(p);  // upper-tail normal deviate
+        const double al = (t * t - 3.0) / 6.0, h = 2.0 / (1.0 / (2.0 * a - 1.0) + 1.0 / (2.0 * b - 1.0));
+        const double w = t * sqrt(al + h) / h -
+                         (1.0 / (2.0 * b - 1.0) - 1.0 / (2.0 * a - 1.0)) * (al + 5.0 / 6.0 - 2.0 / (3.0 * h));
+        x = a / (a + b * exp(2.0 * w));
+        if (p < 1e-12 || !(x > 0.0)) x = exp((log(p) + log(a) + lbeta) / a);  // far lower tail: I ~ x^a / (a B(a, b))
+    } else {
+        const double lna = log(a / (a + b)), lnb = log(b / (a + b));
+        const double t = exp(a * lna) / a, u = exp(b * lnb) / b, w = t + u;
+        x = p < t / w ? pow(a * w * p, 1.0 / a) : 1.0 - pow(b * w * q, 1.0 / b);
+    }
+    x = fmin(fmax(x, 1e-300), 1.0 - 1.1e-16);
+    for (int it = 0; it < 60; ++it) {
+        double P, Q;
+        beta_pq(a, b, lbeta, x, P, Q);
+        const double err = p <= 0.5 ? P - p : q - Q;
+        const double pdf = exp((a - 1.0) * log(x) + (b - 1.0) * log1p(-x) - lbeta);
+        if (!(pdf > 0.0) || isinf(pdf)) break;
+        const double u = err / pdf;
+        const double dx = u / (1.0 - 0.5 * fmin(1.0, u * ((a - 1.0) / x - (b - 1.0) / (1.0 - x))));
+        double xn = x - dx;
+        if (xn <= 0.0) xn = 0.5 * x;
+        if (xn >= 1.0) xn = 0.5 * (x + 1.0);
+        const double moved = fabs(xn - x);
+        x = xn;
+        if (moved < 1e-14 * x) break;
+    }
+    return x;
+}
+
 // The extra priors, out of line and out of the common kernel (EXT = false
 // never references it).
-static __device__ __noinline__ double draw_extended(int dist, double p0, double p1, double u) {
+static __device__ __noinline__ double draw_extended(int dist, double p0, double p1, double p2, double u) {
     switch (dist) {
         case OB2_DIST_EXPON:
             return -log1p(-u);
@@ -133,6 +272,10 @@ static __device__ __noinline__ double draw_extended(int dist, double p0, double 
             const double temp = (floor(vals1) - p0 + 1.0) / p1;
             return temp >= u ? vals1 : vals;
         }
+        case OB2_DIST_GAMMA:  // p0 = a, p1 = lgamma(a)
+            return gamma_ppf(p0, p1, u);
+        case OB2_DIST_BETA:  // p0 = a, p1 = b, p2 = lbeta(a, b)
+            return beta_ppf(p0, p1, p2, u);
         default: {  // OB2_DIST_POISSON, p0 = mu, p1 = exp(-mu): smallest k with cdf(k) >= u
             double k = 0.0, pmf = p1, cdf = p1;
             const double k_max = p0 + 40.0 * sqrt(p0) + 60.0;  // the tail beyond is < 1e-300
@@ -164,7 +307,7 @@ __device__ __forceinline__ double draw_real(const ob2_slot_desc &d, double u) {
             return d.loc;  // scale == 0
         default:  // closed-form inverse CDFs of further scipy priors (scipy's own _ppf formulas)
             if (!EXT) return d.loc;
-            b = draw_extended(d.dist, d.p0, d.p1, u);
+            b = draw_extended(d.dist, d.p0, d.p1, __longlong_as_double((long long)d.hk[3]), u);
             break;
     }
     return __dadd_rn(__dmul_rn(b, d.scale), d.loc);

@@ -100,6 +100,14 @@ def _prior_params(dim):
     if name == 'poisson' and len(args) == 1 and float(args[0]) <= 500.0:
         mu = float(args[0])
         return 17, mu, float(np.exp(-mu)), loc, scale
+    if name in ('gamma', 'erlang') and len(args) == 1:
+        from scipy.special import gammaln
+        a = float(args[0])
+        return 18, a, float(gammaln(a)), loc, scale
+    if name == 'beta' and len(args) == 2:
+        from scipy.special import betaln
+        a, b = float(args[0]), float(args[1])
+        return 19, a, b, loc, scale, float(betaln(a, b))
     # any other scipy prior: bounds-only (contains / transform / dedup work, sampling refuses)
     return _lib.DIST_NONE, 0.0, 0.0, loc, scale
 
@@ -146,10 +154,10 @@ class CompiledSpace(object):
                 cdf_off = len(cdf)
                 cdf.extend(c.tolist())
                 n_cats = len(dim.categories)
-                dist = p0 = p1 = loc = scale = 0
+                dist = p0 = p1 = loc = scale = p2 = 0
                 low, high = 0.0, float(n_cats)
             else:
-                dist, p0, p1, loc, scale = _prior_params(dim)
+                dist, p0, p1, loc, scale, p2 = (tuple(_prior_params(dim)) + (0.0,))[:6]
                 if dist == _lib.DIST_NONE and self.unsamplable is None:
                     self.unsamplable = (dim.name, dim._prior_name)
                 low, high = dim.interval()
@@ -186,6 +194,7 @@ class CompiledSpace(object):
                 sd.low, sd.high = low, high
                 for j, v in enumerate(_hash_keys(s)):
                     sd.hk[j] = v
+                sd.hk[3] = int(np.float64(p2).view(np.uint64))      # third prior parameter (beta: lbeta(a, b))
                 slots.append(sd)
                 self.col_meta.append((col_units, dt))
                 for j in range(width):

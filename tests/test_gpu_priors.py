@@ -18,6 +18,8 @@ PRIORS = [
     ('logistic', []), ('logistic', [1.0, 0.5]), ('laplace', []), ('gumbel_r', [0.5, 2.0]),
     ('weibull_min', [1.5]), ('weibull_min', [0.7, 1.0, 3.0]), ('pareto', [2.5]), ('rayleigh', []),
     ('rayleigh', [0.0, 4.0]), ('halfnorm', []), ('powerlaw', [3.0]), ('powerlaw', [0.5, -1.0, 2.0]),
+    ('gamma', [0.3]), ('gamma', [2.5, 1.0, 3.0]), ('gamma', [400.0]), ('erlang', [3]),
+    ('beta', [2.0, 5.0]), ('beta', [0.5, 0.5]), ('beta', [30.0, 2.0, -1.0, 4.0]), ('beta', [1.0, 3.0]),
 ]
 
 
@@ -32,6 +34,9 @@ def test_from_uniform_matches_scipy_ppf():
     n = 4096
     U = rng.random_sample((len(dims), n))
     U[:, :4] = [1e-300, 2.0 ** -53, 0.5, 1 - 2.0 ** -53]
+    for j, (name, args) in enumerate(PRIORS):
+        if name == 'gamma' and args[0] > 100:
+            U[j, 0] = 1e-100       # P(400, x) itself underflows below ~1e-250 (a Philox u is 0 or >= 2^-53)
     batch = space.compiled().sample_from_uniform(torch.from_numpy(U).cuda())
     got = batch.to_numpy()
     want, ok = so.sample_from_uniform(specs, U)
@@ -143,7 +148,7 @@ def test_dsl_example_priors_philox_marginals():
 def test_unsupported_prior_still_refuses():
     from orion_b200.space import Real, Space
     space = Space()
-    space.register(Real('a', 'gamma', 2.0))
-    assert (3.5,) in space
+    space.register(Real('a', 'vonmises', 2.0))
+    assert (0.5,) in space
     with pytest.raises(NotImplementedError):
         space.sample(1)
