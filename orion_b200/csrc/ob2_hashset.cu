@@ -266,7 +266,7 @@ bucket_kernel(int64_t n, const uint64_t *__restrict__ fp, uint32_t key_base, int
     if (i < n) {
         key = __ldg(reinterpret_cast<const ulonglong2 *>(fp) + i);
         if (key.x != 0) {
-            owner = (int)(key.y % (uint64_t)n_ranks);
+            owner = ob2_owner_of(key.y, (uint32_t)n_ranks);
             rank_in_block = atomicAdd(&s_cnt[owner], 1u);
         }
     }

@@ -327,6 +327,12 @@ __device__ __forceinline__ int draw_cat(const double *cdf, int k, double u) {
     return lo;
 }
 
+// owner rank of a fingerprint: hi % n_ranks (a mask when n_ranks is a power of two: same value,
+// without the ~40-instruction 64-bit division)
+__device__ __forceinline__ int ob2_owner_of(uint64_t hi, uint32_t n_ranks) {
+    return (n_ranks & (n_ranks - 1)) == 0 ? (int)(hi & (uint64_t)(n_ranks - 1)) : (int)(hi % (uint64_t)n_ranks);
+}
+
 // ---- fingerprint pieces
 __device__ __forceinline__ uint64_t fmix64(uint64_t x) {
     x ^= x >> 33;

@@ -101,7 +101,7 @@ xchg_send_kernel(int64_t n, const uint64_t *__restrict__ fp, uint32_t key_base, 
         if (i < n) {
             key[q] = __ldg(reinterpret_cast<const ulonglong2 *>(fp) + i);
             if (key[q].x != 0) {
-                owner[q] = (int)(key[q].y % (uint64_t)world);
+                owner[q] = ob2_owner_of(key[q].y, (uint32_t)world);
                 local_rank[q] = atomicAdd(&s_cnt[owner[q]], 1u);
             }
         }
