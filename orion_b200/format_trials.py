@@ -58,3 +58,48 @@ def trials_to_batch(space, trials):
     typed = [numpy.asarray(c, dtype={'f8': numpy.float64, 'i8': numpy.int64, 'i4': numpy.int32}[dt])
              for c, (_u, dt) in zip(cols, compiled.col_meta)]
     return ColumnBatch.from_numpy(compiled, typed)
+
+
+def columns_to_record_batch(space, host_cols):
+    """Host columns (one per scalar slot, space order; narrow wire dtypes
+    welcome) -> ``pyarrow.RecordBatch``: the columnar form of
+    ``[tuple_to_trial(p) for p in points]`` without one Python object per
+    parameter.  Real -> float64, Integer -> the column's integer type,
+    Categorical -> dictionary-encoded categories; a dimension with ``shape``
+    contributes one field per element, named ``name[i]`` in C order.  The
+    dimension types travel in the schema metadata (``b'orion.types'``)."""
+    import json
+    import pyarrow as pa
+    arrays, names, types = [], [], {}
+    s = 0
+    for dim in space.values():
+        k = int(numpy.prod(dim.shape, dtype=numpy.int64)) if dim.shape else 1
+        types[dim.name] = dim.type
+        for e in range(k):
+            col = numpy.ascontiguousarray(host_cols[s + e])
+            if dim.type == 'categorical':
+                cats = list(dim.categories)
+                try:
+                    dictionary = pa.array(cats)
+                except (pa.ArrowInvalid, pa.ArrowTypeError):      # categories of mixed Python types
+                    dictionary = pa.array([repr(c) for c in cats])
+                arr = pa.DictionaryArray.from_arrays(pa.array(col.astype(numpy.int32, copy=False)), dictionary)
+            else:
+                arr = pa.array(col)                                # zero-copy for primitive columns
+            arrays.append(arr)
+            names.append(dim.name if not dim.shape else '%s[%d]' % (dim.name, e))
+        s += k
+    schema = pa.schema([pa.field(n, a.type) for n, a in zip(names, arrays)],
+                       metadata={b'orion.types': json.dumps(types).encode()})
+    return pa.RecordBatch.from_arrays(arrays, schema=schema)
+
+
+def batch_to_record_batch(space, batch, keep=None):
+    """Surviving rows of a device ColumnBatch as one ``pyarrow.RecordBatch``:
+    survivors are gathered on the device in the narrowed wire layout
+    (``ob2_compact_wire``), copied to the host once, and wrapped column by
+    column -- no per-row Python work (the bulk counterpart of
+    :func:`batch_to_trials`)."""
+    keep = batch.keep if keep is None else keep
+    dense = batch.compact(keep, wire=not batch.transformed) if keep is not None else batch
+    return columns_to_record_batch(space, dense.to_numpy(natural=False))

@@ -111,3 +111,30 @@ def test_compact_wire_matches_natural_compaction(n):
                 assert np.array_equal(narrow.astype(want.dtype), want)            # lossless
             for j in range(len(raw)):                                             # typed device views too
                 assert np.array_equal(wire.column(j).cpu().numpy(), raw[j])
+
+
+def test_batch_to_record_batch_equals_trial_records():
+    """The columnar hand-over (pyarrow) carries exactly the rows batch_to_trials builds."""
+    from orion_b200 import format_trials, spaces
+    from orion_b200.history import TrialHistory
+    space = spaces.mixed64()
+    n = 2000
+    hist = TrialHistory(space, capacity=8 * n)
+    counters = torch.from_numpy(np.random.RandomState(1).randint(0, n // 2, size=n).astype(np.int64)).cuda()
+    batch = space.compiled().sample(n, 3, index=counters, with_fingerprint=True)
+    hist.dedup(batch)
+    rb = format_trials.batch_to_record_batch(space, batch)
+    trials = format_trials.batch_to_trials(space, batch)
+    assert rb.num_rows == len(trials) == int(batch.keep[:n].sum().item())
+    assert rb.schema.names == list(space.keys())
+    table = rb.to_pydict()
+    for j, name in enumerate(space.keys()):
+        want = [t['params'][j]['value'] for t in trials]
+        got = table[name]
+        if space[name].type == 'real':
+            assert np.array_equal(np.asarray(got), np.asarray(want, dtype=np.float64))
+        else:
+            assert [int(g) for g in got] == [int(w) for w in want]
+    # narrow wire integers arrive as narrow arrow types: nothing was widened on the way
+    import pyarrow as pa
+    assert rb.schema.field('i0').type == pa.int8() and rb.schema.field('u0').type == pa.float64()

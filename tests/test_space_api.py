@@ -425,3 +425,25 @@ class TestPriorDSL(object):
         s = spaces.mixed64()
         assert len(s) == 64 and [d.type for d in s.values()].count('categorical') == 16
         assert len(spaces.real16()) == 16 and len(spaces.cat32x100()) == 32 and len(spaces.rosen2()) == 2
+
+
+def test_columns_to_record_batch_schema_and_values():
+    """Host half of the bulk trial hand-over (no GPU involved)."""
+    import json
+    from orion_b200 import format_trials
+    from orion_b200.space import Categorical, Integer, Real, Space
+    space = Space()
+    space.register(Real('lr', 'reciprocal', 1e-5, 1.0))
+    space.register(Integer('layers', 'uniform', 1, 8, shape=2))
+    space.register(Categorical('act', ['relu', 'tanh', 'gelu']))
+    space.register(Categorical('odd', ['asdfa', 2, 3.5]))
+    cols = [np.array([0.1, 0.01, 0.5]), np.array([1, 2, 3], dtype=np.int8), np.array([4, 5, 6], dtype=np.int8),
+            np.array([2, 0, 1], dtype=np.uint8), np.array([1, 1, 0], dtype=np.uint8)]
+    rb = format_trials.columns_to_record_batch(space, cols)
+    assert rb.num_rows == 3 and rb.schema.names == ['lr', 'layers[0]', 'layers[1]', 'act', 'odd']
+    assert json.loads(rb.schema.metadata[b'orion.types']) == {'lr': 'real', 'layers': 'integer', 'act': 'categorical',
+                                                              'odd': 'categorical'}
+    assert rb.column(0).to_pylist() == [0.1, 0.01, 0.5]
+    assert rb.column(1).to_pylist() == [1, 2, 3] and rb.column(2).to_pylist() == [4, 5, 6]
+    assert rb.column(3).to_pylist() == ['gelu', 'relu', 'tanh']
+    assert rb.column(4).to_pylist() == ['2', '2', "'asdfa'"]           # mixed-type categories travel as reprs
