@@ -103,3 +103,40 @@ def batch_to_record_batch(space, batch, keep=None):
     keep = batch.keep if keep is None else keep
     dense = batch.compact(keep, wire=not batch.transformed) if keep is not None else batch
     return columns_to_record_batch(space, dense.to_numpy(natural=False))
+
+
+def record_batch_to_columns(space, record_batch):
+    """Inverse of :func:`columns_to_record_batch`: host columns in the
+    natural dtypes (float64 / int64 / int32 category index), ready for
+    ``ColumnBatch.from_numpy`` -- bulk history ingestion (resume) without
+    going through one trial record per row."""
+    import pyarrow as pa
+    cols = []
+    f = 0
+    for dim in space.values():
+        k = int(numpy.prod(dim.shape, dtype=numpy.int64)) if dim.shape else 1
+        for e in range(k):
+            field = record_batch.schema.field(f)
+            want = dim.name if not dim.shape else '%s[%d]' % (dim.name, e)
+            if field.name != want:
+                raise ValueError("field %d is %r, the space expects %r" % (f, field.name, want))
+            arr = record_batch.column(f)
+            if dim.type == 'categorical':
+                if not pa.types.is_dictionary(arr.type):
+                    raise ValueError("categorical dimension %r needs a dictionary-encoded field" % dim.name)
+                cats = list(dim.categories)
+                try:
+                    expected = pa.array(cats).to_pylist()
+                except (pa.ArrowInvalid, pa.ArrowTypeError):
+                    expected = [repr(c) for c in cats]
+                if arr.dictionary.to_pylist() != expected:
+                    raise ValueError("dictionary of %r does not match the dimension's categories" % field.name)
+                cols.append(arr.indices.to_numpy(zero_copy_only=False).astype(numpy.int32))
+            elif dim.type == 'integer':
+                cols.append(arr.to_numpy(zero_copy_only=False).astype(numpy.int64))
+            else:
+                cols.append(arr.to_numpy(zero_copy_only=False).astype(numpy.float64))
+            f += 1
+    if f != record_batch.num_columns:
+        raise ValueError("record batch has %d fields, the space %d slots" % (record_batch.num_columns, f))
+    return cols

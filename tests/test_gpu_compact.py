@@ -138,3 +138,10 @@ def test_batch_to_record_batch_equals_trial_records():
     # narrow wire integers arrive as narrow arrow types: nothing was widened on the way
     import pyarrow as pa
     assert rb.schema.field('i0').type == pa.int8() and rb.schema.field('u0').type == pa.float64()
+    # ... and back: the record batch re-enters a fresh history as exactly those rows (bulk resume)
+    from orion_b200.columns import ColumnBatch
+    again = ColumnBatch.from_numpy(space.compiled(), format_trials.record_batch_to_columns(space, rb))
+    fresh = TrialHistory(space, capacity=8 * n)
+    fresh.observe(again)
+    assert len(fresh) == rb.num_rows == len(hist)
+    assert int(fresh.dedup(space.compiled().sample(n, 3, index=counters, with_fingerprint=True)).sum().item()) == 0

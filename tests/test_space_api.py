@@ -447,3 +447,8 @@ def test_columns_to_record_batch_schema_and_values():
     assert rb.column(1).to_pylist() == [1, 2, 3] and rb.column(2).to_pylist() == [4, 5, 6]
     assert rb.column(3).to_pylist() == ['gelu', 'relu', 'tanh']
     assert rb.column(4).to_pylist() == ['2', '2', "'asdfa'"]           # mixed-type categories travel as reprs
+    back = format_trials.record_batch_to_columns(space, rb)
+    assert [c.dtype for c in back] == [np.float64, np.int64, np.int64, np.int32, np.int32]
+    assert all(np.array_equal(a, b) for a, b in zip(back, cols))
+    with pytest.raises(ValueError):
+        format_trials.record_batch_to_columns(space, rb.select([1, 0, 2, 3, 4]))
