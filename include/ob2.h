@@ -54,7 +54,12 @@ enum { OB2_DIST_UNIFORM = 0, OB2_DIST_RECIPROCAL = 1, OB2_DIST_NORM = 2, OB2_DIS
        /* GAMMA (also erlang): p0 = a, p1 = lgamma(a).  BETA: p0 = a, p1 = b, hk[3] = bit pattern of
         * the double lbeta(a, b).  Inverse of the regularised incomplete gamma / beta function by
         * Halley steps from a closed-form first guess (scipy: special.gammaincinv / betaincinv). */
-       OB2_DIST_GAMMA = 18, OB2_DIST_BETA = 19, OB2_DIST_LAST = 19 };
+       OB2_DIST_GAMMA = 18, OB2_DIST_BETA = 19,
+       /* CAUCHY: tan(pi (u - 1/2)).  CHI2: p0 = df / 2, p1 = lgamma(df / 2), twice the gamma
+        * inverse.  T: p0 = df, p1 = lbeta(df / 2, 1 / 2), through the beta inverse.  TRUNCNORM (a, b):
+        * hk[3] > 0: ndtri(p0 + u p1) with p0 = Phi(a); hk[3] < 0 (a >= 0, scipy's right-hand
+        * case): -ndtri(p0 + (1 - u) p1) with p0 = Phi(-b); p1 = Phi(b) - Phi(a) either way. */
+       OB2_DIST_CAUCHY = 20, OB2_DIST_CHI2 = 21, OB2_DIST_T = 22, OB2_DIST_TRUNCNORM = 23, OB2_DIST_LAST = 23 };
 
 /* per-slot transformer (build_required_space table) */
 enum {

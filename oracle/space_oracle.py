@@ -184,7 +184,8 @@ CLOSED_FORM_PRIORS = ('expon', 'lognorm', 'logistic', 'laplace', 'gumbel_r', 'we
                       # rv_discrete: rvs adds loc only (scale is 1)
                       'alpha', 'randint', 'poisson',
                       # special.gammaincinv / betaincinv
-                      'gamma', 'erlang', 'beta')
+                      'gamma', 'erlang', 'beta',
+                      'cauchy', 'chi2', 't', 'truncnorm')
 
 
 def _draw(spec: DimSpec, u: np.ndarray) -> np.ndarray:

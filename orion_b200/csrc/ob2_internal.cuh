@@ -240,6 +240,24 @@ static __device__ __noinline__ double beta_ppf(double a, double b, double lbeta,
     return x;
 }
 
+// Student t through the incomplete beta inverse: near the median w = t^2 / (df + t^2) =
+// betaincinv(1/2, df/2, 1 - 2 tail) (accurate for small t), in the tails z = df / (df + t^2) =
+// betaincinv(df/2, 1/2, 2 tail).  lbeta = lbeta(df/2, 1/2).
+static __device__ __noinline__ double t_ppf(double df, double lbeta, double p) {
+    if (p == 0.5) return 0.0;
+    const bool lower = p < 0.5;
+    const double tail = lower ? p : 1.0 - p;
+    double t;
+    if (tail > 0.25) {
+        const double w = beta_ppf(0.5, 0.5 * df, lbeta, 1.0 - 2.0 * tail);
+        t = sqrt(df * w / (1.0 - w));
+    } else {
+        const double z = beta_ppf(0.5 * df, 0.5, lbeta, 2.0 * tail);
+        t = sqrt(df * (1.0 - z) / z);
+    }
+    return lower ? -t : t;
+}
+
 // The extra priors, out of line and out of the common kernel (EXT = false
 // never references it).
 static __device__ __noinline__ double draw_extended(int dist, double p0, double p1, double p2, double u) {
@@ -276,6 +294,15 @@ static __device__ __noinline__ double draw_extended(int dist, double p0, double 
             return gamma_ppf(p0, p1, u);
         case OB2_DIST_BETA:  // p0 = a, p1 = b, p2 = lbeta(a, b)
             return beta_ppf(p0, p1, p2, u);
+        case OB2_DIST_CAUCHY:
+            return -cospi(u) / sinpi(u);  // tan(pi (u - 1/2))
+        case OB2_DIST_CHI2:  // p0 = df / 2, p1 = lgamma(df / 2)
+            return 2.0 * gamma_ppf(p0, p1, u);
+        case OB2_DIST_T:  // p0 = df, p1 = lbeta(df / 2, 1 / 2)
+            return t_ppf(p0, p1, u);
+        case OB2_DIST_TRUNCNORM:  // p0 = Phi(a) (p2 > 0) or Phi(-b) (p2 < 0), p1 = Phi(b) - Phi(a)
+            return p2 > 0.0 ? normcdfinv(__dadd_rn(p0, __dmul_rn(u, p1)))
+                            : -normcdfinv(__dadd_rn(p0, __dmul_rn(1.0 - u, p1)));
         default: {  // OB2_DIST_POISSON, p0 = mu, p1 = exp(-mu): smallest k with cdf(k) >= u
             double k = 0.0, pmf = p1, cdf = p1;
             const double k_max = p0 + 40.0 * sqrt(p0) + 60.0;  // the tail beyond is < 1e-300

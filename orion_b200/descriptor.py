@@ -108,6 +108,24 @@ def _prior_params(dim):
         from scipy.special import betaln
         a, b = float(args[0]), float(args[1])
         return 19, a, b, loc, scale, float(betaln(a, b))
+    if name == 'cauchy' and not args:
+        return 20, 0.0, 0.0, loc, scale
+    if name == 'chi2' and len(args) == 1:
+        from scipy.special import gammaln
+        half = 0.5 * float(args[0])
+        return 21, half, float(gammaln(half)), loc, scale
+    if name == 't' and len(args) == 1:
+        from scipy.special import betaln
+        df = float(args[0])
+        return 22, df, float(betaln(0.5 * df, 0.5)), loc, scale
+    if name == 'truncnorm' and len(args) == 2:
+        from scipy.special import ndtr
+        from scipy.stats._continuous_distns import _log_gauss_mass
+        a, b = float(args[0]), float(args[1])
+        mass = float(np.exp(_log_gauss_mass(np.float64(a), np.float64(b))))
+        if a < 0:           # scipy's left-hand case: Phi(x) = Phi(a) + q mass
+            return 23, float(ndtr(a)), mass, loc, scale, 1.0
+        return 23, float(ndtr(-b)), mass, loc, scale, -1.0      # right-hand: Phi(-x) = Phi(-b) + (1 - q) mass
     # any other scipy prior: bounds-only (contains / transform / dedup work, sampling refuses)
     return _lib.DIST_NONE, 0.0, 0.0, loc, scale
 

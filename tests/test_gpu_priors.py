@@ -20,6 +20,9 @@ PRIORS = [
     ('rayleigh', [0.0, 4.0]), ('halfnorm', []), ('powerlaw', [3.0]), ('powerlaw', [0.5, -1.0, 2.0]),
     ('gamma', [0.3]), ('gamma', [2.5, 1.0, 3.0]), ('gamma', [400.0]), ('erlang', [3]),
     ('beta', [2.0, 5.0]), ('beta', [0.5, 0.5]), ('beta', [30.0, 2.0, -1.0, 4.0]), ('beta', [1.0, 3.0]),
+    ('cauchy', []), ('cauchy', [1.0, 0.1]), ('chi2', [3.0]), ('chi2', [0.7, 0.0, 2.0]),
+    ('t', [1.0]), ('t', [2.5]), ('t', [30.0, 1.0, 0.5]),
+    ('truncnorm', [-1.0, 2.0]), ('truncnorm', [0.5, 3.0, 10.0, 2.0]), ('truncnorm', [-3.0, -1.0]), ('truncnorm', [2.0, 6.0]),
 ]
 
 
@@ -35,8 +38,10 @@ def test_from_uniform_matches_scipy_ppf():
     U = rng.random_sample((len(dims), n))
     U[:, :4] = [1e-300, 2.0 ** -53, 0.5, 1 - 2.0 ** -53]
     for j, (name, args) in enumerate(PRIORS):
-        if name == 'gamma' and args[0] > 100:
-            U[j, 0] = 1e-100       # P(400, x) itself underflows below ~1e-250 (a Philox u is 0 or >= 2^-53)
+        if (name == 'gamma' and args[0] > 100) or name == 't':
+            U[j, 0] = 1e-100       # P(400, x) / the beta variable of t underflow below ~1e-250 (a Philox u is 0 or >= 2^-53)
+        if name == 'truncnorm':
+            U[j, 0] = 1e-10        # at u ~ 0 the draw IS the bound a: in or out of [a, b) by one ulp of ndtri
     batch = space.compiled().sample_from_uniform(torch.from_numpy(U).cuda())
     got = batch.to_numpy()
     want, ok = so.sample_from_uniform(specs, U)
