@@ -26,7 +26,7 @@ def main():
     tspace = build_required_space('real', space)
     compiled = tspace.compiled()
     history = TrialHistory(compiled, capacity=8 * n)
-    pipe = CandidatePipeline(compiled, history, n)
+    pipe = CandidatePipeline(compiled, history, n, fingerprint_in='suggest')      # one kernel per batch + dedup
     torch.cuda.synchronize()
     t0 = time.perf_counter()
     slots = []
