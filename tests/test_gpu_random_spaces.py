@@ -52,3 +52,22 @@ def test_random_space_matches_oracle(case):
     bwant = so.reverse(specs, requirement, twant)
     for a, b in zip(compiled.reverse(tb).to_numpy(), bwant):
         assert a.dtype == b.dtype and np.array_equal(a, b)
+    # the one-kernel suggest over the same counters: every buffer as the staged kernels and the oracle have it
+    sb, st, sk = compiled.suggest(n, seed, base_index=base)
+    for a, b in zip(sb.to_numpy(), got):
+        assert np.array_equal(a, b)
+    for a, b in zip(st.to_numpy(), twant):
+        assert a.dtype == b.dtype and np.array_equal(a, b)
+    for a, b in zip(sk.to_numpy(), bwant):
+        assert a.dtype == b.dtype and np.array_equal(a, b)
+    assert torch.equal(sb.mask[:n], batch.mask[:n]) and torch.equal(sb.n_failed, batch.n_failed)
+    slo, shi = sk.fingerprints_numpy()
+    blo, bhi = so.fingerprint(bwant)
+    assert np.array_equal(slo, blo) and np.array_equal(shi, bhi)
+    # ... and the wire hand-over of a random subset is lossless
+    keep_host = (rng.random_sample(n) < 0.6).astype(np.uint8)
+    keep = torch.from_numpy(keep_host).cuda()
+    in_space = batch.mask[:n].cpu().numpy().astype(bool)
+    wire = batch.compact(keep & batch.mask[:n], wire=True)
+    for a, b in zip(wire.to_numpy(), got):
+        assert np.array_equal(a, b[keep_host.astype(bool) & in_space])
