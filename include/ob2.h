@@ -11,7 +11,9 @@
  *     ob2_last_error() gives the message for the calling thread.
  *   - all data pointers are DEVICE pointers owned by the caller; the library
  *     never allocates caller-visible memory.  Handles own only their small
- *     descriptor tables.
+ *     descriptor tables.  The exceptions are the three *_host entry points
+ *     (small calls with HOST buffers in and out, synchronous): they stage
+ *     through a block the space handle allocates on first use.
  *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default
  *     stream).  Calls are asynchronous on that stream unless stated.
  *   - column sets: one contiguous block per batch; the column of scalar slot s
@@ -91,7 +93,7 @@ typedef struct ob2_slot_desc {
     double p0, p1;     /* reciprocal: log(a), log(b) - log(a)                     */
     double loc, scale; /* x = base(u) * scale + loc  (scipy rv_generic.rvs)       */
     double low, high;  /* accepted iff low <= x < high (space.py:160-164)         */
-    uint64_t hk[4];    /* fingerprint: xor key, 2 x packed odd multipliers; hk[3]: third prior parameter (BETA) */
+    uint64_t hk[4];    /* fingerprint: xor key, 2 x packed odd multipliers; hk[3]: bits of a third prior parameter (BETA, TRUNCNORM) */
 } ob2_slot_desc;
 
 typedef struct ob2_space ob2_space;
