@@ -61,7 +61,10 @@ enum { OB2_DIST_UNIFORM = 0, OB2_DIST_RECIPROCAL = 1, OB2_DIST_NORM = 2, OB2_DIS
         * inverse.  T: p0 = df, p1 = lbeta(df / 2, 1 / 2), through the beta inverse.  TRUNCNORM (a, b):
         * hk[3] > 0: ndtri(p0 + u p1) with p0 = Phi(a); hk[3] < 0 (a >= 0, scipy's right-hand
         * case): -ndtri(p0 + (1 - u) p1) with p0 = Phi(-b); p1 = Phi(b) - Phi(a) either way. */
-       OB2_DIST_CAUCHY = 20, OB2_DIST_CHI2 = 21, OB2_DIST_T = 22, OB2_DIST_TRUNCNORM = 23, OB2_DIST_LAST = 23 };
+       OB2_DIST_CAUCHY = 20, OB2_DIST_CHI2 = 21, OB2_DIST_T = 22, OB2_DIST_TRUNCNORM = 23,
+       /* GEOM: p0 = p, p1 = log1p(-p), scipy's _ppf verbatim.  BINOM: p0 = n, p1 = p, hk[3] = bits of
+        * (1 - p)^n (must not underflow); the smallest k with cdf(k) >= u by summing the pmf. */
+       OB2_DIST_GEOM = 24, OB2_DIST_BINOM = 25, OB2_DIST_LAST = 25 };
 
 /* per-slot transformer (build_required_space table) */
 enum {

@@ -185,7 +185,8 @@ CLOSED_FORM_PRIORS = ('expon', 'lognorm', 'logistic', 'laplace', 'gumbel_r', 'we
                       'alpha', 'randint', 'poisson',
                       # special.gammaincinv / betaincinv
                       'gamma', 'erlang', 'beta',
-                      'cauchy', 'chi2', 't', 'truncnorm')
+                      'cauchy', 'chi2', 't', 'truncnorm',
+                      'geom', 'binom')
 
 
 def _draw(spec: DimSpec, u: np.ndarray) -> np.ndarray:

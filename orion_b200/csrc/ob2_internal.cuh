@@ -303,6 +303,21 @@ static __device__ __noinline__ double draw_extended(int dist, double p0, double 
         case OB2_DIST_TRUNCNORM:  // p0 = Phi(a) (p2 > 0) or Phi(-b) (p2 < 0), p1 = Phi(b) - Phi(a)
             return p2 > 0.0 ? normcdfinv(__dadd_rn(p0, __dmul_rn(u, p1)))
                             : -normcdfinv(__dadd_rn(p0, __dmul_rn(1.0 - u, p1)));
+        case OB2_DIST_GEOM: {  // p0 = p, p1 = log1p(-p); geom_gen._ppf, operation for operation
+            const double vals = ceil(log1p(-u) / p1);
+            const double temp = -expm1(p1 * floor(vals - 1.0));
+            return (temp >= u && vals > 0.0) ? vals - 1.0 : vals;
+        }
+        case OB2_DIST_BINOM: {  // p0 = n, p1 = p, p2 = (1 - p)^n: smallest k with cdf(k) >= u
+            double k = 0.0, pmf = p2, cdf = p2;
+            const double odds = p1 / (1.0 - p1);
+            while (cdf < u && k < p0) {
+                pmf *= (p0 - k) / (k + 1.0) * odds;
+                k += 1.0;
+                cdf += pmf;
+            }
+            return k;
+        }
         default: {  // OB2_DIST_POISSON, p0 = mu, p1 = exp(-mu): smallest k with cdf(k) >= u
             double k = 0.0, pmf = p1, cdf = p1;
             const double k_max = p0 + 40.0 * sqrt(p0) + 60.0;  // the tail beyond is < 1e-300

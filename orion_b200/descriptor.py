@@ -126,6 +126,14 @@ def _prior_params(dim):
         if a < 0:           # scipy's left-hand case: Phi(x) = Phi(a) + q mass
             return 23, float(ndtr(a)), mass, loc, scale, 1.0
         return 23, float(ndtr(-b)), mass, loc, scale, -1.0      # right-hand: Phi(-x) = Phi(-b) + (1 - q) mass
+    if name == 'geom' and len(args) == 1:
+        p = float(args[0])
+        return 24, p, float(np.log1p(-p)), loc, scale
+    if name == 'binom' and len(args) == 2:
+        n_trials, p = float(args[0]), float(args[1])
+        pmf0 = float(np.exp(n_trials * np.log1p(-p))) if p < 1 else 0.0
+        if pmf0 > 1e-290:          # (otherwise the pmf recurrence cannot start: bounds-only)
+            return 25, n_trials, p, loc, scale, pmf0
     # any other scipy prior: bounds-only (contains / transform / dedup work, sampling refuses)
     return _lib.DIST_NONE, 0.0, 0.0, loc, scale
 

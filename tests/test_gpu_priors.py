@@ -87,6 +87,10 @@ DSL_EXAMPLES = [      # the priors of the reference's own DSL examples (space_bu
     dict(name='p', kind='integer', prior='poisson', args=[], kwargs=dict(mu=3)),
     dict(name='p2', kind='integer', prior='poisson', args=[0.5], kwargs=dict(loc=2)),
     dict(name='p3', kind='integer', prior='poisson', args=[120.0]),
+    dict(name='gm', kind='integer', prior='geom', args=[0.3]),
+    dict(name='gm2', kind='integer', prior='geom', args=[0.02], kwargs=dict(loc=-1)),
+    dict(name='bn', kind='integer', prior='binom', args=[20, 0.3]),
+    dict(name='bn2', kind='integer', prior='binom', args=[100, 0.9]),
 ]
 
 
@@ -109,7 +113,7 @@ def test_dsl_example_priors_from_uniform():
         np.testing.assert_allclose(got[j], stats.alpha.ppf(U[j], *DSL_EXAMPLES[j]['args']), rtol=1e-6, atol=1e-300)
     for j in (2, 3):
         assert got[j].dtype == np.int64 and np.array_equal(got[j], want[j])
-    for j in (4, 5, 6):
+    for j in (4, 5, 6, 7, 8, 9, 10):
         assert int((got[j] != want[j]).sum()) <= 1
     assert int((batch.mask.cpu().numpy().astype(bool) != ok).sum()) <= 1
 

@@ -213,7 +213,7 @@ class TestInteger(object):
 
     @gpu
     def test_unsupported_prior_has_no_cpu_fallback(self):
-        dim = Integer('yolo', 'binom', 10, 0.5)
+        dim = Integer('yolo', 'hypergeom', 20, 7, 12)
         assert 3 in dim
         with pytest.raises(NotImplementedError):
             dim.sample()
