@@ -433,3 +433,8 @@ __device__ __forceinline__ void ld_i64x2(const long long *p, long long &a, long 
 __device__ __forceinline__ void ld_i32x2(const int *p, int &a, int &b) {
     asm volatile("ld.global.nc.L1::no_allocate.v2.s32 {%0, %1}, [%2];" : "=r"(a), "=r"(b) : "l"(p));
 }
+
+// One-hot pair: 1.0 = 0x3FF00000'00000000, so only the high words are selected.
+__device__ __forceinline__ void st_onehot_hi(double *p, unsigned h0, unsigned h1) {
+    asm volatile("st.global.cs.v4.u32 [%0], {%1, %2, %1, %3};" ::"l"(p), "r"(0u), "r"(h0), "r"(h1) : "memory");
+}

@@ -28,11 +28,6 @@ __device__ __forceinline__ long long quantize_ll(double x, int t_flags) {
     return __double2ll_rz((t_flags & OB2_TFLAG_FLOOR) ? floor(x) : rint(x));
 }
 
-// One-hot pair: 1.0 = 0x3FF00000'00000000, so only the high words are selected.
-__device__ __forceinline__ void st_onehot_hi(double *p, unsigned h0, unsigned h1) {
-    asm volatile("st.global.cs.v4.u32 [%0], {%1, %2, %1, %3};" ::"l"(p), "r"(0u), "r"(h0), "r"(h1) : "memory");
-}
-
 // Categorical draw = #{j : cdf[j] <= u}.  With equal probabilities floor(u * k)
 // is within one of the answer, so start there and walk to the exact index
 // (exact for ANY non-decreasing cdf; the guess only decides how far the walk is).
