@@ -30,12 +30,26 @@ class Random(BaseAlgorithm):
         """Lazily created :class:`orion_b200.history.TrialHistory`."""
         if self._history is None:
             from ..history import TrialHistory
-            self._history = TrialHistory(self.space, capacity=self.history_capacity)
+            # rows are remembered as they are handed out in the ORIGINAL space (what a trial stores)
+            self._history = TrialHistory(getattr(self.space, 'original', self.space), capacity=self.history_capacity)
         return self._history
+
+    @property
+    def _transformed(self):
+        """Is the algorithm's space a TransformedSpace (the way PrimaryAlgo is meant to wrap it)?"""
+        return hasattr(self.space, 'original')
 
     def suggest_columns(self, num=1, check=True):
         """Device-resident suggestion: ColumnBatch with ``mask`` (and ``keep``
         when dedup is on; kept rows join the history)."""
+        if self._transformed:
+            # one kernel: sample -> transform -> reverse -> fingerprint.  The algorithm's points are the
+            # TRANSFORMED batch; dedup is on the rows as handed out (reverse of it), kept in ``.original``.
+            batch, tbatch, back = self.space.suggest_columns(num, self._rng, check=check)
+            tbatch.mask, tbatch.fp, tbatch.original = batch.mask, back.fp, back
+            if self.dedup:
+                tbatch.keep = self.history.dedup_fingerprints(back.fp, num)
+            return tbatch
         batch = self.space.sample_columns(num, self._rng, with_fingerprint=bool(self.dedup), check=check)
         if self.dedup:
             self.history.dedup(batch)
@@ -51,7 +65,11 @@ class Random(BaseAlgorithm):
             need = num - len(points)
             if need <= 0:
                 break
-            if need <= HOST_SAMPLE_MAX:                 # draw + dedup + copy + sync in one library call
+            if self._transformed:
+                tbatch = self.suggest_columns(need)
+                keep = tbatch.keep[:need].cpu().numpy().astype(bool)
+                rows = self.space._rows_from_tcols(tbatch.to_numpy(), need)
+            elif need <= HOST_SAMPLE_MAX:               # draw + dedup + copy + sync in one library call
                 compiled = self.space.compiled()
                 cols, failed, keep = compiled.sample_host(need, philox_key(self._rng), history=self.history)
                 _raise_if_failed(failed, compiled, list(self.space.values()))
@@ -67,4 +85,6 @@ class Random(BaseAlgorithm):
         """Random search learns nothing from results; with dedup on, observed
         points are recorded so they are never suggested again."""
         if self.dedup and points:
+            if self._transformed:
+                points = self.space.reverse_points(points)
             self.history.observe_points(points)

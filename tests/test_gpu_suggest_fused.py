@@ -165,3 +165,42 @@ def test_pipeline_fused_agrees_with_staged():
     for ra, rb in zip(rows['suggest'], rows['reverse']):
         for a, b in zip(ra, rb):
             assert torch.equal(a, b)
+
+
+@pytest.mark.parametrize('requirement', ['real', 'integer'])
+def test_random_over_a_transformed_space(requirement):
+    """Random wrapped the way PrimaryAlgo is meant to wrap it: its space is the
+    TransformedSpace, its points are transformed points, dedup is on the rows
+    as handed out."""
+    from orion_b200.algo.random import Random
+    from orion_b200.space import Categorical, Integer, Real, Space
+    from orion_b200.transformer import build_required_space
+    space = Space()
+    space.register(Integer('i', 'uniform', 0, 4))
+    space.register(Categorical('c', ['a', 'b', 'c']))
+    space.register(Real('x', 'uniform', 0, 2))
+    # (floor: Quantize by rounding could hand out x = 2.0, outside the original [0, 2) -- Appendix B.2's
+    # `reverse(p) in original` would then reject the point)
+    tspace = build_required_space(requirement, space, quantize='floor')
+    algo = Random(tspace, seed=3)
+    pts = algo.suggest(5)
+    assert len(pts) == 5 and all(p in tspace for p in pts)
+    assert all(tspace.reverse(p) in space for p in pts)
+    tb = algo.suggest_columns(1000)
+    assert tb.transformed and bool(tb.mask[:1000].all()) and tb.original.n == 1000
+    for a, b in zip(tspace.reverse_columns(tb).to_numpy(), tb.original.to_numpy()):
+        assert np.array_equal(a, b)
+    # dedup: 'integer' floors x to {0, 1}: 4 * 3 * 2 = 24 distinct handed-out rows, never one twice
+    dd = Random(tspace, seed=4, dedup=True)
+    if requirement == 'integer':
+        seen = []
+        for _ in range(8):
+            got = dd.suggest(3)
+            seen.extend(tuple(np.asarray(v).tolist() if hasattr(v, 'tolist') else v for v in tspace.reverse(p)) for p in got)
+        assert len(seen) == 24 and len(set(seen)) == 24
+        assert dd.suggest(1) == []
+    else:
+        got = dd.suggest(50)
+        assert len(got) == 50
+        dd.observe(got, [{'objective': 0.0}] * 50)                   # observed points stay known
+        assert len(dd.history) == 50
