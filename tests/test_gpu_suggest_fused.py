@@ -204,3 +204,36 @@ def test_random_over_a_transformed_space(requirement):
         assert len(got) == 50
         dd.observe(got, [{'objective': 0.0}] * 50)                   # observed points stay known
         assert len(dd.history) == 50
+
+
+def test_primary_algo_with_a_requirement_hands_out_original_points():
+    """The design the reference leaves as TODOs (primary_algo.py:13-14,42,55,66):
+    the wrapped algorithm works in the transformed space, the caller only ever
+    sees points of the original one."""
+    from orion_b200.primary_algo import PrimaryAlgo
+    from orion_b200.space import Categorical, Integer, Real, Space
+    space = Space()
+    space.register(Categorical('c', ['a', 'b', 'c', 'd']))
+    space.register(Integer('i', 'uniform', -3, 6))
+    space.register(Real('x', 'reciprocal', 1e-3, 1.0))
+    palgo = PrimaryAlgo(space, {'random': {'seed': 7, 'dedup': True}}, requirement='real')
+    inner = palgo.algorithm
+    assert inner.space is palgo.transformed_space and palgo.space is space
+    assert len(inner.space['c'].shape) == 1 and inner.space['c'].shape[0] == 4      # one-hot inside
+    pts = palgo.suggest(6)
+    assert len(pts) == 6 and all(p in space for p in pts)
+    assert all(p[0] in 'abcd' and int(p[1]) == p[1] for p in pts)
+    back = palgo.suggest_columns(500)
+    assert not back.transformed and back.n == 500 and bool(back.mask[:500].all())
+    assert back.transformed_batch.transformed and back.keep is not None
+    palgo.observe(pts, [{'objective': float(j)} for j in range(len(pts))])   # transformed on the way in
+    assert palgo.score(pts[0]) == 0 and palgo.judge(pts[0], {}) is None
+    before = len(inner.history)
+    palgo.observe(pts, [{'objective': 0.0}] * len(pts))                      # already known: nothing new
+    assert len(inner.history) == before
+    with pytest.raises(AssertionError):
+        palgo.observe([('z', 0, 0.5)], [{'objective': 0.0}])
+    # without a requirement the wrapper is the snapshot's: same space inside and out
+    plain = PrimaryAlgo(space, {'random': {'seed': 7}})
+    assert plain.transformed_space is None and plain.algorithm.space is space
+    assert all(p in space for p in plain.suggest(3))
