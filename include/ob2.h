@@ -154,8 +154,9 @@ int ob2_sample_transform(const ob2_space *space, int64_t n, int64_t n_stride, ui
 /* Random.suggest behind PrimaryAlgo in ONE kernel (src/orion/algo/random.py:24-33 called
  * through src/orion/core/worker/primary_algo.py:44-56): the draw and transform of
  * ob2_sample_transform, plus reverse() of every transformed value while it is still in
- * registers -- written to `back` (the handed-out rows; same layout as `cols`, a distinct
- * 16-byte aligned buffer) -- plus the fingerprint of the `back` rows into `fp` (required).
+ * registers -- written to `back` (the handed-out rows; same layout as `cols`, 16-byte
+ * aligned; `back` == `cols` is allowed and means "keep only the handed-out rows": one store
+ * per value instead of two) -- plus the fingerprint of the `back` rows into `fp` (required).
  * Results are bit-identical to ob2_sample_transform followed by ob2_reverse_fingerprint;
  * what is saved is re-reading the transformed columns (the widest stream of the path).
  * Algorithms that compute in the transformed space keep using the separate kernels. */

@@ -93,7 +93,7 @@ __device__ __forceinline__ bool redraw_dim(const ob2_slot_desc *s_slots, int s_l
                         reinterpret_cast<long long *>(dst)[i] = q;
                     }
                 }
-                if (WITH_B) reinterpret_cast<long long *>(col + bdelta)[i] = bq;
+                if (WITH_B && bdelta != 0) reinterpret_cast<long long *>(col + bdelta)[i] = bq;
                 w = (uint64_t)bq;
             } else {
                 reinterpret_cast<double *>(col)[i] = x;
@@ -107,7 +107,7 @@ __device__ __forceinline__ bool redraw_dim(const ob2_slot_desc *s_slots, int s_l
                         reinterpret_cast<double *>(dst)[i] = x;
                     }
                 }
-                if (WITH_B) reinterpret_cast<double *>(col + bdelta)[i] = bx;
+                if (WITH_B && (bdelta != 0 || d.t_op == OB2_OP_QUANTIZE)) reinterpret_cast<double *>(col + bdelta)[i] = bx;
                 w = canon_f64(WITH_B ? bx : x);
             }
             ok &= (x >= d.low) && (x < d.high);
@@ -160,6 +160,9 @@ sample_kernel(const ob2_slot_desc *__restrict__ g_slots, int n_slots, const doub
     }
     if (!has1) idx1 = idx0;  // the padding candidate replays its neighbour: always well defined
 
+    // back == cols (bdelta == 0): the caller keeps only the handed-out rows; the second store of every
+    // value is skipped (reverse(transform(x)) == x bit for bit except through a lossy Quantize)
+    const bool split = WITH_B && bdelta != 0;
     FpAcc acc0{0, 0}, acc1{0, 0};
     bool ok0 = true, ok1 = true;    // current dimension
     bool all0 = true, all1 = true;  // whole candidate
@@ -226,7 +229,7 @@ sample_kernel(const ob2_slot_desc *__restrict__ g_slots, int n_slots, const doub
                     tcol += (uint64_t)k * s8;
                 }
             }
-            if (WITH_B) st_i32x2(bcol, b0, b1);
+            if (WITH_B && split) st_i32x2(bcol, b0, b1);
             w0 = (uint64_t)(int64_t)b0;
             w1 = (uint64_t)(int64_t)b1;
             if (!PHILOX) {  // an injected u >= 1 can run off the table; a Philox u cannot
@@ -254,7 +257,7 @@ sample_kernel(const ob2_slot_desc *__restrict__ g_slots, int n_slots, const doub
                     }
                     tcol += stride8;
                 }
-                if (WITH_B) st_i64x2(reinterpret_cast<long long *>(col + bdelta), bq0, bq1);
+                if (WITH_B && split) st_i64x2(reinterpret_cast<long long *>(col + bdelta), bq0, bq1);
                 w0 = (uint64_t)bq0;
                 w1 = (uint64_t)bq1;
             } else {
@@ -273,7 +276,9 @@ sample_kernel(const ob2_slot_desc *__restrict__ g_slots, int n_slots, const doub
                     }
                     tcol += stride8;
                 }
-                if (WITH_B) st_f64x2(reinterpret_cast<double *>(col + bdelta), bx0, bx1);
+                // (aliased: only a lossy Quantize round trip differs from what was just stored)
+                if (WITH_B && (split || d.t_op == OB2_OP_QUANTIZE))
+                    st_f64x2(reinterpret_cast<double *>(col + bdelta), bx0, bx1);
                 w0 = canon_f64(bx0);
                 w1 = canon_f64(bx1);
             }
@@ -462,8 +467,8 @@ extern "C" int ob2_suggest(const ob2_space *space, int64_t n, int64_t n_stride, 
         ob2_set_error("ob2_suggest: null transformed / handed-out / fingerprint buffer");
         return OB2_EINVAL;
     }
-    if (back == cols || ((uintptr_t)back & 15) != 0) {
-        ob2_set_error("ob2_suggest: `back` must be a 16-byte aligned buffer distinct from `cols`");
+    if (((uintptr_t)back & 15) != 0) {
+        ob2_set_error("ob2_suggest: `back` must be 16-byte aligned");
         return OB2_EINVAL;
     }
     const SampleArgs a{space, n, n_stride, seed, base_index, index, nullptr, cols, tcols, back, mask, fp, n_failed, stream};

@@ -332,7 +332,9 @@ class CompiledSpace(object):
         sample -> transform -> reverse -> fingerprint.  Returns ``(batch, tbatch,
         back)``; ``back.fp`` holds the fingerprints of the handed-out rows and
         ``batch.mask`` the fused ``point in space``.  Bit-identical to
-        ``sample(transformed_out=...)`` followed by ``reverse(with_fingerprint=True)``."""
+        ``sample(transformed_out=...)`` followed by ``reverse(with_fingerprint=True)``.
+        ``back_out`` may be the same batch as ``out``: only the handed-out rows
+        are then kept (one store per value instead of two)."""
         self._require_samplable()
         batch = out if out is not None else self.empty_columns(n)
         tb = transformed_out if transformed_out is not None else self.empty_columns(n, transformed=True)

@@ -131,13 +131,25 @@ def test_transformed_space_suggest_columns():
     assert np.array_equal(lo, wlo) and np.array_equal(hi, whi)
 
 
-def test_suggest_rejects_aliased_buffers():
-    from orion_b200 import _lib, spaces
+@pytest.mark.parametrize('requirement', ['real', 'integer', None])
+def test_suggest_with_back_aliased_to_cols_keeps_the_handed_out_rows(requirement):
+    """back == cols: one buffer, holding the rows as handed out (which differ
+    from the sampled ones only through a lossy Quantize), same fingerprints,
+    same transformed columns -- redraw rows included."""
     from orion_b200.transformer import build_required_space
-    compiled = build_required_space('real', spaces.rosen2()).compiled()
-    batch = compiled.empty_columns(64)
-    with pytest.raises(_lib.Ob2Error):
-        compiled.suggest(64, 1, out=batch, back_out=batch)
+    g = gu.load('bounded_reject')
+    extra = [dict(d, name='m_' + d['name']) for d in gu.load('mixed_scalar')['dims'][5:]]
+    space = gu.product_space(g['dims'] + extra + [dict(name='sh', kind='categorical', categories=[1, 2, 3], shape=[2])])
+    compiled = build_required_space(requirement, space).compiled()
+    for n in (1, 3001):
+        b0, t0, k0 = compiled.suggest(n, 123)
+        one = compiled.empty_columns(n)
+        b1, t1, k1 = compiled.suggest(n, 123, out=one, back_out=one)
+        assert b1 is k1
+        _same(k1, k0, n)
+        _same(t1, t0, n)
+        assert torch.equal(k1.fp[:n], k0.fp[:n]) and torch.equal(b1.mask[:n], b0.mask[:n])
+        assert torch.equal(b1.n_failed, b0.n_failed)
 
 
 def test_pipeline_fused_agrees_with_staged():
