@@ -26,6 +26,7 @@ struct ob2_space {
     int32_t t_cols;      // number of transformed columns
     size_t smem_bytes;   // descriptor + cdf staging size
     ob2_slot_desc *d_slots;
+    ob2_slot_desc *h_slots;  // host copy of the uploaded table (launch-parameter path of the sampler)
     double *d_cdf;
     bool has_onehot;
     bool has_extended_prior;  // a slot uses one of the OB2_DIST_EXPON.. priors

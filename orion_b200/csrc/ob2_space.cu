@@ -177,7 +177,7 @@ extern "C" int ob2_space_create(const ob2_slot_desc *slots, int32_t n_slots, con
     if (rc == OB2_OK)
         rc = ob2_check_cuda(cudaMemcpy(sp->d_slots, staged, (size_t)n_slots * sizeof(ob2_slot_desc), cudaMemcpyHostToDevice),
                             "cudaMemcpy(slots)");
-    delete[] staged;
+    sp->h_slots = staged;  // kept: small spaces travel in the sampler's launch parameters
     // always allocate at least one element so kernels get a valid pointer
     if (rc == OB2_OK) rc = ob2_check_cuda(cudaMalloc(&sp->d_cdf, (size_t)(cdf_len > 0 ? cdf_len : 1) * sizeof(double)), "cudaMalloc(cdf)");
     if (rc == OB2_OK && cdf_len > 0)
@@ -197,6 +197,7 @@ extern "C" void ob2_space_destroy(ob2_space *sp) {
     if (sp->d_stage) cudaFree(sp->d_stage);
     if (sp->h_stage) cudaFreeHost(sp->h_stage);
     delete sp->stage_mutex;
+    delete[] sp->h_slots;
     delete[] sp->wire_units;
     delete[] sp->wire_bytes;
     delete sp;

@@ -249,3 +249,25 @@ def test_primary_algo_with_a_requirement_hands_out_original_points():
     plain = PrimaryAlgo(space, {'random': {'seed': 7}})
     assert plain.transformed_space is None and plain.algorithm.space is space
     assert all(p in space for p in plain.suggest(3))
+
+
+def test_suggest_on_a_space_too_wide_for_the_launch_parameters():
+    """Up to 192 slots the suggest kernel reads its descriptors from the launch
+    parameters (constant bank); wider spaces go through the shared-memory
+    staging.  Both must agree with the staged kernels."""
+    from orion_b200.space import Categorical, Integer, Real, Space
+    from orion_b200.transformer import build_required_space
+    for width in (96, 100):                       # 2 * width slots: 192 (parameter path) and 200 (shared memory)
+        space = Space()
+        space.register(Real('x', 'uniform', -1, 2, shape=width))
+        space.register(Integer('k', 'uniform', -5, 10, shape=width // 2))
+        space.register(Categorical('c', ['a', 'b', 'c'], shape=width // 2))
+        compiled = build_required_space('real', space).compiled()
+        assert compiled.n_slots == 2 * width
+        n = 1001
+        b0, t0, k0 = _staged(compiled, n, 9)
+        b1, t1, k1 = compiled.suggest(n, 9)
+        _same(b1, b0, n)
+        _same(t1, t0, n)
+        _same(k1, k0, n)
+        assert torch.equal(k1.fp[:n], k0.fp[:n]) and torch.equal(b1.mask[:n], b0.mask[:n])
