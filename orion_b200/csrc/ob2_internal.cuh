@@ -346,10 +346,12 @@ __device__ __forceinline__ double draw_real(const ob2_slot_desc &d, double u) {
         case OB2_DIST_NORM:
             b = normcdfinv(u);
             break;
-        case OB2_DIST_CONST:
-            return d.loc;  // scale == 0
-        default:  // closed-form inverse CDFs of further scipy priors (scipy's own _ppf formulas)
-            if (!EXT) return d.loc;
+        default:
+            // scale == 0 (OB2_DIST_CONST): rvs returns loc.  Without EXT nothing else can arrive here (the
+            // launcher picks the EXT instantiation for spaces with further priors) and the switch is the
+            // three-case one the common kernel was tuned with.
+            if (!EXT || d.dist == OB2_DIST_CONST) return d.loc;
+            // further scipy priors (scipy's own _ppf formulas)
             b = draw_extended(d.dist, d.p0, d.p1, __longlong_as_double((long long)d.hk[3]), u);
             break;
     }
