@@ -428,9 +428,10 @@ int launch_one(const SampleArgs &a, unsigned blocks) {
     auto kern = sample_kernel<PHILOX, WITH_FP, WITH_T, WITH_B, EXT>;
     const int64_t bdelta = WITH_B ? (const char *)a.back - (const char *)a.cols : 0;
     const ob2_space *sp = a.sp;
-    // Descriptors in the launch parameters: measured -1.5 % on the fused suggest kernel (4.39 -> 4.33 ms),
-    // but +8 % on the issue-bound plain sampler (real16: 5.03 -> 5.45 ms per 1e8), so only the former uses it.
-    if (WITH_B && sp->n_slots <= OB2_PARAM_SLOTS && sp->h_slots != nullptr) {
+    // Descriptors in the launch parameters: measured -1.5 % on the fused kernels (suggest 4.39 -> 4.33 ms,
+    // sample+transform 3.46 -> 3.41 ms) but +5 % on the issue-bound plain sampler (real16: 4.99 -> 5.23 ms
+    // per 1e8), so only the store-heavy variants use it.
+    if ((WITH_B || WITH_T) && sp->n_slots <= OB2_PARAM_SLOTS && sp->h_slots != nullptr) {
         auto kern_p = sample_kernel_p<PHILOX, WITH_FP, WITH_T, WITH_B, EXT>;
         static thread_local ob2_slot_table tbl;  // (24 KB: not on the stack)
         memcpy(tbl.s, sp->h_slots, (size_t)sp->n_slots * sizeof(ob2_slot_desc));
