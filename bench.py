@@ -345,7 +345,10 @@ def run_b200(args):
     if table_slots_for(cap_rows, load=0.75) > (1 << 31):
         raise SystemExit("bench.py: %d steps of %d candidates on top of %d history rows need more than the 2^31 slots "
                          "one history table holds; use fewer --steps or --cands" % (total_steps, n, H))
-    history = TrialHistory(compiled, n_slots=table_slots_for(cap_rows, load=0.75))
+    # linear probing: short chains (one 128-byte line) while the table stays under ~40 % full; take the
+    # roomier size when it fits the 2^31-slot limit (69 GB of the 180 GB), else settle for <= 75 %
+    load = 0.4 if table_slots_for(cap_rows, load=0.4) <= (1 << 31) else 0.75
+    history = TrialHistory(compiled, n_slots=table_slots_for(cap_rows, load=load))
     # 'auto': peer-memory inboxes (kernels store straight into the owners' HBM over NVLink) where the
     # ranks can map each other's memory, NCCL all-to-all otherwise
     from orion_b200.dist import PeerShardedHistory, make_sharded_history
@@ -675,6 +678,8 @@ def run_b200(args):
         "serial_ms_per_step": serial_ms,
         "kernels_in_timed_region_ms": contended_ms,
         "staged_path": staged_info,
+        "history_table": {"slots": history.n_slots, "bytes": history.n_slots * 32,
+                          "load_at_end": hist_rows1 / float(history.n_slots)},
         "checks": {"kept_last_step": kept_last, "kept_frac_last_step": kept_last / float(n), "all_in_space": mask_ok,
                    "reverse_of_transform_is_identity": round_trip_ok,
                    "history_rows_before": hist_rows0, "history_rows_after": hist_rows1},
