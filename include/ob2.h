@@ -21,6 +21,10 @@
  *     running sum of element sizes (8 for Real/Integer, 4 for Categorical) and
  *     n_stride >= n is a multiple of 32 (so every column is 128-byte aligned).
  *     Per-candidate arrays (mask, keep, fingerprints, U) are n_stride long.
+ *   - alignment: column blocks (cols, tcols, back, out_cols), fingerprint arrays and U must be
+ *     16-byte aligned (they are accessed 128 bits at a time), mask / ok arrays 2-byte aligned,
+ *     index arrays 8-byte, counters 4-byte.  Anything else is refused with OB2_EINVAL -- a
+ *     misaligned vector access on the device would poison the CUDA context instead.
  */
 #ifndef OB2_H_
 #define OB2_H_
@@ -246,15 +250,21 @@ int ob2_set_dedup(ob2_set *set, int64_t n, const uint64_t *fp, const uint32_t *o
  * synchronise the whole device; a minimal binding that only ever holds the
  * input and output buffers it was given.  The u32-per-entry scratch that
  * ob2_set_dedup takes from the caller is instead a fixed array inside the
- * library: every GPU that loads libob2 carries OB2_STATIC_DEDUP_MAX * 4 bytes
- * (4 MiB) for it until the process exits.  The call itself allocates nothing
- * (no cudaMalloc/cudaFree, no allocating library routine).
+ * library: OB2_STATIC_DEDUP_MAX * 4 bytes (4 MiB) that a GPU carries from the
+ * moment the CUDA module with the hash-set kernels is loaded on it until the
+ * process exits.  Under CUDA's default lazy loading that moment is the first
+ * hash-set call on the GPU -- ob2_set_create, which also looks the array up --
+ * so the 4 MiB are claimed at set-up time, not by a dedup call.  The call
+ * itself allocates nothing (no cudaMalloc/cudaFree, no allocating library
+ * routine, no module load once ob2_set_create has run on that device).
  *   - n > OB2_STATIC_DEDUP_MAX is refused with OB2_ETOOBIG: split the batch
  *     into consecutive calls (a row kept by an earlier call beats its copies
  *     in later ones), or use ob2_set_dedup.
- *   - the first call on each device looks up the array's device address
- *     (cudaGetSymbolAddress, with that device current); make that first call
- *     before any stream capture begins.
+ *   - the array's device address is looked up once per device
+ *     (cudaGetSymbolAddress, with that device current) by ob2_set_create; a set
+ *     created on another device than the one the call runs on is refused, so
+ *     the look-up has always happened.  Create the set before any stream
+ *     capture begins.
  *   - all calls share the one array per GPU, and it keeps whatever the last
  *     call wrote.  Nothing in it needs to start at zero (pass 1 writes every
  *     entry pass 2 reads).  Two calls that overlap on the GPU -- different
@@ -323,8 +333,12 @@ int ob2_scatter_verdict(int64_t n_entries, const uint32_t *src_index, const uint
  *                       (insert_only != 0: history load, no verdicts)
  *     <barrier>
  *     ob2_xchg_collect  scatter the verdicts I received into keep[0..n)
- * `cap` = capacity of one (source, owner) lane; ob2_xchg_send_counts reads back
- * how many entries went to each owner (a count above cap means dropped entries). */
+ * `cap` = capacity of one (source, owner) lane, rounded up by the library to a multiple of 16
+ * (ob2_xchg_cap returns the value in force); ob2_xchg_send_counts reads back how many entries
+ * went to each owner (a count above cap means dropped entries; synchronises), and
+ * ob2_xchg_flag_overflow raises *flag (device u32, never cleared by the library) to 1 on the
+ * stream if any lane of the last send overflowed -- so that the ranks can agree on it with a
+ * collective they run anyway, without a host round trip per batch. */
 typedef struct ob2_xchg ob2_xchg;
 int ob2_xchg_create(int32_t rank, int32_t world, int64_t cap, ob2_xchg **out);
 void ob2_xchg_destroy(ob2_xchg *x);
@@ -336,6 +350,8 @@ int ob2_xchg_send(ob2_xchg *x, int64_t n, const uint64_t *fp, uint32_t key_base,
 int ob2_xchg_dedup(ob2_xchg *x, ob2_set *set, int32_t insert_only, void *stream);
 int ob2_xchg_collect(ob2_xchg *x, int64_t n, uint8_t *keep, void *stream);
 int ob2_xchg_send_counts(const ob2_xchg *x, uint32_t *counts_host, void *stream);
+int64_t ob2_xchg_cap(const ob2_xchg *x);
+int ob2_xchg_flag_overflow(const ob2_xchg *x, uint32_t *flag, void *stream);
 
 #ifdef __cplusplus
 }

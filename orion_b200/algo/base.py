@@ -102,6 +102,8 @@ class _AlgorithmFactory(ABCMeta):
                 for ep in group:
                     try:
                         ep.load()
+                    except ImportError as exc:  # e.g. a plugin for the reference package, which is not installed
+                        log.debug("skipping %s plugin %s: %s", ENTRY_POINT_GROUP, ep.name, exc)
                     except Exception as exc:  # a broken third-party plugin must not take the factory down
                         log.warning("could not load %s plugin %s: %s", ENTRY_POINT_GROUP, ep.name, exc)
             except ImportError:

@@ -56,11 +56,27 @@ class ColumnBatch(object):
         """One numpy array per column (a single device->host copy).  A wire
         batch is widened on the host to the natural dtypes (int64 / int32)
         unless ``natural`` is False."""
-        host = self.buf.cpu().numpy()
+        meta = self._meta
+        sparse = 2 * self.n < self.n_stride         # e.g. the survivors of a compacted batch: rows [0, n) only
+        if sparse:
+            # gather the used prefix of every column into one dense device block, then ONE copy of
+            # just those bytes (not row_bytes * n_stride of mostly unused slots)
+            sizes = [_SIZE[dt] * self.n for _u, dt in meta]
+            offs = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int64)
+            dense = torch.empty(int(offs[-1]), dtype=torch.uint8, device=self.buf.device)
+            for (units, _dt), o, sz in zip(meta, offs[:-1], sizes):
+                start = units * self.n_stride
+                dense[int(o):int(o) + sz].copy_(self.buf[start:start + sz])
+            host = dense.cpu().numpy()
+        else:
+            host = self.buf.cpu().numpy()
         out = []
-        for j, (units, dt) in enumerate(self._meta):
-            start = units * self.n_stride
-            col = host[start:start + _SIZE[dt] * self.n_stride].view(_NUMPY[dt])[:self.n]
+        for j, (units, dt) in enumerate(meta):
+            if sparse:
+                col = host[int(offs[j]):int(offs[j + 1])].view(_NUMPY[dt])
+            else:
+                start = units * self.n_stride
+                col = host[start:start + _SIZE[dt] * self.n_stride].view(_NUMPY[dt])[:self.n]
             if self.wire and natural:
                 out.append(col.astype(_NUMPY[self.compiled.col_meta[j][1]]))
             else:
@@ -101,6 +117,8 @@ class ColumnBatch(object):
         assert not self.wire and not (wire and self.transformed)
         dest = out if out is not None else c.empty_columns(self.n, self.transformed, wire=wire)
         assert dest.wire == wire and dest.transformed == self.transformed
+        assert dest.n_stride >= self.n, "compact(out=...): the destination holds %d rows, up to %d may survive" % (
+            dest.n_stride, self.n)
         nbytes = c.lib.ob2_compact_scratch_bytes(self.n)
         if scratch is None:
             scratch = torch.empty(max(nbytes, 8), dtype=torch.uint8, device=c.device)

@@ -205,6 +205,8 @@ int launch_codec(K kernel, const char *what, size_t smem_floor, const ob2_space 
         ob2_set_error("%s: null buffer", what);
         return OB2_EINVAL;
     }
+    OB2_ALIGNED(in, 16, what);
+    OB2_ALIGNED(out, 16, what);
     if (n == 0) return OB2_OK;
     if (n_stride >= (1ll << 29)) {  // the one-hot loop steps through columns with 32-bit byte strides
         ob2_set_error("%s: n_stride %lld too large for one launch (limit 2^29 - 1); split the batch", what,
@@ -248,5 +250,6 @@ extern "C" int ob2_reverse_fingerprint(const ob2_space *space, int64_t n, int64_
         ob2_set_error("ob2_reverse_fingerprint: null fingerprint buffer");
         return OB2_EINVAL;
     }
+    OB2_ALIGNED(fp, 16, "ob2_reverse_fingerprint");
     return launch_codec(reverse_kernel<true>, "reverse_kernel", 0, space, n, n_stride, tcols, cols, stream, fp);
 }

@@ -185,6 +185,10 @@ int compact_impl(const ob2_space *space, int64_t n, int64_t n_stride, const void
         ob2_set_error("ob2_compact: bad arguments (out_stride must be a multiple of 32)");
         return OB2_EINVAL;
     }
+    OB2_ALIGNED(cols, 16, "ob2_compact");
+    OB2_ALIGNED(out_cols, 16, "ob2_compact");
+    OB2_ALIGNED(scratch, 4, "ob2_compact");
+    OB2_ALIGNED(n_kept, 8, "ob2_compact");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (n == 0) return ob2_check_cuda(cudaMemsetAsync(n_kept, 0, sizeof(uint64_t), st), "cudaMemsetAsync(n_kept)");
     const int64_t blocks = (n + kRowsPerBlock - 1) / kRowsPerBlock;

@@ -363,6 +363,8 @@ extern "C" int ob2_fingerprint(const ob2_space *space, int64_t n, int64_t n_stri
         ob2_set_error("fingerprint: null buffer");
         return OB2_EINVAL;
     }
+    OB2_ALIGNED(cols, 16, "fingerprint");
+    OB2_ALIGNED(fp, 16, "fingerprint");
     if (n == 0) return OB2_OK;
     unsigned blocks;
     rc = grid_for((n + OB2_CPT - 1) / OB2_CPT, &blocks);
@@ -374,6 +376,58 @@ extern "C" int ob2_fingerprint(const ob2_space *space, int64_t n, int64_t n_stri
         space->d_slots, space->n_slots, n, n_stride, (const char *)cols, fp);
     return ob2_check_cuda(cudaGetLastError(), "fingerprint_kernel launch");
 }
+
+// ---------------------------------------------------------------------------
+// ob2_set_dedup_static: the same two-pass dedup for callers that must not
+// allocate device memory.
+//
+// ob2_set_dedup needs n u32 of scratch (the slot index pass 1 hands to pass 2)
+// and leaves it to the caller to provide it.  Some callers cannot: a plugin
+// running inside a host process whose framework has already claimed the whole
+// GPU for its own memory pool (a cudaMalloc from the plugin then fails, or
+// fragments the pool); a producer loop that may not stall, since cudaMalloc and
+// cudaFree synchronise the device; a thin binding (cgo/JNI/ctypes) that only
+// ever owns the input and output buffers it was handed.  For them the scratch
+// lives in the library image itself, in the file-scope array below: once the
+// CUDA module that holds the hash-set kernels is loaded on a GPU (with CUDA's
+// default lazy loading: at the first hash-set call on that GPU, which is
+// ob2_set_create), that GPU holds OB2_STATIC_DEDUP_MAX * 4 bytes (4 MiB) of it
+// until the process exits, whether or not this entry point is used.
+//
+// On the host, `g_static_dedup_scratch` is only a handle for the symbol, not a
+// device address; the address for the current device is looked up once per
+// device with cudaGetSymbolAddress and cached.  ob2_set_create does that
+// look-up (it runs with the set's device current, outside any capture, and is
+// where a caller expects set-up cost), so that by the time a dedup call is
+// made the module is resident and the call itself neither loads nor allocates
+// anything; ob2_set_dedup_static repeats it only if it was never done.
+static __device__ __align__(256) uint32_t g_static_dedup_scratch[OB2_STATIC_DEDUP_MAX];
+
+namespace {
+
+constexpr int kMaxDevices = 64;
+uint32_t *g_static_scratch_ptr[kMaxDevices];  // zero-initialised: not looked up yet
+std::mutex g_static_scratch_mutex;
+
+// Device address of the static scratch on the CURRENT device (set-up on first use).
+int static_scratch_for_current_device(uint32_t **out) {
+    int dev = -1;
+    OB2_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevices) {
+        ob2_set_error("ob2_set_dedup_static: device ordinal %d outside [0, %d)", dev, kMaxDevices);
+        return OB2_EINVAL;
+    }
+    std::lock_guard<std::mutex> lock(g_static_scratch_mutex);
+    if (g_static_scratch_ptr[dev] == nullptr) {
+        void *ptr = nullptr;
+        OB2_CUDA(cudaGetSymbolAddress(&ptr, g_static_dedup_scratch));
+        g_static_scratch_ptr[dev] = static_cast<uint32_t *>(ptr);
+    }
+    *out = g_static_scratch_ptr[dev];
+    return OB2_OK;
+}
+
+}  // namespace
 
 extern "C" int ob2_set_create(void *mem, uint64_t n_slots, void *stream, ob2_set **out) {
     if (out == nullptr || mem == nullptr || n_slots < 64 || (n_slots & (n_slots - 1)) != 0 || n_slots > (1ull << 31)) {
@@ -404,6 +458,11 @@ extern "C" int ob2_set_create(void *mem, uint64_t n_slots, void *stream, ob2_set
         delete set;
         return rc;
     }
+    // Set-up for ob2_set_dedup_static on this device: loads the module that carries its
+    // built-in scratch and caches the array's address.  Best effort -- a failure here is
+    // reported by ob2_set_dedup_static itself if that entry point is ever used.
+    uint32_t *unused = nullptr;
+    (void)static_scratch_for_current_device(&unused);
     *out = set;
     return OB2_OK;
 }
@@ -424,23 +483,20 @@ extern "C" int ob2_set_insert(ob2_set *set, int64_t n, const uint64_t *fp, void 
     return ob2_check_cuda(cudaGetLastError(), "set_insert_kernel launch");
 }
 
-extern "C" int ob2_set_dedup(ob2_set *set, int64_t n, const uint64_t *fp, const uint32_t *order, uint32_t *scratch,
-                             uint8_t *keep, void *stream) {
-    int rc = check_set_args(set, n, fp);
-    if (rc != OB2_OK) return rc;
-    if (n == 0) return OB2_OK;
-    if (scratch == nullptr || keep == nullptr) {
-        ob2_set_error("ob2_set_dedup: null scratch/keep");
-        return OB2_EINVAL;
-    }
-    cudaStream_t st = static_cast<cudaStream_t>(stream);
-    rc = reserve(set, n, st);
+namespace {
+
+// The two passes on `st`, after `n_reserve` incoming entries have been cleared against the
+// 7/8 load limit (n_reserve <= n: an exchange inbox is launched over its padded lanes but
+// only its real entries can be inserted).
+int dedup_launch(ob2_set *set, int64_t n, int64_t n_reserve, const uint64_t *fp, const uint32_t *order,
+                 uint32_t *scratch, uint8_t *keep, cudaStream_t st, const char *who) {
+    int rc = reserve(set, n_reserve, st);
     if (rc != OB2_OK) return rc;
     unsigned blocks;
     rc = grid_for(n, &blocks);
     if (rc != OB2_OK) return rc;
     if (set->epoch == 0xFFFFFFFFu) {
-        ob2_set_error("ob2_set_dedup: epoch counter exhausted");
+        ob2_set_error("%s: epoch counter exhausted", who);
         return OB2_ETOOBIG;
     }
     const uint32_t epoch = ++set->epoch;
@@ -451,51 +507,46 @@ extern "C" int ob2_set_dedup(ob2_set *set, int64_t n, const uint64_t *fp, const 
     return ob2_check_cuda(cudaGetLastError(), "set_dedup_pass2 launch");
 }
 
-// ---------------------------------------------------------------------------
-// ob2_set_dedup_static: the same two-pass dedup for callers that must not
-// allocate device memory.
-//
-// ob2_set_dedup needs n u32 of scratch (the slot index pass 1 hands to pass 2)
-// and leaves it to the caller to provide it.  Some callers cannot: a plugin
-// running inside a host process whose framework has already claimed the whole
-// GPU for its own memory pool (a cudaMalloc from the plugin then fails, or
-// fragments the pool); a producer loop that may not stall, since cudaMalloc and
-// cudaFree synchronise the device; a thin binding (cgo/JNI/ctypes) that only
-// ever owns the input and output buffers it was handed.  For them the scratch
-// lives in the library image itself, in the file-scope array below: every GPU
-// that loads libob2 holds OB2_STATIC_DEDUP_MAX * 4 bytes (4 MiB) of it from
-// load until the process exits, whether or not this entry point is used.
-//
-// On the host, `g_static_dedup_scratch` is only a handle for the symbol, not a
-// device address; the address for the current device is looked up once per
-// device with cudaGetSymbolAddress and cached.
-static __device__ __align__(256) uint32_t g_static_dedup_scratch[OB2_STATIC_DEDUP_MAX];
+}  // namespace
 
-namespace {
-
-constexpr int kMaxDevices = 64;
-uint32_t *g_static_scratch_ptr[kMaxDevices];  // zero-initialised: not looked up yet
-std::mutex g_static_scratch_mutex;
-
-// Device address of the static scratch on the CURRENT device (set-up on first use).
-int static_scratch_for_current_device(uint32_t **out) {
-    int dev = -1;
-    OB2_CUDA(cudaGetDevice(&dev));
-    if (dev < 0 || dev >= kMaxDevices) {
-        ob2_set_error("ob2_set_dedup_static: device ordinal %d outside [0, %d)", dev, kMaxDevices);
+extern "C" int ob2_set_dedup(ob2_set *set, int64_t n, const uint64_t *fp, const uint32_t *order, uint32_t *scratch,
+                             uint8_t *keep, void *stream) {
+    int rc = check_set_args(set, n, fp);
+    if (rc != OB2_OK) return rc;
+    if (n == 0) return OB2_OK;
+    if (scratch == nullptr || keep == nullptr) {
+        ob2_set_error("ob2_set_dedup: null scratch/keep");
         return OB2_EINVAL;
     }
-    std::lock_guard<std::mutex> lock(g_static_scratch_mutex);
-    if (g_static_scratch_ptr[dev] == nullptr) {
-        void *ptr = nullptr;
-        OB2_CUDA(cudaGetSymbolAddress(&ptr, g_static_dedup_scratch));
-        g_static_scratch_ptr[dev] = static_cast<uint32_t *>(ptr);
-    }
-    *out = g_static_scratch_ptr[dev];
-    return OB2_OK;
+    return dedup_launch(set, n, n, fp, order, scratch, keep, static_cast<cudaStream_t>(stream), "ob2_set_dedup");
 }
 
-}  // namespace
+// library-internal (ob2_xchg.cu): an inbox of `n` padded lanes holding `n_real` entries
+bool ob2_set_would_trip(const ob2_set *set, int64_t n) {
+    return set->upper_bound + (uint64_t)n > set->n_slots - set->n_slots / 8;
+}
+
+int ob2_set_dedup_padded(ob2_set *set, int64_t n, int64_t n_real, const uint64_t *fp, const uint32_t *order,
+                         uint32_t *scratch, uint8_t *keep, void *stream) {
+    int rc = check_set_args(set, n, fp);
+    if (rc != OB2_OK) return rc;
+    if (n == 0) return OB2_OK;
+    return dedup_launch(set, n, n_real, fp, order, scratch, keep, static_cast<cudaStream_t>(stream), "ob2_xchg_dedup");
+}
+
+int ob2_set_insert_padded(ob2_set *set, int64_t n, int64_t n_real, const uint64_t *fp, void *stream) {
+    int rc = check_set_args(set, n, fp);
+    if (rc != OB2_OK) return rc;
+    if (n == 0) return OB2_OK;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    rc = reserve(set, n_real, st);
+    if (rc != OB2_OK) return rc;
+    unsigned blocks;
+    rc = grid_for(n, &blocks);
+    if (rc != OB2_OK) return rc;
+    set_insert_kernel<<<blocks, OB2_BLOCK, 0, st>>>(set->header, set->slots, set->n_slots - 1, n, fp);
+    return ob2_check_cuda(cudaGetLastError(), "set_insert_kernel launch");
+}
 
 extern "C" int ob2_set_dedup_static(ob2_set *set, int64_t n, const uint64_t *fp, const uint32_t *order,
                                     uint8_t *keep, void *stream) {
@@ -521,25 +572,10 @@ extern "C" int ob2_set_dedup_static(ob2_set *set, int64_t n, const uint64_t *fp,
     uint32_t *scratch = nullptr;
     rc = static_scratch_for_current_device(&scratch);
     if (rc != OB2_OK) return rc;
-    cudaStream_t st = static_cast<cudaStream_t>(stream);
-    rc = reserve(set, n, st);
-    if (rc != OB2_OK) return rc;
-    unsigned blocks;
-    rc = grid_for(n, &blocks);
-    if (rc != OB2_OK) return rc;
-    if (set->epoch == 0xFFFFFFFFu) {
-        ob2_set_error("ob2_set_dedup_static: epoch counter exhausted");
-        return OB2_ETOOBIG;
-    }
-    const uint32_t epoch = ++set->epoch;
     // Nothing in the scratch has to start at zero: pass 1 writes entry i for
     // every i < n (a slot index, or the "settled" marker) and pass 2 reads only
     // those n entries, so whatever an earlier call left behind is never consumed.
-    set_dedup_pass1<<<blocks, OB2_BLOCK, 0, st>>>(set->header, set->slots, set->n_slots - 1, n, fp, order, epoch, scratch, keep);
-    rc = ob2_check_cuda(cudaGetLastError(), "set_dedup_pass1 launch");
-    if (rc != OB2_OK) return rc;
-    set_dedup_pass2<<<blocks, OB2_BLOCK, 0, st>>>(set->slots, n, order, epoch, scratch, keep);
-    return ob2_check_cuda(cudaGetLastError(), "set_dedup_pass2 launch");
+    return dedup_launch(set, n, n, fp, order, scratch, keep, static_cast<cudaStream_t>(stream), "ob2_set_dedup_static");
 }
 
 extern "C" int ob2_set_probe(const ob2_set *set, int64_t n, const uint64_t *fp, uint8_t *found, void *stream) {

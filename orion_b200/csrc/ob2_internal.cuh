@@ -59,6 +59,35 @@ static inline int ob2_check_batch(const ob2_space *sp, int64_t n, int64_t n_stri
     return OB2_OK;
 }
 
+// Caller pointers the kernels touch with vector instructions (128-bit column / fingerprint accesses,
+// 16-bit mask pairs): a misaligned one would fault on the device -- a sticky error that takes the whole
+// context down -- so it is refused on the host instead.  A null pointer passes (optional arguments).
+static inline int ob2_check_align(const void *p, unsigned align, const char *who, const char *what) {
+    if ((reinterpret_cast<uintptr_t>(p) & (uintptr_t)(align - 1)) != 0) {
+        ob2_set_error("%s: `%s` must be %u-byte aligned", who, what, align);
+        return OB2_EINVAL;
+    }
+    return OB2_OK;
+}
+#define OB2_ALIGNED(p, align, who)                                        \
+    do {                                                                  \
+        int _rc = ob2_check_align((p), (align), (who), #p);               \
+        if (_rc != OB2_OK) return _rc;                                    \
+    } while (0)
+
+#define OB2_ALIGNED_AS(p, name, align, who)                               \
+    do {                                                                  \
+        int _rc = ob2_check_align((p), (align), (who), (name));           \
+        if (_rc != OB2_OK) return _rc;                                    \
+    } while (0)
+
+// library-internal set operations for an exchange inbox: kernels launched over `n` padded lanes,
+// load-factor accounting against the `n_real` entries that can actually be inserted (ob2_hashset.cu)
+bool ob2_set_would_trip(const ob2_set *set, int64_t n);
+int ob2_set_dedup_padded(ob2_set *set, int64_t n, int64_t n_real, const uint64_t *fp, const uint32_t *order,
+                         uint32_t *scratch, uint8_t *keep, void *stream);
+int ob2_set_insert_padded(ob2_set *set, int64_t n, int64_t n_real, const uint64_t *fp, void *stream);
+
 // -------------------------------------------------------------- device side
 #define OB2_BLOCK 256
 #define OB2_CPT 2  // candidates per thread: 2 x 8 B = one 128-bit store per column

@@ -465,6 +465,14 @@ int launch_sample(const SampleArgs &a) {
         ob2_set_error("sample: null buffer");
         return OB2_EINVAL;
     }
+    OB2_ALIGNED_AS(a.cols, "cols", 16, "sample");
+    OB2_ALIGNED_AS(a.tcols, "tcols", 16, "sample");
+    OB2_ALIGNED_AS(a.back, "back", 16, "sample");
+    OB2_ALIGNED_AS(a.fp, "fp", 16, "sample");
+    OB2_ALIGNED_AS(a.U, "U", 16, "sample");
+    OB2_ALIGNED_AS(a.mask, "mask", 2, "sample");
+    OB2_ALIGNED_AS(a.index, "index", 8, "sample");
+    OB2_ALIGNED_AS(a.n_failed, "n_failed", 4, "sample");
     if (a.n == 0) return OB2_OK;
     if (a.n_stride >= (1ll << 29)) {  // the kernel steps through columns with 32-bit byte strides
         ob2_set_error("sample: n_stride %lld too large for one launch (limit 2^29 - 1); split the batch",
@@ -522,10 +530,6 @@ extern "C" int ob2_suggest(const ob2_space *space, int64_t n, int64_t n_stride, 
                            uint32_t *n_failed, void *stream) {
     if (tcols == nullptr || back == nullptr || fp == nullptr) {
         ob2_set_error("ob2_suggest: null transformed / handed-out / fingerprint buffer");
-        return OB2_EINVAL;
-    }
-    if (((uintptr_t)back & 15) != 0) {
-        ob2_set_error("ob2_suggest: `back` must be 16-byte aligned");
         return OB2_EINVAL;
     }
     const SampleArgs a{space, n, n_stride, seed, base_index, index, nullptr, cols, tcols, back, mask, fp, n_failed, stream};
@@ -685,6 +689,8 @@ extern "C" int ob2_contains(const ob2_space *space, int64_t n, int64_t n_stride,
         ob2_set_error("contains: null buffer");
         return OB2_EINVAL;
     }
+    OB2_ALIGNED(cols, 16, "contains");
+    OB2_ALIGNED(mask, 2, "contains");
     if (n == 0) return OB2_OK;
     const int64_t threads = (n + OB2_CPT - 1) / OB2_CPT;
     const int64_t blocks = (threads + OB2_BLOCK - 1) / OB2_BLOCK;

@@ -76,6 +76,18 @@ extern "C" int ob2_space_create(const ob2_slot_desc *slots, int32_t n_slots, con
             ob2_set_error("slot %d: dim_first %d out of order", s, d.dim_first);
             return OB2_EINVAL;
         }
+        // a dimension is a run of slots of one kind sharing dim_first, closed by OB2_SLOT_DIM_LAST
+        // (the whole-dimension redraw walks [dim_first, last] and relies on exactly that)
+        const bool opens = s == 0 || (slots[s - 1].flags & OB2_SLOT_DIM_LAST) != 0;
+        if (opens ? d.dim_first != s : (d.dim_first != slots[s - 1].dim_first || d.kind != slots[s - 1].kind)) {
+            ob2_set_error("slot %d: dim_first %d / kind %d inconsistent with the dimension it belongs to", s,
+                          d.dim_first, d.kind);
+            return OB2_EINVAL;
+        }
+        if (s == n_slots - 1 && !(d.flags & OB2_SLOT_DIM_LAST)) {
+            ob2_set_error("slot %d: the last slot must close its dimension (OB2_SLOT_DIM_LAST)", s);
+            return OB2_EINVAL;
+        }
         if (d.col_units != units || d.t_units != t_units) {
             ob2_set_error("slot %d: col_units/t_units (%d, %d) do not match the running sums (%lld, %lld)", s,
                           d.col_units, d.t_units, (long long)units, (long long)t_units);

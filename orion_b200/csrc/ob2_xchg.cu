@@ -175,6 +175,13 @@ xchg_collect_kernel(int rank, int64_t cap, const uint32_t *__restrict__ send_cnt
     }
 }
 
+// sticky overflow flag: any (source = me, owner) lane that received more than it can hold
+__global__ void xchg_flag_overflow_kernel(int world, int64_t cap, const uint32_t *__restrict__ send_cnt,
+                                          uint32_t *__restrict__ flag) {
+    const int o = threadIdx.x;
+    if (o < world && (int64_t)send_cnt[o] > cap) atomicMax(flag, 1u);
+}
+
 int upload_peers(ob2_xchg *x) {
     PeerTable t;
     for (int r = 0; r < OB2_XCHG_MAX_RANKS; ++r) t.base[r] = r < x->world ? x->peer[r] : nullptr;
@@ -332,10 +339,21 @@ extern "C" int ob2_xchg_dedup(ob2_xchg *x, ob2_set *set, int32_t insert_only, vo
     rc = ob2_check_cuda(cudaGetLastError(), "xchg_pad_kernel launch");
     if (rc != OB2_OK) return rc;
     const int64_t lanes = (int64_t)x->world * x->cap;
-    if (insert_only) return ob2_set_insert(set, lanes, inbox_fp, stream);
+    // The kernels run over the padded lanes, but only the entries really received can be
+    // inserted: when the cheap host bound (which counts the padding) would trip the 7/8 load
+    // limit, read the per-source counts and reserve against the real inbox population.
+    int64_t real = lanes;
+    if (ob2_set_would_trip(set, lanes)) {
+        uint32_t h_cnt[OB2_XCHG_MAX_RANKS];
+        OB2_CUDA(cudaMemcpyAsync(h_cnt, cnt, sizeof(uint32_t) * x->world, cudaMemcpyDeviceToHost, st));
+        OB2_CUDA(cudaStreamSynchronize(st));
+        real = 0;
+        for (int r = 0; r < x->world; ++r) real += (int64_t)h_cnt[r] < x->cap ? (int64_t)h_cnt[r] : x->cap;
+    }
+    if (insert_only) return ob2_set_insert_padded(set, lanes, real, inbox_fp, stream);
     // verdicts stay in MY region, lane by source; the sources pull them (ob2_xchg_collect)
-    return ob2_set_dedup(set, lanes, inbox_fp, inbox_key, x->scratch,
-                         reinterpret_cast<uint8_t *>(x->region + x->lay.verdict_off), stream);
+    return ob2_set_dedup_padded(set, lanes, real, inbox_fp, inbox_key, x->scratch,
+                                reinterpret_cast<uint8_t *>(x->region + x->lay.verdict_off), stream);
 }
 
 extern "C" int ob2_xchg_collect(ob2_xchg *x, int64_t n, uint8_t *keep, void *stream) {
@@ -351,6 +369,17 @@ extern "C" int ob2_xchg_collect(ob2_xchg *x, int64_t n, uint8_t *keep, void *str
     xchg_collect_kernel<<<grid, OB2_BLOCK, 0, st>>>(x->rank, x->cap, x->send_cnt, x->out_src, x->d_peers,
                                                     x->lay.verdict_off, keep);
     return ob2_check_cuda(cudaGetLastError(), "xchg_collect_kernel launch");
+}
+
+extern "C" int64_t ob2_xchg_cap(const ob2_xchg *x) { return x ? x->cap : 0; }
+
+extern "C" int ob2_xchg_flag_overflow(const ob2_xchg *x, uint32_t *flag, void *stream) {
+    if (x == nullptr || flag == nullptr) {
+        ob2_set_error("ob2_xchg_flag_overflow: bad arguments");
+        return OB2_EINVAL;
+    }
+    xchg_flag_overflow_kernel<<<1, OB2_XCHG_MAX_RANKS, 0, static_cast<cudaStream_t>(stream)>>>(x->world, x->cap, x->send_cnt, flag);
+    return ob2_check_cuda(cudaGetLastError(), "xchg_flag_overflow_kernel launch");
 }
 
 extern "C" int ob2_xchg_send_counts(const ob2_xchg *x, uint32_t *counts_host, void *stream) {

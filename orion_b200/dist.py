@@ -236,8 +236,21 @@ def make_sharded_history(history, max_n, exchange='auto', group=None):
 class PeerShardedHistory(object):
     """Sharded dedup whose exchange runs over peer memory (NVLink stores from
     inside the kernels) instead of NCCL all-to-alls; same results as
-    :class:`ShardedHistory`.  Cross-rank ordering uses two 1-element all-reduces
-    per batch as stream-ordered barriers."""
+    :class:`ShardedHistory`.  Cross-rank ordering uses two small all-reduces
+    per batch as stream-ordered barriers.
+
+    Failures are agreed on collectively -- every rank raises, or none does:
+    the barrier all-reduce (MAX) carries two sticky status words, *a lane
+    overflowed* (many copies of few rows, e.g. a small discrete space: equal
+    rows share an owner) and *an owner's table is full*.  With ``check=True``
+    the words are read after each phase (one host sync each): an overflowed
+    batch is re-run by every rank through the NCCL path with worst-case
+    lanes, BEFORE any history has been touched; a full table raises
+    everywhere (with ``auto_grow`` the owner doubles its table instead and
+    nobody notices).  With ``check=False`` nothing is read on the way and
+    :meth:`check_overflow` reports the sticky words after the run."""
+
+    OVERFLOW, FULL = 0, 1
 
     def __init__(self, history, max_n, group=None):
         self.history = history
@@ -246,9 +259,10 @@ class PeerShardedHistory(object):
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.device = history.device
         self.max_n = int(max_n)
-        self.cap = bucket_capacity(self.max_n, self.world)
-        self.xchg = PeerExchange(self.rank, self.world, self.cap, self.device)
-        self._token = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self.xchg = PeerExchange(self.rank, self.world, bucket_capacity(self.max_n, self.world), self.device)
+        self.cap = int(self.xchg.lib.ob2_xchg_cap(self.xchg.handle))     # as rounded by the library
+        self._status = torch.zeros(2, dtype=torch.int32, device=self.device)
+        self._nccl = None
         if self.world > 1:
             mine = torch.tensor(list(self.xchg.ipc_handle()), dtype=torch.uint8, device=self.device)
             everyone = [torch.empty(64, dtype=torch.uint8, device=self.device) for _ in range(self.world)]
@@ -265,8 +279,46 @@ class PeerShardedHistory(object):
                 raise PeerExchangeUnavailable(str(error) if error else "a peer rank could not map the inboxes")
 
     def _barrier(self):
+        """Stream-ordered barrier that also spreads the status words (MAX)."""
         if self.world > 1:
-            dist.all_reduce(self._token, group=self.group)     # stream-ordered; no host sync
+            dist.all_reduce(self._status, op=dist.ReduceOp.MAX, group=self.group)
+
+    def _fallback(self):
+        if self._nccl is None:
+            self._nccl = ShardedHistory(self.history, group=self.group, device=self.device)
+        return self._nccl
+
+    def _send(self, fp, n, key_base):
+        self.xchg.send(fp, n, key_base)
+        _lib.check(self.xchg.lib.ob2_xchg_flag_overflow(self.xchg.handle, self._status[self.OVERFLOW:].data_ptr(),
+                                                       self.xchg._stream()))
+        self._barrier()
+
+    def _owner_side(self, insert_only):
+        """Dedup (or load) my inbox.  A full table grows when the history allows
+        it; otherwise the inbox is left alone and the FULL word is raised for
+        everybody (no exception on this rank alone: the others would hang in
+        the next collective)."""
+        while True:
+            rc = self.xchg.lib.ob2_xchg_dedup(self.xchg.handle, self.history.handle, 1 if insert_only else 0,
+                                              self.xchg._stream())
+            if rc == -4 and self.history.auto_grow and self.history.n_slots < (1 << 31):
+                self.history.grow()
+                continue
+            if rc == -4:
+                self._full_error = _lib.load().ob2_last_error().decode('utf-8', 'replace')
+                self._status[self.FULL:].fill_(1)
+            else:
+                _lib.check(rc)
+            break
+        self._barrier()
+
+    def _read_status(self):
+        return [int(v) for v in self._status.tolist()]          # host sync; same words on every rank
+
+    def _raise_full(self):
+        raise _lib.Ob2Error("a history shard is full (on this or another rank): %s"
+                            % getattr(self, '_full_error', 'see the owning rank'))
 
     def dedup(self, fp, n, per_rank_n=None, keep=None, check=True):
         per_rank_n = n if per_rank_n is None else per_rank_n
@@ -276,26 +328,34 @@ class PeerShardedHistory(object):
             raise ValueError("global candidate index does not fit the 32-bit order key")
         if keep is None:
             keep = torch.empty(fp.shape[0], dtype=torch.uint8, device=self.device)
-        self.xchg.send(fp, n, self.rank * per_rank_n)
-        self._barrier()
-        self.xchg.dedup(self.history)
-        self._barrier()
+        self._send(fp, n, self.rank * per_rank_n)
+        if check and self._read_status()[self.OVERFLOW]:
+            # nothing has touched the history yet: every rank takes this batch through worst-case lanes
+            self._status[self.OVERFLOW:self.OVERFLOW + 1].zero_()
+            return self._fallback().dedup(fp, n, per_rank_n=per_rank_n, keep=keep, check=True)
+        self._owner_side(insert_only=False)
+        if check and self._read_status()[self.FULL]:
+            self._raise_full()
         self.xchg.collect(n, keep)
-        if check:
-            self.check_overflow()
         return keep
 
     def insert(self, fp, n, check=True):
         if n > self.max_n:
             raise ValueError("batch of %d exceeds the exchange capacity sized for %d" % (n, self.max_n))
-        self.xchg.send(fp, n, 0)
-        self._barrier()
-        self.xchg.dedup(self.history, insert_only=True)
-        self._barrier()
-        if check:
-            self.check_overflow()
+        self._send(fp, n, 0)
+        if check and self._read_status()[self.OVERFLOW]:
+            self._status[self.OVERFLOW:self.OVERFLOW + 1].zero_()
+            return self._fallback().insert(fp, n, check=True)
+        self._owner_side(insert_only=True)
+        if check and self._read_status()[self.FULL]:
+            self._raise_full()
 
     def check_overflow(self):
-        worst = max(self.xchg.send_counts())
-        if worst > self.cap:
-            raise RuntimeError("exchange lane overflow: %d fingerprints for one owner, capacity %d" % (worst, self.cap))
+        """After ``check=False`` calls: raise -- on every rank alike -- if any
+        rank dropped fingerprints or ran out of table since the last check."""
+        overflow, full = self._read_status()
+        if full:
+            self._raise_full()
+        if overflow:
+            raise RuntimeError("exchange lane overflow on some rank: more than %d fingerprints for one owner; "
+                               "verdicts of that batch are incomplete (use check=True)" % self.cap)

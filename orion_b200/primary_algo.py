@@ -79,6 +79,31 @@ class PrimaryAlgo(BaseAlgorithm):
         self._assert_in_space([point])
         return self.algorithm.judge(self._to_algo([point])[0], measurements)
 
+    def score_points(self, points):
+        """``score`` for a whole list: what ``Experiment.reserve_trial`` computes as
+        ``map(score_handle, map(trial_to_tuple, new_trials))``
+        (src/orion/core/worker/experiment.py:173-178 over primary_algo.py:75-84), with the
+        ``point in space`` assertions of all points done by ONE ``ob2_contains`` launch
+        (and one transform launch under a requirement) instead of one per point."""
+        points = list(points)
+        if not points:
+            return []
+        self._assert_in_space(points)
+        inner = self._to_algo(points)
+        batched = getattr(self.algorithm, 'score_points', None)
+        if batched is not None:
+            return list(batched(inner))
+        return [self.algorithm.score(p) for p in inner]
+
+    def judge_points(self, points, measurements):
+        """``judge`` for a whole list (primary_algo.py:86-95); same single membership launch."""
+        points = list(points)
+        assert len(points) == len(measurements)
+        if not points:
+            return []
+        self._assert_in_space(points)
+        return [self.algorithm.judge(p, m) for p, m in zip(self._to_algo(points), measurements)]
+
     @property
     def should_suspend(self):
         return self.algorithm.should_suspend

@@ -14,6 +14,7 @@ of it: ``pool_size``, ``space``, ``algorithms``, ``register_trials(trials)`` and
 Trials are the plain records of :mod:`orion_b200.format_trials`.
 """
 import logging
+import random
 
 from . import format_trials
 from .history import TrialHistory
@@ -85,3 +86,25 @@ class Producer(object):
         if self.dedup:
             self.history.observe(format_trials.trials_to_batch(self.space, completed))
         self.algorithm.observe(points, results)
+
+    def select_trial(self, new_trials, score_handle=None):
+        """The scoring half of ``Experiment.reserve_trial``
+        (src/orion/core/worker/experiment.py:170-183): among the *new* trial records pick one
+        with the highest score, at random among ties.  ``score_handle`` defaults to the
+        algorithm's batched ``score_points`` -- every candidate's ``point in space`` assertion
+        in one kernel launch -- and may be any callable taking one point, as in the
+        reference (``workon`` passes ``producer.algorithm.score``, worker/__init__.py:29).
+        The database half (find / find_one_and_update) stays with the experiment object."""
+        if score_handle is not None and not callable(score_handle):
+            raise ValueError("Argument `score_handle` must be callable with a `Trial`.")
+        new_trials = list(new_trials)
+        if not new_trials:
+            return None
+        points = [format_trials.trial_to_tuple(t, self.space) for t in new_trials]
+        if score_handle is None and hasattr(self.algorithm, 'score_points'):
+            scores = list(self.algorithm.score_points(points))
+        else:
+            handle = score_handle if score_handle is not None else self.algorithm.score
+            scores = [handle(p) for p in points]
+        best = max(scores)
+        return random.choice([t for s, t in zip(scores, new_trials) if s == best])

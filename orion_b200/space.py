@@ -52,6 +52,57 @@ class _OneDim(OrderedDict):
     """A throw-away single-dimension space used to compile one Dimension."""
 
 
+# ---- value <-> column helpers.  Module-level and duck-typed (they read only ``type``, ``shape``
+# and ``categories``) so that they also serve the REFERENCE's own dimension objects when a
+# reference ``Space`` is driven through the kernels (compat / plugin).
+def _index_of(dim, value):
+    """Position of ``value`` in ``dim.categories`` by ``==`` (so '2' is not 2), -1 when absent."""
+    try:
+        return tuple(dim.categories).index(value)
+    except ValueError:
+        return -1
+
+
+def _column_values(dim, point):
+    """Flatten one value of ``dim`` into per-slot scalars, or None when its shape does not fit
+    (``point_.shape != self.shape`` -> False, space.py:162,420).  A string offered to a numeric
+    dimension raises TypeError, as the reference's ``point_ < high`` does (space.py:164)."""
+    shape = tuple(dim.shape)
+    if dim.type == 'categorical':
+        arr = numpy.asarray(point, dtype=object)
+        if arr.shape != shape:
+            return None
+        return numpy.asarray([_index_of(dim, v) for v in arr.reshape(-1)], dtype=numpy.int32)
+    probe = numpy.asarray(point)
+    if probe.dtype.kind in 'US':
+        raise TypeError("'<' not supported between a value of dimension '{}' given as {!r} and its bounds"
+                        .format(dim.name, point))
+    try:
+        arr = numpy.asarray(point, dtype=numpy.float64)
+    except (TypeError, ValueError):
+        return None
+    if arr.shape != shape:
+        return None
+    return arr.reshape(-1)
+
+
+def _from_columns(dim, cols, i):
+    """Value i of ``dim`` from its host columns (numpy scalars / category objects for shape (),
+    ndarrays otherwise -- what scipy's rvs and RandomState.choice hand back)."""
+    shape = tuple(dim.shape)
+    if dim.type == 'categorical':
+        cats = dim.categories
+        if shape == ():
+            return cats[cols[0][i]]
+        out = numpy.empty(len(cols), dtype=object)
+        for e, c in enumerate(cols):
+            out[e] = cats[c[i]]
+        return out.reshape(shape)
+    if shape == ():
+        return cols[0][i]
+    return numpy.stack([c[i] for c in cols]).reshape(shape)
+
+
 class Dimension(object):
     """Base class for search space dimensions (reference space.py:47-196).
 
@@ -92,23 +143,10 @@ class Dimension(object):
         return self._compiled_self
 
     def _column_values(self, point):
-        """Flatten one value of this dimension into per-slot scalars, or None
-        when its shape does not fit (``point_.shape != self.shape`` -> False,
-        space.py:162)."""
-        try:
-            arr = numpy.asarray(point, dtype=numpy.float64)
-        except (TypeError, ValueError):
-            return None
-        if arr.shape != self.shape:
-            return None
-        return arr.reshape(-1)
+        return _column_values(self, point)
 
     def _from_columns(self, cols, i):
-        """Value i of this dimension from its host columns (numpy scalars for
-        shape (), ndarrays otherwise -- what scipy's rvs hands back)."""
-        if self.shape == ():
-            return cols[0][i]
-        return numpy.stack([c[i] for c in cols]).reshape(self.shape)
+        return _from_columns(self, cols, i)
 
     # -- reference interface ------------------------------------------------
     def sample(self, n_samples=1, seed=None):
@@ -218,26 +256,7 @@ class Categorical(Dimension):
         super(Categorical, self).__init__(name, prior, **kwargs)
 
     def _index_of(self, value):
-        """Position of ``value`` in ``categories`` by ``==`` (so '2' is not 2),
-        -1 when absent."""
-        try:
-            return self.categories.index(value)
-        except ValueError:
-            return -1
-
-    def _column_values(self, point):
-        arr = numpy.asarray(point, dtype=object)
-        if arr.shape != self.shape:
-            return None
-        return numpy.asarray([self._index_of(v) for v in arr.reshape(-1)], dtype=numpy.int32)
-
-    def _from_columns(self, cols, i):
-        if self.shape == ():
-            return self.categories[cols[0][i]]
-        out = numpy.empty(len(cols), dtype=object)
-        for e, c in enumerate(cols):
-            out[e] = self.categories[c[i]]
-        return out.reshape(self.shape)
+        return _index_of(self, value)
 
     def interval(self, alpha=1.0):
         raise RuntimeError("Categories have no ``interval`` (as they are not ordered).\n"
@@ -321,7 +340,7 @@ class Space(OrderedDict):
                 continue
             k = int(numpy.prod(dim.shape, dtype=numpy.int64))
             cols = host_cols[s:s + k]
-            per_dim.append([dim._from_columns(cols, i) for i in range(n)])
+            per_dim.append([_from_columns(dim, cols, i) for i in range(n)])
             s += k
         return list(zip(*per_dim))
 
@@ -338,8 +357,10 @@ class Space(OrderedDict):
             if dim.type == 'categorical':
                 if any(isinstance(v, (numpy.ndarray, list, tuple)) for v in vals):
                     return None
-                cols.append(numpy.fromiter((dim._index_of(v) for v in vals), dtype=numpy.int32, count=n))
+                cols.append(numpy.fromiter((_index_of(dim, v) for v in vals), dtype=numpy.int32, count=n))
             else:
+                if any(isinstance(v, (str, bytes)) for v in vals):
+                    return None                 # the general loop raises the reference's TypeError
                 try:
                     col = numpy.asarray(vals, dtype=numpy.float64)
                 except (TypeError, ValueError):
@@ -368,7 +389,7 @@ class Space(OrderedDict):
             for j, dim in enumerate(dims):
                 if j >= len(point):
                     break
-                vals = dim._column_values(point[j])
+                vals = _column_values(dim, point[j])
                 if vals is None:
                     row_ok[i] = False
                 else:
@@ -379,7 +400,7 @@ class Space(OrderedDict):
                 # unchecked dimensions: fill with an always-valid value
                 for j in range(len(point), len(dims)):
                     off = sum(widths[:j])
-                    low, high = self.compiled().dim_bounds[j]
+                    low, high = compile_space(self).dim_bounds[j]
                     fill = low if numpy.isfinite(low) else (high - 1 if numpy.isfinite(high) else 0)
                     for e in range(widths[j]):
                         cols[off + e][i] = fill

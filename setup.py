@@ -24,6 +24,13 @@ setup(
     packages=find_packages(include=['orion_b200', 'orion_b200.*']),
     package_data={'orion_b200': ['libob2.so']},
     cmdclass={'build_py': BuildWithKernels},
-    entry_points={'OptimizationAlgorithm': ['random = orion_b200.algo.random:Random']},
-    install_requires=['numpy', 'scipy', 'torch'],
+    # Loaded by the reference's factory (src/orion/core/utils/__init__.py:76-81) AND by the mirror's.  The
+    # name must not collide with the reference's own `random` (its setup.py:67-69); loading it defines a
+    # subclass of whichever `orion.algo.base.BaseAlgorithm` is importable (orion_b200/plugin.py).
+    entry_points={'OptimizationAlgorithm': ['gpurandom = orion_b200.plugin:GPURandom']},
+    # torch (device memory, streams, torch.distributed) is needed at run time but not listed as a hard
+    # requirement: the reference's factory loads entry points through pkg_resources, which re-resolves the
+    # whole requirement tree of the advertising distribution and refuses on any pin conflict inside it.
+    install_requires=['numpy', 'scipy'],
+    extras_require={'gpu': ['torch']},
 )

@@ -144,3 +144,19 @@ def test_wide_space_descriptor_limits():
     with pytest.raises(_lib.Ob2Error) as exc:
         big.compiled()
     assert '200 KiB' in str(exc.value)
+
+
+def test_string_offered_to_a_numeric_dimension_raises_like_the_reference():
+    """The reference compares with `point_ < high` (space.py:164): a str there is a
+    TypeError, not the number it spells; a bool is a number for numpy."""
+    from orion_b200.space import Integer, Real, Space
+    dim = Real('x', 'uniform', 0, 10)
+    with pytest.raises(TypeError):
+        '3' in dim                                        # noqa: B015
+    space = Space()
+    space.register(dim)
+    space.register(Integer('k', 'uniform', 0, 5))
+    with pytest.raises(TypeError):
+        ('3', 1) in space                                 # noqa: B015
+    assert (True, 1) in space
+    assert (3.0, 1) in space and (3.0, 1.5) not in space

@@ -101,3 +101,66 @@ def test_no_kernel_writes_outside_its_buffers(n, requirement):
     for a, b in zip(sb.to_numpy(), fused.to_numpy()):
         assert np.array_equal(a, b)
     assert torch.equal(sk.fp[:n], r3.fp[:n])
+
+
+def test_misaligned_caller_pointers_are_refused_on_the_host():
+    """A column block / fingerprint array offset by 8 bytes would fault inside the kernels
+    (128-bit accesses) and poison the context; the entry points return OB2_EINVAL instead."""
+    import ctypes
+    import torch
+    from orion_b200 import _lib, spaces
+    lib = _lib.load()
+    c = spaces.rosen2().compiled()
+    n = 64
+    buf = torch.zeros(c.row_bytes * n + 64, dtype=torch.uint8, device='cuda')
+    fp = torch.zeros(2 * n + 8, dtype=torch.int64, device='cuda')
+    mask = torch.zeros(n + 8, dtype=torch.uint8, device='cuda')
+    st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    base = buf.data_ptr()
+    assert lib.ob2_sample(c.handle, n, n, 1, 0, None, base + 8, None, None, None, st) == -1
+    assert b'16-byte aligned' in lib.ob2_last_error() and b'cols' in lib.ob2_last_error()
+    assert lib.ob2_sample(c.handle, n, n, 1, 0, None, base, None, fp.data_ptr() + 8, None, st) == -1
+    assert lib.ob2_sample(c.handle, n, n, 1, 0, None, base, mask.data_ptr() + 1, None, None, st) == -1
+    assert lib.ob2_fingerprint(c.handle, n, n, base, fp.data_ptr() + 8, st) == -1
+    assert lib.ob2_contains(c.handle, n, n, base + 4, 0, mask.data_ptr(), st) == -1
+    assert lib.ob2_transform(c.handle, n, n, base + 8, base, st) == -1
+    # the aligned call still works afterwards: nothing reached the device
+    assert lib.ob2_sample(c.handle, n, n, 1, 0, None, base, mask.data_ptr(), fp.data_ptr(), None, st) == 0
+    torch.cuda.synchronize()
+    assert bool(mask[:n].all().item())
+
+
+def test_space_create_rejects_inconsistent_dimension_grouping():
+    import ctypes
+    from orion_b200 import _lib
+    lib = _lib.load()
+
+    def table(fix):
+        arr = (_lib.SlotDesc * 2)()
+        for s in range(2):
+            arr[s].kind, arr[s].dist = _lib.KIND_REAL, _lib.DIST_UNIFORM
+            arr[s].dim_first, arr[s].flags = 0, (_lib.SLOT_DIM_LAST if s == 1 else 0)
+            arr[s].col_units = arr[s].t_units = 8 * s
+            arr[s].t_op, arr[s].t_width = _lib.OP_IDENTITY, 1
+            arr[s].scale, arr[s].high = 1.0, 1.0
+        fix(arr)
+        return arr
+
+    out = ctypes.c_void_p()
+    cdf = (ctypes.c_double * 1)(1.0)
+    ok = table(lambda a: None)
+    assert lib.ob2_space_create(ok, 2, cdf, 0, ctypes.byref(out)) == 0
+    lib.ob2_space_destroy(out)
+
+    def mixed_kinds(a):
+        a[1].kind = _lib.KIND_INTEGER
+    assert lib.ob2_space_create(table(mixed_kinds), 2, cdf, 0, ctypes.byref(out)) == -1
+    assert b'inconsistent' in lib.ob2_last_error()
+
+    def wrong_first(a):
+        a[1].dim_first = 1
+    assert lib.ob2_space_create(table(wrong_first), 2, cdf, 0, ctypes.byref(out)) == -1
+
+    def never_closed(a):
+        a[1].flags = 0
+    assert lib.ob2_space_create(table(never_closed), 2, cdf, 0, ctypes.byref(out)) == -1

@@ -88,3 +88,66 @@ def test_producer_without_dedup_registers_everything_like_the_reference():
     exp = ListExperiment(space, PrimaryAlgo(space, {'random': {'seed': 1}}), pool_size=8)
     Producer(exp, dedup=False).produce()
     assert len(exp.trials) == 8                           # two categories, eight trials: duplicates registered
+
+
+def test_batched_score_matches_the_per_point_path_and_uses_one_membership_launch(monkeypatch):
+    """§8 f4: Experiment.reserve_trial maps score_handle over every new trial
+    (experiment.py:173-178); `score_points` asserts all of them in-space with a
+    single library call and returns what per-point `score` returns."""
+    from orion_b200 import spaces
+    from orion_b200.algo.base import BaseAlgorithm
+    from orion_b200.descriptor import CompiledSpace
+    from orion_b200.primary_algo import PrimaryAlgo
+    from orion_b200.producer import Producer
+    from orion_b200 import format_trials
+
+    class Scorer(BaseAlgorithm):
+        def __init__(self, space):
+            super(Scorer, self).__init__(space)
+
+        def suggest(self, num=1):
+            return self.space.sample(num)
+
+        def observe(self, points, results):
+            pass
+
+        def score(self, point):                           # prefers small |x|
+            return -round(abs(point[0]), 6)
+
+    space = spaces.build_space(['-x~uniform(-5, 10)', '-k~uniform(0, 9, discrete=True)', '-c~choices(["a", "b"])'])
+    algo = PrimaryAlgo(space, 'scorer')
+    points = space.sample(300, seed=3)
+    calls = {'n': 0}
+    real = CompiledSpace.contains_host
+
+    def counting(self, *a, **kw):
+        calls['n'] += 1
+        return real(self, *a, **kw)
+
+    monkeypatch.setattr(CompiledSpace, 'contains_host', counting)
+    batched = algo.score_points(points)
+    assert calls['n'] == 1                                # one launch for 300 points
+    calls['n'] = 0
+    single = [algo.score(p) for p in points]
+    assert calls['n'] == 300                              # the reference's way: one check per point
+    assert batched == single
+    judged = algo.judge_points(points[:5], [{}] * 5)
+    assert judged == [None] * 5
+    # a point outside the space trips the same assertion as the per-point path
+    with pytest.raises(AssertionError):
+        algo.score_points(points[:3] + [(99.0, 1, 'a')])
+    with pytest.raises(AssertionError):
+        algo.score((99.0, 1, 'a'))
+    assert algo.score_points([]) == []
+
+    # the reservation hook: the best-scored new trial is selected, ties at random
+    exp = ListExperiment(space, algo, pool_size=4)
+    producer = Producer(exp, dedup=False)
+    trials = [format_trials.tuple_to_trial(p, space) for p in points]
+    chosen = producer.select_trial(trials)
+    best = max(single)
+    assert algo.score(format_trials.trial_to_tuple(chosen, space)) == best
+    assert producer.select_trial(trials, score_handle=algo.score) is not None
+    assert producer.select_trial([]) is None
+    with pytest.raises(ValueError):
+        producer.select_trial(trials, score_handle=3)

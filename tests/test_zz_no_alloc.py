@@ -107,6 +107,33 @@ def test_static_scratch_dedup_matches_caller_scratch_dedup_twice():
     assert bool(with_scratch.probe_fingerprints(probe).all().item())
 
 
+def test_static_scratch_dedup_leaves_free_device_memory_untouched():
+    """The point of the entry point: between the moment the set exists and the
+    moment the verdicts are there, the amount of free device memory (the
+    driver's cudaMemGetInfo figure, not torch's pool statistics) must not move
+    -- not even on the very first call in a process, because creating the set
+    is what loads the library's hash-set module and finds its built-in scratch.
+    Run alone in a fresh process this IS the first call; after the other tests
+    it is a later one; both must hold."""
+    from orion_b200 import _lib
+    lib = _lib.load()
+    rng = np.random.RandomState(7)
+    hist = _twin_histories(1 << 16, _fingerprints(rng, 1000))[1]       # ob2_set_create: module load + look-up
+    n = 20000
+    fps = [torch.from_numpy(_fingerprints(rng, n)).cuda() for _ in range(3)]
+    keep = torch.zeros(n, dtype=torch.uint8, device='cuda')            # every buffer exists before measuring
+    stream = _stream()
+    torch.cuda.synchronize()
+    free_before, _total = torch.cuda.mem_get_info()
+    for fp in fps:
+        _lib.check(lib.ob2_set_dedup_static(hist.handle, n, fp.data_ptr(), None, keep.data_ptr(), stream))
+        torch.cuda.current_stream().synchronize()
+        free_now, _total = torch.cuda.mem_get_info()
+        assert free_now == free_before, "free device memory moved by %d bytes across a static dedup call" % (
+            free_before - free_now)
+    assert int(keep.sum().item()) == n                                  # fresh rows: all kept
+
+
 def test_static_scratch_dedup_rejects_oversized_batches():
     from orion_b200 import _lib
     lib = _lib.load()
