@@ -558,3 +558,50 @@ def dedup_fingerprints(history: set, lo: np.ndarray, hi: np.ndarray) -> np.ndarr
             history.add(key)
             keep[i] = True
     return keep
+
+
+class SortedHistory:
+    """The same contract as :func:`dedup_fingerprints` for histories too large for a Python
+    set (the CPU baseline dedups against ~1e7 rows per process): the bulk of the history is a
+    sorted ``lo`` array (with ``hi`` alongside) searched with ``numpy.searchsorted``; rows added
+    later (inserted batches, kept candidates) live in a small side set."""
+
+    def __init__(self, lo: np.ndarray, hi: np.ndarray):
+        order = np.argsort(lo, kind='stable')
+        self.lo = np.ascontiguousarray(np.asarray(lo, dtype=U64)[order])
+        self.hi = np.ascontiguousarray(np.asarray(hi, dtype=U64)[order])
+        self.recent = set()
+
+    def __len__(self):
+        return len(self.lo) + len(self.recent)
+
+    def insert(self, lo: np.ndarray, hi: np.ndarray) -> None:
+        self.recent.update(zip(np.asarray(lo, dtype=U64).tolist(), np.asarray(hi, dtype=U64).tolist()))
+
+    def _in_bulk(self, lo: np.ndarray, hi: np.ndarray) -> np.ndarray:
+        left = np.searchsorted(self.lo, lo, side='left')
+        right = np.searchsorted(self.lo, lo, side='right')
+        found = np.zeros(len(lo), dtype=bool)
+        one = right == left + 1                      # the usual case: at most one row shares `lo`
+        found[one] = self.hi[left[one]] == hi[one]
+        for i in np.nonzero(right > left + 1)[0]:    # equal low words (probability ~ n^2 / 2^64)
+            found[i] = bool(np.any(self.hi[left[i]:right[i]] == hi[i]))
+        return found
+
+    def dedup(self, lo: np.ndarray, hi: np.ndarray) -> np.ndarray:
+        lo = np.asarray(lo, dtype=U64)
+        hi = np.asarray(hi, dtype=U64)
+        n = len(lo)
+        packed = np.empty(n, dtype=[('lo', U64), ('hi', U64)])
+        packed['lo'] = lo
+        packed['hi'] = hi
+        _, first = np.unique(packed, return_index=True)
+        keep = np.zeros(n, dtype=bool)
+        keep[first] = ~self._in_bulk(lo[first], hi[first])
+        for i in np.nonzero(keep)[0]:
+            key = (int(lo[i]), int(hi[i]))
+            if key in self.recent:
+                keep[i] = False
+            else:
+                self.recent.add(key)
+        return keep

@@ -6,12 +6,17 @@
 // lo == 0 marks an empty slot (fingerprints never have lo == 0).  Keys are
 // claimed with one 128-bit compare-and-swap, so a slot is either empty or holds
 // a complete key.  Deterministic first-wins inside a batch: every dedup call
-// gets a new epoch.  Pass 1 finds-or-inserts each fingerprint: a key that was
-// there before the call is a duplicate (final, no atomic); a key it inserts is
-// kept provisionally; a key inserted by ANOTHER entry of the same call (`born`
-// == epoch) makes both compete through atomicMax on the slot's stamp
-// ((epoch << 32) | ~order).  Pass 2 revisits only those in-batch duplicates and
-// gives the slot to the smallest order key.  No sort, no per-batch clearing.
+// gets a new epoch.  Pass 1 finds-or-inserts each fingerprint with a BLIND
+// compare-and-swap (no read first: nine entries in ten insert, and what bounds
+// this kernel is the number of L2 transactions per entry, not DRAM bytes --
+// benchmarks/micro/random_access.cu): a key that was there before the call is a
+// duplicate (final, one CAS and one 4-byte read); a key it inserts is kept
+// provisionally and tagged {born = epoch, winner = entry} with ONE 8-byte store;
+// an entry that finds a key inserted by ANOTHER entry of the same call (`born` ==
+// epoch) bids for it with atomicMax on the slot's stamp ((epoch << 32) | ~order).
+// Pass 2 revisits only those in-batch duplicates: the best bid takes the slot
+// from the inserter if its order key is smaller than the inserter's (whose
+// provisional keep is then withdrawn).  No sort, no per-batch clearing.
 #include <mutex>
 #include <new>
 
@@ -69,24 +74,16 @@ __device__ __forceinline__ void ld_key(const SetSlot *slot, uint64_t &lo, uint64
 
 enum { FOUND = 0, INSERTED = 1, OVERFLOW = 2 };
 
-// Find the slot holding (lo, hi), inserting it if absent.
+// Find the slot holding (lo, hi), inserting it if absent.  The probe IS the 128-bit CAS
+// (empty -> key): it returns what the slot held, atomically, so there are no torn keys to
+// re-check and an insert costs one transaction instead of a read and a CAS.
 __device__ __forceinline__ int find_or_insert(SetSlot *slots, uint64_t mask, uint64_t lo, uint64_t hi, uint64_t &pos) {
     pos = lo & mask;
     for (uint64_t step = 0; step <= mask; ++step) {
-        SetSlot *slot = slots + pos;
         uint64_t klo, khi;
-        ld_key(slot, klo, khi);
-        if (klo == 0) {
-            cas128(slot, 0, 0, lo, hi, klo, khi);
-            if (klo == 0 && khi == 0) return INSERTED;
-            if (klo == lo && khi == hi) return FOUND;
-        } else if (klo == lo) {
-            if (khi == hi) return FOUND;
-            // same low word, different high word: true 64-bit collision or a torn
-            // read of a key being written -- re-read atomically to tell
-            cas128(slot, lo, hi, lo, hi, klo, khi);
-            if (klo == lo && khi == hi) return FOUND;
-        }
+        cas128(slots + pos, 0, 0, lo, hi, klo, khi);
+        if (klo == 0 && khi == 0) return INSERTED;
+        if (klo == lo && khi == hi) return FOUND;
         pos = (pos + 1) & mask;
     }
     return OVERFLOW;
@@ -156,17 +153,17 @@ set_dedup_pass1(SetHeader *hdr, SetSlot *slots, uint64_t mask, int64_t n, const 
             uint64_t pos;
             const int r = find_or_insert(slots, mask, key.x, key.y, pos);
             SetSlot *slot = slots + pos;
-            const uint32_t ord = order ? __ldg(order + i) : (uint32_t)i;
             if (r == INSERTED) {
                 inserted = true;
-                slot->winner = (uint32_t)i;  // read by pass 2 only
-                slot->born = epoch;
-                atomicMax(&slot->stamp, dedup_tag(epoch, ord));
+                // {born, winner} in one 8-byte store; the inserter places no bid of its own (pass 2
+                // compares the best bid with the inserter's order key)
+                *reinterpret_cast<uint2 *>(&slot->born) = make_uint2(epoch, (uint32_t)i);
                 verdict = 1;
             } else if (r == FOUND) {
                 uint32_t born;
                 asm volatile("ld.global.cg.u32 %0, [%1];" : "=r"(born) : "l"(&slot->born));
                 if (born == 0 || born == epoch) {
+                    const uint32_t ord = order ? __ldg(order + i) : (uint32_t)i;
                     atomicMax(&slot->stamp, dedup_tag(epoch, ord));
                     conflict = (uint32_t)pos;
                 }
@@ -180,9 +177,11 @@ set_dedup_pass1(SetHeader *hdr, SetSlot *slots, uint64_t mask, int64_t n, const 
     warp_count_add(&hdr->count, inserted);
 }
 
-// Pass 2: only entries that met a key inserted by this same call.  The smallest order key
-// wins the slot; if that is not the entry that physically inserted the key, the inserter's
-// provisional keep = 1 is withdrawn (every loser writes the same 0, so the race is benign).
+// Pass 2: only entries that met a key inserted by this same call.  `stamp` holds the best bid
+// among those FINDERS (largest tag = smallest order key; a slot inserted in this call started
+// with stamp 0).  If that bid beats the inserter's own order key, the bidder takes the slot and
+// the inserter's provisional keep = 1 is withdrawn (every loser writes the same 0, so the race
+// is benign); otherwise the inserter stays and every finder loses.
 __global__ void __launch_bounds__(OB2_BLOCK)
 set_dedup_pass2(const SetSlot *__restrict__ slots, int64_t n, const uint32_t *__restrict__ order, uint32_t epoch,
                 const uint32_t *__restrict__ scratch, uint8_t *__restrict__ keep) {
@@ -192,11 +191,13 @@ set_dedup_pass2(const SetSlot *__restrict__ slots, int64_t n, const uint32_t *__
     if (pos == OB2_NO_CONFLICT) return;
     const SetSlot *slot = slots + pos;
     const unsigned long long stamp = slot->stamp;
-    const uint32_t ord = order ? __ldg(order + i) : (uint32_t)i;
-    if (stamp == dedup_tag(epoch, ord)) keep[i] = 1;
     const uint32_t w = slot->winner;
     const uint32_t ord_w = order ? __ldg(order + w) : w;
-    if (stamp != dedup_tag(epoch, ord_w)) keep[w] = 0;
+    if (stamp > dedup_tag(epoch, ord_w)) {
+        keep[w] = 0;
+        const uint32_t ord = order ? __ldg(order + i) : (uint32_t)i;
+        if (stamp == dedup_tag(epoch, ord)) keep[i] = 1;
+    }
 }
 
 __global__ void __launch_bounds__(OB2_BLOCK)

@@ -33,11 +33,14 @@ from .dist import ShardedHistory
 class BatchSlot(object):
     """One set of buffers travelling through the pipeline."""
 
-    def __init__(self, compiled, n):
+    def __init__(self, compiled, n, sample_only=False):
         dev = compiled.device
         self.batch = compiled.empty_columns(n)                      # original columns + mask + fp + keep
-        self.tbatch = compiled.empty_columns(n, transformed=True)   # transform(sample)
-        self.back = compiled.empty_columns(n)                       # reverse(transform(sample))
+        if sample_only:                                             # no transform chain: the draws are the rows handed out
+            self.tbatch, self.back = None, self.batch
+        else:
+            self.tbatch = compiled.empty_columns(n, transformed=True)   # transform(sample)
+            self.back = compiled.empty_columns(n)                       # reverse(transform(sample))
         self.batch.keep = torch.empty(self.batch.n_stride, dtype=torch.uint8, device=dev)
         self.sampled = torch.cuda.Event()
         self.reversed = torch.cuda.Event()
@@ -54,14 +57,17 @@ class CandidatePipeline(object):
         # writes -- the candidates as handed out; 'sample': by the (issue-bound) sampler over its draws
         # 'suggest': ONE kernel (ob2_suggest) samples, transforms, reverses in registers and fingerprints --
         # the Random.suggest fast path; the transformed columns are written but never read back
-        assert fingerprint_in in ('reverse', 'sample', 'suggest')
-        self.fused = fingerprint_in == 'suggest'
+        # 'sample_only': BASELINE.json config 5 as written -- ob2_sample with the fused fingerprint, then dedup;
+        # no transformed columns at all
+        assert fingerprint_in in ('reverse', 'sample', 'suggest', 'sample_only')
+        self.sample_only = fingerprint_in == 'sample_only'
+        self.fused = fingerprint_in in ('suggest', 'sample_only')     # one kernel before the dedup
         self.fp_in_reverse = fingerprint_in in ('reverse', 'suggest')
         self.compiled = compiled
         self.n = n
         # a ShardedHistory / PeerShardedHistory is used as is; a bare TrialHistory is wrapped
         self.sharded = history if hasattr(history, 'world') else ShardedHistory(history, device=compiled.device)
-        self.slots = [BatchSlot(compiled, n) for _ in range(depth)]
+        self.slots = [BatchSlot(compiled, n, sample_only=self.sample_only) for _ in range(depth)]
         dev = compiled.device
         # The dedup kernels are latency bound (random 32-byte probes) and tiny next to the
         # streaming ones; at equal priority their blocks queue behind the ~24k blocks of
@@ -94,7 +100,10 @@ class CandidatePipeline(object):
                 slot.hold = None
             if ev:
                 ev[0].record()
-            if self.fused:
+            if self.sample_only:
+                c.sample(n, seed, base_index=base_index, index=index, with_mask=True, with_fingerprint=True,
+                         out=slot.batch)
+            elif self.fused:
                 c.suggest(n, seed, base_index=base_index, index=index,
                           out=slot.batch, transformed_out=slot.tbatch, back_out=slot.back)
             else:
@@ -145,7 +154,7 @@ class CandidatePipeline(object):
         k = len(self.timings)
         if self.fused:
             return {
-                'suggest': sum(e[0].elapsed_time(e[1]) for e in self.timings) / k,
+                ('sample+fingerprint' if self.sample_only else 'suggest'): sum(e[0].elapsed_time(e[1]) for e in self.timings) / k,
                 'dedup': sum(e[4].elapsed_time(e[5]) for e in self.timings) / k,
             }
         return {
