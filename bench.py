@@ -2,7 +2,8 @@
 """Benchmark of the candidate-generation hot path (BASELINE.json metric).
 
     python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
-    python bench.py --impl reference --gpus N --steps K ...  # CPU arm (oracle port of the reference path)
+    python bench.py --impl reference --gpus N --steps K ...  # CPU arm: the unmodified reference (oracle/_ref)
+    python bench.py --workload cfg5 | cfg2                   # BASELINE.json configs 5 / 2 as the main line
 
 One "step" = one pass of the whole path over one batch of synthetic candidates
 of the `mixed64` space: sample (Philox, fused bounds check) ->
@@ -42,6 +43,11 @@ BYTES_SAMPLE = 448
 BYTES_TRANSFORM = 448 + 1408
 BYTES_REVERSE = 1408 + 448
 BYTES_DEDUP = 16 + 32 + 16 + 4 + 4 + 1      # fp read, probe sector, insert, scratch w+r, keep
+# what the one-kernel suggest MUST move (every API-visible result written once, nothing re-read):
+# sampled 448 + transformed 1408 + handed-out 448 + fingerprint 16 + mask 1
+BYTES_SUGGEST_COMPULSORY = 448 + 1408 + 448 + 16 + 1
+BYTES_SAMPLE_FP_COMPULSORY = 448 + 16 + 1   # config 5's sampler: columns + fingerprint + mask
+BYTES_CFG5 = 581                            # SURVEY.md 8d yard-stick for sample + fingerprint + dedup (incl. exchange staging)
 
 
 def parse_args():
@@ -56,6 +62,15 @@ def parse_args():
     ap.add_argument('--ref-cands', type=int, default=100000,
                     help='--impl reference: candidates per process per step (a bounded sample of the workload)')
     ap.add_argument('--e2e-steps', type=int, default=4)
+    ap.add_argument('--workload', default='path', choices=['path', 'cfg5', 'cfg2'],
+                    help="path: the whole hot path (config 5's dedup with config 3's transform chain on top, the default "
+                         "line); cfg5: sample + fingerprint + dedup only (BASELINE.json config 5 as written, 581 B/candidate "
+                         "yard-stick); cfg2: Space.sample on real16.  The default line carries cfg5 and cfg2 as sub-objects.")
+    ap.add_argument('--no-extra', action='store_true', help='default workload only: skip the cfg5 / cfg2 / sustained sub-measurements')
+    ap.add_argument('--sustain', type=float, default=2.0,
+                    help='seconds of back-to-back steps for the sustained-clock sub-measurement (0 = off)')
+    ap.add_argument('--ref-literal-cands', type=int, default=96,
+                    help='--impl reference with oracle/_ref: candidates per process per step through the unmodified reference')
     ap.add_argument('--staged', action='store_true',
                     help='sample+transform, reverse+fingerprint and dedup as separate kernels (the path of an '
                          'algorithm that computes in the transformed space) instead of the one-kernel ob2_suggest')
@@ -73,30 +88,14 @@ def parse_args():
 
 
 # --------------------------------------------------------------------------
-# CPU arm: the oracle port, all host cores
+# CPU arm.  Two baselines, both on all host cores (one process per core):
+#   literal -- the UNMODIFIED reference (oracle/_ref, staged by oracle/make_ref.py):
+#              PrimaryAlgo(space, 'random').suggest(n) = Space.sample + `assert point in space`,
+#              pure Python (src/orion/core/worker/primary_algo.py:44-56); the stages the snapshot
+#              lacks (transform / reverse / dedup) run through the numpy port on the points it drew;
+#   port    -- the vectorised numpy restatement (oracle/space_oracle.py) of the whole path.
 # --------------------------------------------------------------------------
-def _cpu_worker(job):
-    """One process: the whole path on `n` candidates with numpy (oracle port)."""
-    import numpy as np
-    from oracle import space_oracle as so
-    n, base, seed, n_hist = job
-    specs = _mixed64_specs()
-    hist_cols, _ = so.sample_philox(specs, n_hist, seed, base_index=HISTORY_BASE + base)
-    history = set(zip(*[x.tolist() for x in so.fingerprint(hist_cols)]))
-    t0 = time.perf_counter()
-    # planted duplicates: 10 % history counters, 1 % repeat an earlier counter
-    cols, failed = so.sample_philox(specs, n, seed, base_index=base)
-    dup = np.arange(n) % 10 == 3
-    for c, h in zip(cols, hist_cols):
-        c[dup] = h[np.arange(n)[dup] % n_hist]
-    ok = so.contains(specs, cols)
-    t = so.transform(specs, 'real', cols)
-    back = so.reverse(specs, 'real', t)
-    lo, hi = so.fingerprint(back)
-    keep = so.dedup_fingerprints(history, lo, hi)
-    dt = time.perf_counter() - t0
-    assert ok.all() and not failed.any() and len(keep) == n
-    return dt, int(keep.sum())
+CPU_HISTORY_ROWS = 12_500_000          # per process: sorted fingerprint array the port dedups against
 
 
 def _mixed64_specs():
@@ -117,17 +116,83 @@ def _mixed64_specs():
     return specs
 
 
-def cpu_path_rate(n_per_proc, procs, steps=1):
-    """candidates/s of the oracle port with `procs` processes; returns
-    (rate, total candidates, seconds)."""
+def _real16_specs():
+    from oracle.space_oracle import DimSpec
+    return ([DimSpec('u%d' % i, 'real', prior='uniform', args=(-1, 2)) for i in range(8)] +
+            [DimSpec('l%d' % i, 'real', prior='reciprocal', args=(1e-5, 1)) for i in range(8)])
+
+
+_CPU = {}          # per-process state of the pool workers
+
+
+def _cpu_init(kind, workload, hist_rows):
+    """Pool initializer (untimed): the space, and the history this process dedups against."""
+    import numpy as np
+    from oracle import space_oracle as so
+    _CPU['workload'] = workload
+    _CPU['specs'] = _real16_specs() if workload == 'cfg2' else _mixed64_specs()
+    if kind == 'literal':
+        from oracle import ref_harness
+        space = ref_harness.build_space(ref_harness.REAL16_ARGS if workload == 'cfg2' else ref_harness.MIXED64_ARGS)
+        _CPU['algo'] = ref_harness.primary_algo(space, 'random')
+    if workload != 'cfg2':
+        rng = np.random.RandomState(os.getpid() & 0x7FFFFFFF)
+        filler = rng.randint(1, 2 ** 62, size=(hist_rows, 2), dtype=np.int64).view(np.uint64)
+        _CPU['history'] = so.SortedHistory(filler[:, 0], filler[:, 1])
+
+
+def _cpu_worker(job):
+    """One process, one step: the whole path on `n` candidates.  Returns (seconds, kept)."""
+    import numpy as np
+    from oracle import space_oracle as so
+    kind, n, base, seed = job
+    specs, workload = _CPU['specs'], _CPU['workload']
+    history = _CPU.get('history')
+    if kind == 'port' and workload != 'cfg2':
+        # planted duplicates need known history rows: a quarter batch of real rows joins the history (untimed)
+        hist_cols, _ = so.sample_philox(specs, max(n // 4, 16), seed, base_index=HISTORY_BASE + base)
+        history.insert(*so.fingerprint(hist_cols))
+    t0 = time.perf_counter()
+    if kind == 'literal':
+        np.random.seed((seed + base) & 0x7FFFFFFF)
+        points = _CPU['algo'].suggest(n)               # the reference: sample + per-point `in space`
+        if workload == 'cfg2':
+            return time.perf_counter() - t0, n
+        cols = [np.asarray(c, dtype={'real': np.float64, 'integer': np.int64, 'categorical': np.int32}[sp.kind])
+                for c, sp in zip(zip(*points), specs)]
+    else:
+        cols, failed = so.sample_philox(specs, n, seed, base_index=base)
+        if workload == 'cfg2':
+            return time.perf_counter() - t0, n
+        dup = np.arange(n) % 10 == 3                   # 10 % copies of history rows
+        for c, h in zip(cols, hist_cols):
+            c[dup] = h[np.arange(n)[dup] % len(h)]
+        ok = so.contains(specs, cols)
+        assert ok.all() and not failed.any()
+    if workload == 'cfg5':
+        lo, hi = so.fingerprint(cols)
+    else:
+        t = so.transform(specs, 'real', cols)
+        back = so.reverse(specs, 'real', t)
+        lo, hi = so.fingerprint(back)
+    keep = history.dedup(lo, hi)
+    dt = time.perf_counter() - t0
+    assert len(keep) == n
+    return dt, int(keep.sum())
+
+
+def cpu_path_rate(kind, n_per_proc, procs, steps=1, workload='path', warm=True):
+    """candidates/s of the CPU path with `procs` processes; returns (rate, total candidates, seconds)."""
     import multiprocessing as mp
     ctx = mp.get_context('spawn')
-    jobs = [(n_per_proc, p * n_per_proc, SEED, max(n_per_proc // 4, 16)) for p in range(procs)]
+    hist_rows = CPU_HISTORY_ROWS if kind == 'port' else 100_000
     total_t = 0.0
     total_n = 0
-    with ctx.Pool(procs) as pool:
-        pool.map(_cpu_worker, [(256, 0, SEED, 64)] * procs)          # warm imports
-        for _ in range(steps):
+    with ctx.Pool(procs, initializer=_cpu_init, initargs=(kind, workload, hist_rows)) as pool:
+        if warm:
+            pool.map(_cpu_worker, [(kind, 8 if kind == 'literal' else 256, 0, SEED)] * procs)      # imports, first calls
+        for step in range(steps):
+            jobs = [(kind, n_per_proc, (step * procs + p) * n_per_proc, SEED) for p in range(procs)]
             t0 = time.perf_counter()
             pool.map(_cpu_worker, jobs)
             total_t += time.perf_counter() - t0
@@ -142,35 +207,77 @@ def host_cores():
         return os.cpu_count() or 1
 
 
+def reference_available():
+    try:
+        from oracle import ref_harness
+        return ref_harness.available()
+    except Exception:
+        return False
+
+
+def cpu_baseline_block(workload, literal_n, port_n, procs):
+    """The `cpu_baseline` object: the literal reference when oracle/_ref is there (kind
+    "reference"), with the vectorised port beside it; the port alone otherwise."""
+    port_rate, port_total, port_s = cpu_path_rate('port', port_n, procs, workload=workload)
+    port = {"value": port_rate, "unit": UNIT, "cores": procs, "kind": "port",
+            "sample": "%d candidates (%d per process x %d processes, %.1f s) through the numpy oracle; each process "
+                      "dedups against a sorted array of %d fingerprints" % (port_total, port_n, procs, port_s,
+                                                                            CPU_HISTORY_ROWS)}
+    if not reference_available():
+        return port
+    rate, total, secs = cpu_path_rate('literal', literal_n, procs, workload=workload)
+    return {"value": rate, "unit": UNIT, "cores": procs, "kind": "reference",
+            "sample": "%d candidates (%d per process x %d processes, %.1f s): the unmodified reference's "
+                      "PrimaryAlgo(space, 'random').suggest(n) (oracle/_ref), then transform / reverse / dedup -- absent "
+                      "from the reference -- through the numpy port on those points" % (total, literal_n, procs, secs),
+            "per_core": rate / procs, "port": port}
+
+
 def run_reference(args):
-    """`--impl reference`: the reference's CPU path (numpy oracle port -- the
-    reference itself is pure Python and cannot travel to the GPU box), all host
-    cores, on bounded samples of the same workload."""
+    """`--impl reference`: the reference's own CPU implementation of the path on all host cores
+    -- the unmodified package staged in oracle/_ref when it is there, else the numpy port --
+    on bounded samples of the same workload."""
     rank = int(os.environ.get('RANK', '0'))
     if rank != 0:
         return
     procs = host_cores()
-    n_per_proc = args.ref_cands
-    for _ in range(args.warmup and 1):
-        cpu_path_rate(2000, procs)
-    rate, total_n, secs = cpu_path_rate(n_per_proc, procs, steps=args.steps)
-    sample = "%d candidates/step (%d per process x %d processes) of the mixed64 workload" % (
-        n_per_proc * procs, n_per_proc, procs)
+    literal = reference_available()
+    kind = 'literal' if literal else 'port'
+    n_per_proc = args.ref_literal_cands if literal else args.ref_cands
+    rate, total_n, secs = cpu_path_rate(kind, n_per_proc, procs, steps=args.steps, workload=args.workload,
+                                        warm=args.warmup > 0)
+    sample = "%d candidates/step (%d per process x %d processes) of the %s workload, %s" % (
+        n_per_proc * procs, n_per_proc, procs, args.workload,
+        "through the unmodified reference (oracle/_ref): PrimaryAlgo.suggest; stages the snapshot lacks via the numpy port"
+        if literal else "through the numpy oracle port (no reference package staged)")
     line = {
         "impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * secs / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
         "data": "synthetic", "config": workload_config(args, args.gpus),
-        "cpu_baseline": {"value": rate, "unit": UNIT, "cores": procs, "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": rate, "unit": UNIT, "cores": procs, "kind": "reference" if literal else "port",
+                         "sample": sample},
         "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     emit(line)
 
 
+WORKLOADS = {
+    'path': "mixed64 (16 uniform + 8 loguniform + 8 normal Real, 16 uniform Integer, 16 Categorical x 8): "
+            "sample + contains + transform('real') + reverse + fingerprint + dedup vs history",
+    'cfg5': "mixed64: sample + contains + fingerprint + dedup vs sharded history (BASELINE.json config 5, no transform chain)",
+    'cfg2': "real16 (8 uniform + 8 loguniform Real): Space.sample (BASELINE.json config 2)",
+}
+
+
 def workload_config(args, world):
+    """Identical for the b200 and the reference arm (the driver compares the two)."""
+    if args.workload == 'cfg2':
+        return {"workload": WORKLOADS['cfg2'], "candidates_per_gpu_per_step": args.cands,
+                "parallelism": "dp%d (candidates sharded by counter)" % world,
+                "l2": "outputs larger than L2 (>= 1.6 GB written per kernel)"}
     return {
-        "workload": "mixed64 (16 uniform + 8 loguniform + 8 normal Real, 16 uniform Integer, 16 Categorical x 8): "
-                    "sample + contains + transform('real') + reverse + fingerprint + dedup vs history",
+        "workload": WORKLOADS[args.workload],
         "candidates_per_gpu_per_step": args.cands, "history_rows_per_gpu": args.history,
         "planted_duplicates": "10% history rows, 1% earlier rows of the batch",
         "parallelism": "dp%d (candidates sharded by counter; history hash set sharded by fingerprint)" % world,
@@ -310,34 +417,172 @@ class SmiClocks(object):
         return out
 
 
-def run_b200(args):
-    import numpy as np
+def csrc_sha16():
+    """Hash of the kernel sources: stamps every ncu-derived figure kept in profiles/."""
+    import glob
+    import hashlib
+    h = hashlib.sha256()
+    files = sorted(glob.glob(os.path.join(ROOT, 'orion_b200', 'csrc', '*.cu')) +
+                   glob.glob(os.path.join(ROOT, 'orion_b200', 'csrc', '*.cuh')) +
+                   [os.path.join(ROOT, 'include', 'ob2.h')])
+    for path in files:
+        h.update(os.path.basename(path).encode())
+        h.update(open(path, 'rb').read())
+    return h.hexdigest()[:16]
+
+
+def measured_traffic(kernel):
+    """ncu dram__bytes (read + write) per launch of `kernel` at 1.25e7 candidates, from
+    profiles/traffic.json -- used only when that capture was taken from THESE kernel sources."""
+    tpath = os.path.join(ROOT, 'profiles', 'traffic.json')
+    if not os.path.exists(tpath):
+        return None, "no profiles/traffic.json"
+    data = json.load(open(tpath))
+    if data.get('csrc_sha16') != csrc_sha16():
+        return None, ("profiles/traffic.json was captured from other kernel sources (%s, now %s): not used"
+                      % (data.get('csrc_sha16'), csrc_sha16()))
+    return data.get(kernel), "ncu capture of these sources (profiles/traffic.json, %s)" % data.get('capture', '?')
+
+
+def hbm_peak():
+    peaks_path = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    if os.path.exists(peaks_path):
+        return float(json.load(open(peaks_path))['hbm_gbs']), "MEASURED_PEAKS.json hbm_gbs (of measured)"
+    return 6650.0, "B200_PROFILING.md fallback 6.65 TB/s (of fallback)"
+
+
+def measure_cfg2(dev, reps=5, warm=2):
+    """BASELINE.json config 2: Space.sample on real16, n = 1e6 (launch-overhead inclusive) and
+    n = 1e8 (steady state); write-only, 128 B per candidate."""
+    import torch
+    from orion_b200 import spaces
+    compiled = spaces.real16().compiled()
+    peak, _src = hbm_peak()
+    out = {}
+    for n in (1_000_000, 100_000_000):
+        buf = compiled.empty_columns(n)
+        e = [torch.cuda.Event(enable_timing=True) for _ in range(reps + 1)]
+        for r in range(warm):
+            compiled.sample(n, SEED - 3, base_index=r * n, with_mask=False, out=buf)
+        torch.cuda.synchronize()
+        e[0].record()
+        for r in range(reps):
+            compiled.sample(n, SEED - 3, base_index=(warm + r) * n, with_mask=False, out=buf)
+            e[r + 1].record()
+        torch.cuda.synchronize()
+        ms = min(e[r].elapsed_time(e[r + 1]) for r in range(reps))
+        rate = n / (ms * 1e-3)
+        out['n=%d' % n] = {"ms": ms, "candidates_per_s": rate, "written_GBps": 128 * rate / 1e9,
+                           "frac_of_hbm_peak": 128 * rate / 1e9 / peak}
+        del buf
+    torch.cuda.empty_cache()
+    out["algorithmic_bytes_per_candidate"] = 128
+    out["roofline_candidates_per_s"] = peak * 1e9 / 128
+    return out
+
+
+def run_cfg2(args):
+    """`--workload cfg2` as the main line: one step = Space.sample of `--cands` real16 candidates."""
     import torch
     import torch.distributed as dist
     from orion_b200 import spaces
-    from orion_b200.dist import ShardedHistory
-    from orion_b200.history import TrialHistory, table_slots_for
-    from orion_b200.transformer import build_required_space
-
     world = int(os.environ.get('WORLD_SIZE', '1'))
     rank = int(os.environ.get('RANK', '0'))
     local_rank = int(os.environ.get('LOCAL_RANK', '0'))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device('cuda', local_rank)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=dev)
+    n, K, W = args.cands, args.steps, args.warmup
+    compiled = spaces.real16().compiled()
+    bufs = [compiled.empty_columns(n) for _ in range(2)]
+    for s in range(W):
+        compiled.sample(n, SEED - 3, base_index=(s * world + rank) * n, with_mask=False, out=bufs[s % 2])
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    clocks = Clocks(local_rank)
+    if rank == 0:
+        clocks.start()
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0.record()
+    for s in range(K):
+        compiled.sample(n, SEED - 3, base_index=((W + s) * world + rank) * n, with_mask=False, out=bufs[s % 2])
+    t1.record()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    clock_info = clocks.stop() if rank == 0 else None
+    ms = t0.elapsed_time(t1)
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    # end to end: Space.sample_columns -> pinned host (the public API with a host result)
+    E = max(args.e2e_steps, 1)
+    host = torch.empty(bufs[0].buf.numel(), dtype=torch.uint8).pin_memory()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for j in range(E):
+        compiled.sample(n, SEED - 4, base_index=(j * world + rank) * n, with_mask=False, out=bufs[0])
+        host.copy_(bufs[0].buf, non_blocking=True)
+    e1.record()
+    torch.cuda.synchronize()
+    e2e_ms = e0.elapsed_time(e1)
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    peak, peak_src = hbm_peak()
+    rate1 = n * K / (ms * 1e-3)
+    line = {"metric": "Space.sample candidates/sec (real16)", "value": world * rate1, "unit": UNIT, "n_gpus": world,
+            "steps": K, "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": workload_config(args, world),
+            "roofline": {"bound": "hbm", "kernel": "sample", "achieved": 128 * rate1 / 1e9, "peak": peak, "unit": "GB/s",
+                         "frac": 128 * rate1 / 1e9 / peak, "traffic": None, "peak_source": peak_src,
+                         "algorithmic_bytes_per_candidate": 128},
+            "e2e": {"value": world * n * E / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": 0,
+                    "d2h_bytes_per_step": int(bufs[0].buf.numel()), "steps": E},
+            "gpu_launches": K, "clocks": clock_info}
+    if not args.no_cpu_baseline and world == 1:
+        line["cpu_baseline"] = cpu_baseline_block('cfg2', 256, 200000, host_cores())
+    emit(line)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    from orion_b200 import spaces
+    from orion_b200.history import TrialHistory, table_slots_for
+    from orion_b200.transformer import build_required_space
+
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device; there is no CPU fallback for the product path")
+    if args.workload == 'cfg2':
+        return run_cfg2(args)
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    rank = int(os.environ.get('RANK', '0'))
+    local_rank = int(os.environ.get('LOCAL_RANK', '0'))
     torch.cuda.set_device(local_rank)
     dev = torch.device('cuda', local_rank)
     if world > 1:
         dist.init_process_group('nccl', device_id=dev)
     assert world == args.gpus or world == 1, "launch with torchrun --nproc-per-node == --gpus"
 
+    cfg5_main = args.workload == 'cfg5'
+    extras = not args.no_extra and not cfg5_main
     n = args.cands
     K, W = args.steps, args.warmup
-    KS = min(K, 5)                                    # steps of the staged-kernels comparison pass
+    KS = 0 if cfg5_main else min(K, 5)                # steps of the staged-kernels comparison pass
     KR = min(K, 20)                                   # steps of the serial per-kernel pass behind the timed region
-    total_steps = K + KR + KS + W + args.e2e_steps + 2  # timed + serial pass + staged pass + e2e (+ its warm-up)
+    K5 = min(K, 10) if extras else 0                  # steps of the config-5 sub-measurement
+    total_steps = K + KR + KS + K5 + W + args.e2e_steps + 4  # timed + serial + staged + cfg5 + e2e (+ warm-ups)
     space = spaces.mixed64()
     tspace = build_required_space('real', space)
-    compiled = tspace.compiled()
+    compiled = space.compiled() if cfg5_main else tspace.compiled()
+    plain = space.compiled()                          # no transform chain: config 5's sampler
 
     # ---- history shard: rows from counters [2^40 + rank*H, ...), fingerprints only
     H = args.history
@@ -364,6 +609,7 @@ def run_b200(args):
         sharded.insert(b.fp, m)
         done += m
     torch.cuda.synchronize()
+    del hb, b
     hist_rows0 = len(history)
 
     # ---- per-step candidate counters with planted duplicates (synthetic input, built before timing)
@@ -379,29 +625,71 @@ def run_b200(args):
         idx = torch.where((r >= 0.10) & (r < 0.11), early, idx)
         return idx
 
+    def expected_keep(idx):
+        """The keep mask this step MUST produce, from the Philox counters alone (a candidate is a
+        function of its counter; continuous dimensions never collide otherwise): not a history
+        counter, and the first global position (rank order) holding that counter.  Fresh counters
+        of different steps are disjoint by construction."""
+        if world > 1:
+            everyone = torch.empty(world * n, dtype=torch.int64, device=dev)
+            dist.all_gather_into_tensor(everyone, idx.contiguous())
+        else:
+            everyone = idx
+        order = torch.argsort(everyone, stable=True)
+        srt = everyone[order]
+        first_sorted = torch.ones(everyone.numel(), dtype=torch.bool, device=dev)
+        first_sorted[1:] = srt[1:] != srt[:-1]
+        first = torch.empty_like(first_sorted)
+        first[order] = first_sorted
+        want = first & (everyone < HISTORY_BASE)
+        return want[rank * n:(rank + 1) * n]
+
+    def all_ranks_true(flag):
+        if world > 1:
+            t = torch.tensor([1 if flag else 0], dtype=torch.int32, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MIN)
+            return bool(t.item())
+        return bool(flag)
+
     index_dev = [step_index(s) for s in range(W + K)]
     # two buffer sets (28 GB each) serve the pipeline, the serial pass and the e2e leg
     from orion_b200.pipeline import CandidatePipeline
     # default: ob2_suggest, ONE kernel for sample -> transform -> reverse -> fingerprint (Random.suggest fast path)
-    one_kernel = not (args.staged or args.unfused or args.fp_in_sampler)
+    one_kernel = not (args.staged or args.unfused or args.fp_in_sampler) and not cfg5_main
     pipe = CandidatePipeline(compiled, sharded, n, depth=2,
-                             fingerprint_in='suggest' if one_kernel else 'sample' if args.fp_in_sampler else 'reverse')
+                             fingerprint_in='sample_only' if cfg5_main else 'suggest' if one_kernel
+                             else 'sample' if args.fp_in_sampler else 'reverse')
     batch, tbatch, back = pipe.slots[0].batch, pipe.slots[0].tbatch, pipe.slots[0].back
     fused = not args.unfused
-    # extra kernels of mine per step for the exchange: NCCL path bucket+pad+scatter; peer path send+counts+pad+return+collect
-    exchange_launches = 0 if world == 1 else (4 if peer_exchange else 3)
+    # extra kernels of mine per step for the exchange: NCCL path bucket+pad+scatter; peer path send+counts+flag+pad+collect
+    exchange_launches = 0 if world == 1 else (5 if peer_exchange else 3)
     fp_in_reverse = fused and not args.fp_in_sampler     # fingerprints computed by the reverse kernel (default)
     rev = 'reverse+fingerprint' if fp_in_reverse else 'reverse'
     kernel_names = ['sample+transform', rev, 'dedup'] if fused else ['sample', 'transform', rev, 'dedup']
     staged_names = list(kernel_names)
     if one_kernel:
         kernel_names = ['suggest', 'dedup']
-    step_launches = (3 if one_kernel else 4 if fused else 5) + exchange_launches    # dedup = 2 launches
+    if cfg5_main:
+        kernel_names = ['sample+fingerprint', 'dedup']
+    step_launches = (3 if (one_kernel or cfg5_main) else 4 if fused else 5) + exchange_launches    # dedup = 2 launches
     ev = [[torch.cuda.Event(enable_timing=True) for _ in range(len(kernel_names) + 1)] for _ in range(K)]
     launches = [0]
 
+    def cfg5_step(idx, events=None):
+        """BASELINE.json config 5 as written: sample (fused contains + fingerprint) -> dedup."""
+        plain.sample(n, SEED, index=idx, with_mask=True, with_fingerprint=True, out=batch)
+        if events:
+            events[1].record()
+        sharded.dedup(batch.fp, n, per_rank_n=n, keep=batch.keep, check=False)
+        if events:
+            events[2].record()
+
     def one_step(step, events=None, staged=False):
         j = 1
+        if cfg5_main:
+            cfg5_step(index_dev[step], events)
+            launches[0] += step_launches
+            return
         if one_kernel and not staged:
             compiled.suggest(n, SEED, index=index_dev[step], out=batch, transformed_out=tbatch, back_out=back)
             if events:
@@ -449,8 +737,8 @@ def run_b200(args):
     clocks = Clocks(local_rank)
     contended_ms = None
     if pipelined:
-        # ---- timed region: K steps through the stream pipeline (sample+transform of step k+1
-        # overlaps reverse and dedup of step k; every result is still materialised)
+        # ---- timed region: K steps through the stream pipeline (the sampling kernel of step k+1
+        # overlaps dedup of step k; every result is still materialised)
         for s in range(W):
             pipe.submit(SEED, index=index_dev[s])
         pipe.drain()
@@ -470,19 +758,6 @@ def run_b200(args):
         contended_ms = pipe.kernel_ms()
         pipe.timed = False
         last_batch, last_back = slot.batch, slot.back
-        kept_last = int(last_batch.keep[:n].sum().item())
-        mask_ok = bool(last_batch.mask[:n].all().item())
-        round_trip_ok = bool(torch.equal(last_back.buf, last_batch.buf))
-        # ---- the same steps (at most 20), one stream, no overlap: clean per-kernel durations for the roofline
-        n_ev = KR
-        for s in range(KR):
-            index_dev[W + s] = step_index(W + K + s)      # fresh counters, same duplicate mix
-        sync_all()
-        for s in range(KR):
-            ev[s][0].record()
-            one_step(W + s, ev[s])
-        sync_all()
-        serial_ms = sum(ev[s][0].elapsed_time(ev[s][-1]) for s in range(KR)) / KR
     else:
         for s in range(W):
             one_step(s)
@@ -500,10 +775,26 @@ def run_b200(args):
         elapsed_ms = max_over_ranks(t_begin.elapsed_time(t_end))
         timed_launches = launches[0]
         serial_ms = elapsed_ms / K
-        kept_last = int(batch.keep[:n].sum().item())
-        mask_ok = bool(batch.mask[:n].all().item())
-        round_trip_ok = bool(torch.equal(back.buf, batch.buf))
-    if world > 1:        # did any (source, owner) lane overflow during the run?
+        last_batch, last_back = batch, back
+    # ---- checks on the last timed step (outside the timed region)
+    kept_last = int(last_batch.keep[:n].sum().item())
+    mask_ok = bool(last_batch.mask[:n].all().item())
+    round_trip_ok = True if cfg5_main else bool(torch.equal(last_back.buf, last_batch.buf))
+    want = expected_keep(index_dev[W + K - 1])
+    keep_mask_exact = all_ranks_true(bool(torch.equal(last_batch.keep[:n].bool(), want)))
+    del want
+    if pipelined:
+        # ---- the same steps (at most 20), one stream, no overlap: clean per-kernel durations for the roofline
+        n_ev = KR
+        for s in range(KR):
+            index_dev[W + s] = step_index(W + K + s)      # fresh counters, same duplicate mix
+        sync_all()
+        for s in range(KR):
+            ev[s][0].record()
+            one_step(W + s, ev[s])
+        sync_all()
+        serial_ms = sum(ev[s][0].elapsed_time(ev[s][-1]) for s in range(KR)) / KR
+    if world > 1:        # did any (source, owner) lane overflow / any shard fill up during the run?
         sharded.check_overflow() if peer_exchange else sharded.check_overflow(n)
     hist_rows1 = len(history)
 
@@ -529,14 +820,72 @@ def run_b200(args):
                        "note": "same workload through ob2_sample_transform -> ob2_reverse_fingerprint -> ob2_set_dedup, "
                                "one stream, run after the timed region"}
 
+    peak, peak_src = hbm_peak()
+
+    # ---- BASELINE.json config 5 on its own yard-stick: sample + fingerprint + dedup, no transform chain
+    cfg5_info = None
+    if K5:
+        base5 = W + K + KR + KS
+        c5 = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(K5)]
+        cfg5_step(step_index(base5))                                  # warm-up (its rows become history)
+        idx5 = None
+        for s in range(K5):
+            idx5 = step_index(base5 + 1 + s)
+            c5[s][0].record()
+            cfg5_step(idx5, c5[s])
+        sync_all()
+        c5_ms = max_over_ranks(sum(e[0].elapsed_time(e[2]) for e in c5) / K5)
+        c5_want = expected_keep(idx5)
+        c5_exact = all_ranks_true(bool(torch.equal(batch.keep[:n].bool(), c5_want)))
+        del c5_want, idx5
+        rate5 = n / (c5_ms * 1e-3)
+        sample_ms = sum(e[0].elapsed_time(e[1]) for e in c5) / K5
+        cfg5_info = {"workload": WORKLOADS['cfg5'], "steps": K5, "ms_per_step": c5_ms, "value": world * rate5, "unit": UNIT,
+                     "kernels_ms": {"sample+fingerprint": sample_ms,
+                                    "dedup": sum(e[1].elapsed_time(e[2]) for e in c5) / K5},
+                     "roofline": {"yardstick_bytes_per_candidate": BYTES_CFG5,
+                                  "roofline_candidates_per_s_per_gpu": peak * 1e9 / BYTES_CFG5,
+                                  "frac": BYTES_CFG5 * rate5 / 1e9 / peak,
+                                  "sampler_frac_of_hbm_peak": BYTES_SAMPLE_FP_COMPULSORY * n / (sample_ms * 1e-3) / 1e9 / peak,
+                                  "note": "per GPU; one stream, CUDA events around each step (the default line's suggest "
+                                          "replaced by ob2_sample with the fused fingerprint)"},
+                     "keep_mask_exact": c5_exact}
+    K5_used = K5 + 1 if K5 else 0
+
+    cfg2_info = None
+    if extras and world == 1:
+        cfg2_info = measure_cfg2(dev)
+
+    # ---- sustained clocks: back-to-back steps for >= S seconds.  The table cannot take S seconds of
+    # fresh rows (2^31 slots), so these steps replay counters already seen: the sampling kernel does its
+    # full work, dedup finds every row (probe only).
+    sustained = None
+    if extras and args.sustain > 0:
+        sclocks = Clocks(local_rank, period_s=0.02)
+        per = max(serial_ms, 1.0)
+        n_sus = int(args.sustain * 1e3 / per) + 1
+        sync_all()
+        s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        if rank == 0:
+            sclocks.start()
+        s0.record()
+        for s in range(n_sus):
+            one_step(W + (s % K))
+        s1.record()
+        sync_all()
+        sus_clock = sclocks.stop() if rank == 0 else None
+        sus_ms = max_over_ranks(s0.elapsed_time(s1))
+        sustained = {"seconds": sus_ms * 1e-3, "steps": n_sus, "ms_per_step": sus_ms / n_sus,
+                     "value": world * n * n_sus / (sus_ms * 1e-3), "unit": UNIT, "clocks": sus_clock,
+                     "note": "replayed counters: the sampling kernel in full, dedup probe-only (every row already in the history)"}
+
     # ---- end to end through the public API with host buffers
     e2e = None
     if args.e2e_steps > 0:
-        from orion_b200.pipeline import CandidatePipeline
         E = args.e2e_steps
         host_idx = [torch.empty(n, dtype=torch.int64).pin_memory() for _ in range(E + 2)]
         for j, h in enumerate(host_idx):
-            h.copy_(step_index(W + K + KR + KS + j))
+            h.copy_(step_index(W + K + KR + KS + K5_used + j))
         # Survivors only cross PCIe: after dedup the kept rows are gathered into a dense block on
         # the device (ob2_compact) and each column's first n_kept elements are copied to pinned
         # host memory.  Two buffer sets: compaction and copies of step j overlap step j+1.
@@ -620,8 +969,10 @@ def run_b200(args):
                "h2d_bytes_per_step": int(n * 8),
                "d2h_bytes_per_step": int(state['d2h'] // max(E, 1)),
                "steps": args.e2e_steps, "kept_last_step": state['kept'],
+               "d2h_GBps_per_gpu": state['d2h'] / (e2e_ms * 1e-3) / 1e9,
                "api": "CandidatePipeline.submit(counters copied from pinned host) -> "
-                      + ("suggest (one kernel) -> dedup " if one_kernel else "sample+transform -> reverse || dedup ") +
+                      + ("sample+fingerprint -> dedup " if cfg5_main else "suggest (one kernel) -> dedup " if one_kernel
+                         else "sample+transform -> reverse || dedup ") +
                       "-> ob2_compact" + ("_wire" if wire else "") + " -> surviving candidates' columns copied to pinned host (copies overlap the next step)"}
 
     if rank != 0:
@@ -629,28 +980,25 @@ def run_b200(args):
             dist.destroy_process_group()
         return
 
-    peaks_path = os.path.join(ROOT, 'MEASURED_PEAKS.json')
-    if os.path.exists(peaks_path):
-        peak = float(json.load(open(peaks_path))['hbm_gbs'])
-        peak_src = "MEASURED_PEAKS.json hbm_gbs (of measured)"
-    else:
-        peak, peak_src = 6650.0, "B200_PROFILING.md fallback 6.65 TB/s (of fallback)"
-    algo_bytes = {'sample': BYTES_SAMPLE, 'transform': BYTES_TRANSFORM, 'reverse': BYTES_REVERSE, 'dedup': BYTES_DEDUP,
-                  'sample+transform': BYTES_SAMPLE + BYTES_TRANSFORM,
-                  'reverse+fingerprint': BYTES_REVERSE,
-                  # the yard-stick stays the table's figure: fusion shows up as frac > naive
-                  'suggest': BYTES_SAMPLE + BYTES_TRANSFORM + BYTES_REVERSE}
-    algo_bytes = {k: algo_bytes[k] for k in kernel_names}
+    # yard-stick bytes (every stage's output AND the re-reads a staged path pays) and the
+    # bytes a kernel must move as built (each API-visible result written once, inputs read once)
+    yard = {'sample': BYTES_SAMPLE, 'transform': BYTES_TRANSFORM, 'reverse': BYTES_REVERSE, 'dedup': BYTES_DEDUP,
+            'sample+transform': BYTES_SAMPLE + BYTES_TRANSFORM, 'reverse+fingerprint': BYTES_REVERSE,
+            'suggest': BYTES_SAMPLE + BYTES_TRANSFORM + BYTES_REVERSE, 'sample+fingerprint': BYTES_SAMPLE}
+    compulsory = dict(yard, **{'suggest': BYTES_SUGGEST_COMPULSORY, 'sample+fingerprint': BYTES_SAMPLE_FP_COMPULSORY,
+                               'sample+transform': 448 + 1408 + 1, 'reverse+fingerprint': 1408 + 448 + 16})
+    yard = {k: yard[k] for k in kernel_names}
     dominant = max(per_kernel_ms, key=per_kernel_ms.get)
-    achieved = algo_bytes[dominant] * n / (per_kernel_ms[dominant] * 1e-3) / 1e9
-    traffic = None
-    tpath = os.path.join(ROOT, 'profiles', 'traffic.json')
-    if os.path.exists(tpath):
-        traffic = json.load(open(tpath)).get(dominant)
-    kernels = {k: {"ms": per_kernel_ms[k], "algorithmic_GBps": algo_bytes[k] * n / (per_kernel_ms[k] * 1e-3) / 1e9,
-                   "frac_of_hbm_peak": algo_bytes[k] * n / (per_kernel_ms[k] * 1e-3) / 1e9 / peak}
+    dom_s = per_kernel_ms[dominant] * 1e-3
+    achieved = compulsory[dominant] * n / dom_s / 1e9
+    traffic, traffic_src = measured_traffic(dominant)
+    if traffic is not None:
+        traffic = traffic * n / 12_500_000
+    kernels = {k: {"ms": per_kernel_ms[k], "algorithmic_GBps": compulsory[k] * n / (per_kernel_ms[k] * 1e-3) / 1e9,
+                   "frac_of_hbm_peak": compulsory[k] * n / (per_kernel_ms[k] * 1e-3) / 1e9 / peak,
+                   "frac_yardstick": yard[k] * n / (per_kernel_ms[k] * 1e-3) / 1e9 / peak}
                for k in kernel_names}
-    step_bytes = sum(algo_bytes.values())
+    step_bytes = BYTES_CFG5 if cfg5_main else sum(yard.values())
     ms_per_step = elapsed_ms / K
     line = {
         "metric": METRIC, "value": world * n * K / (elapsed_ms * 1e-3), "unit": UNIT, "n_gpus": world,
@@ -658,41 +1006,46 @@ def run_b200(args):
         "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": workload_config(args, world),
         "roofline": {"bound": "hbm", "kernel": dominant, "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
-                     # the yard-stick counts the 448 B/candidate re-read that fusing transform into the
-                     # sampler removes; measured DRAM traffic (ncu, profiles/traffic.json) over the same time:
-                     "traffic_frac": (traffic * n / 12_500_000 / (per_kernel_ms[dominant] * 1e-3) / 1e9 / peak
-                                      if traffic else None),
+                     "algorithmic_bytes_per_candidate": compulsory[dominant],
+                     "algorithmic_bytes_note": "what this kernel must move: every API-visible result written once "
+                                               "(suggest: sampled 448 + transformed 1408 + handed-out 448 + fingerprint 16 "
+                                               "+ mask 1), nothing re-read",
+                     # SURVEY.md 8d's per-stage figure, which also counts the re-reads a staged path pays
+                     # (fusion removed them, hence > 1 for the fused kernel): kept beside, never as `frac`
+                     "yardstick_bytes_per_candidate": yard[dominant],
+                     "frac_yardstick": yard[dominant] * n / dom_s / 1e9 / peak,
+                     "traffic_frac": traffic / dom_s / 1e9 / peak if traffic else None,
+                     "traffic_source": traffic_src,
                      "how": ("CUDA events around each kernel over min(K, 20) serial steps run right after the timed region "
                              "(inside it kernels of adjacent steps overlap; those contended durations are in "
                              "kernels_in_timed_region_ms)" if pipelined else
-                             "CUDA events around each kernel inside the timed region"),
-                     "algorithmic_bytes_per_candidate": algo_bytes[dominant]},
+                             "CUDA events around each kernel inside the timed region")},
         "kernels": kernels,
-        "step_roofline": {"algorithmic_bytes_per_candidate": step_bytes,
-                          "achieved_GBps": step_bytes * n / (ms_per_step * 1e-3) / 1e9,
-                          "frac": step_bytes * n / (ms_per_step * 1e-3) / 1e9 / peak},
+        "step_roofline": {"yardstick_bytes_per_candidate": step_bytes,
+                          "frac_yardstick": step_bytes * n / (ms_per_step * 1e-3) / 1e9 / peak,
+                          "note": "per GPU, whole step, SURVEY.md 8d yard-stick (a fused path scores above a staged one)"},
         "e2e": e2e, "gpu_launches": timed_launches, "clocks": clock_info,
         "timed_region": ("K steps through orion_b200.pipeline.CandidatePipeline (%s, 2 buffer sets)"
-                         % ("suggest and dedup on 2 streams" if one_kernel else "3 streams") if pipelined
-                         else "K steps on one stream, kernels back to back"),
+                         % ("one sampling kernel and dedup on 2 streams" if (one_kernel or cfg5_main) else "3 streams")
+                         if pipelined else "K steps on one stream, kernels back to back"),
         "serial_ms_per_step": serial_ms,
         "kernels_in_timed_region_ms": contended_ms,
         "staged_path": staged_info,
+        "cfg5": cfg5_info, "cfg2": cfg2_info, "sustained": sustained,
         "history_table": {"slots": history.n_slots, "bytes": history.n_slots * 32,
                           "load_at_end": hist_rows1 / float(history.n_slots)},
-        "checks": {"kept_last_step": kept_last, "kept_frac_last_step": kept_last / float(n), "all_in_space": mask_ok,
+        "checks": {"keep_mask_exact": keep_mask_exact,
+                   "keep_mask_exact_how": "last timed step, every rank: keep == (first global position of its Philox "
+                                          "counter) & (not a history counter), from the all-gathered counters",
+                   "kept_last_step": kept_last, "kept_frac_last_step": kept_last / float(n), "all_in_space": mask_ok,
                    "reverse_of_transform_is_identity": round_trip_ok,
                    "history_rows_before": hist_rows0, "history_rows_after": hist_rows1},
+        "exchange": ("none (1 GPU)" if world == 1 else
+                     "peer-memory inboxes over CUDA IPC (ob2_xchg_*)" if peer_exchange else "NCCL all-to-all"),
+        "kernel_sources_sha16": csrc_sha16(),
     }
-    line["config"]["exchange"] = ("none (1 GPU)" if world == 1 else
-                                  "peer-memory inboxes over CUDA IPC (ob2_xchg_*)" if peer_exchange else "NCCL all-to-all")
     if not args.no_cpu_baseline and world == 1:
-        procs = host_cores()
-        n_per_proc = 200000
-        rate, total_n, secs = cpu_path_rate(n_per_proc, procs, steps=1)
-        line["cpu_baseline"] = {"value": rate, "unit": UNIT, "cores": procs, "kind": "port",
-                                "sample": "%d candidates (%d per process x %d processes, %.1f s) of the same workload "
-                                          "through the numpy oracle" % (total_n, n_per_proc, procs, secs)}
+        line["cpu_baseline"] = cpu_baseline_block(args.workload, 64, 200000, host_cores())
     emit(line)
     if world > 1:
         dist.destroy_process_group()
