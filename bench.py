@@ -69,6 +69,9 @@ def parse_args():
     ap.add_argument('--no-extra', action='store_true', help='default workload only: skip the cfg5 / cfg2 / sustained sub-measurements')
     ap.add_argument('--sustain', type=float, default=2.0,
                     help='seconds of back-to-back steps for the sustained-clock sub-measurement (0 = off)')
+    ap.add_argument('--ref-impl', default='auto', choices=['auto', 'literal', 'port'],
+                    help='--impl reference: the unmodified reference package (oracle/_ref), the numpy port, or auto = '
+                         'the reference when it is staged')
     ap.add_argument('--ref-literal-cands', type=int, default=96,
                     help='--impl reference with oracle/_ref: candidates per process per step through the unmodified reference')
     ap.add_argument('--staged', action='store_true',
@@ -241,7 +244,7 @@ def run_reference(args):
     if rank != 0:
         return
     procs = host_cores()
-    literal = reference_available()
+    literal = reference_available() if args.ref_impl == 'auto' else args.ref_impl == 'literal'
     kind = 'literal' if literal else 'port'
     n_per_proc = args.ref_literal_cands if literal else args.ref_cands
     rate, total_n, secs = cpu_path_rate(kind, n_per_proc, procs, steps=args.steps, workload=args.workload,
