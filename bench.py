@@ -1048,7 +1048,7 @@ def run_b200(args):
         "kernel_sources_sha16": csrc_sha16(),
     }
     if not args.no_cpu_baseline and world == 1:
-        line["cpu_baseline"] = cpu_baseline_block(args.workload, 64, 200000, host_cores())
+        line["cpu_baseline"] = cpu_baseline_block(args.workload, 256, 200000, host_cores())
     emit(line)
     if world > 1:
         dist.destroy_process_group()

@@ -6,11 +6,12 @@
 // lo == 0 marks an empty slot (fingerprints never have lo == 0).  Keys are
 // claimed with one 128-bit compare-and-swap, so a slot is either empty or holds
 // a complete key.  Deterministic first-wins inside a batch: every dedup call
-// gets a new epoch.  Pass 1 finds-or-inserts each fingerprint with a BLIND
-// compare-and-swap (no read first: nine entries in ten insert, and what bounds
-// this kernel is the number of L2 transactions per entry, not DRAM bytes --
-// benchmarks/micro/random_access.cu): a key that was there before the call is a
-// duplicate (final, one CAS and one 4-byte read); a key it inserts is kept
+// gets a new epoch.  What bounds this kernel is the number of L2 transactions
+// per entry, not DRAM bytes (benchmarks/micro/random_access.cu: 1.25e7 random
+// 16-byte reads take 0.29 ms, read + CAS 0.62, + one store 0.84, + the second
+// store and the atomicMax of the first protocol 1.12), so pass 1 spends as few
+// as it can.  It finds-or-inserts each fingerprint: a key that was there before
+// the call is a duplicate (final, two reads, no atomic); a key it inserts is kept
 // provisionally and tagged {born = epoch, winner = entry} with ONE 8-byte store;
 // an entry that finds a key inserted by ANOTHER entry of the same call (`born` ==
 // epoch) bids for it with atomicMax on the slot's stamp ((epoch << 32) | ~order).
@@ -74,16 +75,28 @@ __device__ __forceinline__ void ld_key(const SetSlot *slot, uint64_t &lo, uint64
 
 enum { FOUND = 0, INSERTED = 1, OVERFLOW = 2 };
 
-// Find the slot holding (lo, hi), inserting it if absent.  The probe IS the 128-bit CAS
-// (empty -> key): it returns what the slot held, atomically, so there are no torn keys to
-// re-check and an insert costs one transaction instead of a read and a CAS.
+// Find the slot holding (lo, hi), inserting it if absent.  Read first, CAS only into a slot seen
+// empty: a blind CAS (one transaction per insert on an EMPTY table, benchmarks/micro/random_access.cu)
+// was tried and doubled the kernel's time on a table that is a quarter full -- every probe of an
+// occupied slot, the ~0.5 extra per entry that linear probing costs at this load plus the 10 %
+// history duplicates, became an atomic on a line that then has to be written back.
 __device__ __forceinline__ int find_or_insert(SetSlot *slots, uint64_t mask, uint64_t lo, uint64_t hi, uint64_t &pos) {
     pos = lo & mask;
     for (uint64_t step = 0; step <= mask; ++step) {
+        SetSlot *slot = slots + pos;
         uint64_t klo, khi;
-        cas128(slots + pos, 0, 0, lo, hi, klo, khi);
-        if (klo == 0 && khi == 0) return INSERTED;
-        if (klo == lo && khi == hi) return FOUND;
+        ld_key(slot, klo, khi);
+        if (klo == 0) {
+            cas128(slot, 0, 0, lo, hi, klo, khi);
+            if (klo == 0 && khi == 0) return INSERTED;
+            if (klo == lo && khi == hi) return FOUND;
+        } else if (klo == lo) {
+            if (khi == hi) return FOUND;
+            // same low word, different high word: true 64-bit collision or a torn
+            // read of a key being written -- re-read atomically to tell
+            cas128(slot, lo, hi, lo, hi, klo, khi);
+            if (klo == lo && khi == hi) return FOUND;
+        }
         pos = (pos + 1) & mask;
     }
     return OVERFLOW;

@@ -376,7 +376,7 @@ class Space(OrderedDict):
         travel as float64 so the device can check integrality."""
         dims = list(self.values())
         n = len(points)
-        fast = self._columns_of_scalar_rows(dims, points, n)
+        fast = Space._columns_of_scalar_rows(dims, points, n)      # (self may be a reference Space)
         if fast is not None:
             return fast, numpy.ones(n, dtype=bool)
         widths = [int(numpy.prod(d.shape, dtype=numpy.int64)) if d.shape else 1 for d in dims]
