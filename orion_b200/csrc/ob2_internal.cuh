@@ -3,11 +3,51 @@
 #pragma once
 
 #include <cuda_runtime.h>
+#include <math_constants.h>
 #include <stdint.h>
 
 #include <mutex>
 
 #include "ob2.h"
+
+// ---------------------------------------------------------------- sampler draw plan
+// Compiled by ob2_space_create from the slot table (ob2_space.cu: compile_plan); the oracle restates
+// the same rules (oracle/space_oracle.py: draw_plan).  Philox mode only -- injected uniforms are
+// doubles for every slot.
+//
+// Which random bits a slot consumes.  Walking the slots in order, a slot takes the next free words of
+// the current Philox4x32 block (counter word 2 = block number, word 3 = attempt):
+//   * 2 words, starting at an even word, for a 53-bit uniform  u = ((w0 >> 5) 2^26 + (w1 >> 6)) / 2^53;
+//   * 1 word for a 32-bit uniform  u = w / 2^32, which is all these slots need:
+//       - a Categorical slot whose cdf thresholds ceil(cdf[j] 2^32), j < k - 1, are all below 2^32
+//         (index = #{j : cdf[j] <= u} = #{j : ceil(cdf[j] 2^32) <= w}, an integer comparison);
+//       - an Integer slot with a uniform prior, integral loc and scale, 1 <= scale <= 2^20,
+//         |loc| <= 2^20 and no user bounds inside [loc, loc + scale): there u * scale + loc is exact in
+//         double precision, so floor(u * scale + loc) = loc + ((w * scale) >> 32), always in bounds.
+// A block is generated when the slot that holds its word 0 is reached.  Spaces of Real dimensions only
+// keep the layout of the first version (block = slot / 2).
+enum {
+    OB2_CLS_UNIFORM = 0,    // Real, uniform prior: x = u * scale + loc
+    OB2_CLS_RECIP = 1,      // Real, loguniform with |log a| + |log b - log a| < 700: bounded exp
+    OB2_CLS_NORM = 2,       // Real, normal: ob2_ndtri
+    OB2_CLS_INT_MULHI = 3,  // Integer, 32-bit word: loc + mulhi(w, scale)
+    OB2_CLS_CAT_MULHI = 4,  // Categorical, 32-bit word, thresholds are exactly ceil((j + 1) 2^32 / k): mulhi(w, k)
+    OB2_CLS_CAT_TABLE = 5,  // Categorical, 32-bit word, search of the u32 threshold table
+    OB2_CLS_GENERIC = 6     // 53-bit uniform through the general prior switch (incl. Integer = floor, Categorical cdf)
+};
+struct ob2_slot_plan {
+    uint16_t block;   // Philox block number
+    uint8_t word;     // first word of the block this slot consumes
+    uint8_t cls;      // OB2_CLS_*
+    uint32_t irange;  // INT_MULHI: scale
+    int32_t iloc;     // INT_MULHI: loc
+    uint32_t thr_off; // CAT_*: offset of the slot's thresholds in the u32 table (same as cdf_off)
+};
+struct ob2_run {      // maximal run of consecutive slots of one class
+    uint16_t first, count;
+    uint32_t cls;
+};
+#define OB2_SLOT_FAST_EXP 4  // internal flag (staged copy of `flags`): loguniform exponent within +-700
 
 // ---------------------------------------------------------------- host side
 struct ob2_space {
@@ -28,6 +68,11 @@ struct ob2_space {
     ob2_slot_desc *d_slots;
     ob2_slot_desc *h_slots;  // host copy of the uploaded table (launch-parameter path of the sampler)
     double *d_cdf;
+    ob2_slot_plan *h_plan, *d_plan;  // sampler draw plan, one entry per slot
+    ob2_run *h_runs, *d_runs;        // its runs
+    int32_t n_runs;
+    uint32_t *d_thr;                 // categorical thresholds ceil(cdf * 2^32), indexed like the cdf table
+    int32_t philox_rounds;           // 10 (default) or 7
     bool has_onehot;
     bool has_extended_prior;  // a slot uses one of the OB2_DIST_EXPON.. priors
     int unsamplable_slot;  // first slot whose prior has no device inverse CDF, or -1
@@ -125,10 +170,77 @@ __device__ __forceinline__ Philox4 philox4x32_10(uint32_t c0, uint32_t c1, uint3
     return Philox4{c0, c1, c2, c3};
 }
 
-// ((w0 >> 5) * 2^26 + (w1 >> 6)) / 2^53, exactly (53-bit integer -> double -> scale)
+// ((w0 >> 5) * 2^26 + (w1 >> 6)) / 2^53, exactly -- without an integer-to-double conversion.
+// The 53-bit integer v = H * 2^32 + L (H = w0 >> 11, L = low word of the composition) is placed
+// into the mantissas of two doubles whose exponents already carry the 2^-53 scale:
+//   {hi word 0x3FE00000, lo word L} = 2^-1 + L * 2^-53      {0x41E00000, H} = 2^31 + H * 2^-21
+// and (second - (2^31 + 2^-1)) + first = v * 2^-53; both additions are exact (every intermediate
+// is a multiple of 2^-53 below 2^53 of them).
 __device__ __forceinline__ double u53(uint32_t w0, uint32_t w1) {
-    const unsigned long long v = ((unsigned long long)(w0 >> 5) << 26) | (unsigned long long)(w1 >> 6);
-    return __ull2double_rn(v) * 1.1102230246251565e-16;  // 2^-53
+    const uint32_t t = w0 >> 5;
+    const uint32_t lo = __funnelshift_r(w1, t, 6);  // (w1 >> 6) | (t << 26)
+    const double d_lo = __hiloint2double(0x3FE00000, (int)lo);
+    const double d_hi = __hiloint2double(0x41E00000, (int)(w0 >> 11));
+    return __dadd_rn(__dadd_rn(d_hi, -2147483648.5), d_lo);
+}
+
+#include "ob2_ndtri_coef.h"
+
+// Inverse normal CDF (scipy's ndtri, which the oracle uses for `norm` under an injected uniform):
+//     ndtri(u) = (2u - 1) * P(w),   w = -log(4 u (1 - u)),   P(w) = sqrt(2) erfinv(x) / x,  x = 2u - 1
+// One logarithm and one polynomial; only w >= 6.25 (u within 4.8e-4 of 0 or 1: about 3 warps in
+// 100) takes the tail branch.  Coefficients and their error bounds (<= 5e-16 relative against
+// 50-digit arithmetic): ob2_ndtri_coef.h, generated by benchmarks/fit/fit_ndtri.py.  CUDA's
+// normcdfinv costs ~2.3x the instructions because most warps execute both of its regions.
+__device__ __forceinline__ double ob2_ndtri(double u) {
+    const double t = u * (1.0 - u);
+    const double x = fma(2.0, u, -1.0);
+    if (!(t > 0.0)) return u == 0.0 ? -CUDART_INF : (u == 1.0 ? CUDART_INF : CUDART_NAN);
+    const double w = -(log(t) + 1.3862943611198906);  // -log(4 t)
+    double p;
+    if (w < OB2_NDTRI_W_SPLIT) {
+        const double z = w - OB2_NDTRI_W_MID;
+        p = 0.0;
+#define OB2_HORNER(c) p = fma(p, z, c);
+        OB2_NDTRI_CENTRAL(OB2_HORNER)
+#undef OB2_HORNER
+    } else {
+        const double s = sqrt(w);
+        if (s > OB2_NDTRI_S_MAX) return normcdfinv(u);  // u < 2^-53: only an injected uniform gets here
+        const double z = s - OB2_NDTRI_S_MID;
+        p = 0.0;
+#define OB2_HORNER(c) p = fma(p, z, c);
+        OB2_NDTRI_TAIL(OB2_HORNER)
+#undef OB2_HORNER
+    }
+    return x * p;
+}
+
+// exp(y) for |y| < 700 (no overflow / underflow / NaN handling: the caller guarantees the range --
+// the library checks |log a| + |log b - log a| of a loguniform prior when it compiles the space).
+// k = round(y / ln 2) through the 1.5 * 2^52 shift, r = y - k ln2 in two steps, Taylor to degree 13
+// on |r| <= 0.347 (truncation 4e-18), 2^k added into the exponent field.  About 0.6 ulp.
+__device__ __forceinline__ double ob2_exp_bounded(double y) {
+    const double shifted = fma(y, 1.4426950408889634, 6755399441055744.0);
+    const int k = __double2loint(shifted);
+    const double kd = shifted - 6755399441055744.0;
+    double r = fma(kd, -6.93147180369123816490e-01, y);
+    r = fma(kd, -1.90821492927058770002e-10, r);
+    double p = 1.6059043836821613e-10;  // 1/13!
+    p = fma(p, r, 2.08767569878681e-09);
+    p = fma(p, r, 2.505210838544172e-08);
+    p = fma(p, r, 2.755731922398589e-07);
+    p = fma(p, r, 2.7557319223985893e-06);
+    p = fma(p, r, 2.48015873015873e-05);
+    p = fma(p, r, 1.984126984126984e-04);
+    p = fma(p, r, 1.388888888888889e-03);
+    p = fma(p, r, 8.333333333333333e-03);
+    p = fma(p, r, 4.1666666666666664e-02);
+    p = fma(p, r, 1.6666666666666666e-01);
+    p = fma(p, r, 0.5);
+    p = fma(p, r, 1.0);
+    p = fma(p, r, 1.0);
+    return __hiloint2double(__double2hiint(p) + (k << 20), __double2loint(p));
 }
 
 // ---- regularised incomplete gamma / beta and their inverses (gamma, erlang, beta priors).

@@ -42,6 +42,71 @@ static int elem_bytes_wire(const ob2_slot_desc &d) {
     return 8;
 }
 
+// The sampler's draw plan (rules: ob2_internal.cuh).  `staged` is the library's copy of the table;
+// `thr` receives the u32 thresholds of every categorical slot (cdf_len entries).
+static int compile_plan(ob2_slot_desc *staged, int n_slots, const double *cdf, ob2_slot_plan *plan, ob2_run *runs,
+                        uint32_t *thr) {
+    int block = 0, word = 0, n_runs = 0;
+    for (int s = 0; s < n_slots; ++s) {
+        ob2_slot_desc &d = staged[s];
+        ob2_slot_plan &p = plan[s];
+        p.irange = 0;
+        p.iloc = 0;
+        p.thr_off = (uint32_t)d.cdf_off;
+        int cls = OB2_CLS_GENERIC;
+        if (d.kind == OB2_KIND_CATEGORICAL) {
+            bool fits = true, exact = true;
+            for (int j = 0; j + 1 < d.n_cats; ++j) {
+                const double v = ceil(cdf[d.cdf_off + j] * 4294967296.0);
+                if (!(v >= 0.0) || v > 4294967295.0) {
+                    fits = false;
+                    break;
+                }
+                thr[d.cdf_off + j] = (uint32_t)v;
+                const uint64_t even = ((((uint64_t)(j + 1)) << 32) + (uint64_t)d.n_cats - 1) / (uint64_t)d.n_cats;
+                exact = exact && even == (uint64_t)v;
+            }
+            if (d.n_cats >= 1) thr[d.cdf_off + d.n_cats - 1] = 0xFFFFFFFFu;  // (never read: cdf = 1 > u)
+            if (fits) cls = exact ? OB2_CLS_CAT_MULHI : OB2_CLS_CAT_TABLE;
+        } else if (d.kind == OB2_KIND_INTEGER) {
+            if (d.dist == OB2_DIST_UNIFORM && d.scale >= 1.0 && d.scale <= 1048576.0 && d.scale == floor(d.scale) &&
+                d.loc == floor(d.loc) && fabs(d.loc) <= 1048576.0 && d.low <= d.loc && d.high >= d.loc + d.scale) {
+                cls = OB2_CLS_INT_MULHI;
+                p.irange = (uint32_t)d.scale;
+                p.iloc = (int32_t)d.loc;
+            }
+        } else if (d.dist == OB2_DIST_UNIFORM) {
+            cls = OB2_CLS_UNIFORM;
+        } else if (d.dist == OB2_DIST_NORM) {
+            cls = OB2_CLS_NORM;
+        }
+        if (d.kind != OB2_KIND_CATEGORICAL && d.dist == OB2_DIST_RECIPROCAL && fabs(d.p0) + fabs(d.p1) < 700.0) {
+            d.flags |= OB2_SLOT_FAST_EXP;
+            if (d.kind == OB2_KIND_REAL) cls = OB2_CLS_RECIP;
+        }
+        const int need = (cls == OB2_CLS_INT_MULHI || cls == OB2_CLS_CAT_MULHI || cls == OB2_CLS_CAT_TABLE) ? 1 : 2;
+        if (need == 2 && (word & 1)) ++word;
+        if (word + need > 4) {
+            ++block;
+            word = 0;
+        }
+        if (block > 0xFFFF) return -1;
+        p.block = (uint16_t)block;
+        p.word = (uint8_t)word;
+        p.cls = (uint8_t)cls;
+        word += need;
+        if (n_runs > 0 && runs[n_runs - 1].cls == (uint32_t)cls && runs[n_runs - 1].count < 0xFFFF) {
+            ++runs[n_runs - 1].count;
+        } else {
+            runs[n_runs].first = (uint16_t)s;
+            runs[n_runs].count = 1;
+            runs[n_runs].cls = (uint32_t)cls;
+            ++n_runs;
+        }
+    }
+    return n_runs;
+}
+
 extern "C" int ob2_space_create(const ob2_slot_desc *slots, int32_t n_slots, const double *cdf,
                                 int32_t cdf_len, ob2_space **out) {
     if (out == nullptr || slots == nullptr || n_slots <= 0 || cdf_len < 0 || (cdf_len > 0 && cdf == nullptr)) {

@@ -118,7 +118,7 @@ def test_static_scratch_dedup_leaves_free_device_memory_untouched():
     from orion_b200 import _lib
     lib = _lib.load()
     rng = np.random.RandomState(7)
-    hist = _twin_histories(1 << 16, _fingerprints(rng, 1000))[1]       # ob2_set_create: module load + look-up
+    hist = _twin_histories(1 << 18, _fingerprints(rng, 1000))[1]       # ob2_set_create: module load + look-up
     n = 20000
     fps = [torch.from_numpy(_fingerprints(rng, n)).cuda() for _ in range(3)]
     keep = torch.zeros(n, dtype=torch.uint8, device='cuda')            # every buffer exists before measuring
