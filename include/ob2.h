@@ -117,6 +117,11 @@ int ob2_version(void);
 int ob2_space_create(const ob2_slot_desc *slots, int32_t n_slots, const double *cdf,
                      int32_t cdf_len, ob2_space **out);
 void ob2_space_destroy(ob2_space *space);
+/* Philox round count of the sampler for this space: 10 (default, Philox4x32-10 as published) or 7
+ * (Philox4x32-7, the smallest variant that passes BigCrush; ~5 % fewer instructions per
+ * candidate).  Different rounds = different draws for the same seed.  No counterpart in the
+ * reference (numpy's MT19937, src/orion/algo/space.py:482). */
+int ob2_space_set_philox_rounds(ob2_space *space, int32_t rounds);
 int64_t ob2_space_row_bytes(const ob2_space *space);  /* bytes per candidate, original set   */
 int64_t ob2_space_trow_bytes(const ob2_space *space); /* bytes per candidate, transformed set */
 /* The "wire" layout used to hand candidates to the host (ob2_compact_wire): same columnar
@@ -132,9 +137,16 @@ int ob2_space_wire_layout(const ob2_space *space, int32_t *units, int32_t *elem_
  * <=4-attempt rejection (space.py:256-276), _Discrete.sample's floor
  * (space.py:281-294) and Categorical.sample (space.py:392-402), as called by
  * Random.suggest (src/orion/algo/random.py:24-33).  Uniforms come from
- * Philox4x32-10: counter (index_lo, index_hi, slot >> 1, attempt), key = seed,
+ * Philox4x32: key = seed, counter (index_lo, index_hi, block, attempt) with
  * candidate index = base_index + i, or index[i] when `index` (device u64[n],
- * nullable) is given -- replaying chosen candidates from their counters.
+ * nullable) is given -- replaying chosen candidates from their counters.  Walking
+ * the slots in order, a slot takes the next free words of the current block: two
+ * (starting at an even word) for a 53-bit uniform ((w0 >> 5) 2^26 + (w1 >> 6)) / 2^53,
+ * or ONE for a 32-bit uniform w / 2^32 where that is all the slot needs -- a
+ * Categorical slot whose cdf thresholds ceil(cdf[j] 2^32) fit 32 bits, and an Integer
+ * slot with a uniform prior, integral loc / scale, 1 <= scale <= 2^20, |loc| <= 2^20 and
+ * no narrower user bounds (there floor(u scale + loc) is exact in integers).  A space
+ * of Real slots only uses block = slot / 2.
  * `mask[i]` (nullable) is the fused
  * `point in space` of PrimaryAlgo.suggest (src/orion/core/worker/primary_algo.py:53-54);
  * `fp` (nullable, [n_stride][2] u64) receives the row fingerprints;

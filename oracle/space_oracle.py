@@ -59,8 +59,8 @@ PHILOX_W0 = 0x9E3779B9
 PHILOX_W1 = 0xBB67AE85
 
 
-def philox4x32_10(c0, c1, c2, c3, k0, k1):
-    """Vectorised Philox4x32-10.  All inputs broadcastable uint32 arrays."""
+def philox4x32_10(c0, c1, c2, c3, k0, k1, rounds=10):
+    """Vectorised Philox4x32-10 (or -7 with ``rounds=7``).  All inputs broadcastable uint32 arrays."""
     c0 = np.asarray(c0, dtype=U64)
     c1 = np.asarray(c1, dtype=U64)
     c2 = np.asarray(c2, dtype=U64)
@@ -70,7 +70,7 @@ def philox4x32_10(c0, c1, c2, c3, k0, k1):
     k1 = int(k1) & 0xFFFFFFFF
     mask = U64(0xFFFFFFFF)
     sh = U64(32)
-    for _ in range(10):
+    for _ in range(rounds):
         p0 = U64(PHILOX_M0) * c0
         p1 = U64(PHILOX_M1) * c2
         hi0, lo0 = p0 >> sh, p0 & mask
@@ -92,20 +92,29 @@ def u53(w0, w1):
     return (a * 67108864.0 + b) / 9007199254740992.0
 
 
-def philox_uniform(seed: int, index, slot: int, attempt: int = 0):
-    """Uniform for (candidate ``index``, scalar slot ``slot``, ``attempt``).
+def philox_uniform(seed: int, index, slot, attempt: int = 0, rounds: int = 10):
+    """Uniform for (candidate ``index``, scalar slot, ``attempt``).
 
-    Counter = (index_lo, index_hi, slot >> 1, attempt), key = (seed_lo,
-    seed_hi).  Even slots take words 0,1 of the block, odd slots words 2,3.
+    Counter = (index_lo, index_hi, block, attempt), key = (seed_lo, seed_hi).
+    ``slot`` is either a plan entry ``(block, word, bits)`` from
+    :func:`draw_plan` -- ``bits == 53``: words (word, word + 1) of the block
+    through :func:`u53`; ``bits == 32``: the one word, ``w / 2**32`` -- or a
+    bare slot number of an all-53-bit space (block = slot // 2, even slots take
+    words 0,1 and odd slots words 2,3: the layout :func:`draw_plan` gives a space
+    of Real dimensions).
     """
+    if isinstance(slot, tuple):
+        block, word, bits = slot
+    else:
+        block, word, bits = slot >> 1, 2 * (slot & 1), 53
     index = np.asarray(index, dtype=U64)
     ilo = (index & U64(0xFFFFFFFF)).astype(U32)
     ihi = (index >> U64(32)).astype(U32)
-    r = philox4x32_10(ilo, ihi, U32(slot >> 1), U32(attempt),
-                      seed & 0xFFFFFFFF, (seed >> 32) & 0xFFFFFFFF)
-    if slot & 1:
-        return u53(r[2], r[3])
-    return u53(r[0], r[1])
+    r = philox4x32_10(ilo, ihi, U32(block), U32(attempt),
+                      seed & 0xFFFFFFFF, (seed >> 32) & 0xFFFFFFFF, rounds=rounds)
+    if bits == 32:
+        return r[word].astype(np.float64) * 2.0 ** -32
+    return u53(r[word], r[word + 1])
 
 
 # --------------------------------------------------------------------------
@@ -176,6 +185,47 @@ def slot_table(specs: Sequence[DimSpec]) -> List[Tuple[int, int]]:
         for e in range(spec.n_slots):
             out.append((d, e))
     return out
+
+
+def uses_32_bit_uniform(spec: "DimSpec") -> bool:
+    """Slots for which a 32-bit uniform ``w / 2**32`` is all the draw needs (the
+    library's rule, ``orion_b200/csrc/ob2_internal.cuh``):
+
+    * Categorical whose thresholds ``ceil(cdf[j] * 2**32)``, j < k - 1, are all below
+      ``2**32`` (then ``cdf[j] <= u  <=>  ceil(cdf[j] 2**32) <= w`` -- an integer test);
+    * Integer with a uniform prior, integral ``loc`` and ``scale``, ``1 <= scale <= 2**20``,
+      ``|loc| <= 2**20``, and no user bounds inside ``[loc, loc + scale)``: there
+      ``u * scale + loc`` is exact in double precision, so its floor is
+      ``loc + ((w * scale) >> 32)`` and always in bounds.
+    """
+    if spec.kind == 'categorical':
+        cdf = categorical_cdf(spec.probs)
+        return bool(np.all(np.ceil(cdf[:-1] * 4294967296.0) <= 4294967295.0))
+    if spec.kind == 'integer' and spec.prior == 'uniform':
+        _dist, _args, loc, scale = _parse(spec)
+        lo, hi = dim_interval(spec)
+        return bool(1.0 <= scale <= 2.0 ** 20 and scale == np.floor(scale) and loc == np.floor(loc) and
+                    abs(loc) <= 2.0 ** 20 and lo <= loc and hi >= loc + scale)
+    return False
+
+
+def draw_plan(specs: Sequence["DimSpec"]) -> List[Tuple[int, int, int]]:
+    """Per scalar slot ``(block, word, bits)``: which words of which Philox block it consumes.
+    Walking the slots in order, a slot takes the next free words of the current block: two,
+    starting at an even word, for a 53-bit uniform; one for a 32-bit uniform
+    (:func:`uses_32_bit_uniform`); a new block when the current one cannot hold them."""
+    plan = []
+    block = word = 0
+    for d, _e in slot_table(specs):
+        need = 1 if uses_32_bit_uniform(specs[d]) else 2
+        if need == 2 and (word & 1):
+            word += 1
+        if word + need > 4:
+            block += 1
+            word = 0
+        plan.append((block, word, 32 if need == 1 else 53))
+        word += need
+    return plan
 
 
 CLOSED_FORM_PRIORS = ('expon', 'lognorm', 'logistic', 'laplace', 'gumbel_r', 'weibull_min', 'pareto',
@@ -281,11 +331,12 @@ def replay_reference_stream(specs: Sequence[DimSpec], n: int, stream: np.ndarray
     return cols, pos
 
 
-def sample_philox(specs: Sequence[DimSpec], n: int, seed: int, base_index: int = 0):
+def sample_philox(specs: Sequence[DimSpec], n: int, seed: int, base_index: int = 0, rounds: int = 10):
     """Philox-mode draw with the reference's <=4-attempt rejection.
 
     Attempt ``a`` of dimension ``d`` for candidate ``i`` uses
-    ``philox_uniform(seed, i, slot, a)`` for each of the dimension's slots; the
+    ``philox_uniform(seed, i, plan[slot], a)`` for each of the dimension's slots
+    (``plan`` = :func:`draw_plan`); the
     whole dimension value is accepted iff every element is in bounds
     (space.py:263-270).  Returns (columns, failed[N]); a True in ``failed`` is
     the reference's ValueError("Improbable bounds").
@@ -293,6 +344,7 @@ def sample_philox(specs: Sequence[DimSpec], n: int, seed: int, base_index: int =
     index = np.arange(n, dtype=U64) + U64(base_index)
     cols: List[np.ndarray] = []
     failed = np.zeros(n, dtype=bool)
+    plan = draw_plan(specs)
     s0 = 0
     for spec in specs:
         k = spec.n_slots
@@ -307,7 +359,7 @@ def sample_philox(specs: Sequence[DimSpec], n: int, seed: int, base_index: int =
             vals = []
             ok = np.ones(rows.size, dtype=bool)
             for e in range(k):
-                u = philox_uniform(seed, index[rows], s0 + e, a)
+                u = philox_uniform(seed, index[rows], plan[s0 + e], a, rounds)
                 x = _draw(spec, u)
                 vals.append(x)
                 if spec.kind != 'categorical':

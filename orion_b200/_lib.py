@@ -57,6 +57,7 @@ SIGNATURES = {
     'ob2_space_create': (ctypes.c_int, [ctypes.POINTER(SlotDesc), _i32, ctypes.POINTER(ctypes.c_double), _i32,
                                         ctypes.POINTER(_vp)]),
     'ob2_space_destroy': (None, [_vp]),
+    'ob2_space_set_philox_rounds': (ctypes.c_int, [_vp, _i32]),
     'ob2_space_row_bytes': (_i64, [_vp]),
     'ob2_space_trow_bytes': (_i64, [_vp]),
     'ob2_sample': (ctypes.c_int, [_vp, _i64, _i64, _u64, _u64, _vp, _vp, _vp, _vp, _vp, _vp]),

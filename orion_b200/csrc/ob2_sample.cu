@@ -34,7 +34,7 @@ __device__ __forceinline__ long long quantize_ll(double x, int t_flags) {
 // Categorical draw = #{j : cdf[j] <= u}.  With equal probabilities floor(u * k)
 // is within one of the answer, so start there and walk to the exact index
 // (exact for ANY non-decreasing cdf; the guess only decides how far the walk is).
-// Otherwise the branch-free descent.
+// Otherwise the branch-free descent.  (53-bit / injected uniforms.)
 __device__ __forceinline__ int draw_cat_fast(const double *cdf, int k, double u, bool uniform) {
     if (!uniform) return draw_cat(cdf, k, u);
     int idx = __double2int_rz(u * (double)k);
@@ -44,18 +44,51 @@ __device__ __forceinline__ int draw_cat_fast(const double *cdf, int k, double u,
     return idx;
 }
 
+// The same count on a 32-bit word w (u = w / 2^32) against the integer thresholds
+// thr[j] = ceil(cdf[j] * 2^32), j < k - 1:  cdf[j] <= u  <=>  thr[j] <= w.
+__device__ __forceinline__ int draw_cat_u32(const uint32_t *thr, int k, uint32_t w, bool uniform) {
+    const int m = k - 1;  // thresholds that can be met (cdf[k - 1] = 1 > u)
+    if (uniform) {
+        int idx = min((int)__umulhi(w, (uint32_t)k), m);
+        while (idx > 0 && thr[idx - 1] > w) --idx;
+        while (idx < m && thr[idx] <= w) ++idx;
+        return idx;
+    }
+    int lo = 0;
+    if (m <= 0) return 0;
+    for (int step = 1 << (31 - __clz(m)); step > 0; step >>= 1) {
+        const int probe = lo + step;
+        const int at = probe <= m ? probe : m;
+        const bool take = (probe <= m) && (thr[at - 1] <= w);
+        lo = take ? probe : lo;
+    }
+    return lo;
+}
+
+__device__ __forceinline__ uint32_t pick_word(const Philox4 &r, uint32_t word) {
+    return word == 0 ? r.x : word == 1 ? r.y : word == 2 ? r.z : r.w;
+}
+
 // Real.sample (space.py:263-270): a draw of dimension [first, s_last] landed
 // outside [low, high): redraw the whole (possibly shaped) value for candidate i,
 // attempts 1..3, overwriting its columns with scalar stores.  Rare path, inlined
 // in a cold branch of the walk: the hot loop carries no redraw state at all --
 // the fingerprint lanes are wrapping sums, so the contribution of the rejected
 // values (read back from the columns this thread just wrote) is subtracted and
-// the redrawn one added.
+// the redrawn one added.  Only slots drawn from a 53-bit uniform can miss their
+// bounds (the 32-bit classes are in bounds by construction), so every slot here
+// takes words (0, 1) or (2, 3) of its block.
 // WITH_B: the fingerprint is over the handed-out row (`back`, at cols + bdelta), which is also rewritten.
-template <bool WITH_FP, bool WITH_T, bool WITH_B, bool EXT>
-__device__ __forceinline__ bool redraw_dim(const ob2_slot_desc *s_slots, int s_last, uint64_t index, int64_t i,
-                                           int64_t n_stride, char *cols, char *tcols, int64_t bdelta, uint32_t k0,
-                                           uint32_t k1, uint32_t pm0, uint32_t pm1, FpAcc &acc) {
+struct Redrawn {
+    FpAcc acc;  // the candidate's fingerprint lanes with the rejected contribution replaced
+    bool ok;
+};
+// (out of line, and everything by value: a reference into the walk state would pin it in local memory)
+template <bool WITH_FP, bool WITH_T, bool WITH_B, bool EXT, int ROUNDS>
+static __device__ __noinline__ Redrawn redraw_dim(const ob2_slot_desc *s_slots, const ob2_slot_plan *s_plan, int s_last,
+                                                  uint64_t index, int64_t i, int64_t n_stride, char *cols, char *tcols,
+                                                  int64_t bdelta, uint32_t k0, uint32_t k1, uint32_t pm0, uint32_t pm1,
+                                                  FpAcc acc) {
     const int first = s_slots[s_last].dim_first;
     if (WITH_FP) {
         FpAcc old{0, 0};
@@ -77,9 +110,10 @@ __device__ __forceinline__ bool redraw_dim(const ob2_slot_desc *s_slots, int s_l
         t = FpAcc{0, 0};
         for (int e = first; e <= s_last; ++e) {
             const ob2_slot_desc &d = s_slots[e];
-            const Philox4 r = philox4x32_10((uint32_t)index, (uint32_t)(index >> 32), (uint32_t)(e >> 1), a, k0, k1, pm0, pm1);
-            const double u = (e & 1) ? u53(r.z, r.w) : u53(r.x, r.y);
-            double x = draw_real<EXT>(d, u);
+            const Philox4 r = philox4x32<ROUNDS>((uint32_t)index, (uint32_t)(index >> 32), (uint32_t)s_plan[e].block, a,
+                                                 k0, k1, pm0, pm1);
+            const double u = s_plan[e].word ? u53(r.z, r.w) : u53(r.x, r.y);
+            double x = draw_real_call(d, u);
             char *col = cols + (int64_t)d.col_units * n_stride;
             char *dst = tcols + (int64_t)d.t_units * n_stride;
             uint64_t w;
@@ -103,9 +137,9 @@ __device__ __forceinline__ bool redraw_dim(const ob2_slot_desc *s_slots, int s_l
                 double bx = x;
                 if (WITH_T) {
                     if (d.t_op == OB2_OP_QUANTIZE) {
-                        const long long t = quantize_ll(x, d.t_flags);
-                        reinterpret_cast<long long *>(dst)[i] = t;
-                        bx = __ll2double_rn(t);
+                        const long long tq = quantize_ll(x, d.t_flags);
+                        reinterpret_cast<long long *>(dst)[i] = tq;
+                        bx = __ll2double_rn(tq);
                     } else {
                         reinterpret_cast<double *>(dst)[i] = x;
                     }
@@ -121,39 +155,322 @@ __device__ __forceinline__ bool redraw_dim(const ob2_slot_desc *s_slots, int s_l
         acc.a += t.a;
         acc.b += t.b;
     }
-    return ok;
+    return Redrawn{acc, ok};
+}
+
+// Per-thread state of the slot walk (two candidates).  Column pointers are running pointers
+// advanced by 4 * n_stride / 8 * n_stride; the fingerprint accumulates straight into its lanes.
+struct Walk {
+    FpAcc acc0, acc1;
+    bool ok0, ok1;    // current dimension
+    bool all0, all1;  // whole candidate
+    char *col;        // element i0 of the current column (a 4-byte column is addressed at half the offset)
+    char *tcol;
+    Philox4 r0, r1;   // the current Philox block of the two candidates
+};
+
+struct WalkConst {  // loop invariants
+    int64_t i0, n_stride, stride4, stride8, bdelta;
+    bool split, has1;
+    uint64_t idx0, idx1;
+    uint32_t k0, k1, pm0, pm1;
+    char *cols, *tcols;
+    uint32_t *n_failed;
+};
+
+// ---- what a drawn pair of values costs downstream: stores (sampled / transformed / handed-out), the
+// fingerprint and the bounds bit.  WITH_B: reverse() of the transformed value, evaluated on what is stored.
+template <bool WITH_FP, bool WITH_T, bool WITH_B>
+__device__ __forceinline__ void emit_real(const ob2_slot_desc &d, double x0, double x1, Walk &w, const WalkConst &c) {
+    st_f64x2(reinterpret_cast<double *>(w.col), x0, x1);
+    double bx0 = x0, bx1 = x1;
+    if (WITH_T) {
+        if (d.t_op == OB2_OP_QUANTIZE) {
+            const long long t0 = quantize_ll(x0, d.t_flags), t1 = quantize_ll(x1, d.t_flags);
+            st_i64x2(reinterpret_cast<long long *>(w.tcol), t0, t1);
+            if (WITH_B) {
+                bx0 = __ll2double_rn(t0);
+                bx1 = __ll2double_rn(t1);
+            }
+        } else {
+            st_f64x2(reinterpret_cast<double *>(w.tcol), x0, x1);
+        }
+        w.tcol += c.stride8;
+    }
+    // (aliased: only a lossy Quantize round trip differs from what was just stored)
+    if (WITH_B && (c.split || d.t_op == OB2_OP_QUANTIZE)) st_f64x2(reinterpret_cast<double *>(w.col + c.bdelta), bx0, bx1);
+    if (WITH_FP) {
+        fp_add(w.acc0, d, canon_f64(bx0));
+        fp_add(w.acc1, d, canon_f64(bx1));
+    }
+    w.col += c.stride8;
+    w.ok0 &= (x0 >= d.low) & (x0 < d.high);  // half-open, space.py:164
+    w.ok1 &= (x1 >= d.low) & (x1 < d.high);
+}
+
+// Integer slot from the floored double (general priors)
+template <bool WITH_FP, bool WITH_T, bool WITH_B>
+__device__ __forceinline__ void emit_int_f(const ob2_slot_desc &d, double x0, double x1, Walk &w, const WalkConst &c) {
+    const long long q0 = __double2ll_rz(x0), q1 = __double2ll_rz(x1);
+    st_i64x2(reinterpret_cast<long long *>(w.col), q0, q1);
+    long long bq0 = q0, bq1 = q1;
+    if (WITH_T) {
+        if (d.t_op == OB2_OP_TO_REAL) {  // the floored double is exactly (double)q
+            st_f64x2(reinterpret_cast<double *>(w.tcol), x0, x1);
+            if (WITH_B) {  // Reverse(Quantize).reverse = Quantize.transform of the stored double
+                bq0 = quantize_ll(x0, d.t_flags);
+                bq1 = quantize_ll(x1, d.t_flags);
+            }
+        } else {
+            st_i64x2(reinterpret_cast<long long *>(w.tcol), q0, q1);
+        }
+        w.tcol += c.stride8;
+    }
+    if (WITH_B && c.split) st_i64x2(reinterpret_cast<long long *>(w.col + c.bdelta), bq0, bq1);
+    if (WITH_FP) {
+        fp_add(w.acc0, d, (uint64_t)bq0);
+        fp_add(w.acc1, d, (uint64_t)bq1);
+    }
+    w.col += c.stride8;
+    w.ok0 &= (x0 >= d.low) & (x0 < d.high);
+    w.ok1 &= (x1 >= d.low) & (x1 < d.high);
+}
+
+// Integer slot from the exact integer (OB2_CLS_INT_MULHI: |q| < 2^21, in bounds by construction;
+// the cast to double and the Quantize of it back are exact, so the handed-out value is q itself)
+template <bool WITH_FP, bool WITH_T, bool WITH_B>
+__device__ __forceinline__ void emit_int_q(const ob2_slot_desc &d, int v0, int v1, Walk &w, const WalkConst &c) {
+    const long long q0 = v0, q1 = v1;
+    st_i64x2(reinterpret_cast<long long *>(w.col), q0, q1);
+    if (WITH_T) {
+        if (d.t_op == OB2_OP_TO_REAL) {
+            st_f64x2(reinterpret_cast<double *>(w.tcol), __int2double_rn(v0), __int2double_rn(v1));
+        } else {
+            st_i64x2(reinterpret_cast<long long *>(w.tcol), q0, q1);
+        }
+        w.tcol += c.stride8;
+    }
+    if (WITH_B && c.split) st_i64x2(reinterpret_cast<long long *>(w.col + c.bdelta), q0, q1);
+    if (WITH_FP) {
+        fp_add(w.acc0, d, (uint64_t)q0);
+        fp_add(w.acc1, d, (uint64_t)q1);
+    }
+    w.col += c.stride8;
+}
+
+template <bool WITH_FP, bool WITH_T, bool WITH_B>
+__device__ __forceinline__ void emit_cat(const ob2_slot_desc &d, int c0, int c1, Walk &w, const WalkConst &c) {
+    st_i32x2(reinterpret_cast<int *>(w.col - c.i0 * 4), c0, c1);
+    int *bcol = reinterpret_cast<int *>(w.col - c.i0 * 4 + c.bdelta);
+    w.col += c.stride4;
+    int b0 = c0, b1 = c1;  // WITH_B: reverse() of the transformed value, evaluated on what is stored
+    if (WITH_T) {
+        if (d.t_op != OB2_OP_ONEHOT) {  // Enumerate / Identity: the index both ways
+            st_i32x2(reinterpret_cast<int *>(w.tcol - c.i0 * 4), c0, c1);
+            w.tcol += c.stride4;
+        } else if (d.t_width == 1) {
+            const double t0 = (double)c0, t1 = (double)c1;
+            st_f64x2(reinterpret_cast<double *>(w.tcol), t0, t1);
+            w.tcol += c.stride8;
+            if (WITH_B) {  // k == 2: (v > 0.5); k == 1: always category 0
+                b0 = (d.n_cats == 2 && t0 > 0.5) ? 1 : 0;
+                b1 = (d.n_cats == 2 && t1 > 0.5) ? 1 : 0;
+            }
+        } else {
+            // column j is at tcol + j * stride8; the launcher guarantees stride8 < 2^32,
+            // so each address is ONE 32x32+64 multiply-add (IMAD.WIDE.U32)
+            const uint32_t s8 = (uint32_t)c.stride8, k = (uint32_t)d.t_width;
+            // WITH_B: reverse_kernel's argmax (first maximum) over these k values is the position
+            // of the single 1.0 stored below, i.e. the index itself: the Philox draw is always in
+            // [0, k).  Tracking the maximum while storing (tried: 6 more instructions per column
+            // pair) costs the kernel 4.5 % for the same bytes, so the identity is used; the staged
+            // kernels and tests/test_gpu_suggest_fused.py hold it to account.
+#pragma unroll 4
+            for (uint32_t j = 0; j < k; ++j) {
+                const unsigned h0 = c0 == (int)j ? 0x3FF00000u : 0u, h1 = c1 == (int)j ? 0x3FF00000u : 0u;
+                st_onehot_hi(reinterpret_cast<double *>(w.tcol + (uint64_t)j * s8), h0, h1);
+            }
+            w.tcol += (uint64_t)k * s8;
+        }
+    }
+    if (WITH_B && c.split) st_i32x2(bcol, b0, b1);
+    if (WITH_FP) {
+        fp_add(w.acc0, d, (uint64_t)(int64_t)b0);
+        fp_add(w.acc1, d, (uint64_t)(int64_t)b1);
+    }
+}
+
+// End of a dimension whose slots can miss their bounds: the <= 4-attempt redraw (cold).
+template <bool PHILOX, bool WITH_FP, bool WITH_T, bool WITH_B, bool EXT, int ROUNDS>
+__device__ __forceinline__ void dim_end(const ob2_slot_desc *s_slots, const ob2_slot_plan *s_plan, int s, Walk &w,
+                                        const WalkConst &c) {
+    if (!(s_slots[s].flags & OB2_SLOT_DIM_LAST)) return;
+    if (!(w.ok0 & w.ok1)) {  // cold: only Real/Integer slots can clear ok
+        if (PHILOX) {
+            if (!w.ok0) {
+                const Redrawn rd = redraw_dim<WITH_FP, WITH_T, WITH_B, EXT, ROUNDS>(
+                    s_slots, s_plan, s, c.idx0, c.i0, c.n_stride, c.cols, c.tcols, c.bdelta, c.k0, c.k1, c.pm0, c.pm1, w.acc0);
+                w.acc0 = rd.acc;
+                w.ok0 = rd.ok;
+            }
+            if (!w.ok1) {
+                const Redrawn rd = redraw_dim<WITH_FP, WITH_T, WITH_B, EXT, ROUNDS>(
+                    s_slots, s_plan, s, c.idx1, c.i0 + 1, c.n_stride, c.cols, c.tcols, c.bdelta, c.k0, c.k1, c.pm0, c.pm1, w.acc1);
+                w.acc1 = rd.acc;
+                w.ok1 = rd.ok;
+            }
+            if (c.n_failed != nullptr) {  // 4 misses: the reference raises "Improbable bounds"
+                const unsigned bad = (w.ok0 ? 0u : 1u) + ((w.ok1 || !c.has1) ? 0u : 1u);
+                if (bad) atomicAdd(c.n_failed + s_slots[s].dim_first, bad);
+            }
+        }
+        w.all0 &= w.ok0;
+        w.all1 &= w.ok1;
+        w.ok0 = w.ok1 = true;
+    }
+}
+
+// One slot through the general prior switch, from a pair of double uniforms (injected uniforms,
+// and in Philox mode the slots no specialised run takes: further priors, Integer over a real prior,
+// constants, categoricals whose thresholds do not fit 32 bits).
+template <bool PHILOX, bool WITH_FP, bool WITH_T, bool WITH_B, bool EXT, int ROUNDS>
+__device__ __forceinline__ void generic_slot(const ob2_slot_desc *s_slots, const ob2_slot_plan *s_plan, const double *s_cdf,
+                                             int s, double u0, double u1, Walk &w, const WalkConst &c) {
+    const ob2_slot_desc &d = s_slots[s];
+    if (d.kind == OB2_KIND_CATEGORICAL) {
+        const double *cdf = s_cdf + d.cdf_off;
+        const bool uni = (d.flags & OB2_SLOT_CAT_UNIFORM) != 0;
+        const int c0 = draw_cat_fast(cdf, d.n_cats, u0, uni);
+        const int c1 = draw_cat_fast(cdf, d.n_cats, u1, uni);
+        emit_cat<WITH_FP, WITH_T, WITH_B>(d, c0, c1, w, c);
+        if (!PHILOX) {  // an injected u >= 1 can run off the table; a Philox u cannot
+            w.ok0 &= c0 < d.n_cats;
+            w.ok1 &= c1 < d.n_cats;
+        }
+    } else {
+        double x0 = draw_real_call(d, u0);
+        double x1 = draw_real_call(d, u1);
+        if (d.kind == OB2_KIND_INTEGER) {
+            x0 = floor(x0);  // _Discrete.sample, space.py:294
+            x1 = floor(x1);
+            emit_int_f<WITH_FP, WITH_T, WITH_B>(d, x0, x1, w, c);
+        } else {
+            emit_real<WITH_FP, WITH_T, WITH_B>(d, x0, x1, w, c);
+        }
+    }
+    dim_end<PHILOX, WITH_FP, WITH_T, WITH_B, EXT, ROUNDS>(s_slots, s_plan, s, w, c);
+}
+
+// The Philox block `blk` of both candidates (attempt 0).
+template <int ROUNDS>
+__device__ __forceinline__ void new_block(uint32_t blk, Walk &w, const WalkConst &c) {
+    w.r0 = philox4x32<ROUNDS>((uint32_t)c.idx0, (uint32_t)(c.idx0 >> 32), blk, 0u, c.k0, c.k1, c.pm0, c.pm1);
+    w.r1 = philox4x32<ROUNDS>((uint32_t)c.idx1, (uint32_t)(c.idx1 >> 32), blk, 0u, c.k0, c.k1, c.pm0, c.pm1);
+}
+
+// ---- a run of Real slots of one prior off 53-bit uniforms: words (0, 1) then (2, 3) of a block
+template <int CLS, bool WITH_FP, bool WITH_T, bool WITH_B, bool EXT, int ROUNDS>
+__device__ __forceinline__ void real_slot(const ob2_slot_desc *s_slots, const ob2_slot_plan *s_plan, int e, double u0,
+                                          double u1, Walk &w, const WalkConst &c) {
+    const ob2_slot_desc &d = s_slots[e];
+    double b0, b1;
+    if (CLS == OB2_CLS_UNIFORM) {
+        b0 = u0;
+        b1 = u1;
+    } else if (CLS == OB2_CLS_RECIP) {
+        b0 = ob2_exp_bounded(__dadd_rn(d.p0, __dmul_rn(u0, d.p1)));
+        b1 = ob2_exp_bounded(__dadd_rn(d.p0, __dmul_rn(u1, d.p1)));
+    } else {
+        b0 = ob2_ndtri(u0);
+        b1 = ob2_ndtri(u1);
+    }
+    // base(u) * scale + loc, rounded multiply then rounded add (scipy rv_generic.rvs)
+    emit_real<WITH_FP, WITH_T, WITH_B>(d, __dadd_rn(__dmul_rn(b0, d.scale), d.loc), __dadd_rn(__dmul_rn(b1, d.scale), d.loc),
+                                       w, c);
+    dim_end<true, WITH_FP, WITH_T, WITH_B, EXT, ROUNDS>(s_slots, s_plan, e, w, c);
+}
+
+template <int CLS, bool WITH_FP, bool WITH_T, bool WITH_B, bool EXT, int ROUNDS>
+__device__ __forceinline__ void run_real(const ob2_slot_desc *s_slots, const ob2_slot_plan *s_plan, int s, int end,
+                                         Walk &w, const WalkConst &c) {
+    // ONE copy of the slot body (the loguniform / normal ones are long): the slot's words are selected
+    // by its position in the block, a warp-uniform predicate
+#pragma unroll 1
+    for (; s < end; ++s) {
+        const bool first = s_plan[s].word == 0;
+        if (first) new_block<ROUNDS>(s_plan[s].block, w, c);
+        const double u0 = first ? u53(w.r0.x, w.r0.y) : u53(w.r0.z, w.r0.w);
+        const double u1 = first ? u53(w.r1.x, w.r1.y) : u53(w.r1.z, w.r1.w);
+        real_slot<CLS, WITH_FP, WITH_T, WITH_B, EXT, ROUNDS>(s_slots, s_plan, s, u0, u1, w, c);
+    }
+}
+
+// ---- a run of slots that take one 32-bit word each: four share a block; integer arithmetic only,
+// in bounds by construction (no bounds bit, no redraw)
+template <int CLS, bool WITH_FP, bool WITH_T, bool WITH_B>
+__device__ __forceinline__ void word_slot(const ob2_slot_desc *s_slots, const ob2_slot_plan *s_plan, const uint32_t *s_thr,
+                                          int e, uint32_t w0, uint32_t w1, Walk &w, const WalkConst &c) {
+    const ob2_slot_desc &d = s_slots[e];
+    if (CLS == OB2_CLS_INT_MULHI) {
+        const uint32_t range = s_plan[e].irange;
+        const int loc = s_plan[e].iloc;
+        emit_int_q<WITH_FP, WITH_T, WITH_B>(d, loc + (int)__umulhi(w0, range), loc + (int)__umulhi(w1, range), w, c);
+    } else if (CLS == OB2_CLS_CAT_MULHI) {
+        const uint32_t k = (uint32_t)d.n_cats;
+        emit_cat<WITH_FP, WITH_T, WITH_B>(d, (int)__umulhi(w0, k), (int)__umulhi(w1, k), w, c);
+    } else {
+        const uint32_t *thr = s_thr + s_plan[e].thr_off;
+        const bool uni = (d.flags & OB2_SLOT_CAT_UNIFORM) != 0;
+        emit_cat<WITH_FP, WITH_T, WITH_B>(d, draw_cat_u32(thr, d.n_cats, w0, uni), draw_cat_u32(thr, d.n_cats, w1, uni), w, c);
+    }
+}
+
+template <int CLS, bool WITH_FP, bool WITH_T, bool WITH_B, int ROUNDS>
+__device__ __forceinline__ void run_words(const ob2_slot_desc *s_slots, const ob2_slot_plan *s_plan, int s, int end,
+                                          Walk &w, const WalkConst &c, const uint32_t *s_thr) {
+    while (s < end) {
+        const uint32_t word = s_plan[s].word;
+        if (word == 0) new_block<ROUNDS>(s_plan[s].block, w, c);
+        if (word == 0 && s + 4 <= end) {  // the next three slots own words 1, 2, 3
+            word_slot<CLS, WITH_FP, WITH_T, WITH_B>(s_slots, s_plan, s_thr, s, w.r0.x, w.r1.x, w, c);
+            word_slot<CLS, WITH_FP, WITH_T, WITH_B>(s_slots, s_plan, s_thr, s + 1, w.r0.y, w.r1.y, w, c);
+            word_slot<CLS, WITH_FP, WITH_T, WITH_B>(s_slots, s_plan, s_thr, s + 2, w.r0.z, w.r1.z, w, c);
+            word_slot<CLS, WITH_FP, WITH_T, WITH_B>(s_slots, s_plan, s_thr, s + 3, w.r0.w, w.r1.w, w, c);
+            s += 4;
+        } else {
+            word_slot<CLS, WITH_FP, WITH_T, WITH_B>(s_slots, s_plan, s_thr, s, pick_word(w.r0, word), pick_word(w.r1, word), w, c);
+            ++s;
+        }
+    }
 }
 
 // pm0 / pm1 are the Philox multipliers, passed as kernel parameters so that the
 // multiplies read them straight from the constant bank.
 //
-// Hot-loop economy (the kernel is issue bound): column pointers are running
-// pointers advanced by 4*n_stride / 8*n_stride instead of being recomputed from
-// the descriptor; the fingerprint accumulates straight into its lanes; the
-// second candidate of a trailing odd pair replays the first (no `has1` tests
-// until the final stores).
+// The walk is run-specialised (Philox mode): ob2_space_create groups consecutive slots of one
+// draw class into runs (ob2_internal.cuh), and each class has its own tight loop here -- no
+// per-slot switch on kind / prior, a Philox block shared by the 2 (53-bit) or 4 (32-bit) slots
+// that consume it, integer-only arithmetic for the classes that allow it.  The kernel is issue
+// bound on its own (profiles/): every instruction not spent is time.
 //
 // WITH_B (Random.suggest behind PrimaryAlgo, in one pass): also evaluate reverse() on the
 // transformed values while they are still in registers and store the handed-out row to
 // `back` = cols + bdelta (same column layout); the fingerprint is then that of the `back`
-// row, exactly what reverse_kernel<true> computes from the materialised tcols.  Per op:
-// Quantize of the stored double, the cast back of the stored integer and (v > 0.5) for k = 2
-// are evaluated on the transformed value; Identity / Enumerate pass the value through; the
-// argmax over a k > 2 one-hot block is the position of its single 1.0, the drawn index.
+// row, exactly what reverse_kernel<true> computes from the materialised tcols.
 //
-// sample_body is the whole per-thread job.  `s_slots` is either the table staged in shared
-// memory (sample_kernel) or the table passed BY VALUE as a kernel parameter (sample_kernel_p):
-// the parameter lives in the constant bank, so every descriptor field is read with a uniform
-// load into a uniform register and the kind / prior / op branches are known to be warp-uniform
-// (no convergence barriers around them, no per-thread LDS of the descriptors).
-template <bool PHILOX, bool WITH_FP, bool WITH_T, bool WITH_B, bool EXT>
-__device__ __forceinline__ void sample_body(const ob2_slot_desc *s_slots, const double *s_cdf, int n_slots, int64_t n,
-                                            int64_t n_stride, int64_t stride4, int64_t stride8, uint32_t k0,
-                                            uint32_t k1, uint32_t pm0, uint32_t pm1, uint64_t base_index,
-                                            const uint64_t *__restrict__ index, const double *__restrict__ U,
-                                            char *__restrict__ cols, char *__restrict__ tcols, int64_t bdelta,
-                                            uint8_t *__restrict__ mask, uint64_t *__restrict__ fp,
-                                            uint32_t *__restrict__ n_failed) {
+// sample_body is the whole per-thread job.  The tables are either staged in shared memory
+// (sample_kernel) or passed BY VALUE as a kernel parameter (sample_kernel_p): the parameter
+// lives in the constant bank, so every descriptor field is read with a uniform load into a
+// uniform register and the class / op branches are known to be warp-uniform.
+template <bool PHILOX, bool WITH_FP, bool WITH_T, bool WITH_B, bool EXT, int ROUNDS>
+__device__ __forceinline__ void sample_body(const ob2_slot_desc *s_slots, const ob2_slot_plan *s_plan,
+                                            const ob2_run *s_runs, int n_runs, const double *s_cdf,
+                                            const uint32_t *s_thr, int n_slots, int64_t n, int64_t n_stride,
+                                            int64_t stride4, int64_t stride8, uint32_t k0, uint32_t k1, uint32_t pm0,
+                                            uint32_t pm1, uint64_t base_index, const uint64_t *__restrict__ index,
+                                            const double *__restrict__ U, char *__restrict__ cols,
+                                            char *__restrict__ tcols, int64_t bdelta, uint8_t *__restrict__ mask,
+                                            uint64_t *__restrict__ fp, uint32_t *__restrict__ n_failed) {
     const int64_t i0 = ((int64_t)blockIdx.x * OB2_BLOCK + threadIdx.x) * OB2_CPT;
     if (i0 >= n) return;
     const bool has1 = i0 + 1 < n;
@@ -164,201 +481,172 @@ __device__ __forceinline__ void sample_body(const ob2_slot_desc *s_slots, const 
     }
     if (!has1) idx1 = idx0;  // the padding candidate replays its neighbour: always well defined
 
+    WalkConst c;
+    c.i0 = i0;
+    c.n_stride = n_stride;
+    c.stride4 = stride4;  // 4 * n_stride / 8 * n_stride arrive as kernel parameters: the pointer bumps
+    c.stride8 = stride8;  // take them straight from the constant bank
+    c.bdelta = bdelta;
     // back == cols (bdelta == 0): the caller keeps only the handed-out rows; the second store of every
     // value is skipped (reverse(transform(x)) == x bit for bit except through a lossy Quantize)
-    const bool split = WITH_B && bdelta != 0;
-    FpAcc acc0{0, 0}, acc1{0, 0};
-    bool ok0 = true, ok1 = true;    // current dimension
-    bool all0 = true, all1 = true;  // whole candidate
-    Philox4 r0{0, 0, 0, 0}, r1{0, 0, 0, 0};
-    // stride4 / stride8 = 4 * n_stride / 8 * n_stride arrive as kernel parameters: the pointer bumps then
-    // take them straight from the constant bank instead of re-deriving them every slot
-    char *col = cols + i0 * 8;                          // running pointers: element i0 of the current column
-    char *tcol = WITH_T ? tcols + i0 * 8 : nullptr;     // (a 4-byte column is addressed at half the offset)
-    const double *ucol = PHILOX ? nullptr : U + i0;
+    c.split = WITH_B && bdelta != 0;
+    c.has1 = has1;
+    c.idx0 = idx0;
+    c.idx1 = idx1;
+    c.k0 = k0;
+    c.k1 = k1;
+    c.pm0 = pm0;
+    c.pm1 = pm1;
+    c.cols = cols;
+    c.tcols = tcols;
+    c.n_failed = n_failed;
+    Walk w;
+    w.acc0 = w.acc1 = FpAcc{0, 0};
+    w.ok0 = w.ok1 = w.all0 = w.all1 = true;
+    w.col = cols + i0 * 8;
+    w.tcol = WITH_T ? tcols + i0 * 8 : nullptr;
+    w.r0 = w.r1 = Philox4{0, 0, 0, 0};
 
-    for (int s = 0; s < n_slots; ++s) {
-        const ob2_slot_desc &d = s_slots[s];
-        double u0, u1;
-        if (PHILOX) {
-            if ((s & 1) == 0) {
-                r0 = philox4x32_10((uint32_t)idx0, (uint32_t)(idx0 >> 32), (uint32_t)(s >> 1), 0u, k0, k1, pm0, pm1);
-                r1 = philox4x32_10((uint32_t)idx1, (uint32_t)(idx1 >> 32), (uint32_t)(s >> 1), 0u, k0, k1, pm0, pm1);
-                u0 = u53(r0.x, r0.y);
-                u1 = u53(r1.x, r1.y);
-            } else {
-                u0 = u53(r0.z, r0.w);
-                u1 = u53(r1.z, r1.w);
-            }
-        } else {
+    if (!PHILOX) {
+        const double *ucol = U + i0;
+        for (int s = 0; s < n_slots; ++s) {
+            double u0, u1;
             ld_f64x2(ucol, u0, u1);
             ucol += n_stride;
+            generic_slot<false, WITH_FP, WITH_T, WITH_B, EXT, ROUNDS>(s_slots, s_plan, s_cdf, s, u0, u1, w, c);
         }
-        uint64_t w0, w1;
-        if (d.kind == OB2_KIND_CATEGORICAL) {
-            const double *cdf = s_cdf + d.cdf_off;
-            const bool uni = (d.flags & OB2_SLOT_CAT_UNIFORM) != 0;
-            const int c0 = draw_cat_fast(cdf, d.n_cats, u0, uni);
-            const int c1 = draw_cat_fast(cdf, d.n_cats, u1, uni);
-            st_i32x2(reinterpret_cast<int *>(col - i0 * 4), c0, c1);
-            int *bcol = reinterpret_cast<int *>(col - i0 * 4 + bdelta);
-            col += stride4;
-            int b0 = c0, b1 = c1;  // WITH_B: reverse() of the transformed value, evaluated on what is stored
-            if (WITH_T) {
-                if (d.t_op != OB2_OP_ONEHOT) {  // Enumerate / Identity: the index both ways
-                    st_i32x2(reinterpret_cast<int *>(tcol - i0 * 4), c0, c1);
-                    tcol += stride4;
-                } else if (d.t_width == 1) {
-                    const double t0 = (double)c0, t1 = (double)c1;
-                    st_f64x2(reinterpret_cast<double *>(tcol), t0, t1);
-                    tcol += stride8;
-                    if (WITH_B) {  // k == 2: (v > 0.5); k == 1: always category 0
-                        b0 = (d.n_cats == 2 && t0 > 0.5) ? 1 : 0;
-                        b1 = (d.n_cats == 2 && t1 > 0.5) ? 1 : 0;
-                    }
-                } else {
-                    // column j is at tcol + j * stride8; the launcher guarantees stride8 < 2^32,
-                    // so each address is ONE 32x32+64 multiply-add (IMAD.WIDE.U32)
-                    const uint32_t s8 = (uint32_t)stride8, k = (uint32_t)d.t_width;
-                    // WITH_B: reverse_kernel's argmax (first maximum) over these k values is the position
-                    // of the single 1.0 stored below, i.e. the index itself: the Philox draw is always in
-                    // [0, k).  Tracking the maximum while storing (tried: 6 more instructions per column
-                    // pair) costs the kernel 4.5 % for the same bytes, so the identity is used; the staged
-                    // kernels and tests/test_gpu_suggest_fused.py hold it to account.
-#pragma unroll 4
-                    for (uint32_t j = 0; j < k; ++j) {
-                        const unsigned h0 = c0 == (int)j ? 0x3FF00000u : 0u, h1 = c1 == (int)j ? 0x3FF00000u : 0u;
-                        st_onehot_hi(reinterpret_cast<double *>(tcol + (uint64_t)j * s8), h0, h1);
-                    }
-                    tcol += (uint64_t)k * s8;
-                }
-            }
-            if (WITH_B && split) st_i32x2(bcol, b0, b1);
-            w0 = (uint64_t)(int64_t)b0;
-            w1 = (uint64_t)(int64_t)b1;
-            if (!PHILOX) {  // an injected u >= 1 can run off the table; a Philox u cannot
-                ok0 &= c0 < d.n_cats;
-                ok1 &= c1 < d.n_cats;
-            }
-        } else {
-            double x0 = draw_real<EXT>(d, u0);
-            double x1 = draw_real<EXT>(d, u1);
-            if (d.kind == OB2_KIND_INTEGER) {
-                x0 = floor(x0);  // _Discrete.sample, space.py:294
-                x1 = floor(x1);
-                const long long q0 = __double2ll_rz(x0), q1 = __double2ll_rz(x1);
-                st_i64x2(reinterpret_cast<long long *>(col), q0, q1);
-                long long bq0 = q0, bq1 = q1;
-                if (WITH_T) {
-                    if (d.t_op == OB2_OP_TO_REAL) {  // the floored double is exactly (double)q
-                        st_f64x2(reinterpret_cast<double *>(tcol), x0, x1);
-                        if (WITH_B) {  // Reverse(Quantize).reverse = Quantize.transform of the stored double
-                            bq0 = quantize_ll(x0, d.t_flags);
-                            bq1 = quantize_ll(x1, d.t_flags);
+    } else {
+        for (int r = 0; r < n_runs; ++r) {
+            const int first = s_runs[r].first, end = first + s_runs[r].count;
+#define OB2_RUN_ARGS s_slots, s_plan, first, end, w, c
+            switch (s_runs[r].cls) {
+                case OB2_CLS_UNIFORM:
+                    run_real<OB2_CLS_UNIFORM, WITH_FP, WITH_T, WITH_B, EXT, ROUNDS>(OB2_RUN_ARGS);
+                    break;
+                case OB2_CLS_RECIP:
+                    run_real<OB2_CLS_RECIP, WITH_FP, WITH_T, WITH_B, EXT, ROUNDS>(OB2_RUN_ARGS);
+                    break;
+                case OB2_CLS_NORM:
+                    run_real<OB2_CLS_NORM, WITH_FP, WITH_T, WITH_B, EXT, ROUNDS>(OB2_RUN_ARGS);
+                    break;
+                case OB2_CLS_INT_MULHI:
+                    run_words<OB2_CLS_INT_MULHI, WITH_FP, WITH_T, WITH_B, ROUNDS>(OB2_RUN_ARGS, s_thr);
+                    break;
+                case OB2_CLS_CAT_MULHI:
+                    run_words<OB2_CLS_CAT_MULHI, WITH_FP, WITH_T, WITH_B, ROUNDS>(OB2_RUN_ARGS, s_thr);
+                    break;
+                case OB2_CLS_CAT_TABLE:
+                    run_words<OB2_CLS_CAT_TABLE, WITH_FP, WITH_T, WITH_B, ROUNDS>(OB2_RUN_ARGS, s_thr);
+                    break;
+                default:
+                    for (int s = first; s < end; ++s) {
+                        double u0, u1;
+                        if (s_plan[s].word == 0) {
+                            new_block<ROUNDS>(s_plan[s].block, w, c);
+                            u0 = u53(w.r0.x, w.r0.y);
+                            u1 = u53(w.r1.x, w.r1.y);
+                        } else {
+                            u0 = u53(w.r0.z, w.r0.w);
+                            u1 = u53(w.r1.z, w.r1.w);
                         }
-                    } else {
-                        st_i64x2(reinterpret_cast<long long *>(tcol), q0, q1);
+                        generic_slot<true, WITH_FP, WITH_T, WITH_B, EXT, ROUNDS>(s_slots, s_plan, s_cdf, s, u0, u1, w, c);
                     }
-                    tcol += stride8;
-                }
-                if (WITH_B && split) st_i64x2(reinterpret_cast<long long *>(col + bdelta), bq0, bq1);
-                w0 = (uint64_t)bq0;
-                w1 = (uint64_t)bq1;
-            } else {
-                st_f64x2(reinterpret_cast<double *>(col), x0, x1);
-                double bx0 = x0, bx1 = x1;
-                if (WITH_T) {
-                    if (d.t_op == OB2_OP_QUANTIZE) {
-                        const long long t0 = quantize_ll(x0, d.t_flags), t1 = quantize_ll(x1, d.t_flags);
-                        st_i64x2(reinterpret_cast<long long *>(tcol), t0, t1);
-                        if (WITH_B) {
-                            bx0 = __ll2double_rn(t0);
-                            bx1 = __ll2double_rn(t1);
-                        }
-                    } else {
-                        st_f64x2(reinterpret_cast<double *>(tcol), x0, x1);
-                    }
-                    tcol += stride8;
-                }
-                // (aliased: only a lossy Quantize round trip differs from what was just stored)
-                if (WITH_B && (split || d.t_op == OB2_OP_QUANTIZE))
-                    st_f64x2(reinterpret_cast<double *>(col + bdelta), bx0, bx1);
-                w0 = canon_f64(bx0);
-                w1 = canon_f64(bx1);
+                    break;
             }
-            col += stride8;
-            ok0 &= (x0 >= d.low) & (x0 < d.high);  // half-open, space.py:164
-            ok1 &= (x1 >= d.low) & (x1 < d.high);
-        }
-        if (WITH_FP) {
-            fp_add(acc0, d, w0);
-            fp_add(acc1, d, w1);
-        }
-        if (d.flags & OB2_SLOT_DIM_LAST) {
-            if (!(ok0 & ok1)) {  // cold: only Real/Integer slots can clear ok
-                if (PHILOX) {
-                    if (!ok0)
-                        ok0 = redraw_dim<WITH_FP, WITH_T, WITH_B, EXT>(s_slots, s, idx0, i0, n_stride, cols, tcols, bdelta, k0, k1, pm0, pm1, acc0);
-                    if (!ok1)
-                        ok1 = redraw_dim<WITH_FP, WITH_T, WITH_B, EXT>(s_slots, s, idx1, i0 + 1, n_stride, cols, tcols, bdelta, k0, k1, pm0, pm1, acc1);
-                    if (n_failed != nullptr) {  // 4 misses: the reference raises "Improbable bounds"
-                        const unsigned bad = (ok0 ? 0u : 1u) + ((ok1 || !has1) ? 0u : 1u);
-                        if (bad) atomicAdd(n_failed + d.dim_first, bad);
-                    }
-                }
-                all0 &= ok0;
-                all1 &= ok1;
-                ok0 = ok1 = true;
-            }
+#undef OB2_RUN_ARGS
         }
     }
     if (mask != nullptr) {
-        *reinterpret_cast<uchar2 *>(mask + i0) = make_uchar2(all0 ? 1 : 0, (all1 && has1) ? 1 : 0);
+        *reinterpret_cast<uchar2 *>(mask + i0) = make_uchar2(w.all0 ? 1 : 0, (w.all1 && has1) ? 1 : 0);
     }
     if (WITH_FP) {
         uint64_t lo0, hi0, lo1, hi1;
-        fp_finish(acc0, n_slots, lo0, hi0);
-        fp_finish(acc1, n_slots, lo1, hi1);
+        fp_finish(w.acc0, n_slots, lo0, hi0);
+        fp_finish(w.acc1, n_slots, lo1, hi1);
         if (!has1) lo1 = hi1 = 0;  // padding entry
         st_u64x4(fp + 2 * i0, lo0, hi0, lo1, hi1);
     }
 }
 
-template <bool PHILOX, bool WITH_FP, bool WITH_T, bool WITH_B, bool EXT>
-__global__ void __launch_bounds__(OB2_BLOCK, WITH_B ? OB2_SUGGEST_CTAS : 4)
-sample_kernel(const ob2_slot_desc *__restrict__ g_slots, int n_slots, const double *__restrict__ g_cdf,
-              int cdf_len, int64_t n, int64_t n_stride, int64_t stride4, int64_t stride8, uint32_t k0, uint32_t k1,
-              uint32_t pm0, uint32_t pm1,
-              uint64_t base_index, const uint64_t *__restrict__ index, const double *__restrict__ U,
-              char *__restrict__ cols, char *__restrict__ tcols, int64_t bdelta, uint8_t *__restrict__ mask,
-              uint64_t *__restrict__ fp, uint32_t *__restrict__ n_failed) {
-    extern __shared__ __align__(16) unsigned char smem[];
-    ob2_slot_desc *s_slots = reinterpret_cast<ob2_slot_desc *>(smem);
-    double *s_cdf = reinterpret_cast<double *>(smem + (size_t)n_slots * sizeof(ob2_slot_desc));
-    ob2_stage_tables(g_slots, n_slots, g_cdf, cdf_len, s_slots, s_cdf);
-    sample_body<PHILOX, WITH_FP, WITH_T, WITH_B, EXT>(s_slots, s_cdf, n_slots, n, n_stride, stride4, stride8, k0, k1, pm0,
-                                                      pm1, base_index, index, U, cols, tcols, bdelta, mask, fp, n_failed);
+// shared-memory layout of the staged tables: [slots][plan][runs][cdf][thr]
+struct StagedTables {
+    ob2_slot_desc *slots;
+    ob2_slot_plan *plan;
+    ob2_run *runs;
+    double *cdf;
+    uint32_t *thr;
+};
+__device__ __forceinline__ StagedTables carve_tables(unsigned char *smem, int n_slots, int cdf_len) {
+    StagedTables t;
+    t.slots = reinterpret_cast<ob2_slot_desc *>(smem);
+    t.plan = reinterpret_cast<ob2_slot_plan *>(t.slots + n_slots);
+    t.runs = reinterpret_cast<ob2_run *>(t.plan + n_slots);
+    t.cdf = reinterpret_cast<double *>(t.runs + n_slots);
+    t.thr = reinterpret_cast<uint32_t *>(t.cdf + cdf_len);
+    return t;
 }
 
-// The same kernel for spaces of up to OB2_PARAM_SLOTS slots: the descriptor table travels in the
-// launch parameters (constant bank); only the categorical cdf tables are staged in shared memory.
+template <bool PHILOX, bool WITH_FP, bool WITH_T, bool WITH_B, bool EXT, int ROUNDS>
+__global__ void __launch_bounds__(OB2_BLOCK, WITH_B ? OB2_SUGGEST_CTAS : 4)
+sample_kernel(const ob2_slot_desc *__restrict__ g_slots, const ob2_slot_plan *__restrict__ g_plan,
+              const ob2_run *__restrict__ g_runs, int n_runs, int n_slots, const double *__restrict__ g_cdf,
+              const uint32_t *__restrict__ g_thr, int cdf_len, int64_t n, int64_t n_stride, int64_t stride4,
+              int64_t stride8, uint32_t k0, uint32_t k1, uint32_t pm0, uint32_t pm1, uint64_t base_index,
+              const uint64_t *__restrict__ index, const double *__restrict__ U, char *__restrict__ cols,
+              char *__restrict__ tcols, int64_t bdelta, uint8_t *__restrict__ mask, uint64_t *__restrict__ fp,
+              uint32_t *__restrict__ n_failed) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    const StagedTables t = carve_tables(smem, n_slots, cdf_len);
+    // descriptors (128 B) and plan entries (16 B) are 16-byte multiples: copy as uint4
+    {
+        const uint4 *src = reinterpret_cast<const uint4 *>(g_slots);
+        uint4 *dst = reinterpret_cast<uint4 *>(t.slots);
+        for (int i = threadIdx.x; i < n_slots * 8; i += blockDim.x) dst[i] = __ldg(src + i);
+        const uint4 *psrc = reinterpret_cast<const uint4 *>(g_plan);
+        uint4 *pdst = reinterpret_cast<uint4 *>(t.plan);
+        for (int i = threadIdx.x; i < n_slots; i += blockDim.x) pdst[i] = __ldg(psrc + i);
+        const uint2 *rsrc = reinterpret_cast<const uint2 *>(g_runs);
+        uint2 *rdst = reinterpret_cast<uint2 *>(t.runs);
+        for (int i = threadIdx.x; i < n_runs; i += blockDim.x) rdst[i] = __ldg(rsrc + i);
+        for (int i = threadIdx.x; i < cdf_len; i += blockDim.x) {
+            t.cdf[i] = __ldg(g_cdf + i);
+            t.thr[i] = __ldg(g_thr + i);
+        }
+        __syncthreads();
+    }
+    sample_body<PHILOX, WITH_FP, WITH_T, WITH_B, EXT, ROUNDS>(t.slots, t.plan, t.runs, n_runs, t.cdf, t.thr, n_slots, n, n_stride,
+                                                              stride4, stride8, k0, k1, pm0, pm1, base_index, index, U, cols,
+                                                              tcols, bdelta, mask, fp, n_failed);
+}
+
+// The same kernel for spaces of up to OB2_PARAM_SLOTS slots: descriptors, plan and runs travel in the
+// launch parameters (constant bank); only the categorical tables are staged in shared memory.
 struct ob2_slot_table {
     ob2_slot_desc s[OB2_PARAM_SLOTS];
+    ob2_slot_plan p[OB2_PARAM_SLOTS];
+    ob2_run r[OB2_PARAM_SLOTS];
 };
+static_assert(sizeof(ob2_slot_table) <= 30 * 1024, "the table must fit the 32 KB launch parameter space");
 
-template <bool PHILOX, bool WITH_FP, bool WITH_T, bool WITH_B, bool EXT>
+template <bool PHILOX, bool WITH_FP, bool WITH_T, bool WITH_B, bool EXT, int ROUNDS>
 __global__ void __launch_bounds__(OB2_BLOCK, WITH_B ? OB2_SUGGEST_CTAS : 4)
-sample_kernel_p(const __grid_constant__ ob2_slot_table tbl, int n_slots, const double *__restrict__ g_cdf, int cdf_len,
-                int64_t n, int64_t n_stride, int64_t stride4, int64_t stride8, uint32_t k0, uint32_t k1, uint32_t pm0,
-                uint32_t pm1, uint64_t base_index, const uint64_t *__restrict__ index,
-                const double *__restrict__ U, char *__restrict__ cols, char *__restrict__ tcols, int64_t bdelta,
-                uint8_t *__restrict__ mask, uint64_t *__restrict__ fp, uint32_t *__restrict__ n_failed) {
+sample_kernel_p(const __grid_constant__ ob2_slot_table tbl, int n_runs, int n_slots, const double *__restrict__ g_cdf,
+                const uint32_t *__restrict__ g_thr, int cdf_len, int64_t n, int64_t n_stride, int64_t stride4,
+                int64_t stride8, uint32_t k0, uint32_t k1, uint32_t pm0, uint32_t pm1, uint64_t base_index,
+                const uint64_t *__restrict__ index, const double *__restrict__ U, char *__restrict__ cols,
+                char *__restrict__ tcols, int64_t bdelta, uint8_t *__restrict__ mask, uint64_t *__restrict__ fp,
+                uint32_t *__restrict__ n_failed) {
     extern __shared__ __align__(16) unsigned char smem[];
     double *s_cdf = reinterpret_cast<double *>(smem);
-    for (int i = threadIdx.x; i < cdf_len; i += blockDim.x) s_cdf[i] = g_cdf[i];
+    uint32_t *s_thr = reinterpret_cast<uint32_t *>(s_cdf + cdf_len);
+    for (int i = threadIdx.x; i < cdf_len; i += blockDim.x) {
+        s_cdf[i] = g_cdf[i];
+        s_thr[i] = g_thr[i];
+    }
     __syncthreads();
-    sample_body<PHILOX, WITH_FP, WITH_T, WITH_B, EXT>(tbl.s, s_cdf, n_slots, n, n_stride, stride4, stride8, k0, k1, pm0,
-                                                      pm1, base_index, index, U, cols, tcols, bdelta, mask, fp, n_failed);
+    sample_body<PHILOX, WITH_FP, WITH_T, WITH_B, EXT, ROUNDS>(tbl.s, tbl.p, tbl.r, n_runs, s_cdf, s_thr, n_slots, n, n_stride,
+                                                              stride4, stride8, k0, k1, pm0, pm1, base_index, index, U, cols,
+                                                              tcols, bdelta, mask, fp, n_failed);
 }
 
 // Space.__contains__ over columns.
@@ -423,34 +711,61 @@ struct SampleArgs {
     void *stream;
 };
 
-template <bool PHILOX, bool WITH_FP, bool WITH_T, bool EXT, bool WITH_B = false>
-int launch_one(const SampleArgs &a, unsigned blocks) {
-    auto kern = sample_kernel<PHILOX, WITH_FP, WITH_T, WITH_B, EXT>;
-    const int64_t bdelta = WITH_B ? (const char *)a.back - (const char *)a.cols : 0;
+// Which instantiations exist (each is a large kernel; the build time is proportional to their number):
+//   Philox mode, tables in the launch parameters (spaces of up to OB2_PARAM_SLOTS slots): 5 output
+//     combinations x {10, 7} rounds;
+//   Philox mode, tables staged in shared memory (larger spaces): the 5 combinations, 10 rounds;
+//   injected uniforms (parity mode): shared-memory staging, with / without the fingerprint.
+// The further priors (draw_extended) are reached through an out-of-line call from the general slot
+// path only, so one instantiation serves every space.
+template <bool WITH_FP, bool WITH_T, bool WITH_B, int ROUNDS>
+int launch_param(const SampleArgs &a, unsigned blocks) {
     const ob2_space *sp = a.sp;
-    // Descriptors in the launch parameters: measured -1.5 % on the fused kernels (suggest 4.39 -> 4.33 ms,
-    // sample+transform 3.46 -> 3.41 ms) but +5 % on the issue-bound plain sampler (real16: 4.99 -> 5.23 ms
-    // per 1e8), so only the store-heavy variants use it.
-    if ((WITH_B || WITH_T) && sp->n_slots <= OB2_PARAM_SLOTS && sp->h_slots != nullptr) {
-        auto kern_p = sample_kernel_p<PHILOX, WITH_FP, WITH_T, WITH_B, EXT>;
-        static thread_local ob2_slot_table tbl;  // (24 KB: not on the stack)
-        memcpy(tbl.s, sp->h_slots, (size_t)sp->n_slots * sizeof(ob2_slot_desc));
-        const size_t smem_p = (size_t)(sp->cdf_len > 0 ? sp->cdf_len : 1) * sizeof(double);
-        int rc_p = prepare_smem(kern_p, smem_p);
-        if (rc_p != OB2_OK) return rc_p;
-        kern_p<<<blocks, OB2_BLOCK, smem_p, static_cast<cudaStream_t>(a.stream)>>>(
-            tbl, sp->n_slots, sp->d_cdf, sp->cdf_len, a.n, a.n_stride, 4 * a.n_stride, 8 * a.n_stride, (uint32_t)a.seed,
-            (uint32_t)(a.seed >> 32), 0xD2511F53u, 0xCD9E8D57u, a.base_index, a.index, a.U, (char *)a.cols,
-            (char *)a.tcols, bdelta, a.mask, a.fp, a.n_failed);
-        return ob2_check_cuda(cudaGetLastError(), "sample_kernel_p launch");
-    }
+    const int64_t bdelta = WITH_B ? (const char *)a.back - (const char *)a.cols : 0;
+    auto kern_p = sample_kernel_p<true, WITH_FP, WITH_T, WITH_B, true, ROUNDS>;
+    static thread_local ob2_slot_table tbl;  // (29 KB: not on the stack)
+    memcpy(tbl.s, sp->h_slots, (size_t)sp->n_slots * sizeof(ob2_slot_desc));
+    memcpy(tbl.p, sp->h_plan, (size_t)sp->n_slots * sizeof(ob2_slot_plan));
+    memcpy(tbl.r, sp->h_runs, (size_t)sp->n_runs * sizeof(ob2_run));
+    const size_t smem_p = (size_t)(sp->cdf_len > 0 ? sp->cdf_len : 1) * (sizeof(double) + sizeof(uint32_t));
+    int rc_p = prepare_smem(kern_p, smem_p);
+    if (rc_p != OB2_OK) return rc_p;
+    kern_p<<<blocks, OB2_BLOCK, smem_p, static_cast<cudaStream_t>(a.stream)>>>(
+        tbl, sp->n_runs, sp->n_slots, sp->d_cdf, sp->d_thr, sp->cdf_len, a.n, a.n_stride, 4 * a.n_stride, 8 * a.n_stride,
+        (uint32_t)a.seed, (uint32_t)(a.seed >> 32), 0xD2511F53u, 0xCD9E8D57u, a.base_index, a.index, a.U, (char *)a.cols,
+        (char *)a.tcols, bdelta, a.mask, a.fp, a.n_failed);
+    return ob2_check_cuda(cudaGetLastError(), "sample_kernel_p launch");
+}
+
+template <bool PHILOX, bool WITH_FP, bool WITH_T, bool WITH_B>
+int launch_smem(const SampleArgs &a, unsigned blocks) {
+    const ob2_space *sp = a.sp;
+    const int64_t bdelta = WITH_B ? (const char *)a.back - (const char *)a.cols : 0;
+    auto kern = sample_kernel<PHILOX, WITH_FP, WITH_T, WITH_B, true, 10>;
     int rc = prepare_smem(kern, sp->smem_bytes);
     if (rc != OB2_OK) return rc;
     kern<<<blocks, OB2_BLOCK, sp->smem_bytes, static_cast<cudaStream_t>(a.stream)>>>(
-        sp->d_slots, sp->n_slots, sp->d_cdf, sp->cdf_len, a.n, a.n_stride, 4 * a.n_stride, 8 * a.n_stride, (uint32_t)a.seed,
-        (uint32_t)(a.seed >> 32), 0xD2511F53u, 0xCD9E8D57u, a.base_index, a.index, a.U, (char *)a.cols, (char *)a.tcols, bdelta, a.mask, a.fp,
-        a.n_failed);
+        sp->d_slots, sp->d_plan, sp->d_runs, sp->n_runs, sp->n_slots, sp->d_cdf, sp->d_thr, sp->cdf_len, a.n, a.n_stride,
+        4 * a.n_stride, 8 * a.n_stride, (uint32_t)a.seed, (uint32_t)(a.seed >> 32), 0xD2511F53u, 0xCD9E8D57u, a.base_index,
+        a.index, a.U, (char *)a.cols, (char *)a.tcols, bdelta, a.mask, a.fp, a.n_failed);
     return ob2_check_cuda(cudaGetLastError(), "sample_kernel launch");
+}
+
+template <bool WITH_FP, bool WITH_T, bool WITH_B>
+int launch_philox(const SampleArgs &a, unsigned blocks) {
+    const ob2_space *sp = a.sp;
+    if (sp->n_slots <= OB2_PARAM_SLOTS && sp->h_slots != nullptr) {
+        // Tables in the launch parameters: descriptor / plan / run fields become uniform loads from the
+        // constant bank and the class branches are provably warp-uniform.
+        if (sp->philox_rounds == 7) return launch_param<WITH_FP, WITH_T, WITH_B, 7>(a, blocks);
+        return launch_param<WITH_FP, WITH_T, WITH_B, 10>(a, blocks);
+    }
+    if (sp->philox_rounds != 10) {
+        ob2_set_error("sample: %d-round Philox is built for spaces of up to %d slots only", sp->philox_rounds,
+                      (int)OB2_PARAM_SLOTS);
+        return OB2_EINVAL;
+    }
+    return launch_smem<true, WITH_FP, WITH_T, WITH_B>(a, blocks);
 }
 
 template <bool PHILOX>
@@ -487,22 +802,14 @@ int launch_sample(const SampleArgs &a) {
     }
     const unsigned b = (unsigned)blocks;
     const bool with_fp = a.fp != nullptr, with_t = a.tcols != nullptr;
-    if (a.back != nullptr) {  // ob2_suggest: Philox, transform, reverse and fingerprint, all in the one pass
-        if (a.sp->has_extended_prior) return launch_one<PHILOX, true, true, true, PHILOX>(a, b);
-        return launch_one<PHILOX, true, true, false, PHILOX>(a, b);
+    if (!PHILOX) {  // parity mode: ob2_sample_from_uniform (no transformed / handed-out outputs)
+        return with_fp ? launch_smem<false, true, false, false>(a, b) : launch_smem<false, false, false, false>(a, b);
     }
-    // EXT = the space uses one of the extra closed-form priors: those inverse CDFs live in a
-    // separate instantiation so that the common kernel keeps its registers and code size
-    if (a.sp->has_extended_prior) {
-        if (with_fp && with_t) return launch_one<PHILOX, true, true, true>(a, b);
-        if (with_fp) return launch_one<PHILOX, true, false, true>(a, b);
-        if (with_t) return launch_one<PHILOX, false, true, true>(a, b);
-        return launch_one<PHILOX, false, false, true>(a, b);
-    }
-    if (with_fp && with_t) return launch_one<PHILOX, true, true, false>(a, b);
-    if (with_fp) return launch_one<PHILOX, true, false, false>(a, b);
-    if (with_t) return launch_one<PHILOX, false, true, false>(a, b);
-    return launch_one<PHILOX, false, false, false>(a, b);
+    if (a.back != nullptr) return launch_philox<true, true, true>(a, b);  // ob2_suggest: everything in the one pass
+    if (with_fp && with_t) return launch_philox<true, true, false>(a, b);
+    if (with_fp) return launch_philox<true, false, false>(a, b);
+    if (with_t) return launch_philox<false, true, false>(a, b);
+    return launch_philox<false, false, false>(a, b);
 }
 
 }  // namespace

@@ -206,7 +206,9 @@ extern "C" int ob2_space_create(const ob2_slot_desc *slots, int32_t n_slots, con
             return OB2_ETOOBIG;
         }
     }
-    const size_t smem = (size_t)n_slots * sizeof(ob2_slot_desc) + (size_t)cdf_len * sizeof(double);
+    // staged per block by the sampler: descriptors, draw plan, runs, cdf tables and their u32 thresholds
+    const size_t smem = (size_t)n_slots * (sizeof(ob2_slot_desc) + sizeof(ob2_slot_plan) + sizeof(ob2_run)) +
+                        (size_t)cdf_len * (sizeof(double) + sizeof(uint32_t));
     if (smem > 200 * 1024) {
         ob2_set_error("space needs %zu bytes of descriptor staging; the limit is 200 KiB", smem);
         return OB2_ETOOBIG;
@@ -227,6 +229,11 @@ extern "C" int ob2_space_create(const ob2_slot_desc *slots, int32_t n_slots, con
     sp->has_extended_prior = extended;
     sp->d_slots = nullptr;
     sp->d_cdf = nullptr;
+    sp->h_plan = sp->d_plan = nullptr;
+    sp->h_runs = sp->d_runs = nullptr;
+    sp->d_thr = nullptr;
+    sp->n_runs = 0;
+    sp->philox_rounds = 10;
     sp->d_stage = sp->h_stage = nullptr;
     sp->stage_mutex = new (std::nothrow) std::mutex();
     // the device copy of the table carries the wire layout in `reserved`: (offset units << 4) | element bytes
@@ -249,12 +256,39 @@ extern "C" int ob2_space_create(const ob2_slot_desc *slots, int32_t n_slots, con
         wire += w;
     }
     sp->wire_row_bytes = wire;
+    sp->h_slots = staged;  // kept: small spaces travel in the sampler's launch parameters
+    // the sampler's draw plan (sets OB2_SLOT_FAST_EXP in the staged flags: before the upload)
+    sp->h_plan = new (std::nothrow) ob2_slot_plan[n_slots];
+    sp->h_runs = new (std::nothrow) ob2_run[n_slots];
+    uint32_t *h_thr = new (std::nothrow) uint32_t[cdf_len > 0 ? cdf_len : 1]();
+    if (sp->h_plan == nullptr || sp->h_runs == nullptr || h_thr == nullptr) {
+        delete[] h_thr;
+        ob2_space_destroy(sp);
+        ob2_set_error("out of host memory");
+        return OB2_ENOMEM;
+    }
+    sp->n_runs = compile_plan(staged, n_slots, cdf, sp->h_plan, sp->h_runs, h_thr);
+    if (sp->n_runs < 0) {
+        delete[] h_thr;
+        ob2_space_destroy(sp);
+        ob2_set_error("space needs more than 65536 Philox blocks per candidate");
+        return OB2_ETOOBIG;
+    }
     int rc = ob2_check_cuda(cudaGetDevice(&sp->device), "cudaGetDevice");
+    if (rc == OB2_OK) rc = ob2_check_cuda(cudaMalloc(&sp->d_plan, (size_t)n_slots * sizeof(ob2_slot_plan)), "cudaMalloc(plan)");
+    if (rc == OB2_OK)
+        rc = ob2_check_cuda(cudaMemcpy(sp->d_plan, sp->h_plan, (size_t)n_slots * sizeof(ob2_slot_plan), cudaMemcpyHostToDevice), "cudaMemcpy(plan)");
+    if (rc == OB2_OK) rc = ob2_check_cuda(cudaMalloc(&sp->d_runs, (size_t)n_slots * sizeof(ob2_run)), "cudaMalloc(runs)");
+    if (rc == OB2_OK)
+        rc = ob2_check_cuda(cudaMemcpy(sp->d_runs, sp->h_runs, (size_t)sp->n_runs * sizeof(ob2_run), cudaMemcpyHostToDevice), "cudaMemcpy(runs)");
+    if (rc == OB2_OK) rc = ob2_check_cuda(cudaMalloc(&sp->d_thr, (size_t)(cdf_len > 0 ? cdf_len : 1) * sizeof(uint32_t)), "cudaMalloc(thr)");
+    if (rc == OB2_OK)
+        rc = ob2_check_cuda(cudaMemcpy(sp->d_thr, h_thr, (size_t)(cdf_len > 0 ? cdf_len : 1) * sizeof(uint32_t), cudaMemcpyHostToDevice), "cudaMemcpy(thr)");
+    delete[] h_thr;
     if (rc == OB2_OK) rc = ob2_check_cuda(cudaMalloc(&sp->d_slots, (size_t)n_slots * sizeof(ob2_slot_desc)), "cudaMalloc(slots)");
     if (rc == OB2_OK)
         rc = ob2_check_cuda(cudaMemcpy(sp->d_slots, staged, (size_t)n_slots * sizeof(ob2_slot_desc), cudaMemcpyHostToDevice),
                             "cudaMemcpy(slots)");
-    sp->h_slots = staged;  // kept: small spaces travel in the sampler's launch parameters
     // always allocate at least one element so kernels get a valid pointer
     if (rc == OB2_OK) rc = ob2_check_cuda(cudaMalloc(&sp->d_cdf, (size_t)(cdf_len > 0 ? cdf_len : 1) * sizeof(double)), "cudaMalloc(cdf)");
     if (rc == OB2_OK && cdf_len > 0)
@@ -271,6 +305,11 @@ extern "C" void ob2_space_destroy(ob2_space *sp) {
     if (sp == nullptr) return;
     if (sp->d_slots) cudaFree(sp->d_slots);
     if (sp->d_cdf) cudaFree(sp->d_cdf);
+    if (sp->d_plan) cudaFree(sp->d_plan);
+    if (sp->d_runs) cudaFree(sp->d_runs);
+    if (sp->d_thr) cudaFree(sp->d_thr);
+    delete[] sp->h_plan;
+    delete[] sp->h_runs;
     if (sp->d_stage) cudaFree(sp->d_stage);
     if (sp->h_stage) cudaFreeHost(sp->h_stage);
     delete sp->stage_mutex;
@@ -278,6 +317,15 @@ extern "C" void ob2_space_destroy(ob2_space *sp) {
     delete[] sp->wire_units;
     delete[] sp->wire_bytes;
     delete sp;
+}
+
+extern "C" int ob2_space_set_philox_rounds(ob2_space *sp, int32_t rounds) {
+    if (sp == nullptr || (rounds != 7 && rounds != 10)) {
+        ob2_set_error("ob2_space_set_philox_rounds: rounds must be 7 or 10");
+        return OB2_EINVAL;
+    }
+    sp->philox_rounds = rounds;
+    return OB2_OK;
 }
 
 extern "C" int64_t ob2_space_row_bytes(const ob2_space *sp) { return sp ? sp->row_bytes : -1; }

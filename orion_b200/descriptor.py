@@ -141,7 +141,7 @@ def _prior_params(dim):
 class CompiledSpace(object):
     """A Space compiled for the device, under one transform requirement."""
 
-    def __init__(self, space, requirement=None, quantize='round', device=None):
+    def __init__(self, space, requirement=None, quantize='round', device=None, philox_rounds=10):
         if requirement not in REQUIREMENTS:
             raise TypeError("Unsupported requirement: {}".format(requirement))
         if quantize not in ('round', 'floor'):
@@ -244,6 +244,9 @@ class CompiledSpace(object):
         with torch.cuda.device(self.device):
             _lib.check(self.lib.ob2_space_create(arr, self.n_slots, cdf_arr, len(cdf), ctypes.byref(handle)))
         self.handle = handle
+        self.philox_rounds = int(philox_rounds)
+        if self.philox_rounds != 10:                    # 7: Philox4x32-7 (fewer instructions, other draws)
+            _lib.check(self.lib.ob2_space_set_philox_rounds(handle, self.philox_rounds))
         self._host_cols = self._host_failed = None      # sample_host's reusable host block
         assert self.lib.ob2_space_row_bytes(handle) == self.row_bytes
         assert self.lib.ob2_space_trow_bytes(handle) == self.trow_bytes
@@ -480,13 +483,13 @@ class CompiledSpace(object):
 _CACHE_ATTR = '_ob2_compiled'
 
 
-def compile_space(space, requirement=None, quantize='round', device=None):
+def compile_space(space, requirement=None, quantize='round', device=None, philox_rounds=10):
     """Compile (and memoise on the Space object) for the given requirement."""
     key = (requirement, quantize, str(device) if device is not None else torch.cuda.current_device(),
-           tuple(id(d) for d in space.values()))
+           tuple(id(d) for d in space.values()), philox_rounds)
     cache = space.__dict__.setdefault(_CACHE_ATTR, {}) if hasattr(space, '__dict__') else {}
     hit = cache.get(key)
     if hit is None:
-        hit = CompiledSpace(space, requirement, quantize, device)
+        hit = CompiledSpace(space, requirement, quantize, device, philox_rounds)
         cache[key] = hit
     return hit

@@ -293,8 +293,8 @@ class Space(OrderedDict):
         self[dimension.name] = dimension
 
     # -- tensor fast path ---------------------------------------------------
-    def compiled(self, requirement=None, quantize='round'):
-        return compile_space(self, requirement, quantize)
+    def compiled(self, requirement=None, quantize='round', philox_rounds=10):
+        return compile_space(self, requirement, quantize, philox_rounds=philox_rounds)
 
     def sample_columns(self, n_samples=1, seed=None, base_index=0, with_fingerprint=False, check=True):
         """Device-resident draw: returns a :class:`ColumnBatch` whose ``mask``

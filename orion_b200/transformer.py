@@ -230,8 +230,8 @@ class TransformedSpace(Space):
             # (Space.__setitem__ only admits Dimension instances)
             OrderedDict.__setitem__(self, dim.name, TransformedDimension(t, dim, requirement, quantize))
 
-    def compiled(self, requirement=None, quantize=None):
-        return compile_space(self.original, self.requirement, self.quantize)
+    def compiled(self, requirement=None, quantize=None, philox_rounds=10):
+        return compile_space(self.original, self.requirement, self.quantize, philox_rounds=philox_rounds)
 
     # -- batches -------------------------------------------------------------
     def transform_columns(self, batch, out=None):
