@@ -195,28 +195,26 @@ __device__ __forceinline__ double u53(uint32_t w0, uint32_t w1) {
 // 100) takes the tail branch.  Coefficients and their error bounds (<= 5e-16 relative against
 // 50-digit arithmetic): ob2_ndtri_coef.h, generated by benchmarks/fit/fit_ndtri.py.  CUDA's
 // normcdfinv costs ~2.3x the instructions because most warps execute both of its regions.
-// (the tail: out of line, about 3 warps in 100 come here)
-static __device__ __noinline__ double ob2_ndtri_tail(double u, double w, double x) {
-    const double s = sqrt(w);
-    if (s > OB2_NDTRI_S_MAX) return normcdfinv(u);  // u < 2^-53: only an injected uniform gets here
-    const double z = s - OB2_NDTRI_S_MID;
-    double p = 0.0;
-#define OB2_HORNER(c) p = fma(p, z, c);
-    OB2_NDTRI_TAIL(OB2_HORNER)
-#undef OB2_HORNER
-    return x * p;
-}
-
 __device__ __forceinline__ double ob2_ndtri(double u) {
     const double t = u * (1.0 - u);
     const double x = fma(2.0, u, -1.0);
     if (!(t > 0.0)) return u == 0.0 ? -CUDART_INF : (u == 1.0 ? CUDART_INF : CUDART_NAN);
     const double w = -(log(t) + 1.3862943611198906);  // -log(4 t)
-    if (w >= OB2_NDTRI_W_SPLIT) return ob2_ndtri_tail(u, w, x);
-    const double z = w - OB2_NDTRI_W_MID;
     double p = 0.0;
 #define OB2_HORNER(c) p = fma(p, z, c);
-    OB2_NDTRI_CENTRAL(OB2_HORNER)
+    if (w < OB2_NDTRI_W_SPLIT) {
+        const double z = w - OB2_NDTRI_W_MID;
+        OB2_NDTRI_CENTRAL(OB2_HORNER)
+    } else {  // about 3 warps in 100 come here
+        const double s = sqrt(w);
+        if (s <= OB2_NDTRI_S_MAX) {
+            const double z = s - OB2_NDTRI_S_MID;
+            OB2_NDTRI_TAIL(OB2_HORNER)
+        } else {  // u < 2^-53: only an injected uniform is that small
+            const double z = s - OB2_NDTRI_F_MID;
+            OB2_NDTRI_FAR(OB2_HORNER)
+        }
+    }
 #undef OB2_HORNER
     return x * p;
 }
@@ -504,24 +502,6 @@ __device__ __forceinline__ double draw_real(const ob2_slot_desc &d, double u) {
             break;
     }
     return __dadd_rn(__dmul_rn(b, d.scale), d.loc);
-}
-
-// The same draw out of line, for the general slot path and the redraw (cold or slow paths: every
-// call site of the inline version carries the code of all the inverse CDFs).
-static __device__ __noinline__ double draw_real_any(int dist, int flags, double p0, double p1, uint64_t hk3, double loc,
-                                                    double scale, double u) {
-    ob2_slot_desc d;
-    d.dist = dist;
-    d.flags = flags;
-    d.p0 = p0;
-    d.p1 = p1;
-    d.hk[3] = hk3;
-    d.loc = loc;
-    d.scale = scale;
-    return draw_real<true>(d, u);
-}
-__device__ __forceinline__ double draw_real_call(const ob2_slot_desc &d, double u) {
-    return draw_real_any(d.dist, d.flags, d.p0, d.p1, d.hk[3], d.loc, d.scale, u);
 }
 
 // numpy searchsorted(cdf, u, side='right')

@@ -69,101 +69,119 @@ __device__ __forceinline__ uint32_t pick_word(const Philox4 &r, uint32_t word) {
     return word == 0 ? r.x : word == 1 ? r.y : word == 2 ? r.z : r.w;
 }
 
-// Real.sample (space.py:263-270): a draw of dimension [first, s_last] landed
-// outside [low, high): redraw the whole (possibly shaped) value for candidate i,
-// attempts 1..3, overwriting its columns with scalar stores.  Rare path, inlined
-// in a cold branch of the walk: the hot loop carries no redraw state at all --
-// the fingerprint lanes are wrapping sums, so the contribution of the rejected
-// values (read back from the columns this thread just wrote) is subtracted and
-// the redrawn one added.  Only slots drawn from a 53-bit uniform can miss their
-// bounds (the 32-bit classes are in bounds by construction), so every slot here
-// takes words (0, 1) or (2, 3) of its block.
+// Real.sample (space.py:263-270): a draw that lands outside [low, high) is redrawn -- the whole
+// (possibly shaped) value of that dimension, up to 4 attempts.  The walk itself only ANDs the
+// bounds bits; a candidate that missed somewhere (rare) comes here afterwards, ONCE: every
+// Real / Integer dimension is re-checked from the values just written, and those that missed
+// are redrawn with attempts 1..3 (counter word 3), overwriting their columns with scalar
+// stores.  The fingerprint lanes are wrapping sums, so the contribution of the rejected values
+// is subtracted and the redrawn one added.  Out of line and everything by value: this is the
+// only call in the kernel, made when the walk's state is dead, so that the hot loops keep
+// their registers.  Only slots drawn from a 53-bit uniform can miss (the 32-bit classes are in
+// bounds by construction), so every slot redrawn here owns words (0, 1) or (2, 3) of its block.
 // WITH_B: the fingerprint is over the handed-out row (`back`, at cols + bdelta), which is also rewritten.
-struct Redrawn {
-    FpAcc acc;  // the candidate's fingerprint lanes with the rejected contribution replaced
+struct Fixed {
+    FpAcc acc;
     bool ok;
 };
-// (out of line, and everything by value: a reference into the walk state would pin it in local memory)
 template <bool WITH_FP, bool WITH_T, bool WITH_B, bool EXT, int ROUNDS>
-static __device__ __noinline__ Redrawn redraw_dim(const ob2_slot_desc *s_slots, const ob2_slot_plan *s_plan, int s_last,
-                                                  uint64_t index, int64_t i, int64_t n_stride, char *cols, char *tcols,
-                                                  int64_t bdelta, uint32_t k0, uint32_t k1, uint32_t pm0, uint32_t pm1,
-                                                  FpAcc acc) {
-    const int first = s_slots[s_last].dim_first;
-    if (WITH_FP) {
-        FpAcc old{0, 0};
-        for (int e = first; e <= s_last; ++e) {
-            const ob2_slot_desc &d = s_slots[e];
-            const char *col = cols + (int64_t)d.col_units * n_stride + (WITH_B ? bdelta : 0);
-            const uint64_t w = d.kind == OB2_KIND_INTEGER
-                                   ? (uint64_t) reinterpret_cast<const volatile long long *>(col)[i]
-                                   : canon_f64(reinterpret_cast<const volatile double *>(col)[i]);
-            fp_add(old, d, w);
-        }
-        acc.a -= old.a;
-        acc.b -= old.b;
-    }
-    bool ok = false;
-    FpAcc t{0, 0};
-    for (uint32_t a = 1; a < 4 && !ok; ++a) {
-        ok = true;
-        t = FpAcc{0, 0};
-        for (int e = first; e <= s_last; ++e) {
-            const ob2_slot_desc &d = s_slots[e];
-            const Philox4 r = philox4x32<ROUNDS>((uint32_t)index, (uint32_t)(index >> 32), (uint32_t)s_plan[e].block, a,
-                                                 k0, k1, pm0, pm1);
-            const double u = s_plan[e].word ? u53(r.z, r.w) : u53(r.x, r.y);
-            double x = draw_real_call(d, u);
-            char *col = cols + (int64_t)d.col_units * n_stride;
-            char *dst = tcols + (int64_t)d.t_units * n_stride;
-            uint64_t w;
-            if (d.kind == OB2_KIND_INTEGER) {
-                x = floor(x);
-                const long long q = __double2ll_rz(x);
-                reinterpret_cast<long long *>(col)[i] = q;
-                long long bq = q;
-                if (WITH_T) {
-                    if (d.t_op == OB2_OP_TO_REAL) {
-                        reinterpret_cast<double *>(dst)[i] = x;
-                        if (WITH_B) bq = quantize_ll(x, d.t_flags);
-                    } else {
-                        reinterpret_cast<long long *>(dst)[i] = q;
-                    }
-                }
-                if (WITH_B && bdelta != 0) reinterpret_cast<long long *>(col + bdelta)[i] = bq;
-                w = (uint64_t)bq;
-            } else {
-                reinterpret_cast<double *>(col)[i] = x;
-                double bx = x;
-                if (WITH_T) {
-                    if (d.t_op == OB2_OP_QUANTIZE) {
-                        const long long tq = quantize_ll(x, d.t_flags);
-                        reinterpret_cast<long long *>(dst)[i] = tq;
-                        bx = __ll2double_rn(tq);
-                    } else {
-                        reinterpret_cast<double *>(dst)[i] = x;
-                    }
-                }
-                if (WITH_B && (bdelta != 0 || d.t_op == OB2_OP_QUANTIZE)) reinterpret_cast<double *>(col + bdelta)[i] = bx;
-                w = canon_f64(WITH_B ? bx : x);
+static __device__ __noinline__ Fixed fixup_candidate(const ob2_slot_desc *s_slots, const ob2_slot_plan *s_plan, int n_slots,
+                                                     uint64_t index, int64_t i, int64_t n_stride, char *cols, char *tcols,
+                                                     int64_t bdelta, uint32_t k0, uint32_t k1, uint32_t pm0, uint32_t pm1,
+                                                     FpAcc acc, uint32_t *n_failed) {
+    bool all = true;
+    for (int first = 0; first < n_slots;) {
+        int s_last = first;
+        while (!(s_slots[s_last].flags & OB2_SLOT_DIM_LAST)) ++s_last;
+        bool ok = true;
+        if (s_slots[first].kind != OB2_KIND_CATEGORICAL) {
+            for (int e = first; e <= s_last; ++e) {
+                const ob2_slot_desc &d = s_slots[e];
+                const char *col = cols + (int64_t)d.col_units * n_stride;
+                const double x = d.kind == OB2_KIND_INTEGER
+                                     ? __ll2double_rn(reinterpret_cast<const volatile long long *>(col)[i])
+                                     : reinterpret_cast<const volatile double *>(col)[i];
+                ok &= (x >= d.low) && (x < d.high);
             }
-            ok &= (x >= d.low) && (x < d.high);
-            if (WITH_FP) fp_add(t, d, w);
         }
+        if (!ok) {
+            if (WITH_FP) {
+                FpAcc old{0, 0};
+                for (int e = first; e <= s_last; ++e) {
+                    const ob2_slot_desc &d = s_slots[e];
+                    const char *col = cols + (int64_t)d.col_units * n_stride + (WITH_B ? bdelta : 0);
+                    const uint64_t w = d.kind == OB2_KIND_INTEGER
+                                           ? (uint64_t) reinterpret_cast<const volatile long long *>(col)[i]
+                                           : canon_f64(reinterpret_cast<const volatile double *>(col)[i]);
+                    fp_add(old, d, w);
+                }
+                acc.a -= old.a;
+                acc.b -= old.b;
+            }
+            FpAcc t{0, 0};
+            for (uint32_t a = 1; a < 4 && !ok; ++a) {
+                ok = true;
+                t = FpAcc{0, 0};
+                for (int e = first; e <= s_last; ++e) {
+                    const ob2_slot_desc &d = s_slots[e];
+                    const Philox4 r = philox4x32<ROUNDS>((uint32_t)index, (uint32_t)(index >> 32), (uint32_t)s_plan[e].block,
+                                                         a, k0, k1, pm0, pm1);
+                    const double u = s_plan[e].word ? u53(r.z, r.w) : u53(r.x, r.y);
+                    double x = draw_real<EXT>(d, u);
+                    char *col = cols + (int64_t)d.col_units * n_stride;
+                    char *dst = tcols + (int64_t)d.t_units * n_stride;
+                    uint64_t w;
+                    if (d.kind == OB2_KIND_INTEGER) {
+                        x = floor(x);
+                        const long long q = __double2ll_rz(x);
+                        reinterpret_cast<long long *>(col)[i] = q;
+                        long long bq = q;
+                        if (WITH_T) {
+                            if (d.t_op == OB2_OP_TO_REAL) {
+                                reinterpret_cast<double *>(dst)[i] = x;
+                                if (WITH_B) bq = quantize_ll(x, d.t_flags);
+                            } else {
+                                reinterpret_cast<long long *>(dst)[i] = q;
+                            }
+                        }
+                        if (WITH_B && bdelta != 0) reinterpret_cast<long long *>(col + bdelta)[i] = bq;
+                        w = (uint64_t)bq;
+                    } else {
+                        reinterpret_cast<double *>(col)[i] = x;
+                        double bx = x;
+                        if (WITH_T) {
+                            if (d.t_op == OB2_OP_QUANTIZE) {
+                                const long long tq = quantize_ll(x, d.t_flags);
+                                reinterpret_cast<long long *>(dst)[i] = tq;
+                                bx = __ll2double_rn(tq);
+                            } else {
+                                reinterpret_cast<double *>(dst)[i] = x;
+                            }
+                        }
+                        if (WITH_B && (bdelta != 0 || d.t_op == OB2_OP_QUANTIZE)) reinterpret_cast<double *>(col + bdelta)[i] = bx;
+                        w = canon_f64(WITH_B ? bx : x);
+                    }
+                    ok &= (x >= d.low) && (x < d.high);
+                    if (WITH_FP) fp_add(t, d, w);
+                }
+            }
+            if (WITH_FP) {
+                acc.a += t.a;
+                acc.b += t.b;
+            }
+            if (!ok && n_failed != nullptr) atomicAdd(n_failed + first, 1u);  // 4 misses: the reference raises "Improbable bounds"
+            all &= ok;
+        }
+        first = s_last + 1;
     }
-    if (WITH_FP) {
-        acc.a += t.a;
-        acc.b += t.b;
-    }
-    return Redrawn{acc, ok};
+    return Fixed{acc, all};
 }
 
 // Per-thread state of the slot walk (two candidates).  Column pointers are running pointers
 // advanced by 4 * n_stride / 8 * n_stride; the fingerprint accumulates straight into its lanes.
 struct Walk {
     FpAcc acc0, acc1;
-    bool ok0, ok1;    // current dimension
-    bool all0, all1;  // whole candidate
+    bool all0, all1;  // every bounds check so far passed (first attempt)
     char *col;        // element i0 of the current column (a 4-byte column is addressed at half the offset)
     char *tcol;
     Philox4 r0, r1;   // the current Philox block of the two candidates
@@ -174,8 +192,6 @@ struct WalkConst {  // loop invariants
     bool split, has1;
     uint64_t idx0, idx1;
     uint32_t k0, k1, pm0, pm1;
-    char *cols, *tcols;
-    uint32_t *n_failed;
 };
 
 // ---- what a drawn pair of values costs downstream: stores (sampled / transformed / handed-out), the
@@ -204,8 +220,8 @@ __device__ __forceinline__ void emit_real(const ob2_slot_desc &d, double x0, dou
         fp_add(w.acc1, d, canon_f64(bx1));
     }
     w.col += c.stride8;
-    w.ok0 &= (x0 >= d.low) & (x0 < d.high);  // half-open, space.py:164
-    w.ok1 &= (x1 >= d.low) & (x1 < d.high);
+    w.all0 &= (x0 >= d.low) & (x0 < d.high);  // half-open, space.py:164
+    w.all1 &= (x1 >= d.low) & (x1 < d.high);
 }
 
 // Integer slot from the floored double (general priors)
@@ -232,8 +248,8 @@ __device__ __forceinline__ void emit_int_f(const ob2_slot_desc &d, double x0, do
         fp_add(w.acc1, d, (uint64_t)bq1);
     }
     w.col += c.stride8;
-    w.ok0 &= (x0 >= d.low) & (x0 < d.high);
-    w.ok1 &= (x1 >= d.low) & (x1 < d.high);
+    w.all0 &= (x0 >= d.low) & (x0 < d.high);
+    w.all1 &= (x1 >= d.low) & (x1 < d.high);
 }
 
 // Integer slot from the exact integer (OB2_CLS_INT_MULHI: |q| < 2^21, in bounds by construction;
@@ -300,36 +316,6 @@ __device__ __forceinline__ void emit_cat(const ob2_slot_desc &d, int c0, int c1,
     }
 }
 
-// End of a dimension whose slots can miss their bounds: the <= 4-attempt redraw (cold).
-template <bool PHILOX, bool WITH_FP, bool WITH_T, bool WITH_B, bool EXT, int ROUNDS>
-__device__ __forceinline__ void dim_end(const ob2_slot_desc *s_slots, const ob2_slot_plan *s_plan, int s, Walk &w,
-                                        const WalkConst &c) {
-    if (!(s_slots[s].flags & OB2_SLOT_DIM_LAST)) return;
-    if (!(w.ok0 & w.ok1)) {  // cold: only Real/Integer slots can clear ok
-        if (PHILOX) {
-            if (!w.ok0) {
-                const Redrawn rd = redraw_dim<WITH_FP, WITH_T, WITH_B, EXT, ROUNDS>(
-                    s_slots, s_plan, s, c.idx0, c.i0, c.n_stride, c.cols, c.tcols, c.bdelta, c.k0, c.k1, c.pm0, c.pm1, w.acc0);
-                w.acc0 = rd.acc;
-                w.ok0 = rd.ok;
-            }
-            if (!w.ok1) {
-                const Redrawn rd = redraw_dim<WITH_FP, WITH_T, WITH_B, EXT, ROUNDS>(
-                    s_slots, s_plan, s, c.idx1, c.i0 + 1, c.n_stride, c.cols, c.tcols, c.bdelta, c.k0, c.k1, c.pm0, c.pm1, w.acc1);
-                w.acc1 = rd.acc;
-                w.ok1 = rd.ok;
-            }
-            if (c.n_failed != nullptr) {  // 4 misses: the reference raises "Improbable bounds"
-                const unsigned bad = (w.ok0 ? 0u : 1u) + ((w.ok1 || !c.has1) ? 0u : 1u);
-                if (bad) atomicAdd(c.n_failed + s_slots[s].dim_first, bad);
-            }
-        }
-        w.all0 &= w.ok0;
-        w.all1 &= w.ok1;
-        w.ok0 = w.ok1 = true;
-    }
-}
-
 // One slot through the general prior switch, from a pair of double uniforms (injected uniforms,
 // and in Philox mode the slots no specialised run takes: further priors, Integer over a real prior,
 // constants, categoricals whose thresholds do not fit 32 bits).
@@ -344,12 +330,12 @@ __device__ __forceinline__ void generic_slot(const ob2_slot_desc *s_slots, const
         const int c1 = draw_cat_fast(cdf, d.n_cats, u1, uni);
         emit_cat<WITH_FP, WITH_T, WITH_B>(d, c0, c1, w, c);
         if (!PHILOX) {  // an injected u >= 1 can run off the table; a Philox u cannot
-            w.ok0 &= c0 < d.n_cats;
-            w.ok1 &= c1 < d.n_cats;
+            w.all0 &= c0 < d.n_cats;
+            w.all1 &= c1 < d.n_cats;
         }
     } else {
-        double x0 = draw_real_call(d, u0);
-        double x1 = draw_real_call(d, u1);
+        double x0 = draw_real<EXT>(d, u0);
+        double x1 = draw_real<EXT>(d, u1);
         if (d.kind == OB2_KIND_INTEGER) {
             x0 = floor(x0);  // _Discrete.sample, space.py:294
             x1 = floor(x1);
@@ -358,7 +344,6 @@ __device__ __forceinline__ void generic_slot(const ob2_slot_desc *s_slots, const
             emit_real<WITH_FP, WITH_T, WITH_B>(d, x0, x1, w, c);
         }
     }
-    dim_end<PHILOX, WITH_FP, WITH_T, WITH_B, EXT, ROUNDS>(s_slots, s_plan, s, w, c);
 }
 
 // The Philox block `blk` of both candidates (attempt 0).
@@ -387,7 +372,6 @@ __device__ __forceinline__ void real_slot(const ob2_slot_desc *s_slots, const ob
     // base(u) * scale + loc, rounded multiply then rounded add (scipy rv_generic.rvs)
     emit_real<WITH_FP, WITH_T, WITH_B>(d, __dadd_rn(__dmul_rn(b0, d.scale), d.loc), __dadd_rn(__dmul_rn(b1, d.scale), d.loc),
                                        w, c);
-    dim_end<true, WITH_FP, WITH_T, WITH_B, EXT, ROUNDS>(s_slots, s_plan, e, w, c);
 }
 
 template <int CLS, bool WITH_FP, bool WITH_T, bool WITH_B, bool EXT, int ROUNDS>
@@ -497,12 +481,9 @@ __device__ __forceinline__ void sample_body(const ob2_slot_desc *s_slots, const 
     c.k1 = k1;
     c.pm0 = pm0;
     c.pm1 = pm1;
-    c.cols = cols;
-    c.tcols = tcols;
-    c.n_failed = n_failed;
     Walk w;
     w.acc0 = w.acc1 = FpAcc{0, 0};
-    w.ok0 = w.ok1 = w.all0 = w.all1 = true;
+    w.all0 = w.all1 = true;
     w.col = cols + i0 * 8;
     w.tcol = WITH_T ? tcols + i0 * 8 : nullptr;
     w.r0 = w.r1 = Philox4{0, 0, 0, 0};
@@ -556,13 +537,29 @@ __device__ __forceinline__ void sample_body(const ob2_slot_desc *s_slots, const 
 #undef OB2_RUN_ARGS
         }
     }
+    FpAcc acc0 = w.acc0, acc1 = w.acc1;
+    bool all0 = w.all0, all1 = w.all1 || !has1;
+    if (PHILOX && !(all0 & all1)) {  // cold: some dimension of this pair missed its bounds on the first attempt
+        if (!all0) {
+            const Fixed fx = fixup_candidate<WITH_FP, WITH_T, WITH_B, EXT, ROUNDS>(s_slots, s_plan, n_slots, idx0, i0, n_stride, cols,
+                                                                                   tcols, bdelta, k0, k1, pm0, pm1, acc0, n_failed);
+            acc0 = fx.acc;
+            all0 = fx.ok;
+        }
+        if (!all1) {
+            const Fixed fx = fixup_candidate<WITH_FP, WITH_T, WITH_B, EXT, ROUNDS>(s_slots, s_plan, n_slots, idx1, i0 + 1, n_stride,
+                                                                                   cols, tcols, bdelta, k0, k1, pm0, pm1, acc1, n_failed);
+            acc1 = fx.acc;
+            all1 = fx.ok;
+        }
+    }
     if (mask != nullptr) {
-        *reinterpret_cast<uchar2 *>(mask + i0) = make_uchar2(w.all0 ? 1 : 0, (w.all1 && has1) ? 1 : 0);
+        *reinterpret_cast<uchar2 *>(mask + i0) = make_uchar2(all0 ? 1 : 0, (all1 && has1) ? 1 : 0);
     }
     if (WITH_FP) {
         uint64_t lo0, hi0, lo1, hi1;
-        fp_finish(w.acc0, n_slots, lo0, hi0);
-        fp_finish(w.acc1, n_slots, lo1, hi1);
+        fp_finish(acc0, n_slots, lo0, hi0);
+        fp_finish(acc1, n_slots, lo1, hi1);
         if (!has1) lo1 = hi1 = 0;  // padding entry
         st_u64x4(fp + 2 * i0, lo0, hi0, lo1, hi1);
     }
@@ -713,16 +710,16 @@ struct SampleArgs {
 
 // Which instantiations exist (each is a large kernel; the build time is proportional to their number):
 //   Philox mode, tables in the launch parameters (spaces of up to OB2_PARAM_SLOTS slots): 5 output
-//     combinations x {10, 7} rounds;
-//   Philox mode, tables staged in shared memory (larger spaces): the 5 combinations, 10 rounds;
-//   injected uniforms (parity mode): shared-memory staging, with / without the fingerprint.
-// The further priors (draw_extended) are reached through an out-of-line call from the general slot
-// path only, so one instantiation serves every space.
-template <bool WITH_FP, bool WITH_T, bool WITH_B, int ROUNDS>
+//     combinations x {10 rounds, 7 rounds, 10 rounds with the further priors};
+//   Philox mode, tables staged in shared memory (larger spaces): the 5 combinations x {common, further priors};
+//   injected uniforms (parity mode): shared-memory staging, with / without the fingerprint, x the same two.
+// EXT = the space uses one of the further priors: their inverse CDFs sit behind an out-of-line call, and a
+// call anywhere in the walk costs the hot loops their register allocation, so the common kernels have none.
+template <bool WITH_FP, bool WITH_T, bool WITH_B, bool EXT, int ROUNDS>
 int launch_param(const SampleArgs &a, unsigned blocks) {
     const ob2_space *sp = a.sp;
     const int64_t bdelta = WITH_B ? (const char *)a.back - (const char *)a.cols : 0;
-    auto kern_p = sample_kernel_p<true, WITH_FP, WITH_T, WITH_B, true, ROUNDS>;
+    auto kern_p = sample_kernel_p<true, WITH_FP, WITH_T, WITH_B, EXT, ROUNDS>;
     static thread_local ob2_slot_table tbl;  // (29 KB: not on the stack)
     memcpy(tbl.s, sp->h_slots, (size_t)sp->n_slots * sizeof(ob2_slot_desc));
     memcpy(tbl.p, sp->h_plan, (size_t)sp->n_slots * sizeof(ob2_slot_plan));
@@ -737,11 +734,11 @@ int launch_param(const SampleArgs &a, unsigned blocks) {
     return ob2_check_cuda(cudaGetLastError(), "sample_kernel_p launch");
 }
 
-template <bool PHILOX, bool WITH_FP, bool WITH_T, bool WITH_B>
+template <bool PHILOX, bool WITH_FP, bool WITH_T, bool WITH_B, bool EXT>
 int launch_smem(const SampleArgs &a, unsigned blocks) {
     const ob2_space *sp = a.sp;
     const int64_t bdelta = WITH_B ? (const char *)a.back - (const char *)a.cols : 0;
-    auto kern = sample_kernel<PHILOX, WITH_FP, WITH_T, WITH_B, true, 10>;
+    auto kern = sample_kernel<PHILOX, WITH_FP, WITH_T, WITH_B, EXT, 10>;
     int rc = prepare_smem(kern, sp->smem_bytes);
     if (rc != OB2_OK) return rc;
     kern<<<blocks, OB2_BLOCK, sp->smem_bytes, static_cast<cudaStream_t>(a.stream)>>>(
@@ -754,18 +751,21 @@ int launch_smem(const SampleArgs &a, unsigned blocks) {
 template <bool WITH_FP, bool WITH_T, bool WITH_B>
 int launch_philox(const SampleArgs &a, unsigned blocks) {
     const ob2_space *sp = a.sp;
+    const bool ext = sp->has_extended_prior;  // a slot uses one of the further priors (draw_extended)
+    if (sp->philox_rounds != 10 && (ext || sp->n_slots > OB2_PARAM_SLOTS)) {
+        ob2_set_error("sample: %d-round Philox is built for spaces of up to %d slots over the uniform / loguniform / "
+                      "normal priors only", sp->philox_rounds, (int)OB2_PARAM_SLOTS);
+        return OB2_EINVAL;
+    }
     if (sp->n_slots <= OB2_PARAM_SLOTS && sp->h_slots != nullptr) {
         // Tables in the launch parameters: descriptor / plan / run fields become uniform loads from the
         // constant bank and the class branches are provably warp-uniform.
-        if (sp->philox_rounds == 7) return launch_param<WITH_FP, WITH_T, WITH_B, 7>(a, blocks);
-        return launch_param<WITH_FP, WITH_T, WITH_B, 10>(a, blocks);
+        if (ext) return launch_param<WITH_FP, WITH_T, WITH_B, true, 10>(a, blocks);
+        if (sp->philox_rounds == 7) return launch_param<WITH_FP, WITH_T, WITH_B, false, 7>(a, blocks);
+        return launch_param<WITH_FP, WITH_T, WITH_B, false, 10>(a, blocks);
     }
-    if (sp->philox_rounds != 10) {
-        ob2_set_error("sample: %d-round Philox is built for spaces of up to %d slots only", sp->philox_rounds,
-                      (int)OB2_PARAM_SLOTS);
-        return OB2_EINVAL;
-    }
-    return launch_smem<true, WITH_FP, WITH_T, WITH_B>(a, blocks);
+    return ext ? launch_smem<true, WITH_FP, WITH_T, WITH_B, true>(a, blocks)
+               : launch_smem<true, WITH_FP, WITH_T, WITH_B, false>(a, blocks);
 }
 
 template <bool PHILOX>
@@ -803,7 +803,9 @@ int launch_sample(const SampleArgs &a) {
     const unsigned b = (unsigned)blocks;
     const bool with_fp = a.fp != nullptr, with_t = a.tcols != nullptr;
     if (!PHILOX) {  // parity mode: ob2_sample_from_uniform (no transformed / handed-out outputs)
-        return with_fp ? launch_smem<false, true, false, false>(a, b) : launch_smem<false, false, false, false>(a, b);
+        if (a.sp->has_extended_prior)
+            return with_fp ? launch_smem<false, true, false, false, true>(a, b) : launch_smem<false, false, false, false, true>(a, b);
+        return with_fp ? launch_smem<false, true, false, false, false>(a, b) : launch_smem<false, false, false, false, false>(a, b);
     }
     if (a.back != nullptr) return launch_philox<true, true, true>(a, b);  // ob2_suggest: everything in the one pass
     if (with_fp && with_t) return launch_philox<true, true, false>(a, b);

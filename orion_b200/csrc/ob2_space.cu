@@ -209,8 +209,8 @@ extern "C" int ob2_space_create(const ob2_slot_desc *slots, int32_t n_slots, con
     // staged per block by the sampler: descriptors, draw plan, runs, cdf tables and their u32 thresholds
     const size_t smem = (size_t)n_slots * (sizeof(ob2_slot_desc) + sizeof(ob2_slot_plan) + sizeof(ob2_run)) +
                         (size_t)cdf_len * (sizeof(double) + sizeof(uint32_t));
-    if (smem > 200 * 1024) {
-        ob2_set_error("space needs %zu bytes of descriptor staging; the limit is 200 KiB", smem);
+    if (smem > 227 * 1024) {  // the most one thread block may allocate on sm_100
+        ob2_set_error("space needs %zu bytes of descriptor staging; the limit is 227 KiB", smem);
         return OB2_ETOOBIG;
     }
     ob2_space *sp = new (std::nothrow) ob2_space();

@@ -131,19 +131,19 @@ def test_determinism_across_runs():
 
 
 def test_wide_space_descriptor_limits():
-    """A space whose descriptor does not fit the 200 KiB staging limit is
+    """A space whose descriptor does not fit the 227 KiB staging limit (all the shared memory of one block) is
     refused with a clear error; a wide one below it works."""
     from orion_b200 import _lib
     from orion_b200.space import Real, Space
     space = Space()
     space.register(Real('x', 'uniform', 0, 1, shape=(1500,)))
-    batch = space.sample_columns(100, seed=1)                   # 1500 slots x 128 B = 187.5 KiB: fits
+    batch = space.sample_columns(100, seed=1)                   # 1500 slots x 152 B (descriptor + draw plan + run) = 223 KiB: fits
     assert bool(batch.mask[:100].all().item())
     big = Space()
     big.register(Real('x', 'uniform', 0, 1, shape=(1700,)))
     with pytest.raises(_lib.Ob2Error) as exc:
         big.compiled()
-    assert '200 KiB' in str(exc.value)
+    assert '227 KiB' in str(exc.value)
 
 
 def test_string_offered_to_a_numeric_dimension_raises_like_the_reference():
