@@ -71,19 +71,74 @@ __device__ __forceinline__ uint32_t pick_word(const Philox4 &r, uint32_t word) {
 
 // Real.sample (space.py:263-270): a draw that lands outside [low, high) is redrawn -- the whole
 // (possibly shaped) value of that dimension, up to 4 attempts.  The walk itself only ANDs the
-// bounds bits; a candidate that missed somewhere (rare) comes here afterwards, ONCE: every
-// Real / Integer dimension is re-checked from the values just written, and those that missed
-// are redrawn with attempts 1..3 (counter word 3), overwriting their columns with scalar
-// stores.  The fingerprint lanes are wrapping sums, so the contribution of the rejected values
-// is subtracted and the redrawn one added.  Out of line and everything by value: this is the
-// only call in the kernel, made when the walk's state is dead, so that the hot loops keep
-// their registers.  Only slots drawn from a 53-bit uniform can miss (the 32-bit classes are in
-// bounds by construction), so every slot redrawn here owns words (0, 1) or (2, 3) of its block.
+// bounds bits; a candidate that missed somewhere (rare) comes here afterwards, ONCE: the first
+// attempt of every Real / Integer dimension is recomputed (same arithmetic, nothing stored; not
+// read back, because with `back` aliased to `cols` a lossy Quantize has overwritten the draw),
+// and those that missed are redrawn with attempts 1..3 (counter word 3), overwriting their
+// columns with scalar stores.  The fingerprint lanes are wrapping sums, so the contribution of
+// the rejected values is subtracted and the redrawn one added.  Out of line and everything by
+// value: this is the only call in the kernel, made when the walk's state is dead, so that the
+// hot loops keep their registers.  Only slots drawn from a 53-bit uniform can miss (the 32-bit
+// classes are in bounds by construction), so every slot here owns words (0, 1) or (2, 3) of its block.
 // WITH_B: the fingerprint is over the handed-out row (`back`, at cols + bdelta), which is also rewritten.
 struct Fixed {
     FpAcc acc;
     bool ok;
 };
+
+// Attempt `a` of dimension [first, s_last] for one candidate: its values, optionally stored,
+// their fingerprint contribution in `t`; returns whether every element is in bounds.
+template <bool STORE, bool WITH_FP, bool WITH_T, bool WITH_B, bool EXT, int ROUNDS>
+__device__ __forceinline__ bool draw_dimension(const ob2_slot_desc *s_slots, const ob2_slot_plan *s_plan, int first, int s_last,
+                                               uint32_t a, uint64_t index, int64_t i, int64_t n_stride, char *cols, char *tcols,
+                                               int64_t bdelta, uint32_t k0, uint32_t k1, uint32_t pm0, uint32_t pm1, FpAcc &t) {
+    bool ok = true;
+    t = FpAcc{0, 0};
+    for (int e = first; e <= s_last; ++e) {
+        const ob2_slot_desc &d = s_slots[e];
+        const Philox4 r = philox4x32<ROUNDS>((uint32_t)index, (uint32_t)(index >> 32), (uint32_t)s_plan[e].block, a, k0, k1,
+                                             pm0, pm1);
+        const double u = s_plan[e].word ? u53(r.z, r.w) : u53(r.x, r.y);
+        double x = draw_real<EXT>(d, u);
+        char *col = cols + (int64_t)d.col_units * n_stride;
+        char *dst = tcols + (int64_t)d.t_units * n_stride;
+        uint64_t w;
+        if (d.kind == OB2_KIND_INTEGER) {
+            x = floor(x);
+            const long long q = __double2ll_rz(x);
+            if (STORE) reinterpret_cast<long long *>(col)[i] = q;
+            long long bq = q;
+            if (WITH_T) {
+                if (d.t_op == OB2_OP_TO_REAL) {
+                    if (STORE) reinterpret_cast<double *>(dst)[i] = x;
+                    if (WITH_B) bq = quantize_ll(x, d.t_flags);
+                } else if (STORE) {
+                    reinterpret_cast<long long *>(dst)[i] = q;
+                }
+            }
+            if (STORE && WITH_B && bdelta != 0) reinterpret_cast<long long *>(col + bdelta)[i] = bq;
+            w = (uint64_t)bq;
+        } else {
+            if (STORE) reinterpret_cast<double *>(col)[i] = x;
+            double bx = x;
+            if (WITH_T) {
+                if (d.t_op == OB2_OP_QUANTIZE) {
+                    const long long tq = quantize_ll(x, d.t_flags);
+                    if (STORE) reinterpret_cast<long long *>(dst)[i] = tq;
+                    bx = __ll2double_rn(tq);
+                } else if (STORE) {
+                    reinterpret_cast<double *>(dst)[i] = x;
+                }
+            }
+            if (STORE && WITH_B && (bdelta != 0 || d.t_op == OB2_OP_QUANTIZE)) reinterpret_cast<double *>(col + bdelta)[i] = bx;
+            w = canon_f64(WITH_B ? bx : x);
+        }
+        ok &= (x >= d.low) && (x < d.high);
+        if (WITH_FP) fp_add(t, d, w);
+    }
+    return ok;
+}
+
 template <bool WITH_FP, bool WITH_T, bool WITH_B, bool EXT, int ROUNDS>
 static __device__ __noinline__ Fixed fixup_candidate(const ob2_slot_desc *s_slots, const ob2_slot_plan *s_plan, int n_slots,
                                                      uint64_t index, int64_t i, int64_t n_stride, char *cols, char *tcols,
@@ -93,84 +148,26 @@ static __device__ __noinline__ Fixed fixup_candidate(const ob2_slot_desc *s_slot
     for (int first = 0; first < n_slots;) {
         int s_last = first;
         while (!(s_slots[s_last].flags & OB2_SLOT_DIM_LAST)) ++s_last;
-        bool ok = true;
-        if (s_slots[first].kind != OB2_KIND_CATEGORICAL) {
-            for (int e = first; e <= s_last; ++e) {
-                const ob2_slot_desc &d = s_slots[e];
-                const char *col = cols + (int64_t)d.col_units * n_stride;
-                const double x = d.kind == OB2_KIND_INTEGER
-                                     ? __ll2double_rn(reinterpret_cast<const volatile long long *>(col)[i])
-                                     : reinterpret_cast<const volatile double *>(col)[i];
-                ok &= (x >= d.low) && (x < d.high);
-            }
-        }
-        if (!ok) {
-            if (WITH_FP) {
-                FpAcc old{0, 0};
-                for (int e = first; e <= s_last; ++e) {
-                    const ob2_slot_desc &d = s_slots[e];
-                    const char *col = cols + (int64_t)d.col_units * n_stride + (WITH_B ? bdelta : 0);
-                    const uint64_t w = d.kind == OB2_KIND_INTEGER
-                                           ? (uint64_t) reinterpret_cast<const volatile long long *>(col)[i]
-                                           : canon_f64(reinterpret_cast<const volatile double *>(col)[i]);
-                    fp_add(old, d, w);
+        const uint32_t cls = s_plan[first].cls;
+        if (cls <= OB2_CLS_NORM || (cls == OB2_CLS_GENERIC && s_slots[first].kind != OB2_KIND_CATEGORICAL)) {
+            FpAcc t;
+            bool ok = draw_dimension<false, WITH_FP, WITH_T, WITH_B, EXT, ROUNDS>(s_slots, s_plan, first, s_last, 0u, index, i,
+                                                                                 n_stride, cols, tcols, bdelta, k0, k1, pm0, pm1, t);
+            if (!ok) {
+                if (WITH_FP) {  // the rejected first attempt leaves the fingerprint
+                    acc.a -= t.a;
+                    acc.b -= t.b;
                 }
-                acc.a -= old.a;
-                acc.b -= old.b;
-            }
-            FpAcc t{0, 0};
-            for (uint32_t a = 1; a < 4 && !ok; ++a) {
-                ok = true;
-                t = FpAcc{0, 0};
-                for (int e = first; e <= s_last; ++e) {
-                    const ob2_slot_desc &d = s_slots[e];
-                    const Philox4 r = philox4x32<ROUNDS>((uint32_t)index, (uint32_t)(index >> 32), (uint32_t)s_plan[e].block,
-                                                         a, k0, k1, pm0, pm1);
-                    const double u = s_plan[e].word ? u53(r.z, r.w) : u53(r.x, r.y);
-                    double x = draw_real<EXT>(d, u);
-                    char *col = cols + (int64_t)d.col_units * n_stride;
-                    char *dst = tcols + (int64_t)d.t_units * n_stride;
-                    uint64_t w;
-                    if (d.kind == OB2_KIND_INTEGER) {
-                        x = floor(x);
-                        const long long q = __double2ll_rz(x);
-                        reinterpret_cast<long long *>(col)[i] = q;
-                        long long bq = q;
-                        if (WITH_T) {
-                            if (d.t_op == OB2_OP_TO_REAL) {
-                                reinterpret_cast<double *>(dst)[i] = x;
-                                if (WITH_B) bq = quantize_ll(x, d.t_flags);
-                            } else {
-                                reinterpret_cast<long long *>(dst)[i] = q;
-                            }
-                        }
-                        if (WITH_B && bdelta != 0) reinterpret_cast<long long *>(col + bdelta)[i] = bq;
-                        w = (uint64_t)bq;
-                    } else {
-                        reinterpret_cast<double *>(col)[i] = x;
-                        double bx = x;
-                        if (WITH_T) {
-                            if (d.t_op == OB2_OP_QUANTIZE) {
-                                const long long tq = quantize_ll(x, d.t_flags);
-                                reinterpret_cast<long long *>(dst)[i] = tq;
-                                bx = __ll2double_rn(tq);
-                            } else {
-                                reinterpret_cast<double *>(dst)[i] = x;
-                            }
-                        }
-                        if (WITH_B && (bdelta != 0 || d.t_op == OB2_OP_QUANTIZE)) reinterpret_cast<double *>(col + bdelta)[i] = bx;
-                        w = canon_f64(WITH_B ? bx : x);
-                    }
-                    ok &= (x >= d.low) && (x < d.high);
-                    if (WITH_FP) fp_add(t, d, w);
+                for (uint32_t a = 1; a < 4 && !ok; ++a)
+                    ok = draw_dimension<true, WITH_FP, WITH_T, WITH_B, EXT, ROUNDS>(s_slots, s_plan, first, s_last, a, index, i,
+                                                                                   n_stride, cols, tcols, bdelta, k0, k1, pm0, pm1, t);
+                if (WITH_FP) {  // values of a 4-times-failed dimension stay as the last attempt
+                    acc.a += t.a;
+                    acc.b += t.b;
                 }
+                if (!ok && n_failed != nullptr) atomicAdd(n_failed + first, 1u);  // the reference raises "Improbable bounds"
+                all &= ok;
             }
-            if (WITH_FP) {
-                acc.a += t.a;
-                acc.b += t.b;
-            }
-            if (!ok && n_failed != nullptr) atomicAdd(n_failed + first, 1u);  // 4 misses: the reference raises "Improbable bounds"
-            all &= ok;
         }
         first = s_last + 1;
     }
