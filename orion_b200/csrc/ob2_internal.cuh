@@ -195,27 +195,73 @@ __device__ __forceinline__ double u53(uint32_t w0, uint32_t w1) {
 // 100) takes the tail branch.  Coefficients and their error bounds (<= 5e-16 relative against
 // 50-digit arithmetic): ob2_ndtri_coef.h, generated by benchmarks/fit/fit_ndtri.py.  CUDA's
 // normcdfinv costs ~2.3x the instructions because most warps execute both of its regions.
+// (coefficient tables in constant memory: a DFMA then takes its coefficient straight from the
+// constant bank; as immediates every 64-bit coefficient costs two extra move instructions)
+#define OB2_COEF(c) c,
+static __constant__ double ob2_ndtri_central[OB2_NDTRI_CENTRAL_N] = {OB2_NDTRI_CENTRAL(OB2_COEF)};
+static __constant__ double ob2_ndtri_tail[OB2_NDTRI_TAIL_N] = {OB2_NDTRI_TAIL(OB2_COEF)};
+static __constant__ double ob2_ndtri_far[OB2_NDTRI_FAR_N] = {OB2_NDTRI_FAR(OB2_COEF)};
+#undef OB2_COEF
+// 1/13!, 1/12!, ..., 1/2!, 1, 1
+static __constant__ double ob2_exp_taylor[14] = {1.6059043836821613e-10, 2.08767569878681e-09, 2.505210838544172e-08,
+                                                 2.755731922398589e-07,  2.7557319223985893e-06, 2.48015873015873e-05,
+                                                 1.984126984126984e-04,  1.388888888888889e-03,  8.333333333333333e-03,
+                                                 4.1666666666666664e-02, 1.6666666666666666e-01, 0.5,
+                                                 1.0,                    1.0};
+
+// log(t) for a normal, positive, finite t (the caller checks): the classic split t = 2^k m,
+// m in [sqrt(1/2), sqrt(2)), s = (m - 1) / (m + 1), log m = 2 s + s^3 R(s^2) with the degree-7 minimax
+// R of W. Kahan's fdlibm e_log.c (error < 1 ulp).  The division is a reciprocal estimate and two
+// Newton steps; no special cases -- CUDA's log() spends ~80 instructions, this ~35.
+__device__ __forceinline__ double ob2_log_normal(double t) {
+    int hi = __double2hiint(t);
+    int k = (hi >> 20) - 1023;
+    hi = (hi & 0x000FFFFF) | 0x3FF00000;
+    if (hi >= 0x3FF6A09F) {  // m >= sqrt(2): halve it
+        hi -= 0x00100000;
+        ++k;
+    }
+    const double f = __hiloint2double(hi, __double2loint(t)) - 1.0;
+    const double den = 2.0 + f;
+    double rcp;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(rcp) : "d"(den));
+    rcp = fma(rcp, fma(-den, rcp, 1.0), rcp);
+    rcp = fma(rcp, fma(-den, rcp, 1.0), rcp);
+    const double s = f * rcp;
+    const double z = s * s, w = z * z;
+    const double t1 = w * fma(w, fma(w, 1.531383769920937332e-01, 2.222219843214978396e-01), 3.999999999940941908e-01);
+    const double t2 = z * fma(w, fma(w, fma(w, 1.479819860511658591e-01, 1.818357216161805012e-01), 2.857142874366239149e-01),
+                              6.666666666666735130e-01);
+    const double R = t2 + t1, hfsq = 0.5 * f * f, dk = __int2double_rn(k);
+    return fma(dk, 6.93147180369123816490e-01, -((hfsq - fma(s, hfsq + R, dk * 1.90821492927058770002e-10)) - f));
+}
+
 __device__ __forceinline__ double ob2_ndtri(double u) {
     const double t = u * (1.0 - u);
     const double x = fma(2.0, u, -1.0);
     if (!(t > 0.0)) return u == 0.0 ? -CUDART_INF : (u == 1.0 ? CUDART_INF : CUDART_NAN);
-    const double w = -(log(t) + 1.3862943611198906);  // -log(4 t)
-    double p = 0.0;
-#define OB2_HORNER(c) p = fma(p, z, c);
+    // -log(4 t); a denormal t (u below 2^-1022: injected uniforms only) takes the library log
+    const double w = -((t >= 2.2250738585072014e-308 ? ob2_log_normal(t) : log(t)) + 1.3862943611198906);
+    double p;
     if (w < OB2_NDTRI_W_SPLIT) {
         const double z = w - OB2_NDTRI_W_MID;
-        OB2_NDTRI_CENTRAL(OB2_HORNER)
+        p = ob2_ndtri_central[0];
+#pragma unroll
+        for (int i = 1; i < OB2_NDTRI_CENTRAL_N; ++i) p = fma(p, z, ob2_ndtri_central[i]);
     } else {  // about 3 warps in 100 come here
         const double s = sqrt(w);
         if (s <= OB2_NDTRI_S_MAX) {
             const double z = s - OB2_NDTRI_S_MID;
-            OB2_NDTRI_TAIL(OB2_HORNER)
+            p = ob2_ndtri_tail[0];
+#pragma unroll 1
+            for (int i = 1; i < OB2_NDTRI_TAIL_N; ++i) p = fma(p, z, ob2_ndtri_tail[i]);
         } else {  // u < 2^-53: only an injected uniform is that small
             const double z = s - OB2_NDTRI_F_MID;
-            OB2_NDTRI_FAR(OB2_HORNER)
+            p = ob2_ndtri_far[0];
+#pragma unroll 1
+            for (int i = 1; i < OB2_NDTRI_FAR_N; ++i) p = fma(p, z, ob2_ndtri_far[i]);
         }
     }
-#undef OB2_HORNER
     return x * p;
 }
 
@@ -229,20 +275,9 @@ __device__ __forceinline__ double ob2_exp_bounded(double y) {
     const double kd = shifted - 6755399441055744.0;
     double r = fma(kd, -6.93147180369123816490e-01, y);
     r = fma(kd, -1.90821492927058770002e-10, r);
-    double p = 1.6059043836821613e-10;  // 1/13!
-    p = fma(p, r, 2.08767569878681e-09);
-    p = fma(p, r, 2.505210838544172e-08);
-    p = fma(p, r, 2.755731922398589e-07);
-    p = fma(p, r, 2.7557319223985893e-06);
-    p = fma(p, r, 2.48015873015873e-05);
-    p = fma(p, r, 1.984126984126984e-04);
-    p = fma(p, r, 1.388888888888889e-03);
-    p = fma(p, r, 8.333333333333333e-03);
-    p = fma(p, r, 4.1666666666666664e-02);
-    p = fma(p, r, 1.6666666666666666e-01);
-    p = fma(p, r, 0.5);
-    p = fma(p, r, 1.0);
-    p = fma(p, r, 1.0);
+    double p = ob2_exp_taylor[0];
+#pragma unroll
+    for (int i = 1; i < 14; ++i) p = fma(p, r, ob2_exp_taylor[i]);
     return __hiloint2double(__double2hiint(p) + (k << 20), __double2loint(p));
 }
 
@@ -546,11 +581,16 @@ struct FpAcc {
 // 64x64 -> 128-bit product.  Lanes are wrapping sums over slots, so any partition
 // of the slots over threads gives the same fingerprint, and a contribution can
 // be subtracted again (the redraw path does).
+__device__ __forceinline__ uint64_t mad_wide(uint32_t a, uint32_t b, uint64_t c) {  // a * b + c, one IMAD.WIDE.U32
+    uint64_t r;
+    asm("mad.wide.u32 %0, %1, %2, %3;" : "=l"(r) : "r"(a), "r"(b), "l"(c));
+    return r;
+}
 __device__ __forceinline__ void fp_add(FpAcc &acc, const ob2_slot_desc &d, uint64_t w) {
     const uint64_t x = w ^ d.hk[0];
     const uint32_t xl = (uint32_t)x, xh = (uint32_t)(x >> 32);
-    acc.a += (uint64_t)xl * (uint32_t)d.hk[1] + (uint64_t)xh * (uint32_t)(d.hk[1] >> 32);
-    acc.b += (uint64_t)xl * (uint32_t)d.hk[2] + (uint64_t)xh * (uint32_t)(d.hk[2] >> 32);
+    acc.a = mad_wide(xh, (uint32_t)(d.hk[1] >> 32), mad_wide(xl, (uint32_t)d.hk[1], acc.a));
+    acc.b = mad_wide(xh, (uint32_t)(d.hk[2] >> 32), mad_wide(xl, (uint32_t)d.hk[2], acc.b));
 }
 __device__ __forceinline__ void fp_finish(const FpAcc &acc, int n_slots, uint64_t &lo, uint64_t &hi) {
     lo = fmix64(acc.a ^ ((uint64_t)n_slots * 0x9E3779B97F4A7C15ull));
