@@ -74,6 +74,10 @@ def parse_args():
                          'the reference when it is staged')
     ap.add_argument('--ref-literal-cands', type=int, default=96,
                     help='--impl reference with oracle/_ref: candidates per process per step through the unmodified reference')
+    ap.add_argument('--three-buffers', action='store_true',
+                    help='keep the pre-transform draw in a buffer of its own beside the handed-out rows (448 B/candidate '
+                         'more to write; under the real requirement the two are equal bit for bit).  Default: ob2_suggest '
+                         'with back == cols')
     ap.add_argument('--staged', action='store_true',
                     help='sample+transform, reverse+fingerprint and dedup as separate kernels (the path of an '
                          'algorithm that computes in the transformed space) instead of the one-kernel ob2_suggest')
@@ -283,6 +287,10 @@ def workload_config(args, world):
         "workload": WORKLOADS[args.workload],
         "candidates_per_gpu_per_step": args.cands, "history_rows_per_gpu": args.history,
         "planted_duplicates": "10% history rows, 1% earlier rows of the batch",
+        "materialised_per_candidate": ("sampled columns, mask, fingerprint, keep" if args.workload == 'cfg5' else
+                                       "transformed columns, handed-out (reversed) rows, mask, fingerprint, keep"
+                                       + (", and the pre-transform draw in its own buffer" if args.three_buffers else
+                                          " (the pre-transform draw shares the handed-out rows' buffer: equal bit for bit)")),
         "parallelism": "dp%d (candidates sharded by counter; history hash set sharded by fingerprint)" % world,
         "l2": "inputs larger than L2 (>= 5.6 GB touched per kernel)",
     }
@@ -659,7 +667,11 @@ def run_b200(args):
     from orion_b200.pipeline import CandidatePipeline
     # default: ob2_suggest, ONE kernel for sample -> transform -> reverse -> fingerprint (Random.suggest fast path)
     one_kernel = not (args.staged or args.unfused or args.fp_in_sampler) and not cfg5_main
-    pipe = CandidatePipeline(compiled, sharded, n, depth=2,
+    # Random.suggest behind PrimaryAlgo hands out the reversed rows and lets the algorithm see the transformed
+    # ones; the draw before the transform is an intermediate.  By default it therefore shares its buffer with
+    # the handed-out rows (ob2_suggest, back == cols); --three-buffers materialises it separately as well.
+    alias = one_kernel and not args.three_buffers
+    pipe = CandidatePipeline(compiled, sharded, n, depth=2, alias_back=alias,
                              fingerprint_in='sample_only' if cfg5_main else 'suggest' if one_kernel
                              else 'sample' if args.fp_in_sampler else 'reverse')
     batch, tbatch, back = pipe.slots[0].batch, pipe.slots[0].tbatch, pipe.slots[0].back
@@ -677,6 +689,7 @@ def run_b200(args):
     step_launches = (3 if (one_kernel or cfg5_main) else 4 if fused else 5) + exchange_launches    # dedup = 2 launches
     ev = [[torch.cuda.Event(enable_timing=True) for _ in range(len(kernel_names) + 1)] for _ in range(K)]
     launches = [0]
+    stage = {'back': back}          # where the staged comparison pass reverses into (a buffer of its own if `alias`)
 
     def cfg5_step(idx, events=None):
         """BASELINE.json config 5 as written: sample (fused contains + fingerprint) -> dedup."""
@@ -713,10 +726,11 @@ def run_b200(args):
             compiled.transform(batch, out=tbatch)
         if events:
             events[j].record()
-        compiled.reverse(tbatch, out=back, with_fingerprint=fp_in_reverse)
+        sback = stage['back']
+        compiled.reverse(tbatch, out=sback, with_fingerprint=fp_in_reverse)
         if events:
             events[j + 1].record()
-        sharded.dedup(back.fp if fp_in_reverse else batch.fp, n, per_rank_n=n, keep=batch.keep, check=False)
+        sharded.dedup(sback.fp if fp_in_reverse else batch.fp, n, per_rank_n=n, keep=batch.keep, check=False)
         if events:
             events[j + 2].record()
         launches[0] += (4 if fused else 5) + exchange_launches
@@ -782,7 +796,7 @@ def run_b200(args):
     # ---- checks on the last timed step (outside the timed region)
     kept_last = int(last_batch.keep[:n].sum().item())
     mask_ok = bool(last_batch.mask[:n].all().item())
-    round_trip_ok = True if cfg5_main else bool(torch.equal(last_back.buf, last_batch.buf))
+    round_trip_ok = None if (cfg5_main or alias) else bool(torch.equal(last_back.buf, last_batch.buf))
     want = expected_keep(index_dev[W + K - 1])
     keep_mask_exact = all_ranks_true(bool(torch.equal(last_batch.keep[:n].bool(), want)))
     del want
@@ -808,7 +822,25 @@ def run_b200(args):
     # ---- for comparison: the same K steps through the separate kernels (what an algorithm that works in the
     # transformed space pays: the transformed columns are read back by reverse), one stream
     staged_info = None
+    three_info = None
     if one_kernel:
+        if alias:       # the staged kernels (and the three-buffer suggest) need the separate buffer after all
+            stage['back'] = compiled.empty_columns(n)
+            last_rows = batch.buf.clone()
+            last_serial = (W + KR - 1) if pipelined else (W + K - 1)
+            compiled.suggest(n, SEED, index=index_dev[last_serial], out=batch, transformed_out=tbatch, back_out=stage['back'])
+            # the one-buffer suggest wrote the same handed-out rows as the three-buffer one, and draw == handed-out
+            round_trip_ok = bool(torch.equal(stage['back'].buf, last_rows)) and bool(torch.equal(stage['back'].buf, batch.buf))
+            del last_rows
+            tev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+            for j in range(3):
+                tev[j].record()
+                compiled.suggest(n, SEED, index=index_dev[W], out=batch, transformed_out=tbatch, back_out=stage['back'])
+            tev[3].record()
+            torch.cuda.synchronize()
+            three_info = {"ms": min(tev[j].elapsed_time(tev[j + 1]) for j in range(3)),
+                          "bytes_per_candidate": BYTES_SUGGEST_COMPULSORY,
+                          "note": "ob2_suggest with the pre-transform draw in a buffer of its own (--three-buffers)"}
         sev = [[torch.cuda.Event(enable_timing=True) for _ in range(len(staged_names) + 1)] for _ in range(KS)]
         for s in range(KS):
             index_dev[W + s] = step_index(W + K + KR + s)
@@ -988,7 +1020,8 @@ def run_b200(args):
     yard = {'sample': BYTES_SAMPLE, 'transform': BYTES_TRANSFORM, 'reverse': BYTES_REVERSE, 'dedup': BYTES_DEDUP,
             'sample+transform': BYTES_SAMPLE + BYTES_TRANSFORM, 'reverse+fingerprint': BYTES_REVERSE,
             'suggest': BYTES_SAMPLE + BYTES_TRANSFORM + BYTES_REVERSE, 'sample+fingerprint': BYTES_SAMPLE}
-    compulsory = dict(yard, **{'suggest': BYTES_SUGGEST_COMPULSORY, 'sample+fingerprint': BYTES_SAMPLE_FP_COMPULSORY,
+    compulsory = dict(yard, **{'suggest': BYTES_SUGGEST_COMPULSORY - (448 if alias else 0),
+                               'sample+fingerprint': BYTES_SAMPLE_FP_COMPULSORY,
                                'sample+transform': 448 + 1408 + 1, 'reverse+fingerprint': 1408 + 448 + 16})
     yard = {k: yard[k] for k in kernel_names}
     dominant = max(per_kernel_ms, key=per_kernel_ms.get)
@@ -1010,9 +1043,9 @@ def run_b200(args):
         "roofline": {"bound": "hbm", "kernel": dominant, "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                      "algorithmic_bytes_per_candidate": compulsory[dominant],
-                     "algorithmic_bytes_note": "what this kernel must move: every API-visible result written once "
-                                               "(suggest: sampled 448 + transformed 1408 + handed-out 448 + fingerprint 16 "
-                                               "+ mask 1), nothing re-read",
+                     "algorithmic_bytes_note": "what this kernel must move: every API-visible result written once, nothing "
+                                               "re-read (suggest: transformed 1408 + handed-out 448 + fingerprint 16 + mask 1"
+                                               + (")" if alias else " + the pre-transform draw 448)"),
                      # SURVEY.md 8d's per-stage figure, which also counts the re-reads a staged path pays
                      # (fusion removed them, hence > 1 for the fused kernel): kept beside, never as `frac`
                      "yardstick_bytes_per_candidate": yard[dominant],
@@ -1033,7 +1066,7 @@ def run_b200(args):
                          if pipelined else "K steps on one stream, kernels back to back"),
         "serial_ms_per_step": serial_ms,
         "kernels_in_timed_region_ms": contended_ms,
-        "staged_path": staged_info,
+        "staged_path": staged_info, "suggest_three_buffers": three_info,
         "cfg5": cfg5_info, "cfg2": cfg2_info, "sustained": sustained,
         "history_table": {"slots": history.n_slots, "bytes": history.n_slots * 32,
                           "load_at_end": hist_rows1 / float(history.n_slots)},

@@ -374,6 +374,20 @@ __device__ __forceinline__ void real_slot(const ob2_slot_desc *s_slots, const ob
 template <int CLS, bool WITH_FP, bool WITH_T, bool WITH_B, bool EXT, int ROUNDS>
 __device__ __forceinline__ void run_real(const ob2_slot_desc *s_slots, const ob2_slot_plan *s_plan, int s, int end,
                                          Walk &w, const WalkConst &c) {
+    if (WITH_T) {
+        // store-heavy variants: ONE copy of the slot body, its words selected by the slot's position in the
+        // block (a warp-uniform predicate) -- the pairwise form below costs these kernels registers
+        // (suggest 4.25 -> 4.41 ms) where it gains the plain sampler 2 %
+#pragma unroll 1
+        for (; s < end; ++s) {
+            const bool first = s_plan[s].word == 0;
+            if (first) new_block<ROUNDS>(s_plan[s].block, w, c);
+            const double u0 = first ? u53(w.r0.x, w.r0.y) : u53(w.r0.z, w.r0.w);
+            const double u1 = first ? u53(w.r1.x, w.r1.y) : u53(w.r1.z, w.r1.w);
+            real_slot<CLS, WITH_FP, WITH_T, WITH_B, EXT, ROUNDS>(s_slots, s_plan, s, u0, u1, w, c);
+        }
+        return;
+    }
     if (s < end && s_plan[s].word != 0) {  // the run begins in the second half of a block another class opened
         real_slot<CLS, WITH_FP, WITH_T, WITH_B, EXT, ROUNDS>(s_slots, s_plan, s, u53(w.r0.z, w.r0.w), u53(w.r1.z, w.r1.w), w, c);
         ++s;

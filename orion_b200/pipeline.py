@@ -33,14 +33,16 @@ from .dist import ShardedHistory
 class BatchSlot(object):
     """One set of buffers travelling through the pipeline."""
 
-    def __init__(self, compiled, n, sample_only=False):
+    def __init__(self, compiled, n, sample_only=False, alias_back=False):
         dev = compiled.device
         self.batch = compiled.empty_columns(n)                      # original columns + mask + fp + keep
         if sample_only:                                             # no transform chain: the draws are the rows handed out
             self.tbatch, self.back = None, self.batch
         else:
             self.tbatch = compiled.empty_columns(n, transformed=True)   # transform(sample)
-            self.back = compiled.empty_columns(n)                       # reverse(transform(sample))
+            # reverse(transform(sample)): the rows handed out.  alias_back: ONE buffer for them and the draw
+            # (ob2_suggest with back == cols) -- the pre-transform draw is an intermediate nobody is handed
+            self.back = self.batch if alias_back else compiled.empty_columns(n)
         self.batch.keep = torch.empty(self.batch.n_stride, dtype=torch.uint8, device=dev)
         self.sampled = torch.cuda.Event()
         self.reversed = torch.cuda.Event()
@@ -52,7 +54,7 @@ class BatchSlot(object):
 class CandidatePipeline(object):
     """sample+transform -> (reverse || dedup) over a ring of ``depth`` buffer sets."""
 
-    def __init__(self, compiled, history, n, depth=2, timed=False, fingerprint_in='reverse'):
+    def __init__(self, compiled, history, n, depth=2, timed=False, fingerprint_in='reverse', alias_back=False):
         # 'reverse': the fingerprints are computed by the (bandwidth-bound) reverse kernel over the rows it
         # writes -- the candidates as handed out; 'sample': by the (issue-bound) sampler over its draws
         # 'suggest': ONE kernel (ob2_suggest) samples, transforms, reverses in registers and fingerprints --
@@ -67,7 +69,8 @@ class CandidatePipeline(object):
         self.n = n
         # a ShardedHistory / PeerShardedHistory is used as is; a bare TrialHistory is wrapped
         self.sharded = history if hasattr(history, 'world') else ShardedHistory(history, device=compiled.device)
-        self.slots = [BatchSlot(compiled, n, sample_only=self.sample_only) for _ in range(depth)]
+        assert not alias_back or fingerprint_in == 'suggest', "only the one-kernel suggest can write both rows into one buffer"
+        self.slots = [BatchSlot(compiled, n, sample_only=self.sample_only, alias_back=alias_back) for _ in range(depth)]
         dev = compiled.device
         # The dedup kernels are latency bound (random 32-byte probes) and tiny next to the
         # streaming ones; at equal priority their blocks queue behind the ~24k blocks of
