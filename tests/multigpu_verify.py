@@ -168,7 +168,7 @@ def main():
         sc = small.compiled()
         m = 200_000
         for exchange in exchanges:
-            history = TrialHistory(sc, capacity=1 << 16)
+            history = TrialHistory(sc, capacity=1 << 21)         # (the worst-case lanes of the fallback count as incoming rows)
             sharded = make_sharded_history(history, max_n=m, exchange=exchange)
             used = 'peer' if isinstance(sharded, PeerShardedHistory) else 'nccl'
             b = sc.sample(m, SEED + 7, base_index=rank * m, with_fingerprint=True)
