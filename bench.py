@@ -428,6 +428,52 @@ class SmiClocks(object):
         return out
 
 
+def bind_to_gpu_cpus(local_rank):
+    """CPU affinity of this process := the CPUs NVML names as local to its GPU, so that pinned host
+    buffers allocated afterwards are first touched on that GPU's NUMA node.  Returns the number of
+    CPUs, or None when NVML cannot tell."""
+    try:
+        import pynvml
+        import torch
+        pynvml.nvmlInit()
+        uuid = str(torch.cuda.get_device_properties(local_rank).uuid)
+        handle = None
+        for i in range(pynvml.nvmlDeviceGetCount()):
+            h = pynvml.nvmlDeviceGetHandleByIndex(i)
+            u = pynvml.nvmlDeviceGetUUID(h)
+            u = u.decode() if isinstance(u, bytes) else u
+            if uuid in u:
+                handle = h
+        if handle is None:
+            return None
+        words = pynvml.nvmlDeviceGetCpuAffinity(handle, (os.cpu_count() + 63) // 64)
+        cpus = [64 * w + b for w, word in enumerate(words) for b in range(64) if (word >> b) & 1]
+        allowed = set(os.sched_getaffinity(0))
+        cpus = [c for c in cpus if c in allowed]
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return len(cpus)
+    except Exception:
+        return None
+
+
+def d2h_ceiling(world):
+    """Measured device -> pinned-host copy ceiling for `world` GPUs at once (benchmarks/pcie_probe.py,
+    kept in profiles/pcie_probe.json), or None."""
+    path = os.path.join(ROOT, 'profiles', 'pcie_probe.json')
+    if not os.path.exists(path):
+        return None
+    try:
+        entry = json.load(open(path)).get(str(world))
+    except ValueError:
+        return None
+    if not entry:
+        return None
+    best = max(entry[k]['aggregate_GBps'] for k in ('unbound', 'gpu_local_cpus') if k in entry)
+    return {"aggregate_GBps": best, "source": "profiles/pcie_probe.json (benchmarks/pcie_probe.py, %d GPUs at once)" % world}
+
+
 def csrc_sha16():
     """Hash of the kernel sources: stamps every ncu-derived figure kept in profiles/."""
     import glob
@@ -918,6 +964,8 @@ def run_b200(args):
     e2e = None
     if args.e2e_steps > 0:
         E = args.e2e_steps
+        affinity0 = os.sched_getaffinity(0)
+        cpus_bound = bind_to_gpu_cpus(local_rank)          # pinned buffers below: first touched NUMA-local to this GPU
         host_idx = [torch.empty(n, dtype=torch.int64).pin_memory() for _ in range(E + 2)]
         for j, h in enumerate(host_idx):
             h.copy_(step_index(W + K + KR + KS + K5_used + j))
@@ -933,6 +981,9 @@ def run_b200(args):
         out_row = compiled.wire_row_bytes if wire else compiled.row_bytes
         host_cols = [torch.empty(out_row * ns, dtype=torch.uint8).pin_memory() for _ in range(2)]
         host_cnt = [torch.zeros(1, dtype=torch.int64).pin_memory() for _ in range(2)]
+        for h in host_cols:
+            h.zero_()                                      # first touch while bound
+        os.sched_setaffinity(0, affinity0)                 # (the CPU baseline later wants every core again)
         dense = [compiled.empty_columns(n, wire=wire) for _ in range(2)]
         cnt_dev = [torch.zeros(1, dtype=torch.int64, device=dev) for _ in range(2)]
         cscratch = [torch.empty(max(int(compiled.lib.ob2_compact_scratch_bytes(n)), 8), dtype=torch.uint8, device=dev)
@@ -951,9 +1002,8 @@ def run_b200(args):
             compacted[b].synchronize()              # the host needs n_kept; the GPU already works on the next step
             k = int(host_cnt[b][0])
             with torch.cuda.stream(s_copy):
-                for units, dt in out_meta:
-                    start, nbytes = units * ns, k * _SIZE[dt]
-                    host_cols[b][start:start + nbytes].copy_(dense[b].buf[start:start + nbytes], non_blocking=True)
+                # the survivors' rows of every column: ob2_columns_to_host, one 2-D copy per run of equal-width columns
+                dense[b].copy_rows_to_host(host_cols[b], k)
                 copied[b].record()
             state['d2h'] += k * out_row + 8
             state['kept'] = k
@@ -1005,11 +1055,14 @@ def run_b200(args):
                "d2h_bytes_per_step": int(state['d2h'] // max(E, 1)),
                "steps": args.e2e_steps, "kept_last_step": state['kept'],
                "d2h_GBps_per_gpu": state['d2h'] / (e2e_ms * 1e-3) / 1e9,
+               "d2h_ceiling": d2h_ceiling(world), "host_cpus_bound_per_rank": cpus_bound,
                "api": "CandidatePipeline.submit(counters copied from pinned host) -> "
                       + ("sample+fingerprint -> dedup " if cfg5_main else "suggest (one kernel) -> dedup " if one_kernel
                          else "sample+transform -> reverse || dedup ") +
                       "-> ob2_compact" + ("_wire" if wire else "") + " -> surviving candidates' columns copied to pinned host (copies overlap the next step)"}
 
+    if e2e and e2e.get("d2h_ceiling"):
+        e2e["frac_of_d2h_ceiling"] = world * e2e["d2h_GBps_per_gpu"] / e2e["d2h_ceiling"]["aggregate_GBps"]
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()

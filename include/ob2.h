@@ -320,6 +320,16 @@ int ob2_compact_wire(const ob2_space *space, int64_t n, int64_t n_stride, const 
                      const uint8_t *keep, int64_t out_stride, void *out_cols, void *scratch,
                      uint64_t *n_kept, void *stream);
 
+/* ... and their way to the host: copy the first n_rows of every column of a device column block
+ * (layout 0 = original, 1 = transformed, 2 = wire; stride src_stride) into a HOST block of the same
+ * layout with stride dst_stride, asynchronously on `stream` (pin the host block for a true async
+ * copy).  Runs of adjacent equal-width columns go as one 2-D copy each, so a compacted batch of
+ * k survivors crosses PCIe as k * row_bytes bytes in 2-3 transfers -- what
+ * Experiment.register_trials then turns into trial documents
+ * (src/orion/core/worker/experiment.py:216-228). */
+int ob2_columns_to_host(const ob2_space *space, int32_t layout, int64_t n_rows, int64_t src_stride,
+                        const void *src_cols, int64_t dst_stride, void *dst_cols, void *stream);
+
 /* Multi-GPU exchange helpers: owner rank of a fingerprint is
  * fp.hi % n_ranks.  bucket writes (fp, global order key) into
  * out_fp[n_ranks][cap][2] / out_key[n_ranks][cap], zero-pads each bucket's

@@ -86,6 +86,7 @@ SIGNATURES = {
     'ob2_space_wire_layout': (ctypes.c_int, [_vp, ctypes.POINTER(_i32), ctypes.POINTER(_i32)]),
     'ob2_compact_wire': (ctypes.c_int, [_vp, _i64, _i64, _vp, _vp, _i64, _vp, _vp, _vp, _vp]),
     'ob2_compact': (ctypes.c_int, [_vp, _i64, _i64, _vp, _vp, _i32, _i64, _vp, _vp, _vp, _vp]),
+    'ob2_columns_to_host': (ctypes.c_int, [_vp, _i32, _i64, _i64, _vp, _i64, _vp, _vp]),
     'ob2_bucket_by_owner': (ctypes.c_int, [_i64, _vp, _u32, _i32, _i64, _vp, _vp, _vp, _vp, _vp]),
     'ob2_scatter_verdict': (ctypes.c_int, [_i64, _vp, _vp, _vp, _vp, _vp]),
     'ob2_xchg_create': (ctypes.c_int, [_i32, _i32, _i64, ctypes.POINTER(_vp)]),

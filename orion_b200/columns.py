@@ -139,6 +139,21 @@ class ColumnBatch(object):
             dest.n = int(count.item())
         return dest
 
+    def copy_rows_to_host(self, host_buf, n_rows=None, host_stride=None):
+        """Asynchronously copy the first ``n_rows`` of every column into ``host_buf`` (a pinned
+        uint8 tensor laid out like this batch with stride ``host_stride``, default the batch's):
+        ``ob2_columns_to_host`` -- 2-3 two-dimensional copies, whatever the number of columns."""
+        import ctypes
+        from . import _lib
+        c = self.compiled
+        n_rows = self.n if n_rows is None else int(n_rows)
+        host_stride = self.n_stride if host_stride is None else int(host_stride)
+        layout = 2 if self.wire else (1 if self.transformed else 0)
+        stream = ctypes.c_void_p(torch.cuda.current_stream(c.device).cuda_stream)
+        _lib.check(c.lib.ob2_columns_to_host(c.handle, layout, n_rows, self.n_stride, self.buf.data_ptr(),
+                                             host_stride, host_buf.data_ptr(), stream))
+        return host_buf
+
     def fingerprints_numpy(self):
         """(lo, hi) uint64 arrays of the first n fingerprints."""
         f = self.fp[:self.n].cpu().numpy().view(np.uint64)

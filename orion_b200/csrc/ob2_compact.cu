@@ -227,3 +227,54 @@ extern "C" int ob2_compact_wire(const ob2_space *space, int64_t n, int64_t n_str
                                 uint64_t *n_kept, void *stream) {
     return compact_impl(space, n, n_stride, cols, keep, 0, true, out_stride, out_cols, scratch, n_kept, stream);
 }
+
+// The host half of the hand-over: copy the first n_rows of every column of a device column block
+// into a HOST block of the same layout (stride dst_stride), asynchronously on `stream`.  Adjacent
+// columns of one element size form a 2-D array (pitch = element size x stride), so a whole run of
+// them is ONE cudaMemcpy2DAsync: 2 copies for mixed64 instead of one per column.
+extern "C" int ob2_columns_to_host(const ob2_space *space, int32_t layout, int64_t n_rows, int64_t src_stride,
+                                   const void *src_cols, int64_t dst_stride, void *dst_cols, void *stream) {
+    if (space == nullptr || src_cols == nullptr || dst_cols == nullptr || n_rows < 0 || n_rows > src_stride ||
+        n_rows > dst_stride || layout < 0 || layout > 2) {
+        ob2_set_error("ob2_columns_to_host: bad arguments (layout 0 = original, 1 = transformed, 2 = wire)");
+        return OB2_EINVAL;
+    }
+    if (n_rows == 0) return OB2_OK;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const ob2_slot_desc *slots = space->h_slots;
+    // walk the columns of the chosen layout: (offset units, element bytes, number of columns of the slot)
+    int64_t run_units = -1, run_elem = 0, run_cols = 0;
+    auto flush = [&]() -> int {
+        if (run_cols == 0) return OB2_OK;
+        const char *src = static_cast<const char *>(src_cols) + run_units * src_stride;
+        char *dst = static_cast<char *>(dst_cols) + run_units * dst_stride;
+        return ob2_check_cuda(cudaMemcpy2DAsync(dst, (size_t)(run_elem * dst_stride), src, (size_t)(run_elem * src_stride),
+                                                (size_t)(run_elem * n_rows), (size_t)run_cols, cudaMemcpyDeviceToHost, st),
+                              "cudaMemcpy2DAsync(columns to host)");
+    };
+    for (int s = 0; s < space->n_slots; ++s) {
+        const ob2_slot_desc &d = slots[s];
+        int64_t units, elem, cols = 1;
+        if (layout == 2) {
+            units = space->wire_units[s];
+            elem = space->wire_bytes[s];
+        } else if (layout == 1) {
+            units = d.t_units;
+            cols = d.t_width;
+            elem = (d.t_op == OB2_OP_ENUMERATE || (d.t_op == OB2_OP_IDENTITY && d.kind == OB2_KIND_CATEGORICAL)) ? 4 : 8;
+        } else {
+            units = d.col_units;
+            elem = d.kind == OB2_KIND_CATEGORICAL ? 4 : 8;
+        }
+        if (run_cols > 0 && elem == run_elem && units == run_units + run_elem * run_cols) {
+            run_cols += cols;
+            continue;
+        }
+        const int rc = flush();
+        if (rc != OB2_OK) return rc;
+        run_units = units;
+        run_elem = elem;
+        run_cols = cols;
+    }
+    return flush();
+}

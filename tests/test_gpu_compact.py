@@ -145,3 +145,43 @@ def test_batch_to_record_batch_equals_trial_records():
     fresh.observe(again)
     assert len(fresh) == rb.num_rows == len(hist)
     assert int(fresh.dedup(space.compiled().sample(n, 3, index=counters, with_fingerprint=True)).sum().item()) == 0
+
+
+@pytest.mark.parametrize('wire', [False, True])
+def test_columns_to_host_copies_the_used_rows_of_every_column(wire):
+    """ob2_columns_to_host: the survivors' rows into a pinned host block of the same layout with
+    a few 2-D copies; equal to what to_numpy reads back, for the original, the wire and the
+    transformed layout, including a host stride different from the device stride."""
+    import torch
+    from orion_b200 import spaces
+    from orion_b200.columns import ColumnBatch, _NUMPY, _SIZE
+    from orion_b200.transformer import build_required_space
+    space = spaces.mixed64()
+    compiled = space.compiled()
+    n = 5000
+    batch = compiled.sample(n, 11, with_mask=True)
+    keep = (torch.arange(batch.n_stride, device='cuda') % 3 != 0).to(torch.uint8)
+    dense = batch.compact(keep=keep, wire=wire)
+    k = dense.n
+    assert 0 < k < n
+    want = dense.to_numpy(natural=False)
+    for host_stride in (dense.n_stride, 4096):
+        row = compiled.wire_row_bytes if wire else compiled.row_bytes
+        host = torch.full((row * host_stride,), 255, dtype=torch.uint8).pin_memory()
+        dense.copy_rows_to_host(host, k, host_stride=host_stride)
+        torch.cuda.synchronize()
+        h = host.numpy()
+        for (units, dt), w in zip(dense._meta, want):
+            got = h[units * host_stride:units * host_stride + _SIZE[dt] * k].view(_NUMPY[dt])
+            assert np.array_equal(got, w)
+        # nothing beyond the k rows of a column was touched
+        units, dt = dense._meta[0]
+        assert (h[units * host_stride + _SIZE[dt] * k:units * host_stride + _SIZE[dt] * host_stride] == 255).all()
+    if not wire:        # transformed layout (one-hot columns are a run of 8-byte columns)
+        tc = build_required_space('real', space).compiled()
+        _b, tb, _k = tc.suggest(1000, 3)
+        host = torch.zeros(tc.trow_bytes * tb.n_stride, dtype=torch.uint8).pin_memory()
+        tb.copy_rows_to_host(host, 1000)
+        torch.cuda.synchronize()
+        assert torch.equal(host[:tb.buf.numel()].reshape(-1, tb.n_stride * 8)[:, :8000],
+                           tb.buf.cpu().reshape(-1, tb.n_stride * 8)[:, :8000])
