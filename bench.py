@@ -468,7 +468,7 @@ def d2h_ceiling(world):
         entry = json.load(open(path)).get(str(world))
     except ValueError:
         return None
-    if not entry:
+    if not isinstance(entry, dict):
         return None
     best = max(entry[k]['aggregate_GBps'] for k in ('unbound', 'gpu_local_cpus') if k in entry)
     return {"aggregate_GBps": best, "source": "profiles/pcie_probe.json (benchmarks/pcie_probe.py, %d GPUs at once)" % world}

@@ -69,7 +69,11 @@ struct ob2_xchg {
 namespace {
 
 constexpr int kSendPerThread = 4;
-constexpr int kSendTile = OB2_BLOCK * kSendPerThread;  // 1024 fingerprints per block
+constexpr int kSendTile = OB2_BLOCK * kSendPerThread;  // 1024 fingerprints per tile
+#ifndef OB2_SEND_GRID
+#define OB2_SEND_GRID 296   // 2 blocks per SM
+#endif
+constexpr int kSendGrid = OB2_SEND_GRID;
 
 // Bucket-and-push.  A block takes a tile of 1024 fingerprints, counting-sorts it by owner in
 // shared memory, reserves one contiguous run per owner in that owner's inbox lane, and then
@@ -86,9 +90,14 @@ xchg_send_kernel(int64_t n, const uint64_t *__restrict__ fp, uint32_t key_base, 
     __shared__ ulonglong2 s_fp[kSendTile];
     __shared__ uint32_t s_idx[kSendTile];
     const int tid = threadIdx.x;
+    // A capped grid walks the tiles: the kernel is NVLink bound (it saturates the links from a
+    // fraction of the SMs), and it runs beside the next batch's sampling kernel -- flooding
+    // every SM with its blocks would only take issue slots from that one.
+    const int64_t n_tiles = (n + kSendTile - 1) / kSendTile;
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
     if (tid < world) s_cnt[tid] = 0;
     __syncthreads();
-    const int64_t tile0 = (int64_t)blockIdx.x * kSendTile;
+    const int64_t tile0 = tile * kSendTile;
     ulonglong2 key[kSendPerThread];
     int owner[kSendPerThread];
     uint32_t local_rank[kSendPerThread];
@@ -138,6 +147,8 @@ xchg_send_kernel(int64_t n, const uint64_t *__restrict__ fp, uint32_t key_base, 
             reinterpret_cast<uint32_t *>(dst + key_off)[lane] = key_base + local;
             out_src[(int64_t)o * cap + pos] = local;
         }
+    }
+    __syncthreads();  // the staging arrays are reused by the next tile
     }
 }
 
@@ -313,7 +324,8 @@ extern "C" int ob2_xchg_send(ob2_xchg *x, int64_t n, const uint64_t *fp, uint32_
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     OB2_CUDA(cudaMemsetAsync(x->send_cnt, 0, sizeof(uint32_t) * x->world, st));
     if (n > 0) {
-        const int64_t blocks = (n + kSendTile - 1) / kSendTile;
+        int64_t blocks = (n + kSendTile - 1) / kSendTile;
+        if (blocks > kSendGrid) blocks = kSendGrid;
         xchg_send_kernel<<<(unsigned)blocks, OB2_BLOCK, 0, st>>>(n, fp, key_base, x->rank, x->world, x->cap, x->d_peers,
                                                                   x->lay.fp_off, x->lay.key_off, x->out_src, x->send_cnt);
         rc = ob2_check_cuda(cudaGetLastError(), "xchg_send_kernel launch");
