@@ -44,6 +44,22 @@ def main():
     dt = time.perf_counter() - t0
     out['config1_rosen2_suggest10_x100'] = {'seconds': dt, 'candidates_per_s': 1000 / dt, 'best_objective': best,
                                             'note': 'list-of-tuples API: launch + D2H + Python tuples per call'}
+    # the same loop through the UNMODIFIED reference (oracle/_ref), for the record: it is config 1's own CPU path
+    try:
+        from oracle import ref_harness
+        ref_space = ref_harness.build_space(['-x~uniform(-5, 10)', '-y~uniform(-5, 10)'])
+        ref_algo = ref_harness.primary_algo(ref_space, 'random')
+        ref_algo.suggest(10)
+        t0 = time.perf_counter()
+        ref_best = float('inf')
+        for _ in range(100):
+            rp = ref_algo.suggest(10)
+            ref_best = min(ref_best, min((1 - x) ** 2 + 100 * (y - x ** 2) ** 2 for x, y in rp))
+        rdt = time.perf_counter() - t0
+        out['config1_reference_cpu_path'] = {'seconds': rdt, 'candidates_per_s': 1000 / rdt, 'best_objective': ref_best,
+                                             'note': "the reference's PrimaryAlgo(space, 'random').suggest(10) x 100, one core"}
+    except ImportError as exc:
+        out['config1_reference_cpu_path'] = {'unavailable': str(exc)}
     space = spaces.rosen2()
     for label, fn in (('space.sample(10)', lambda: space.sample(10)),
                       ('space.sample(1)', lambda: space.sample(1)),

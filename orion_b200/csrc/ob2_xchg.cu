@@ -17,6 +17,7 @@
 // barriers per batch (any tiny collective on the same stream): one after send,
 // one after dedup.  No staging buffers, no zero-padding of bucket tails on the
 // wire (counts travel instead), three collectives fewer per batch.
+#include <cstdlib>
 #include <cstring>
 #include <new>
 
@@ -325,7 +326,12 @@ extern "C" int ob2_xchg_send(ob2_xchg *x, int64_t n, const uint64_t *fp, uint32_
     OB2_CUDA(cudaMemsetAsync(x->send_cnt, 0, sizeof(uint32_t) * x->world, st));
     if (n > 0) {
         int64_t blocks = (n + kSendTile - 1) / kSendTile;
-        if (blocks > kSendGrid) blocks = kSendGrid;
+        static const int grid_cap = [] {  // OB2_SEND_GRID in the environment overrides the built-in cap (experiments)
+            const char *e = getenv("OB2_SEND_GRID");
+            const int v = e ? atoi(e) : 0;
+            return v > 0 ? v : kSendGrid;
+        }();
+        if (blocks > grid_cap) blocks = grid_cap;
         xchg_send_kernel<<<(unsigned)blocks, OB2_BLOCK, 0, st>>>(n, fp, key_base, x->rank, x->world, x->cap, x->d_peers,
                                                                   x->lay.fp_off, x->lay.key_off, x->out_src, x->send_cnt);
         rc = ob2_check_cuda(cudaGetLastError(), "xchg_send_kernel launch");

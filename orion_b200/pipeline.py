@@ -25,6 +25,8 @@ This is the producer loop of the reference (``Producer.produce`` ->
 ``src/orion/core/worker/producer.py:42-52``) restated for device-resident
 batches; every result of the unfused path is still materialised.
 """
+import os
+
 import torch
 
 from .dist import ShardedHistory
@@ -78,7 +80,7 @@ class CandidatePipeline(object):
         # they are dispatched as soon as SM slots free up and really co-reside.
         self.s_sample = torch.cuda.Stream(device=dev, priority=0)
         self.s_reverse = torch.cuda.Stream(device=dev, priority=0)
-        self.s_dedup = torch.cuda.Stream(device=dev, priority=-1)
+        self.s_dedup = torch.cuda.Stream(device=dev, priority=int(os.environ.get('OB2_DEDUP_PRIORITY', '-1')))
         self.k = 0
         self.timed = timed
         self.timings = []          # per step: (sample_ms_events, reverse_events, dedup_events) when timed
