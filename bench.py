@@ -533,6 +533,23 @@ def measure_cfg2(dev, reps=5, warm=2):
                            "frac_of_hbm_peak": 128 * rate / 1e9 / peak}
         del buf
     torch.cuda.empty_cache()
+    # the same draw over Philox4x32-7 (ob2_space_set_philox_rounds): other values, fewer instructions
+    c7 = spaces.real16().compiled(philox_rounds=7)
+    n = 100_000_000
+    buf = c7.empty_columns(n)
+    e = [torch.cuda.Event(enable_timing=True) for _ in range(reps + 1)]
+    c7.sample(n, SEED - 3, with_mask=False, out=buf)
+    torch.cuda.synchronize()
+    e[0].record()
+    for r in range(reps):
+        c7.sample(n, SEED - 3, base_index=(1 + r) * n, with_mask=False, out=buf)
+        e[r + 1].record()
+    torch.cuda.synchronize()
+    ms = min(e[r].elapsed_time(e[r + 1]) for r in range(reps))
+    out['n=100000000, 7 Philox rounds'] = {"ms": ms, "candidates_per_s": n / (ms * 1e-3),
+                                           "frac_of_hbm_peak": 128 * n / (ms * 1e-3) / 1e9 / peak}
+    del buf
+    torch.cuda.empty_cache()
     out["algorithmic_bytes_per_candidate"] = 128
     out["roofline_candidates_per_s"] = peak * 1e9 / 128
     return out

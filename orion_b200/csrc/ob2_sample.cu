@@ -1,4 +1,4 @@
-// K1: candidate sampling (Philox4x32-10 or injected uniforms -> per-slot
+// K1: candidate sampling (Philox4x32 or injected uniforms -> per-slot
 // inverse CDF), fused with the bounds check, the <=4-attempt rejection, the row
 // fingerprint and -- optionally -- the transform chain and its reverse (the
 // one-kernel ob2_suggest); the standalone Space.__contains__ kernel; and the
@@ -10,10 +10,11 @@
 // contiguous bytes of that slot's column.  Output is columnar [S][n_stride].
 //
 // On its own the sampler is instruction-issue bound (Philox + fp64 inverse CDFs
-// + fingerprint multiplies, ~8-10k instructions per candidate of mixed64) while
-// transform and reverse are pure memory traffic; fusing them in (WITH_T, WITH_B)
-// lets the stores ride under the arithmetic and removes every re-read: the fused
-// kernel ends up at the HBM write ceiling (profiles/r1g_full_suggest.md).
+// + fingerprint multiplies: ~3.1k warp instructions per candidate of mixed64,
+// 75 % issue utilisation, profiles/r2f_sampler.md) while transform and reverse are
+// pure memory traffic; fusing them in (WITH_T, WITH_B) lets the stores ride under
+// the arithmetic and removes every re-read: the fused kernel runs at the HBM
+// write ceiling (profiles/r2k_full_step.md).
 #include <cstring>
 
 #include "ob2_internal.cuh"

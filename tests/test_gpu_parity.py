@@ -85,6 +85,94 @@ def test_philox_matches_oracle_mixed64(n):
     assert np.array_equal(lo, wlo) and np.array_equal(hi, whi)
 
 
+def test_philox_7_rounds_matches_oracle_and_differs_from_10():
+    """ob2_space_set_philox_rounds(7): the same plan and arithmetic over Philox4x32-7 (known
+    answers: tests/test_oracle_plan.py); transform chain and fingerprints follow."""
+    from orion_b200 import spaces
+    from orion_b200.transformer import build_required_space
+    space = spaces.mixed64()
+    specs = specs_from_space(space)
+    n, seed = 3001, 424242
+    b7 = space.compiled(philox_rounds=7).sample(n, seed, base_index=99, with_fingerprint=True)
+    want, failed = so.sample_philox(specs, n, seed, base_index=99, rounds=7)
+    assert not failed.any()
+    got = b7.to_numpy()
+    _compare_cols(specs, got, want)
+    b10 = space.compiled().sample(n, seed, base_index=99).to_numpy()
+    assert not np.array_equal(got[0], b10[0]) and not np.array_equal(got[40], b10[40])
+    lo, hi = b7.fingerprints_numpy()
+    wlo, whi = so.fingerprint(got)
+    assert np.array_equal(lo, wlo) and np.array_equal(hi, whi)
+    # the one-kernel suggest with 7 rounds hands out the same rows
+    sb, st, sk = build_required_space('real', space).compiled(philox_rounds=7).suggest(n, seed, base_index=99)
+    for a, b in zip(sk.to_numpy(), got):
+        assert np.array_equal(a, b)
+    twant = so.transform(specs, 'real', got)
+    assert all(np.array_equal(a, b) for a, b in zip(st.to_numpy(), twant))
+
+
+def test_philox_plan_with_alternating_widths_and_rejections_matches_oracle():
+    """Slots of one and two words interleaved (blocks shared across classes, skipped odd words),
+    shaped dimensions, a weighted categorical (threshold search), a 100-category one (equal
+    probabilities whose cdf is NOT exactly j/100), an Integer that misses the shortcut (user
+    bound), a dimension that rejects: device == oracle, value for value."""
+    from orion_b200.space import Categorical, Integer, Real, Space
+    space = Space()
+    space.register(Categorical('c3', {'a': 0.2, 'b': 0.3, 'c': 0.5}))
+    space.register(Real('x', 'uniform', 0, 1))
+    space.register(Integer('k', 'uniform', 0, 10))
+    space.register(Categorical('c100', list(range(100)), shape=(3,)))
+    space.register(Real('g', 'norm', 0, 1, low=-1.5, high=1.5, shape=(2,)))      # rejects ~13 % per element
+    space.register(Integer('kb', 'uniform', 0, 10, high=7))                       # user bound inside the support
+    space.register(Categorical('c2', [True, False]))
+    space.register(Real('l', 'reciprocal', 1e-3, 10.0))
+    space.register(Integer('kn', 'norm', 0, 5))
+    specs = specs_from_space(space)
+    plan = so.draw_plan(specs)
+    assert [p[2] for p in plan] == [32, 53, 32, 32, 32, 32, 53, 53, 53, 32, 53, 53]
+    n, seed = 20000, 5
+    batch = space.compiled().sample(n, seed, with_fingerprint=True)
+    want, failed = so.sample_philox(specs, n, seed)
+    got = batch.to_numpy()
+    _compare_cols(specs, got, want)
+    mask = batch.mask[:n].cpu().numpy().astype(bool)
+    assert np.array_equal(mask, ~failed) and (~mask).sum() < n // 100
+    first, _ = so.sample_from_uniform(specs, np.stack([so.philox_uniform(seed, np.arange(n), p) for p in plan]))
+    assert not np.array_equal(first[6], got[6])                     # some rows of `g` were redrawn
+    lo, hi = batch.fingerprints_numpy()
+    wlo, whi = so.fingerprint(got)
+    assert np.array_equal(lo, wlo) and np.array_equal(hi, whi)
+
+
+def test_inverse_cdfs_are_double_precision_grade():
+    """The sampler's own ndtri (one logarithm + polynomial) and bounded exp against scipy /
+    numpy on a dense sweep of injected uniforms, tails included: far inside the 1e-6 the
+    contract allows -- these are not reduced-precision shortcuts."""
+    from scipy.special import ndtri
+    from orion_b200.space import Real, Space
+    space = Space()
+    space.register(Real('g', 'norm', 0, 1))
+    space.register(Real('l', 'reciprocal', 1e-5, 1.0))
+    compiled = space.compiled()
+    rng = np.random.RandomState(12)
+    u = np.concatenate([rng.random_sample(400000), 10.0 ** rng.uniform(-300, -1, 100000),
+                        1 - 10.0 ** rng.uniform(-15.9, -1, 100000), 0.5 + rng.uniform(-1e-7, 1e-7, 20000),
+                        np.array([2.0 ** -53, 1 - 2.0 ** -53, 0.5, 5e-324, 1e-310])])
+    u = u[(u > 0) & (u < 1)]
+    n = len(u)
+    U, _ = _pad_U(np.stack([u, u]))
+    got = compiled.sample_from_uniform(U, n).to_numpy()
+    want_g = ndtri(u)
+    nz = want_g != 0
+    rel_g = np.abs(got[0][nz] - want_g[nz]) / np.abs(want_g[nz])
+    body = u[nz] >= 2.0 ** -53
+    assert rel_g[body].max() < 4e-15, rel_g[body].max()
+    assert rel_g[~body].max() < 1e-9                                 # below 2^-53: injected uniforms only
+    assert got[0][~nz].tolist() == want_g[~nz].tolist()
+    want_l = np.exp(np.log(1e-5) + u * (np.log(1.0) - np.log(1e-5)))
+    assert (np.abs(got[1] - want_l) / want_l).max() < 1e-15
+
+
 def test_philox_explicit_counters():
     """index[i] replaces base_index + i: replaying counters reproduces rows."""
     from orion_b200 import spaces
