@@ -136,7 +136,7 @@ def test_philox_plan_with_alternating_widths_and_rejections_matches_oracle():
     got = batch.to_numpy()
     _compare_cols(specs, got, want)
     mask = batch.mask[:n].cpu().numpy().astype(bool)
-    assert np.array_equal(mask, ~failed) and (~mask).sum() < n // 100
+    assert np.array_equal(mask, ~failed) and 0 < (~mask).sum() < n // 20        # (four misses in a row: ~1 %)
     first, _ = so.sample_from_uniform(specs, np.stack([so.philox_uniform(seed, np.arange(n), p) for p in plan]))
     assert not np.array_equal(first[6], got[6])                     # some rows of `g` were redrawn
     lo, hi = batch.fingerprints_numpy()
