@@ -88,7 +88,7 @@ def parse_args():
                     help='e2e leg: copy the survivors out at the natural column widths (int64 / int32) instead of '
                          'the narrowed wire layout')
     ap.add_argument('--serial', action='store_true', help='no stream pipeline: one stream, kernels back to back')
-    ap.add_argument('--exchange', default='auto', choices=['auto', 'nccl', 'peer'],
+    ap.add_argument('--exchange', default='auto', choices=['auto', 'nccl', 'peer', 'peer-store'],
                     help='multi-GPU dedup exchange: peer-memory stores from inside the kernels, NCCL all-to-all, '
                          'or auto (peer where the ranks can map each other, else NCCL)')
     return ap.parse_args()
@@ -740,7 +740,7 @@ def run_b200(args):
     batch, tbatch, back = pipe.slots[0].batch, pipe.slots[0].tbatch, pipe.slots[0].back
     fused = not args.unfused
     # extra kernels of mine per step for the exchange: NCCL path bucket+pad+scatter; peer path send+counts+flag+pad+collect
-    exchange_launches = 0 if world == 1 else (5 if peer_exchange else 3)
+    exchange_launches = 0 if world == 1 else ((4 if sharded.copy else 5) if peer_exchange else 3)
     fp_in_reverse = fused and not args.fp_in_sampler     # fingerprints computed by the reverse kernel (default)
     rev = 'reverse+fingerprint' if fp_in_reverse else 'reverse'
     kernel_names = ['sample+transform', rev, 'dedup'] if fused else ['sample', 'transform', rev, 'dedup']
@@ -1147,7 +1147,8 @@ def run_b200(args):
                    "reverse_of_transform_is_identity": round_trip_ok,
                    "history_rows_before": hist_rows0, "history_rows_after": hist_rows1},
         "exchange": ("none (1 GPU)" if world == 1 else
-                     "peer-memory inboxes over CUDA IPC (ob2_xchg_*)" if peer_exchange else "NCCL all-to-all"),
+                     ("peer-memory inboxes over CUDA IPC (ob2_xchg_*), %s" % ("DMA transfers" if sharded.copy else "remote stores from the kernels"))
+                     if peer_exchange else "NCCL all-to-all"),
         "kernel_sources_sha16": csrc_sha16(),
     }
     if not args.no_cpu_baseline and world == 1:

@@ -352,7 +352,7 @@ int ob2_scatter_verdict(int64_t n_entries, const uint32_t *src_index, const uint
  *     <barrier>         any stream-ordered collective (e.g. a 1-element all-reduce)
  *     ob2_xchg_dedup    dedup my inbox against my shard, store the verdicts
  *                       straight into the sources' verdict inboxes
- *                       (insert_only != 0: history load, no verdicts)
+ *                       (insert_only bit 0: history load, no verdicts; bit 1: lanes arrive padded)
  *     <barrier>
  *     ob2_xchg_collect  scatter the verdicts I received into keep[0..n)
  * `cap` = capacity of one (source, owner) lane, rounded up by the library to a multiple of 16
@@ -372,6 +372,13 @@ int ob2_xchg_send(ob2_xchg *x, int64_t n, const uint64_t *fp, uint32_t key_base,
 int ob2_xchg_dedup(ob2_xchg *x, ob2_set *set, int32_t insert_only, void *stream);
 int ob2_xchg_collect(ob2_xchg *x, int64_t n, uint8_t *keep, void *stream);
 int ob2_xchg_send_counts(const ob2_xchg *x, uint32_t *counts_host, void *stream);
+/* The same two phases with the bytes moved by the DMA engines (cudaMemcpyAsync into / out of the
+ * peers' regions) instead of remote stores and loads issued by kernels: ob2_xchg_send_copy buckets
+ * into local staging and ships whole zero-padded lanes (call ob2_xchg_dedup with bit 1 of
+ * `insert_only` set: no padding pass needed); ob2_xchg_collect_copy pulls the verdict lanes and
+ * scatters them.  Same inboxes, same verdicts; the transfers do not occupy SMs. */
+int ob2_xchg_send_copy(ob2_xchg *x, int64_t n, const uint64_t *fp, uint32_t key_base, void *stream);
+int ob2_xchg_collect_copy(ob2_xchg *x, int64_t n, uint8_t *keep, void *stream);
 int64_t ob2_xchg_cap(const ob2_xchg *x);
 int ob2_xchg_flag_overflow(const ob2_xchg *x, uint32_t *flag, void *stream);
 

@@ -99,6 +99,8 @@ SIGNATURES = {
     'ob2_xchg_dedup': (ctypes.c_int, [_vp, _vp, _i32, _vp]),
     'ob2_xchg_collect': (ctypes.c_int, [_vp, _i64, _vp, _vp]),
     'ob2_xchg_send_counts': (ctypes.c_int, [_vp, ctypes.POINTER(_u32), _vp]),
+    'ob2_xchg_send_copy': (ctypes.c_int, [_vp, _i64, _vp, _u32, _vp]),
+    'ob2_xchg_collect_copy': (ctypes.c_int, [_vp, _i64, _vp, _vp]),
     'ob2_xchg_cap': (_i64, [_vp]),
     'ob2_xchg_flag_overflow': (ctypes.c_int, [_vp, _vp, _vp]),
 }

@@ -64,6 +64,10 @@ struct ob2_xchg {
     uint32_t *out_src;     // [world][cap] local index of what I sent to each owner
     uint32_t *send_cnt;    // [world]
     uint32_t *scratch;     // [world * cap] dedup scratch
+    // copy-engine variant: local staging of the bucketed batch and of the pulled verdicts
+    uint64_t *stage_fp;    // [world][cap][2]
+    uint32_t *stage_key;   // [world][cap]
+    uint8_t *stage_verdict;  // [world * cap]
     bool peers_ready;
 };
 
@@ -247,6 +251,9 @@ extern "C" int ob2_xchg_create(int32_t rank, int32_t world, int64_t cap, ob2_xch
     if (rc == OB2_OK) rc = ob2_check_cuda(cudaMalloc(&x->out_src, lanes * 4), "cudaMalloc(out_src)");
     if (rc == OB2_OK) rc = ob2_check_cuda(cudaMalloc(&x->send_cnt, 256), "cudaMalloc(send_cnt)");
     if (rc == OB2_OK) rc = ob2_check_cuda(cudaMalloc(&x->scratch, lanes * 4), "cudaMalloc(scratch)");
+    if (rc == OB2_OK) rc = ob2_check_cuda(cudaMalloc(&x->stage_fp, lanes * 16), "cudaMalloc(stage_fp)");
+    if (rc == OB2_OK) rc = ob2_check_cuda(cudaMalloc(&x->stage_key, lanes * 4), "cudaMalloc(stage_key)");
+    if (rc == OB2_OK) rc = ob2_check_cuda(cudaMalloc(&x->stage_verdict, (lanes + 255) / 256 * 256), "cudaMalloc(stage_verdict)");
     if (rc != OB2_OK) {
         ob2_xchg_destroy(x);
         return rc;
@@ -270,6 +277,9 @@ extern "C" void ob2_xchg_destroy(ob2_xchg *x) {
     if (x->out_src) cudaFree(x->out_src);
     if (x->send_cnt) cudaFree(x->send_cnt);
     if (x->scratch) cudaFree(x->scratch);
+    if (x->stage_fp) cudaFree(x->stage_fp);
+    if (x->stage_key) cudaFree(x->stage_key);
+    if (x->stage_verdict) cudaFree(x->stage_verdict);
     delete x;
 }
 
@@ -352,10 +362,12 @@ extern "C" int ob2_xchg_dedup(ob2_xchg *x, ob2_set *set, int32_t insert_only, vo
     uint64_t *inbox_fp = reinterpret_cast<uint64_t *>(x->region + x->lay.fp_off);
     const uint32_t *inbox_key = reinterpret_cast<const uint32_t *>(x->region + x->lay.key_off);
     const uint32_t *cnt = reinterpret_cast<const uint32_t *>(x->region + x->lay.cnt_off);
-    const dim3 grid(lane_blocks(x->cap), (unsigned)x->world);
-    xchg_pad_kernel<<<grid, OB2_BLOCK, 0, st>>>(x->cap, cnt, inbox_fp);
-    rc = ob2_check_cuda(cudaGetLastError(), "xchg_pad_kernel launch");
-    if (rc != OB2_OK) return rc;
+    if (!(insert_only & 2)) {  // (bit 1: the senders shipped whole zero-padded lanes, ob2_xchg_send_copy)
+        const dim3 grid(lane_blocks(x->cap), (unsigned)x->world);
+        xchg_pad_kernel<<<grid, OB2_BLOCK, 0, st>>>(x->cap, cnt, inbox_fp);
+        rc = ob2_check_cuda(cudaGetLastError(), "xchg_pad_kernel launch");
+        if (rc != OB2_OK) return rc;
+    }
     const int64_t lanes = (int64_t)x->world * x->cap;
     // The kernels run over the padded lanes, but only the entries really received can be
     // inserted: when the cheap host bound (which counts the padding) would trip the 7/8 load
@@ -368,7 +380,7 @@ extern "C" int ob2_xchg_dedup(ob2_xchg *x, ob2_set *set, int32_t insert_only, vo
         real = 0;
         for (int r = 0; r < x->world; ++r) real += (int64_t)h_cnt[r] < x->cap ? (int64_t)h_cnt[r] : x->cap;
     }
-    if (insert_only) return ob2_set_insert_padded(set, lanes, real, inbox_fp, stream);
+    if (insert_only & 1) return ob2_set_insert_padded(set, lanes, real, inbox_fp, stream);
     // verdicts stay in MY region, lane by source; the sources pull them (ob2_xchg_collect)
     return ob2_set_dedup_padded(set, lanes, real, inbox_fp, inbox_key, x->scratch,
                                 reinterpret_cast<uint8_t *>(x->region + x->lay.verdict_off), stream);
@@ -387,6 +399,48 @@ extern "C" int ob2_xchg_collect(ob2_xchg *x, int64_t n, uint8_t *keep, void *str
     xchg_collect_kernel<<<grid, OB2_BLOCK, 0, st>>>(x->rank, x->cap, x->send_cnt, x->out_src, x->d_peers,
                                                     x->lay.verdict_off, keep);
     return ob2_check_cuda(cudaGetLastError(), "xchg_collect_kernel launch");
+}
+
+// ---- copy-engine variant of send / collect: the same inboxes, but the bytes cross NVLink as
+// cudaMemcpyAsync transfers (DMA engines, no SM involved) instead of remote stores from a kernel.
+// The store-based send is NVLink bound yet holds SM slots -- and store-queue space -- that the
+// next batch's store-bound sampling kernel wants; DMA transfers run entirely beside it.
+extern "C" int ob2_xchg_send_copy(ob2_xchg *x, int64_t n, const uint64_t *fp, uint32_t key_base, void *stream) {
+    int rc = check_ready(x, "ob2_xchg_send_copy");
+    if (rc != OB2_OK) return rc;
+    if (n < 0 || (n > 0 && fp == nullptr) || n >= 0xFFFFFFFFll) {
+        ob2_set_error("ob2_xchg_send_copy: bad arguments");
+        return OB2_EINVAL;
+    }
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    // bucket by owner into local staging, tails zero-padded (counts land in send_cnt)
+    rc = ob2_bucket_by_owner(n, fp, key_base, x->world, x->cap, x->stage_fp, x->stage_key, x->out_src, x->send_cnt, stream);
+    if (rc != OB2_OK) return rc;
+    for (int o = 0; o < x->world; ++o) {
+        char *dst = x->peer[o];
+        const size_t lane = (size_t)x->rank * x->cap;
+        OB2_CUDA(cudaMemcpyAsync(dst + x->lay.fp_off + lane * 16, x->stage_fp + (size_t)o * x->cap * 2, (size_t)x->cap * 16,
+                                 cudaMemcpyDefault, st));
+        OB2_CUDA(cudaMemcpyAsync(dst + x->lay.key_off + lane * 4, x->stage_key + (size_t)o * x->cap, (size_t)x->cap * 4,
+                                 cudaMemcpyDefault, st));
+    }
+    xchg_counts_kernel<<<1, OB2_XCHG_MAX_RANKS, 0, st>>>(x->rank, x->world, x->d_peers, x->lay.cnt_off, x->send_cnt);
+    return ob2_check_cuda(cudaGetLastError(), "xchg_counts_kernel launch");
+}
+
+extern "C" int ob2_xchg_collect_copy(ob2_xchg *x, int64_t n, uint8_t *keep, void *stream) {
+    int rc = check_ready(x, "ob2_xchg_collect_copy");
+    if (rc != OB2_OK) return rc;
+    if (n < 0 || keep == nullptr) {
+        ob2_set_error("ob2_xchg_collect_copy: bad arguments");
+        return OB2_EINVAL;
+    }
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    OB2_CUDA(cudaMemsetAsync(keep, 0, (size_t)n, st));  // padding entries and bucket overflow stay 0
+    for (int o = 0; o < x->world; ++o)  // pull my verdict lane out of every owner's region
+        OB2_CUDA(cudaMemcpyAsync(x->stage_verdict + (size_t)o * x->cap, x->peer[o] + x->lay.verdict_off + (size_t)x->rank * x->cap,
+                                 (size_t)x->cap, cudaMemcpyDefault, st));
+    return ob2_scatter_verdict((int64_t)x->world * x->cap, x->out_src, x->stage_verdict, x->stage_fp, keep, stream);
 }
 
 extern "C" int64_t ob2_xchg_cap(const ob2_xchg *x) { return x ? x->cap : 0; }

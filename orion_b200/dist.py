@@ -199,14 +199,17 @@ class PeerExchange(object):
     def region(self):
         return self.lib.ob2_xchg_region(self.handle)
 
-    def send(self, fp, n, key_base):
-        _lib.check(self.lib.ob2_xchg_send(self.handle, n, fp.data_ptr(), key_base, self._stream()))
+    def send(self, fp, n, key_base, copy=False):
+        fn = self.lib.ob2_xchg_send_copy if copy else self.lib.ob2_xchg_send
+        _lib.check(fn(self.handle, n, fp.data_ptr(), key_base, self._stream()))
 
-    def dedup(self, history, insert_only=False):
-        _lib.check(self.lib.ob2_xchg_dedup(self.handle, history.handle, 1 if insert_only else 0, self._stream()))
+    def dedup(self, history, insert_only=False, padded=False):
+        _lib.check(self.lib.ob2_xchg_dedup(self.handle, history.handle, (1 if insert_only else 0) | (2 if padded else 0),
+                                           self._stream()))
 
-    def collect(self, n, keep):
-        _lib.check(self.lib.ob2_xchg_collect(self.handle, n, keep.data_ptr(), self._stream()))
+    def collect(self, n, keep, copy=False):
+        fn = self.lib.ob2_xchg_collect_copy if copy else self.lib.ob2_xchg_collect
+        _lib.check(fn(self.handle, n, keep.data_ptr(), self._stream()))
 
     def send_counts(self):
         out = (ctypes.c_uint32 * self.world)()
@@ -220,15 +223,17 @@ class PeerExchangeUnavailable(RuntimeError):
 
 def make_sharded_history(history, max_n, exchange='auto', group=None):
     """The sharded history for this process group: ``'peer'`` (peer-memory
-    inboxes), ``'nccl'`` (all-to-all), or ``'auto'`` = peer where the ranks can
-    map each other's memory, NCCL otherwise.  Collective: call on every rank."""
+    inboxes filled by DMA transfers), ``'peer-store'`` (the same inboxes filled
+    by remote stores from the bucketing kernel), ``'nccl'`` (all-to-all), or
+    ``'auto'`` = peer where the ranks can map each other's memory, NCCL
+    otherwise.  Collective: call on every rank."""
     world = dist.get_world_size(group) if dist.is_initialized() else 1
     if world == 1 or exchange == 'nccl':
         return ShardedHistory(history, group=group)
     try:
-        return PeerShardedHistory(history, max_n, group=group)
+        return PeerShardedHistory(history, max_n, group=group, transfers='store' if exchange == 'peer-store' else 'copy')
     except PeerExchangeUnavailable:
-        if exchange == 'peer':
+        if exchange in ('peer', 'peer-store'):
             raise
         return ShardedHistory(history, group=group)
 
@@ -252,7 +257,11 @@ class PeerShardedHistory(object):
 
     OVERFLOW, FULL = 0, 1
 
-    def __init__(self, history, max_n, group=None):
+    def __init__(self, history, max_n, group=None, transfers='copy'):
+        # 'copy': the bytes cross NVLink as DMA transfers (ob2_xchg_send_copy / collect_copy);
+        # 'store': as remote stores / loads issued by the exchange kernels themselves
+        assert transfers in ('copy', 'store')
+        self.copy = transfers == 'copy'
         self.history = history
         self.group = group
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
@@ -289,7 +298,7 @@ class PeerShardedHistory(object):
         return self._nccl
 
     def _send(self, fp, n, key_base):
-        self.xchg.send(fp, n, key_base)
+        self.xchg.send(fp, n, key_base, copy=self.copy)
         _lib.check(self.xchg.lib.ob2_xchg_flag_overflow(self.xchg.handle, self._status[self.OVERFLOW:].data_ptr(),
                                                        self.xchg._stream()))
         self._barrier()
@@ -300,8 +309,8 @@ class PeerShardedHistory(object):
         everybody (no exception on this rank alone: the others would hang in
         the next collective)."""
         while True:
-            rc = self.xchg.lib.ob2_xchg_dedup(self.xchg.handle, self.history.handle, 1 if insert_only else 0,
-                                              self.xchg._stream())
+            rc = self.xchg.lib.ob2_xchg_dedup(self.xchg.handle, self.history.handle,
+                                              (1 if insert_only else 0) | (2 if self.copy else 0), self.xchg._stream())
             if rc == -4 and self.history.auto_grow and self.history.n_slots < (1 << 31):
                 self.history.grow()
                 continue
@@ -336,7 +345,7 @@ class PeerShardedHistory(object):
         self._owner_side(insert_only=False)
         if check and self._read_status()[self.FULL]:
             self._raise_full()
-        self.xchg.collect(n, keep)
+        self.xchg.collect(n, keep, copy=self.copy)
         return keep
 
     def insert(self, fp, n, check=True):
