@@ -88,7 +88,7 @@ def parse_args():
                     help='e2e leg: copy the survivors out at the natural column widths (int64 / int32) instead of '
                          'the narrowed wire layout')
     ap.add_argument('--serial', action='store_true', help='no stream pipeline: one stream, kernels back to back')
-    ap.add_argument('--exchange', default='auto', choices=['auto', 'nccl', 'peer', 'peer-store'],
+    ap.add_argument('--exchange', default='auto', choices=['auto', 'nccl', 'peer', 'peer-copy'],
                     help='multi-GPU dedup exchange: peer-memory stores from inside the kernels, NCCL all-to-all, '
                          'or auto (peer where the ranks can map each other, else NCCL)')
     return ap.parse_args()

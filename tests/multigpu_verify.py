@@ -46,7 +46,7 @@ def main():
     ap.add_argument('--cands', type=int, default=12_500_000)
     ap.add_argument('--history', type=int, default=25_000_000, help='history rows loaded per rank')
     ap.add_argument('--steps', type=int, default=3)
-    ap.add_argument('--exchange', default='both', choices=['both', 'peer', 'peer-store', 'nccl'])
+    ap.add_argument('--exchange', default='both', choices=['both', 'peer', 'peer-copy', 'nccl'])
     ap.add_argument('--out', default=None)
     args = ap.parse_args()
 
@@ -113,14 +113,14 @@ def main():
 
     report = {"world": world, "cands_per_rank": n, "history_rows_per_rank": H, "steps": steps, "runs": []}
     ok_all = True
-    exchanges = ['peer', 'peer-store', 'nccl'] if args.exchange == 'both' else [args.exchange]
+    exchanges = ['peer', 'peer-copy', 'nccl'] if args.exchange == 'both' else [args.exchange]
     if world == 1:
         exchanges = ['nccl']            # one rank: no exchange either way
     for exchange in exchanges:
         rows_cap = H + (steps + 1) * n
         history = TrialHistory(compiled, n_slots=table_slots_for(rows_cap, load=0.5))
         sharded = make_sharded_history(history, max_n=n, exchange=exchange)
-        used = ('peer' if sharded.copy else 'peer-store') if isinstance(sharded, PeerShardedHistory) else 'nccl'
+        used = ('peer-copy' if sharded.copy else 'peer') if isinstance(sharded, PeerShardedHistory) else 'nccl'
         done = 0
         while done < H:
             m = min(n, H - done)
@@ -170,7 +170,7 @@ def main():
         for exchange in exchanges:
             history = TrialHistory(sc, capacity=1 << 21)         # (the worst-case lanes of the fallback count as incoming rows)
             sharded = make_sharded_history(history, max_n=m, exchange=exchange)
-            used = ('peer' if sharded.copy else 'peer-store') if isinstance(sharded, PeerShardedHistory) else 'nccl'
+            used = ('peer-copy' if sharded.copy else 'peer') if isinstance(sharded, PeerShardedHistory) else 'nccl'
             b = sc.sample(m, SEED + 7, base_index=rank * m, with_fingerprint=True)
             k = sharded.dedup(b.fp, m, per_rank_n=m, check=True)
             cols = b.columns
