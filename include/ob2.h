@@ -278,8 +278,8 @@ int ob2_set_dedup(ob2_set *set, int64_t n, const uint64_t *fp, const uint32_t *o
  *     the look-up has always happened.  Create the set before any stream
  *     capture begins.
  *   - all calls share the one array per GPU, and it keeps whatever the last
- *     call wrote.  Nothing in it needs to start at zero (pass 1 writes every
- *     entry pass 2 reads).  Two calls that overlap on the GPU -- different
+ *     call wrote.  Nothing in it needs to start at zero (pass 1 builds the
+ *     list pass 2 reads, from empty, every call).  Two calls that overlap on the GPU -- different
  *     streams, or different sets -- race on it: keep them ordered. */
 #define OB2_STATIC_DEDUP_MAX (1 << 20)
 int ob2_set_dedup_static(ob2_set *set, int64_t n, const uint64_t *fp, const uint32_t *order,

@@ -36,6 +36,7 @@ static_assert(sizeof(SetSlot) == OB2_SET_SLOT_BYTES, "slot size");
 struct SetHeader {
     unsigned long long count;  // distinct fingerprints stored
     uint32_t overflow;         // a probe sequence wrapped the whole table
+    uint32_t n_conflicts;      // entries of the running dedup call that met a key inserted by the same call
 };
 
 }  // namespace
@@ -115,6 +116,18 @@ __device__ __forceinline__ bool find(const SetSlot *slots, uint64_t mask, uint64
     return false;
 }
 
+// Slot index of a key that is known to be stored.
+__device__ __forceinline__ uint64_t locate(const SetSlot *slots, uint64_t mask, uint64_t lo, uint64_t hi) {
+    uint64_t pos = lo & mask;
+    for (uint64_t step = 0; step <= mask; ++step) {
+        uint64_t klo, khi;
+        ld_key(slots + pos, klo, khi);
+        if ((klo == lo && khi == hi) || klo == 0) break;
+        pos = (pos + 1) & mask;
+    }
+    return pos;
+}
+
 __device__ __forceinline__ void warp_count_add(unsigned long long *counter, bool flag) {
     const unsigned ballot = __ballot_sync(__activemask(), flag);
     if (flag && (threadIdx.x & 31) == (__ffs(ballot) - 1)) atomicAdd(counter, (unsigned long long)__popc(ballot));
@@ -144,12 +157,12 @@ __device__ __forceinline__ unsigned long long dedup_tag(uint32_t epoch, uint32_t
     return ((unsigned long long)epoch << 32) | (unsigned long long)(0xFFFFFFFFu - ord);  // max tag = smallest order key
 }
 
-// Pass 1 settles almost every entry with ONE probe:
+// Pass 1 settles almost every entry with ONE probe (scratch: the list of entry indices left to pass 2):
 //   - key absent  -> insert it (128-bit CAS), keep = 1 for now, remember who won the slot;
 //   - key present since an earlier call (born != 0 and != epoch) -> keep = 0, no atomic at all;
 //   - key present and inserted during THIS call (born == epoch, or 0 = the winner's store is
 //     still in flight) -> a duplicate inside the batch: compete for the slot's stamp and leave
-//     the verdict to pass 2 (scratch[i] = slot index).
+//     the verdict to pass 2 (the entry's index is appended to the list in `scratch`).
 // Only the last class -- the rows that really are duplicated inside the batch -- touches the
 // table a second time.
 __global__ void __launch_bounds__(OB2_BLOCK)
@@ -157,10 +170,9 @@ set_dedup_pass1(SetHeader *hdr, SetSlot *slots, uint64_t mask, int64_t n, const 
                 const uint32_t *__restrict__ order, uint32_t epoch, uint32_t *__restrict__ scratch,
                 uint8_t *__restrict__ keep) {
     const int64_t i = (int64_t)blockIdx.x * OB2_BLOCK + threadIdx.x;
-    bool inserted = false;
+    bool inserted = false, conflict = false;
     if (i < n) {
         uint8_t verdict = 0;
-        uint32_t conflict = OB2_NO_CONFLICT;
         const ulonglong2 key = __ldg(reinterpret_cast<const ulonglong2 *>(fp) + i);
         if (key.x != 0) {  // lo == 0 is padding
             uint64_t pos;
@@ -178,38 +190,48 @@ set_dedup_pass1(SetHeader *hdr, SetSlot *slots, uint64_t mask, int64_t n, const 
                 if (born == 0 || born == epoch) {
                     const uint32_t ord = order ? __ldg(order + i) : (uint32_t)i;
                     atomicMax(&slot->stamp, dedup_tag(epoch, ord));
-                    conflict = (uint32_t)pos;
+                    conflict = true;
                 }
             } else {
                 hdr->overflow = 1;
             }
         }
         keep[i] = verdict;
-        scratch[i] = conflict;
+    }
+    // the ~1 % that met a key of this same call go on a list for pass 2 (scratch = their entry indices)
+    const unsigned bidders = __ballot_sync(0xFFFFFFFFu, conflict);
+    if (bidders) {
+        const unsigned lane = threadIdx.x & 31, leader = __ffs(bidders) - 1;
+        uint32_t base = 0;
+        if (lane == leader) base = atomicAdd(&hdr->n_conflicts, (uint32_t)__popc(bidders));
+        base = __shfl_sync(0xFFFFFFFFu, base, leader);
+        if (conflict) scratch[base + __popc(bidders & ((1u << lane) - 1))] = (uint32_t)i;
     }
     warp_count_add(&hdr->count, inserted);
 }
 
-// Pass 2: only entries that met a key inserted by this same call.  `stamp` holds the best bid
-// among those FINDERS (largest tag = smallest order key; a slot inserted in this call started
-// with stamp 0).  If that bid beats the inserter's own order key, the bidder takes the slot and
-// the inserter's provisional keep = 1 is withdrawn (every loser writes the same 0, so the race
-// is benign); otherwise the inserter stays and every finder loses.
+// Pass 2: only the listed entries -- those that met a key inserted by this same call.  `stamp` holds
+// the best bid among those FINDERS (largest tag = smallest order key; a slot inserted in this call
+// started with stamp 0).  If that bid beats the inserter's own order key, the bidder takes the slot and
+// the inserter's provisional keep = 1 is withdrawn (every loser writes the same 0, so the race is
+// benign); otherwise the inserter stays and every finder loses.  A small fixed grid walks the list.
 __global__ void __launch_bounds__(OB2_BLOCK)
-set_dedup_pass2(const SetSlot *__restrict__ slots, int64_t n, const uint32_t *__restrict__ order, uint32_t epoch,
+set_dedup_pass2(const SetHeader *__restrict__ hdr, const SetSlot *__restrict__ slots, uint64_t mask,
+                const uint64_t *__restrict__ fp, const uint32_t *__restrict__ order, uint32_t epoch,
                 const uint32_t *__restrict__ scratch, uint8_t *__restrict__ keep) {
-    const int64_t i = (int64_t)blockIdx.x * OB2_BLOCK + threadIdx.x;
-    if (i >= n) return;
-    const uint32_t pos = scratch[i];
-    if (pos == OB2_NO_CONFLICT) return;
-    const SetSlot *slot = slots + pos;
-    const unsigned long long stamp = slot->stamp;
-    const uint32_t w = slot->winner;
-    const uint32_t ord_w = order ? __ldg(order + w) : w;
-    if (stamp > dedup_tag(epoch, ord_w)) {
-        keep[w] = 0;
-        const uint32_t ord = order ? __ldg(order + i) : (uint32_t)i;
-        if (stamp == dedup_tag(epoch, ord)) keep[i] = 1;
+    const uint32_t n_listed = hdr->n_conflicts;
+    for (uint32_t j = blockIdx.x * OB2_BLOCK + threadIdx.x; j < n_listed; j += gridDim.x * OB2_BLOCK) {
+        const uint32_t i = scratch[j];
+        const ulonglong2 key = __ldg(reinterpret_cast<const ulonglong2 *>(fp) + i);
+        const SetSlot *slot = slots + locate(slots, mask, key.x, key.y);
+        const unsigned long long stamp = slot->stamp;
+        const uint32_t w = slot->winner;
+        const uint32_t ord_w = order ? __ldg(order + w) : w;
+        if (stamp > dedup_tag(epoch, ord_w)) {
+            keep[w] = 0;
+            const uint32_t ord = order ? __ldg(order + i) : i;
+            if (stamp == dedup_tag(epoch, ord)) keep[i] = 1;
+        }
     }
 }
 
@@ -514,10 +536,12 @@ int dedup_launch(ob2_set *set, int64_t n, int64_t n_reserve, const uint64_t *fp,
         return OB2_ETOOBIG;
     }
     const uint32_t epoch = ++set->epoch;
+    OB2_CUDA(cudaMemsetAsync(&set->header->n_conflicts, 0, sizeof(uint32_t), st));
     set_dedup_pass1<<<blocks, OB2_BLOCK, 0, st>>>(set->header, set->slots, set->n_slots - 1, n, fp, order, epoch, scratch, keep);
     rc = ob2_check_cuda(cudaGetLastError(), "set_dedup_pass1 launch");
     if (rc != OB2_OK) return rc;
-    set_dedup_pass2<<<blocks, OB2_BLOCK, 0, st>>>(set->slots, n, order, epoch, scratch, keep);
+    const unsigned blocks2 = blocks < 592u ? blocks : 592u;  // the list is ~1 % of the batch: 4 CTAs per SM walk it
+    set_dedup_pass2<<<blocks2, OB2_BLOCK, 0, st>>>(set->header, set->slots, set->n_slots - 1, fp, order, epoch, scratch, keep);
     return ob2_check_cuda(cudaGetLastError(), "set_dedup_pass2 launch");
 }
 
@@ -586,9 +610,10 @@ extern "C" int ob2_set_dedup_static(ob2_set *set, int64_t n, const uint64_t *fp,
     uint32_t *scratch = nullptr;
     rc = static_scratch_for_current_device(&scratch);
     if (rc != OB2_OK) return rc;
-    // Nothing in the scratch has to start at zero: pass 1 writes entry i for
-    // every i < n (a slot index, or the "settled" marker) and pass 2 reads only
-    // those n entries, so whatever an earlier call left behind is never consumed.
+    // Nothing in the scratch has to start at zero: pass 1 appends the entries that need a second
+    // look to a list that starts empty on every call (its length lives in the set's header, which
+    // the call resets), and pass 2 reads exactly that many -- whatever an earlier call left
+    // behind in the array is never consumed.
     return dedup_launch(set, n, n, fp, order, scratch, keep, static_cast<cudaStream_t>(stream), "ob2_set_dedup_static");
 }
 
