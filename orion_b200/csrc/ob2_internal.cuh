@@ -236,6 +236,11 @@ __device__ __forceinline__ double ob2_log_normal(double t) {
     return fma(dk, 6.93147180369123816490e-01, -((hfsq - fma(s, hfsq + R, dk * 1.90821492927058770002e-10)) - f));
 }
 
+// IMM: coefficients as immediates instead of constant-bank operands.  The issue-bound plain
+// sampler wants the operand form (an immediate costs two moves per coefficient); the store-heavy
+// fused variants have issue slots to spare but stall on constant-cache misses (their descriptor
+// tables already overflow it), so they take the immediates.
+template <bool IMM>
 __device__ __forceinline__ double ob2_ndtri(double u) {
     const double t = u * (1.0 - u);
     const double x = fma(2.0, u, -1.0);
@@ -245,9 +250,16 @@ __device__ __forceinline__ double ob2_ndtri(double u) {
     double p;
     if (w < OB2_NDTRI_W_SPLIT) {
         const double z = w - OB2_NDTRI_W_MID;
-        p = ob2_ndtri_central[0];
+        if (IMM) {
+            p = 0.0;
+#define OB2_HORNER(c) p = fma(p, z, c);
+            OB2_NDTRI_CENTRAL(OB2_HORNER)
+#undef OB2_HORNER
+        } else {
+            p = ob2_ndtri_central[0];
 #pragma unroll
-        for (int i = 1; i < OB2_NDTRI_CENTRAL_N; ++i) p = fma(p, z, ob2_ndtri_central[i]);
+            for (int i = 1; i < OB2_NDTRI_CENTRAL_N; ++i) p = fma(p, z, ob2_ndtri_central[i]);
+        }
     } else {  // about 3 warps in 100 come here
         const double s = sqrt(w);
         if (s <= OB2_NDTRI_S_MAX) {
@@ -269,15 +281,34 @@ __device__ __forceinline__ double ob2_ndtri(double u) {
 // the library checks |log a| + |log b - log a| of a loguniform prior when it compiles the space).
 // k = round(y / ln 2) through the 1.5 * 2^52 shift, r = y - k ln2 in two steps, Taylor to degree 13
 // on |r| <= 0.347 (truncation 4e-18), 2^k added into the exponent field.  About 0.6 ulp.
+template <bool IMM>
 __device__ __forceinline__ double ob2_exp_bounded(double y) {
     const double shifted = fma(y, 1.4426950408889634, 6755399441055744.0);
     const int k = __double2loint(shifted);
     const double kd = shifted - 6755399441055744.0;
     double r = fma(kd, -6.93147180369123816490e-01, y);
     r = fma(kd, -1.90821492927058770002e-10, r);
-    double p = ob2_exp_taylor[0];
+    double p;
+    if (IMM) {
+        p = 1.6059043836821613e-10;  // 1/13!
+        p = fma(p, r, 2.08767569878681e-09);
+        p = fma(p, r, 2.505210838544172e-08);
+        p = fma(p, r, 2.755731922398589e-07);
+        p = fma(p, r, 2.7557319223985893e-06);
+        p = fma(p, r, 2.48015873015873e-05);
+        p = fma(p, r, 1.984126984126984e-04);
+        p = fma(p, r, 1.388888888888889e-03);
+        p = fma(p, r, 8.333333333333333e-03);
+        p = fma(p, r, 4.1666666666666664e-02);
+        p = fma(p, r, 1.6666666666666666e-01);
+        p = fma(p, r, 0.5);
+        p = fma(p, r, 1.0);
+        p = fma(p, r, 1.0);
+    } else {
+        p = ob2_exp_taylor[0];
 #pragma unroll
-    for (int i = 1; i < 14; ++i) p = fma(p, r, ob2_exp_taylor[i]);
+        for (int i = 1; i < 14; ++i) p = fma(p, r, ob2_exp_taylor[i]);
+    }
     return __hiloint2double(__double2hiint(p) + (k << 20), __double2loint(p));
 }
 
@@ -521,11 +552,11 @@ __device__ __forceinline__ double draw_real(const ob2_slot_desc &d, double u) {
             break;
         case OB2_DIST_RECIPROCAL: {
             const double y = __dadd_rn(d.p0, __dmul_rn(u, d.p1));
-            b = (d.flags & OB2_SLOT_FAST_EXP) ? ob2_exp_bounded(y) : exp(y);
+            b = (d.flags & OB2_SLOT_FAST_EXP) ? ob2_exp_bounded<false>(y) : exp(y);
             break;
         }
         case OB2_DIST_NORM:
-            b = ob2_ndtri(u);
+            b = ob2_ndtri<false>(u);
             break;
         default:
             // scale == 0 (OB2_DIST_CONST): rvs returns loc.  Without EXT nothing else can arrive here (the

@@ -361,11 +361,11 @@ __device__ __forceinline__ void real_slot(const ob2_slot_desc *s_slots, const ob
         b0 = u0;
         b1 = u1;
     } else if (CLS == OB2_CLS_RECIP) {
-        b0 = ob2_exp_bounded(__dadd_rn(d.p0, __dmul_rn(u0, d.p1)));
-        b1 = ob2_exp_bounded(__dadd_rn(d.p0, __dmul_rn(u1, d.p1)));
+        b0 = ob2_exp_bounded<WITH_T>(__dadd_rn(d.p0, __dmul_rn(u0, d.p1)));
+        b1 = ob2_exp_bounded<WITH_T>(__dadd_rn(d.p0, __dmul_rn(u1, d.p1)));
     } else {
-        b0 = ob2_ndtri(u0);
-        b1 = ob2_ndtri(u1);
+        b0 = ob2_ndtri<WITH_T>(u0);
+        b1 = ob2_ndtri<WITH_T>(u1);
     }
     // base(u) * scale + loc, rounded multiply then rounded add (scipy rv_generic.rvs)
     emit_real<WITH_FP, WITH_T, WITH_B>(d, __dadd_rn(__dmul_rn(b0, d.scale), d.loc), __dadd_rn(__dmul_rn(b1, d.scale), d.loc),
