@@ -136,11 +136,27 @@ __device__ __forceinline__ void warp_count_add(unsigned long long *counter, bool
 #define OB2_BORN_HISTORY 0xFFFFFFFFu  // inserted by ob2_set_insert (not by a dedup call)
 #define OB2_NO_CONFLICT 0xFFFFFFFFu   // scratch marker: verdict already final after pass 1
 
+// Which entry a thread owns.  Flat batches: the global thread index, valid below n.  An exchange
+// inbox (lane_cnt != nullptr): blockIdx.y is the source lane of `lane_cap` entries of which the
+// first lane_cnt[y] are real -- the tails are never read, so nobody has to blank them.
+__device__ __forceinline__ bool entry_index(int64_t n, const uint32_t *__restrict__ lane_cnt, int64_t lane_cap, int64_t &i) {
+    const int64_t local = (int64_t)blockIdx.x * OB2_BLOCK + threadIdx.x;
+    if (lane_cnt == nullptr) {
+        i = local;
+        return i < n;
+    }
+    i = (int64_t)blockIdx.y * lane_cap + local;
+    const int64_t used = (int64_t)__ldg(lane_cnt + blockIdx.y);
+    return local < (used < lane_cap ? used : lane_cap);
+}
+
 __global__ void __launch_bounds__(OB2_BLOCK)
-set_insert_kernel(SetHeader *hdr, SetSlot *slots, uint64_t mask, int64_t n, const uint64_t *__restrict__ fp) {
-    const int64_t i = (int64_t)blockIdx.x * OB2_BLOCK + threadIdx.x;
+set_insert_kernel(SetHeader *hdr, SetSlot *slots, uint64_t mask, int64_t n, const uint64_t *__restrict__ fp,
+                  const uint32_t *__restrict__ lane_cnt, int64_t lane_cap) {
+    int64_t i;
+    const bool valid = entry_index(n, lane_cnt, lane_cap, i);
     bool inserted = false;
-    if (i < n) {
+    if (valid) {
         const ulonglong2 key = __ldg(reinterpret_cast<const ulonglong2 *>(fp) + i);
         if (key.x != 0) {
             uint64_t pos;
@@ -168,10 +184,11 @@ __device__ __forceinline__ unsigned long long dedup_tag(uint32_t epoch, uint32_t
 __global__ void __launch_bounds__(OB2_BLOCK)
 set_dedup_pass1(SetHeader *hdr, SetSlot *slots, uint64_t mask, int64_t n, const uint64_t *__restrict__ fp,
                 const uint32_t *__restrict__ order, uint32_t epoch, uint32_t *__restrict__ scratch,
-                uint8_t *__restrict__ keep) {
-    const int64_t i = (int64_t)blockIdx.x * OB2_BLOCK + threadIdx.x;
+                uint8_t *__restrict__ keep, const uint32_t *__restrict__ lane_cnt, int64_t lane_cap) {
+    int64_t i;
+    const bool valid = entry_index(n, lane_cnt, lane_cap, i);
     bool inserted = false, conflict = false;
-    if (i < n) {
+    if (valid) {
         uint8_t verdict = 0;
         const ulonglong2 key = __ldg(reinterpret_cast<const ulonglong2 *>(fp) + i);
         if (key.x != 0) {  // lo == 0 is padding
@@ -515,7 +532,7 @@ extern "C" int ob2_set_insert(ob2_set *set, int64_t n, const uint64_t *fp, void 
     unsigned blocks;
     rc = grid_for(n, &blocks);
     if (rc != OB2_OK) return rc;
-    set_insert_kernel<<<blocks, OB2_BLOCK, 0, st>>>(set->header, set->slots, set->n_slots - 1, n, fp);
+    set_insert_kernel<<<blocks, OB2_BLOCK, 0, st>>>(set->header, set->slots, set->n_slots - 1, n, fp, nullptr, 0);
     return ob2_check_cuda(cudaGetLastError(), "set_insert_kernel launch");
 }
 
@@ -525,19 +542,23 @@ namespace {
 // 7/8 load limit (n_reserve <= n: an exchange inbox is launched over its padded lanes but
 // only its real entries can be inserted).
 int dedup_launch(ob2_set *set, int64_t n, int64_t n_reserve, const uint64_t *fp, const uint32_t *order,
-                 uint32_t *scratch, uint8_t *keep, cudaStream_t st, const char *who) {
+                 uint32_t *scratch, uint8_t *keep, cudaStream_t st, const char *who,
+                 const uint32_t *lane_cnt = nullptr, int64_t lane_cap = 0) {
     int rc = reserve(set, n_reserve, st);
     if (rc != OB2_OK) return rc;
     unsigned blocks;
     rc = grid_for(n, &blocks);
     if (rc != OB2_OK) return rc;
+    dim3 grid1(blocks);
+    if (lane_cnt != nullptr) grid1 = dim3((unsigned)((lane_cap + OB2_BLOCK - 1) / OB2_BLOCK), (unsigned)(n / lane_cap));
     if (set->epoch == 0xFFFFFFFFu) {
         ob2_set_error("%s: epoch counter exhausted", who);
         return OB2_ETOOBIG;
     }
     const uint32_t epoch = ++set->epoch;
     OB2_CUDA(cudaMemsetAsync(&set->header->n_conflicts, 0, sizeof(uint32_t), st));
-    set_dedup_pass1<<<blocks, OB2_BLOCK, 0, st>>>(set->header, set->slots, set->n_slots - 1, n, fp, order, epoch, scratch, keep);
+    set_dedup_pass1<<<grid1, OB2_BLOCK, 0, st>>>(set->header, set->slots, set->n_slots - 1, n, fp, order, epoch, scratch, keep,
+                                                 lane_cnt, lane_cap);
     rc = ob2_check_cuda(cudaGetLastError(), "set_dedup_pass1 launch");
     if (rc != OB2_OK) return rc;
     const unsigned blocks2 = blocks < 592u ? blocks : 592u;  // the list is ~1 % of the batch: 4 CTAs per SM walk it
@@ -565,14 +586,16 @@ bool ob2_set_would_trip(const ob2_set *set, int64_t n) {
 }
 
 int ob2_set_dedup_padded(ob2_set *set, int64_t n, int64_t n_real, const uint64_t *fp, const uint32_t *order,
-                         uint32_t *scratch, uint8_t *keep, void *stream) {
+                         uint32_t *scratch, uint8_t *keep, void *stream, const uint32_t *lane_cnt, int64_t lane_cap) {
     int rc = check_set_args(set, n, fp);
     if (rc != OB2_OK) return rc;
     if (n == 0) return OB2_OK;
-    return dedup_launch(set, n, n_real, fp, order, scratch, keep, static_cast<cudaStream_t>(stream), "ob2_xchg_dedup");
+    return dedup_launch(set, n, n_real, fp, order, scratch, keep, static_cast<cudaStream_t>(stream), "ob2_xchg_dedup",
+                        lane_cnt, lane_cap);
 }
 
-int ob2_set_insert_padded(ob2_set *set, int64_t n, int64_t n_real, const uint64_t *fp, void *stream) {
+int ob2_set_insert_padded(ob2_set *set, int64_t n, int64_t n_real, const uint64_t *fp, void *stream,
+                          const uint32_t *lane_cnt, int64_t lane_cap) {
     int rc = check_set_args(set, n, fp);
     if (rc != OB2_OK) return rc;
     if (n == 0) return OB2_OK;
@@ -582,7 +605,9 @@ int ob2_set_insert_padded(ob2_set *set, int64_t n, int64_t n_real, const uint64_
     unsigned blocks;
     rc = grid_for(n, &blocks);
     if (rc != OB2_OK) return rc;
-    set_insert_kernel<<<blocks, OB2_BLOCK, 0, st>>>(set->header, set->slots, set->n_slots - 1, n, fp);
+    dim3 grid(blocks);
+    if (lane_cnt != nullptr) grid = dim3((unsigned)((lane_cap + OB2_BLOCK - 1) / OB2_BLOCK), (unsigned)(n / lane_cap));
+    set_insert_kernel<<<grid, OB2_BLOCK, 0, st>>>(set->header, set->slots, set->n_slots - 1, n, fp, lane_cnt, lane_cap);
     return ob2_check_cuda(cudaGetLastError(), "set_insert_kernel launch");
 }
 

@@ -129,9 +129,11 @@ static inline int ob2_check_align(const void *p, unsigned align, const char *who
 // library-internal set operations for an exchange inbox: kernels launched over `n` padded lanes,
 // load-factor accounting against the `n_real` entries that can actually be inserted (ob2_hashset.cu)
 bool ob2_set_would_trip(const ob2_set *set, int64_t n);
+// (lane_cnt != nullptr: the batch is `n / lane_cap` lanes of which only the first lane_cnt[y] entries are read)
 int ob2_set_dedup_padded(ob2_set *set, int64_t n, int64_t n_real, const uint64_t *fp, const uint32_t *order,
-                         uint32_t *scratch, uint8_t *keep, void *stream);
-int ob2_set_insert_padded(ob2_set *set, int64_t n, int64_t n_real, const uint64_t *fp, void *stream);
+                         uint32_t *scratch, uint8_t *keep, void *stream, const uint32_t *lane_cnt, int64_t lane_cap);
+int ob2_set_insert_padded(ob2_set *set, int64_t n, int64_t n_real, const uint64_t *fp, void *stream,
+                          const uint32_t *lane_cnt, int64_t lane_cap);
 
 // -------------------------------------------------------------- device side
 #define OB2_BLOCK 256

@@ -15,8 +15,9 @@
 //
 // The caller orders the three phases across ranks with two stream-ordered
 // barriers per batch (any tiny collective on the same stream): one after send,
-// one after dedup.  No staging buffers, no zero-padding of bucket tails on the
-// wire (counts travel instead), three collectives fewer per batch.
+// one after dedup.  No staging buffers, no zero-padding of bucket tails anywhere
+// (counts travel instead, and the owner's set kernels read only what arrived),
+// three collectives fewer per batch.
 #include <cstdlib>
 #include <cstring>
 #include <new>
@@ -162,15 +163,6 @@ __global__ void xchg_counts_kernel(int rank, int world, const PeerTable *__restr
                                    const uint32_t *__restrict__ send_cnt) {
     const int o = threadIdx.x;
     if (o < world) reinterpret_cast<uint32_t *>(peers->base[o] + cnt_off)[rank] = send_cnt[o];
-}
-
-// owner side: blank the unused tail of every source lane so the inbox is a flat, padded batch
-__global__ void __launch_bounds__(OB2_BLOCK)
-xchg_pad_kernel(int64_t cap, const uint32_t *__restrict__ cnt, uint64_t *__restrict__ inbox_fp) {
-    const int src = blockIdx.y;
-    const int64_t used = min((int64_t)cnt[src], cap);
-    for (int64_t p = used + (int64_t)blockIdx.x * OB2_BLOCK + threadIdx.x; p < cap; p += (int64_t)gridDim.x * OB2_BLOCK)
-        reinterpret_cast<ulonglong2 *>(inbox_fp)[(int64_t)src * cap + p] = make_ulonglong2(0, 0);
 }
 
 // source side: PULL the verdicts of what I sent to owner `blockIdx.y` out of that owner's
@@ -362,12 +354,10 @@ extern "C" int ob2_xchg_dedup(ob2_xchg *x, ob2_set *set, int32_t insert_only, vo
     uint64_t *inbox_fp = reinterpret_cast<uint64_t *>(x->region + x->lay.fp_off);
     const uint32_t *inbox_key = reinterpret_cast<const uint32_t *>(x->region + x->lay.key_off);
     const uint32_t *cnt = reinterpret_cast<const uint32_t *>(x->region + x->lay.cnt_off);
-    if (!(insert_only & 2)) {  // (bit 1: the senders shipped whole zero-padded lanes, ob2_xchg_send_copy)
-        const dim3 grid(lane_blocks(x->cap), (unsigned)x->world);
-        xchg_pad_kernel<<<grid, OB2_BLOCK, 0, st>>>(x->cap, cnt, inbox_fp);
-        rc = ob2_check_cuda(cudaGetLastError(), "xchg_pad_kernel launch");
-        if (rc != OB2_OK) return rc;
-    }
+    // Store-based sends leave the tails of the lanes unwritten: the set kernels are launched lane by lane
+    // and read only the cnt[src] entries that arrived (no padding pass).  Bit 1 of insert_only: the senders
+    // shipped whole zero-padded lanes (ob2_xchg_send_copy), a flat launch is fine.
+    const uint32_t *lane_cnt = (insert_only & 2) ? nullptr : cnt;
     const int64_t lanes = (int64_t)x->world * x->cap;
     // The kernels run over the padded lanes, but only the entries really received can be
     // inserted: when the cheap host bound (which counts the padding) would trip the 7/8 load
@@ -380,10 +370,10 @@ extern "C" int ob2_xchg_dedup(ob2_xchg *x, ob2_set *set, int32_t insert_only, vo
         real = 0;
         for (int r = 0; r < x->world; ++r) real += (int64_t)h_cnt[r] < x->cap ? (int64_t)h_cnt[r] : x->cap;
     }
-    if (insert_only & 1) return ob2_set_insert_padded(set, lanes, real, inbox_fp, stream);
+    if (insert_only & 1) return ob2_set_insert_padded(set, lanes, real, inbox_fp, stream, lane_cnt, x->cap);
     // verdicts stay in MY region, lane by source; the sources pull them (ob2_xchg_collect)
     return ob2_set_dedup_padded(set, lanes, real, inbox_fp, inbox_key, x->scratch,
-                                reinterpret_cast<uint8_t *>(x->region + x->lay.verdict_off), stream);
+                                reinterpret_cast<uint8_t *>(x->region + x->lay.verdict_off), stream, lane_cnt, x->cap);
 }
 
 extern "C" int ob2_xchg_collect(ob2_xchg *x, int64_t n, uint8_t *keep, void *stream) {
