@@ -740,7 +740,7 @@ def run_b200(args):
     batch, tbatch, back = pipe.slots[0].batch, pipe.slots[0].tbatch, pipe.slots[0].back
     fused = not args.unfused
     # extra kernels of mine per step for the exchange: NCCL path bucket+pad+scatter; peer path send+counts+flag+pad+collect
-    exchange_launches = 0 if world == 1 else ((4 if sharded.copy else 5) if peer_exchange else 3)
+    exchange_launches = 0 if world == 1 else (4 if peer_exchange else 3)    # peer: send + counts + flag + collect (or bucket + pad + counts + flag, scatter)
     fp_in_reverse = fused and not args.fp_in_sampler     # fingerprints computed by the reverse kernel (default)
     rev = 'reverse+fingerprint' if fp_in_reverse else 'reverse'
     kernel_names = ['sample+transform', rev, 'dedup'] if fused else ['sample', 'transform', rev, 'dedup']
