@@ -61,7 +61,7 @@ def parse_args():
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--ref-cands', type=int, default=100000,
                     help='--impl reference: candidates per process per step (a bounded sample of the workload)')
-    ap.add_argument('--e2e-steps', type=int, default=4)
+    ap.add_argument('--e2e-steps', type=int, default=8)
     ap.add_argument('--workload', default='path', choices=['path', 'cfg5', 'cfg2'],
                     help="path: the whole hot path (config 5's dedup with config 3's transform chain on top, the default "
                          "line); cfg5: sample + fingerprint + dedup only (BASELINE.json config 5 as written, 581 B/candidate "
