@@ -135,7 +135,8 @@ class ShardedHistory(object):
             self.ops.dedup(self.history, fp[:n], None, keep)
             return keep
         b = self._route(fp, n, per_rank_n, check)
-        self.ops.dedup(self.history, b['in_fp'].view(-1, 2), b['in_key'].view(-1), b['verdict'])
+        self._owner_side(check, lambda: self.ops.dedup(self.history, b['in_fp'].view(-1, 2), b['in_key'].view(-1),
+                                                       b['verdict']))
         dist.all_to_all_single(b['back'], b['verdict'], group=self.group)
         keep.zero_()
         self.ops.scatter(b['out_src'].view(-1), b['back'], b['out_fp'].view(-1, 2), keep)
@@ -147,7 +148,25 @@ class ShardedHistory(object):
             self.ops.insert(self.history, fp[:n])
             return
         b = self._route(fp, n, n, check)
-        self.ops.insert(self.history, b['in_fp'].view(-1, 2))
+        self._owner_side(check, lambda: self.ops.insert(self.history, b['in_fp'].view(-1, 2)))
+
+    def _owner_side(self, check, call):
+        """Run the owner-side set operation.  With ``check`` a failure on ANY rank (a full
+        table that may not grow) is raised on EVERY rank -- a rank raising alone would leave
+        the others waiting in the next all-to-all."""
+        error = None
+        try:
+            call()
+        except _lib.Ob2Error as exc:
+            if not check:
+                raise
+            error = exc
+        if check:
+            failed = torch.tensor([1 if error else 0], dtype=torch.int32, device=self.device)
+            dist.all_reduce(failed, op=dist.ReduceOp.MAX, group=self.group)
+            if int(failed.item()):
+                raise _lib.Ob2Error("a history shard refused the batch (on this or another rank): %s"
+                                    % (error if error else "see the owning rank"))
 
     def check_overflow(self, n):
         """After a run of ``check=False`` calls with batches of ``n``: raise if
