@@ -211,6 +211,18 @@ int ob2_sample_from_uniform(const ob2_space *space, int64_t n, int64_t n_stride,
                             const double *U, void *cols, uint8_t *ok, uint64_t *fp,
                             void *stream);
 
+/* The same with the caller's OWN random stream, so that a seeded Space.sample(n, seed) returns the
+ * reference's values: B[S][n_stride] holds, per slot, what numpy's RandomState hands scipy for one
+ * draw (src/orion/algo/space.py:133-136 -> rv_generic.rvs): a uniform of random_sample() for uniform /
+ * reciprocal / Categorical slots (RandomState.choice, space.py:402-403) and, with
+ * OB2_BASE_NORMAL_VARIATE in flags, a variate of standard_normal() for norm slots (the kernel then only
+ * applies scale, loc, floor and the bounds check).  One attempt, no redraw: ok[i] tells the host which
+ * rows the reference would have drawn again (Real.sample, space.py:262-274). */
+#define OB2_BASE_NORMAL_VARIATE 1u
+int ob2_sample_from_base(const ob2_space *space, int64_t n, int64_t n_stride,
+                         const double *B, uint32_t flags, void *cols, uint8_t *ok, uint64_t *fp,
+                         void *stream);
+
 /* Space.__contains__ over N points -- src/orion/algo/space.py:521-545 over
  * Dimension.__contains__ :150-164, Integer.__contains__ :335-347 and
  * Categorical.__contains__ :415-426 (device: 0 <= index < n_cats).  With

@@ -15,6 +15,7 @@ DIST_UNIFORM, DIST_RECIPROCAL, DIST_NORM, DIST_CONST, DIST_NONE = 0, 1, 2, 3, 4
 OP_IDENTITY, OP_QUANTIZE, OP_TO_REAL, OP_ENUMERATE, OP_ONEHOT = 0, 1, 2, 3, 4
 TFLAG_FLOOR = 1
 SLOT_DIM_LAST = 1
+BASE_NORMAL_VARIATE = 1          # ob2_sample_from_base: norm slots receive standard normal variates
 SLOT_CAT_UNIFORM = 2
 SET_SLOT_BYTES = 32
 SET_HEADER_BYTES = 256
@@ -67,6 +68,7 @@ SIGNATURES = {
     'ob2_sample_dedup_host': (ctypes.c_int, [_vp, _vp, _i64, _u64, _u64, _vp, _vp, _vp, _vp]),
     'ob2_contains_host': (ctypes.c_int, [_vp, _i64, _vp, _i32, _vp, _vp]),
     'ob2_sample_from_uniform': (ctypes.c_int, [_vp, _i64, _i64, _vp, _vp, _vp, _vp, _vp]),
+    'ob2_sample_from_base': (ctypes.c_int, [_vp, _i64, _i64, _vp, ctypes.c_uint32, _vp, _vp, _vp, _vp]),
     'ob2_contains': (ctypes.c_int, [_vp, _i64, _i64, _vp, _i32, _vp, _vp]),
     'ob2_transform': (ctypes.c_int, [_vp, _i64, _i64, _vp, _vp, _vp]),
     'ob2_reverse': (ctypes.c_int, [_vp, _i64, _i64, _vp, _vp, _vp]),

@@ -190,6 +190,7 @@ struct WalkConst {  // loop invariants
     bool split, has1;
     uint64_t idx0, idx1;
     uint32_t k0, k1, pm0, pm1;
+    bool base_normal;  // injected mode only: norm slots receive standard normal variates, not uniforms
 };
 
 // ---- what a drawn pair of values costs downstream: stores (sampled / transformed / handed-out), the
@@ -332,8 +333,15 @@ __device__ __forceinline__ void generic_slot(const ob2_slot_desc *s_slots, const
             w.all1 &= c1 < d.n_cats;
         }
     } else {
-        double x0 = draw_real<EXT>(d, u0);
-        double x1 = draw_real<EXT>(d, u1);
+        double x0, x1;
+        if (!PHILOX && c.base_normal && d.dist == OB2_DIST_NORM) {
+            // the variate itself arrives (what RandomState.standard_normal hands scipy's norm._rvs)
+            x0 = __dadd_rn(__dmul_rn(u0, d.scale), d.loc);
+            x1 = __dadd_rn(__dmul_rn(u1, d.scale), d.loc);
+        } else {
+            x0 = draw_real<EXT>(d, u0);
+            x1 = draw_real<EXT>(d, u1);
+        }
         if (d.kind == OB2_KIND_INTEGER) {
             x0 = floor(x0);  // _Discrete.sample, space.py:294
             x1 = floor(x1);
@@ -511,6 +519,7 @@ __device__ __forceinline__ void sample_body(const ob2_slot_desc *s_slots, const 
     c.k1 = k1;
     c.pm0 = pm0;
     c.pm1 = pm1;
+    c.base_normal = !PHILOX && (base_index & OB2_BASE_NORMAL_VARIATE) != 0;  // injected mode: base_index carries the flags
     Walk w;
     w.acc0 = w.acc1 = FpAcc{0, 0};
     w.all0 = w.all1 = true;
@@ -1017,6 +1026,17 @@ extern "C" int ob2_contains_host(ob2_space *space, int64_t n, const void *host_c
 extern "C" int ob2_sample_from_uniform(const ob2_space *space, int64_t n, int64_t n_stride, const double *U,
                                        void *cols, uint8_t *ok, uint64_t *fp, void *stream) {
     const SampleArgs a{space, n, n_stride, 0, 0, nullptr, U, cols, nullptr, nullptr, ok, fp, nullptr, stream};
+    return launch_sample<false>(a);
+}
+
+extern "C" int ob2_sample_from_base(const ob2_space *space, int64_t n, int64_t n_stride, const double *B, uint32_t flags,
+                                    void *cols, uint8_t *ok, uint64_t *fp, void *stream) {
+    if (flags & ~(uint32_t)OB2_BASE_NORMAL_VARIATE) {
+        ob2_set_error("ob2_sample_from_base: unknown flag bits 0x%x", flags);
+        return OB2_EINVAL;
+    }
+    // the injected-mode kernels have no Philox counter: the base_index argument carries the flags
+    const SampleArgs a{space, n, n_stride, 0, flags, nullptr, B, cols, nullptr, nullptr, ok, fp, nullptr, stream};
     return launch_sample<false>(a);
 }
 

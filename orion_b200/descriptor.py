@@ -159,6 +159,7 @@ class CompiledSpace(object):
         self.unsamplable = None        # (dimension name, prior) without a device inverse CDF
         self.dim_first = []            # first slot of each dimension
         self.dim_bounds = []
+        self.dim_dists = []            # prior code of each dimension (None: categorical)
         slots = []
         cdf = []
         col_units = t_units = 0
@@ -190,6 +191,7 @@ class CompiledSpace(object):
                 low, high = float(low), float(high)
                 cdf_off = n_cats = 0
             self.dim_bounds.append((low, high))
+            self.dim_dists.append(None if kind == 'categorical' else dist)
             op = _OPS[requirement][kind]
             if op == _lib.OP_ONEHOT:
                 width, t_elem, t_dt = (1 if n_cats <= 2 else n_cats), 8, 'f8'
@@ -419,8 +421,10 @@ class CompiledSpace(object):
                 "Dimension '{}': prior '{}' has no device inverse CDF yet (supported: uniform, "
                 "reciprocal/loguniform, norm). There is no CPU fallback.".format(*self.unsamplable))
 
-    def sample_from_uniform(self, U, n=None, with_fingerprint=False):
-        """Parity mode: U is a float64 tensor [n_slots][n_stride] (device)."""
+    def sample_from_uniform(self, U, n=None, with_fingerprint=False, normal_variates=False):
+        """Injected random stream: U is a float64 tensor [n_slots][n_stride] (device) of uniforms -- the
+        parity mode -- or, with ``normal_variates``, of what numpy's RandomState hands scipy per draw
+        (standard normal variates for ``norm`` slots; ``ob2_sample_from_base``, see :mod:`.mt_stream`)."""
         self._require_samplable()
         assert U.dtype == torch.float64 and U.is_cuda and U.dim() == 2 and U.shape[0] == self.n_slots
         ns = U.shape[1]
@@ -432,8 +436,9 @@ class CompiledSpace(object):
         batch.mask = torch.empty(ns, dtype=torch.uint8, device=self.device)
         if with_fingerprint:
             batch.fp = torch.empty((ns, 2), dtype=torch.int64, device=self.device)
-        _lib.check(self.lib.ob2_sample_from_uniform(
-            self.handle, n, ns, U.data_ptr(), batch.buf.data_ptr(), batch.mask.data_ptr(),
+        _lib.check(self.lib.ob2_sample_from_base(
+            self.handle, n, ns, U.data_ptr(), _lib.BASE_NORMAL_VARIATE if normal_variates else 0,
+            batch.buf.data_ptr(), batch.mask.data_ptr(),
             batch.fp.data_ptr() if with_fingerprint else None, self._stream()))
         return batch
 

@@ -1,0 +1,166 @@
+"""The reference's own random stream for the list-returning interface.
+
+``Space.sample(n, seed)`` / ``Dimension.sample(n, seed)`` of the reference draw every value through
+numpy's MT19937 ``RandomState`` (reference ``src/orion/algo/space.py:133-136, 262-274, 294, 400-404,
+482-484``): scipy's ``rvs`` asks it for ONE number per scalar -- ``random_sample()`` for ``uniform``
+(``uniform_gen._rvs``), ``reciprocal`` / ``loguniform`` (the generic ``_ppf(uniform())``) and for
+``RandomState.choice`` of a Categorical, ``standard_normal()`` for ``norm`` -- dimension by dimension,
+sample by sample, drawing a rejected Real / Integer value again up to four times.
+
+This module hands that stream to the device: the host only ASKS numpy for the numbers (that is where
+the reference's random state lives; the caller may own it, or it is numpy's global one), the kernel
+turns them into values (inverse CDF or scale/shift, ``floor``, cdf search, bounds check;
+``ob2_sample_from_base``), and the accept / reject book-keeping of ``Real.sample`` is replayed on the
+verdict bytes it returns.  A seeded call therefore returns what the reference returns for the same
+seed and leaves the ``RandomState`` where the reference leaves it: bit for bit for ``uniform``,
+``norm``, Integer and Categorical dimensions, to the last ulp or two of ``exp`` for ``reciprocal``.
+
+Priors whose scipy ``_rvs`` uses another numpy generator (``expon`` -> ``standard_exponential``,
+``gamma``, ``poisson`` ...) and ``numpy.random.Generator`` seeds cannot be reproduced this way;
+:func:`reproducible` says no for them and the callers keep the Philox stream of the tensor path.
+"""
+import numpy
+import torch
+
+from . import _lib
+from .descriptor import round_up
+
+UNIFORM, NORMAL, NOTHING = 'random_sample', 'standard_normal', 'nothing'
+
+#: switch for the list-returning interface (``Space.sample``, ``Dimension.sample``,
+#: ``Random.suggest`` without dedup): False keeps every draw on the Philox stream
+ENABLED = True
+
+_KIND_OF_DIST = {_lib.DIST_UNIFORM: UNIFORM, _lib.DIST_RECIPROCAL: UNIFORM, _lib.DIST_NORM: NORMAL,
+                 _lib.DIST_CONST: NOTHING,       # scale == 0: rvs returns loc without drawing
+                 None: UNIFORM}                  # Categorical: RandomState.choice -> random_sample
+
+
+def stream_kinds(compiled):
+    """Which RandomState method feeds each dimension of ``compiled``, or None when some prior's
+    ``_rvs`` is not a function of ``random_sample`` / ``standard_normal`` numbers."""
+    kinds = [_KIND_OF_DIST.get(d, None) for d in compiled.dim_dists]
+    return None if any(k is None for k in kinds) else kinds
+
+
+def reproducible(compiled, rng):
+    return ENABLED and isinstance(rng, numpy.random.RandomState) and stream_kinds(compiled) is not None
+
+
+def _ask(rng, kind, count):
+    if kind == UNIFORM:
+        return rng.random_sample(count)
+    if kind == NORMAL:
+        return rng.standard_normal(count)
+    return numpy.empty(0)
+
+
+def _evaluate(compiled, base, n):
+    """base: float64 [n_slots][n] -> (host columns, ok[n]) through the kernel."""
+    ns = round_up(max(n, 1))
+    block = numpy.full((compiled.n_slots, ns), 0.5)
+    block[:, :n] = base
+    batch = compiled.sample_from_uniform(torch.from_numpy(block).to(compiled.device), n, normal_variates=True)
+    ok = batch.mask[:n].cpu().numpy().astype(bool)
+    return batch.to_numpy(), ok
+
+
+def _improbable(dim):
+    return ValueError("Improbable bounds: (low={0}, high={1}). "
+                      "Please make interval larger.".format(dim._low, dim._high))
+
+
+def sample_space(dims, compiled, n, rng):
+    """All dimensions in ONE launch, for the (overwhelmingly common) call in which no value is
+    rejected: dimension-major stream, exactly ``[dim.sample(n, rng) for dim in space.values()]``.
+    Returns the host columns, or None -- with ``rng`` put back where it was -- when some row missed
+    its bounds and the caller has to go dimension by dimension."""
+    kinds = stream_kinds(compiled)
+    state = rng.get_state()
+    base = numpy.full((compiled.n_slots, n), 0.5)
+    for first, width, kind in zip(compiled.dim_first, compiled.dim_widths, kinds):
+        if kind != NOTHING:
+            base[first:first + width] = _ask(rng, kind, n * width).reshape(n, width).T
+    cols, ok = _evaluate(compiled, base, n)
+    rejecting = [d.type in ('real', 'integer') for d in dims]
+    if ok.all() or not any(rejecting):
+        return cols
+    rng.set_state(state)
+    return None
+
+
+def space_columns(dims, compiled, solo, n, rng):
+    """Host columns of ``[dim.sample(n, rng) for dim in dims]`` (space.py:482-484): one launch when
+    nothing is rejected, else dimension by dimension (``solo(dim)``: that dimension compiled alone)."""
+    cols = sample_space(dims, compiled, n, rng)
+    if cols is None:
+        cols = []
+        for dim in dims:
+            cols.extend(sample_dimension(dim, solo(dim), n, rng))
+    return cols
+
+
+def sample_dimension(dim, compiled, n, seed):
+    """``dim.sample(n, seed)`` of the reference as host columns (one per element of the shape).
+
+    ``compiled``: the dimension compiled as a one-dimension space.  An attempt consumes exactly
+    ``width`` numbers whether it is accepted or not, so the stream is a sequence of equal chunks:
+    the kernel evaluates a run of chunks at once and the four-attempt rule of ``Real.sample``
+    (space.py:262-274) is replayed over their verdicts; the RandomState is then left exactly as
+    many chunks further as the reference consumes."""
+    from scipy._lib._util import check_random_state
+    kind = stream_kinds(compiled)[0]
+    width = compiled.n_slots
+    rejects = dim.type in ('real', 'integer')       # bare Dimension and Categorical take what comes
+    if n <= 0:
+        return [numpy.empty(0, dtype=dt) for _, dt in compiled.col_meta]
+    if isinstance(seed, (int, numpy.integer)) and dim.type != 'categorical':
+        # rvs(random_state=<int>) seeds a fresh RandomState for EVERY draw (space.py:128-131 warns
+        # about it): n copies of one value, and a rejected one is rejected four times over
+        cols, ok = _evaluate(compiled, _ask(numpy.random.RandomState(seed), kind, width).reshape(1, -1).T
+                             if kind != NOTHING else numpy.full((width, 1), 0.5), 1)
+        if rejects and not ok[0]:
+            raise _improbable(dim)
+        return [numpy.repeat(c[:1], n) for c in cols]
+    rng = check_random_state(seed)
+    if kind == NOTHING:
+        cols, ok = _evaluate(compiled, numpy.full((width, 1), 0.5), 1)
+        if rejects and not ok[0]:
+            raise _improbable(dim)
+        return [numpy.repeat(c[:1], n) for c in cols]
+    state = rng.get_state()
+    chunks = n
+    while True:
+        cols, ok = _evaluate(compiled, _ask(rng, kind, chunks * width).reshape(chunks, width).T, chunks)
+        if not rejects or ok[:n].all():
+            take, used, failed = slice(0, n), n, False
+        else:
+            take, used, failed = _replay_attempts(ok, n)
+            if take is None:                        # ran out of evaluated chunks: look further ahead
+                rng.set_state(state)
+                chunks = 2 * chunks + 8
+                continue
+        if used != chunks:                          # leave the RandomState where the reference leaves it
+            rng.set_state(state)
+            _ask(rng, kind, used * width)
+        if failed:
+            raise _improbable(dim)
+        return [c[take] for c in cols]
+
+
+def _replay_attempts(ok, n):
+    """Real.sample over the verdicts of consecutive attempts: (indices taken, chunks consumed,
+    gave up?) or (None, ..) when ``ok`` is too short to decide."""
+    take = []
+    j = 0
+    for _ in range(n):
+        for _attempt in range(4):
+            if j >= len(ok):
+                return None, j, False
+            j += 1
+            if ok[j - 1]:
+                take.append(j - 1)
+                break
+        else:
+            return take, j, True
+    return numpy.asarray(take, dtype=numpy.int64), j, False

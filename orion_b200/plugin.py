@@ -44,8 +44,12 @@ def _define():
 
         def suggest(self, num=1):
             from .space import Space as MirrorSpace
-            batch = self.suggest_columns(num)
-            return MirrorSpace.rows_from_columns(self.space, batch.to_numpy(), num)
+            # Random.suggest is space.sample(num) on numpy's global state (random.py:24-33): the same
+            # numbers go to the kernel, so after numpy.random.seed(s) this returns what `random` returns
+            cols = MirrorSpace.reference_stream_columns(self.space, num, None)
+            if cols is None:                        # a prior scipy does not draw from uniforms / normals
+                cols = self.suggest_columns(num).to_numpy()
+            return MirrorSpace.rows_from_columns(self.space, cols, num)
 
         def observe(self, points, results):
             pass

@@ -5,11 +5,16 @@ names (`Dimension`, `Real`, `Integer`, `Categorical`, `Space`), constructor
 arguments, error behaviour and return types, so code written against
 ``orion.algo.space`` runs unchanged.  What differs is where the work happens:
 
-* ``sample`` draws on the GPU (Philox4x32-10 -> inverse CDF -> fused bounds
-  check and <=4-attempt rejection; :mod:`orion_b200.csrc`), not through
-  ``scipy.rvs`` one scalar at a time.  A seed (None / int / RandomState, as in
-  the reference) selects the Philox key, so draws are reproducible under the
-  same seeding discipline but are not MT19937's values.
+* ``sample`` computes on the GPU, not through ``scipy.rvs`` one scalar at a
+  time.  The list-returning calls (``Space.sample``, ``Dimension.sample``)
+  feed the kernel the reference's own MT19937 stream (:mod:`.mt_stream`), so
+  a seed (None / int / RandomState) returns the reference's values and leaves
+  the RandomState where the reference leaves it -- for the priors whose scipy
+  ``_rvs`` is a function of ``random_sample`` / ``standard_normal`` numbers
+  (uniform, reciprocal / loguniform, norm, Categorical).  The tensor calls
+  (``sample_columns`` and everything bulk) and the remaining priors draw from
+  Philox4x32 keyed by the seed (inverse CDF, fused bounds check, <= 4 attempts):
+  reproducible under the same seeding discipline, other values.
 * ``in`` checks run the ``ob2_contains`` kernel with bounds resolved once.
 * ``Space.sample_columns`` / ``Space.contains_columns`` are the added
   tensor-returning fast path; ``Space.sample`` converts the same device result
@@ -24,6 +29,7 @@ import numpy
 from scipy._lib._util import check_random_state
 from scipy.stats import distributions
 
+from . import mt_stream
 from ._lib import HOST_SAMPLE_MAX
 from .columns import ColumnBatch
 from .descriptor import compile_space
@@ -34,6 +40,27 @@ _BANNED = {
     'discrete': "Do not use kwarg 'discrete' on `Dimension`, use pure `_Discrete` class instead!",
     'size': "Use 'shape' keyword only instead of 'size'.",
 }
+
+
+def _stream_owner(seed):
+    """The RandomState a seed argument stands for (an int seeds fresh ones: any RandomState will do
+    to say so), or whatever else ``check_random_state`` makes of it."""
+    if isinstance(seed, (int, numpy.integer)):
+        return _ANY_RANDOM_STATE
+    return check_random_state(seed)
+
+
+_ANY_RANDOM_STATE = numpy.random.RandomState(0)
+
+
+def _solo_compiled(dim):
+    """``dim`` compiled as a one-dimension space, cached on the object (also a reference Dimension)."""
+    compiled = dim.__dict__.get('_compiled_self')
+    if compiled is None:
+        solo = _OneDim()
+        solo[dim.name or '_'] = dim
+        compiled = dim.__dict__['_compiled_self'] = compile_space(solo)
+    return compiled
 
 
 def philox_key(seed):
@@ -136,11 +163,7 @@ class Dimension(object):
     # -- device plumbing ---------------------------------------------------
     def _compiled(self):
         """This dimension compiled as a one-dimension space (cached)."""
-        if self._compiled_self is None:
-            solo = _OneDim()
-            solo[self.name or '_'] = self
-            self._compiled_self = compile_space(solo)
-        return self._compiled_self
+        return _solo_compiled(self)
 
     def _column_values(self, point):
         return _column_values(self, point)
@@ -153,11 +176,15 @@ class Dimension(object):
         """Draw ``n_samples`` values from the prior; returns a list.
 
         ``seed``: None | int | numpy.random.RandomState, as in the reference
-        (space.py:110-136).  An int re-creates the same key on every call, so
-        the same values come back; pass a RandomState to advance.
+        (space.py:110-136), and with the reference's values for it when the
+        prior draws from ``random_sample`` / ``standard_normal`` numbers
+        (:mod:`.mt_stream`): an int seeds afresh for every draw, so the same
+        value comes back ``n_samples`` times; pass a RandomState to advance.
         """
         compiled = self._compiled()
-        if n_samples <= HOST_SAMPLE_MAX:            # one library call: kernel + copy + sync
+        if mt_stream.reproducible(compiled, _stream_owner(seed)):
+            cols = mt_stream.sample_dimension(self, compiled, n_samples, seed)
+        elif n_samples <= HOST_SAMPLE_MAX:          # one library call: kernel + copy + sync
             cols, failed = compiled.sample_host(n_samples, philox_key(seed))
             _raise_if_failed(failed, compiled, [self])
         else:
@@ -316,6 +343,9 @@ class Space(OrderedDict):
         order (space.py:456-484)."""
         if not self:
             return []
+        cols = self.reference_stream_columns(n_samples, seed)
+        if cols is not None:
+            return self.rows_from_columns(cols, n_samples)
         if n_samples <= HOST_SAMPLE_MAX:            # one library call: kernel + copy + sync
             compiled = self.compiled()
             cols, failed = compiled.sample_host(n_samples, philox_key(seed))
@@ -323,6 +353,16 @@ class Space(OrderedDict):
             return self.rows_from_columns(cols, n_samples)
         batch = self.sample_columns(n_samples, seed)
         return self.rows_from_columns(batch.to_numpy(), n_samples)
+
+    def reference_stream_columns(self, n_samples, seed):
+        """Host columns of ``[dim.sample(n, rng) for dim in self.values()]`` drawn from the reference's
+        own MT19937 stream (space.py:482-484; :mod:`.mt_stream`), or None when this space or seed
+        cannot be reproduced that way.  ``self`` may be a reference Space."""
+        compiled = compile_space(self)
+        rng = check_random_state(seed)
+        if n_samples <= 0 or not mt_stream.reproducible(compiled, rng):
+            return None
+        return mt_stream.space_columns(list(self.values()), compiled, _solo_compiled, n_samples, rng)
 
     def rows_from_columns(self, host_cols, n):
         """Host columns -> the reference's list of tuples."""

@@ -344,6 +344,10 @@ class TransformedSpace(Space):
     def sample(self, n_samples=1, seed=None):
         """``[transform(p) for p in original.sample(n, seed)]`` -- computed as
         one device batch."""
+        cols = self.original.reference_stream_columns(n_samples, seed)
+        if cols is not None:                        # the reference's own stream, then the transform kernel
+            batch = ColumnBatch.from_numpy(self.compiled(), cols)
+            return self._rows_from_tcols(self.compiled().transform(batch).to_numpy(), n_samples)
         _, tbatch = self.sample_columns(n_samples, seed)
         return self._rows_from_tcols(tbatch.to_numpy(), n_samples)
 

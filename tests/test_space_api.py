@@ -2,11 +2,11 @@
 
 These follow the reference's own ``tests/unittests/algo/test_space.py`` case
 by case (same constructions, same expected intervals / membership / errors /
-reprs).  What cannot carry over literally is equality with MT19937-seeded scipy
-draws -- values come from Philox on the device -- so those assertions become:
-same type and shape, inside the dimension, reproducible under the reference's
-seeding discipline.  Construction-only checks run on CPU; anything that samples
-or tests membership needs the GPU.
+reprs), INCLUDING its equalities with MT19937-seeded scipy draws: the
+list-returning calls feed the kernel the reference's own random stream
+(orion_b200/mt_stream.py), so ``dists.norm.rvs(0.9, 0.1) == samples[0]`` and the
+known answers -2 / 'asdfa' / 2 hold as written there.  Construction-only checks
+run on CPU; anything that samples or tests membership needs the GPU.
 """
 from collections import OrderedDict
 
@@ -35,8 +35,7 @@ class TestDimension(object):
         samples = dim.sample(seed=seed)
         assert len(samples) == 1
         assert isinstance(samples[0], np.float64)
-        # seeded instance and the same global seed pick the same Philox key (test_space.py:29-32)
-        assert dim.sample()[0] == samples[0]
+        assert dists.norm.rvs(0.9, 0.1) == samples[0]           # test_space.py:30
         assert dists.norm.interval(1.0, 0.9, 0.1) == dim.interval()
         assert dists.norm.interval(0.5, 0.9, 0.1) == dim.interval(0.5)
         assert 1.0 in dim
@@ -51,10 +50,12 @@ class TestDimension(object):
         samples = dim.sample(seed=seed)
         assert len(samples) == 1
         assert samples[0].shape == (3, 2) and samples[0].dtype == np.float64
+        assert np.array_equal(dists.norm.rvs(0.9, size=(3, 2)), samples[0])     # test_space.py:48
         assert dim.shape == (3, 2)
         dim = Dimension('yolo', 'norm', 0.9, shape=4)
         samples = dim.sample(seed=seed)
         assert samples[0].shape == (4,)
+        assert np.array_equal(dists.norm.rvs(0.9, size=4), samples[0])          # test_space.py:55
         assert dim.shape == (4,)
 
     def test_ban_size_kwarg(self):
@@ -73,7 +74,8 @@ class TestDimension(object):
     def test_with_predefined_dist(self, seed):
         dim = Dimension('yolo', dists.norm, 0.9)
         samples = dim.sample(seed=seed)
-        assert len(samples) == 1 and np.isfinite(samples[0])
+        assert len(samples) == 1
+        assert dists.norm.rvs(0.9) == samples[0]                # test_space.py:79
 
     def test_ban_discrete_kwarg(self):
         with pytest.raises(ValueError) as exc:
@@ -85,16 +87,18 @@ class TestDimension(object):
         dim = Dimension('yolo', 'uniform', -3, 4, shape=(4, 4))
         samples = dim.sample(n_samples=4, seed=seed)
         assert len(samples) == 4
+        assert np.array_equal(dists.uniform.rvs(-3, 4, size=(4, 4)), samples[0])    # test_space.py:93
         assert all(s.shape == (4, 4) for s in samples)
         assert not np.array_equal(samples[0], samples[1])
         assert all(s in dim for s in samples)
 
     @gpu
     def test_int_seed_repeats_and_random_state_advances(self):
-        """space.py:118-127: an int seed gives the same draw every call; a
-        RandomState carries on."""
+        """space.py:118-131: an int seed gives the same draw every call -- every VALUE, since
+        scipy seeds afresh per rvs; a RandomState carries on."""
         dim = Real('yolo', 'uniform', -3, 4)
         assert dim.sample(3, seed=7) == dim.sample(3, seed=7)
+        assert dim.sample(3, seed=7) == [dists.uniform.rvs(-3, 4, random_state=7)] * 3
         rng = np.random.RandomState(7)
         assert dim.sample(3, seed=rng) != dim.sample(3, seed=rng)
 
@@ -134,6 +138,7 @@ class TestReal(object):
         dim = Real('yolo', 'norm', 0.9)
         samples = dim.sample(seed=seed)
         assert len(samples) == 1
+        assert dists.norm.rvs(0.9) == samples[0]                # test_space.py:134
         assert dists.norm.interval(1.0, 0.9) == dim.interval()
         assert dists.norm.interval(0.5, 0.9) == dim.interval(0.5)
         assert 1.0 in dim
@@ -187,7 +192,8 @@ class TestInteger(object):
         dim = Integer('yolo', 'uniform', -3, 6)
         samples = dim.sample(seed=seed)
         assert len(samples) == 1
-        assert isinstance(samples[0], np.int64) and -3 <= samples[0] < 3
+        assert isinstance(samples[0], np.int64)
+        assert samples[0] == -2                                 # test_space.py:198
         assert dim.interval() == (-3, 3)
         assert dim.interval(0.5) == (-2, 2)
         assert 1.0 in dim
@@ -229,7 +235,7 @@ class TestCategorical(object):
         dim = Categorical('yolo', categories)
         samples = dim.sample(seed=seed)
         assert len(samples) == 1
-        assert samples[0] in categories
+        assert samples[0] == 'asdfa'                            # test_space.py:250
         assert dim._probs == (0.5, 0.5)
         assert categories == dim.categories
         assert 2 in dim
@@ -245,7 +251,8 @@ class TestCategorical(object):
         categories = ('asdfa', 2, 3, 4)
         dim = Categorical('yolo', OrderedDict(zip(categories, probs)))
         samples = dim.sample(seed=seed)
-        assert len(samples) == 1 and samples[0] in categories
+        assert len(samples) == 1
+        assert samples[0] == 2                                  # test_space.py:271
         assert dim._probs == probs
         assert categories == dim.categories
         assert 2 in dim
@@ -334,8 +341,19 @@ class TestSpace(object):
     def test_sample(self, seed):
         """Ordering = dimension order; one seed drives the whole call (test_space.py:384-417)."""
         space = _three_dim_space(cat_shape=(2, 2))
+        dim1, dim2, dim3 = space.values()
         point = space.sample(seed=seed)
-        assert len(point) == 1 and len(point[0]) == 3
+        test_point = [(dim1.sample()[0], dim2.sample()[0], dim3.sample()[0])]      # numpy's global state, seeded alike
+        assert len(point) == len(test_point) == 1 and len(point[0]) == len(test_point[0]) == 3
+        assert np.all(point[0][0] == test_point[0][0])
+        assert point[0][1] == test_point[0][1] and point[0][2] == test_point[0][2]
+        points = space.sample(2, seed=seed)
+        points1, points2, points3 = dim1.sample(2), dim2.sample(2), dim3.sample(2)
+        for i in range(2):
+            assert np.all(points[i][0] == points1[i])
+            assert points[i][1] == points2[i] and points[i][2] == points3[i]
+        seed = np.random.RandomState(5)
+        point = space.sample(seed=seed)
         assert point[0][0].shape == (2, 2) and point[0] in space
         assert isinstance(point[0][1], np.int64) and isinstance(point[0][2], np.float64)
         points = space.sample(2, seed=seed)
@@ -349,8 +367,10 @@ class TestSpace(object):
         assert all(np.all(x[0] == y[0]) and x[1:] == y[1:] for x, y in zip(a, b))
 
     @gpu
-    def test_sample_columns_fast_path(self):
-        """The tensor path returns the same values the tuple path converts."""
+    def test_sample_columns_fast_path(self, monkeypatch):
+        """The tensor path returns the same values the tuple path converts when both use Philox."""
+        from orion_b200 import mt_stream
+        monkeypatch.setattr(mt_stream, 'ENABLED', False)
         space = _three_dim_space(cat_shape=(2, 2))
         batch = space.sample_columns(100, seed=4)
         rows = space.rows_from_columns(batch.to_numpy(), 100)
