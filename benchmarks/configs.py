@@ -34,28 +34,39 @@ def timed(fn, reps, warm=3):
 def main():
     out = {}
     # config 1: random search on 2-dim Rosenbrock, suggest(10) x 100, in process
-    algo = PrimaryAlgo(spaces.rosen2(), {'random': {'seed': 1}})
+    # (seed None: numpy's global state, as the reference's Random draws -- the kernel is fed that stream, so both
+    # loops below see the same 1000 points after the same numpy.random.seed)
+    import numpy
+    algo = PrimaryAlgo(spaces.rosen2(), 'random')
     algo.suggest(10)
+    numpy.random.seed(1)
     t0 = time.perf_counter()
     best = float('inf')
+    mine = []
     for _ in range(100):
         pts = algo.suggest(10)
+        mine.extend(pts)
         best = min(best, min((1 - x) ** 2 + 100 * (y - x ** 2) ** 2 for x, y in pts))
     dt = time.perf_counter() - t0
     out['config1_rosen2_suggest10_x100'] = {'seconds': dt, 'candidates_per_s': 1000 / dt, 'best_objective': best,
-                                            'note': 'list-of-tuples API: launch + D2H + Python tuples per call'}
+                                            'note': "list-of-tuples API on the reference's own MT19937 stream: numbers in, "
+                                                    "launch, D2H, Python tuples per call"}
     # the same loop through the UNMODIFIED reference (oracle/_ref), for the record: it is config 1's own CPU path
     try:
         from oracle import ref_harness
         ref_space = ref_harness.build_space(['-x~uniform(-5, 10)', '-y~uniform(-5, 10)'])
         ref_algo = ref_harness.primary_algo(ref_space, 'random')
         ref_algo.suggest(10)
+        numpy.random.seed(1)
         t0 = time.perf_counter()
         ref_best = float('inf')
+        theirs = []
         for _ in range(100):
             rp = ref_algo.suggest(10)
+            theirs.extend(rp)
             ref_best = min(ref_best, min((1 - x) ** 2 + 100 * (y - x ** 2) ** 2 for x, y in rp))
         rdt = time.perf_counter() - t0
+        out['config1_same_1000_points_as_the_reference'] = bool(mine == theirs)
         out['config1_reference_cpu_path'] = {'seconds': rdt, 'candidates_per_s': 1000 / rdt, 'best_objective': ref_best,
                                              'note': "the reference's PrimaryAlgo(space, 'random').suggest(10) x 100, one core"}
     except ImportError as exc:
@@ -65,11 +76,18 @@ def main():
                       ('space.sample(1)', lambda: space.sample(1)),
                       ('points in space (10)', lambda: space.contains_points(pts)),
                       ('mixed64.sample(10)', lambda m=spaces.mixed64(): m.sample(10))):
-        fn()
-        t0 = time.perf_counter()
-        for _ in range(300):
+        from orion_b200 import mt_stream
+        for stream in ('reference stream', 'Philox stream'):
+            if stream == 'Philox stream' and 'sample' not in label:
+                continue
+            mt_stream.ENABLED = stream == 'reference stream'
             fn()
-        out['config1_us_per_call ' + label] = (time.perf_counter() - t0) / 300 * 1e6
+            t0 = time.perf_counter()
+            for _ in range(300):
+                fn()
+            key = 'config1_us_per_call ' + label + (' [%s]' % stream if 'sample' in label else '')
+            out[key] = (time.perf_counter() - t0) / 300 * 1e6
+        mt_stream.ENABLED = True
     # config 2: Space.sample 1M points, real16
     c = spaces.real16().compiled()
     for n in (1_000_000, 100_000_000):

@@ -223,6 +223,13 @@ int ob2_sample_from_base(const ob2_space *space, int64_t n, int64_t n_stride,
                          const double *B, uint32_t flags, void *cols, uint8_t *ok, uint64_t *fp,
                          void *stream);
 
+/* The same for a handful of points with HOST buffers (n <= OB2_HOST_SAMPLE_MAX; the seeded
+ * Space.sample(n, seed) / Dimension.sample calls of the reference's users and tests): host_base is
+ * [S][n_stride] with n_stride = n rounded up to 32, host_cols a column block of that stride, host_ok
+ * n verdict bytes.  One copy in, one kernel, one copy out, one synchronisation. */
+int ob2_sample_from_base_host(ob2_space *space, int64_t n, const double *host_base, uint32_t flags,
+                              void *host_cols, uint8_t *host_ok, void *stream);
+
 /* Space.__contains__ over N points -- src/orion/algo/space.py:521-545 over
  * Dimension.__contains__ :150-164, Integer.__contains__ :335-347 and
  * Categorical.__contains__ :415-426 (device: 0 <= index < n_cats).  With

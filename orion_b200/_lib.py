@@ -69,6 +69,7 @@ SIGNATURES = {
     'ob2_contains_host': (ctypes.c_int, [_vp, _i64, _vp, _i32, _vp, _vp]),
     'ob2_sample_from_uniform': (ctypes.c_int, [_vp, _i64, _i64, _vp, _vp, _vp, _vp, _vp]),
     'ob2_sample_from_base': (ctypes.c_int, [_vp, _i64, _i64, _vp, ctypes.c_uint32, _vp, _vp, _vp, _vp]),
+    'ob2_sample_from_base_host': (ctypes.c_int, [_vp, _i64, _vp, ctypes.c_uint32, _vp, _vp, _vp]),
     'ob2_contains': (ctypes.c_int, [_vp, _i64, _i64, _vp, _i32, _vp, _vp]),
     'ob2_transform': (ctypes.c_int, [_vp, _i64, _i64, _vp, _vp, _vp]),
     'ob2_reverse': (ctypes.c_int, [_vp, _i64, _i64, _vp, _vp, _vp]),

@@ -62,6 +62,7 @@ struct ob2_space {
     // ob2_sample_host: one device block and its pinned mirror, allocated on first use
     // ([columns: row_bytes * OB2_HOST_SAMPLE_MAX][n_failed: n_slots u32]); calls serialise on the mutex
     void *d_stage, *h_stage;
+    void *d_base, *h_base;  // ob2_sample_from_base_host: the caller's random numbers, [n_slots][OB2_HOST_SAMPLE_MAX] doubles
     std::mutex *stage_mutex;
     int32_t t_cols;      // number of transformed columns
     size_t smem_bytes;   // descriptor + cdf staging size

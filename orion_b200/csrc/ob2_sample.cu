@@ -1040,6 +1040,52 @@ extern "C" int ob2_sample_from_base(const ob2_space *space, int64_t n, int64_t n
     return launch_sample<false>(a);
 }
 
+// Space.sample(n, seed) for a handful of points on the caller's own random stream (see ob2_sample_from_base):
+// numbers in, kernel, columns and row verdicts out, one synchronisation.
+extern "C" int ob2_sample_from_base_host(ob2_space *space, int64_t n, const double *host_base, uint32_t flags,
+                                         void *host_cols, uint8_t *host_ok, void *stream) {
+    if (space == nullptr || host_base == nullptr || host_cols == nullptr || host_ok == nullptr) {
+        ob2_set_error("ob2_sample_from_base_host: null argument");
+        return OB2_EINVAL;
+    }
+    if (n < 0 || n > OB2_HOST_SAMPLE_MAX) {
+        ob2_set_error("ob2_sample_from_base_host: n = %lld outside [0, %d]; use ob2_sample_from_base for bulk draws",
+                      (long long)n, (int)OB2_HOST_SAMPLE_MAX);
+        return OB2_ETOOBIG;
+    }
+    if (n == 0) return OB2_OK;
+    const int64_t n_stride = (n + 31) / 32 * 32;
+    int rc = ob2_check_batch(space, n, n_stride);
+    if (rc != OB2_OK) return rc;
+    std::lock_guard<std::mutex> lock(*space->stage_mutex);
+    rc = ensure_stage(space);
+    if (rc != OB2_OK) return rc;
+    if (space->d_base == nullptr) {
+        const size_t bytes = (size_t)space->n_slots * sizeof(double) * OB2_HOST_SAMPLE_MAX;
+        OB2_CUDA(cudaMalloc(&space->d_base, bytes));
+        rc = ob2_check_cuda(cudaMallocHost(&space->h_base, bytes), "cudaMallocHost(base)");
+        if (rc != OB2_OK) {
+            cudaFree(space->d_base);
+            space->d_base = nullptr;
+            return rc;
+        }
+    }
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    char *d = static_cast<char *>(space->d_stage), *h = static_cast<char *>(space->h_stage);
+    const size_t used = (size_t)space->row_bytes * n_stride;
+    const size_t base_bytes = (size_t)space->n_slots * sizeof(double) * n_stride;
+    memcpy(space->h_base, host_base, base_bytes);
+    OB2_CUDA(cudaMemcpyAsync(space->d_base, space->h_base, base_bytes, cudaMemcpyHostToDevice, st));
+    rc = ob2_sample_from_base(space, n, n_stride, static_cast<const double *>(space->d_base), flags, d,
+                              reinterpret_cast<uint8_t *>(d + used), nullptr, st);
+    if (rc != OB2_OK) return rc;
+    OB2_CUDA(cudaMemcpyAsync(h, d, used + (size_t)n_stride, cudaMemcpyDeviceToHost, st));  // the verdicts sit behind the columns
+    OB2_CUDA(cudaStreamSynchronize(st));
+    memcpy(host_cols, h, used);
+    memcpy(host_ok, h + used, (size_t)n);
+    return OB2_OK;
+}
+
 extern "C" int ob2_contains(const ob2_space *space, int64_t n, int64_t n_stride, const void *cols,
                             int32_t int_as_f64, uint8_t *mask, void *stream) {
     int rc = ob2_check_batch(space, n, n_stride);

@@ -235,6 +235,7 @@ extern "C" int ob2_space_create(const ob2_slot_desc *slots, int32_t n_slots, con
     sp->n_runs = 0;
     sp->philox_rounds = 10;
     sp->d_stage = sp->h_stage = nullptr;
+    sp->d_base = sp->h_base = nullptr;
     sp->stage_mutex = new (std::nothrow) std::mutex();
     // the device copy of the table carries the wire layout in `reserved`: (offset units << 4) | element bytes
     ob2_slot_desc *staged = new (std::nothrow) ob2_slot_desc[n_slots];
@@ -312,6 +313,8 @@ extern "C" void ob2_space_destroy(ob2_space *sp) {
     delete[] sp->h_runs;
     if (sp->d_stage) cudaFree(sp->d_stage);
     if (sp->h_stage) cudaFreeHost(sp->h_stage);
+    if (sp->d_base) cudaFree(sp->d_base);
+    if (sp->h_base) cudaFreeHost(sp->h_base);
     delete sp->stage_mutex;
     delete[] sp->h_slots;
     delete[] sp->wire_units;

@@ -400,6 +400,25 @@ class CompiledSpace(object):
             return cols, self._host_failed, keep
         return cols, self._host_failed
 
+    def sample_from_base_host(self, base, n, normal_variates=True):
+        """``base``: float64 numpy [n_slots][n] of the caller's random numbers (n <= ``_lib.HOST_SAMPLE_MAX``)
+        -> (list of numpy columns, bool ok[n]) by ONE library call (``ob2_sample_from_base_host``)."""
+        self._require_samplable()
+        n = int(n)
+        ns = round_up(max(n, 1))
+        block = np.full((self.n_slots, ns), 0.5)
+        block[:, :n] = base
+        blk = np.empty(self.row_bytes * ns, dtype=np.uint8)
+        ok = np.empty(max(n, 1), dtype=np.uint8)
+        _lib.check(self.lib.ob2_sample_from_base_host(
+            self.handle, n, block.ctypes.data, _lib.BASE_NORMAL_VARIATE if normal_variates else 0,
+            blk.ctypes.data, ok.ctypes.data, self._stream()))
+        cols = []
+        for units, dt, count in self._col_runs:
+            e = _ELEM[dt]
+            cols.extend(blk[units * ns:(units + e * count) * ns].view(dt).reshape(count, ns)[:, :n])
+        return cols, ok[:n].astype(bool)
+
     def contains_host(self, cols, n, int_as_f64=True):
         """``point in space`` for n <= ``_lib.HOST_SAMPLE_MAX`` host rows given as
         columns (Integer columns as float64 when ``int_as_f64``), by ONE library

@@ -57,6 +57,8 @@ def _ask(rng, kind, count):
 
 def _evaluate(compiled, base, n):
     """base: float64 [n_slots][n] -> (host columns, ok[n]) through the kernel."""
+    if n <= _lib.HOST_SAMPLE_MAX:                   # numbers in, kernel, columns + verdicts out: one library call
+        return compiled.sample_from_base_host(base, n)
     ns = round_up(max(n, 1))
     block = numpy.full((compiled.n_slots, ns), 0.5)
     block[:, :n] = base
