@@ -1080,6 +1080,9 @@ def run_b200(args):
 
     if e2e and e2e.get("d2h_ceiling"):
         e2e["frac_of_d2h_ceiling"] = world * e2e["d2h_GBps_per_gpu"] / e2e["d2h_ceiling"]["aggregate_GBps"]
+        if e2e["frac_of_d2h_ceiling"] > 1.05:       # the ceiling was probed on ANOTHER box of the pool
+            e2e["d2h_ceiling"]["note"] = ("this box moves more than the probed one (PCIe topology differs between "
+                                          "the pool's boxes): re-run benchmarks/pcie_probe.py here for its own ceiling")
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
