@@ -40,10 +40,13 @@ def load(name):
     return out
 
 
-def product_space(dims):
-    """The same fixture spec as an orion_b200 Space (imports the product lazily)."""
+def product_space(dims, module=None):
+    """The same fixture spec as an orion_b200 Space (imports the product lazily) -- or, given the
+    reference's ``orion.algo.space`` as ``module``, as a reference Space."""
     from collections import OrderedDict
-    from orion_b200.space import Categorical, Integer, Real, Space
+    if module is None:
+        from orion_b200 import space as module
+    Categorical, Integer, Real, Space = module.Categorical, module.Integer, module.Real, module.Space
     space = Space()
     for d in dims:
         kw = dict(d.get('kwargs', {}))

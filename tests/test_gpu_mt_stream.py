@@ -13,7 +13,7 @@ import pytest
 import torch
 
 from oracle import ref_harness
-from tests.test_mt_stream import CASES, make, same_state, spaces
+from tests.test_mt_stream import CASES, make, random_dims, same_state, spaces
 
 pytestmark = [pytest.mark.gpu,
               pytest.mark.skipif(not ref_harness.available(), reason="no reference package staged (oracle/make_ref.py)")]
@@ -122,6 +122,35 @@ def test_space_sample_is_the_reference_s(which, n):
                 except ValueError as exc:
                     return str(exc)
             assert outcome() == outcome()
+
+
+@pytest.mark.parametrize('case', range(20))
+def test_random_spaces_sample_the_reference_s_points(case):
+    """Generated spaces (tests/test_oracle_vs_reference_random.py::_random_dims) through the live reference
+    and through the kernels; reciprocal values to 2 ulp (an Integer over one may then floor differently:
+    those cases compare to +-1), everything else exact."""
+    from tests import golden_util as gu
+    dims_json = random_dims(case)
+    ref_space, space = gu.product_space(dims_json, ref_classes()), gu.product_space(dims_json)
+    for n in (1, 12):
+        ref_rng, rng = np.random.RandomState(case), np.random.RandomState(case)
+        try:
+            expect = ref_space.sample(n, ref_rng)
+        except ValueError as exc:
+            with pytest.raises(ValueError) as mine:
+                space.sample(n, rng)
+            assert str(mine.value) == str(exc)
+            assert same_state(rng, ref_rng)
+            continue
+        got = space.sample(n, rng)
+        assert len(got) == len(expect) == n
+        for grow, erow in zip(got, expect):
+            for d, g, e in zip(dims_json, grow, erow):
+                if d.get('prior') == 'reciprocal' and d['kind'] == 'integer':
+                    assert np.all(np.abs(np.asarray(g) - np.asarray(e)) <= 1)
+                else:
+                    assert equal_values(g, e, exact=d.get('prior') != 'reciprocal'), (case, d)
+        assert same_state(rng, ref_rng)
 
 
 def test_transformed_space_sample_is_transform_of_the_reference_s_points():

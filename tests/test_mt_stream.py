@@ -242,6 +242,38 @@ def test_space_sample_matches_the_reference(which, n):
             assert same_state(rng, ref_rng)
 
 
+def random_dims(case):
+    from tests.test_oracle_vs_reference_random import _random_dims
+    return _random_dims(np.random.RandomState(3000 + case))
+
+
+@pytest.mark.parametrize('case', range(20))
+def test_random_spaces_match_the_reference(case):
+    """Generated spaces (1-6 dimensions of every kind, shapes, skewed probabilities, user bounds around
+    +-2.5 sigma) through the reference and through this module: same points, same final state."""
+    from tests import golden_util as gu
+    dims_json = random_dims(case)
+    ref_space, space = gu.product_space(dims_json, ref_classes()), gu.product_space(dims_json)
+    dims = list(space.values())
+    compiled = HostCompiled(dims)
+    for n in (1, 12):
+        ref_rng, rng = np.random.RandomState(case), np.random.RandomState(case)
+        try:
+            expect = ref_space.sample(n, ref_rng)
+        except ValueError as exc:
+            with pytest.raises(ValueError) as mine:
+                mt_stream.space_columns(dims, compiled, lambda d: HostCompiled([d]), n, rng)
+            assert str(mine.value) == str(exc)
+            assert same_state(rng, ref_rng)
+            continue
+        cols = mt_stream.space_columns(dims, compiled, lambda d: HostCompiled([d]), n, rng)
+        got = mirror.Space.rows_from_columns(space, cols, n)
+        for grow, erow in zip(got, expect):
+            for g, e in zip(grow, erow):
+                assert np.array_equal(np.asarray(g, dtype=object), np.asarray(e, dtype=object))
+        assert same_state(rng, ref_rng)
+
+
 def test_reference_known_answers_on_this_path():
     """The reference's own golden values (tests/unittests/algo/test_space.py:195-198, 246-250, 266-271)."""
     def draw(dim):
