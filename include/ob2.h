@@ -68,7 +68,22 @@ enum { OB2_DIST_UNIFORM = 0, OB2_DIST_RECIPROCAL = 1, OB2_DIST_NORM = 2, OB2_DIS
        OB2_DIST_CAUCHY = 20, OB2_DIST_CHI2 = 21, OB2_DIST_T = 22, OB2_DIST_TRUNCNORM = 23,
        /* GEOM: p0 = p, p1 = log1p(-p), scipy's _ppf verbatim.  BINOM: p0 = n, p1 = p, hk[3] = bits of
         * (1 - p)^n (must not underflow); the smallest k with cdf(k) >= u by summing the pmf. */
-       OB2_DIST_GEOM = 24, OB2_DIST_BINOM = 25, OB2_DIST_LAST = 25 };
+       OB2_DIST_GEOM = 24, OB2_DIST_BINOM = 25,
+       /* more closed forms, each scipy's own _ppf formula (scipy/stats/_continuous_distns.py); p0 / p1 = the
+        * shape parameters in scipy's order unless said otherwise.  The gamma-based ones carry p1 = lgamma(p0):
+        * CHI (also maxwell = chi(3)): p0 = df / 2, sqrt(2 gammaincinv);  INVGAMMA: p0 = a, 1 / gammainccinv;
+        * NAKAGAMI: p0 = nu, sqrt(gammaincinv / nu);  DGAMMA: p0 = a, signed;  GENNORM: p0 = 1 / beta, p1 =
+        * lgamma(1 / beta), hk[3] = bits of beta.  RDIST (also semicircular = rdist(3)): p0 = c / 2, hk[3] = bits of
+        * lbeta(c / 2, c / 2), 2 betaincinv - 1.  FISK = BURR with d = 1. */
+       OB2_DIST_GUMBEL_L = 26, OB2_DIST_GENPARETO = 27, OB2_DIST_LOMAX = 28, OB2_DIST_BURR = 29, OB2_DIST_BURR12 = 30,
+       OB2_DIST_INVWEIBULL = 31, OB2_DIST_TRUNCEXPON = 32, OB2_DIST_BRADFORD = 33, OB2_DIST_ARCSINE = 34,
+       OB2_DIST_TRIANG = 35, OB2_DIST_LOGLAPLACE = 36, OB2_DIST_EXPONPOW = 37, OB2_DIST_GOMPERTZ = 38,
+       OB2_DIST_GENLOGISTIC = 39, OB2_DIST_HYPSECANT = 40, OB2_DIST_HALFCAUCHY = 41, OB2_DIST_HALFLOGISTIC = 42,
+       OB2_DIST_CHI = 43, OB2_DIST_INVGAMMA = 44, OB2_DIST_NAKAGAMI = 45, OB2_DIST_GIBRAT = 46,
+       OB2_DIST_GENEXTREME = 47, OB2_DIST_KAPPA3 = 48, OB2_DIST_DWEIBULL = 49, OB2_DIST_ANGLIT = 50,
+       OB2_DIST_EXPONWEIB = 51, OB2_DIST_MIELKE = 52, OB2_DIST_GENHALFLOGISTIC = 53, OB2_DIST_TUKEYLAMBDA = 54,
+       OB2_DIST_LEVY = 55, OB2_DIST_LEVY_L = 56, OB2_DIST_WEIBULL_MAX = 57, OB2_DIST_RDIST = 58, OB2_DIST_DGAMMA = 59,
+       OB2_DIST_GENNORM = 60, OB2_DIST_MOYAL = 61, OB2_DIST_WRAPCAUCHY = 62, OB2_DIST_LAST = 62 };
 
 /* per-slot transformer (build_required_space table) */
 enum {

@@ -236,7 +236,13 @@ CLOSED_FORM_PRIORS = ('expon', 'lognorm', 'logistic', 'laplace', 'gumbel_r', 'we
                       # special.gammaincinv / betaincinv
                       'gamma', 'erlang', 'beta',
                       'cauchy', 'chi2', 't', 'truncnorm',
-                      'geom', 'binom')
+                      'geom', 'binom',
+                      # more closed forms (each scipy's own _ppf)
+                      'gumbel_l', 'genpareto', 'lomax', 'burr', 'fisk', 'burr12', 'invweibull', 'truncexpon', 'bradford',
+                      'arcsine', 'triang', 'loglaplace', 'exponpow', 'gompertz', 'genlogistic', 'hypsecant',
+                      'halfcauchy', 'halflogistic', 'chi', 'maxwell', 'invgamma', 'nakagami', 'gibrat', 'genextreme',
+                      'kappa3', 'dweibull', 'anglit', 'exponweib', 'mielke', 'genhalflogistic', 'tukeylambda', 'levy',
+                      'levy_l', 'weibull_max', 'rdist', 'semicircular', 'dgamma', 'gennorm', 'moyal', 'wrapcauchy')
 
 
 def _draw(spec: DimSpec, u: np.ndarray) -> np.ndarray:

@@ -351,17 +351,17 @@ __device__ __forceinline__ void gamma_pq(double a, double x, double lga, double 
     }
 }
 
-static __device__ __noinline__ double gamma_ppf(double a, double lga, double p) {
+// x with P(a, x) = p and Q(a, x) = q, p + q = 1: the caller hands over both so that the small one is exact
+static __device__ __noinline__ double gamma_inv(double a, double lga, double p, double q) {
     if (p <= 0.0) return 0.0;
-    const double q = 1.0 - p;
     double x;
     if (a > 1.0) {  // Wilson-Hilferty
-        const double t = normcdfinv(p), s = 1.0 - 1.0 / (9.0 * a) + t / (3.0 * sqrt(a));
+        const double t = p <= 0.5 ? normcdfinv(p) : -normcdfinv(q), s = 1.0 - 1.0 / (9.0 * a) + t / (3.0 * sqrt(a));
         x = a * s * s * s;
         if (!(x > 0.0)) x = exp((log(p) + lga + log(a)) / a);  // far lower tail: P ~ x^a / Gamma(a + 1)
     } else {
         const double t = 1.0 - a * (0.253 + 0.12 * a);
-        x = p < t ? pow(p / t, 1.0 / a) : 1.0 - log1p(-(p - t) / (1.0 - t));
+        x = p < t ? pow(p / t, 1.0 / a) : 1.0 - log(q / (1.0 - t));
     }
     for (int it = 0; it < 40; ++it) {
         if (!(x > 0.0)) return 0.0;
@@ -378,6 +378,9 @@ static __device__ __noinline__ double gamma_ppf(double a, double lga, double p) 
     }
     return x;
 }
+__device__ __forceinline__ double gamma_ppf(double a, double lga, double p) { return gamma_inv(a, lga, p, 1.0 - p); }
+// special.gammainccinv: the upper tail given exactly
+__device__ __forceinline__ double gamma_isf(double a, double lga, double q) { return gamma_inv(a, lga, 1.0 - q, q); }
 
 // continued fraction of the incomplete beta function (modified Lentz)
 __device__ __forceinline__ double beta_cf(double a, double b, double x) {
@@ -531,6 +534,103 @@ static __device__ __noinline__ double draw_extended(int dist, double p0, double 
                 cdf += pmf;
             }
             return k;
+        }
+        // ---- more closed forms: scipy's _ppf of the same name, with expm1 / log1p where scipy's own
+        // helper (powm1, boxcox1p) avoids a cancellation
+        case OB2_DIST_GUMBEL_L:
+            return log(-log1p(-u));
+        case OB2_DIST_GENPARETO:  // -boxcox1p(-u, -c)
+            return p0 != 0.0 ? expm1(-p0 * log1p(-u)) / p0 : -log1p(-u);
+        case OB2_DIST_LOMAX:
+            return expm1(-log1p(-u) / p0);
+        case OB2_DIST_BURR:  // (u^(-1/d) - 1)^(-1/c)
+            return pow(expm1(-log(u) / p1), -1.0 / p0);
+        case OB2_DIST_BURR12:
+            return pow(expm1(-1.0 / p1 * log1p(-u)), 1.0 / p0);
+        case OB2_DIST_INVWEIBULL:
+            return pow(-log(u), -1.0 / p0);
+        case OB2_DIST_TRUNCEXPON:
+            return -log1p(u * expm1(-p0));
+        case OB2_DIST_BRADFORD:
+            return expm1(u * log1p(p0)) / p0;
+        case OB2_DIST_ARCSINE: {
+            const double s = sinpi(0.5 * u);
+            return s * s;
+        }
+        case OB2_DIST_TRIANG:
+            return u < p0 ? sqrt(p0 * u) : 1.0 - sqrt((1.0 - p0) * (1.0 - u));
+        case OB2_DIST_LOGLAPLACE:
+            return u < 0.5 ? pow(2.0 * u, 1.0 / p0) : pow(2.0 * (1.0 - u), -1.0 / p0);
+        case OB2_DIST_EXPONPOW:
+            return pow(log1p(-log1p(-u)), 1.0 / p0);
+        case OB2_DIST_GOMPERTZ:
+            return log1p(-1.0 / p0 * log1p(-u));
+        case OB2_DIST_GENLOGISTIC:  // -log(powm1(u, -1/c))
+            return -log(expm1(-log(u) / p0));
+        case OB2_DIST_HYPSECANT:
+            return log(sinpi(0.5 * u) / cospi(0.5 * u));
+        case OB2_DIST_HALFCAUCHY:
+            return sinpi(0.5 * u) / cospi(0.5 * u);
+        case OB2_DIST_HALFLOGISTIC:
+            return 2.0 * atanh(u);
+        case OB2_DIST_CHI:  // p0 = df / 2
+            return sqrt(2.0 * gamma_ppf(p0, p1, u));
+        case OB2_DIST_INVGAMMA:  // 1 / gammainccinv(a, u)
+            return 1.0 / gamma_isf(p0, p1, u);
+        case OB2_DIST_NAKAGAMI:
+            return sqrt(gamma_ppf(p0, p1, u) / p0);
+        case OB2_DIST_GIBRAT:
+            return exp(normcdfinv(u));
+        case OB2_DIST_GENEXTREME: {
+            const double x = -log(-log(u));
+            return p0 != 0.0 ? -expm1(-p0 * x) / p0 : x;
+        }
+        case OB2_DIST_KAPPA3:  // (a / (u^-a - 1))^(1/a)
+            return pow(p0 / expm1(-p0 * log(u)), 1.0 / p0);
+        case OB2_DIST_DWEIBULL: {
+            const double fac = pow(-log(2.0 * (u <= 0.5 ? u : 1.0 - u)), 1.0 / p0);
+            return u > 0.5 ? fac : -fac;
+        }
+        case OB2_DIST_ANGLIT:
+            return asin(sqrt(u)) - 0.78539816339744830962;
+        case OB2_DIST_EXPONWEIB:  // (-log1p(-u^(1/a)))^(1/c)
+            return pow(-log1p(-pow(u, 1.0 / p0)), 1.0 / p1);
+        case OB2_DIST_MIELKE: {  // k, s
+            const double qsk = pow(u, p1 / p0);
+            return pow(qsk / (1.0 - qsk), 1.0 / p1);
+        }
+        case OB2_DIST_GENHALFLOGISTIC:
+            return 1.0 / p0 * (1.0 - pow((1.0 - u) / (1.0 + u), p0));
+        case OB2_DIST_TUKEYLAMBDA:  // boxcox(u, lam) - boxcox1p(-u, lam)
+            return p0 != 0.0 ? (expm1(p0 * log(u)) - expm1(p0 * log1p(-u))) / p0 : log(u) - log1p(-u);
+        case OB2_DIST_LEVY: {  // 1 / norm.isf(u / 2)^2
+            const double v = normcdfinv(0.5 * u);
+            return 1.0 / (v * v);
+        }
+        case OB2_DIST_LEVY_L: {
+            const double v = normcdfinv(0.5 * (u + 1.0));
+            return -1.0 / (v * v);
+        }
+        case OB2_DIST_WEIBULL_MAX:
+            return -pow(-log(u), 1.0 / p0);
+        case OB2_DIST_RDIST:  // p0 = c / 2, p2 = lbeta(c / 2, c / 2)
+            return 2.0 * beta_ppf(p0, p0, p2, u) - 1.0;
+        case OB2_DIST_DGAMMA:
+            return u > 0.5 ? gamma_ppf(p0, p1, 2.0 * u - 1.0) : -gamma_isf(p0, p1, 2.0 * u);
+        case OB2_DIST_GENNORM: {  // p0 = 1 / beta, p2 = beta: c gammainccinv(1/beta, (1 + c) - 2 c u)^(1/beta), c = sign(u - 1/2)
+            if (u == 0.5) return 0.0;
+            const double upper = u > 0.5 ? 2.0 * (1.0 - u) : 2.0 * u;
+            const double r = pow(gamma_isf(p0, p1, upper), p0);
+            return u > 0.5 ? r : -r;
+        }
+        case OB2_DIST_MOYAL: {
+            const double e = erfcinv(u);
+            return -log(2.0 * e * e);
+        }
+        case OB2_DIST_WRAPCAUCHY: {  // p0 = c
+            const double val = (1.0 - p0) / (1.0 + p0);
+            return u < 0.5 ? 2.0 * atan(val * (sinpi(u) / cospi(u)))
+                           : 6.28318530717958647692 - 2.0 * atan(val * (sinpi(1.0 - u) / cospi(1.0 - u)));
         }
         default: {  // OB2_DIST_POISSON, p0 = mu, p1 = exp(-mu): smallest k with cdf(k) >= u
             double k = 0.0, pmf = p1, cdf = p1;

@@ -63,6 +63,22 @@ _CLOSED_FORM = {
 }
 
 
+# more closed forms (ob2.h OB2_DIST_GUMBEL_L..): name -> (dist code, number of shape parameters); p0 / p1 carry them as given
+_CLOSED_FORM_2 = {
+    'gumbel_l': (26, 0), 'genpareto': (27, 1), 'lomax': (28, 1), 'burr': (29, 2), 'burr12': (30, 2), 'invweibull': (31, 1),
+    'truncexpon': (32, 1), 'bradford': (33, 1), 'arcsine': (34, 0), 'triang': (35, 1), 'loglaplace': (36, 1),
+    'exponpow': (37, 1), 'gompertz': (38, 1), 'genlogistic': (39, 1), 'hypsecant': (40, 0), 'halfcauchy': (41, 0),
+    'halflogistic': (42, 0), 'gibrat': (46, 0), 'genextreme': (47, 1), 'kappa3': (48, 1), 'dweibull': (49, 1),
+    'anglit': (50, 0), 'exponweib': (51, 2), 'mielke': (52, 2), 'genhalflogistic': (53, 1), 'tukeylambda': (54, 1),
+    'levy': (55, 0), 'levy_l': (56, 0), 'weibull_max': (57, 1), 'moyal': (61, 0), 'wrapcauchy': (62, 1),
+}
+# ... and those that go through the incomplete gamma inverse: name -> (dist code, a as a function of the shape parameters)
+_GAMMA_BASED = {
+    'chi': (43, lambda df: 0.5 * df), 'maxwell': (43, lambda: 1.5), 'invgamma': (44, lambda a: a),
+    'nakagami': (45, lambda nu: nu), 'dgamma': (59, lambda a: a), 'gennorm': (60, lambda beta: 1.0 / beta),
+}
+
+
 def _prior_params(dim):
     """(dist code, p0, p1, loc, scale) of a Real/Integer dimension."""
     name = dim._prior_name
@@ -90,6 +106,20 @@ def _prior_params(dim):
         p0 = float(args[0]) if n_shape else 0.0
         p1 = reciprocal_sign / p0 if (n_shape and reciprocal_sign) else 0.0
         return code, p0, p1, loc, scale
+    if name in _CLOSED_FORM_2 and len(args) == _CLOSED_FORM_2[name][1]:
+        shapes = [float(a) for a in args] + [0.0, 0.0]
+        return _CLOSED_FORM_2[name][0], shapes[0], shapes[1], loc, scale
+    if name == 'fisk' and len(args) == 1:               # burr(c, 1)
+        return 29, float(args[0]), 1.0, loc, scale
+    if name in _GAMMA_BASED:
+        from scipy.special import gammaln
+        code, shape_of = _GAMMA_BASED[name]
+        a = float(shape_of(*[float(x) for x in args]))
+        return code, a, float(gammaln(a)), loc, scale, (float(args[0]) if name == 'gennorm' else 0.0)
+    if name in ('rdist', 'semicircular') and len(args) == (1 if name == 'rdist' else 0):
+        from scipy.special import betaln
+        half = 0.5 * (float(args[0]) if name == 'rdist' else 3.0)
+        return 58, half, 0.0, loc, scale, float(betaln(half, half))
     if name == 'alpha' and len(args) == 1:
         from scipy.special import ndtr
         a = float(args[0])
