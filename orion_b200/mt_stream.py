@@ -80,9 +80,25 @@ def sample_space(dims, compiled, n, rng):
     kinds = stream_kinds(compiled)
     state = rng.get_state()
     base = numpy.full((compiled.n_slots, n), 0.5)
-    for first, width, kind in zip(compiled.dim_first, compiled.dim_widths, kinds):
-        if kind != NOTHING:
-            base[first:first + width] = _ask(rng, kind, n * width).reshape(n, width).T
+    firsts, widths = compiled.dim_first, compiled.dim_widths
+    d = 0
+    while d < len(kinds):
+        # consecutive dimensions fed by the same RandomState method: ONE request for all their numbers
+        # (the stream is dimension-major, so this is the sequence the separate requests would return)
+        end = d + 1
+        while end < len(kinds) and kinds[end] == kinds[d]:
+            end += 1
+        if kinds[d] != NOTHING:
+            slots = sum(widths[d:end])
+            numbers = _ask(rng, kinds[d], n * slots)
+            if slots == end - d:                    # all scalar: dimension j's n numbers are row j
+                base[firsts[d]:firsts[d] + slots] = numbers.reshape(slots, n)
+            else:
+                pos = 0
+                for first, width in zip(firsts[d:end], widths[d:end]):
+                    base[first:first + width] = numbers[pos:pos + n * width].reshape(n, width).T
+                    pos += n * width
+        d = end
     cols, ok = _evaluate(compiled, base, n)
     rejecting = [d.type in ('real', 'integer') for d in dims]
     if ok.all() or not any(rejecting):
