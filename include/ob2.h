@@ -83,7 +83,15 @@ enum { OB2_DIST_UNIFORM = 0, OB2_DIST_RECIPROCAL = 1, OB2_DIST_NORM = 2, OB2_DIS
        OB2_DIST_GENEXTREME = 47, OB2_DIST_KAPPA3 = 48, OB2_DIST_DWEIBULL = 49, OB2_DIST_ANGLIT = 50,
        OB2_DIST_EXPONWEIB = 51, OB2_DIST_MIELKE = 52, OB2_DIST_GENHALFLOGISTIC = 53, OB2_DIST_TUKEYLAMBDA = 54,
        OB2_DIST_LEVY = 55, OB2_DIST_LEVY_L = 56, OB2_DIST_WEIBULL_MAX = 57, OB2_DIST_RDIST = 58, OB2_DIST_DGAMMA = 59,
-       OB2_DIST_GENNORM = 60, OB2_DIST_MOYAL = 61, OB2_DIST_WRAPCAUCHY = 62, OB2_DIST_LAST = 62 };
+       OB2_DIST_GENNORM = 60, OB2_DIST_MOYAL = 61, OB2_DIST_WRAPCAUCHY = 62,
+       /* F: p0 = dfn, p1 = dfd, hk[3] = bits of lbeta(dfn / 2, dfd / 2); through the beta inverse, from whichever
+        * tail is the small one.  LOGGAMMA: p0 = c, p1 = lgamma(c), hk[3] = bits of lgamma(c + 1) (scipy's
+        * one-term form where gammaincinv underflows).  NBINOM: p0 = n, p1 = p, hk[3] = bits of p^n (must not
+        * underflow); HYPERGEOM: p0 = M, p1 = n, hk[3] = bits of N: the smallest k with cdf(k) >= u by summing
+        * the pmf from the lower end of the support.  VONMISES: p0 = kappa (< 50), p1 = 1 / (2 pi i0e(kappa));
+        * safeguarded Newton steps on the cdf series scipy itself sums (Hill's algorithm 518). */
+       OB2_DIST_F = 63, OB2_DIST_LOGGAMMA = 64, OB2_DIST_NBINOM = 65, OB2_DIST_HYPERGEOM = 66, OB2_DIST_VONMISES = 67,
+       OB2_DIST_LAST = 67 };
 
 /* per-slot transformer (build_required_space table) */
 enum {

@@ -475,6 +475,38 @@ static __device__ __noinline__ double t_ppf(double df, double lbeta, double p) {
     return lower ? -t : t;
 }
 
+// von Mises cdf on [-pi, pi] by the backward series scipy sums (scipy/stats/_stats.pyx von_mises_cdf_series,
+// Hill 1977), and its inverse by Newton steps kept inside a shrinking bracket.
+__device__ __forceinline__ double vonmises_cdf(double k, double x, int p) {
+    double s, c, sn, cn;
+    sincos(x, &s, &c);
+    sincos((double)p * x, &sn, &cn);
+    double R = 0.0, V = 0.0;
+    for (int n = p - 1; n > 0; --n) {
+        const double sn2 = sn * c - cn * s;
+        cn = cn * c + sn * s;
+        sn = sn2;
+        R = 1.0 / (2.0 * n / k + R);
+        V = R * (sn / n + V);
+    }
+    return 0.5 + x / 6.28318530717958647692 + V / 3.14159265358979323846;
+}
+static __device__ __noinline__ double vonmises_ppf(double k, double inv_norm, double u) {
+    const int p = (int)(1.0 + 28.0 + 0.5 * k - 100.0 / (k + 5.0));
+    double lo = -3.14159265358979323846, hi = 3.14159265358979323846;
+    double x = fmin(fmax(normcdfinv(u) * rsqrt(fmax(k, 0.25)), 0.9 * lo), 0.9 * hi);
+    for (int it = 0; it < 80; ++it) {
+        const double err = vonmises_cdf(k, x, p) - u;
+        if (err > 0.0) hi = x; else lo = x;
+        const double pdf = exp(k * (cos(x) - 1.0)) * inv_norm;
+        double nx = x - err / pdf;
+        if (!(nx > lo && nx < hi)) nx = 0.5 * (lo + hi);  // Newton left the bracket: bisect
+        if (fabs(nx - x) <= 1e-15 * fmax(1.0, fabs(x)) || hi - lo <= 1e-15) return nx;
+        x = nx;
+    }
+    return x;
+}
+
 // The extra priors, out of line and out of the common kernel (EXT = false
 // never references it).
 static __device__ __noinline__ double draw_extended(int dist, double p0, double p1, double p2, double u) {
@@ -632,6 +664,45 @@ static __device__ __noinline__ double draw_extended(int dist, double p0, double 
             return u < 0.5 ? 2.0 * atan(val * (sinpi(u) / cospi(u)))
                            : 6.28318530717958647692 - 2.0 * atan(val * (sinpi(1.0 - u) / cospi(1.0 - u)));
         }
+        case OB2_DIST_F: {  // p0 = dfn, p1 = dfd, p2 = lbeta(dfn / 2, dfd / 2)
+            if (u <= 0.5) {
+                const double b = beta_ppf(0.5 * p0, 0.5 * p1, p2, u);
+                return p1 * b / (p0 * (1.0 - b));
+            }
+            const double bc = beta_ppf(0.5 * p1, 0.5 * p0, p2, 1.0 - u);  // 1 - b, from the small tail
+            return p1 * (1.0 - bc) / (p0 * bc);
+        }
+        case OB2_DIST_LOGGAMMA: {  // p0 = c, p1 = lgamma(c), p2 = lgamma(c + 1)
+            const double g = gamma_ppf(p0, p1, u);
+            return g < 2.2250738585072014e-308 ? (log(u) + p2) / p0 : log(g);
+        }
+        case OB2_DIST_NBINOM: {  // p0 = n, p1 = p, p2 = p^n
+            double k = 0.0, pmf = p2, cdf = p2;
+            const double fail = 1.0 - p1, mean = p0 * fail / p1;
+            const double k_max = mean + 40.0 * sqrt(mean / p1) + 60.0 / p1;
+            while (cdf < u && k < k_max) {
+                pmf *= (k + p0) / (k + 1.0) * fail;
+                k += 1.0;
+                cdf += pmf;
+            }
+            return k;
+        }
+        case OB2_DIST_HYPERGEOM: {  // p0 = M, p1 = n, p2 = N: k successes in N draws, n of the M objects being successes
+            const double lo = fmax(0.0, p2 - (p0 - p1)), hi = fmin(p1, p2);
+            double k = lo;
+            double pmf = exp(lgamma(p1 + 1.0) - lgamma(k + 1.0) - lgamma(p1 - k + 1.0) + lgamma(p0 - p1 + 1.0) -
+                             lgamma(p2 - k + 1.0) - lgamma(p0 - p1 - p2 + k + 1.0) - lgamma(p0 + 1.0) + lgamma(p2 + 1.0) +
+                             lgamma(p0 - p2 + 1.0));
+            double cdf = pmf;
+            while (cdf < u && k < hi) {
+                pmf *= (p1 - k) * (p2 - k) / ((k + 1.0) * (p0 - p1 - p2 + k + 1.0));
+                k += 1.0;
+                cdf += pmf;
+            }
+            return k;
+        }
+        case OB2_DIST_VONMISES:  // p0 = kappa, p1 = 1 / (2 pi i0e(kappa))
+            return vonmises_ppf(p0, p1, u);
         default: {  // OB2_DIST_POISSON, p0 = mu, p1 = exp(-mu): smallest k with cdf(k) >= u
             double k = 0.0, pmf = p1, cdf = p1;
             const double k_max = p0 + 40.0 * sqrt(p0) + 60.0;  // the tail beyond is < 1e-300

@@ -120,6 +120,25 @@ def _prior_params(dim):
         from scipy.special import betaln
         half = 0.5 * (float(args[0]) if name == 'rdist' else 3.0)
         return 58, half, 0.0, loc, scale, float(betaln(half, half))
+    if name == 'f' and len(args) == 2:
+        from scipy.special import betaln
+        dfn, dfd = float(args[0]), float(args[1])
+        return 63, dfn, dfd, loc, scale, float(betaln(0.5 * dfn, 0.5 * dfd))
+    if name == 'loggamma' and len(args) == 1:
+        from scipy.special import gammaln
+        c = float(args[0])
+        return 64, c, float(gammaln(c)), loc, scale, float(gammaln(c + 1.0))
+    if name == 'nbinom' and len(args) == 2:
+        n_succ, p = float(args[0]), float(args[1])
+        pmf0 = float(np.exp(n_succ * np.log(p))) if p > 0 else 0.0
+        if pmf0 > 1e-290:          # (otherwise the pmf recurrence cannot start: bounds-only)
+            return 65, n_succ, p, loc, scale, pmf0
+    if name == 'hypergeom' and len(args) == 3:
+        return 66, float(args[0]), float(args[1]), loc, scale, float(args[2])
+    if name == 'vonmises' and len(args) == 1 and float(args[0]) < 50.0:     # (scipy switches to a normal approximation at 50)
+        from scipy.special import i0e
+        kappa = float(args[0])
+        return 67, kappa, float(1.0 / (2.0 * np.pi * i0e(kappa))), loc, scale
     if name == 'alpha' and len(args) == 1:
         from scipy.special import ndtr
         a = float(args[0])

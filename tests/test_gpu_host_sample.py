@@ -34,7 +34,7 @@ def test_sample_host_limits_and_errors():
         compiled.sample_host(_lib.HOST_SAMPLE_MAX + 1, 1)
     assert 'ob2_sample' in str(exc.value)
     space = Space()
-    space.register(Real('g', 'vonmises', 2.0))              # no device inverse CDF: refuses, never falls back
+    space.register(Real('g', 'ncx2', 3.0, 1.0))            # no device inverse CDF: refuses, never falls back
     with pytest.raises(NotImplementedError):
         space.sample(1)
     improbable = gu.load('improbable')
