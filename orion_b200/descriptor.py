@@ -486,8 +486,9 @@ class CompiledSpace(object):
     def _require_samplable(self):
         if self.unsamplable is not None:
             raise NotImplementedError(
-                "Dimension '{}': prior '{}' has no device inverse CDF yet (supported: uniform, "
-                "reciprocal/loguniform, norm). There is no CPU fallback.".format(*self.unsamplable))
+                "Dimension '{}': prior '{}' has no device inverse CDF yet (supported: uniform, reciprocal / "
+                "loguniform, norm and the sixty-seven further scipy priors INTEGRATION.md lists). "
+                "There is no CPU fallback.".format(*self.unsamplable))
 
     def sample_from_uniform(self, U, n=None, with_fingerprint=False, normal_variates=False):
         """Injected random stream: U is a float64 tensor [n_slots][n_stride] (device) of uniforms -- the
