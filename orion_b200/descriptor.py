@@ -79,6 +79,13 @@ _GAMMA_BASED = {
 }
 
 
+def _draws_by_inverse_cdf(prior):
+    """True when scipy's rvs for this prior is the generic ``_ppf(random_state.uniform(size))``
+    (rv_generic._rvs) rather than a generator of its own."""
+    from scipy.stats._distn_infrastructure import rv_continuous, rv_generic
+    return isinstance(prior, rv_continuous) and getattr(type(prior), '_rvs', None) is rv_generic._rvs
+
+
 def _prior_params(dim):
     """(dist code, p0, p1, loc, scale) of a Real/Integer dimension."""
     name = dim._prior_name
@@ -209,6 +216,7 @@ class CompiledSpace(object):
         self.dim_first = []            # first slot of each dimension
         self.dim_bounds = []
         self.dim_dists = []            # prior code of each dimension (None: categorical)
+        self.dim_generic_rvs = []      # does scipy draw this prior as _ppf(random_state.uniform())? (mt_stream)
         slots = []
         cdf = []
         col_units = t_units = 0
@@ -241,6 +249,7 @@ class CompiledSpace(object):
                 cdf_off = n_cats = 0
             self.dim_bounds.append((low, high))
             self.dim_dists.append(None if kind == 'categorical' else dist)
+            self.dim_generic_rvs.append(kind != 'categorical' and _draws_by_inverse_cdf(dim.prior))
             op = _OPS[requirement][kind]
             if op == _lib.OP_ONEHOT:
                 width, t_elem, t_dt = (1 if n_cats <= 2 else n_cats), 8, 'f8'

@@ -14,6 +14,9 @@ turns them into values (inverse CDF or scale/shift, ``floor``, cdf search, bound
 verdict bytes it returns.  A seeded call therefore returns what the reference returns for the same
 seed and leaves the ``RandomState`` where the reference leaves it: bit for bit for ``uniform``,
 ``norm``, Integer and Categorical dimensions, to the last ulp or two of ``exp`` for ``reciprocal``.
+The further priors scipy draws the same generic way (``fisk``, ``genpareto``, ``lomax``, ``invgamma``
+... : no ``_rvs`` of their own) are fed uniforms too and come out within the device inverse CDF's
+1e-6 (typically 1e-15) of the reference's values.
 
 Priors whose scipy ``_rvs`` uses another numpy generator (``expon`` -> ``standard_exponential``,
 ``gamma``, ``poisson`` ...) and ``numpy.random.Generator`` seeds cannot be reproduced this way;
@@ -39,8 +42,15 @@ _KIND_OF_DIST = {_lib.DIST_UNIFORM: UNIFORM, _lib.DIST_RECIPROCAL: UNIFORM, _lib
 def stream_kinds(compiled):
     """Which RandomState method feeds each dimension of ``compiled``, or None when some prior's
     ``_rvs`` is not a function of ``random_sample`` / ``standard_normal`` numbers."""
-    kinds = [_KIND_OF_DIST.get(d, None) for d in compiled.dim_dists]
-    return None if any(k is None for k in kinds) else kinds
+    kinds = []
+    for dist, by_inverse_cdf in zip(compiled.dim_dists, compiled.dim_generic_rvs):
+        kind = _KIND_OF_DIST.get(dist)
+        if kind is None and dist is not None and dist > _lib.DIST_NONE and by_inverse_cdf:
+            kind = UNIFORM                          # a further prior scipy draws as _ppf(uniform()): the device's _ppf
+        if kind is None:
+            return None
+        kinds.append(kind)
+    return kinds
 
 
 def reproducible(compiled, rng):
