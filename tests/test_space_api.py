@@ -219,10 +219,12 @@ class TestInteger(object):
 
     @gpu
     def test_unsupported_prior_has_no_cpu_fallback(self):
-        dim = Integer('yolo', 'hypergeom', 20, 7, 12)
+        dim = Integer('yolo', 'skellam', 3.0, 2.0)                       # no device inverse CDF
         assert 3 in dim
         with pytest.raises(NotImplementedError):
             dim.sample()
+        draws = Integer('yolo', 'hypergeom', 20, 7, 12).sample(50, seed=1)
+        assert all(int(x) == x and 0 <= x <= 7 for x in draws) and len(set(draws)) > 2
         draws = Integer('yolo', 'poisson', 5).sample(50, seed=1)         # this one has a device inverse CDF
         assert all(int(x) == x and x >= 0 for x in draws) and len(set(draws)) > 3
 
