@@ -13,6 +13,8 @@ _TORCH = {'f8': torch.float64, 'i8': torch.int64, 'i4': torch.int32, 'i2': torch
 _NUMPY = {'f8': np.float64, 'i8': np.int64, 'i4': np.int32, 'i2': np.int16, 'i1': np.int8,
           'u2': np.uint16, 'u1': np.uint8}
 _SIZE = {'f8': 8, 'i8': 8, 'i4': 4, 'i2': 2, 'i1': 1, 'u2': 2, 'u1': 1}
+_PINNED_FROM = 4 << 20          # host round trips of at least this many bytes go through pinned memory ...
+_PINNED_UP_TO = 1 << 30         # ... unless they would pin more than this at once
 
 
 class ColumnBatch(object):
@@ -53,10 +55,23 @@ class ColumnBatch(object):
 
     # ---- host round trips (compatibility path and tests)
     def to_numpy(self, natural=True):
-        """One numpy array per column (a single device->host copy).  A wire
-        batch is widened on the host to the natural dtypes (int64 / int32)
-        unless ``natural`` is False."""
+        """One numpy array per column (a single device->host copy of the first n rows).  A wire
+        batch is widened on the host to the natural dtypes (int64 / int32) unless ``natural`` is
+        False.  Big batches land in ONE pinned block (``ob2_columns_to_host``) that the returned
+        arrays are views of -- no pageable bounce, no second copy on the host."""
         meta = self._meta
+        row_units = max(u + _SIZE[dt] for u, dt in meta)
+        if _PINNED_FROM <= self.n * row_units <= _PINNED_UP_TO:
+            hs = -(-self.n // 32) * 32
+            pinned = torch.empty(row_units * hs, dtype=torch.uint8, pin_memory=True)
+            self.copy_rows_to_host(pinned, self.n, hs)
+            torch.cuda.current_stream(self.buf.device).synchronize()
+            host = pinned.numpy()
+            out = []
+            for j, (units, dt) in enumerate(meta):
+                col = host[units * hs:units * hs + _SIZE[dt] * self.n].view(_NUMPY[dt])
+                out.append(col.astype(_NUMPY[self.compiled.col_meta[j][1]]) if self.wire and natural else col)
+            return out
         sparse = 2 * self.n < self.n_stride         # e.g. the survivors of a compacted batch: rows [0, n) only
         if sparse:
             # gather the used prefix of every column into one dense device block, then ONE copy of
@@ -91,14 +106,18 @@ class ColumnBatch(object):
         batch = compiled.empty_columns(n, transformed)
         meta = batch._meta
         assert len(cols) == len(meta), "expected %d columns, got %d" % (len(meta), len(cols))
-        host = np.zeros(batch.buf.numel(), dtype=np.uint8)
+        big = _PINNED_FROM <= batch.buf.numel() <= _PINNED_UP_TO     # a pinned block and an asynchronous copy; only the tails are zeroed
+        staged = torch.empty(batch.buf.numel(), dtype=torch.uint8, pin_memory=True) if big else None
+        host = staged.numpy() if big else np.zeros(batch.buf.numel(), dtype=np.uint8)
         for (units, dt), col in zip(meta, cols):
             want = np.float64 if (int_as_f64 and dt == 'i8' and not transformed) else _NUMPY[dt]
             arr = np.ascontiguousarray(col, dtype=want)
             assert arr.shape == (n,)
             start = units * batch.n_stride
             host[start:start + arr.nbytes] = arr.view(np.uint8)
-        batch.buf.copy_(torch.from_numpy(host))
+            if big:
+                host[start + arr.nbytes:start + _SIZE[dt] * batch.n_stride] = 0
+        batch.buf.copy_(staged if big else torch.from_numpy(host), non_blocking=big)
         return batch
 
     def compact(self, keep=None, out=None, count=None, scratch=None, wire=False):

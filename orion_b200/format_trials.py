@@ -50,7 +50,13 @@ def trials_to_batch(space, trials):
     ``Producer.update`` -> ``trial_to_tuple`` -> ``observe``,
     ``src/orion/core/worker/producer.py:54-67``)."""
     from .columns import ColumnBatch
-    points = [trial_to_tuple(t, space) for t in trials]
+    dims = list(space.values())
+    names = [d.name for d in dims]
+    points = []
+    for trial in trials:                        # trial_to_tuple for every trial, the space looked up once
+        params = trial['params']
+        assert len(params) == len(dims) and [p['name'] for p in params] == names
+        points.append(tuple(p['value'] for p in params))
     cols, row_ok = space.columns_from_rows(points)
     if not row_ok.all():
         raise ValueError("a trial does not match the shape of the space")
