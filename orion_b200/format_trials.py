@@ -137,11 +137,11 @@ def record_batch_to_columns(space, record_batch):
                     expected = [repr(c) for c in cats]
                 if arr.dictionary.to_pylist() != expected:
                     raise ValueError("dictionary of %r does not match the dimension's categories" % field.name)
-                cols.append(arr.indices.to_numpy(zero_copy_only=False).astype(numpy.int32))
+                cols.append(arr.indices.to_numpy(zero_copy_only=False).astype(numpy.int32, copy=False))
             elif dim.type == 'integer':
-                cols.append(arr.to_numpy(zero_copy_only=False).astype(numpy.int64))
+                cols.append(arr.to_numpy(zero_copy_only=False).astype(numpy.int64, copy=False))
             else:
-                cols.append(arr.to_numpy(zero_copy_only=False).astype(numpy.float64))
+                cols.append(arr.to_numpy(zero_copy_only=False).astype(numpy.float64, copy=False))    # (a view of the arrow buffer)
             f += 1
     if f != record_batch.num_columns:
         raise ValueError("record batch has %d fields, the space %d slots" % (record_batch.num_columns, f))
