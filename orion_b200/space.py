@@ -392,22 +392,26 @@ class Space(OrderedDict):
         if any(d.shape != () for d in dims) or any(len(p) != len(dims) for p in points):
             return None
         cols = []
-        for j, dim in enumerate(dims):
-            vals = [p[j] for p in points]
+        by_dim = list(zip(*points)) if n else [()] * len(dims)     # the transpose, done in C
+        for dim, vals in zip(dims, by_dim):
             if dim.type == 'categorical':
-                if any(isinstance(v, (numpy.ndarray, list, tuple)) for v in vals):
-                    return None
-                cols.append(numpy.fromiter((_index_of(dim, v) for v in vals), dtype=numpy.int32, count=n))
-            else:
-                if any(isinstance(v, (str, bytes)) for v in vals):
-                    return None                 # the general loop raises the reference's TypeError
+                lookup = {}
                 try:
-                    col = numpy.asarray(vals, dtype=numpy.float64)
-                except (TypeError, ValueError):
+                    for i, c in enumerate(dim.categories):
+                        lookup.setdefault(c, i)                      # first match, like tuple.index; 2 == 2.0, '2' != 2
+                    cols.append(numpy.fromiter((lookup.get(v, -1) for v in vals), dtype=numpy.int32, count=n))
+                except TypeError:                                    # an unhashable category or value (list, ndarray)
                     return None
-                if col.shape != (n,):
+            else:
+                # (a str among the values makes numpy pick a string dtype, None an object one: the
+                # general loop then raises the reference's TypeError or rejects the row)
+                try:
+                    probe = numpy.asarray(vals) if n else numpy.empty(0)
+                except ValueError:                                   # ragged: a mis-shaped value among them
                     return None
-                cols.append(col)
+                if probe.dtype.kind not in 'fiub' or probe.shape != (n,):
+                    return None
+                cols.append(probe.astype(numpy.float64, copy=False))
         return cols
 
     def columns_from_rows(self, points):
