@@ -90,6 +90,21 @@ def _index_of(dim, value):
         return -1
 
 
+def _category_lookup(dim):
+    """category -> first index with an equal category (what ``tuple.index`` finds: 2 == 2.0, '2' != 2), cached on
+    the dimension; None when some category is unhashable."""
+    lookup = dim.__dict__.get('_ob2_lookup', False)
+    if lookup is False:
+        lookup = {}
+        try:
+            for i, c in enumerate(dim.categories):
+                lookup.setdefault(c, i)
+        except TypeError:
+            lookup = None
+        dim.__dict__['_ob2_lookup'] = lookup
+    return lookup
+
+
 def _column_values(dim, point):
     """Flatten one value of ``dim`` into per-slot scalars, or None when its shape does not fit
     (``point_.shape != self.shape`` -> False, space.py:162,420).  A string offered to a numeric
@@ -395,12 +410,12 @@ class Space(OrderedDict):
         by_dim = list(zip(*points)) if n else [()] * len(dims)     # the transpose, done in C
         for dim, vals in zip(dims, by_dim):
             if dim.type == 'categorical':
-                lookup = {}
+                lookup = _category_lookup(dim)
+                if lookup is None:
+                    return None
                 try:
-                    for i, c in enumerate(dim.categories):
-                        lookup.setdefault(c, i)                      # first match, like tuple.index; 2 == 2.0, '2' != 2
                     cols.append(numpy.fromiter((lookup.get(v, -1) for v in vals), dtype=numpy.int32, count=n))
-                except TypeError:                                    # an unhashable category or value (list, ndarray)
+                except TypeError:                                    # an unhashable value (list, ndarray)
                     return None
             else:
                 # (a str among the values makes numpy pick a string dtype, None an object one: the
