@@ -652,7 +652,7 @@ def run_b200(args):
     KS = 0 if cfg5_main else min(K, 5)                # steps of the staged-kernels comparison pass
     KR = min(K, 20)                                   # steps of the serial per-kernel pass behind the timed region
     K5 = min(K, 10) if extras else 0                  # steps of the config-5 sub-measurement
-    total_steps = K + KR + KS + K5 + W + args.e2e_steps + 4  # timed + serial + staged + cfg5 + e2e (+ warm-ups)
+    total_steps = K + KR + KS + 3 * K5 + W + args.e2e_steps + 7  # timed + serial + staged + cfg5 (serial, pipelined) + e2e (+ warm-ups)
     space = spaces.mixed64()
     tspace = build_required_space('real', space)
     compiled = space.compiled() if cfg5_main else tspace.compiled()
@@ -936,19 +936,49 @@ def run_b200(args):
         c5_want = expected_keep(idx5)
         c5_exact = all_ranks_true(bool(torch.equal(batch.keep[:n].bool(), c5_want)))
         del c5_want, idx5
-        rate5 = n / (c5_ms * 1e-3)
         sample_ms = sum(e[0].elapsed_time(e[1]) for e in c5) / K5
-        cfg5_info = {"workload": WORKLOADS['cfg5'], "steps": K5, "ms_per_step": c5_ms, "value": world * rate5, "unit": UNIT,
+        # ... and as it is meant to run: batch after batch through the pipeline, the dedup of batch k on a second
+        # stream as a SMALL walking grid (ob2_set_set_dedup_grid) that shares the SMs with the issue-bound
+        # sampler of batch k + 1 (with its one-thread-per-entry grid the two kernels take turns and the times add up)
+        pipe5 = CandidatePipeline(plain, sharded, n, depth=2, fingerprint_in='sample_only')
+        base5p = base5 + 1 + K5
+        KP5 = 2 * K5                                                  # (enough batches to amortise the pipeline's fill and tail)
+        idx5p = [step_index(base5p + s) for s in range(KP5 + 2)]
+        for s in range(2):
+            pipe5.submit(SEED, index=idx5p[s])
+        pipe5.drain()
+        sync_all()
+        p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        p0.record()
+        slot5 = None
+        for s in range(KP5):
+            slot5 = pipe5.submit(SEED, index=idx5p[2 + s])
+        pipe5.drain()
+        p1.record()
+        sync_all()
+        c5_pipe_ms = max_over_ranks(p0.elapsed_time(p1) / KP5)
+        c5_want = expected_keep(idx5p[-1])
+        c5_exact = c5_exact and all_ranks_true(bool(torch.equal(slot5.batch.keep[:n].bool(), c5_want)))
+        sharded.set_dedup_grid(0)
+        dedup_grid5 = pipe5.dedup_grid
+        del c5_want, idx5p, pipe5, slot5
+        torch.cuda.empty_cache()
+        rate5 = n / (c5_pipe_ms * 1e-3)
+        cfg5_info = {"workload": WORKLOADS['cfg5'], "steps": KP5, "ms_per_step": c5_pipe_ms, "value": world * rate5, "unit": UNIT,
+                     "serial_ms_per_step": c5_ms, "dedup_grid_ctas": dedup_grid5,
                      "kernels_ms": {"sample+fingerprint": sample_ms,
                                     "dedup": sum(e[1].elapsed_time(e[2]) for e in c5) / K5},
                      "roofline": {"yardstick_bytes_per_candidate": BYTES_CFG5,
                                   "roofline_candidates_per_s_per_gpu": peak * 1e9 / BYTES_CFG5,
                                   "frac": BYTES_CFG5 * rate5 / 1e9 / peak,
+                                  "frac_serial": BYTES_CFG5 * n / (c5_ms * 1e-3) / 1e9 / peak,
                                   "sampler_frac_of_hbm_peak": BYTES_SAMPLE_FP_COMPULSORY * n / (sample_ms * 1e-3) / 1e9 / peak,
-                                  "note": "per GPU; one stream, CUDA events around each step (the default line's suggest "
-                                          "replaced by ob2_sample with the fused fingerprint)"},
+                                  "note": "per GPU; ms_per_step: 2 K5 batches through CandidatePipeline(fingerprint_in="
+                                          "'sample_only') on two streams, the dedup as a walking grid beside the next "
+                                          "batch's sampler; kernels_ms / serial_ms_per_step: one stream, CUDA events around "
+                                          "each kernel, one-thread-per-entry dedup"},
                      "keep_mask_exact": c5_exact}
-    K5_used = K5 + 1 if K5 else 0
+    K5_used = 3 * K5 + 3 if K5 else 0        # serial: 1 + K5 steps; pipelined: 2 + 2 K5
 
     cfg2_info = None
     if extras and world == 1:

@@ -296,6 +296,16 @@ int ob2_set_insert(ob2_set *set, int64_t n, const uint64_t *fp, void *stream);
  * fingerprints stay in the set.  `scratch` is n u32 of caller scratch. */
 int ob2_set_dedup(ob2_set *set, int64_t n, const uint64_t *fp, const uint32_t *order,
                   uint32_t *scratch, uint8_t *keep, void *stream);
+
+/* How ob2_set_dedup (and the exchange's inbox dedup) lays out its first pass.  0 (default): one thread per
+ * entry -- the fastest when the kernel has the GPU to itself (0.91 ms per 1.25e7 entries).  ctas > 0: a fixed
+ * grid of that many CTAs walks the entries instead.  Alone that is slower (148 CTAs: 1.7 ms, 296: 1.2 ms), but a
+ * small resident grid SHARES the SMs with a kernel running on another stream, where the big grid takes turns
+ * with it: next to the issue-bound sampler of BASELINE.json's config 5 (ob2_sample with the fused fingerprint,
+ * 2.30 ms) the step drops from 3.14 ms (the sum) to 2.48 ms with 148-222 CTAs.  Next to a kernel that already
+ * saturates HBM (ob2_suggest's stores) there is nothing to share and the default stays best.  The verdicts do
+ * not depend on the setting.  The environment variable OB2_DEDUP_GRID sets the initial value of new sets. */
+int ob2_set_set_dedup_grid(ob2_set *set, int32_t ctas);
 /* Same verdicts as ob2_set_dedup, for callers that cannot allocate device
  * memory (no counterpart in the reference, which has no device code at all).
  * Who that is: a plugin inside a process whose framework already owns all of

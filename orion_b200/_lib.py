@@ -79,6 +79,7 @@ SIGNATURES = {
     'ob2_set_destroy': (None, [_vp]),
     'ob2_set_insert': (ctypes.c_int, [_vp, _i64, _vp, _vp]),
     'ob2_set_dedup': (ctypes.c_int, [_vp, _i64, _vp, _vp, _vp, _vp, _vp]),
+    'ob2_set_set_dedup_grid': (ctypes.c_int, [_vp, ctypes.c_int32]),
     'ob2_set_dedup_static': (ctypes.c_int, [_vp, _i64, _vp, _vp, _vp, _vp]),
     'ob2_set_probe': (ctypes.c_int, [_vp, _i64, _vp, _vp, _vp]),
     'ob2_set_rehash': (ctypes.c_int, [_vp, _vp, _vp]),

@@ -48,6 +48,7 @@ struct ob2_set {
     uint64_t n_slots;
     uint64_t upper_bound;  // host-side bound on entries inserted so far
     uint32_t epoch;
+    int32_t dedup_grid;  // 0: one thread per entry; > 0: that many CTAs walk the entries (ob2_set_set_dedup_grid)
 };
 
 namespace {
@@ -181,12 +182,10 @@ __device__ __forceinline__ unsigned long long dedup_tag(uint32_t epoch, uint32_t
 //     the verdict to pass 2 (the entry's index is appended to the list in `scratch`).
 // Only the last class -- the rows that really are duplicated inside the batch -- touches the
 // table a second time.
-__global__ void __launch_bounds__(OB2_BLOCK)
-set_dedup_pass1(SetHeader *hdr, SetSlot *slots, uint64_t mask, int64_t n, const uint64_t *__restrict__ fp,
-                const uint32_t *__restrict__ order, uint32_t epoch, uint32_t *__restrict__ scratch,
-                uint8_t *__restrict__ keep, const uint32_t *__restrict__ lane_cnt, int64_t lane_cap) {
-    int64_t i;
-    const bool valid = entry_index(n, lane_cnt, lane_cap, i);
+__device__ __forceinline__ void dedup_pass1_entry(SetHeader *hdr, SetSlot *slots, uint64_t mask, int64_t i, bool valid,
+                                                  const uint64_t *__restrict__ fp, const uint32_t *__restrict__ order,
+                                                  uint32_t epoch, uint32_t *__restrict__ scratch,
+                                                  uint8_t *__restrict__ keep) {
     bool inserted = false, conflict = false;
     if (valid) {
         uint8_t verdict = 0;
@@ -225,6 +224,42 @@ set_dedup_pass1(SetHeader *hdr, SetSlot *slots, uint64_t mask, int64_t n, const 
         if (conflict) scratch[base + __popc(bidders & ((1u << lane) - 1))] = (uint32_t)i;
     }
     warp_count_add(&hdr->count, inserted);
+}
+
+__global__ void __launch_bounds__(OB2_BLOCK)
+set_dedup_pass1(SetHeader *hdr, SetSlot *slots, uint64_t mask, int64_t n, const uint64_t *__restrict__ fp,
+                const uint32_t *__restrict__ order, uint32_t epoch, uint32_t *__restrict__ scratch,
+                uint8_t *__restrict__ keep, const uint32_t *__restrict__ lane_cnt, int64_t lane_cap) {
+    int64_t i;
+    const bool valid = entry_index(n, lane_cnt, lane_cap, i);
+    dedup_pass1_entry(hdr, slots, mask, i, valid, fp, order, epoch, scratch, keep);
+}
+
+// The same over a small fixed grid that walks the entries (ob2_set_set_dedup_grid): few CTAs, resident for the
+// whole pass.  A grid of one thread per entry takes every SM slot a kernel of another stream frees (the two
+// take turns, their times add up); a walking grid of one or two CTAs per SM leaves the rest to that kernel.
+__global__ void __launch_bounds__(OB2_BLOCK)
+set_dedup_pass1_walk(SetHeader *hdr, SetSlot *slots, uint64_t mask, int64_t n, const uint64_t *__restrict__ fp,
+                     const uint32_t *__restrict__ order, uint32_t epoch, uint32_t *__restrict__ scratch,
+                     uint8_t *__restrict__ keep, const uint32_t *__restrict__ lane_cnt, int64_t lane_cap) {
+    if (lane_cnt == nullptr) {
+        const int64_t stride = (int64_t)gridDim.x * OB2_BLOCK;
+        for (int64_t base = (int64_t)blockIdx.x * OB2_BLOCK; base < n; base += stride) {
+            const int64_t i = base + threadIdx.x;
+            dedup_pass1_entry(hdr, slots, mask, i, i < n, fp, order, epoch, scratch, keep);
+        }
+        return;
+    }
+    // an exchange inbox: n / lane_cap lanes, the first lane_cnt[lane] entries of each are real
+    const int64_t per_lane = (lane_cap + OB2_BLOCK - 1) / OB2_BLOCK, tiles = per_lane * (n / lane_cap);
+    for (int64_t t = blockIdx.x; t < tiles; t += gridDim.x) {
+        const int64_t lane = t / per_lane, first = (t - lane * per_lane) * OB2_BLOCK;
+        int64_t used = (int64_t)__ldg(lane_cnt + lane);
+        used = used < lane_cap ? used : lane_cap;
+        if (first >= used) continue;  // (the whole CTA takes this branch together)
+        const int64_t local = first + threadIdx.x;
+        dedup_pass1_entry(hdr, slots, mask, lane * lane_cap + local, local < used, fp, order, epoch, scratch, keep);
+    }
 }
 
 // Pass 2: only the listed entries -- those that met a key inserted by this same call.  `stamp` holds
@@ -502,6 +537,7 @@ extern "C" int ob2_set_create(void *mem, uint64_t n_slots, void *stream, ob2_set
     set->n_slots = n_slots;
     set->upper_bound = 0;
     set->epoch = 0;
+    set->dedup_grid = getenv("OB2_DEDUP_GRID") ? atoi(getenv("OB2_DEDUP_GRID")) : 0;
     int rc = ob2_check_cuda(cudaGetDevice(&set->device), "cudaGetDevice");
     if (rc == OB2_OK)
         rc = ob2_check_cuda(cudaMemsetAsync(mem, 0, OB2_SET_HEADER_BYTES + n_slots * OB2_SET_SLOT_BYTES,
@@ -557,8 +593,13 @@ int dedup_launch(ob2_set *set, int64_t n, int64_t n_reserve, const uint64_t *fp,
     }
     const uint32_t epoch = ++set->epoch;
     OB2_CUDA(cudaMemsetAsync(&set->header->n_conflicts, 0, sizeof(uint32_t), st));
-    set_dedup_pass1<<<grid1, OB2_BLOCK, 0, st>>>(set->header, set->slots, set->n_slots - 1, n, fp, order, epoch, scratch, keep,
-                                                 lane_cnt, lane_cap);
+    if (set->dedup_grid > 0 && blocks > (unsigned)set->dedup_grid) {
+        set_dedup_pass1_walk<<<(unsigned)set->dedup_grid, OB2_BLOCK, 0, st>>>(set->header, set->slots, set->n_slots - 1, n, fp,
+                                                                              order, epoch, scratch, keep, lane_cnt, lane_cap);
+    } else {
+        set_dedup_pass1<<<grid1, OB2_BLOCK, 0, st>>>(set->header, set->slots, set->n_slots - 1, n, fp, order, epoch, scratch,
+                                                     keep, lane_cnt, lane_cap);
+    }
     rc = ob2_check_cuda(cudaGetLastError(), "set_dedup_pass1 launch");
     if (rc != OB2_OK) return rc;
     const unsigned blocks2 = blocks < 592u ? blocks : 592u;  // the list is ~1 % of the batch: 4 CTAs per SM walk it
@@ -578,6 +619,15 @@ extern "C" int ob2_set_dedup(ob2_set *set, int64_t n, const uint64_t *fp, const 
         return OB2_EINVAL;
     }
     return dedup_launch(set, n, n, fp, order, scratch, keep, static_cast<cudaStream_t>(stream), "ob2_set_dedup");
+}
+
+extern "C" int ob2_set_set_dedup_grid(ob2_set *set, int32_t ctas) {
+    if (set == nullptr || ctas < 0 || ctas > 65535) {
+        ob2_set_error("ob2_set_set_dedup_grid: null set or a CTA count outside [0, 65535]");
+        return OB2_EINVAL;
+    }
+    set->dedup_grid = ctas;
+    return OB2_OK;
 }
 
 // library-internal (ob2_xchg.cu): an inbox of `n` padded lanes holding `n_real` entries

@@ -168,6 +168,9 @@ class ShardedHistory(object):
                 raise _lib.Ob2Error("a history shard refused the batch (on this or another rank): %s"
                                     % (error if error else "see the owning rank"))
 
+    def set_dedup_grid(self, ctas):
+        self.history.set_dedup_grid(ctas)
+
     def check_overflow(self, n):
         """After a run of ``check=False`` calls with batches of ``n``: raise if
         the last one dropped fingerprints."""
@@ -378,6 +381,9 @@ class PeerShardedHistory(object):
         self._owner_side(insert_only=True)
         if check and self._read_status()[self.FULL]:
             self._raise_full()
+
+    def set_dedup_grid(self, ctas):
+        self.history.set_dedup_grid(ctas)
 
     def check_overflow(self):
         """After ``check=False`` calls: raise -- on every rank alike -- if any

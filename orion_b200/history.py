@@ -44,6 +44,12 @@ class TrialHistory(object):
         _lib.check(self.lib.ob2_set_create(table.data_ptr(), n_slots, self._stream(), ctypes.byref(handle)))
         return table, handle
 
+    def set_dedup_grid(self, ctas):
+        """0: the dedup's first pass runs one thread per entry (fastest alone); ctas > 0: that many CTAs
+        walk the entries, so the pass shares the SMs with a kernel on another stream instead of taking
+        turns with it (``ob2_set_set_dedup_grid``; what the config-5 pipeline uses next to its sampler)."""
+        _lib.check(self.lib.ob2_set_set_dedup_grid(self.handle, int(ctas)))
+
     def grow(self, n_slots=None):
         """Move the history into a table of ``n_slots`` (default: twice as many);
         everything stored so far stays a duplicate for future batches."""

@@ -56,7 +56,12 @@ class BatchSlot(object):
 class CandidatePipeline(object):
     """sample+transform -> (reverse || dedup) over a ring of ``depth`` buffer sets."""
 
-    def __init__(self, compiled, history, n, depth=2, timed=False, fingerprint_in='reverse', alias_back=False):
+    #: CTAs of the walking dedup grid next to the issue-bound sampler of config 5 (1.5 per SM: the pass then
+    #: SHARES the SMs with the next batch's sampler -- step 3.14 -> 2.48 ms -- instead of taking turns with it)
+    SAMPLE_ONLY_DEDUP_GRID = 222
+
+    def __init__(self, compiled, history, n, depth=2, timed=False, fingerprint_in='reverse', alias_back=False,
+                 dedup_grid=None):
         # 'reverse': the fingerprints are computed by the (bandwidth-bound) reverse kernel over the rows it
         # writes -- the candidates as handed out; 'sample': by the (issue-bound) sampler over its draws
         # 'suggest': ONE kernel (ob2_suggest) samples, transforms, reverses in registers and fingerprints --
@@ -71,6 +76,9 @@ class CandidatePipeline(object):
         self.n = n
         # a ShardedHistory / PeerShardedHistory is used as is; a bare TrialHistory is wrapped
         self.sharded = history if hasattr(history, 'world') else ShardedHistory(history, device=compiled.device)
+        # next to a kernel that saturates HBM (ob2_suggest's stores, the staged kernels) there is nothing to
+        # share: the dedup keeps its one-thread-per-entry grid, the fastest alone
+        self.dedup_grid = (self.SAMPLE_ONLY_DEDUP_GRID if self.sample_only else 0) if dedup_grid is None else int(dedup_grid)
         assert not alias_back or fingerprint_in == 'suggest', "only the one-kernel suggest can write both rows into one buffer"
         self.slots = [BatchSlot(compiled, n, sample_only=self.sample_only, alias_back=alias_back) for _ in range(depth)]
         dev = compiled.device
@@ -134,6 +142,7 @@ class CandidatePipeline(object):
             if ev:
                 ev[4].record()
             fp = slot.back.fp if self.fp_in_reverse else slot.batch.fp
+            self.sharded.set_dedup_grid(self.dedup_grid)            # (a host-side field; the history may be shared)
             self.sharded.dedup(fp, n, per_rank_n=n, keep=slot.batch.keep, check=False)
             if ev:
                 ev[5].record()

@@ -9,8 +9,9 @@ import torch
 pytestmark = pytest.mark.gpu
 
 
+@pytest.mark.parametrize('dedup_grid', [0, 5])     # 5: the inbox dedup as a walking grid of five CTAs over the lanes
 @pytest.mark.parametrize('world', [1, 2, 8])
-def test_peer_exchange_emulated_on_one_gpu(world):
+def test_peer_exchange_emulated_on_one_gpu(world, dedup_grid):
     from orion_b200 import spaces
     from orion_b200.dist import PeerExchange, bucket_capacity
     from orion_b200.history import TrialHistory
@@ -33,6 +34,8 @@ def test_peer_exchange_emulated_on_one_gpu(world):
         if world > 1:
             x.set_peers(regions)
     shards = [TrialHistory(space, capacity=8 * n) for _ in range(world)]
+    for shard in shards:
+        shard.set_dedup_grid(dedup_grid)
 
     # history load through the exchange (insert_only)
     parts = np.array_split(history_fp, world)
