@@ -66,6 +66,9 @@ def parse_args():
                     help="path: the whole hot path (config 5's dedup with config 3's transform chain on top, the default "
                          "line); cfg5: sample + fingerprint + dedup only (BASELINE.json config 5 as written, 581 B/candidate "
                          "yard-stick); cfg2: Space.sample on real16.  The default line carries cfg5 and cfg2 as sub-objects.")
+    ap.add_argument('--dedup-grid', type=int, default=None,
+                    help="CTAs of the dedup's first pass (ob2_set_set_dedup_grid): 0 = one thread per entry; default: the "
+                         "pipeline's choice (0 next to ob2_suggest, a walking grid next to config 5's sampler)")
     ap.add_argument('--no-extra', action='store_true', help='default workload only: skip the cfg5 / cfg2 / sustained sub-measurements')
     ap.add_argument('--sustain', type=float, default=2.0,
                     help='seconds of back-to-back steps for the sustained-clock sub-measurement (0 = off)')
@@ -734,7 +737,7 @@ def run_b200(args):
     # ones; the draw before the transform is an intermediate.  By default it therefore shares its buffer with
     # the handed-out rows (ob2_suggest, back == cols); --three-buffers materialises it separately as well.
     alias = one_kernel and not args.three_buffers
-    pipe = CandidatePipeline(compiled, sharded, n, depth=2, alias_back=alias,
+    pipe = CandidatePipeline(compiled, sharded, n, depth=2, alias_back=alias, dedup_grid=args.dedup_grid,
                              fingerprint_in='sample_only' if cfg5_main else 'suggest' if one_kernel
                              else 'sample' if args.fp_in_sampler else 'reverse')
     batch, tbatch, back = pipe.slots[0].batch, pipe.slots[0].tbatch, pipe.slots[0].back
@@ -863,6 +866,8 @@ def run_b200(args):
     want = expected_keep(index_dev[W + K - 1])
     keep_mask_exact = all_ranks_true(bool(torch.equal(last_batch.keep[:n].bool(), want)))
     del want
+    dedup_grid_timed = pipe.dedup_grid if pipelined else 0
+    sharded.set_dedup_grid(0)       # the serial passes time every kernel alone: the dedup with its one-thread-per-entry grid
     if pipelined:
         # ---- the same steps (at most 20), one stream, no overlap: clean per-kernel durations for the roofline
         n_ev = KR
@@ -1170,6 +1175,7 @@ def run_b200(args):
         "serial_ms_per_step": serial_ms,
         "kernels_in_timed_region_ms": contended_ms,
         "staged_path": staged_info, "suggest_three_buffers": three_info,
+        "dedup_grid_ctas": dedup_grid_timed,
         "cfg5": cfg5_info, "cfg2": cfg2_info, "sustained": sustained,
         "history_table": {"slots": history.n_slots, "bytes": history.n_slots * 32,
                           "load_at_end": hist_rows1 / float(history.n_slots)},
