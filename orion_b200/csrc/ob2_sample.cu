@@ -763,10 +763,7 @@ int launch_param(const SampleArgs &a, unsigned blocks) {
     memcpy(tbl.s, sp->h_slots, (size_t)sp->n_slots * sizeof(ob2_slot_desc));
     memcpy(tbl.p, sp->h_plan, (size_t)sp->n_slots * sizeof(ob2_slot_plan));
     memcpy(tbl.r, sp->h_runs, (size_t)sp->n_runs * sizeof(ob2_run));
-    // OB2_SAMPLE_SMEM_PAD (bytes, experiments): extra dynamic shared memory per CTA, i.e. fewer resident CTAs of
-    // this kernel per SM, so that the CTAs of a kernel on another stream (the dedup) can be resident beside them
-    static const size_t smem_pad = getenv("OB2_SAMPLE_SMEM_PAD") ? (size_t)atol(getenv("OB2_SAMPLE_SMEM_PAD")) : 0;
-    const size_t smem_p = (size_t)(sp->cdf_len > 0 ? sp->cdf_len : 1) * (sizeof(double) + sizeof(uint32_t)) + smem_pad;
+    const size_t smem_p = (size_t)(sp->cdf_len > 0 ? sp->cdf_len : 1) * (sizeof(double) + sizeof(uint32_t));
     int rc_p = prepare_smem(kern_p, smem_p);
     if (rc_p != OB2_OK) return rc_p;
     kern_p<<<blocks, OB2_BLOCK, smem_p, static_cast<cudaStream_t>(a.stream)>>>(
