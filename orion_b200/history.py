@@ -49,6 +49,7 @@ class TrialHistory(object):
         walk the entries, so the pass shares the SMs with a kernel on another stream instead of taking
         turns with it (``ob2_set_set_dedup_grid``; what the config-5 pipeline uses next to its sampler)."""
         _lib.check(self.lib.ob2_set_set_dedup_grid(self.handle, int(ctas)))
+        self._dedup_grid = int(ctas)
 
     def grow(self, n_slots=None):
         """Move the history into a table of ``n_slots`` (default: twice as many);
@@ -60,6 +61,8 @@ class TrialHistory(object):
         _lib.check(self.lib.ob2_set_rehash(self.handle, handle, self._stream()))
         self.lib.ob2_set_destroy(self.handle)
         self.table, self.handle, self.n_slots = table, handle, n_slots
+        if getattr(self, '_dedup_grid', None) is not None:          # the setting belongs to the history, not to one table
+            self.set_dedup_grid(self._dedup_grid)
 
     def _guarded(self, call):
         """Run a set operation; with ``auto_grow`` a full table is doubled and

@@ -47,3 +47,18 @@ def test_bad_grid_is_refused():
         t.set_dedup_grid(-1)
     with pytest.raises(_lib.Ob2Error):
         t.set_dedup_grid(1 << 20)
+
+
+def test_grid_setting_survives_growth():
+    from orion_b200 import spaces
+    from orion_b200.history import TrialHistory
+    rng = np.random.RandomState(3)
+    n = 50_000
+    fp = torch.from_numpy(rng.randint(1, 2 ** 62, size=(n, 2), dtype=np.int64)).cuda()
+    small = TrialHistory(spaces.rosen2(), capacity=1 << 12, auto_grow=True)     # far too small: grows on the way
+    small.set_dedup_grid(3)
+    keep = small.dedup_fingerprints(fp, n)
+    assert int(keep[:n].sum().item()) == n == len(small)
+    assert small._dedup_grid == 3
+    again = small.dedup_fingerprints(fp, n)
+    assert int(again[:n].sum().item()) == 0
