@@ -65,15 +65,20 @@ def _ask(rng, kind, count):
     return numpy.empty(0)
 
 
-def _evaluate(compiled, base, n):
-    """base: float64 [n_slots][n] -> (host columns, ok[n]) through the kernel."""
-    if n <= _lib.HOST_SAMPLE_MAX:                   # numbers in, kernel, columns + verdicts out: one library call
-        return compiled.sample_from_base_host(base, n)
+def _evaluate_on_device(compiled, base, n):
+    """base: float64 [n_slots][n] -> (device ColumnBatch, ok[n] on the host) through the kernel."""
     ns = round_up(max(n, 1))
     block = numpy.full((compiled.n_slots, ns), 0.5)
     block[:, :n] = base
     batch = compiled.sample_from_uniform(torch.from_numpy(block).to(compiled.device), n, normal_variates=True)
-    ok = batch.mask[:n].cpu().numpy().astype(bool)
+    return batch, batch.mask[:n].cpu().numpy().astype(bool)
+
+
+def _evaluate(compiled, base, n):
+    """base: float64 [n_slots][n] -> (host columns, ok[n]) through the kernel."""
+    if n <= _lib.HOST_SAMPLE_MAX:                   # numbers in, kernel, columns + verdicts out: one library call
+        return compiled.sample_from_base_host(base, n)
+    batch, ok = _evaluate_on_device(compiled, base, n)
     return batch.to_numpy(), ok
 
 
@@ -82,11 +87,12 @@ def _improbable(dim):
                       "Please make interval larger.".format(dim._low, dim._high))
 
 
-def sample_space(dims, compiled, n, rng):
+def sample_space(dims, compiled, n, rng, on_device=False):
     """All dimensions in ONE launch, for the (overwhelmingly common) call in which no value is
     rejected: dimension-major stream, exactly ``[dim.sample(n, rng) for dim in space.values()]``.
-    Returns the host columns, or None -- with ``rng`` put back where it was -- when some row missed
-    its bounds and the caller has to go dimension by dimension."""
+    Returns the host columns (``on_device``: the device ColumnBatch), or None -- with ``rng`` put
+    back where it was -- when some row missed its bounds and the caller has to go dimension by
+    dimension."""
     kinds = stream_kinds(compiled)
     state = rng.get_state()
     base = numpy.full((compiled.n_slots, n), 0.5)
@@ -109,7 +115,7 @@ def sample_space(dims, compiled, n, rng):
                     base[first:first + width] = numbers[pos:pos + n * width].reshape(n, width).T
                     pos += n * width
         d = end
-    cols, ok = _evaluate(compiled, base, n)
+    cols, ok = (_evaluate_on_device if on_device else _evaluate)(compiled, base, n)
     rejecting = [d.type in ('real', 'integer') for d in dims]
     if ok.all() or not any(rejecting):
         return cols
@@ -126,6 +132,18 @@ def space_columns(dims, compiled, solo, n, rng):
         for dim in dims:
             cols.extend(sample_dimension(dim, solo(dim), n, rng))
     return cols
+
+
+def space_batch(dims, compiled, solo, n, rng):
+    """The same as a device ColumnBatch (``Space.sample_columns(..., reference_stream=True)``): the values of
+    the reference's seeded ``Space.sample`` in the tensor interface.  The host still asks numpy for every
+    number (a few ns each), so this is for reproducing a reference run, not for throughput."""
+    from .columns import ColumnBatch
+    batch = sample_space(dims, compiled, n, rng, on_device=True)
+    if batch is None:
+        batch = ColumnBatch.from_numpy(compiled, space_columns(dims, compiled, solo, n, rng))
+        batch.mask = torch.ones(batch.n_stride, dtype=torch.uint8, device=compiled.device)   # accepted rows only
+    return batch
 
 
 def sample_dimension(dim, compiled, n, seed):

@@ -338,10 +338,24 @@ class Space(OrderedDict):
     def compiled(self, requirement=None, quantize='round', philox_rounds=10):
         return compile_space(self, requirement, quantize, philox_rounds=philox_rounds)
 
-    def sample_columns(self, n_samples=1, seed=None, base_index=0, with_fingerprint=False, check=True):
+    def sample_columns(self, n_samples=1, seed=None, base_index=0, with_fingerprint=False, check=True,
+                       reference_stream=False):
         """Device-resident draw: returns a :class:`ColumnBatch` whose ``mask``
         is the fused ``point in space``.  ``check=False`` skips the
-        synchronising read of the rejection counters."""
+        synchronising read of the rejection counters.  ``reference_stream``: the
+        values of the reference's ``Space.sample(n_samples, seed)`` -- its MT19937
+        stream is what the kernel is fed (:mod:`.mt_stream`; the host asks numpy for
+        every number, so this reproduces a reference run rather than racing it)."""
+        if reference_stream:
+            compiled = self.compiled()
+            rng = check_random_state(seed)
+            if not mt_stream.reproducible(compiled, rng):
+                raise NotImplementedError("this space or seed cannot be drawn from the reference's stream "
+                                          "(a prior scipy draws with another numpy generator, or a Generator seed)")
+            batch = mt_stream.space_batch(list(self.values()), compiled, _solo_compiled, n_samples, rng)
+            if with_fingerprint:
+                compiled.fingerprint(batch)
+            return batch
         batch = self.compiled().sample(n_samples, philox_key(seed), base_index=base_index,
                                        with_mask=True, with_fingerprint=with_fingerprint)
         if check:

@@ -155,6 +155,28 @@ def test_random_spaces_sample_the_reference_s_points(case):
         assert same_state(rng, ref_rng)
 
 
+@pytest.mark.parametrize('which', [0, 1])
+def test_sample_columns_on_the_reference_stream(which):
+    """The tensor interface fed the reference's stream: the columns of the reference's seeded Space.sample
+    (space 1 has user bounds: the rejections take the dimension-by-dimension path)."""
+    ref_space, space = spaces(ref_classes())[which], spaces(mirror())[which]
+    n = 3000
+    ref_rng, rng = np.random.RandomState(8), np.random.RandomState(8)
+    expect = ref_space.sample(n, ref_rng)
+    batch = space.sample_columns(n, rng, reference_stream=True, with_fingerprint=True)
+    assert batch.buf.is_cuda and batch.n == n and bool(batch.mask[:n].all().item()) and batch.fp is not None
+    got = space.rows_from_columns(batch.to_numpy(), n)
+    for grow, erow in zip(got, expect):
+        assert equal_values(grow[0], erow[0], exact=(which == 1))
+        assert all(equal_values(g, e) for g, e in zip(grow[1:], erow[1:]))
+    assert same_state(rng, ref_rng)
+    from orion_b200.space import Real, Space
+    other = Space()
+    other.register(Real('e', 'expon'))
+    with pytest.raises(NotImplementedError):
+        other.sample_columns(4, 1, reference_stream=True)
+
+
 def test_transformed_space_sample_is_transform_of_the_reference_s_points():
     from orion_b200.transformer import build_required_space
     ref_space, space = spaces(ref_classes())[1], spaces(mirror())[1]
