@@ -1024,7 +1024,6 @@ def run_b200(args):
         # Survivors only cross PCIe: after dedup the kept rows are gathered into a dense block on
         # the device (ob2_compact) and each column's first n_kept elements are copied to pinned
         # host memory.  Two buffer sets: compaction and copies of step j overlap step j+1.
-        from orion_b200.columns import _SIZE
         ns = batch.n_stride
         # ... in the wire layout: Integer / Categorical columns at their narrowest lossless width
         # (mixed64: 288 instead of 448 bytes per candidate)
