@@ -90,6 +90,20 @@ def _index_of(dim, value):
         return -1
 
 
+_MINUS_ONES = __import__('itertools').repeat(-1)
+
+
+def _layout_of(space):
+    """``([dim.shape ...], [dim.type ...])`` of a space, remembered on it (scipy parses the prior's arguments
+    for every ``shape`` of a reference Dimension; the key notices a dimension registered since)."""
+    key = tuple(map(id, space.values()))
+    hit = space.__dict__.get('_ob2_layout')
+    if hit is None or hit[0] != key:
+        dims = list(space.values())
+        hit = space.__dict__['_ob2_layout'] = (key, [tuple(d.shape) for d in dims], [d.type for d in dims])
+    return hit[1], hit[2]
+
+
 def _category_lookup(dim):
     """category -> first index with an equal category (what ``tuple.index`` finds: 2 == 2.0, '2' != 2), cached on
     the dimension; None when some category is unhashable."""
@@ -240,8 +254,13 @@ class Dimension(object):
 
     @property
     def shape(self):
-        size = self.prior._parse_args_rvs(*self._args, size=self._shape, **self._kwargs)[3]  # pylint:disable=protected-access
-        return tuple(int(s) for s in size)
+        # (scipy's argument parsing costs ~8 us and every conversion between points and columns asks
+        # for the shape of every dimension: parsed once -- prior, arguments and shape are fixed at construction)
+        shape = self.__dict__.get('_shape_parsed')
+        if shape is None:
+            size = self.prior._parse_args_rvs(*self._args, size=self._shape, **self._kwargs)[3]  # pylint:disable=protected-access
+            shape = self.__dict__['_shape_parsed'] = tuple(int(s) for s in size)
+        return shape
 
 
 class Real(Dimension):
@@ -397,50 +416,57 @@ class Space(OrderedDict):
         """Host columns -> the reference's list of tuples."""
         per_dim = []
         s = 0
-        for dim in self.values():
-            if dim.shape == ():                 # a whole column at once (numpy scalars, like scipy's rvs)
+        shapes, kinds = _layout_of(self)            # (parsed once per space; `self` may be a reference Space)
+        for dim, shape, kind in zip(self.values(), shapes, kinds):
+            if shape == ():                     # a whole column at once (numpy scalars, like scipy's rvs)
                 col = host_cols[s][:n]
-                if dim.type == 'categorical':
+                if kind == 'categorical':
                     cats = dim.categories
                     per_dim.append([cats[c] for c in col.tolist()])
                 else:
                     per_dim.append(list(col))
                 s += 1
                 continue
-            k = int(numpy.prod(dim.shape, dtype=numpy.int64))
+            k = int(numpy.prod(shape, dtype=numpy.int64))
             cols = host_cols[s:s + k]
             per_dim.append([_from_columns(dim, cols, i) for i in range(n)])
             s += k
         return list(zip(*per_dim))
 
     @staticmethod
-    def _columns_of_scalar_rows(dims, points, n):
+    def _columns_of_scalar_rows(dims, points, n, layout=None):
         """The common case -- every dimension scalar, every point a full row of
         plain scalars -- column by column; None when anything is unusual (the
         general loop then decides row by row)."""
-        if any(d.shape != () for d in dims) or any(len(p) != len(dims) for p in points):
+        shapes, kinds = layout if layout is not None else ([d.shape for d in dims], [d.type for d in dims])
+        width = len(dims)
+        if any(shapes) or any(len(p) != width for p in points):    # (a non-scalar shape is a non-empty tuple)
             return None
-        cols = []
         by_dim = list(zip(*points)) if n else [()] * len(dims)     # the transpose, done in C
-        for dim, vals in zip(dims, by_dim):
-            if dim.type == 'categorical':
+        cols = [None] * len(dims)
+        numeric = [j for j, kind in enumerate(kinds) if kind != 'categorical']
+        if numeric:
+            # ONE conversion for all numeric dimensions.  A str among the values makes numpy pick a string
+            # dtype, None an object one, a list a ragged error: the general loop then raises the reference's
+            # TypeError or rejects the row
+            try:
+                block = numpy.asarray([by_dim[j] for j in numeric]) if n else numpy.empty((len(numeric), 0))
+            except ValueError:
+                return None
+            if block.dtype.kind not in 'fiub' or block.shape != (len(numeric), n):
+                return None
+            block = block.astype(numpy.float64, copy=False)
+            for row, j in enumerate(numeric):
+                cols[j] = block[row]
+        for j, (dim, kind) in enumerate(zip(dims, kinds)):
+            if kind == 'categorical':
                 lookup = _category_lookup(dim)
                 if lookup is None:
                     return None
                 try:
-                    cols.append(numpy.fromiter((lookup.get(v, -1) for v in vals), dtype=numpy.int32, count=n))
+                    cols[j] = numpy.fromiter(map(lookup.get, by_dim[j], _MINUS_ONES), dtype=numpy.int32, count=n)
                 except TypeError:                                    # an unhashable value (list, ndarray)
                     return None
-            else:
-                # (a str among the values makes numpy pick a string dtype, None an object one: the
-                # general loop then raises the reference's TypeError or rejects the row)
-                try:
-                    probe = numpy.asarray(vals) if n else numpy.empty(0)
-                except ValueError:                                   # ragged: a mis-shaped value among them
-                    return None
-                if probe.dtype.kind not in 'fiub' or probe.shape != (n,):
-                    return None
-                cols.append(probe.astype(numpy.float64, copy=False))
         return cols
 
     def columns_from_rows(self, points):
@@ -449,7 +475,7 @@ class Space(OrderedDict):
         travel as float64 so the device can check integrality."""
         dims = list(self.values())
         n = len(points)
-        fast = Space._columns_of_scalar_rows(dims, points, n)      # (self may be a reference Space)
+        fast = Space._columns_of_scalar_rows(dims, points, n, _layout_of(self))     # (self may be a reference Space)
         if fast is not None:
             return fast, numpy.ones(n, dtype=bool)
         widths = [int(numpy.prod(d.shape, dtype=numpy.int64)) if d.shape else 1 for d in dims]
