@@ -91,7 +91,14 @@ enum { OB2_DIST_UNIFORM = 0, OB2_DIST_RECIPROCAL = 1, OB2_DIST_NORM = 2, OB2_DIS
         * the pmf from the lower end of the support.  VONMISES: p0 = kappa (< 50), p1 = 1 / (2 pi i0e(kappa));
         * safeguarded Newton steps on the cdf series scipy itself sums (Hill's algorithm 518). */
        OB2_DIST_F = 63, OB2_DIST_LOGGAMMA = 64, OB2_DIST_NBINOM = 65, OB2_DIST_HYPERGEOM = 66, OB2_DIST_VONMISES = 67,
-       OB2_DIST_LAST = 67 };
+       /* a third batch, again scipy's own _ppf formulas with the shape parameters in scipy's order (a third one in
+        * hk[3]).  GENGAMMA: p0 = a, p1 = lgamma(a), hk[3] = bits of c.  PLANCK / DLAPLACE / BOLTZMANN: scipy's
+        * ceil-then-correct forms, operation for operation (bernoulli = BINOM with n = 1). */
+       OB2_DIST_JOHNSONSB = 68, OB2_DIST_JOHNSONSU = 69, OB2_DIST_FATIGUELIFE = 70, OB2_DIST_POWERNORM = 71,
+       OB2_DIST_POWERLOGNORM = 72, OB2_DIST_GENGAMMA = 73, OB2_DIST_KAPPA4 = 74, OB2_DIST_LAPLACE_ASYMMETRIC = 75,
+       OB2_DIST_TRAPEZOID = 76, OB2_DIST_TRUNCPARETO = 77, OB2_DIST_TRUNCWEIBULL_MIN = 78, OB2_DIST_SKEWCAUCHY = 79,
+       OB2_DIST_PLANCK = 80, OB2_DIST_DLAPLACE = 81, OB2_DIST_BOLTZMANN = 82,
+       OB2_DIST_LAST = 82 };
 
 /* per-slot transformer (build_required_space table) */
 enum {

@@ -245,7 +245,11 @@ CLOSED_FORM_PRIORS = ('expon', 'lognorm', 'logistic', 'laplace', 'gumbel_r', 'we
                       'levy_l', 'weibull_max', 'rdist', 'semicircular', 'dgamma', 'gennorm', 'moyal', 'wrapcauchy',
                       # the judge's list: f, loggamma; nbinom, hypergeom (rv_discrete); vonmises has no
                       # _ppf of its own -- scipy inverts its cdf numerically
-                      'f', 'loggamma', 'nbinom', 'hypergeom', 'vonmises')
+                      'f', 'loggamma', 'nbinom', 'hypergeom', 'vonmises',
+                      # a third batch of closed forms
+                      'johnsonsb', 'johnsonsu', 'fatiguelife', 'powernorm', 'powerlognorm', 'gengamma', 'kappa4',
+                      'laplace_asymmetric', 'trapezoid', 'truncpareto', 'truncweibull_min', 'skewcauchy',
+                      'bernoulli', 'planck', 'dlaplace', 'boltzmann')
 
 
 def _draw(spec: DimSpec, u: np.ndarray) -> np.ndarray:

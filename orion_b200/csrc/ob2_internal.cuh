@@ -703,6 +703,60 @@ static __device__ __noinline__ double draw_extended(int dist, double p0, double 
         }
         case OB2_DIST_VONMISES:  // p0 = kappa, p1 = 1 / (2 pi i0e(kappa))
             return vonmises_ppf(p0, p1, u);
+        case OB2_DIST_JOHNSONSB:  // expit((ndtri(u) - a) / b)
+            return 1.0 / (1.0 + exp(-(1.0 / p1 * (normcdfinv(u) - p0))));
+        case OB2_DIST_JOHNSONSU:
+            return sinh((normcdfinv(u) - p0) / p1);
+        case OB2_DIST_FATIGUELIFE: {
+            const double t = p0 * normcdfinv(u), r = t + sqrt(t * t + 4.0);
+            return 0.25 * r * r;
+        }
+        case OB2_DIST_POWERNORM:
+            return -normcdfinv(pow(1.0 - u, 1.0 / p0));
+        case OB2_DIST_POWERLOGNORM:  // c, s
+            return exp(-normcdfinv(pow(1.0 - u, 1.0 / p0)) * p1);
+        case OB2_DIST_GENGAMMA:  // p0 = a, p1 = lgamma(a), p2 = c
+            return pow(p2 > 0.0 ? gamma_ppf(p0, p1, u) : gamma_isf(p0, p1, u), 1.0 / p2);
+        case OB2_DIST_KAPPA4: {  // h, k
+            if (p0 != 0.0 && p1 != 0.0) return 1.0 / p1 * (1.0 - pow((1.0 - pow(u, p0)) / p0, p1));
+            if (p0 == 0.0 && p1 != 0.0) return 1.0 / p1 * (1.0 - pow(-log(u), p1));
+            if (p0 != 0.0) return -log1p(-pow(u, p0)) + log(p0);
+            return -log(-log(u));
+        }
+        case OB2_DIST_LAPLACE_ASYMMETRIC: {  // kappa
+            const double kapinv = 1.0 / p0, both = p0 + kapinv;
+            return u >= p0 / both ? -log((1.0 - u) * both * p0) * kapinv : log(u * both / p0) * p0;
+        }
+        case OB2_DIST_TRAPEZOID: {  // c, d
+            const double w = p1 - p0 + 1.0, qc = p0 / w, qd = (p0 + 2.0 * (p1 - p0)) / w;
+            if (u < qc) return sqrt(u * p0 * (1.0 + p1 - p0));
+            if (u <= qd) return 0.5 * u * (1.0 + p1 - p0) + 0.5 * p0;
+            return 1.0 - sqrt((1.0 - u) * w * (1.0 - p1));
+        }
+        case OB2_DIST_TRUNCPARETO:  // b, c
+            return pow(1.0 - (1.0 - 1.0 / pow(p1, p0)) * u, -1.0 / p0);
+        case OB2_DIST_TRUNCWEIBULL_MIN:  // c, a, b
+            return pow(-log((1.0 - u) * exp(-pow(p1, p0)) + u * exp(-pow(p2, p0))), 1.0 / p0);
+        case OB2_DIST_SKEWCAUCHY: {  // a
+            const double s = u < 0.5 * (1.0 - p0) ? 1.0 - p0 : 1.0 + p0, x = (u - 0.5 * (1.0 - p0)) / s;
+            return sinpi(x) / cospi(x) * s;
+        }
+        case OB2_DIST_PLANCK: {  // lambda
+            const double vals = ceil(-1.0 / p0 * log1p(-u) - 1.0), vals1 = fmax(vals - 1.0, 0.0);
+            return -expm1(-p0 * (floor(vals1) + 1.0)) >= u ? vals1 : vals;
+        }
+        case OB2_DIST_DLAPLACE: {  // a
+            const double c = 1.0 + exp(p0);
+            const double vals = ceil(u < 1.0 / (1.0 + exp(-p0)) ? log(u * c) / p0 - 1.0 : -log((1.0 - u) * c) / p0);
+            const double k = floor(vals - 1.0);
+            const double cdf = k >= 0.0 ? 1.0 - exp(-p0 * k) / (exp(p0) + 1.0) : exp(p0 * (k + 1.0)) / (exp(p0) + 1.0);
+            return cdf >= u ? vals - 1.0 : vals;
+        }
+        case OB2_DIST_BOLTZMANN: {  // lambda, N
+            const double norm = 1.0 - exp(-p0 * p1);
+            const double vals = ceil(-1.0 / p0 * log(1.0 - u * norm) - 1.0), vals1 = fmax(vals - 1.0, 0.0);
+            return (1.0 - exp(-p0 * (floor(vals1) + 1.0))) / norm >= u ? vals1 : vals;
+        }
         default: {  // OB2_DIST_POISSON, p0 = mu, p1 = exp(-mu): smallest k with cdf(k) >= u
             double k = 0.0, pmf = p1, cdf = p1;
             const double k_max = p0 + 40.0 * sqrt(p0) + 60.0;  // the tail beyond is < 1e-300

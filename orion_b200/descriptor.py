@@ -71,6 +71,9 @@ _CLOSED_FORM_2 = {
     'halflogistic': (42, 0), 'gibrat': (46, 0), 'genextreme': (47, 1), 'kappa3': (48, 1), 'dweibull': (49, 1),
     'anglit': (50, 0), 'exponweib': (51, 2), 'mielke': (52, 2), 'genhalflogistic': (53, 1), 'tukeylambda': (54, 1),
     'levy': (55, 0), 'levy_l': (56, 0), 'weibull_max': (57, 1), 'moyal': (61, 0), 'wrapcauchy': (62, 1),
+    'johnsonsb': (68, 2), 'johnsonsu': (69, 2), 'fatiguelife': (70, 1), 'powernorm': (71, 1), 'powerlognorm': (72, 2),
+    'kappa4': (74, 2), 'laplace_asymmetric': (75, 1), 'trapezoid': (76, 2), 'truncpareto': (77, 2), 'truncweibull_min': (78, 3),
+    'skewcauchy': (79, 1), 'planck': (80, 1), 'dlaplace': (81, 1), 'boltzmann': (82, 2),
 }
 # ... and those that go through the incomplete gamma inverse: name -> (dist code, a as a function of the shape parameters)
 _GAMMA_BASED = {
@@ -114,8 +117,16 @@ def _prior_params(dim):
         p1 = reciprocal_sign / p0 if (n_shape and reciprocal_sign) else 0.0
         return code, p0, p1, loc, scale
     if name in _CLOSED_FORM_2 and len(args) == _CLOSED_FORM_2[name][1]:
-        shapes = [float(a) for a in args] + [0.0, 0.0]
-        return _CLOSED_FORM_2[name][0], shapes[0], shapes[1], loc, scale
+        shapes = [float(a) for a in args] + [0.0, 0.0, 0.0]
+        return _CLOSED_FORM_2[name][0], shapes[0], shapes[1], loc, scale, shapes[2]
+    if name == 'gengamma' and len(args) == 2 and float(args[1]) != 0.0:
+        from scipy.special import gammaln
+        a = float(args[0])
+        return 73, a, float(gammaln(a)), loc, scale, float(args[1])
+    if name == 'bernoulli' and len(args) == 1:          # binom(1, p)
+        p = float(args[0])
+        if p < 1:
+            return 25, 1.0, p, loc, scale, 1.0 - p
     if name == 'fisk' and len(args) == 1:               # burr(c, 1)
         return 29, float(args[0]), 1.0, loc, scale
     if name in _GAMMA_BASED:
@@ -496,7 +507,7 @@ class CompiledSpace(object):
         if self.unsamplable is not None:
             raise NotImplementedError(
                 "Dimension '{}': prior '{}' has no device inverse CDF yet (supported: uniform, reciprocal / "
-                "loguniform, norm and the sixty-seven further scipy priors INTEGRATION.md lists). "
+                "loguniform, norm and the eighty-three further scipy priors INTEGRATION.md lists). "
                 "There is no CPU fallback.".format(*self.unsamplable))
 
     def sample_from_uniform(self, U, n=None, with_fingerprint=False, normal_variates=False):

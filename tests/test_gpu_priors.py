@@ -287,3 +287,68 @@ def test_named_priors_philox_marginals():
             for k, c in zip(ks, counts):
                 expect = dist.pmf(k) / mass
                 assert abs(c / len(x) - expect) < 5 * np.sqrt(expect / n) + 1e-4, (d['name'], k, c / len(x), expect)
+
+
+# ---- a third batch of closed forms (ob2.h OB2_DIST_JOHNSONSB .. OB2_DIST_BOLTZMANN)
+PRIORS_4 = [
+    dict(name='jb', kind='real', prior='johnsonsb', args=[0.5, 1.5]),
+    dict(name='ju', kind='real', prior='johnsonsu', args=[-0.5, 2.0, 1.0, 3.0]),
+    dict(name='fl', kind='real', prior='fatiguelife', args=[0.7]),
+    dict(name='pn', kind='real', prior='powernorm', args=[2.5]),
+    dict(name='pl', kind='real', prior='powerlognorm', args=[2.0, 0.5]),
+    dict(name='gg', kind='real', prior='gengamma', args=[2.0, 1.5]),
+    dict(name='gg2', kind='real', prior='gengamma', args=[2.0, -1.5]),
+    dict(name='k4', kind='real', prior='kappa4', args=[0.5, 0.3]),
+    dict(name='k4b', kind='real', prior='kappa4', args=[0.0, 0.3]),
+    dict(name='k4c', kind='real', prior='kappa4', args=[0.5, 0.0]),
+    dict(name='k4d', kind='real', prior='kappa4', args=[0.0, 0.0]),
+    dict(name='la', kind='real', prior='laplace_asymmetric', args=[1.7]),
+    dict(name='tz', kind='real', prior='trapezoid', args=[0.2, 0.7]),
+    dict(name='tp', kind='real', prior='truncpareto', args=[2.0, 5.0]),
+    dict(name='tw', kind='real', prior='truncweibull_min', args=[1.5, 0.5, 3.0]),
+    dict(name='sc', kind='real', prior='skewcauchy', args=[0.3]),
+    dict(name='pk', kind='integer', prior='planck', args=[0.5]),
+    dict(name='dl', kind='integer', prior='dlaplace', args=[0.8]),
+    dict(name='bz', kind='integer', prior='boltzmann', args=[1.4, 19]),
+    dict(name='be', kind='integer', prior='bernoulli', args=[0.3]),       # (the half-open interval leaves only 0)
+]
+
+
+def test_third_batch_from_uniform_matches_scipy():
+    specs = gu.specs_from_json(PRIORS_4)
+    space = gu.product_space(PRIORS_4)
+    rng = np.random.RandomState(6)
+    n = 4096
+    U = rng.random_sample((len(specs), n))
+    U[:, :4] = [1e-9, 1e-4, 0.5, 1 - 1e-6]
+    batch = space.compiled().sample_from_uniform(torch.from_numpy(U).cuda())
+    got = batch.to_numpy()
+    want, ok = so.sample_from_uniform(specs, U)
+    for j, d in enumerate(PRIORS_4):
+        if d['kind'] == 'real':
+            np.testing.assert_allclose(got[j], want[j], rtol=1e-6, atol=1e-12, err_msg=d['name'])
+        else:
+            assert got[j].dtype == np.int64 and int((got[j] != want[j]).sum()) <= 1, d['name']
+    assert int((batch.mask.cpu().numpy().astype(bool) != ok).sum()) <= 2
+
+
+def test_third_batch_philox_marginals():
+    dims = PRIORS_4[:-1]
+    space = gu.product_space(dims)
+    n = 200_000
+    cols = space.compiled().sample(n, 999).to_numpy()
+    for d, x in zip(dims, cols):
+        dist = getattr(stats, d['prior'])(*d['args'])
+        if d['kind'] == 'real':
+            p = stats.kstest(x, dist.cdf).pvalue
+            assert p > 1e-4, '%s: p = %g' % (d['name'], p)
+        else:
+            lo, hi = space[d['name']].interval()
+            x = x[(x >= lo) & (x < hi)]
+            assert len(x) > n - 50
+            ks, counts = np.unique(x, return_counts=True)
+            inside = np.arange(max(lo, max(dist.support()[0], ks.min())), min(hi, ks.max() + 1))
+            mass = dist.pmf(inside).sum()
+            for k, c in zip(ks, counts):
+                expect = dist.pmf(k) / mass
+                assert abs(c / len(x) - expect) < 5 * np.sqrt(expect / n) + 2e-4, (d['name'], k, c / len(x), expect)
