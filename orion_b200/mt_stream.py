@@ -18,8 +18,10 @@ The further priors scipy draws the same generic way (``fisk``, ``genpareto``, ``
 ... : no ``_rvs`` of their own) are fed uniforms too and come out within the device inverse CDF's
 1e-6 (typically 1e-15) of the reference's values.
 
-Priors whose scipy ``_rvs`` uses another numpy generator (``expon`` -> ``standard_exponential``,
-``gamma``, ``poisson`` ...) and ``numpy.random.Generator`` seeds cannot be reproduced this way;
+So are ``expon``, ``logistic`` and ``laplace``, whose numpy generators are that same inverse CDF of one uniform.
+
+Priors whose scipy ``_rvs`` uses another numpy generator (``gamma`` -> ``standard_gamma``, ``beta``,
+``poisson``, ``lognorm`` ...) and ``numpy.random.Generator`` seeds cannot be reproduced this way;
 :func:`reproducible` says no for them and the callers keep the Philox stream of the tensor path.
 """
 import numpy
@@ -39,13 +41,19 @@ _KIND_OF_DIST = {_lib.DIST_UNIFORM: UNIFORM, _lib.DIST_RECIPROCAL: UNIFORM, _lib
                  None: UNIFORM}                  # Categorical: RandomState.choice -> random_sample
 
 
+# priors with an ``_rvs`` of their own that still is ONE uniform per value put through the inverse CDF: numpy's
+# legacy standard_exponential is -log(1 - u), logistic log(u / (1 - u)), laplace -log(2 - 2u) | log(2u)
+# (numpy/random/src/legacy/legacy-distributions.c) -- checked against RandomState in tests/test_mt_stream.py
+_UNIFORM_FED = (5, 7, 8)        # OB2_DIST_EXPON, OB2_DIST_LOGISTIC, OB2_DIST_LAPLACE
+
+
 def stream_kinds(compiled):
     """Which RandomState method feeds each dimension of ``compiled``, or None when some prior's
     ``_rvs`` is not a function of ``random_sample`` / ``standard_normal`` numbers."""
     kinds = []
     for dist, by_inverse_cdf in zip(compiled.dim_dists, compiled.dim_generic_rvs):
         kind = _KIND_OF_DIST.get(dist)
-        if kind is None and dist is not None and dist > _lib.DIST_NONE and by_inverse_cdf:
+        if kind is None and dist is not None and dist > _lib.DIST_NONE and (by_inverse_cdf or dist in _UNIFORM_FED):
             kind = UNIFORM                          # a further prior scipy draws as _ppf(uniform()): the device's _ppf
         if kind is None:
             return None

@@ -172,7 +172,7 @@ def test_sample_columns_on_the_reference_stream(which):
     assert same_state(rng, ref_rng)
     from orion_b200.space import Real, Space
     other = Space()
-    other.register(Real('e', 'expon'))
+    other.register(Real('e', 'gamma', 2.0))
     with pytest.raises(NotImplementedError):
         other.sample_columns(4, 1, reference_stream=True)
 

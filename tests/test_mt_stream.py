@@ -101,10 +101,13 @@ CASES = [
     ('real', ('genpareto', 0.1, 1.0, 2.0), {'shape': 2}),
     ('integer', ('lomax', 2.0, 0, 10), {'high': 40}),
     ('real', ('invgamma', 3.0), {'low': 0.1, 'high': 2.0}),
+    ('real', ('expon', 0.0, 2.0), {}),                                        # numpy generators of their own that are one uniform
+    ('real', ('laplace',), {'shape': 2}),                                     # through the inverse CDF
+    ('integer', ('logistic', 0, 5), {}),
 ]
 
 
-FURTHER = ('fisk', 'genpareto', 'lomax', 'invgamma')
+FURTHER = ('fisk', 'genpareto', 'lomax', 'invgamma', 'expon', 'laplace', 'logistic')
 
 
 def make(module, kind, args, kwargs, name='yolo'):
@@ -302,10 +305,28 @@ def test_reference_known_answers_on_this_path():
 def test_which_priors_are_reproducible():
     rng = np.random.RandomState(0)
     assert mt_stream.reproducible(HostCompiled([mirror.Real('x', 'uniform', 0, 1)]), rng)
-    assert not mt_stream.reproducible(HostCompiled([mirror.Real('x', 'expon')]), rng)         # standard_exponential
+    assert mt_stream.reproducible(HostCompiled([mirror.Real('x', 'expon')]), rng)             # standard_exponential = -log(1 - u)
+    assert not mt_stream.reproducible(HostCompiled([mirror.Real('x', 'gamma', 2.0)]), rng)    # standard_gamma
     assert mt_stream.reproducible(HostCompiled([mirror.Real('x', 'fisk', 3.0)]), rng)         # _ppf(uniform())
     assert not mt_stream.reproducible(HostCompiled([mirror.Real('x', 'maxwell')]), rng)       # chi._rvs
     assert not mt_stream.reproducible(HostCompiled([mirror.Real('x', 'uniform', 0, 1)]), np.random.default_rng(0))
+
+
+def test_numpy_generators_that_are_one_uniform_through_the_inverse_cdf():
+    """What mt_stream._UNIFORM_FED relies on, against numpy's legacy RandomState: the same number of uniforms
+    consumed, the same values to the last ulp or two (numpy's vectorised log and the C library's differ there)."""
+    def same(x, y):
+        return np.allclose(x, y, rtol=4.5e-16, atol=0)
+    a, b = np.random.RandomState(3), np.random.RandomState(3)
+    u = b.random_sample(1000)
+    assert same(a.standard_exponential(1000), -np.log(1 - u)) and a.random_sample() == b.random_sample()
+    a, b = np.random.RandomState(4), np.random.RandomState(4)
+    u = b.random_sample(1000)
+    assert same(a.logistic(size=1000), np.log(u / (1 - u))) and a.random_sample() == b.random_sample()
+    a, b = np.random.RandomState(5), np.random.RandomState(5)
+    u = b.random_sample(1000)
+    assert same(a.laplace(0, 1, 1000), np.where(u >= 0.5, -np.log(2 - u - u), np.log(u + u)))
+    assert a.random_sample() == b.random_sample()
 
 
 def test_replay_of_attempts():
